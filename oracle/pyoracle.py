@@ -1,0 +1,250 @@
+"""TEST INFRASTRUCTURE ONLY — ctypes bindings for the CPU oracle.
+
+`Oracle`  wraps oracle/liboracle.so  (plain-C restatement, polar_oracle.c; kind "port").
+`Ref`     wraps oracle/_ref/libpolar_ref.so (the unmodified reference compiled in place by
+          oracle/Makefile; kind "reference").  Both expose the same methods so a test can
+          run either against the CUDA path.
+
+Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs may
+import this module.  The product package never does.
+"""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ORACLE_SO = os.path.join(HERE, "liboracle.so")
+REF_SO = os.path.join(HERE, "_ref", "libpolar_ref.so")
+
+_ip = np.ctypeslib.ndpointer(dtype=np.int32, flags="C_CONTIGUOUS")
+_dp = np.ctypeslib.ndpointer(dtype=np.float64, flags="C_CONTIGUOUS")
+
+
+def build(force=False):
+    """Compile liboracle.so (always possible) and oracle/_ref (only where /root/reference exists)."""
+    need = force or not os.path.exists(ORACLE_SO) or (
+        os.path.getmtime(ORACLE_SO) < os.path.getmtime(os.path.join(HERE, "polar_oracle.c")))
+    if need or (os.path.isdir("/root/reference/PolarCodes") and not os.path.exists(REF_SO)):
+        subprocess.check_call(["make", "-C", HERE, "all"], stdout=subprocess.DEVNULL)
+
+
+def _i32(a):
+    return np.ascontiguousarray(a, dtype=np.int32)
+
+
+def _f64(a):
+    return np.ascontiguousarray(a, dtype=np.float64)
+
+
+class _Base:
+    kind = "?"
+
+    def make_code(self, n, k, crc, snr_db, zcomputer=2):
+        """(sigma, info indexes, frozen mask) exactly as PolarCodes.cpp:123-128."""
+        sigma = self.sigma(n, k, snr_db)
+        inf = self.inf_indexes_bec(n, k) if zcomputer == 1 else self.inf_indexes_awgn(n, k + crc, sigma)
+        return sigma, inf, self.frozen_mask(n, inf)
+
+
+class Oracle(_Base):
+    kind = "port"
+
+    def __init__(self):
+        build()
+        L = self.lib = C.CDLL(ORACLE_SO)
+        L.po_sigma.restype = C.c_double
+        L.po_sigma.argtypes = [C.c_int, C.c_int, C.c_double]
+        L.po_inf_indexes_awgn.argtypes = [C.c_int, C.c_int, C.c_double, _ip]
+        L.po_inf_indexes_bec.argtypes = [C.c_int, C.c_int, _ip]
+        L.po_frozen_mask.argtypes = [C.c_int, _ip, C.c_int, _ip]
+        L.po_add_frozen_bits.argtypes = [_ip, _ip, C.c_int, _ip, C.c_int]
+        L.po_encode.argtypes = [C.c_int, _ip, _ip, C.c_int]
+        L.po_crc8.restype = C.c_uint
+        L.po_crc8.argtypes = [_ip, C.c_int]
+        L.po_crc16.restype = C.c_uint
+        L.po_crc16.argtypes = [_ip, C.c_int]
+        L.po_append_crc.argtypes = [_ip, C.c_int, C.c_int]
+        L.po_decode_batch.restype = C.c_int
+        L.po_decode_batch.argtypes = [C.c_int] * 5 + [C.c_double, _dp, _ip, _ip, C.c_int]
+        L.po_time_decode.restype = C.c_double
+        L.po_time_decode.argtypes = [C.c_int] * 5 + [C.c_double, _dp, _ip, C.c_int, C.c_int]
+
+    def sigma(self, n, k, snr_db):
+        return self.lib.po_sigma(n, k, snr_db)
+
+    def inf_indexes_awgn(self, n, k, sigma):
+        out = np.zeros(k, np.int32)
+        self.lib.po_inf_indexes_awgn(n, k, sigma, out)
+        return out
+
+    def inf_indexes_bec(self, n, k):
+        out = np.zeros(k, np.int32)
+        self.lib.po_inf_indexes_bec(n, k, out)
+        return out
+
+    def frozen_mask(self, n, inf):
+        inf = _i32(inf)
+        out = np.zeros(n, np.int32)
+        self.lib.po_frozen_mask(n, inf, len(inf), out)
+        return out
+
+    def add_frozen_bits(self, xinf, n, inf):
+        xinf, inf = _i32(xinf), _i32(inf)
+        x = np.zeros(n, np.int32)
+        self.lib.po_add_frozen_bits(xinf, x, n, inf, len(inf))
+        return x
+
+    def encode(self, u, with_shuffle):
+        u = _i32(u)
+        x = np.zeros_like(u)
+        for f in range(u.reshape(-1, u.shape[-1]).shape[0]):
+            self.lib.po_encode(u.shape[-1], u.reshape(-1, u.shape[-1])[f], x.reshape(-1, u.shape[-1])[f],
+                               int(with_shuffle))
+        return x
+
+    def crc8(self, bits, length=None):
+        bits = _i32(bits)
+        return self.lib.po_crc8(bits, len(bits) if length is None else length)
+
+    def crc16(self, bits, length=None):
+        bits = _i32(bits)
+        return self.lib.po_crc16(bits, len(bits) if length is None else length)
+
+    def append_crc(self, xinf, k, crc):
+        xinf = _i32(xinf).copy()
+        self.lib.po_append_crc(xinf, k, crc)
+        return xinf
+
+    def decode(self, decoder, n, L, k, crc, sigma, y, mask):
+        y = _f64(y).reshape(-1, n)
+        stride = k + crc if decoder == 3 else n
+        sol = np.zeros((y.shape[0], stride), np.int32)
+        rc = self.lib.po_decode_batch(decoder, n, L, k, crc, sigma, y, _i32(mask), sol, y.shape[0])
+        assert rc == 0
+        return sol
+
+    def time_decode(self, decoder, n, L, k, crc, sigma, y, mask, reps=1):
+        y = _f64(y).reshape(-1, n)
+        return self.lib.po_time_decode(decoder, n, L, k, crc, sigma, y, _i32(mask), y.shape[0], reps)
+
+
+class Ref(_Base):
+    kind = "reference"
+
+    @staticmethod
+    def available():
+        if not os.path.exists(REF_SO) and os.path.isdir("/root/reference/PolarCodes"):
+            build()
+        return os.path.exists(REF_SO)
+
+    def __init__(self):
+        if not Ref.available():
+            raise RuntimeError("oracle/_ref/libpolar_ref.so not built (reference sources absent)")
+        L = self.lib = C.CDLL(REF_SO)
+        L.ref_seed.argtypes = [C.c_uint32]
+        L.ref_sigma.restype = C.c_double
+        L.ref_sigma.argtypes = [C.c_int, C.c_int, C.c_double]
+        L.ref_inf_indexes_awgn.argtypes = [C.c_int, C.c_int, C.c_double, _ip]
+        L.ref_inf_indexes_bec.argtypes = [C.c_int, C.c_int, _ip]
+        L.ref_frozen_mask.argtypes = [C.c_int, _ip, C.c_int, _ip]
+        L.ref_add_frozen_bits.argtypes = [_ip, _ip, C.c_int, _ip, C.c_int]
+        L.ref_encode.argtypes = [C.c_int, _ip, _ip, C.c_int]
+        L.ref_crc8.restype = C.c_uint
+        L.ref_crc8.argtypes = [_ip, C.c_int]
+        L.ref_crc16.restype = C.c_uint
+        L.ref_crc16.argtypes = [_ip, C.c_int]
+        L.ref_sc_decode.argtypes = [C.c_int, _dp, _ip, C.c_double, _ip]
+        L.ref_scms_decode.argtypes = [C.c_int, _dp, _ip, _ip]
+        L.ref_scl_init.argtypes = [C.c_int] * 4
+        L.ref_scl_decode.argtypes = [C.c_int, C.c_int, _dp, _ip, _ip]
+        L.ref_gen_frame.argtypes = [C.c_int, C.c_int, C.c_int, _ip, C.c_double, C.c_int, _ip, _ip, _ip, _dp]
+        L.ref_time_decode.restype = C.c_double
+        L.ref_time_decode.argtypes = [C.c_int] * 5 + [_dp, _ip, C.c_double, C.c_int, C.c_int, C.c_void_p]
+        L.ref_fer_point.restype = C.c_int
+        L.ref_fer_point.argtypes = [C.c_int] * 6 + [C.c_double, C.c_int]
+
+    def seed(self, s):
+        self.lib.ref_seed(s)
+
+    def sigma(self, n, k, snr_db):
+        return self.lib.ref_sigma(n, k, snr_db)
+
+    def inf_indexes_awgn(self, n, k, sigma):
+        out = np.zeros(k, np.int32)
+        self.lib.ref_inf_indexes_awgn(n, k, sigma, out)
+        return out
+
+    def inf_indexes_bec(self, n, k):
+        out = np.zeros(k, np.int32)
+        self.lib.ref_inf_indexes_bec(n, k, out)
+        return out
+
+    def frozen_mask(self, n, inf):
+        inf = _i32(inf)
+        out = np.zeros(n, np.int32)
+        self.lib.ref_frozen_mask(n, inf, len(inf), out)
+        return out
+
+    def add_frozen_bits(self, xinf, n, inf):
+        xinf, inf = _i32(xinf), _i32(inf)
+        x = np.zeros(n, np.int32)
+        self.lib.ref_add_frozen_bits(xinf, x, n, inf, len(inf))
+        return x
+
+    def encode(self, u, with_shuffle):
+        u = _i32(u)
+        n = u.shape[-1]
+        x = np.zeros_like(u)
+        uu, xx = u.reshape(-1, n), x.reshape(-1, n)
+        for f in range(uu.shape[0]):
+            self.lib.ref_encode(n, uu[f], xx[f], int(with_shuffle))
+        return x
+
+    def crc8(self, bits, length=None):
+        bits = _i32(bits)
+        return self.lib.ref_crc8(bits, len(bits) if length is None else length)
+
+    def crc16(self, bits, length=None):
+        bits = _i32(bits)
+        return self.lib.ref_crc16(bits, len(bits) if length is None else length)
+
+    def decode(self, decoder, n, L, k, crc, sigma, y, mask):
+        y = _f64(y).reshape(-1, n)
+        mask = _i32(mask)
+        stride = k + crc if decoder == 3 else n
+        sol = np.zeros((y.shape[0], max(stride, n)), np.int32)
+        if decoder == 3:
+            self.lib.ref_scl_init(n, L, k, crc)
+        for f in range(y.shape[0]):
+            if decoder == 1:
+                self.lib.ref_sc_decode(n, y[f], mask, sigma, sol[f])
+            elif decoder == 2:
+                self.lib.ref_scms_decode(n, y[f], mask, sol[f])
+            else:
+                self.lib.ref_scl_decode(n, L, y[f], mask, sol[f])
+        return np.ascontiguousarray(sol[:, :stride])
+
+    def gen_frames(self, n, k, crc, inf, sigma, with_shuffle, frames):
+        """frames iterations of PolarCodes.cpp:133-158 drawing from the (seeded) global engine."""
+        inf = _i32(inf)
+        xinf = np.zeros((frames, k + crc), np.int32)
+        x = np.zeros((frames, n), np.int32)
+        cw = np.zeros((frames, n), np.int32)
+        y = np.zeros((frames, n), np.float64)
+        for f in range(frames):
+            self.lib.ref_gen_frame(n, k, crc, inf, sigma, int(with_shuffle), xinf[f], x[f], cw[f], y[f])
+        return xinf, x, cw, y
+
+    def time_decode(self, decoder, n, L, k, crc, sigma, y, mask, reps=1):
+        y = _f64(y).reshape(-1, n)
+        return self.lib.ref_time_decode(decoder, n, L, k, crc, y, _i32(mask), sigma, y.shape[0], reps, None)
+
+    def fer_point(self, n, k, crc, L, decoder, zcomputer, snr_db, loop):
+        return self.lib.ref_fer_point(n, k, crc, L, decoder, zcomputer, snr_db, loop)
+
+
+def best_cpu():
+    """The strongest available checker: the compiled reference if present, else the C port."""
+    return Ref() if Ref.available() else Oracle()
