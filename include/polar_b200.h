@@ -1,0 +1,119 @@
+/* polar_b200.h — C ABI of the B200-native batched polar encoder / SC / SCL decoder.
+ *
+ * This is the drop-in boundary for the hot path of dim49v/polarCodes (the per-frame loop body
+ * of PolarCodes.cpp:132-192).  The reference has no FFI layer: its "plugin API" is the set of
+ * free functions the Monte-Carlo loop calls.  Each entry point below cites the reference
+ * function it replaces (paths relative to /root/reference/PolarCodes/).  Plain pointers and
+ * sizes only; every pointer is a HOST pointer unless the name ends in _dev.
+ *
+ * Conventions: functions return 0 on success, a negative PCB_E* code on failure, and
+ * pcb_last_error() returns a thread-local human readable message.  A handle owns all device
+ * memory and streams for one (GPU, code configuration); calls on one handle must be
+ * serialised by the caller (same rule as the reference's namespace-global decoder state,
+ * SCLDecoderMinsum.cpp:17-38).  There is NO CPU fallback: without a CUDA device pcb_create
+ * fails.
+ */
+#ifndef POLAR_B200_H
+#define POLAR_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define PCB_OK 0
+#define PCB_EINVAL (-1)   /* bad argument / unsupported configuration */
+#define PCB_ECUDA (-2)    /* CUDA runtime error (message in pcb_last_error) */
+#define PCB_ENODEV (-3)   /* no CUDA device */
+#define PCB_ESTATE (-4)   /* call order (e.g. decode before pcb_set_code) */
+
+/* decoder ids are the reference's conf.txt values (PolarCodes.cpp:159-188) */
+#define PCB_DEC_SC 1        /* SCDecoder::Decode        SCDecoder.cpp:74        fp64 tanh/atanh */
+#define PCB_DEC_SCMINSUM 2  /* SCDecoderMinsum::Decode  SCDecoderMinsum.cpp:68  fp64 min-sum   */
+#define PCB_DEC_SCLMINSUM 3 /* SCLDecoderMinsum::Decode SCLDecoderMinsum.cpp:401 fp32 list     */
+
+/* precision: 0 = strict (the reference's arithmetic type: fp64 for decoders 1,2, fp32 for 3),
+ *            1 = fp32 fast mode for decoder 2 (not bit-exact by contract; FER checked statistically) */
+#define PCB_PREC_STRICT 0
+#define PCB_PREC_FP32 1
+
+typedef struct pcb_handle pcb_handle;
+
+const char* pcb_last_error(void);
+const char* pcb_version(void);
+int pcb_device_count(void);
+
+/* ---- code construction (host side, runs once per SNR point) -------------------------- */
+/* PolarCodes.cpp:123  sigma = sqrt(n / (2 k 10^(snr/10))) */
+double pcb_sigma(int n, int k, double snr_db);
+/* PolarCodes.cpp:59-74 InfIndexesAWGN: the k most reliable positions, ascending. out[k] */
+int pcb_inf_indexes_awgn(int n, int k, double sigma, int* out);
+/* PolarCodes.cpp:77-92 InfIndexesBEC. out[k] */
+int pcb_inf_indexes_bec(int n, int k, int* out);
+/* Encoder.cpp:43-55 FrozenBits with the all-zero frozen vector of PolarCodes.cpp:127:
+ * mask[i] = -1 for an information position, else the frozen value (0). mask[n] */
+int pcb_frozen_mask(int n, const int* inf, int ninf, int* mask);
+/* Encoder.cpp:17-33 AddFrozenBits (frozen values all zero). x[n] */
+int pcb_add_frozen_bits(const int* xinf, int* x, int n, const int* inf, int ninf);
+/* Resources.cpp:108-122 / :124-138 — one int per bit, MSB first, len a multiple of 8 */
+unsigned pcb_crc8(const int* bits, int len);
+unsigned pcb_crc16(const int* bits, int len);
+/* PolarCodes.cpp:136-155 — append the crc (0/8/16) MSB first at xinf[k..k+crc) */
+int pcb_append_crc(int* xinf, int k, int crc);
+
+/* ---- handle -------------------------------------------------------------------------- */
+/* Replaces the per-run allocations of PolarCodes.cpp:99-121 and
+ * SCLDecoderMinsum::InitializeDataStructures (SCLDecoderMinsum.cpp:60-118).
+ * n: power of two in [2, 65536]; L: power of two in [1, 32] (decoder 3; ignored otherwise);
+ * crc in {0, 8, 16} (decoder 3); device: CUDA ordinal. Returns NULL on failure. */
+pcb_handle* pcb_create(int device, int n, int k, int crc, int L, int decoder, int precision);
+void pcb_destroy(pcb_handle* h);
+
+/* Uploads the frozen mask (the vector FrozenBits() returns, Encoder.cpp:43) and sigma.
+ * The number of -1 entries must be k + crc (decoder 3) — decoders 1,2 accept any count. */
+int pcb_set_code(pcb_handle* h, const int* frozen_mask, double sigma);
+
+/* Encode (Encoder.cpp:77-83), batched: u[B][n] one int per bit -> x[B][n].
+ * with_shuffle != 0: x = bitrev(u) F^(x)m (used with decoders 1,2); 0: x = u F^(x)m (decoder 3). */
+int pcb_encode_batch(pcb_handle* h, const int* u, int* x, int with_shuffle, int B);
+
+/* Decode B frames. y[B][n] are the raw channel values the reference passes to *::Decode
+ * (PolarCodes.cpp:162,171,180).  sol is [B][n] for decoders 1,2 (full u-hat incl. frozen
+ * positions) and [B][k+crc] for decoder 3 (info + crc bits), one int per bit. */
+int pcb_decode_batch(pcb_handle* h, const double* y, int* sol, int B);
+/* Same with fp32 channel values. Bit-exact with pcb_decode_batch for decoder 3 when
+ * yf[i] == (float)y[i] (SCLDecoderMinsum.cpp:406-408 does that conversion itself). */
+int pcb_decode_batch_f32(pcb_handle* h, const float* y, int* sol, int B);
+/* Packed output variant: sol_bits[B][words] with words = ceil(stride/32), bit t of the frame's
+ * solution at word t/32, bit t%32 (stride = n or k+crc as above). */
+int pcb_decode_batch_f32_packed(pcb_handle* h, const float* y, uint32_t* sol_bits, int B);
+/* Device-resident variant: y_dev is a device pointer ([B][n] float if y_is_f32 else double),
+ * sol_bits_dev a device pointer to [B][words] uint32. Runs on the handle's stream and
+ * synchronises before returning. ms (may be NULL) receives the kernel time from CUDA events. */
+int pcb_decode_batch_dev(pcb_handle* h, const void* y_dev, int y_is_f32, uint32_t* sol_bits_dev, int B,
+                         float* ms);
+
+/* Batched Monte-Carlo body (PolarCodes.cpp:132-192) with on-device Philox4x32-10 BPSK/AWGN:
+ * frames [first_frame_id, first_frame_id + frames) of the stream keyed by `seed`; results do
+ * not depend on batch size or GPU count. Counters are ADDED to *frame_errors / *bit_errors
+ * (bit errors over the k info bits for decoder 3, over all n u-bits for decoders 1,2 — the
+ * reference counts frame errors only, PolarCodes.cpp:163-186). seconds = decode-kernel time. */
+int pcb_montecarlo(pcb_handle* h, double snr_db, uint64_t frames, uint64_t seed, uint64_t first_frame_id,
+                   uint64_t* frames_done, uint64_t* frame_errors, uint64_t* bit_errors, double* seconds);
+
+/* Generate one batch of channel values on the device exactly as pcb_montecarlo would and copy
+ * it to the host (verification hook: feed the result to the oracle). y[B][n] float,
+ * xinf[B][k+crc] int (decoder 3) or u[B][n] (decoders 1,2). */
+int pcb_generate_batch(pcb_handle* h, double snr_db, uint64_t seed, uint64_t first_frame_id, int B, float* y,
+                       int* tx_bits);
+
+/* introspection for bench / roofline accounting */
+int pcb_info(pcb_handle* h, int* sm_count, int* warps_per_block, int* blocks, int* smem_per_block,
+             int* first_smem_layer, uint64_t* kernel_launches);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* POLAR_B200_H */

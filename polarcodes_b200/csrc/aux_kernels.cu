@@ -1,0 +1,251 @@
+// Encoder, on-device frame generation (Philox4x32-10 + Box-Muller BPSK/AWGN) and error counting.
+//
+// Reference (paths relative to /root/reference/PolarCodes/):
+//   Encode / EncodeNode     Encoder.cpp:57-83   x = u F^(x)m (natural) or bitrev(u) F^(x)m (withShuffle)
+//   ReverseShuffle          Resources.cpp:148-158 (folded into the bit-reversed gather)
+//   AddFrozenBits           Encoder.cpp:17-33
+//   Crc8 / Crc16 + append   Resources.cpp:108-138, PolarCodes.cpp:136-155
+//   Transform / Awgn        Encoder.cpp:13-15,35-41  y = (c==0 ? 1 : -1) + N(0, sigma)
+//   frame-error compare     PolarCodes.cpp:163-168,172-177,181-186
+// Bits are packed 32 per word; butterfly stages with stride < 32 are in-word shifts/XORs,
+// larger strides are word XORs in shared memory.
+#include "aux_kernels.h"
+
+namespace pcb {
+
+// x ^= x >> s on the positions with bit s clear: the natural-order butterfly inside one word
+__device__ __forceinline__ uint32_t inword_transform(uint32_t x, int nbits) {
+    if (nbits > 1) x ^= (x >> 1) & 0x55555555u;
+    if (nbits > 2) x ^= (x >> 2) & 0x33333333u;
+    if (nbits > 4) x ^= (x >> 4) & 0x0F0F0F0Fu;
+    if (nbits > 8) x ^= (x >> 8) & 0x00FF00FFu;
+    if (nbits > 16) x ^= (x >> 16) & 0x0000FFFFu;
+    return x;
+}
+
+// in-place x = x F^(x)m on a warp-private packed array W[NW] (NW = max(n/32,1))
+__device__ __forceinline__ void warp_transform(uint32_t* W, int n, int lane) {
+    const int NW = n >= 32 ? n / 32 : 1;
+    for (int a = lane; a < NW; a += 32) W[a] = inword_transform(W[a], n);
+    __syncwarp();
+    for (int sw = 1; sw < NW; sw <<= 1) {
+        for (int a = lane; a < NW; a += 32)
+            if (!(a & sw)) W[a] ^= W[a + sw];
+        __syncwarp();
+    }
+}
+
+__global__ void __launch_bounds__(128) encode_kernel(const int* __restrict__ u, int* __restrict__ x, int n, int m,
+                                                     int with_shuffle, int B) {
+    extern __shared__ uint32_t enc_smem[];
+    const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5, wpb = blockDim.x >> 5;
+    const int NW = n >= 32 ? n / 32 : 1;
+    uint32_t* W = enc_smem + wib * NW;
+    for (int frame = blockIdx.x * wpb + wib; frame < B; frame += gridDim.x * wpb) {
+        const int* uf = u + (size_t)frame * n;
+        for (int w = 0; w < NW; w++) {
+            const int i = w * 32 + lane;
+            int bit = 0;
+            if (i < n) {
+                const int src = with_shuffle ? (int)(__brev((unsigned)i) >> (32 - m)) : i;
+                bit = uf[src] & 1;
+            }
+            const unsigned wd = __ballot_sync(0xffffffffu, bit);
+            if (lane == 0) W[w] = wd;
+        }
+        __syncwarp();
+        warp_transform(W, n, lane);
+        int* xf = x + (size_t)frame * n;
+        for (int i = lane; i < n; i += 32) xf[i] = (W[i >> 5] >> (i & 31)) & 1;
+        __syncwarp();
+    }
+}
+
+cudaError_t launch_encode(const int* d_u, int* d_x, int n, int m, int with_shuffle, int B, int sm_count,
+                          cudaStream_t st) {
+    const int wpb = 4;
+    const int NW = n >= 32 ? n / 32 : 1;
+    int blocks = (B + wpb - 1) / wpb;
+    if (blocks > sm_count * 8) blocks = sm_count * 8;
+    encode_kernel<<<blocks, wpb * 32, (size_t)wpb * NW * 4, st>>>(d_u, d_x, n, m, with_shuffle, B);
+    return cudaGetLastError();
+}
+
+// ---------------------------------------------------------------- Philox4x32-10 ---------
+struct Philox {
+    uint32_t k0, k1;
+    __device__ __forceinline__ uint4 operator()(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3) const {
+        uint32_t a = k0, b = k1;
+#pragma unroll
+        for (int r = 0; r < 10; r++) {
+            const uint32_t hi0 = __umulhi(0xD2511F53u, c0), lo0 = 0xD2511F53u * c0;
+            const uint32_t hi1 = __umulhi(0xCD9E8D57u, c2), lo1 = 0xCD9E8D57u * c2;
+            const uint32_t n0 = hi1 ^ c1 ^ a, n1 = lo1, n2 = hi0 ^ c3 ^ b, n3 = lo0;
+            c0 = n0; c1 = n1; c2 = n2; c3 = n3;
+            a += 0x9E3779B9u; b += 0xBB67AE85u;
+        }
+        return make_uint4(c0, c1, c2, c3);
+    }
+};
+
+__device__ __forceinline__ void box_muller(uint32_t a, uint32_t b, float& z0, float& z1) {
+    const float u1 = ((float)(a >> 8) + 0.5f) * (1.0f / 16777216.0f);   // (0,1), 24-bit grid
+    const float u2 = ((float)(b >> 8) + 0.5f) * (1.0f / 16777216.0f);
+    const float r = sqrtf(-2.0f * logf(u1));
+    float sn, cs;
+    sincospif(2.0f * u2, &sn, &cs);
+    z0 = r * cs; z1 = r * sn;
+}
+
+// One warp generates one frame: random info bits -> CRC -> scatter by the info positions ->
+// encode -> BPSK + AWGN.  The random stream is a function of (seed, global frame id, index)
+// only, so results do not depend on the batch size or the number of GPUs.
+__global__ void __launch_bounds__(128) generate_kernel(GenArgs G) {
+    extern __shared__ uint32_t gen_smem[];
+    __shared__ unsigned short crc_tab[256];
+    const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5, wpb = blockDim.x >> 5;
+    const int n = G.n, m = G.m;
+    const int NW = n >= 32 ? n / 32 : 1;
+    const int ninf = G.k + G.crc;
+    const int IW = (ninf + 31) >> 5;
+    uint32_t* W = gen_smem + wib * (NW + IW);
+    uint32_t* XI = W + NW;
+    if (G.crc) {
+        for (int t = threadIdx.x; t < 256; t += blockDim.x) {
+            unsigned r = G.crc == 8 ? (unsigned)t : ((unsigned)t << 8);
+            for (int b = 0; b < 8; b++) {
+                if (G.crc == 8) r = (r & 0x80) ? ((r << 1) ^ 0x31) & 0xFF : (r << 1) & 0xFF;
+                else r = (r & 0x8000) ? ((r << 1) ^ 0x1021) & 0xFFFF : (r << 1) & 0xFFFF;
+            }
+            crc_tab[t] = (unsigned short)r;
+        }
+    }
+    __syncthreads();
+    Philox ph{(uint32_t)G.seed, (uint32_t)(G.seed >> 32)};
+    for (int f = blockIdx.x * wpb + wib; f < G.B; f += gridDim.x * wpb) {
+        const uint64_t fid = G.first_frame + (uint64_t)f;
+        const uint32_t f_lo = (uint32_t)fid, f_hi = (uint32_t)(fid >> 32);
+        // information bits (PolarCodes.cpp:133-135)
+        for (int w = lane; w < IW; w += 32) {
+            const uint4 r = ph(f_lo, f_hi, (uint32_t)(w >> 2), 0x696E666Fu);
+            uint32_t v = (w & 3) == 0 ? r.x : (w & 3) == 1 ? r.y : (w & 3) == 2 ? r.z : r.w;
+            const int hi = G.k - w * 32;
+            if (hi < 32) v = hi > 0 ? (v & ((1u << hi) - 1)) : 0u;
+            XI[w] = v;
+        }
+        for (int w = lane; w < NW; w += 32) W[w] = 0;
+        __syncwarp();
+        if (G.crc && lane == 0) {   // PolarCodes.cpp:136-155, MSB first at xinf[k..k+crc)
+            unsigned r = G.crc == 8 ? 0xFFu : 0xFFFFu;
+            for (int b = 0; b < G.k / 8; b++) {
+                const unsigned byte = __brev((XI[b >> 2] >> (8 * (b & 3))) & 0xFFu) >> 24;
+                if (G.crc == 8) r = crc_tab[(r ^ byte) & 0xFF];
+                else r = ((r << 8) ^ crc_tab[((r >> 8) ^ byte) & 0xFF]) & 0xFFFF;
+            }
+            for (int t = 0; t < G.crc; t++) {
+                const int q = G.k + t;
+                XI[q >> 5] |= ((r >> (G.crc - 1 - t)) & 1u) << (q & 31);
+            }
+        }
+        __syncwarp();
+        // AddFrozenBits (frozen values from the mask) + the encoder's input order
+        for (int t = lane; t < ninf; t += 32) {
+            const uint32_t bit = (XI[t >> 5] >> (t & 31)) & 1u;
+            int pos = G.info_pos[t];
+            if (G.with_shuffle) pos = (int)(__brev((unsigned)pos) >> (32 - m));
+            if (bit) atomicOr(&W[pos >> 5], 1u << (pos & 31));
+        }
+        for (int w = lane; w < NW; w += 32) {   // frozen values (all zero in the reference)
+            uint32_t fv = G.frozen_val[w] & ~G.info_mask[w];
+            if (fv) {
+                for (int b = 0; b < 32; b++)
+                    if ((fv >> b) & 1) {
+                        int pos = w * 32 + b;
+                        if (G.with_shuffle) pos = (int)(__brev((unsigned)pos) >> (32 - m));
+                        atomicOr(&W[pos >> 5], 1u << (pos & 31));
+                    }
+            }
+        }
+        __syncwarp();
+        if (G.tx_bits) {   // what the decoder output is compared with
+            const int TW = G.tx_words;
+            uint32_t* tx = G.tx_bits + (size_t)f * TW;
+            if (G.tx_is_u) {
+                // u in natural index order: undo the shuffle on the fly
+                for (int w = lane; w < TW; w += 32) {
+                    uint32_t v = 0;
+                    if (!G.with_shuffle) v = W[w];
+                    else
+                        for (int b = 0; b < 32 && w * 32 + b < n; b++) {
+                            const int src = (int)(__brev((unsigned)(w * 32 + b)) >> (32 - m));
+                            v |= ((W[src >> 5] >> (src & 31)) & 1u) << b;
+                        }
+                    tx[w] = v;
+                }
+            } else {
+                for (int w = lane; w < TW; w += 32) tx[w] = XI[w];
+            }
+        }
+        __syncwarp();
+        warp_transform(W, n, lane);
+        // Transform (Encoder.cpp:35-41)
+        float* y = G.y + (size_t)f * n;
+        for (int q = lane; q < (n + 3) / 4; q += 32) {
+            const uint4 r = ph(f_lo, f_hi, (uint32_t)q, 0x6E6F6973u);
+            float z[4];
+            box_muller(r.x, r.y, z[0], z[1]);
+            box_muller(r.z, r.w, z[2], z[3]);
+#pragma unroll
+            for (int t = 0; t < 4; t++) {
+                const int i = q * 4 + t;
+                if (i < n) {
+                    const float s = ((W[i >> 5] >> (i & 31)) & 1u) ? -1.f : 1.f;
+                    y[i] = s + G.sigma * z[t];
+                }
+            }
+        }
+        __syncwarp();
+    }
+}
+
+cudaError_t launch_generate(const GenArgs& g, int sm_count, cudaStream_t st) {
+    const int wpb = 4;
+    const int NW = g.n >= 32 ? g.n / 32 : 1;
+    const int IW = (g.k + g.crc + 31) >> 5;
+    int blocks = (g.B + wpb - 1) / wpb;
+    if (blocks > sm_count * 8) blocks = sm_count * 8;
+    generate_kernel<<<blocks, wpb * 32, (size_t)wpb * (NW + IW) * 4, st>>>(g);
+    return cudaGetLastError();
+}
+
+// counters[0] += frame errors, counters[1] += bit errors over the first `nbits` bits
+__global__ void count_errors_kernel(const uint32_t* __restrict__ dec, const uint32_t* __restrict__ tx, int words,
+                                    int nbits, int B, unsigned long long* counters) {
+    const int f = blockIdx.x * blockDim.x + threadIdx.x;
+    int be = 0;
+    if (f < B) {
+        const uint32_t* a = dec + (size_t)f * words;
+        const uint32_t* b = tx + (size_t)f * words;
+        for (int w = 0; w * 32 < nbits; w++) {
+            uint32_t x = a[w] ^ b[w];
+            const int rem = nbits - w * 32;
+            if (rem < 32) x &= (1u << rem) - 1;
+            be += __popc(x);
+        }
+    }
+    const unsigned fem = __ballot_sync(0xffffffffu, be > 0);
+    int tot = be;
+    for (int o = 16; o; o >>= 1) tot += __shfl_xor_sync(0xffffffffu, tot, o);
+    if ((threadIdx.x & 31) == 0 && fem) {
+        atomicAdd(&counters[0], (unsigned long long)__popc(fem));
+        atomicAdd(&counters[1], (unsigned long long)tot);
+    }
+}
+
+cudaError_t launch_count(const uint32_t* dec, const uint32_t* tx, int words, int nbits, int B,
+                         unsigned long long* counters, cudaStream_t st) {
+    count_errors_kernel<<<(B + 127) / 128, 128, 0, st>>>(dec, tx, words, nbits, B, counters);
+    return cudaGetLastError();
+}
+
+}  // namespace pcb

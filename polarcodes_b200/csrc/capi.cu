@@ -1,0 +1,450 @@
+// C ABI (include/polar_b200.h): handle, code upload, batched encode / decode / Monte-Carlo.
+// There is no CPU fallback anywhere in this file: every compute entry point launches CUDA
+// kernels and fails loudly if the device or the launch is unavailable.
+#include <cstdarg>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <vector>
+
+#include "../../include/polar_b200.h"
+#include "aux_kernels.h"
+#include "decode_launch.h"
+#include "errors.h"
+
+namespace pcb {
+static thread_local char g_err[512] = "";
+int fail(int code, const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+    return code;
+}
+cudaError_t decode_generic_occupancy(int L, int mode, int fp64, int wpb, size_t smem, int* bps);
+}  // namespace pcb
+
+using namespace pcb;
+
+#define CK(call)                                                                                   \
+    do {                                                                                           \
+        cudaError_t e_ = (call);                                                                   \
+        if (e_ != cudaSuccess)                                                                     \
+            return fail(PCB_ECUDA, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__); \
+    } while (0)
+
+struct pcb_handle {
+    int device = 0, n = 0, m = 0, k = 0, crc = 0, L = 1, decoder = 0, precision = 0;
+    int stride = 0, EW = 0, fp64 = 0, sizeofT = 4;
+    bool code_set = false;
+    double sigma = 1.0;
+    int sm_count = 0, wpb = 4, bps = 1, ls = 1, warp_smem = 0;
+    size_t scratch_per_warp = 0;
+    cudaStream_t sc = nullptr, sin = nullptr, sout = nullptr;
+    cudaEvent_t ev_in[2] = {}, ev_k[2] = {}, ev_out[2] = {}, t0 = nullptr, t1 = nullptr;
+    uint32_t *d_info_mask = nullptr, *d_frozen_val = nullptr;
+    uint16_t* d_info_pos = nullptr;
+    unsigned char* d_scratch = nullptr;
+    // host-buffer pipeline (two slots)
+    size_t slot_frames = 0;
+    void* d_y[2] = {};
+    int* d_sol[2] = {};
+    uint32_t* d_solb[2] = {};
+    // Monte-Carlo buffers
+    size_t mc_frames = 0;
+    float* d_ymc = nullptr;
+    uint32_t *d_tx = nullptr, *d_dec = nullptr;
+    unsigned long long* d_counters = nullptr;
+    // encode buffers
+    size_t enc_frames = 0;
+    int *d_eu = nullptr, *d_ex = nullptr;
+    uint64_t launches = 0;
+};
+
+static int max_blocks(const pcb_handle* h) { return h->sm_count * h->bps; }
+
+static int ensure_device(pcb_handle* h) {
+    CK(cudaSetDevice(h->device));
+    return PCB_OK;
+}
+
+// choose the LLR-layer placement and the launch shape: the smallest first_smem_layer whose
+// per-warp slice fits the budget, then the warps-per-block with the best occupancy.
+static int configure(pcb_handle* h) {
+    const char* env = getenv("PCB_WARP_SMEM");
+    const int budget = env ? atoi(env) : 19200;
+    const int mode = h->decoder;
+    int ls = 1;
+    for (; ls < h->m; ls++) {
+        const int tot = warp_layout(h->sizeofT, h->L, h->n, ls, h->stride, mode).total;
+        if (tot <= budget) break;
+        const int pbytes = h->sizeofT * h->L * ((h->n >> (ls - 1)) - 1);
+        if (pbytes <= 4096) break;
+    }
+    h->ls = ls;
+    h->warp_smem = warp_layout(h->sizeofT, h->L, h->n, ls, h->stride, mode).total;
+    h->scratch_per_warp = (warp_scratch_bytes(h->sizeofT, h->L, h->n, ls) + 255) & ~(size_t)255;
+    const char* wenv = getenv("PCB_WPB");
+    int best_w = 0, best_wpb = 1, best_bps = 1;
+    const int cands[] = {1, 2, 3, 4, 6, 8};
+    for (int wpb : cands) {
+        if (wenv && atoi(wenv) != wpb) continue;
+        const size_t smem = (size_t)h->warp_smem * wpb;
+        if (smem > 227 * 1024) continue;
+        int bps = 0;
+        if (decode_generic_occupancy(h->L, mode, h->fp64, wpb, smem, &bps) != cudaSuccess) { cudaGetLastError(); continue; }
+        if (bps * wpb > best_w) { best_w = bps * wpb; best_wpb = wpb; best_bps = bps; }
+    }
+    if (best_w == 0) return fail(PCB_EINVAL, "configuration does not fit one SM (warp slice %d B)", h->warp_smem);
+    h->wpb = best_wpb;
+    h->bps = best_bps;
+    return PCB_OK;
+}
+
+extern "C" {
+
+const char* pcb_last_error(void) { return g_err; }
+const char* pcb_version(void) { return "polarcodes_b200 0.1 (sm_100a)"; }
+
+int pcb_device_count(void) {
+    int c = 0;
+    if (cudaGetDeviceCount(&c) != cudaSuccess) { cudaGetLastError(); return 0; }
+    return c;
+}
+
+pcb_handle* pcb_create(int device, int n, int k, int crc, int L, int decoder, int precision) {
+    int m = 0;
+    while ((1 << m) < n) m++;
+    if (n < 2 || n > 65536 || (1 << m) != n) { fail(PCB_EINVAL, "n must be a power of two in [2, 65536]"); return nullptr; }
+    if (decoder < 1 || decoder > 3) { fail(PCB_EINVAL, "decoder must be 1 (SC), 2 (SCMinsum) or 3 (SCLMinsum)"); return nullptr; }
+    if (decoder != 3) { L = 1; crc = 0; }
+    if (L < 1 || L > 32 || (L & (L - 1))) { fail(PCB_EINVAL, "L must be a power of two in [1, 32]"); return nullptr; }
+    if (crc != 0 && crc != 8 && crc != 16) { fail(PCB_EINVAL, "crc must be 0, 8 or 16"); return nullptr; }
+    if (k < 1 || k + crc > n) { fail(PCB_EINVAL, "need 1 <= k and k + crc <= n"); return nullptr; }
+    if (crc && k % 8) { fail(PCB_EINVAL, "k must be a multiple of 8 when a crc is used (Resources.cpp:108-138)"); return nullptr; }
+    int lb = 0;
+    while ((1 << lb) < L) lb++;
+    if (decoder == 3 && k + crc < lb) { fail(PCB_EINVAL, "k + crc must be >= log2(L) (the list never fills otherwise)"); return nullptr; }
+    if (lb * (m - 1) > 64) { fail(PCB_EINVAL, "log2(L) * (log2(n) - 1) must be <= 64"); return nullptr; }
+    int cnt = 0;
+    if (cudaGetDeviceCount(&cnt) != cudaSuccess || cnt == 0) {
+        cudaGetLastError();
+        fail(PCB_ENODEV, "no CUDA device: polarcodes_b200 has no CPU fallback");
+        return nullptr;
+    }
+    if (device < 0 || device >= cnt) { fail(PCB_EINVAL, "device %d out of range (%d devices)", device, cnt); return nullptr; }
+    pcb_handle* h = new pcb_handle();
+    h->device = device; h->n = n; h->m = m; h->k = k; h->crc = crc; h->L = L; h->decoder = decoder;
+    h->precision = precision;
+    h->fp64 = (decoder == 1) || (decoder == 2 && precision == PCB_PREC_STRICT);
+    h->sizeofT = h->fp64 ? 8 : 4;
+    h->stride = decoder == 3 ? k + crc : n;
+    h->EW = (h->stride + 31) / 32;
+    auto bail = [&](const char* what, cudaError_t e) -> pcb_handle* {
+        fail(PCB_ECUDA, "%s: %s", what, cudaGetErrorString(e));
+        pcb_destroy(h);
+        return nullptr;
+    };
+    cudaError_t e;
+    if ((e = cudaSetDevice(device)) != cudaSuccess) return bail("cudaSetDevice", e);
+    cudaDeviceProp prop;
+    if ((e = cudaGetDeviceProperties(&prop, device)) != cudaSuccess) return bail("cudaGetDeviceProperties", e);
+    h->sm_count = prop.multiProcessorCount;
+    if (configure(h) != PCB_OK) { pcb_destroy(h); return nullptr; }
+    if ((e = cudaStreamCreateWithFlags(&h->sc, cudaStreamNonBlocking)) != cudaSuccess) return bail("stream", e);
+    if ((e = cudaStreamCreateWithFlags(&h->sin, cudaStreamNonBlocking)) != cudaSuccess) return bail("stream", e);
+    if ((e = cudaStreamCreateWithFlags(&h->sout, cudaStreamNonBlocking)) != cudaSuccess) return bail("stream", e);
+    for (int s = 0; s < 2; s++) {
+        if ((e = cudaEventCreateWithFlags(&h->ev_in[s], cudaEventDisableTiming)) != cudaSuccess) return bail("event", e);
+        if ((e = cudaEventCreateWithFlags(&h->ev_k[s], cudaEventDisableTiming)) != cudaSuccess) return bail("event", e);
+        if ((e = cudaEventCreateWithFlags(&h->ev_out[s], cudaEventDisableTiming)) != cudaSuccess) return bail("event", e);
+    }
+    if ((e = cudaEventCreate(&h->t0)) != cudaSuccess) return bail("event", e);
+    if ((e = cudaEventCreate(&h->t1)) != cudaSuccess) return bail("event", e);
+    const int NW = (n + 31) / 32;
+    if ((e = cudaMalloc(&h->d_info_mask, NW * 4)) != cudaSuccess) return bail("cudaMalloc", e);
+    if ((e = cudaMalloc(&h->d_frozen_val, NW * 4)) != cudaSuccess) return bail("cudaMalloc", e);
+    if ((e = cudaMalloc(&h->d_info_pos, (size_t)n * 2)) != cudaSuccess) return bail("cudaMalloc", e);
+    const size_t sbytes = h->scratch_per_warp * (size_t)max_blocks(h) * h->wpb;
+    if (sbytes && (e = cudaMalloc(&h->d_scratch, sbytes)) != cudaSuccess) return bail("cudaMalloc(scratch)", e);
+    if ((e = cudaMalloc(&h->d_counters, 16)) != cudaSuccess) return bail("cudaMalloc", e);
+    return h;
+}
+
+void pcb_destroy(pcb_handle* h) {
+    if (!h) return;
+    cudaSetDevice(h->device);
+    cudaDeviceSynchronize();
+    cudaFree(h->d_info_mask); cudaFree(h->d_frozen_val); cudaFree(h->d_info_pos); cudaFree(h->d_scratch);
+    for (int s = 0; s < 2; s++) {
+        cudaFree(h->d_y[s]); cudaFree(h->d_sol[s]); cudaFree(h->d_solb[s]);
+        if (h->ev_in[s]) cudaEventDestroy(h->ev_in[s]);
+        if (h->ev_k[s]) cudaEventDestroy(h->ev_k[s]);
+        if (h->ev_out[s]) cudaEventDestroy(h->ev_out[s]);
+    }
+    cudaFree(h->d_ymc); cudaFree(h->d_tx); cudaFree(h->d_dec); cudaFree(h->d_counters);
+    cudaFree(h->d_eu); cudaFree(h->d_ex);
+    if (h->t0) cudaEventDestroy(h->t0);
+    if (h->t1) cudaEventDestroy(h->t1);
+    if (h->sc) cudaStreamDestroy(h->sc);
+    if (h->sin) cudaStreamDestroy(h->sin);
+    if (h->sout) cudaStreamDestroy(h->sout);
+    cudaGetLastError();
+    delete h;
+}
+
+int pcb_set_code(pcb_handle* h, const int* frozen_mask, double sigma) {
+    if (!h || !frozen_mask) return fail(PCB_EINVAL, "pcb_set_code: null argument");
+    if (int r = ensure_device(h)) return r;
+    const int n = h->n, NW = (n + 31) / 32;
+    std::vector<uint32_t> im(NW, 0), fv(NW, 0);
+    std::vector<uint16_t> pos;
+    for (int i = 0; i < n; i++) {
+        if (frozen_mask[i] == -1) { im[i >> 5] |= 1u << (i & 31); pos.push_back((uint16_t)i); }
+        else if (frozen_mask[i] == 1) fv[i >> 5] |= 1u << (i & 31);
+        else if (frozen_mask[i] != 0) return fail(PCB_EINVAL, "frozen_mask[%d] = %d (want -1, 0 or 1)", i, frozen_mask[i]);
+    }
+    if (h->decoder == 3 && (int)pos.size() != h->k + h->crc)
+        return fail(PCB_EINVAL, "frozen mask has %d information positions, expected k + crc = %d", (int)pos.size(),
+                    h->k + h->crc);
+    if (h->decoder != 3 && (int)pos.size() != h->k)
+        return fail(PCB_EINVAL, "frozen mask has %d information positions, expected k = %d", (int)pos.size(), h->k);
+    pos.resize(n, 0);
+    CK(cudaMemcpyAsync(h->d_info_mask, im.data(), NW * 4, cudaMemcpyHostToDevice, h->sc));
+    CK(cudaMemcpyAsync(h->d_frozen_val, fv.data(), NW * 4, cudaMemcpyHostToDevice, h->sc));
+    CK(cudaMemcpyAsync(h->d_info_pos, pos.data(), (size_t)n * 2, cudaMemcpyHostToDevice, h->sc));
+    CK(cudaStreamSynchronize(h->sc));
+    h->sigma = sigma;
+    h->code_set = true;
+    return PCB_OK;
+}
+
+int pcb_info(pcb_handle* h, int* sm_count, int* warps_per_block, int* blocks, int* smem_per_block,
+             int* first_smem_layer, uint64_t* kernel_launches) {
+    if (!h) return fail(PCB_EINVAL, "pcb_info: null handle");
+    if (sm_count) *sm_count = h->sm_count;
+    if (warps_per_block) *warps_per_block = h->wpb;
+    if (blocks) *blocks = max_blocks(h);
+    if (smem_per_block) *smem_per_block = h->warp_smem * h->wpb;
+    if (first_smem_layer) *first_smem_layer = h->ls;
+    if (kernel_launches) *kernel_launches = h->launches;
+    return PCB_OK;
+}
+
+}  // extern "C"
+
+// ------------------------------------------------------------------ decode plumbing ------
+static DecodeArgs make_args(pcb_handle* h, const void* d_y, int y_f32, int* d_sol, uint32_t* d_solb, int B) {
+    DecodeArgs a;
+    a.n = h->n; a.m = h->m; a.k = h->k; a.crc = h->crc; a.B = B;
+    a.first_smem_layer = h->ls; a.warp_smem_bytes = h->warp_smem; a.stride = h->stride;
+    a.y = d_y; a.y_f32 = y_f32;
+    a.info_mask = h->d_info_mask; a.frozen_val = h->d_frozen_val; a.info_pos = h->d_info_pos;
+    a.sol = d_sol; a.sol_bits = d_solb;
+    a.scratch = h->d_scratch; a.scratch_per_warp = h->scratch_per_warp;
+    a.sigma = h->sigma;
+    return a;
+}
+
+static cudaError_t launch(pcb_handle* h, const DecodeArgs& a, cudaStream_t st) {
+    int blocks = (a.B + h->wpb - 1) / h->wpb;
+    if (blocks > max_blocks(h)) blocks = max_blocks(h);
+    h->launches++;
+    return launch_decode_generic(a, h->L, h->decoder, h->fp64, blocks, h->wpb, st);
+}
+
+static int ensure_slots(pcb_handle* h, size_t frames, size_t ybytes_per_frame) {
+    if (h->slot_frames >= frames) return PCB_OK;
+    for (int s = 0; s < 2; s++) {
+        cudaFree(h->d_y[s]); cudaFree(h->d_sol[s]); cudaFree(h->d_solb[s]);
+        h->d_y[s] = nullptr; h->d_sol[s] = nullptr; h->d_solb[s] = nullptr;
+    }
+    h->slot_frames = 0;
+    for (int s = 0; s < 2; s++) {
+        CK(cudaMalloc(&h->d_y[s], frames * (size_t)h->n * 8));
+        CK(cudaMalloc(&h->d_sol[s], frames * (size_t)h->stride * 4));
+        CK(cudaMalloc(&h->d_solb[s], frames * (size_t)h->EW * 4));
+    }
+    (void)ybytes_per_frame;
+    h->slot_frames = frames;
+    return PCB_OK;
+}
+
+// host buffers -> chunked, double-buffered pipeline: H2D on `sin`, kernel on `sc`, D2H on `sout`
+static int decode_host(pcb_handle* h, const void* y, int y_f32, int* sol, uint32_t* solb, int B) {
+    if (!h || !y || (!sol && !solb)) return fail(PCB_EINVAL, "pcb_decode_batch: null argument");
+    if (!h->code_set) return fail(PCB_ESTATE, "pcb_decode_batch: call pcb_set_code first");
+    if (B < 0) return fail(PCB_EINVAL, "pcb_decode_batch: B < 0");
+    if (B == 0) return PCB_OK;
+    if (int r = ensure_device(h)) return r;
+    const size_t ybpf = (size_t)h->n * (y_f32 ? 4 : 8);
+    size_t chunk = ((size_t)48 << 20) / ((size_t)h->n * 8);
+    const char* cenv = getenv("PCB_CHUNK_FRAMES");
+    if (cenv) chunk = (size_t)atol(cenv);
+    if (chunk < 1) chunk = 1;
+    if (chunk > (size_t)B) chunk = (size_t)B;
+    if (int r = ensure_slots(h, chunk, ybpf)) return r;
+    int c = 0;
+    for (size_t f0 = 0; f0 < (size_t)B; f0 += chunk, c++) {
+        const int s = c & 1;
+        const int nb = (int)((size_t)B - f0 < chunk ? (size_t)B - f0 : chunk);
+        if (c >= 2) CK(cudaStreamWaitEvent(h->sin, h->ev_k[s], 0));      // slot input consumed
+        CK(cudaMemcpyAsync(h->d_y[s], (const char*)y + f0 * ybpf, (size_t)nb * ybpf, cudaMemcpyHostToDevice, h->sin));
+        CK(cudaEventRecord(h->ev_in[s], h->sin));
+        CK(cudaStreamWaitEvent(h->sc, h->ev_in[s], 0));
+        if (c >= 2) CK(cudaStreamWaitEvent(h->sc, h->ev_out[s], 0));     // slot output drained
+        DecodeArgs a = make_args(h, h->d_y[s], y_f32, sol ? h->d_sol[s] : nullptr, solb ? h->d_solb[s] : nullptr, nb);
+        CK(launch(h, a, h->sc));
+        CK(cudaEventRecord(h->ev_k[s], h->sc));
+        CK(cudaStreamWaitEvent(h->sout, h->ev_k[s], 0));
+        if (sol)
+            CK(cudaMemcpyAsync(sol + f0 * h->stride, h->d_sol[s], (size_t)nb * h->stride * 4, cudaMemcpyDeviceToHost, h->sout));
+        if (solb)
+            CK(cudaMemcpyAsync(solb + f0 * h->EW, h->d_solb[s], (size_t)nb * h->EW * 4, cudaMemcpyDeviceToHost, h->sout));
+        CK(cudaEventRecord(h->ev_out[s], h->sout));
+    }
+    CK(cudaStreamSynchronize(h->sout));
+    CK(cudaStreamSynchronize(h->sc));
+    CK(cudaStreamSynchronize(h->sin));
+    return PCB_OK;
+}
+
+extern "C" {
+
+int pcb_decode_batch(pcb_handle* h, const double* y, int* sol, int B) { return decode_host(h, y, 0, sol, nullptr, B); }
+int pcb_decode_batch_f32(pcb_handle* h, const float* y, int* sol, int B) { return decode_host(h, y, 1, sol, nullptr, B); }
+int pcb_decode_batch_f32_packed(pcb_handle* h, const float* y, uint32_t* sol_bits, int B) {
+    return decode_host(h, y, 1, nullptr, sol_bits, B);
+}
+
+int pcb_decode_batch_dev(pcb_handle* h, const void* y_dev, int y_is_f32, uint32_t* sol_bits_dev, int B, float* ms) {
+    if (!h || !y_dev || !sol_bits_dev) return fail(PCB_EINVAL, "pcb_decode_batch_dev: null argument");
+    if (!h->code_set) return fail(PCB_ESTATE, "pcb_decode_batch_dev: call pcb_set_code first");
+    if (B <= 0) return B == 0 ? PCB_OK : fail(PCB_EINVAL, "B < 0");
+    if (int r = ensure_device(h)) return r;
+    DecodeArgs a = make_args(h, y_dev, y_is_f32, nullptr, sol_bits_dev, B);
+    CK(cudaEventRecord(h->t0, h->sc));
+    CK(launch(h, a, h->sc));
+    CK(cudaEventRecord(h->t1, h->sc));
+    CK(cudaStreamSynchronize(h->sc));
+    if (ms) CK(cudaEventElapsedTime(ms, h->t0, h->t1));
+    return PCB_OK;
+}
+
+int pcb_encode_batch(pcb_handle* h, const int* u, int* x, int with_shuffle, int B) {
+    if (!h || !u || !x) return fail(PCB_EINVAL, "pcb_encode_batch: null argument");
+    if (B <= 0) return B == 0 ? PCB_OK : fail(PCB_EINVAL, "B < 0");
+    if (int r = ensure_device(h)) return r;
+    size_t chunk = ((size_t)64 << 20) / ((size_t)h->n * 4);
+    if (chunk < 1) chunk = 1;
+    if (chunk > (size_t)B) chunk = (size_t)B;
+    if (h->enc_frames < chunk) {
+        cudaFree(h->d_eu); cudaFree(h->d_ex);
+        h->d_eu = h->d_ex = nullptr; h->enc_frames = 0;
+        CK(cudaMalloc(&h->d_eu, chunk * (size_t)h->n * 4));
+        CK(cudaMalloc(&h->d_ex, chunk * (size_t)h->n * 4));
+        h->enc_frames = chunk;
+    }
+    for (size_t f0 = 0; f0 < (size_t)B; f0 += chunk) {
+        const int nb = (int)((size_t)B - f0 < chunk ? (size_t)B - f0 : chunk);
+        CK(cudaMemcpyAsync(h->d_eu, u + f0 * h->n, (size_t)nb * h->n * 4, cudaMemcpyHostToDevice, h->sc));
+        CK(launch_encode(h->d_eu, h->d_ex, h->n, h->m, with_shuffle != 0, nb, h->sm_count, h->sc));
+        h->launches++;
+        CK(cudaMemcpyAsync(x + f0 * h->n, h->d_ex, (size_t)nb * h->n * 4, cudaMemcpyDeviceToHost, h->sc));
+        CK(cudaStreamSynchronize(h->sc));
+    }
+    return PCB_OK;
+}
+
+static int ensure_mc(pcb_handle* h, size_t frames) {
+    if (h->mc_frames >= frames) return PCB_OK;
+    cudaFree(h->d_ymc); cudaFree(h->d_tx); cudaFree(h->d_dec);
+    h->d_ymc = nullptr; h->d_tx = h->d_dec = nullptr; h->mc_frames = 0;
+    CK(cudaMalloc(&h->d_ymc, frames * (size_t)h->n * 4));
+    CK(cudaMalloc(&h->d_tx, frames * (size_t)h->EW * 4));
+    CK(cudaMalloc(&h->d_dec, frames * (size_t)h->EW * 4));
+    h->mc_frames = frames;
+    return PCB_OK;
+}
+
+static GenArgs gen_args(pcb_handle* h, double snr_db, uint64_t seed, uint64_t first, int B) {
+    GenArgs g;
+    g.n = h->n; g.m = h->m; g.k = h->k; g.crc = h->crc; g.B = B;
+    g.with_shuffle = h->decoder != 3;
+    g.tx_is_u = h->decoder != 3;
+    g.tx_words = h->EW;
+    g.sigma = (float)pcb_sigma(h->n, h->k, snr_db);
+    g.seed = seed; g.first_frame = first;
+    g.info_mask = h->d_info_mask; g.frozen_val = h->d_frozen_val; g.info_pos = h->d_info_pos;
+    g.y = h->d_ymc; g.tx_bits = h->d_tx;
+    return g;
+}
+
+static size_t mc_batch(pcb_handle* h) {
+    size_t b = ((size_t)256 << 20) / ((size_t)h->n * 4);
+    const char* env = getenv("PCB_MC_BATCH");
+    if (env) b = (size_t)atol(env);
+    const size_t minb = (size_t)max_blocks(h) * h->wpb;
+    if (b < minb) b = minb;
+    return b;
+}
+
+int pcb_montecarlo(pcb_handle* h, double snr_db, uint64_t frames, uint64_t seed, uint64_t first_frame_id,
+                   uint64_t* frames_done, uint64_t* frame_errors, uint64_t* bit_errors, double* seconds) {
+    if (!h) return fail(PCB_EINVAL, "pcb_montecarlo: null handle");
+    if (!h->code_set) return fail(PCB_ESTATE, "pcb_montecarlo: call pcb_set_code first");
+    if (int r = ensure_device(h)) return r;
+    size_t batch = mc_batch(h);
+    if (batch > frames) batch = (size_t)frames;
+    if (frames == 0) return PCB_OK;
+    if (int r = ensure_mc(h, batch)) return r;
+    CK(cudaMemsetAsync(h->d_counters, 0, 16, h->sc));
+    double secs = 0;
+    const int nbits = h->decoder == 3 ? h->k : h->n;
+    h->sigma = pcb_sigma(h->n, h->k, snr_db);
+    for (uint64_t f0 = 0; f0 < frames; f0 += batch) {
+        const int nb = (int)(frames - f0 < batch ? frames - f0 : batch);
+        GenArgs g = gen_args(h, snr_db, seed, first_frame_id + f0, nb);
+        CK(launch_generate(g, h->sm_count, h->sc));
+        DecodeArgs a = make_args(h, h->d_ymc, 1, nullptr, h->d_dec, nb);
+        CK(cudaEventRecord(h->t0, h->sc));
+        CK(launch(h, a, h->sc));
+        CK(cudaEventRecord(h->t1, h->sc));
+        CK(launch_count(h->d_dec, h->d_tx, h->EW, nbits, nb, h->d_counters, h->sc));
+        h->launches += 2;
+        CK(cudaStreamSynchronize(h->sc));
+        float ms = 0;
+        CK(cudaEventElapsedTime(&ms, h->t0, h->t1));
+        secs += ms * 1e-3;
+    }
+    unsigned long long cnt[2];
+    CK(cudaMemcpy(cnt, h->d_counters, 16, cudaMemcpyDeviceToHost));
+    if (frames_done) *frames_done += frames;
+    if (frame_errors) *frame_errors += cnt[0];
+    if (bit_errors) *bit_errors += cnt[1];
+    if (seconds) *seconds += secs;
+    return PCB_OK;
+}
+
+int pcb_generate_batch(pcb_handle* h, double snr_db, uint64_t seed, uint64_t first_frame_id, int B, float* y,
+                       int* tx_bits) {
+    if (!h || !y) return fail(PCB_EINVAL, "pcb_generate_batch: null argument");
+    if (!h->code_set) return fail(PCB_ESTATE, "pcb_generate_batch: call pcb_set_code first");
+    if (B <= 0) return B == 0 ? PCB_OK : fail(PCB_EINVAL, "B < 0");
+    if (int r = ensure_device(h)) return r;
+    if (int r = ensure_mc(h, (size_t)B)) return r;
+    GenArgs g = gen_args(h, snr_db, seed, first_frame_id, B);
+    CK(launch_generate(g, h->sm_count, h->sc));
+    h->launches++;
+    CK(cudaMemcpyAsync(y, h->d_ymc, (size_t)B * h->n * 4, cudaMemcpyDeviceToHost, h->sc));
+    std::vector<uint32_t> tx((size_t)B * h->EW);
+    CK(cudaMemcpyAsync(tx.data(), h->d_tx, tx.size() * 4, cudaMemcpyDeviceToHost, h->sc));
+    CK(cudaStreamSynchronize(h->sc));
+    if (tx_bits)
+        for (int f = 0; f < B; f++)
+            for (int t = 0; t < h->stride; t++)
+                tx_bits[(size_t)f * h->stride + t] = (tx[(size_t)f * h->EW + (t >> 5)] >> (t & 31)) & 1;
+    return PCB_OK;
+}
+
+}  // extern "C"

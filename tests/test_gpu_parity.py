@@ -1,0 +1,180 @@
+"""GPU parity tests proper: the CUDA path (through the C ABI) against the committed golden
+vectors (outputs of the unmodified reference) and against the CPU oracle on fresh seeded
+inputs.  Bar: bit-exact for the encoder and the min-sum SC / SCL decoders."""
+import glob
+import os
+
+import numpy as np
+import pytest
+
+from conftest import GOLDEN
+
+pytestmark = pytest.mark.gpu
+
+DECODE = sorted(os.path.basename(p)[:-4] for p in glob.glob(os.path.join(GOLDEN, "sc*.npz")))
+
+
+def _decoder(dec, n, k, crc, L, mask, sigma):
+    import polarcodes_b200 as pb
+    d = pb.Decoder(n, k, crc, L, dec)
+    d.set_code(mask, sigma)
+    return d
+
+
+@pytest.mark.parametrize("name", DECODE)
+def test_decode_golden(name):
+    g = np.load(os.path.join(GOLDEN, name + ".npz"))
+    dec, n, k, crc, L = (int(g[x]) for x in ("decoder", "n", "k", "crc", "L"))
+    d = _decoder(dec, n, k, crc, L, g["mask"], float(g["sigma"]))
+    sol = d.decode(g["y"])
+    assert sol.shape == g["sol"].shape
+    bad = np.nonzero((sol != g["sol"]).any(axis=1))[0]
+    if dec == 1:
+        # exact SC: CUDA tanh/atanh differ from glibc in ulps -> statistical parity only;
+        # on these 41 frames a differing decision would need an LLR within ulps of zero.
+        assert bad.size <= 1, f"{name}: frames {bad.tolist()} differ"
+    else:
+        assert bad.size == 0, f"{name}: frames {bad.tolist()} differ from the reference"
+
+
+@pytest.mark.parametrize("name", [x for x in DECODE if x.startswith("scl")])
+def test_decode_golden_f32_and_packed(name):
+    import polarcodes_b200 as pb
+    g = np.load(os.path.join(GOLDEN, name + ".npz"))
+    dec, n, k, crc, L = (int(g[x]) for x in ("decoder", "n", "k", "crc", "L"))
+    d = _decoder(dec, n, k, crc, L, g["mask"], float(g["sigma"]))
+    yf = g["y"].astype(np.float32)   # SCLDecoderMinsum.cpp:406-408 makes this conversion itself
+    assert (d.decode(yf) == g["sol"]).all()
+    assert (pb.unpack_bits(d.decode_packed(yf), k + crc) == g["sol"]).all()
+
+
+def test_encode_golden():
+    import polarcodes_b200 as pb
+    g = np.load(os.path.join(GOLDEN, "encode.npz"))
+    for n in (2, 4, 8, 32, 64, 256, 1024, 2048):
+        d = pb.Decoder(n, 1, 0, 1, pb.SCMINSUM)
+        u = g[f"u{n}"]
+        assert (d.encode(u, 0) == g[f"x{n}_nat"]).all(), n
+        assert (d.encode(u, 1) == g[f"x{n}_shuf"]).all(), n
+
+
+CASES = [  # decoder, n, k, crc, L, snr, frames
+    (2, 1024, 512, 0, 1, 2.0, 64),
+    (2, 64, 32, 0, 1, 1.0, 256),
+    (2, 2, 1, 0, 1, 1.0, 64),
+    (2, 8, 4, 0, 1, 1.0, 64),
+    (2, 4096, 2048, 0, 1, 2.0, 8),
+    (3, 1024, 512, 0, 8, 2.0, 64),
+    (3, 1024, 512, 16, 8, 1.0, 64),
+    (3, 1024, 512, 8, 8, 1.5, 64),
+    (3, 2048, 1024, 16, 32, 2.0, 6),
+    (3, 512, 256, 16, 16, 1.5, 32),
+    (3, 256, 128, 8, 4, 1.5, 128),
+    (3, 64, 32, 0, 2, 1.0, 256),
+    (3, 32, 16, 0, 16, 1.0, 128),
+    (3, 16, 8, 0, 4, 1.0, 128),
+    (3, 8, 8, 0, 8, 1.0, 64),
+    (3, 128, 64, 8, 1, 2.0, 128),
+    (3, 4096, 2048, 16, 8, 2.0, 4),
+]
+
+
+@pytest.mark.parametrize("dec,n,k,crc,L,snr,frames", CASES)
+def test_cuda_equals_oracle(oracle, dec, n, k, crc, L, snr, frames):
+    rng = np.random.default_rng(1000 + n + 7 * L + crc)
+    sigma, inf, mask = oracle.make_code(n, k, crc, snr)
+    # the all-zero codeword is a codeword: BPSK +1 plus noise exercises the same decode path
+    xinf = rng.integers(0, 2, (frames, k + crc)).astype(np.int32)
+    y = np.empty((frames, n))
+    for f in range(frames):
+        xi = oracle.append_crc(xinf[f], k, crc) if dec == 3 else xinf[f]
+        x = oracle.add_frozen_bits(xi, n, inf)
+        cw = oracle.encode(x, dec != 3)
+        y[f] = (1 - 2 * cw) + sigma * rng.standard_normal(n)
+    d = _decoder(dec, n, k, crc, L, mask, sigma)
+    got = d.decode(y)
+    want = oracle.decode(dec, n, L, k, crc, sigma, y, mask)
+    bad = np.nonzero((got != want).any(axis=1))[0]
+    assert bad.size == 0, f"frames {bad.tolist()} differ"
+
+
+def test_quantised_inputs_force_ties(oracle):
+    """Integer-grid LLRs make exact metric ties at the median common (pass 2,
+    SCLDecoderMinsum.cpp:362-371) and exercise the slot-order discipline."""
+    rng = np.random.default_rng(5)
+    for n, k, crc, L in ((128, 64, 0, 8), (256, 128, 8, 4), (64, 32, 0, 16), (1024, 512, 16, 8), (256, 128, 0, 32),
+                         (64, 32, 0, 1), (64, 32, 0, 2)):
+        sigma, inf, mask = oracle.make_code(n, k, crc, 2.0)
+        y = rng.integers(-3, 4, (48, n)).astype(np.float64)
+        d = _decoder(3, n, k, crc, L, mask, sigma)
+        assert (d.decode(y) == oracle.decode(3, n, L, k, crc, sigma, y, mask)).all(), (n, L)
+
+
+def test_frozen_value_one(oracle):
+    """Encoder.cpp:43-55 lets frozen positions carry a value; the decoders must honour a 1."""
+    rng = np.random.default_rng(9)
+    n, k, L = 128, 64, 4
+    sigma, inf, mask = oracle.make_code(n, k, 0, 2.0)
+    mask = mask.copy()
+    fz = np.nonzero(mask == 0)[0]
+    mask[fz[::3]] = 1
+    y = rng.standard_normal((32, n)) + 0.5
+    for dec, LL in ((3, L), (2, 1)):
+        d = _decoder(dec, n, k, 0, LL, mask, sigma)
+        assert (d.decode(y) == oracle.decode(dec, n, LL, k, 0, sigma, y, mask)).all()
+
+
+def test_large_batch_matches_small_batches(oracle):
+    """Ragged / multi-chunk host batches: results are independent of batching."""
+    rng = np.random.default_rng(3)
+    n, k, crc, L = 256, 128, 8, 8
+    sigma, inf, mask = oracle.make_code(n, k, crc, 1.5)
+    y = (1 + sigma * rng.standard_normal((5000, n)))
+    d = _decoder(3, n, k, crc, L, mask, sigma)
+    full = d.decode(y)
+    os.environ["PCB_CHUNK_FRAMES"] = "777"
+    try:
+        d2 = _decoder(3, n, k, crc, L, mask, sigma)
+        parts = d2.decode(y)
+    finally:
+        del os.environ["PCB_CHUNK_FRAMES"]
+    assert (full == parts).all()
+    assert (full[:200] == oracle.decode(3, n, L, k, crc, sigma, y[:200], mask)).all()
+    assert d.decode(y[:0]).shape == (0, k + crc)
+
+
+def test_montecarlo_consistency(oracle):
+    """On-device Philox frames: the device-side error counters equal what the oracle finds on
+    the very same generated batch, and do not depend on how the frame range is split."""
+    import polarcodes_b200 as pb
+    n, k, crc, L, snr = 256, 128, 8, 4, 1.0
+    code = pb.Code(n, k, crc, snr)
+    d = _decoder(3, n, k, crc, L, code.mask, code.sigma)
+    y, tx = d.generate(snr, 512, seed=77)
+    for f in range(8):  # generated frames are self-consistent codewords
+        assert (oracle.append_crc(tx[f], k, crc) == tx[f]).all()
+    want = oracle.decode(3, n, L, k, crc, code.sigma, y.astype(np.float64), code.mask)
+    errs = (want[:, :k] != tx[:, :k])
+    r = d.montecarlo(snr, 512, seed=77)
+    assert r["frames"] == 512
+    assert r["frame_errors"] == int(errs.any(axis=1).sum())
+    assert r["bit_errors"] == int(errs.sum())
+    a = d.montecarlo(snr, 200, seed=77, first_frame_id=0)
+    b = d.montecarlo(snr, 312, seed=77, first_frame_id=200)
+    assert a["frame_errors"] + b["frame_errors"] == r["frame_errors"]
+    assert a["bit_errors"] + b["bit_errors"] == r["bit_errors"]
+    # noise statistics of the generator
+    s = pb.lib().pcb_sigma(n, k, snr)
+    cw = np.where(y > 0, 1.0, -1.0)
+    noise = (y - cw)[np.abs(y) > 1.0]
+    assert abs(np.std(y - np.sign(y) * 1.0) / s - 1) < 0.2
+
+
+def test_sc_montecarlo_fer_matches_published():
+    """pc.txt:3 (SC min-sum (1024,512), BEC construction, 2 dB): FER 0.1255 with 10 000 frames."""
+    import polarcodes_b200 as pb
+    code = pb.Code(1024, 512, 0, 2.0, zcomputer=1)
+    d = _decoder(2, 1024, 512, 0, 1, code.mask, code.sigma)
+    r = d.montecarlo(2.0, 20000, seed=11)
+    fer = r["frame_errors"] / r["frames"]
+    assert abs(fer - 0.1255) < 4 * np.sqrt(0.1255 * 0.8745 * (1 / 20000 + 1 / 10000)), fer
