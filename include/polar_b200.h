@@ -109,6 +109,11 @@ int pcb_montecarlo(pcb_handle* h, double snr_db, uint64_t frames, uint64_t seed,
 int pcb_generate_batch(pcb_handle* h, double snr_db, uint64_t seed, uint64_t first_frame_id, int B, float* y,
                        int* tx_bits);
 
+/* Same, into caller-provided DEVICE buffers: y_dev[B][n] float, tx_bits_dev[B][ceil(stride/32)]
+ * packed (may be NULL). Synchronises before returning. */
+int pcb_generate_batch_dev(pcb_handle* h, double snr_db, uint64_t seed, uint64_t first_frame_id, int B,
+                           float* y_dev, uint32_t* tx_bits_dev);
+
 /* introspection for bench / roofline accounting */
 int pcb_info(pcb_handle* h, int* sm_count, int* warps_per_block, int* blocks, int* smem_per_block,
              int* first_smem_layer, uint64_t* kernel_launches);

@@ -47,6 +47,7 @@ SIGNATURES = {
     "pcb_montecarlo": (C.c_int, [C.c_void_p, C.c_double, C.c_uint64, C.c_uint64, C.c_uint64, _u64p, _u64p, _u64p,
                                  C.POINTER(C.c_double)]),
     "pcb_generate_batch": (C.c_int, [C.c_void_p, C.c_double, C.c_uint64, C.c_uint64, C.c_int, _fp, _ip]),
+    "pcb_generate_batch_dev": (C.c_int, [C.c_void_p, C.c_double, C.c_uint64, C.c_uint64, C.c_int, C.c_void_p, C.c_void_p]),
     "pcb_info": (C.c_int, [C.c_void_p] + [C.POINTER(C.c_int)] * 5 + [_u64p]),
 }
 
@@ -195,6 +196,10 @@ class Decoder:
         tx = np.zeros((B, self.stride), np.int32)
         _check(lib().pcb_generate_batch(self._h, float(snr_db), int(seed), int(first_frame_id), B, y, tx))
         return y, tx
+
+    def generate_dev(self, snr_db, B, y_dev_ptr, tx_dev_ptr=None, seed=0x5EED0000, first_frame_id=0):
+        _check(lib().pcb_generate_batch_dev(self._h, float(snr_db), int(seed), int(first_frame_id), B, y_dev_ptr,
+                                            tx_dev_ptr))
 
     def info(self):
         v = [C.c_int(0) for _ in range(5)]

@@ -426,6 +426,20 @@ int pcb_montecarlo(pcb_handle* h, double snr_db, uint64_t frames, uint64_t seed,
     return PCB_OK;
 }
 
+int pcb_generate_batch_dev(pcb_handle* h, double snr_db, uint64_t seed, uint64_t first_frame_id, int B,
+                           float* y_dev, uint32_t* tx_bits_dev) {
+    if (!h || !y_dev) return fail(PCB_EINVAL, "pcb_generate_batch_dev: null argument");
+    if (!h->code_set) return fail(PCB_ESTATE, "pcb_generate_batch_dev: call pcb_set_code first");
+    if (B <= 0) return B == 0 ? PCB_OK : fail(PCB_EINVAL, "B < 0");
+    if (int r = ensure_device(h)) return r;
+    GenArgs g = gen_args(h, snr_db, seed, first_frame_id, B);
+    g.y = y_dev; g.tx_bits = tx_bits_dev;
+    CK(launch_generate(g, h->sm_count, h->sc));
+    h->launches++;
+    CK(cudaStreamSynchronize(h->sc));
+    return PCB_OK;
+}
+
 int pcb_generate_batch(pcb_handle* h, double snr_db, uint64_t seed, uint64_t first_frame_id, int B, float* y,
                        int* tx_bits) {
     if (!h || !y) return fail(PCB_EINVAL, "pcb_generate_batch: null argument");
