@@ -22,6 +22,10 @@ int fail(int code, const char* fmt, ...) {
     return code;
 }
 cudaError_t decode_generic_occupancy(int L, int mode, int fp64, int wpb, size_t smem, int* bps);
+// tuned list-8 kernel (decode_scl8.cu)
+bool scl8_supported(int m);
+cudaError_t launch_decode_scl8(const DecodeArgs& a, int blocks, int wpb, cudaStream_t st);
+cudaError_t scl8_occupancy(int m, int wpb, int* bps, int* warp_bytes);
 }  // namespace pcb
 
 using namespace pcb;
@@ -39,6 +43,7 @@ struct pcb_handle {
     bool code_set = false;
     double sigma = 1.0;
     int sm_count = 0, wpb = 4, bps = 1, ls = 1, warp_smem = 0;
+    bool fast8 = false;             // tuned list-8 kernel (decode_scl8.cu) instead of the generic one
     size_t scratch_per_warp = 0;
     cudaStream_t sc = nullptr, sin = nullptr, sout = nullptr;
     cudaEvent_t ev_in[2] = {}, ev_k[2] = {}, ev_out[2] = {}, t0 = nullptr, t1 = nullptr;
@@ -71,6 +76,21 @@ static int ensure_device(pcb_handle* h) {
 // choose the LLR-layer placement and the launch shape: the smallest first_smem_layer whose
 // per-warp slice fits the budget, then the warps-per-block with the best occupancy.
 static int configure(pcb_handle* h) {
+    const char* wenv = getenv("PCB_WPB");
+    h->fast8 = h->decoder == 3 && h->L == 8 && scl8_supported(h->m) && !getenv("PCB_FORCE_GENERIC");
+    if (h->fast8) {
+        int best_w = 0;
+        for (int wpb = 1; wpb <= 12; wpb++) {
+            if (wenv && atoi(wenv) != wpb) continue;
+            int bps = 0, wb = 0;
+            if (scl8_occupancy(h->m, wpb, &bps, &wb) != cudaSuccess) { cudaGetLastError(); continue; }
+            if (bps * wpb > best_w) { best_w = bps * wpb; h->wpb = wpb; h->bps = bps; h->warp_smem = wb; }
+        }
+        if (best_w == 0) return fail(PCB_EINVAL, "list-8 kernel does not fit one SM");
+        h->ls = 2;
+        h->scratch_per_warp = 0;
+        return PCB_OK;
+    }
     const char* env = getenv("PCB_WARP_SMEM");
     const int budget = env ? atoi(env) : 19200;
     const int mode = h->decoder;
@@ -84,7 +104,6 @@ static int configure(pcb_handle* h) {
     h->ls = ls;
     h->warp_smem = warp_layout(h->sizeofT, h->L, h->n, ls, h->stride, mode).total;
     h->scratch_per_warp = (warp_scratch_bytes(h->sizeofT, h->L, h->n, ls) + 255) & ~(size_t)255;
-    const char* wenv = getenv("PCB_WPB");
     int best_w = 0, best_wpb = 1, best_bps = 1;
     const int cands[] = {1, 2, 3, 4, 6, 8};
     for (int wpb : cands) {
@@ -250,6 +269,7 @@ static cudaError_t launch(pcb_handle* h, const DecodeArgs& a, cudaStream_t st) {
     int blocks = (a.B + h->wpb - 1) / h->wpb;
     if (blocks > max_blocks(h)) blocks = max_blocks(h);
     h->launches++;
+    if (h->fast8) return launch_decode_scl8(a, blocks, h->wpb, st);
     return launch_decode_generic(a, h->L, h->decoder, h->fp64, blocks, h->wpb, st);
 }
 

@@ -1,0 +1,497 @@
+// Tuned list-8 SCL min-sum decoder (SCLDecoderMinsum.cpp:225-478 semantics, bit-exact with
+// decode_generic.cu): ONE WARP DECODES ONE FRAME, lane = sub*8 + p with p the path slot (0..7)
+// and sub (0..3) the quarter of every LLR layer that lane owns.
+//
+// Layout choices:
+//  * LLR element j of a layer belongs to sub = j mod 4.  The half-split pair (j, j+s) is then
+//    lane-local on every layer of size >= 4, so a whole f/g chain from a large layer down to
+//    size 4 needs no shuffle and no __syncwarp; the chunk of a lane is contiguous in shared
+//    memory ("sub-major" order) and moves as float4 / float2.
+//  * layers 0 (channel) and 1 are never stored: layer 2 is computed straight from y with the
+//    two top levels fused (phases 0, n/4, n/2, 3n/4), which saves half of the LLR storage.
+//  * layers of size 4, 2, 1 live in registers; a clone copies the live ones with shuffles.
+//  * lazy copy: slot p writes its own arrays; a per-path word holds, per layer, the slot to
+//    read from (3 bits per layer).  A clone copies that word.
+//  * prune: 16 candidates x 16 = 256 compares = 8 per lane on the metric bit patterns.
+#include "decode_common.cuh"
+#include "decode_launch.h"
+
+namespace pcb {
+
+namespace s8 {
+
+constexpr unsigned FULL = 0xffffffffu;
+
+template <int M>
+struct Geo {
+    static constexpr int N = 1 << M;
+    static constexpr int LTOP = 2;          // first stored LLR layer
+    static constexpr int LBOT = M - 3;      // last stored LLR layer (size 8); sizes 4,2,1 are registers
+    static constexpr int NW = N / 32;       // partial-sum words per slot (heap: layer of size S at bits [S,2S))
+    static constexpr int HS = NW + 1;       // padded slot stride of the heap (bank spread)
+    __host__ __device__ static constexpr int c(int lam) { return (N >> lam) / 4; }
+    __host__ __device__ static constexpr int cs(int lam) { return (c(lam) % 8 == 0) ? c(lam) + 4 : c(lam); }
+    __host__ __device__ static constexpr int off(int lam) {
+        int o = 0;
+        for (int l = LTOP; l < lam; ++l) o += 32 * cs(l);
+        return o;
+    }
+    static constexpr int PFLOATS = off(LBOT + 1);
+    static constexpr int XW = 8 * HS;                      // final codeword estimates (alias the LLR region)
+    static constexpr int EW_MAX = N / 32;
+    // byte offsets inside the warp slice
+    static constexpr int OFF_P = 0;
+    static constexpr int P_BYTES = ((PFLOATS > XW + 8 * EW_MAX ? PFLOATS : XW + 8 * EW_MAX) * 4 + 15) & ~15;
+    static constexpr int OFF_H = P_BYTES;
+    static constexpr int OFF_KEYS = OFF_H + ((8 * HS * 4 + 15) & ~15);
+    static constexpr int TOTAL = OFF_KEYS + 64;
+};
+
+__device__ __forceinline__ float ff(float a, float b) { return f_minsum<float>(a, b); }
+// g with the partial-sum bit already moved to the sign position (0 or 0x80000000)
+__device__ __forceinline__ float gs(float a, float b, uint32_t signbit) {
+    return b + __uint_as_float(__float_as_uint(a) ^ signbit);
+}
+__device__ __forceinline__ uint32_t sgn(uint32_t w, int pos) { return (w << (31 - pos)) & 0x80000000u; }
+
+template <int M, typename YT>
+struct Dec {
+    using G = Geo<M>;
+    // ---- per-lane state ----
+    int lane, sub, p;
+    float* P;          // warp slice
+    uint32_t* H;
+    uint32_t* keys;
+    const unsigned char* lut;
+    const YT* y;
+    float met;
+    uint32_t pidx, cidx, w0;
+    float A2, A1_0, A1_1, A0;
+    int nact;
+
+    __device__ __forceinline__ float* chunk(int lam, int slot) const {
+        return P + G::off(lam) + (sub * 8 + slot) * G::cs(lam);
+    }
+    __device__ __forceinline__ int pfield(int lam) const { return (pidx >> (3 * (lam - 2))) & 7; }
+    __device__ __forceinline__ int cfield(int lam) const { return (cidx >> (3 * (lam - 1))) & 7; }
+    __device__ __forceinline__ float ldy(int j) const { return (float)y[j]; }
+
+    // bits of partial-sum layer `lam` (size s >= 32) for this lane's elements j = sub + 4k,
+    // k in [8*w8, 8*w8+8): returned word has element k's bit at position 4*(k&7)
+    __device__ __forceinline__ uint32_t cword(int lam, int w8) const {
+        const int s = G::N >> lam;
+        return H[cfield(lam) * G::HS + (s >> 5) + w8] >> sub;
+    }
+
+    // ---- layer 2 straight from the channel values (layers 0 and 1 are virtual) --------
+    // g1: layer 1 is a g-layer (second half of the codeword); g2: layer 2 is a g-layer
+    template <bool G1, bool G2>
+    __device__ __forceinline__ void top_chain() {
+        constexpr int Q = G::N / 4;           // layer-2 size
+        constexpr int C2 = G::c(2);
+        float* dst = chunk(2, p);
+#pragma unroll 2
+        for (int k0 = 0; k0 < C2; k0 += 8) {
+            uint32_t c1a = 0, c1b = 0, c2w = 0;
+            if (G1) {   // layer-1 bits j and j+Q: words (j>>5) and (j+Q)>>5 of the size-N/2 layer
+                const int s1 = G::N >> 1;
+                const uint32_t* h = H + cfield(1) * G::HS + (s1 >> 5);
+                c1a = h[k0 >> 3] >> sub;
+                c1b = h[(Q >> 5) + (k0 >> 3)] >> sub;
+            }
+            if (G2) c2w = cword(2, k0 >> 3);
+#pragma unroll
+            for (int kk = 0; kk < 8; kk += 4) {
+                float o[4];
+#pragma unroll
+                for (int e = 0; e < 4; e++) {
+                    const int k = k0 + kk + e, j = sub + 4 * k;
+                    const float y0 = ldy(j), y1 = ldy(j + Q), y2 = ldy(j + 2 * Q), y3 = ldy(j + 3 * Q);
+                    float la, lb;
+                    if (G1) { la = gs(y0, y2, sgn(c1a, 4 * (kk + e))); lb = gs(y1, y3, sgn(c1b, 4 * (kk + e))); }
+                    else { la = ff(y0, y2); lb = ff(y1, y3); }
+                    o[e] = G2 ? gs(la, lb, sgn(c2w, 4 * (kk + e))) : ff(la, lb);
+                }
+                *reinterpret_cast<float4*>(dst + k0 + kk) = make_float4(o[0], o[1], o[2], o[3]);
+            }
+        }
+    }
+
+    // ---- one stored layer from the previous stored layer ------------------------------
+    // ISG: g-layer (first layer of a chain, source slot is the lazily shared one)
+    template <int LAM, bool ISG>
+    __device__ __forceinline__ void layer() {
+        constexpr int C = G::c(LAM);          // outputs per lane
+        const int slot = ISG ? pfield(LAM - 1) : p;
+        const float* src = chunk(LAM - 1, slot);
+        float* dst = chunk(LAM, p);
+        if constexpr (C >= 8) {
+#pragma unroll 2
+            for (int k0 = 0; k0 < C; k0 += 8) {
+                uint32_t cw = 0;
+                if (ISG) cw = cword(LAM, k0 >> 3);
+#pragma unroll
+                for (int kk = 0; kk < 8; kk += 4) {
+                    const float4 a = *reinterpret_cast<const float4*>(src + k0 + kk);
+                    const float4 b = *reinterpret_cast<const float4*>(src + C + k0 + kk);
+                    float4 o;
+                    if (ISG) {
+                        o.x = gs(a.x, b.x, sgn(cw, 4 * kk)); o.y = gs(a.y, b.y, sgn(cw, 4 * kk + 4));
+                        o.z = gs(a.z, b.z, sgn(cw, 4 * kk + 8)); o.w = gs(a.w, b.w, sgn(cw, 4 * kk + 12));
+                    } else { o.x = ff(a.x, b.x); o.y = ff(a.y, b.y); o.z = ff(a.z, b.z); o.w = ff(a.w, b.w); }
+                    *reinterpret_cast<float4*>(dst + k0 + kk) = o;
+                }
+            }
+        } else if constexpr (C == 4) {        // size 16: bits 16 + sub + 4k of w0
+            const float4 a = *reinterpret_cast<const float4*>(src);
+            const float4 b = *reinterpret_cast<const float4*>(src + 4);
+            float4 o;
+            if (ISG) {
+                const uint32_t cw = w0 >> (16 + sub);
+                o.x = gs(a.x, b.x, sgn(cw, 0)); o.y = gs(a.y, b.y, sgn(cw, 4));
+                o.z = gs(a.z, b.z, sgn(cw, 8)); o.w = gs(a.w, b.w, sgn(cw, 12));
+            } else { o.x = ff(a.x, b.x); o.y = ff(a.y, b.y); o.z = ff(a.z, b.z); o.w = ff(a.w, b.w); }
+            *reinterpret_cast<float4*>(dst) = o;
+        } else {                              // C == 2, size 8: bits 8 + sub + 4k of w0
+            const float4 ab = *reinterpret_cast<const float4*>(src);   // a0 a1 b0 b1
+            float2 o;
+            if (ISG) {
+                const uint32_t cw = w0 >> (8 + sub);
+                o.x = gs(ab.x, ab.z, sgn(cw, 0)); o.y = gs(ab.y, ab.w, sgn(cw, 4));
+            } else { o.x = ff(ab.x, ab.z); o.y = ff(ab.y, ab.w); }
+            *reinterpret_cast<float2*>(dst) = o;
+        }
+    }
+
+    template <int LAM>
+    __device__ __forceinline__ void f_down() {   // f layers LAM..LBOT
+        if constexpr (LAM <= G::LBOT) {
+            layer<LAM, false>();
+            f_down<LAM + 1>();
+        }
+    }
+    template <int LAM>
+    __device__ __forceinline__ void chain_g() {  // g at LAM (3 <= LAM <= LBOT), then f below
+        layer<LAM, true>();
+        f_down<LAM + 1>();
+    }
+    template <int LAM>
+    __device__ __forceinline__ void chain_dispatch(int ll) {
+        if constexpr (LAM <= G::LBOT) {
+            if (ll == LAM) chain_g<LAM>();
+            else chain_dispatch<LAM + 1>(ll);
+        }
+    }
+
+    // LLR work at the first phase i0 = 8*blk of a size-8 subtree, down to layer LBOT
+    __device__ __forceinline__ void upper(int blk) {
+        int ll;
+        if (blk == 0) { top_chain<false, false>(); f_down<3>(); ll = 2; }
+        else {
+            ll = G::LBOT - (__ffs(blk) - 1);
+            if (ll <= 2) {
+                if (ll == 1) top_chain<true, false>();
+                else if (blk & (G::N / 16)) top_chain<true, true>();
+                else top_chain<false, true>();
+                f_down<3>();
+                ll = 2;
+            } else chain_dispatch<3>(ll);
+        }
+        // layers >= ll are now this slot's own
+        const uint32_t low = (1u << (3 * (ll - 2))) - 1;
+        pidx = (pidx & low) | ((0x9249249u * (uint32_t)p) & ~low);
+    }
+
+    // ---- register layers ------------------------------------------------------------
+    __device__ __forceinline__ void a1_from_a2(bool isg) {
+        const float x = __shfl_xor_sync(FULL, A2, 16);
+        float own;
+        if (isg) {
+            const float lo = (sub < 2) ? A2 : x, hi = (sub < 2) ? x : A2;
+            own = gs(lo, hi, sgn(w0, 2 + (sub & 1)));
+        } else own = ff(A2, x);
+        const float oth = __shfl_xor_sync(FULL, own, 8);
+        A1_0 = (sub & 1) ? oth : own;
+        A1_1 = (sub & 1) ? own : oth;
+    }
+    __device__ __forceinline__ void a2_from_a3(bool isg) {
+        const int slot = isg ? pfield(G::LBOT) : p;
+        const float2 v = *reinterpret_cast<const float2*>(chunk(G::LBOT, slot));
+        A2 = isg ? gs(v.x, v.y, sgn(w0, 4 + sub)) : ff(v.x, v.y);
+    }
+
+    // ---- fork / prune of one information bit (SCLDecoderMinsum.cpp:315-400) ----------
+    // LIVE: bit0 A2 live, bit1 A1 live after this phase.  Returns this slot's bit.
+    template <int LIVE>
+    __device__ __forceinline__ int fork() {
+        const float pf0 = met + fmaxf(-A0, 0.f);   // pen(llr,0) = |llr| iff llr < 0
+        const float pf1 = met + fmaxf(A0, 0.f);    // pen(llr,1) = |llr| iff llr > 0
+        int u;
+        int srcp = p;
+        bool take = false;
+        if (nact < 8) {                            // growth (:329-341)
+            const int pbase = 8 - nact;
+            take = p >= pbase - nact && p < pbase;
+            srcp = take ? (2 * pbase - 1 - p) : p;
+            u = 0; met = pf0;
+            nact *= 2;
+        } else {
+            if (sub == 0) *reinterpret_cast<uint2*>(keys + 2 * p) = make_uint2(__float_as_uint(pf0), __float_as_uint(pf1));
+            __syncwarp();
+            const uint32_t kc = __float_as_uint((sub & 1) ? pf1 : pf0);
+            const uint4 ka = *reinterpret_cast<const uint4*>(keys + 8 * (sub >> 1));
+            const uint4 kb = *reinterpret_cast<const uint4*>(keys + 8 * (sub >> 1) + 4);
+            int cnt = (ka.x < kc) + (ka.y < kc) + (ka.z < kc) + (ka.w < kc) + (kb.x < kc) + (kb.y < kc) + (kb.z < kc) + (kb.w < kc);
+            cnt += __shfl_xor_sync(FULL, cnt, 16);
+            unsigned bal = __ballot_sync(FULL, cnt < 8) & 0xFFFFu;
+            if (__popc(bal) != 8) {                // a tie straddles the median (:362-371)
+                const bool in = (bal >> (lane & 15)) & 1;
+                const unsigned tkey = __reduce_max_sync(FULL, in ? kc : 0u);
+                const unsigned tb = __ballot_sync(FULL, in && kc == tkey) & 0xFFFFu;
+                const int need = 8 - (__popc(bal) - __popc(tb));
+                const unsigned t0 = tb & 0xFF, t1 = tb >> 8, lt = (1u << p) - 1;
+                const int before = __popc(t0 & lt) + __popc(t1 & lt) + ((sub & 1) ? ((t0 >> p) & 1) : 0);
+                bal = __ballot_sync(FULL, in && (kc < tkey || before < need)) & 0xFFFFu;
+            }
+            __syncwarp();
+            const unsigned k0m = bal & 0xFF, k1m = bal >> 8;
+            const unsigned nonem = ~(k0m | k1m) & 0xFF, bothm = k0m & k1m;
+            const bool k0 = (k0m >> p) & 1;
+            u = k0 ? 0 : 1;
+            met = k0 ? pf0 : pf1;
+            if (nonem == 0) return u;
+            take = (nonem >> p) & 1;
+            if (take) srcp = lut[bothm * 4 + __popc(nonem & ((1u << p) - 1))];
+        }
+        // clones: copy the parent's state (:145-156 without copying arrays)
+        __syncwarp();   // orders the parent's shared-memory writes before the clone's lazy reads
+        const int sl = (lane & 24) | srcp;
+        const float m1 = __shfl_sync(FULL, pf1, sl);
+        const uint32_t pi = __shfl_sync(FULL, pidx, sl);
+        const uint32_t ci = __shfl_sync(FULL, cidx, sl);
+        const uint32_t ww = __shfl_sync(FULL, w0, sl);
+        if (take) { met = m1; pidx = pi; cidx = ci; w0 = ww; u = 1; }
+        if (LIVE & 1) { const float t = __shfl_sync(FULL, A2, sl); if (take) A2 = t; }
+        if (LIVE & 2) {
+            const float t0 = __shfl_sync(FULL, A1_0, sl), t1 = __shfl_sync(FULL, A1_1, sl);
+            if (take) { A1_0 = t0; A1_1 = t1; }
+        }
+        return u;
+    }
+
+    // decision at phase i0+T with the leaf LLR in A0
+    template <int T, int LIVE>
+    __device__ __forceinline__ int decide(uint32_t infobyte, uint32_t fvbyte) {
+        if ((infobyte >> T) & 1) return fork<LIVE>();
+        const int fv = (fvbyte >> T) & 1;
+        met += fv ? fmaxf(A0, 0.f) : fmaxf(-A0, 0.f);   // :413-418
+        return fv;
+    }
+
+    // partial-sum combine at the last phase of a subtree (t = 7): d2 = 3 + ctz(blk+1)
+    __device__ __forceinline__ void setbit_last(int blk, int u) {
+        const int d2 = min(M, 3 + __ffs(blk + 1) - 1);
+        uint32_t T = (uint32_t)u;
+        T = (((w0 >> 1) ^ T) & 1u) | (T << 1);
+        T = (((w0 >> 2) ^ T) & 3u) | (T << 2);
+        T = (((w0 >> 4) ^ T) & 15u) | (T << 4);
+        if (d2 == 3) { w0 = (w0 & ~0xFF00u) | (T << 8); return; }
+        T = (((w0 >> 8) ^ T) & 0xFFu) | (T << 8);
+        if (d2 == 4) { w0 = (w0 & 0x0000FFFFu) | (T << 16); return; }
+        T = (((w0 >> 16) ^ T) & 0xFFFFu) | (T << 16);
+        const int D = 1 << d2;
+        // destination layer m-d2 sits at heap words [D/32, 2D/32); layer 0 (the final codeword
+        // estimate, written at the very last phase) goes to the then-dead LLR region instead
+        uint32_t* hp = (d2 == M) ? (reinterpret_cast<uint32_t*>(P) + p * G::HS - G::NW) : (H + p * G::HS);
+        if (sub == 0) hp[2 * D / 32 - 1] = T;
+        __syncwarp();
+        for (int w = 32; w < D; w <<= 1) {
+            const int lgw = 31 - __clz(w), layc = M - lgw, nw = w >> 5;
+            const uint32_t* cs = H + cfield(layc) * G::HS + nw;
+            for (int kk = sub; kk < nw; kk += 4)
+                hp[(2 * D - 2 * w) / 32 + kk] = cs[kk] ^ hp[(2 * D - w) / 32 + kk];
+            __syncwarp();
+        }
+        if (d2 < M) {
+            const int sh = 3 * (M - d2 - 1);
+            cidx = (cidx & ~(7u << sh)) | ((uint32_t)p << sh);
+        }
+    }
+
+    // the 8 phases of one size-8 subtree; layer LBOT of this subtree is already computed
+    __device__ __forceinline__ void leaf8(int blk, uint32_t ib, uint32_t fb) {
+        int u;
+        // t = 0
+        a2_from_a3(false); a1_from_a2(false); A0 = ff(A1_0, A1_1);
+        u = decide<0, 3>(ib, fb); w0 = (w0 & ~2u) | ((uint32_t)u << 1);
+        // t = 1
+        A0 = gs(A1_0, A1_1, sgn(w0, 1));
+        u = decide<1, 1>(ib, fb);
+        { uint32_t T = (((w0 >> 1) ^ u) & 1u) | ((uint32_t)u << 1); w0 = (w0 & ~0xCu) | (T << 2); }
+        // t = 2
+        a1_from_a2(true); A0 = ff(A1_0, A1_1);
+        u = decide<2, 2>(ib, fb); w0 = (w0 & ~2u) | ((uint32_t)u << 1);
+        // t = 3
+        A0 = gs(A1_0, A1_1, sgn(w0, 1));
+        u = decide<3, 0>(ib, fb);
+        { uint32_t T = (((w0 >> 1) ^ u) & 1u) | ((uint32_t)u << 1); T = (((w0 >> 2) ^ T) & 3u) | (T << 2);
+          w0 = (w0 & ~0xF0u) | (T << 4); }
+        // t = 4
+        a2_from_a3(true); a1_from_a2(false); A0 = ff(A1_0, A1_1);
+        u = decide<4, 3>(ib, fb); w0 = (w0 & ~2u) | ((uint32_t)u << 1);
+        // t = 5
+        A0 = gs(A1_0, A1_1, sgn(w0, 1));
+        u = decide<5, 1>(ib, fb);
+        { uint32_t T = (((w0 >> 1) ^ u) & 1u) | ((uint32_t)u << 1); w0 = (w0 & ~0xCu) | (T << 2); }
+        // t = 6
+        a1_from_a2(true); A0 = ff(A1_0, A1_1);
+        u = decide<6, 2>(ib, fb); w0 = (w0 & ~2u) | ((uint32_t)u << 1);
+        // t = 7
+        A0 = gs(A1_0, A1_1, sgn(w0, 1));
+        u = decide<7, 0>(ib, fb);
+        setbit_last(blk, u);
+    }
+};
+
+}  // namespace s8
+
+template <int M, typename YT>
+__global__ void __launch_bounds__(384, 1) decode_scl8_kernel(const DecodeArgs A) {
+    using G = s8::Geo<M>;
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    __shared__ unsigned short crc_tab[256];
+    __shared__ unsigned char lut[1024];
+    constexpr unsigned FULL = 0xffffffffu;
+    const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5, wpb = blockDim.x >> 5;
+    if (A.crc) {
+        for (int t = threadIdx.x; t < 256; t += blockDim.x) {
+            unsigned r = A.crc == 8 ? (unsigned)t : ((unsigned)t << 8);
+            for (int b = 0; b < 8; b++) {
+                if (A.crc == 8) r = (r & 0x80) ? ((r << 1) ^ 0x31) & 0xFF : (r << 1) & 0xFF;
+                else r = (r & 0x8000) ? ((r << 1) ^ 0x1021) & 0xFFFF : (r << 1) & 0xFFFF;
+            }
+            crc_tab[t] = (unsigned short)r;
+        }
+    }
+    // lut[mask*4 + j] = position of the j-th HIGHEST set bit of the 8-bit mask
+    for (int t = threadIdx.x; t < 1024; t += blockDim.x) {
+        unsigned bm = (unsigned)t >> 2;
+        for (int j = 0; j < (t & 3); j++) if (bm) bm &= ~(0x80000000u >> __clz(bm));
+        lut[t] = bm ? (unsigned char)(31 - __clz(bm)) : 0;
+    }
+    __syncthreads();
+
+    unsigned char* ws = smem_raw + (size_t)wib * G::TOTAL;
+    s8::Dec<M, YT> D;
+    D.lane = lane; D.sub = lane >> 3; D.p = lane & 7;
+    D.P = reinterpret_cast<float*>(ws + G::OFF_P);
+    D.H = reinterpret_cast<uint32_t*>(ws + G::OFF_H);
+    D.keys = reinterpret_cast<uint32_t*>(ws + G::OFF_KEYS);
+    D.lut = lut;
+    const int n = G::N;
+    const int EW = (A.stride + 31) >> 5;
+    const int gwarp = blockIdx.x * wpb + wib, total_warps = gridDim.x * wpb;
+
+    for (int frame = gwarp; frame < A.B; frame += total_warps) {
+        D.y = reinterpret_cast<const YT*>(A.y) + (size_t)frame * n;
+        D.met = 0.f; D.pidx = 0; D.cidx = 0; D.w0 = 0; D.nact = 1;
+        D.A2 = D.A1_0 = D.A1_1 = D.A0 = 0.f;
+        uint32_t iw = 0, fw = 0;
+        for (int blk = 0; blk < n / 8; ++blk) {
+            if ((blk & 3) == 0) { iw = __ldg(A.info_mask + (blk >> 2)); fw = __ldg(A.frozen_val + (blk >> 2)); }
+            D.upper(blk);
+            D.leaf8(blk, (iw >> (8 * (blk & 3))) & 0xFF, (fw >> (8 * (blk & 3))) & 0xFF);
+        }
+        __syncwarp();
+        // ---- final selection (:432-473): u-hat = x-hat F^(x)m per slot, CRC, first pass wins ----
+        uint32_t* X = reinterpret_cast<uint32_t*>(D.P);          // x-hat of every slot (setbit_last, d2 == M)
+        uint32_t* E = X + G::XW;
+        constexpr int NW = G::NW, HS = G::HS, lgN = M - 5;
+        for (int e = lane; e < (8 << lgN); e += 32) {
+            const int q = e >> lgN, a = e & (NW - 1);
+            uint32_t x = X[q * HS + a];
+            x ^= (x >> 1) & 0x55555555u; x ^= (x >> 2) & 0x33333333u; x ^= (x >> 4) & 0x0F0F0F0Fu;
+            x ^= (x >> 8) & 0x00FF00FFu; x ^= (x >> 16) & 0x0000FFFFu;
+            X[q * HS + a] = x;
+        }
+        __syncwarp();
+        for (int sw = 1; sw < NW; sw <<= 1) {
+            for (int e = lane; e < (8 << lgN); e += 32) {
+                const int q = e >> lgN, a = e & (NW - 1);
+                if (!(a & sw)) X[q * HS + a] ^= X[q * HS + a + sw];
+            }
+            __syncwarp();
+        }
+        for (int q = 0; q < 8; q++) {
+            for (int t0 = 0; t0 < A.stride; t0 += 32) {
+                const int t = t0 + lane;
+                int bit = 0;
+                if (t < A.stride) { const int pos = A.info_pos[t]; bit = (X[q * HS + (pos >> 5)] >> (pos & 31)) & 1; }
+                const unsigned wd = __ballot_sync(FULL, bit);
+                if (lane == 0) E[q * EW + (t0 >> 5)] = wd;
+            }
+        }
+        __syncwarp();
+        bool ok = false;
+        if (A.crc && lane < 8) {
+            const uint32_t* e = E + lane * EW;
+            unsigned r = A.crc == 8 ? 0xFFu : 0xFFFFu;
+            for (int b = 0; b < A.k / 8; b++) {
+                const unsigned byte = __brev((e[b >> 2] >> (8 * (b & 3))) & 0xFFu) >> 24;
+                if (A.crc == 8) r = crc_tab[(r ^ byte) & 0xFF];
+                else r = ((r << 8) ^ crc_tab[((r >> 8) ^ byte) & 0xFF]) & 0xFFFF;
+            }
+            unsigned rx = 0;
+            for (int t = 0; t < A.crc; t++) { const int q = A.k + t; rx = (rx << 1) | ((e[q >> 5] >> (q & 31)) & 1); }
+            ok = (rx == r);
+        }
+        const unsigned okm = __ballot_sync(FULL, ok);
+        const int chosen = okm ? (__ffs(okm) - 1) : 7;
+        if (A.sol)
+            for (int t = lane; t < A.stride; t += 32)
+                A.sol[(size_t)frame * A.stride + t] = (E[chosen * EW + (t >> 5)] >> (t & 31)) & 1;
+        if (A.sol_bits)
+            for (int t = lane; t < EW; t += 32) A.sol_bits[(size_t)frame * EW + t] = E[chosen * EW + t];
+        __syncwarp();
+    }
+}
+
+template <int M, typename YT>
+static cudaError_t launch_m(const DecodeArgs& a, int blocks, int wpb, cudaStream_t st) {
+    const size_t smem = (size_t)s8::Geo<M>::TOTAL * wpb;
+    cudaError_t e = cudaFuncSetAttribute(decode_scl8_kernel<M, YT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    decode_scl8_kernel<M, YT><<<blocks, wpb * 32, smem, st>>>(a);
+    return cudaGetLastError();
+}
+
+template <int M, typename YT>
+static cudaError_t occ_m(int wpb, int* bps, int* warp_bytes) {
+    const size_t smem = (size_t)s8::Geo<M>::TOTAL * wpb;
+    *warp_bytes = s8::Geo<M>::TOTAL;
+    cudaError_t e = cudaFuncSetAttribute(decode_scl8_kernel<M, YT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    return cudaOccupancyMaxActiveBlocksPerMultiprocessor(bps, decode_scl8_kernel<M, YT>, wpb * 32, smem);
+}
+
+bool scl8_supported(int m) { return m >= 8 && m <= 11; }
+
+cudaError_t launch_decode_scl8(const DecodeArgs& a, int blocks, int wpb, cudaStream_t st) {
+#define PCB_CASE(MM)                                                                    \
+    case MM: return a.y_f32 ? launch_m<MM, float>(a, blocks, wpb, st) : launch_m<MM, double>(a, blocks, wpb, st);
+    switch (a.m) { PCB_CASE(8) PCB_CASE(9) PCB_CASE(10) PCB_CASE(11) }
+#undef PCB_CASE
+    return cudaErrorInvalidValue;
+}
+
+cudaError_t scl8_occupancy(int m, int wpb, int* bps, int* warp_bytes) {
+    switch (m) {
+        case 8: return occ_m<8, float>(wpb, bps, warp_bytes);
+        case 9: return occ_m<9, float>(wpb, bps, warp_bytes);
+        case 10: return occ_m<10, float>(wpb, bps, warp_bytes);
+        case 11: return occ_m<11, float>(wpb, bps, warp_bytes);
+    }
+    return cudaErrorInvalidValue;
+}
+
+}  // namespace pcb

@@ -76,6 +76,11 @@ CASES = [  # decoder, n, k, crc, L, snr, frames
     (3, 8, 8, 0, 8, 1.0, 64),
     (3, 128, 64, 8, 1, 2.0, 128),
     (3, 4096, 2048, 16, 8, 2.0, 4),
+    (3, 256, 128, 8, 8, 1.0, 256),
+    (3, 512, 256, 16, 8, 1.5, 128),
+    (3, 2048, 1024, 16, 8, 1.5, 32),
+    (3, 1024, 256, 0, 8, 0.0, 64),
+    (3, 1024, 768, 8, 8, 3.0, 64),
 ]
 
 
@@ -102,7 +107,7 @@ def test_quantised_inputs_force_ties(oracle):
     """Integer-grid LLRs make exact metric ties at the median common (pass 2,
     SCLDecoderMinsum.cpp:362-371) and exercise the slot-order discipline."""
     rng = np.random.default_rng(5)
-    for n, k, crc, L in ((128, 64, 0, 8), (256, 128, 8, 4), (64, 32, 0, 16), (1024, 512, 16, 8), (256, 128, 0, 32),
+    for n, k, crc, L in ((128, 64, 0, 8), (256, 128, 8, 8), (2048, 1024, 0, 8), (256, 128, 8, 4), (64, 32, 0, 16), (1024, 512, 16, 8), (256, 128, 0, 32),
                          (64, 32, 0, 1), (64, 32, 0, 2)):
         sigma, inf, mask = oracle.make_code(n, k, crc, 2.0)
         y = rng.integers(-3, 4, (48, n)).astype(np.float64)
