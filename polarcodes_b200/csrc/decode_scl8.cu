@@ -224,6 +224,16 @@ struct Dec {
     // LIVE: bit0 A2 live, bit1 A1 live after this phase.  Returns this slot's bit.
     template <int LIVE>
     __device__ __forceinline__ int fork() {
+        if (nact == 8) {
+            // Fast exit (no kill, no clone): the candidates of path p are {met, met + |llr|}.  If
+            // every penalised candidate is strictly above every unpenalised one, the L smallest
+            // are exactly the L unpenalised ones (no tie possible), each path keeps its likely
+            // bit and its metric.  ~85 % of the prune calls at the operating point end here.
+            const float hi = met + fmaxf(fabsf(A0), 0.f);          // NaN llr -> penalty 0 (as :308-313)
+            const unsigned maxlo = __reduce_max_sync(FULL, __float_as_uint(met));
+            const unsigned minhi = __reduce_min_sync(FULL, __float_as_uint(hi));
+            if (maxlo < minhi) return A0 < 0.f ? 1 : 0;
+        }
         const float pf0 = met + fmaxf(-A0, 0.f);   // pen(llr,0) = |llr| iff llr < 0
         const float pf1 = met + fmaxf(A0, 0.f);    // pen(llr,1) = |llr| iff llr > 0
         int u;
@@ -236,12 +246,16 @@ struct Dec {
             u = 0; met = pf0;
             nact *= 2;
         } else {
-            if (sub == 0) *reinterpret_cast<uint2*>(keys + 2 * p) = make_uint2(__float_as_uint(pf0), __float_as_uint(pf1));
+            // keys are stored complemented: key < kc  <=>  carry-out of (kc + ~key)
+            if (sub == 0) *reinterpret_cast<uint2*>(keys + 2 * p) = make_uint2(~__float_as_uint(pf0), ~__float_as_uint(pf1));
             __syncwarp();
             const uint32_t kc = __float_as_uint((sub & 1) ? pf1 : pf0);
             const uint4 ka = *reinterpret_cast<const uint4*>(keys + 8 * (sub >> 1));
             const uint4 kb = *reinterpret_cast<const uint4*>(keys + 8 * (sub >> 1) + 4);
-            int cnt = (ka.x < kc) + (ka.y < kc) + (ka.z < kc) + (ka.w < kc) + (kb.x < kc) + (kb.y < kc) + (kb.z < kc) + (kb.w < kc);
+            int cnt = 0;   // number of keys below kc, accumulated with carry chains (IADD3 + IADD3.X)
+#define PCB_LT(x) asm("{ .reg .u32 t; add.cc.u32 t, %1, %2; addc.u32 %0, %0, 0; }" : "+r"(cnt) : "r"(x), "r"(kc));
+            PCB_LT(ka.x) PCB_LT(ka.y) PCB_LT(ka.z) PCB_LT(ka.w) PCB_LT(kb.x) PCB_LT(kb.y) PCB_LT(kb.z) PCB_LT(kb.w)
+#undef PCB_LT
             cnt += __shfl_xor_sync(FULL, cnt, 16);
             unsigned bal = __ballot_sync(FULL, cnt < 8) & 0xFFFFu;
             if (__popc(bal) != 8) {                // a tie straddles the median (:362-371)
@@ -283,8 +297,9 @@ struct Dec {
     template <int T, int LIVE>
     __device__ __forceinline__ int decide(uint32_t infobyte, uint32_t fvbyte) {
         if ((infobyte >> T) & 1) return fork<LIVE>();
+        if (fvbyte == 0) { met += fmaxf(-A0, 0.f); return 0; }   // :413-418, frozen value 0
         const int fv = (fvbyte >> T) & 1;
-        met += fv ? fmaxf(A0, 0.f) : fmaxf(-A0, 0.f);   // :413-418
+        met += fv ? fmaxf(A0, 0.f) : fmaxf(-A0, 0.f);
         return fv;
     }
 

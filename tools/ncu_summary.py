@@ -1,0 +1,31 @@
+#!/usr/bin/env python
+"""Print the handful of ncu raw-page metrics this project tracks. usage: ncu_summary.py <rep> [frames]"""
+import csv
+import subprocess
+import sys
+
+rep = sys.argv[1]
+frames = int(sys.argv[2]) if len(sys.argv) > 2 else 0
+out = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+rows = list(csv.reader(out.splitlines()))
+hdr, units, vals = rows[0], rows[1], rows[2]
+d = {h: (v, u) for h, u, v in zip(hdr, units, vals)}
+keys = ["Kernel Name", "gpu__time_duration.sum", "launch__registers_per_thread", "launch__grid_size", "launch__block_size",
+        "launch__shared_mem_per_block_dynamic", "launch__occupancy_limit_shared_mem", "launch__occupancy_limit_registers",
+        "sm__warps_active.avg.pct_of_peak_sustained_active", "smsp__inst_executed.sum",
+        "smsp__issue_active.avg.pct_of_peak_sustained_active", "sm__inst_executed_pipe_alu.sum", "sm__inst_executed_pipe_fma.sum",
+        "sm__inst_executed_pipe_fmaheavy.sum", "sm__inst_executed_pipe_fmalite.sum",
+        "sm__inst_executed_pipe_lsu.sum", "sm__inst_executed_pipe_cbu.sum", "sm__inst_executed_pipe_adu.sum",
+        "sm__inst_executed_pipe_uniform.sum", "sm__inst_executed_pipe_xu.sum",
+        "sm__pipe_alu_cycles_active.avg.pct_of_peak_sustained_active", "sm__pipe_fma_cycles_active.avg.pct_of_peak_sustained_active",
+        "smsp__thread_inst_executed_per_inst_executed.ratio", "dram__bytes_read.sum", "dram__bytes_write.sum",
+        "l1tex__data_bank_conflicts_pipe_lsu_mem_shared.sum", "l1tex__data_pipe_lsu_wavefronts_mem_shared.sum",
+        "sm__cycles_elapsed.max"]
+for k in keys:
+    if k in d:
+        print(f"{k:70s} {d[k][0]} {d[k][1]}")
+for h in hdr:
+    if "issue_stalled" in h and h.endswith("per_issue_active.ratio"):
+        print(f"{h:90s} {d[h][0]}")
+if frames:
+    print("warp-instructions per frame:", float(d["smsp__inst_executed.sum"][0].replace(",", "")) / frames)
