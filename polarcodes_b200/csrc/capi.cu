@@ -80,7 +80,7 @@ static int configure(pcb_handle* h) {
     h->fast8 = h->decoder == 3 && h->L == 8 && scl8_supported(h->m) && !getenv("PCB_FORCE_GENERIC");
     if (h->fast8) {
         int best_w = 0;
-        for (int wpb = 1; wpb <= 12; wpb++) {
+        for (int wpb = 1; wpb <= 16; wpb++) {
             if (wenv && atoi(wenv) != wpb) continue;
             int bps = 0, wb = 0;
             if (scl8_occupancy(h->m, wpb, &bps, &wb) != cudaSuccess) { cudaGetLastError(); continue; }

@@ -7,12 +7,15 @@
 //    lane-local on every layer of size >= 4, so a whole f/g chain from a large layer down to
 //    size 4 needs no shuffle and no __syncwarp; the chunk of a lane is contiguous in shared
 //    memory ("sub-major" order) and moves as float4 / float2.
-//  * layers 0 (channel) and 1 are never stored: layer 2 is computed straight from y with the
-//    two top levels fused (phases 0, n/4, n/2, 3n/4), which saves half of the LLR storage.
-//  * layers of size 4, 2, 1 live in registers; a clone copies the live ones with shuffles.
+//  * layers 0 (channel), 1 and 2 are never stored: layer 3 is computed straight from y with
+//    the three top levels fused (every n/8 phases).  y is converted once per event and staged
+//    in the shared-memory region of layers 4.. (dead at those phases).  This cuts the LLR
+//    storage of a frame from 32 KB to 9.5 KB, i.e. 16 resident frames per SM instead of 6.
+//  * layers of size 4, 2, 1 live in registers; a clone copies them with shuffles.
 //  * lazy copy: slot p writes its own arrays; a per-path word holds, per layer, the slot to
 //    read from (3 bits per layer).  A clone copies that word.
-//  * prune: 16 candidates x 16 = 256 compares = 8 per lane on the metric bit patterns.
+//  * prune: ~85 % of the calls exit early (every penalised candidate above every unpenalised
+//    one); otherwise 16 candidates x 16 = 256 compares = 8 per lane on the metric bit patterns.
 #include "decode_common.cuh"
 #include "decode_launch.h"
 
@@ -25,7 +28,7 @@ constexpr unsigned FULL = 0xffffffffu;
 template <int M>
 struct Geo {
     static constexpr int N = 1 << M;
-    static constexpr int LTOP = 2;          // first stored LLR layer
+    static constexpr int LTOP = 3;          // first stored LLR layer (size N/8)
     static constexpr int LBOT = M - 3;      // last stored LLR layer (size 8); sizes 4,2,1 are registers
     static constexpr int NW = N / 32;       // partial-sum words per slot (heap: layer of size S at bits [S,2S))
     static constexpr int HS = NW + 1;       // padded slot stride of the heap (bank spread)
@@ -37,9 +40,9 @@ struct Geo {
         return o;
     }
     static constexpr int PFLOATS = off(LBOT + 1);
+    static constexpr bool STAGE = (PFLOATS - off(LTOP + 1)) >= N;   // y fits in the region of layers 4..
     static constexpr int XW = 8 * HS;                      // final codeword estimates (alias the LLR region)
     static constexpr int EW_MAX = N / 32;
-    // byte offsets inside the warp slice
     static constexpr int OFF_P = 0;
     static constexpr int P_BYTES = ((PFLOATS > XW + 8 * EW_MAX ? PFLOATS : XW + 8 * EW_MAX) * 4 + 15) & ~15;
     static constexpr int OFF_H = P_BYTES;
@@ -53,14 +56,59 @@ __device__ __forceinline__ float gs(float a, float b, uint32_t signbit) {
     return b + __uint_as_float(__float_as_uint(a) ^ signbit);
 }
 __device__ __forceinline__ uint32_t sgn(uint32_t w, int pos) { return (w << (31 - pos)) & 0x80000000u; }
+__device__ __forceinline__ float4 ff4(float4 a, float4 b) {
+    return make_float4(ff(a.x, b.x), ff(a.y, b.y), ff(a.z, b.z), ff(a.w, b.w));
+}
+// bits of the 4 elements at positions pos, pos+4, pos+8, pos+12 of cw
+__device__ __forceinline__ float4 gs4(float4 a, float4 b, uint32_t cw, int pos) {
+    return make_float4(gs(a.x, b.x, sgn(cw, pos)), gs(a.y, b.y, sgn(cw, pos + 4)), gs(a.z, b.z, sgn(cw, pos + 8)),
+                       gs(a.w, b.w, sgn(cw, pos + 12)));
+}
+
+// Slow part of the prune (SCLDecoderMinsum.cpp:342-399), one copy in the binary.
+// Returns u | take<<1 | srcp<<2 | any<<5: this slot's bit, whether the slot is re-used for a
+// clone, the slot it is cloned from, and whether any slot was re-used at all.
+__device__ __noinline__ uint32_t prune_core(float pf0, float pf1, int lane, uint32_t* keys, const unsigned char* lut) {
+    const int sub = lane >> 3, p = lane & 7;
+    // keys are stored complemented: key < kc  <=>  carry-out of (kc + ~key)
+    if (sub == 0) *reinterpret_cast<uint2*>(keys + 2 * p) = make_uint2(~__float_as_uint(pf0), ~__float_as_uint(pf1));
+    __syncwarp();
+    const uint32_t kc = __float_as_uint((sub & 1) ? pf1 : pf0);
+    const uint4 ka = *reinterpret_cast<const uint4*>(keys + 8 * (sub >> 1));
+    const uint4 kb = *reinterpret_cast<const uint4*>(keys + 8 * (sub >> 1) + 4);
+    int cnt = 0;   // number of keys below kc, accumulated with carry chains (IADD3 + IADD3.X)
+#define PCB_LT(x) asm("{ .reg .u32 t; add.cc.u32 t, %1, %2; addc.u32 %0, %0, 0; }" : "+r"(cnt) : "r"(x), "r"(kc));
+    PCB_LT(ka.x) PCB_LT(ka.y) PCB_LT(ka.z) PCB_LT(ka.w) PCB_LT(kb.x) PCB_LT(kb.y) PCB_LT(kb.z) PCB_LT(kb.w)
+#undef PCB_LT
+    cnt += __shfl_xor_sync(FULL, cnt, 16);
+    unsigned bal = __ballot_sync(FULL, cnt < 8) & 0xFFFFu;
+    if (__popc(bal) != 8) {                // a tie straddles the median (:362-371)
+        const bool in = (bal >> (lane & 15)) & 1;
+        const unsigned tkey = __reduce_max_sync(FULL, in ? kc : 0u);
+        const unsigned tb = __ballot_sync(FULL, in && kc == tkey) & 0xFFFFu;
+        const int need = 8 - (__popc(bal) - __popc(tb));
+        const unsigned t0 = tb & 0xFF, t1 = tb >> 8, lt = (1u << p) - 1;
+        const int before = __popc(t0 & lt) + __popc(t1 & lt) + ((sub & 1) ? ((t0 >> p) & 1) : 0);
+        bal = __ballot_sync(FULL, in && (kc < tkey || before < need)) & 0xFFFFu;
+    }
+    __syncwarp();
+    const unsigned k0m = bal & 0xFF, k1m = bal >> 8;
+    const unsigned nonem = ~(k0m | k1m) & 0xFF, bothm = k0m & k1m;
+    uint32_t r = ((k0m >> p) & 1) ? 0u : 1u;
+    if (nonem == 0) return r | ((uint32_t)p << 2);
+    // killed slots are pushed ascending (:372-376) and popped by the cloning parents in ascending
+    // order (:382-389): the j-th killed slot receives the clone of the j-th HIGHEST parent
+    if ((nonem >> p) & 1) r = 1u | 2u | ((uint32_t)lut[bothm * 4 + __popc(nonem & ((1u << p) - 1))] << 2);
+    else r |= (uint32_t)p << 2;
+    return r | 32u;
+}
 
 template <int M, typename YT>
 struct Dec {
     using G = Geo<M>;
-    // ---- per-lane state ----
     int lane, sub, p;
-    float* P;          // warp slice
-    uint32_t* H;
+    float* P;          // warp slice: LLR layers
+    uint32_t* H;       // partial-sum heaps
     uint32_t* keys;
     const unsigned char* lut;
     const YT* y;
@@ -72,49 +120,74 @@ struct Dec {
     __device__ __forceinline__ float* chunk(int lam, int slot) const {
         return P + G::off(lam) + (sub * 8 + slot) * G::cs(lam);
     }
-    __device__ __forceinline__ int pfield(int lam) const { return (pidx >> (3 * (lam - 2))) & 7; }
+    __device__ __forceinline__ int pfield(int lam) const { return (pidx >> (3 * (lam - G::LTOP))) & 7; }
     __device__ __forceinline__ int cfield(int lam) const { return (cidx >> (3 * (lam - 1))) & 7; }
-    __device__ __forceinline__ float ldy(int j) const { return (float)y[j]; }
-
-    // bits of partial-sum layer `lam` (size s >= 32) for this lane's elements j = sub + 4k,
-    // k in [8*w8, 8*w8+8): returned word has element k's bit at position 4*(k&7)
-    __device__ __forceinline__ uint32_t cword(int lam, int w8) const {
-        const int s = G::N >> lam;
-        return H[cfield(lam) * G::HS + (s >> 5) + w8] >> sub;
+    // word of partial-sum layer `lam` (size >= 32) holding this lane's elements k in [8*w8, 8*w8+8)
+    // of the sub-array starting at element `base`: element k's bit ends up at position 4*(k&7)
+    __device__ __forceinline__ uint32_t cword(int lam, int base, int w8) const {
+        return H[cfield(lam) * G::HS + ((G::N >> lam) >> 5) + (base >> 5) + w8] >> sub;
     }
 
-    // ---- layer 2 straight from the channel values (layers 0 and 1 are virtual) --------
-    // g1: layer 1 is a g-layer (second half of the codeword); g2: layer 2 is a g-layer
-    template <bool G1, bool G2>
-    __device__ __forceinline__ void top_chain() {
-        constexpr int Q = G::N / 4;           // layer-2 size
-        constexpr int C2 = G::c(2);
-        float* dst = chunk(2, p);
-#pragma unroll 2
-        for (int k0 = 0; k0 < C2; k0 += 8) {
-            uint32_t c1a = 0, c1b = 0, c2w = 0;
-            if (G1) {   // layer-1 bits j and j+Q: words (j>>5) and (j+Q)>>5 of the size-N/2 layer
-                const int s1 = G::N >> 1;
-                const uint32_t* h = H + cfield(1) * G::HS + (s1 >> 5);
-                c1a = h[k0 >> 3] >> sub;
-                c1b = h[(Q >> 5) + (k0 >> 3)] >> sub;
+    // ---- layer 3 straight from the channel values (layers 0, 1, 2 are virtual) ---------
+    // ev = i0 / (N/8) in 0..7: bit 2 -> layer 1 is a g-layer, bit 1 -> layer 2, bit 0 -> layer 3.
+    // L1[x] = op1(y[x], y[x+4E]), L2[x] = op2(L1[x], L1[x+2E]), L3[j] = op3(L2[j], L2[j+E]), E = N/8.
+    __device__ __forceinline__ void top3(int ev) {
+        constexpr int E = G::N / 8, C3 = G::c(3), E4 = E / 4;
+        const bool g1 = ev & 4, g2 = ev & 2, g3 = ev & 1;
+        float* Y = P + G::off(G::LTOP + 1);      // staging area: [sub][N/4] floats, element j at [j&3][j>>2]
+        if (G::STAGE) {
+            __syncwarp();                        // everyone is done with layers 4.. of the previous subtree
+            for (int q = lane; q < G::N / 4; q += 32) {
+                float v0, v1, v2, v3;
+                if (sizeof(YT) == 8) {
+                    const double2 a = *reinterpret_cast<const double2*>(y + 4 * q);
+                    const double2 b = *reinterpret_cast<const double2*>(y + 4 * q + 2);
+                    v0 = (float)a.x; v1 = (float)a.y; v2 = (float)b.x; v3 = (float)b.y;   // :406-408
+                } else {
+                    const float4 a = *reinterpret_cast<const float4*>(y + 4 * q);
+                    v0 = a.x; v1 = a.y; v2 = a.z; v3 = a.w;
+                }
+                Y[q] = v0; Y[G::N / 4 + q] = v1; Y[2 * (G::N / 4) + q] = v2; Y[3 * (G::N / 4) + q] = v3;
             }
-            if (G2) c2w = cword(2, k0 >> 3);
+            __syncwarp();
+        }
+        const float* ys = Y + sub * (G::N / 4);
+        float* dst = chunk(3, p);
+#pragma unroll 1
+        for (int k0 = 0; k0 < C3; k0 += 8) {
+            uint32_t c1[4] = {0, 0, 0, 0}, c2[2] = {0, 0}, c3w = 0;
+            if (g1) {
+#pragma unroll
+                for (int t = 0; t < 4; t++) c1[t] = cword(1, t * E, k0 >> 3);
+            }
+            if (g2) { c2[0] = cword(2, 0, k0 >> 3); c2[1] = cword(2, E, k0 >> 3); }
+            if (g3) c3w = cword(3, 0, k0 >> 3);
 #pragma unroll
             for (int kk = 0; kk < 8; kk += 4) {
-                float o[4];
+                float4 yv[8];
 #pragma unroll
-                for (int e = 0; e < 4; e++) {
-                    const int k = k0 + kk + e, j = sub + 4 * k;
-                    const float y0 = ldy(j), y1 = ldy(j + Q), y2 = ldy(j + 2 * Q), y3 = ldy(j + 3 * Q);
-                    float la, lb;
-                    if (G1) { la = gs(y0, y2, sgn(c1a, 4 * (kk + e))); lb = gs(y1, y3, sgn(c1b, 4 * (kk + e))); }
-                    else { la = ff(y0, y2); lb = ff(y1, y3); }
-                    o[e] = G2 ? gs(la, lb, sgn(c2w, 4 * (kk + e))) : ff(la, lb);
+                for (int t = 0; t < 8; t++) {
+                    if (G::STAGE) yv[t] = *reinterpret_cast<const float4*>(ys + t * E4 + k0 + kk);
+                    else {
+                        const int j = sub + 4 * (k0 + kk) + t * E;
+                        yv[t] = make_float4((float)y[j], (float)y[j + 4], (float)y[j + 8], (float)y[j + 12]);
+                    }
                 }
-                *reinterpret_cast<float4*>(dst + k0 + kk) = make_float4(o[0], o[1], o[2], o[3]);
+                float4 l1[4], l2[2], o;
+                if (g1) {
+#pragma unroll
+                    for (int t = 0; t < 4; t++) l1[t] = gs4(yv[t], yv[t + 4], c1[t], 4 * kk);
+                } else {
+#pragma unroll
+                    for (int t = 0; t < 4; t++) l1[t] = ff4(yv[t], yv[t + 4]);
+                }
+                if (g2) { l2[0] = gs4(l1[0], l1[2], c2[0], 4 * kk); l2[1] = gs4(l1[1], l1[3], c2[1], 4 * kk); }
+                else { l2[0] = ff4(l1[0], l1[2]); l2[1] = ff4(l1[1], l1[3]); }
+                o = g3 ? gs4(l2[0], l2[1], c3w, 4 * kk) : ff4(l2[0], l2[1]);
+                *reinterpret_cast<float4*>(dst + k0 + kk) = o;
             }
         }
+        if (G::STAGE) __syncwarp();              // staging area is overwritten by layer 4 next
     }
 
     // ---- one stored layer from the previous stored layer ------------------------------
@@ -126,32 +199,21 @@ struct Dec {
         const float* src = chunk(LAM - 1, slot);
         float* dst = chunk(LAM, p);
         if constexpr (C >= 8) {
-#pragma unroll 2
+#pragma unroll 1
             for (int k0 = 0; k0 < C; k0 += 8) {
                 uint32_t cw = 0;
-                if (ISG) cw = cword(LAM, k0 >> 3);
+                if (ISG) cw = cword(LAM, 0, k0 >> 3);
 #pragma unroll
                 for (int kk = 0; kk < 8; kk += 4) {
                     const float4 a = *reinterpret_cast<const float4*>(src + k0 + kk);
                     const float4 b = *reinterpret_cast<const float4*>(src + C + k0 + kk);
-                    float4 o;
-                    if (ISG) {
-                        o.x = gs(a.x, b.x, sgn(cw, 4 * kk)); o.y = gs(a.y, b.y, sgn(cw, 4 * kk + 4));
-                        o.z = gs(a.z, b.z, sgn(cw, 4 * kk + 8)); o.w = gs(a.w, b.w, sgn(cw, 4 * kk + 12));
-                    } else { o.x = ff(a.x, b.x); o.y = ff(a.y, b.y); o.z = ff(a.z, b.z); o.w = ff(a.w, b.w); }
-                    *reinterpret_cast<float4*>(dst + k0 + kk) = o;
+                    *reinterpret_cast<float4*>(dst + k0 + kk) = ISG ? gs4(a, b, cw, 4 * kk) : ff4(a, b);
                 }
             }
         } else if constexpr (C == 4) {        // size 16: bits 16 + sub + 4k of w0
             const float4 a = *reinterpret_cast<const float4*>(src);
             const float4 b = *reinterpret_cast<const float4*>(src + 4);
-            float4 o;
-            if (ISG) {
-                const uint32_t cw = w0 >> (16 + sub);
-                o.x = gs(a.x, b.x, sgn(cw, 0)); o.y = gs(a.y, b.y, sgn(cw, 4));
-                o.z = gs(a.z, b.z, sgn(cw, 8)); o.w = gs(a.w, b.w, sgn(cw, 12));
-            } else { o.x = ff(a.x, b.x); o.y = ff(a.y, b.y); o.z = ff(a.z, b.z); o.w = ff(a.w, b.w); }
-            *reinterpret_cast<float4*>(dst) = o;
+            *reinterpret_cast<float4*>(dst) = ISG ? gs4(a, b, w0 >> (16 + sub), 0) : ff4(a, b);
         } else {                              // C == 2, size 8: bits 8 + sub + 4k of w0
             const float4 ab = *reinterpret_cast<const float4*>(src);   // a0 a1 b0 b1
             float2 o;
@@ -163,42 +225,32 @@ struct Dec {
         }
     }
 
+    // g at layer ll (one of LTOP+1..LBOT); every g variant appears once in the binary
     template <int LAM>
-    __device__ __forceinline__ void f_down() {   // f layers LAM..LBOT
-        if constexpr (LAM <= G::LBOT) {
-            layer<LAM, false>();
-            f_down<LAM + 1>();
+    __device__ __forceinline__ void g_dispatch(int ll) {
+        if constexpr (LAM > G::LTOP) {
+            if (ll == LAM) layer<LAM, true>();
+            else g_dispatch<LAM - 1>(ll);
         }
     }
+    // f layers ll+1..LBOT; every f variant appears once in the binary
     template <int LAM>
-    __device__ __forceinline__ void chain_g() {  // g at LAM (3 <= LAM <= LBOT), then f below
-        layer<LAM, true>();
-        f_down<LAM + 1>();
-    }
-    template <int LAM>
-    __device__ __forceinline__ void chain_dispatch(int ll) {
+    __device__ __forceinline__ void f_below(int ll) {
         if constexpr (LAM <= G::LBOT) {
-            if (ll == LAM) chain_g<LAM>();
-            else chain_dispatch<LAM + 1>(ll);
+            if (ll < LAM) layer<LAM, false>();
+            f_below<LAM + 1>(ll);
         }
     }
 
     // LLR work at the first phase i0 = 8*blk of a size-8 subtree, down to layer LBOT
     __device__ __forceinline__ void upper(int blk) {
+        const int z = blk ? (__ffs(blk) - 1) : 31;
         int ll;
-        if (blk == 0) { top_chain<false, false>(); f_down<3>(); ll = 2; }
-        else {
-            ll = G::LBOT - (__ffs(blk) - 1);
-            if (ll <= 2) {
-                if (ll == 1) top_chain<true, false>();
-                else if (blk & (G::N / 16)) top_chain<true, true>();
-                else top_chain<false, true>();
-                f_down<3>();
-                ll = 2;
-            } else chain_dispatch<3>(ll);
-        }
+        if (z >= M - 6) { top3(blk >> (M - 6)); ll = G::LTOP; }     // i0 is a multiple of N/8
+        else { ll = G::LBOT - z; g_dispatch<G::LBOT>(ll); }
+        f_below<G::LTOP + 1>(ll);
         // layers >= ll are now this slot's own
-        const uint32_t low = (1u << (3 * (ll - 2))) - 1;
+        const uint32_t low = (1u << (3 * (ll - G::LTOP))) - 1;
         pidx = (pidx & low) | ((0x9249249u * (uint32_t)p) & ~low);
     }
 
@@ -221,9 +273,9 @@ struct Dec {
     }
 
     // ---- fork / prune of one information bit (SCLDecoderMinsum.cpp:315-400) ----------
-    // LIVE: bit0 A2 live, bit1 A1 live after this phase.  Returns this slot's bit.
-    template <int LIVE>
     __device__ __forceinline__ int fork() {
+        uint32_t r;
+        float pf0, pf1;
         if (nact == 8) {
             // Fast exit (no kill, no clone): the candidates of path p are {met, met + |llr|}.  If
             // every penalised candidate is strictly above every unpenalised one, the L smallest
@@ -233,70 +285,39 @@ struct Dec {
             const unsigned maxlo = __reduce_max_sync(FULL, __float_as_uint(met));
             const unsigned minhi = __reduce_min_sync(FULL, __float_as_uint(hi));
             if (maxlo < minhi) return A0 < 0.f ? 1 : 0;
-        }
-        const float pf0 = met + fmaxf(-A0, 0.f);   // pen(llr,0) = |llr| iff llr < 0
-        const float pf1 = met + fmaxf(A0, 0.f);    // pen(llr,1) = |llr| iff llr > 0
-        int u;
-        int srcp = p;
-        bool take = false;
-        if (nact < 8) {                            // growth (:329-341)
+            pf0 = met + fmaxf(-A0, 0.f);   // pen(llr,0) = |llr| iff llr < 0
+            pf1 = met + fmaxf(A0, 0.f);    // pen(llr,1) = |llr| iff llr > 0
+            r = prune_core(pf0, pf1, lane, keys, lut);
+        } else {                           // growth (:329-341): parent q clones into 2*pbase-1-q
+            pf0 = met + fmaxf(-A0, 0.f);
+            pf1 = met + fmaxf(A0, 0.f);
             const int pbase = 8 - nact;
-            take = p >= pbase - nact && p < pbase;
-            srcp = take ? (2 * pbase - 1 - p) : p;
-            u = 0; met = pf0;
+            const bool take = p >= pbase - nact && p < pbase;
+            r = take ? (3u | ((uint32_t)(2 * pbase - 1 - p) << 2)) : ((uint32_t)p << 2);
+            r |= 32u;
             nact *= 2;
-        } else {
-            // keys are stored complemented: key < kc  <=>  carry-out of (kc + ~key)
-            if (sub == 0) *reinterpret_cast<uint2*>(keys + 2 * p) = make_uint2(~__float_as_uint(pf0), ~__float_as_uint(pf1));
-            __syncwarp();
-            const uint32_t kc = __float_as_uint((sub & 1) ? pf1 : pf0);
-            const uint4 ka = *reinterpret_cast<const uint4*>(keys + 8 * (sub >> 1));
-            const uint4 kb = *reinterpret_cast<const uint4*>(keys + 8 * (sub >> 1) + 4);
-            int cnt = 0;   // number of keys below kc, accumulated with carry chains (IADD3 + IADD3.X)
-#define PCB_LT(x) asm("{ .reg .u32 t; add.cc.u32 t, %1, %2; addc.u32 %0, %0, 0; }" : "+r"(cnt) : "r"(x), "r"(kc));
-            PCB_LT(ka.x) PCB_LT(ka.y) PCB_LT(ka.z) PCB_LT(ka.w) PCB_LT(kb.x) PCB_LT(kb.y) PCB_LT(kb.z) PCB_LT(kb.w)
-#undef PCB_LT
-            cnt += __shfl_xor_sync(FULL, cnt, 16);
-            unsigned bal = __ballot_sync(FULL, cnt < 8) & 0xFFFFu;
-            if (__popc(bal) != 8) {                // a tie straddles the median (:362-371)
-                const bool in = (bal >> (lane & 15)) & 1;
-                const unsigned tkey = __reduce_max_sync(FULL, in ? kc : 0u);
-                const unsigned tb = __ballot_sync(FULL, in && kc == tkey) & 0xFFFFu;
-                const int need = 8 - (__popc(bal) - __popc(tb));
-                const unsigned t0 = tb & 0xFF, t1 = tb >> 8, lt = (1u << p) - 1;
-                const int before = __popc(t0 & lt) + __popc(t1 & lt) + ((sub & 1) ? ((t0 >> p) & 1) : 0);
-                bal = __ballot_sync(FULL, in && (kc < tkey || before < need)) & 0xFFFFu;
-            }
-            __syncwarp();
-            const unsigned k0m = bal & 0xFF, k1m = bal >> 8;
-            const unsigned nonem = ~(k0m | k1m) & 0xFF, bothm = k0m & k1m;
-            const bool k0 = (k0m >> p) & 1;
-            u = k0 ? 0 : 1;
-            met = k0 ? pf0 : pf1;
-            if (nonem == 0) return u;
-            take = (nonem >> p) & 1;
-            if (take) srcp = lut[bothm * 4 + __popc(nonem & ((1u << p) - 1))];
         }
-        // clones: copy the parent's state (:145-156 without copying arrays)
-        __syncwarp();   // orders the parent's shared-memory writes before the clone's lazy reads
-        const int sl = (lane & 24) | srcp;
-        const float m1 = __shfl_sync(FULL, pf1, sl);
-        const uint32_t pi = __shfl_sync(FULL, pidx, sl);
-        const uint32_t ci = __shfl_sync(FULL, cidx, sl);
-        const uint32_t ww = __shfl_sync(FULL, w0, sl);
-        if (take) { met = m1; pidx = pi; cidx = ci; w0 = ww; u = 1; }
-        if (LIVE & 1) { const float t = __shfl_sync(FULL, A2, sl); if (take) A2 = t; }
-        if (LIVE & 2) {
+        int u = r & 1;
+        met = u ? pf1 : pf0;
+        if (r & 32u) {
+            // clones copy the parent's state (:145-156 without copying arrays)
+            __syncwarp();   // orders the parent's shared-memory writes before the clone's lazy reads
+            const int sl = (lane & 24) | ((r >> 2) & 7);
+            const float m1 = __shfl_sync(FULL, pf1, sl);
+            const uint32_t pi = __shfl_sync(FULL, pidx, sl);
+            const uint32_t ci = __shfl_sync(FULL, cidx, sl);
+            const uint32_t ww = __shfl_sync(FULL, w0, sl);
+            const float t2 = __shfl_sync(FULL, A2, sl);
             const float t0 = __shfl_sync(FULL, A1_0, sl), t1 = __shfl_sync(FULL, A1_1, sl);
-            if (take) { A1_0 = t0; A1_1 = t1; }
+            if (r & 2u) { met = m1; pidx = pi; cidx = ci; w0 = ww; A2 = t2; A1_0 = t0; A1_1 = t1; }
         }
         return u;
     }
 
     // decision at phase i0+T with the leaf LLR in A0
-    template <int T, int LIVE>
+    template <int T>
     __device__ __forceinline__ int decide(uint32_t infobyte, uint32_t fvbyte) {
-        if ((infobyte >> T) & 1) return fork<LIVE>();
+        if ((infobyte >> T) & 1) return fork();
         if (fvbyte == 0) { met += fmaxf(-A0, 0.f); return 0; }   // :413-418, frozen value 0
         const int fv = (fvbyte >> T) & 1;
         met += fv ? fmaxf(A0, 0.f) : fmaxf(-A0, 0.f);
@@ -318,6 +339,7 @@ struct Dec {
         // destination layer m-d2 sits at heap words [D/32, 2D/32); layer 0 (the final codeword
         // estimate, written at the very last phase) goes to the then-dead LLR region instead
         uint32_t* hp = (d2 == M) ? (reinterpret_cast<uint32_t*>(P) + p * G::HS - G::NW) : (H + p * G::HS);
+        __syncwarp();
         if (sub == 0) hp[2 * D / 32 - 1] = T;
         __syncwarp();
         for (int w = 32; w < D; w <<= 1) {
@@ -338,32 +360,32 @@ struct Dec {
         int u;
         // t = 0
         a2_from_a3(false); a1_from_a2(false); A0 = ff(A1_0, A1_1);
-        u = decide<0, 3>(ib, fb); w0 = (w0 & ~2u) | ((uint32_t)u << 1);
+        u = decide<0>(ib, fb); w0 = (w0 & ~2u) | ((uint32_t)u << 1);
         // t = 1
         A0 = gs(A1_0, A1_1, sgn(w0, 1));
-        u = decide<1, 1>(ib, fb);
+        u = decide<1>(ib, fb);
         { uint32_t T = (((w0 >> 1) ^ u) & 1u) | ((uint32_t)u << 1); w0 = (w0 & ~0xCu) | (T << 2); }
         // t = 2
         a1_from_a2(true); A0 = ff(A1_0, A1_1);
-        u = decide<2, 2>(ib, fb); w0 = (w0 & ~2u) | ((uint32_t)u << 1);
+        u = decide<2>(ib, fb); w0 = (w0 & ~2u) | ((uint32_t)u << 1);
         // t = 3
         A0 = gs(A1_0, A1_1, sgn(w0, 1));
-        u = decide<3, 0>(ib, fb);
+        u = decide<3>(ib, fb);
         { uint32_t T = (((w0 >> 1) ^ u) & 1u) | ((uint32_t)u << 1); T = (((w0 >> 2) ^ T) & 3u) | (T << 2);
           w0 = (w0 & ~0xF0u) | (T << 4); }
         // t = 4
         a2_from_a3(true); a1_from_a2(false); A0 = ff(A1_0, A1_1);
-        u = decide<4, 3>(ib, fb); w0 = (w0 & ~2u) | ((uint32_t)u << 1);
+        u = decide<4>(ib, fb); w0 = (w0 & ~2u) | ((uint32_t)u << 1);
         // t = 5
         A0 = gs(A1_0, A1_1, sgn(w0, 1));
-        u = decide<5, 1>(ib, fb);
+        u = decide<5>(ib, fb);
         { uint32_t T = (((w0 >> 1) ^ u) & 1u) | ((uint32_t)u << 1); w0 = (w0 & ~0xCu) | (T << 2); }
         // t = 6
         a1_from_a2(true); A0 = ff(A1_0, A1_1);
-        u = decide<6, 2>(ib, fb); w0 = (w0 & ~2u) | ((uint32_t)u << 1);
+        u = decide<6>(ib, fb); w0 = (w0 & ~2u) | ((uint32_t)u << 1);
         // t = 7
         A0 = gs(A1_0, A1_1, sgn(w0, 1));
-        u = decide<7, 0>(ib, fb);
+        u = decide<7>(ib, fb);
         setbit_last(blk, u);
     }
 };
@@ -371,7 +393,7 @@ struct Dec {
 }  // namespace s8
 
 template <int M, typename YT>
-__global__ void __launch_bounds__(384, 1) decode_scl8_kernel(const DecodeArgs A) {
+__global__ void __launch_bounds__(512, 1) decode_scl8_kernel(const DecodeArgs A) {
     using G = s8::Geo<M>;
     extern __shared__ __align__(16) unsigned char smem_raw[];
     __shared__ unsigned short crc_tab[256];
@@ -412,6 +434,7 @@ __global__ void __launch_bounds__(384, 1) decode_scl8_kernel(const DecodeArgs A)
         D.met = 0.f; D.pidx = 0; D.cidx = 0; D.w0 = 0; D.nact = 1;
         D.A2 = D.A1_0 = D.A1_1 = D.A0 = 0.f;
         uint32_t iw = 0, fw = 0;
+#pragma unroll 1
         for (int blk = 0; blk < n / 8; ++blk) {
             if ((blk & 3) == 0) { iw = __ldg(A.info_mask + (blk >> 2)); fw = __ldg(A.frozen_val + (blk >> 2)); }
             D.upper(blk);
@@ -499,12 +522,13 @@ cudaError_t launch_decode_scl8(const DecodeArgs& a, int blocks, int wpb, cudaStr
     return cudaErrorInvalidValue;
 }
 
+// occupancy of the more register-hungry (double input) variant, so one launch shape serves both
 cudaError_t scl8_occupancy(int m, int wpb, int* bps, int* warp_bytes) {
     switch (m) {
-        case 8: return occ_m<8, float>(wpb, bps, warp_bytes);
-        case 9: return occ_m<9, float>(wpb, bps, warp_bytes);
-        case 10: return occ_m<10, float>(wpb, bps, warp_bytes);
-        case 11: return occ_m<11, float>(wpb, bps, warp_bytes);
+        case 8: return occ_m<8, double>(wpb, bps, warp_bytes);
+        case 9: return occ_m<9, double>(wpb, bps, warp_bytes);
+        case 10: return occ_m<10, double>(wpb, bps, warp_bytes);
+        case 11: return occ_m<11, double>(wpb, bps, warp_bytes);
     }
     return cudaErrorInvalidValue;
 }
