@@ -1,0 +1,94 @@
+"""GPU tests of the C++ host side: the reference-signature shim (B = 1 per call) reproduces the
+golden outputs of the reference, and the conf.txt driver writes a reference-format result file
+whose FER agrees with the published pc.txt numbers."""
+import glob
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+from conftest import GOLDEN, ROOT
+
+pytestmark = pytest.mark.gpu
+HOST = os.path.join(ROOT, "polarcodes_b200", "host")
+
+SHIM_PROG = r"""
+#include <cstdio>
+#include <vector>
+#include "polar_b200_shim.h"
+// argv: decoder n k crc L frames ; stdin: mask[n] ints, sigma, y[frames][n] doubles (binary)
+int main(int argc, char** argv) {
+    int dec = atoi(argv[1]), n = atoi(argv[2]), k = atoi(argv[3]), crc = atoi(argv[4]), L = atoi(argv[5]), F = atoi(argv[6]);
+    std::vector<int> mask(n); double sigma;
+    fread(mask.data(), 4, n, stdin); fread(&sigma, 8, 1, stdin);
+    std::vector<double> y(n); std::vector<int> sol(n);
+    if (dec == 3) SCLDecoderMinsum::InitializeDataStructures(n, L, k, crc);
+    int stride = dec == 3 ? k + crc : n;
+    for (int f = 0; f < F; f++) {
+        fread(y.data(), 8, n, stdin);
+        if (dec == 1) SCDecoder::Decode(n, y.data(), nullptr, nullptr, sol.data(), mask, sigma);
+        else if (dec == 2) SCDecoderMinsum::Decode(n, y.data(), nullptr, nullptr, sol.data(), mask);
+        else SCLDecoderMinsum::Decode(n, L, y.data(), nullptr, sol.data(), mask, 2);
+        fwrite(sol.data(), 4, stride, stdout);
+    }
+    // Encode through the shim: result in encTree[0]
+    std::vector<int> u(n, 0), out(n); u[n - 1] = 1; int* tree[1] = {out.data()};
+    Encode(n, u.data(), tree, false);
+    for (int i = 0; i < n; i++) if (out[i] != 1) return 3;   // last row of F^(x)m is all ones
+    return 0;
+}
+"""
+
+
+@pytest.fixture(scope="module")
+def shim_exe(tmp_path_factory):
+    d = tmp_path_factory.mktemp("shim")
+    (d / "prog.cpp").write_text(SHIM_PROG)
+    lib = os.path.join(ROOT, "polarcodes_b200")
+    subprocess.check_call(["g++", "-std=c++17", "-O1", "-w", "-I", HOST, str(d / "prog.cpp"), "-L", lib, "-lpolar_b200",
+                           f"-Wl,-rpath,{lib}", "-Wl,-rpath,/usr/local/cuda/lib64", "-o", str(d / "prog")])
+    return str(d / "prog")
+
+
+@pytest.mark.parametrize("name", ["scl8_1024_512_crc16", "scl4_256_128_crc8", "scms_1024_512", "scl2_64_32_crc0"])
+def test_shim_matches_golden(shim_exe, name):
+    g = np.load(os.path.join(GOLDEN, name + ".npz"))
+    dec, n, k, crc, L = (int(g[x]) for x in ("decoder", "n", "k", "crc", "L"))
+    F = min(12, g["y"].shape[0])
+    blob = g["mask"].astype(np.int32).tobytes() + np.float64(g["sigma"]).tobytes() + g["y"][:F].astype(np.float64).tobytes()
+    r = subprocess.run([shim_exe] + [str(v) for v in (dec, n, k, crc, L, F)], input=blob, capture_output=True)
+    assert r.returncode == 0, r.stderr.decode()
+    sol = np.frombuffer(r.stdout, np.int32).reshape(F, -1)
+    assert (sol == g["sol"][:F]).all()
+
+
+def test_driver_reproduces_pc_txt(tmp_path):
+    """pc.txt:1-9 col 2 (SC min-sum (1024,512), BEC construction): 0.3611 @1.5 dB, 0.1255 @2 dB, 0.0351 @2.5 dB."""
+    subprocess.check_call(["make", "-s", "-C", HOST])
+    (tmp_path / "conf.txt").write_text("1\n1024\n512\n40000\n2\n1\n1\n0\n2\n3\n1.5 2 2.5\n")
+    env = dict(os.environ, PCB_CSV=str(tmp_path / "out.csv"))
+    r = subprocess.run([os.path.join(HOST, "polarcodes_driver")], cwd=tmp_path, capture_output=True, text=True, env=env)
+    assert r.returncode == 0, r.stderr
+    files = glob.glob(str(tmp_path / "SC_1_1024_512_L1_CRC0_*.txt"))
+    assert len(files) == 1
+    lines = open(files[0]).read().split("\n")
+    int(lines[0])   # elapsed ticks, PolarCodes.cpp:304
+    got = {float(a): float(b) for a, b in (ln.split("\t") for ln in lines[1:] if ln)}
+    want = {1.5: 0.3611, 2.0: 0.1255, 2.5: 0.0351}
+    for snr, p in want.items():
+        tol = 4 * np.sqrt(p * (1 - p) * (1 / 40000 + 1 / 10000))
+        assert abs(got[snr] - p) < tol, (snr, got[snr], p)
+    csv = open(tmp_path / "out.csv").read().strip().split("\n")
+    assert csv[0].startswith("snr_db,frames,frame_errors,bit_errors") and len(csv) == 4
+
+
+def test_driver_scl_crc16_and_throughput_mode(tmp_path):
+    subprocess.check_call(["make", "-s", "-C", HOST])
+    (tmp_path / "conf.txt").write_text("2\n1024\n512\n20000\n3\n2\n8\n16\n2\n1\n2\n")
+    r = subprocess.run([os.path.join(HOST, "polarcodes_driver")], cwd=tmp_path, capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    files = glob.glob(str(tmp_path / "SC_2_1024_512_L8_CRC16_*.txt"))
+    assert len(files) == 1
+    ticks = float(open(files[0]).read().split("\n")[1].split("\t")[1])
+    assert ticks > 0   # decode time of 20000 frames in clock ticks
