@@ -24,8 +24,9 @@ int fail(int code, const char* fmt, ...) {
 cudaError_t decode_generic_occupancy(int L, int mode, int fp64, int wpb, size_t smem, int* bps);
 // tuned list-8 kernel (decode_scl8.cu)
 bool scl8_supported(int m);
-cudaError_t launch_decode_scl8(const DecodeArgs& a, int blocks, int wpb, cudaStream_t st);
-cudaError_t scl8_occupancy(int m, int wpb, int* bps, int* warp_bytes);
+cudaError_t launch_decode_scl8(const DecodeArgs& a, const uint32_t* info_w, const uint32_t* fv_w, int blocks,
+                               cudaStream_t st);
+cudaError_t scl8_occupancy(int m, int* bps, int* warp_bytes);
 }  // namespace pcb
 
 using namespace pcb;
@@ -64,6 +65,7 @@ struct pcb_handle {
     size_t enc_frames = 0;
     int *d_eu = nullptr, *d_ex = nullptr;
     uint64_t launches = 0;
+    std::vector<uint32_t> h_info_w, h_fv_w;   // host copies of the mask words (kernel parameters of the list-8 kernel)
 };
 
 static int max_blocks(const pcb_handle* h) { return h->sm_count * h->bps; }
@@ -79,14 +81,9 @@ static int configure(pcb_handle* h) {
     const char* wenv = getenv("PCB_WPB");
     h->fast8 = h->decoder == 3 && h->L == 8 && scl8_supported(h->m) && !getenv("PCB_FORCE_GENERIC");
     if (h->fast8) {
-        int best_w = 0;
-        for (int wpb = 1; wpb <= 16; wpb++) {
-            if (wenv && atoi(wenv) != wpb) continue;
-            int bps = 0, wb = 0;
-            if (scl8_occupancy(h->m, wpb, &bps, &wb) != cudaSuccess) { cudaGetLastError(); continue; }
-            if (bps * wpb > best_w) { best_w = bps * wpb; h->wpb = wpb; h->bps = bps; h->warp_smem = wb; }
-        }
-        if (best_w == 0) return fail(PCB_EINVAL, "list-8 kernel does not fit one SM");
+        int bps = 0, wb = 0;   // one warp (= one frame) per block
+        if (scl8_occupancy(h->m, &bps, &wb) != cudaSuccess || bps == 0) { cudaGetLastError(); return fail(PCB_EINVAL, "list-8 kernel does not fit one SM"); }
+        h->wpb = 1; h->bps = bps; h->warp_smem = wb;
         h->ls = 2;
         h->scratch_per_warp = 0;
         return PCB_OK;
@@ -233,6 +230,7 @@ int pcb_set_code(pcb_handle* h, const int* frozen_mask, double sigma) {
     CK(cudaMemcpyAsync(h->d_frozen_val, fv.data(), NW * 4, cudaMemcpyHostToDevice, h->sc));
     CK(cudaMemcpyAsync(h->d_info_pos, pos.data(), (size_t)n * 2, cudaMemcpyHostToDevice, h->sc));
     CK(cudaStreamSynchronize(h->sc));
+    h->h_info_w = im; h->h_fv_w = fv;
     h->sigma = sigma;
     h->code_set = true;
     return PCB_OK;
@@ -269,7 +267,7 @@ static cudaError_t launch(pcb_handle* h, const DecodeArgs& a, cudaStream_t st) {
     int blocks = (a.B + h->wpb - 1) / h->wpb;
     if (blocks > max_blocks(h)) blocks = max_blocks(h);
     h->launches++;
-    if (h->fast8) return launch_decode_scl8(a, blocks, h->wpb, st);
+    if (h->fast8) return launch_decode_scl8(a, h->h_info_w.data(), h->h_fv_w.data(), blocks, st);
     return launch_decode_generic(a, h->L, h->decoder, h->fp64, blocks, h->wpb, st);
 }
 

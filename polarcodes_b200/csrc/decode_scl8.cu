@@ -94,13 +94,11 @@ __device__ __noinline__ uint32_t prune_core(float pf0, float pf1, int lane, uint
     __syncwarp();
     const unsigned k0m = bal & 0xFF, k1m = bal >> 8;
     const unsigned nonem = ~(k0m | k1m) & 0xFF, bothm = k0m & k1m;
-    uint32_t r = ((k0m >> p) & 1) ? 0u : 1u;
-    if (nonem == 0) return r | ((uint32_t)p << 2);
+    const uint32_t r = ((k0m >> p) & 1) ? 0u : 1u;
     // killed slots are pushed ascending (:372-376) and popped by the cloning parents in ascending
     // order (:382-389): the j-th killed slot receives the clone of the j-th HIGHEST parent
-    if ((nonem >> p) & 1) r = 1u | 2u | ((uint32_t)lut[bothm * 4 + __popc(nonem & ((1u << p) - 1))] << 2);
-    else r |= (uint32_t)p << 2;
-    return r | 32u;
+    const uint32_t src = lut[bothm * 4 + (__popc(nonem & ((1u << p) - 1)) & 3)];
+    return ((nonem >> p) & 1) ? (3u | (src << 2)) : (r | ((uint32_t)p << 2));
 }
 
 template <int M, typename YT>
@@ -115,7 +113,7 @@ struct Dec {
     float met;
     uint32_t pidx, cidx, w0;
     float A2, A1_0, A1_1, A0;
-    int nact;
+    int ninfo;         // information bits seen so far (warp-uniform): the list is full from the 4th on
 
     __device__ __forceinline__ float* chunk(int lam, int slot) const {
         return P + G::off(lam) + (sub * 8 + slot) * G::cs(lam);
@@ -276,7 +274,7 @@ struct Dec {
     __device__ __forceinline__ int fork() {
         uint32_t r;
         float pf0, pf1;
-        if (nact == 8) {
+        if (ninfo >= 3) {
             // Fast exit (no kill, no clone): the candidates of path p are {met, met + |llr|}.  If
             // every penalised candidate is strictly above every unpenalised one, the L smallest
             // are exactly the L unpenalised ones (no tie possible), each path keeps its likely
@@ -291,26 +289,25 @@ struct Dec {
         } else {                           // growth (:329-341): parent q clones into 2*pbase-1-q
             pf0 = met + fmaxf(-A0, 0.f);
             pf1 = met + fmaxf(A0, 0.f);
-            const int pbase = 8 - nact;
+            const int nact = 1 << ninfo, pbase = 8 - nact;
             const bool take = p >= pbase - nact && p < pbase;
             r = take ? (3u | ((uint32_t)(2 * pbase - 1 - p) << 2)) : ((uint32_t)p << 2);
-            r |= 32u;
-            nact *= 2;
+            ninfo++;
         }
         int u = r & 1;
         met = u ? pf1 : pf0;
-        if (r & 32u) {
-            // clones copy the parent's state (:145-156 without copying arrays)
-            __syncwarp();   // orders the parent's shared-memory writes before the clone's lazy reads
-            const int sl = (lane & 24) | ((r >> 2) & 7);
-            const float m1 = __shfl_sync(FULL, pf1, sl);
-            const uint32_t pi = __shfl_sync(FULL, pidx, sl);
-            const uint32_t ci = __shfl_sync(FULL, cidx, sl);
-            const uint32_t ww = __shfl_sync(FULL, w0, sl);
-            const float t2 = __shfl_sync(FULL, A2, sl);
-            const float t0 = __shfl_sync(FULL, A1_0, sl), t1 = __shfl_sync(FULL, A1_1, sl);
-            if (r & 2u) { met = m1; pidx = pi; cidx = ci; w0 = ww; A2 = t2; A1_0 = t0; A1_1 = t1; }
-        }
+        // clones copy the parent's state (:145-156 without copying arrays).  Unconditional: the
+        // non-trivial path nearly always re-uses a slot, and a data-dependent branch around warp
+        // synchronising instructions would make the compiler give up on proving convergence.
+        __syncwarp();   // orders the parent's shared-memory writes before the clone's lazy reads
+        const int sl = (lane & 24) | ((r >> 2) & 7);
+        const float m1 = __shfl_sync(FULL, pf1, sl);
+        const uint32_t pi = __shfl_sync(FULL, pidx, sl);
+        const uint32_t ci = __shfl_sync(FULL, cidx, sl);
+        const uint32_t ww = __shfl_sync(FULL, w0, sl);
+        const float t2 = __shfl_sync(FULL, A2, sl);
+        const float t0 = __shfl_sync(FULL, A1_0, sl), t1 = __shfl_sync(FULL, A1_1, sl);
+        if (r & 2u) { met = m1; pidx = pi; cidx = ci; w0 = ww; A2 = t2; A1_0 = t0; A1_1 = t1; }
         return u;
     }
 
@@ -392,14 +389,25 @@ struct Dec {
 
 }  // namespace s8
 
+// Kernel parameters: the generic arguments plus the frozen pattern itself.  Reading the mask
+// words from the constant bank with a loop-counter index keeps every branch on them provably
+// warp-uniform (no divergence bookkeeping around the shuffles).
+struct Scl8Args {
+    DecodeArgs a;
+    uint32_t info_w[64];   // n <= 2048
+    uint32_t fv_w[64];
+};
+
+// One warp per block (blockDim.x == 32): the frame index depends on blockIdx only.
 template <int M, typename YT>
-__global__ void __launch_bounds__(512, 1) decode_scl8_kernel(const DecodeArgs A) {
+__global__ void __launch_bounds__(32, 16) decode_scl8_kernel(const __grid_constant__ Scl8Args S) {
+    const DecodeArgs& A = S.a;
     using G = s8::Geo<M>;
     extern __shared__ __align__(16) unsigned char smem_raw[];
     __shared__ unsigned short crc_tab[256];
     __shared__ unsigned char lut[1024];
     constexpr unsigned FULL = 0xffffffffu;
-    const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5, wpb = blockDim.x >> 5;
+    const int lane = threadIdx.x;
     if (A.crc) {
         for (int t = threadIdx.x; t < 256; t += blockDim.x) {
             unsigned r = A.crc == 8 ? (unsigned)t : ((unsigned)t << 8);
@@ -418,7 +426,7 @@ __global__ void __launch_bounds__(512, 1) decode_scl8_kernel(const DecodeArgs A)
     }
     __syncthreads();
 
-    unsigned char* ws = smem_raw + (size_t)wib * G::TOTAL;
+    unsigned char* ws = smem_raw;
     s8::Dec<M, YT> D;
     D.lane = lane; D.sub = lane >> 3; D.p = lane & 7;
     D.P = reinterpret_cast<float*>(ws + G::OFF_P);
@@ -427,16 +435,15 @@ __global__ void __launch_bounds__(512, 1) decode_scl8_kernel(const DecodeArgs A)
     D.lut = lut;
     const int n = G::N;
     const int EW = (A.stride + 31) >> 5;
-    const int gwarp = blockIdx.x * wpb + wib, total_warps = gridDim.x * wpb;
 
-    for (int frame = gwarp; frame < A.B; frame += total_warps) {
+    for (int frame = blockIdx.x; frame < A.B; frame += gridDim.x) {
         D.y = reinterpret_cast<const YT*>(A.y) + (size_t)frame * n;
-        D.met = 0.f; D.pidx = 0; D.cidx = 0; D.w0 = 0; D.nact = 1;
+        D.met = 0.f; D.pidx = 0; D.cidx = 0; D.w0 = 0; D.ninfo = 0;
         D.A2 = D.A1_0 = D.A1_1 = D.A0 = 0.f;
         uint32_t iw = 0, fw = 0;
 #pragma unroll 1
         for (int blk = 0; blk < n / 8; ++blk) {
-            if ((blk & 3) == 0) { iw = __ldg(A.info_mask + (blk >> 2)); fw = __ldg(A.frozen_val + (blk >> 2)); }
+            iw = S.info_w[blk >> 2]; fw = S.fv_w[blk >> 2];
             D.upper(blk);
             D.leaf8(blk, (iw >> (8 * (blk & 3))) & 0xFF, (fw >> (8 * (blk & 3))) & 0xFF);
         }
@@ -495,40 +502,45 @@ __global__ void __launch_bounds__(512, 1) decode_scl8_kernel(const DecodeArgs A)
 }
 
 template <int M, typename YT>
-static cudaError_t launch_m(const DecodeArgs& a, int blocks, int wpb, cudaStream_t st) {
-    const size_t smem = (size_t)s8::Geo<M>::TOTAL * wpb;
+static cudaError_t launch_m(const Scl8Args& a, int blocks, cudaStream_t st) {
+    const size_t smem = (size_t)s8::Geo<M>::TOTAL;
     cudaError_t e = cudaFuncSetAttribute(decode_scl8_kernel<M, YT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
-    decode_scl8_kernel<M, YT><<<blocks, wpb * 32, smem, st>>>(a);
+    decode_scl8_kernel<M, YT><<<blocks, 32, smem, st>>>(a);
     return cudaGetLastError();
 }
 
 template <int M, typename YT>
-static cudaError_t occ_m(int wpb, int* bps, int* warp_bytes) {
-    const size_t smem = (size_t)s8::Geo<M>::TOTAL * wpb;
+static cudaError_t occ_m(int* bps, int* warp_bytes) {
+    const size_t smem = (size_t)s8::Geo<M>::TOTAL;
     *warp_bytes = s8::Geo<M>::TOTAL;
     cudaError_t e = cudaFuncSetAttribute(decode_scl8_kernel<M, YT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
-    return cudaOccupancyMaxActiveBlocksPerMultiprocessor(bps, decode_scl8_kernel<M, YT>, wpb * 32, smem);
+    return cudaOccupancyMaxActiveBlocksPerMultiprocessor(bps, decode_scl8_kernel<M, YT>, 32, smem);
 }
 
 bool scl8_supported(int m) { return m >= 8 && m <= 11; }
 
-cudaError_t launch_decode_scl8(const DecodeArgs& a, int blocks, int wpb, cudaStream_t st) {
-#define PCB_CASE(MM)                                                                    \
-    case MM: return a.y_f32 ? launch_m<MM, float>(a, blocks, wpb, st) : launch_m<MM, double>(a, blocks, wpb, st);
+// info_w / fv_w: host copies of the mask words (ceil(n/32) each), passed as kernel parameters
+cudaError_t launch_decode_scl8(const DecodeArgs& a, const uint32_t* info_w, const uint32_t* fv_w, int blocks,
+                               cudaStream_t st) {
+    Scl8Args s;
+    s.a = a;
+    for (int i = 0; i < 64; i++) { s.info_w[i] = i < a.n / 32 ? info_w[i] : 0; s.fv_w[i] = i < a.n / 32 ? fv_w[i] : 0; }
+#define PCB_CASE(MM) \
+    case MM: return a.y_f32 ? launch_m<MM, float>(s, blocks, st) : launch_m<MM, double>(s, blocks, st);
     switch (a.m) { PCB_CASE(8) PCB_CASE(9) PCB_CASE(10) PCB_CASE(11) }
 #undef PCB_CASE
     return cudaErrorInvalidValue;
 }
 
-// occupancy of the more register-hungry (double input) variant, so one launch shape serves both
-cudaError_t scl8_occupancy(int m, int wpb, int* bps, int* warp_bytes) {
+// resident blocks (= warps = frames) per SM of the more register-hungry (double input) variant
+cudaError_t scl8_occupancy(int m, int* bps, int* warp_bytes) {
     switch (m) {
-        case 8: return occ_m<8, double>(wpb, bps, warp_bytes);
-        case 9: return occ_m<9, double>(wpb, bps, warp_bytes);
-        case 10: return occ_m<10, double>(wpb, bps, warp_bytes);
-        case 11: return occ_m<11, double>(wpb, bps, warp_bytes);
+        case 8: return occ_m<8, double>(bps, warp_bytes);
+        case 9: return occ_m<9, double>(bps, warp_bytes);
+        case 10: return occ_m<10, double>(bps, warp_bytes);
+        case 11: return occ_m<11, double>(bps, warp_bytes);
     }
     return cudaErrorInvalidValue;
 }
