@@ -45,6 +45,11 @@ struct pcb_handle {
     double sigma = 1.0;
     int sm_count = 0, wpb = 4, bps = 1, ls = 1, warp_smem = 0;
     bool fast8 = false;             // tuned list-8 kernel (decode_scl8.cu) instead of the generic one
+    // launch shape of the tuned kernel (the fields above always describe the generic kernel, which
+    // also re-decodes the frames the tuned kernel hands over)
+    int f_bps = 0, f_warp_smem = 0;
+    int* d_redo = nullptr;          // [0] = count, [1..] = frame list
+    size_t redo_cap = 0;
     size_t scratch_per_warp = 0;
     cudaStream_t sc = nullptr, sin = nullptr, sout = nullptr;
     cudaEvent_t ev_in[2] = {}, ev_k[2] = {}, ev_out[2] = {}, t0 = nullptr, t1 = nullptr;
@@ -68,7 +73,10 @@ struct pcb_handle {
     std::vector<uint32_t> h_info_w, h_fv_w;   // host copies of the mask words (kernel parameters of the list-8 kernel)
 };
 
-static int max_blocks(const pcb_handle* h) { return h->sm_count * h->bps; }
+// resident grid of the generic kernel; with the tuned kernel in front it only sees the rare
+// out-of-range frames, so one block per SM is plenty (and keeps its scratch small)
+static int max_blocks(const pcb_handle* h) { return h->sm_count * (h->fast8 ? 1 : h->bps); }
+static int fast_blocks(const pcb_handle* h) { return h->sm_count * h->f_bps; }
 
 static int ensure_device(pcb_handle* h) {
     CK(cudaSetDevice(h->device));
@@ -83,10 +91,7 @@ static int configure(pcb_handle* h) {
     if (h->fast8) {
         int bps = 0, wb = 0;   // one warp (= one frame) per block
         if (scl8_occupancy(h->m, &bps, &wb) != cudaSuccess || bps == 0) { cudaGetLastError(); return fail(PCB_EINVAL, "list-8 kernel does not fit one SM"); }
-        h->wpb = 1; h->bps = bps; h->warp_smem = wb;
-        h->ls = 2;
-        h->scratch_per_warp = 0;
-        return PCB_OK;
+        h->f_bps = bps; h->f_warp_smem = wb;
     }
     const char* env = getenv("PCB_WARP_SMEM");
     const int budget = env ? atoi(env) : 19200;
@@ -199,7 +204,7 @@ void pcb_destroy(pcb_handle* h) {
         if (h->ev_out[s]) cudaEventDestroy(h->ev_out[s]);
     }
     cudaFree(h->d_ymc); cudaFree(h->d_tx); cudaFree(h->d_dec); cudaFree(h->d_counters);
-    cudaFree(h->d_eu); cudaFree(h->d_ex);
+    cudaFree(h->d_eu); cudaFree(h->d_ex); cudaFree(h->d_redo);
     if (h->t0) cudaEventDestroy(h->t0);
     if (h->t1) cudaEventDestroy(h->t1);
     if (h->sc) cudaStreamDestroy(h->sc);
@@ -240,9 +245,9 @@ int pcb_info(pcb_handle* h, int* sm_count, int* warps_per_block, int* blocks, in
              int* first_smem_layer, uint64_t* kernel_launches) {
     if (!h) return fail(PCB_EINVAL, "pcb_info: null handle");
     if (sm_count) *sm_count = h->sm_count;
-    if (warps_per_block) *warps_per_block = h->wpb;
-    if (blocks) *blocks = max_blocks(h);
-    if (smem_per_block) *smem_per_block = h->warp_smem * h->wpb;
+    if (warps_per_block) *warps_per_block = h->fast8 ? 1 : h->wpb;
+    if (blocks) *blocks = h->fast8 ? fast_blocks(h) : max_blocks(h);
+    if (smem_per_block) *smem_per_block = h->fast8 ? h->f_warp_smem : h->warp_smem * h->wpb;
     if (first_smem_layer) *first_smem_layer = h->ls;
     if (kernel_launches) *kernel_launches = h->launches;
     return PCB_OK;
@@ -260,14 +265,33 @@ static DecodeArgs make_args(pcb_handle* h, const void* d_y, int y_f32, int* d_so
     a.sol = d_sol; a.sol_bits = d_solb;
     a.scratch = h->d_scratch; a.scratch_per_warp = h->scratch_per_warp;
     a.sigma = h->sigma;
+    a.redo_count = nullptr; a.redo_list = nullptr; a.use_redo_list = 0;
     return a;
 }
 
 static cudaError_t launch(pcb_handle* h, const DecodeArgs& a, cudaStream_t st) {
+    h->launches++;
+    if (h->fast8) {
+        if (h->redo_cap < (size_t)a.B + 1) {   // (re)allocation synchronises the device: safe, and rare
+            cudaFree(h->d_redo); h->d_redo = nullptr; h->redo_cap = 0;
+            cudaError_t e0 = cudaMalloc(&h->d_redo, ((size_t)a.B + 1) * sizeof(int));
+            if (e0 != cudaSuccess) return e0;
+            h->redo_cap = (size_t)a.B + 1;
+        }
+        // tuned kernel first; frames outside its safe input range come back in the redo list and
+        // are decoded by the generic kernel right behind it (normally an empty launch)
+        DecodeArgs f = a;
+        f.redo_count = h->d_redo; f.redo_list = h->d_redo + 1; f.use_redo_list = 0;
+        cudaError_t e = cudaMemsetAsync(h->d_redo, 0, sizeof(int), st);
+        if (e != cudaSuccess) return e;
+        e = launch_decode_scl8(f, h->h_info_w.data(), h->h_fv_w.data(), a.B < fast_blocks(h) ? a.B : fast_blocks(h), st);
+        if (e != cudaSuccess) return e;
+        f.use_redo_list = 1;
+        h->launches++;
+        return launch_decode_generic(f, h->L, h->decoder, h->fp64, max_blocks(h), h->wpb, st);
+    }
     int blocks = (a.B + h->wpb - 1) / h->wpb;
     if (blocks > max_blocks(h)) blocks = max_blocks(h);
-    h->launches++;
-    if (h->fast8) return launch_decode_scl8(a, h->h_info_w.data(), h->h_fv_w.data(), blocks, st);
     return launch_decode_generic(a, h->L, h->decoder, h->fp64, blocks, h->wpb, st);
 }
 
@@ -402,7 +426,7 @@ static size_t mc_batch(pcb_handle* h) {
     size_t b = ((size_t)256 << 20) / ((size_t)h->n * 4);
     const char* env = getenv("PCB_MC_BATCH");
     if (env) b = (size_t)atol(env);
-    const size_t minb = (size_t)max_blocks(h) * h->wpb;
+    const size_t minb = h->fast8 ? (size_t)fast_blocks(h) : (size_t)max_blocks(h) * h->wpb;
     if (b < minb) b = minb;
     return b;
 }

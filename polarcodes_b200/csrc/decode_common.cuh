@@ -30,6 +30,13 @@ struct DecodeArgs {
     unsigned char* scratch;     // global scratch for LLR layers < first_smem_layer
     size_t scratch_per_warp;
     double sigma;               // exact SC: LLR = 2y/sigma^2
+    // Out-of-range hand-over between the tuned list-8 kernel and the generic kernel: the tuned
+    // kernel uses arithmetic shortcuts that are bit-exact only when every |y| is 0 or within
+    // [2^-40, 2^100]; it appends any other frame to `redo_list` (count in *redo_count) and skips
+    // it, and a follow-up launch of the generic kernel decodes exactly those frames.
+    int* redo_count;            // device counter (tuned kernel: written; generic kernel: read)
+    int* redo_list;             // device list of frame indexes
+    int use_redo_list;          // generic kernel: decode frames redo_list[0 .. *redo_count) only
 };
 
 __device__ __forceinline__ float pcb_abs(float a) { return fabsf(a); }

@@ -85,7 +85,9 @@ __global__ void __launch_bounds__(256) decode_generic_kernel(const DecodeArgs A)
 
     const double inv_s2 = A.sigma * A.sigma;
 
-    for (int frame = gwarp; frame < A.B; frame += total_warps) {
+    const int nframes = A.use_redo_list ? *A.redo_count : A.B;
+    for (int fidx = gwarp; fidx < nframes; fidx += total_warps) {
+        const int frame = A.use_redo_list ? A.redo_list[fidx] : fidx;
         const float* yf = reinterpret_cast<const float*>(A.y) + (size_t)frame * n;
         const double* yd = reinterpret_cast<const double*>(A.y) + (size_t)frame * n;
         auto ch = [&](int j) -> T {

@@ -50,7 +50,16 @@ struct Geo {
     static constexpr int TOTAL = OFF_KEYS + 64;
 };
 
-__device__ __forceinline__ float ff(float a, float b) { return f_minsum<float>(a, b); }
+// f for frames whose channel values are all 0 or within [2^-40, 2^100] (checked per frame, see
+// the kernel): every LLR is then an integer multiple of 2^-63 below 2^111, so no sum overflows,
+// no NaN appears and no product of two non-zero LLRs underflows.  Under these conditions
+// min(|a|,|b|) * (a*b < 0 ? -1 : 1) (SCLDecoderMinsum.cpp:40-42) equals fminf(|a|,|b|) with the
+// sign bit of the product (a zero result may come out as -0, which nothing can observe).
+__device__ __forceinline__ float ff(float a, float b) {
+    const float m = fminf(fabsf(a), fabsf(b));
+    const float pr = a * b;
+    return __uint_as_float(__float_as_uint(m) | (__float_as_uint(pr) & 0x80000000u));
+}
 // g with the partial-sum bit already moved to the sign position (0 or 0x80000000)
 __device__ __forceinline__ float gs(float a, float b, uint32_t signbit) {
     return b + __uint_as_float(__float_as_uint(a) ^ signbit);
@@ -65,40 +74,71 @@ __device__ __forceinline__ float4 gs4(float4 a, float4 b, uint32_t cw, int pos) 
                        gs(a.w, b.w, sgn(cw, pos + 12)));
 }
 
-// Slow part of the prune (SCLDecoderMinsum.cpp:342-399), one copy in the binary.
-// Returns u | take<<1 | srcp<<2 | any<<5: this slot's bit, whether the slot is re-used for a
-// clone, the slot it is cloned from, and whether any slot was re-used at all.
-__device__ __noinline__ uint32_t prune_core(float pf0, float pf1, int lane, uint32_t* keys, const unsigned char* lut) {
+// Per-path state that a fork can replace (a clone takes its parent's).
+struct PathState {
+    float met;
+    uint32_t pidx, cidx, w0;
+    float A2, A1_0, A1_1;
+    int u;
+};
+
+// Everything of continuePaths_UnfrozenBit (SCLDecoderMinsum.cpp:315-400) except the fast exit:
+// growth while the list is not full, else the median select; then the clones take over their
+// parents' state.  One copy in the binary (arguments and result travel in registers).
+__device__ __noinline__ PathState fork_slow(PathState s, float A0, int lane, int ninfo, uint32_t* keys,
+                                            const unsigned char* lut) {
     const int sub = lane >> 3, p = lane & 7;
-    // keys are stored complemented: key < kc  <=>  carry-out of (kc + ~key)
-    if (sub == 0) *reinterpret_cast<uint2*>(keys + 2 * p) = make_uint2(~__float_as_uint(pf0), ~__float_as_uint(pf1));
-    __syncwarp();
-    const uint32_t kc = __float_as_uint((sub & 1) ? pf1 : pf0);
-    const uint4 ka = *reinterpret_cast<const uint4*>(keys + 8 * (sub >> 1));
-    const uint4 kb = *reinterpret_cast<const uint4*>(keys + 8 * (sub >> 1) + 4);
-    int cnt = 0;   // number of keys below kc, accumulated with carry chains (IADD3 + IADD3.X)
+    const float pf0 = s.met + fmaxf(-A0, 0.f);   // pen(llr,0) = |llr| iff llr < 0   (:308-313)
+    const float pf1 = s.met + fmaxf(A0, 0.f);    // pen(llr,1) = |llr| iff llr > 0
+    uint32_t r;   // u | take<<1 | srcp<<2
+    if (ninfo < 3) {
+        // growth (:329-341): live slots are [8-nact, 8); parent q clones into slot 2*pbase-1-q
+        const int nact = 1 << ninfo, pbase = 8 - nact;
+        const bool take = p >= pbase - nact && p < pbase;
+        r = take ? (3u | ((uint32_t)(2 * pbase - 1 - p) << 2)) : ((uint32_t)p << 2);
+    } else {
+        // keys are stored complemented: key < kc  <=>  carry-out of (kc + ~key)
+        if (sub == 0) *reinterpret_cast<uint2*>(keys + 2 * p) = make_uint2(~__float_as_uint(pf0), ~__float_as_uint(pf1));
+        __syncwarp();
+        const uint32_t kc = __float_as_uint((sub & 1) ? pf1 : pf0);
+        const uint4 ka = *reinterpret_cast<const uint4*>(keys + 8 * (sub >> 1));
+        const uint4 kb = *reinterpret_cast<const uint4*>(keys + 8 * (sub >> 1) + 4);
+        int cnt = 0;   // number of keys below kc, accumulated with carry chains (IADD3 + IADD3.X)
 #define PCB_LT(x) asm("{ .reg .u32 t; add.cc.u32 t, %1, %2; addc.u32 %0, %0, 0; }" : "+r"(cnt) : "r"(x), "r"(kc));
-    PCB_LT(ka.x) PCB_LT(ka.y) PCB_LT(ka.z) PCB_LT(ka.w) PCB_LT(kb.x) PCB_LT(kb.y) PCB_LT(kb.z) PCB_LT(kb.w)
+        PCB_LT(ka.x) PCB_LT(ka.y) PCB_LT(ka.z) PCB_LT(ka.w) PCB_LT(kb.x) PCB_LT(kb.y) PCB_LT(kb.z) PCB_LT(kb.w)
 #undef PCB_LT
-    cnt += __shfl_xor_sync(FULL, cnt, 16);
-    unsigned bal = __ballot_sync(FULL, cnt < 8) & 0xFFFFu;
-    if (__popc(bal) != 8) {                // a tie straddles the median (:362-371)
-        const bool in = (bal >> (lane & 15)) & 1;
-        const unsigned tkey = __reduce_max_sync(FULL, in ? kc : 0u);
-        const unsigned tb = __ballot_sync(FULL, in && kc == tkey) & 0xFFFFu;
-        const int need = 8 - (__popc(bal) - __popc(tb));
-        const unsigned t0 = tb & 0xFF, t1 = tb >> 8, lt = (1u << p) - 1;
-        const int before = __popc(t0 & lt) + __popc(t1 & lt) + ((sub & 1) ? ((t0 >> p) & 1) : 0);
-        bal = __ballot_sync(FULL, in && (kc < tkey || before < need)) & 0xFFFFu;
+        cnt += __shfl_xor_sync(FULL, cnt, 16);
+        unsigned bal = __ballot_sync(FULL, cnt < 8) & 0xFFFFu;
+        if (__popc(bal) != 8) {                // a tie straddles the median (:362-371)
+            const bool in = (bal >> (lane & 15)) & 1;
+            const unsigned tkey = __reduce_max_sync(FULL, in ? kc : 0u);
+            const unsigned tb = __ballot_sync(FULL, in && kc == tkey) & 0xFFFFu;
+            const int need = 8 - (__popc(bal) - __popc(tb));
+            const unsigned t0 = tb & 0xFF, t1 = tb >> 8, lt = (1u << p) - 1;
+            const int before = __popc(t0 & lt) + __popc(t1 & lt) + ((sub & 1) ? ((t0 >> p) & 1) : 0);
+            bal = __ballot_sync(FULL, in && (kc < tkey || before < need)) & 0xFFFFu;
+        }
+        __syncwarp();
+        const unsigned k0m = bal & 0xFF, k1m = bal >> 8;
+        const unsigned nonem = ~(k0m | k1m) & 0xFF, bothm = k0m & k1m;
+        // killed slots are pushed ascending (:372-376) and popped by the cloning parents in ascending
+        // order (:382-389): the j-th killed slot receives the clone of the j-th HIGHEST parent
+        const uint32_t src = lut[bothm * 4 + (__popc(nonem & ((1u << p) - 1)) & 3)];
+        r = ((nonem >> p) & 1) ? (3u | (src << 2)) : ((((k0m >> p) & 1) ? 0u : 1u) | ((uint32_t)p << 2));
     }
-    __syncwarp();
-    const unsigned k0m = bal & 0xFF, k1m = bal >> 8;
-    const unsigned nonem = ~(k0m | k1m) & 0xFF, bothm = k0m & k1m;
-    const uint32_t r = ((k0m >> p) & 1) ? 0u : 1u;
-    // killed slots are pushed ascending (:372-376) and popped by the cloning parents in ascending
-    // order (:382-389): the j-th killed slot receives the clone of the j-th HIGHEST parent
-    const uint32_t src = lut[bothm * 4 + (__popc(nonem & ((1u << p) - 1)) & 3)];
-    return ((nonem >> p) & 1) ? (3u | (src << 2)) : (r | ((uint32_t)p << 2));
+    s.u = r & 1;
+    s.met = s.u ? pf1 : pf0;
+    // clones copy the parent's state (:145-156 without copying arrays)
+    __syncwarp();   // orders the parent's shared-memory writes before the clone's lazy reads
+    const int sl = (lane & 24) | ((r >> 2) & 7);
+    const float m1 = __shfl_sync(FULL, pf1, sl);
+    const uint32_t pi = __shfl_sync(FULL, s.pidx, sl);
+    const uint32_t ci = __shfl_sync(FULL, s.cidx, sl);
+    const uint32_t ww = __shfl_sync(FULL, s.w0, sl);
+    const float t2 = __shfl_sync(FULL, s.A2, sl);
+    const float t0 = __shfl_sync(FULL, s.A1_0, sl), t1 = __shfl_sync(FULL, s.A1_1, sl);
+    if (r & 2u) { s.met = m1; s.pidx = pi; s.cidx = ci; s.w0 = ww; s.A2 = t2; s.A1_0 = t0; s.A1_1 = t1; }
+    return s;
 }
 
 template <int M, typename YT>
@@ -272,8 +312,6 @@ struct Dec {
 
     // ---- fork / prune of one information bit (SCLDecoderMinsum.cpp:315-400) ----------
     __device__ __forceinline__ int fork() {
-        uint32_t r;
-        float pf0, pf1;
         if (ninfo >= 3) {
             // Fast exit (no kill, no clone): the candidates of path p are {met, met + |llr|}.  If
             // every penalised candidate is strictly above every unpenalised one, the L smallest
@@ -283,32 +321,12 @@ struct Dec {
             const unsigned maxlo = __reduce_max_sync(FULL, __float_as_uint(met));
             const unsigned minhi = __reduce_min_sync(FULL, __float_as_uint(hi));
             if (maxlo < minhi) return A0 < 0.f ? 1 : 0;
-            pf0 = met + fmaxf(-A0, 0.f);   // pen(llr,0) = |llr| iff llr < 0
-            pf1 = met + fmaxf(A0, 0.f);    // pen(llr,1) = |llr| iff llr > 0
-            r = prune_core(pf0, pf1, lane, keys, lut);
-        } else {                           // growth (:329-341): parent q clones into 2*pbase-1-q
-            pf0 = met + fmaxf(-A0, 0.f);
-            pf1 = met + fmaxf(A0, 0.f);
-            const int nact = 1 << ninfo, pbase = 8 - nact;
-            const bool take = p >= pbase - nact && p < pbase;
-            r = take ? (3u | ((uint32_t)(2 * pbase - 1 - p) << 2)) : ((uint32_t)p << 2);
-            ninfo++;
         }
-        int u = r & 1;
-        met = u ? pf1 : pf0;
-        // clones copy the parent's state (:145-156 without copying arrays).  Unconditional: the
-        // non-trivial path nearly always re-uses a slot, and a data-dependent branch around warp
-        // synchronising instructions would make the compiler give up on proving convergence.
-        __syncwarp();   // orders the parent's shared-memory writes before the clone's lazy reads
-        const int sl = (lane & 24) | ((r >> 2) & 7);
-        const float m1 = __shfl_sync(FULL, pf1, sl);
-        const uint32_t pi = __shfl_sync(FULL, pidx, sl);
-        const uint32_t ci = __shfl_sync(FULL, cidx, sl);
-        const uint32_t ww = __shfl_sync(FULL, w0, sl);
-        const float t2 = __shfl_sync(FULL, A2, sl);
-        const float t0 = __shfl_sync(FULL, A1_0, sl), t1 = __shfl_sync(FULL, A1_1, sl);
-        if (r & 2u) { met = m1; pidx = pi; cidx = ci; w0 = ww; A2 = t2; A1_0 = t0; A1_1 = t1; }
-        return u;
+        PathState s{met, pidx, cidx, w0, A2, A1_0, A1_1, 0};
+        s = fork_slow(s, A0, lane, ninfo, keys, lut);
+        met = s.met; pidx = s.pidx; cidx = s.cidx; w0 = s.w0; A2 = s.A2; A1_0 = s.A1_0; A1_1 = s.A1_1;
+        if (ninfo < 3) ninfo++;
+        return s.u;
     }
 
     // decision at phase i0+T with the leaf LLR in A0
@@ -409,6 +427,7 @@ __global__ void __launch_bounds__(32, 16) decode_scl8_kernel(const __grid_consta
     constexpr unsigned FULL = 0xffffffffu;
     const int lane = threadIdx.x;
     if (A.crc) {
+#pragma unroll 1
         for (int t = threadIdx.x; t < 256; t += blockDim.x) {
             unsigned r = A.crc == 8 ? (unsigned)t : ((unsigned)t << 8);
             for (int b = 0; b < 8; b++) {
@@ -419,6 +438,7 @@ __global__ void __launch_bounds__(32, 16) decode_scl8_kernel(const __grid_consta
         }
     }
     // lut[mask*4 + j] = position of the j-th HIGHEST set bit of the 8-bit mask
+#pragma unroll 1
     for (int t = threadIdx.x; t < 1024; t += blockDim.x) {
         unsigned bm = (unsigned)t >> 2;
         for (int j = 0; j < (t & 3); j++) if (bm) bm &= ~(0x80000000u >> __clz(bm));
@@ -438,6 +458,30 @@ __global__ void __launch_bounds__(32, 16) decode_scl8_kernel(const __grid_consta
 
     for (int frame = blockIdx.x; frame < A.B; frame += gridDim.x) {
         D.y = reinterpret_cast<const YT*>(A.y) + (size_t)frame * n;
+        {   // range check that licenses the arithmetic shortcuts of ff(): |y| == 0 or in [2^-40, 2^100]
+            bool ok = true;
+#pragma unroll 1
+            for (int q = lane; q < n / 4; q += 32) {
+                float v[4];
+                if (sizeof(YT) == 8) {
+                    const double2 a = *reinterpret_cast<const double2*>(D.y + 4 * q);
+                    const double2 b = *reinterpret_cast<const double2*>(D.y + 4 * q + 2);
+                    v[0] = (float)a.x; v[1] = (float)a.y; v[2] = (float)b.x; v[3] = (float)b.y;
+                } else {
+                    const float4 a = *reinterpret_cast<const float4*>(D.y + 4 * q);
+                    v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w;
+                }
+#pragma unroll
+                for (int e = 0; e < 4; e++) {
+                    const float a = fabsf(v[e]);
+                    ok = ok && (a == 0.f || (a >= 0x1p-40f && a <= 0x1p100f));
+                }
+            }
+            if (!__all_sync(FULL, ok)) {   // hand the frame to the generic (reference-literal) kernel
+                if (lane == 0) A.redo_list[atomicAdd(A.redo_count, 1)] = frame;
+                continue;
+            }
+        }
         D.met = 0.f; D.pidx = 0; D.cidx = 0; D.w0 = 0; D.ninfo = 0;
         D.A2 = D.A1_0 = D.A1_1 = D.A0 = 0.f;
         uint32_t iw = 0, fw = 0;
@@ -452,6 +496,7 @@ __global__ void __launch_bounds__(32, 16) decode_scl8_kernel(const __grid_consta
         uint32_t* X = reinterpret_cast<uint32_t*>(D.P);          // x-hat of every slot (setbit_last, d2 == M)
         uint32_t* E = X + G::XW;
         constexpr int NW = G::NW, HS = G::HS, lgN = M - 5;
+#pragma unroll 1
         for (int e = lane; e < (8 << lgN); e += 32) {
             const int q = e >> lgN, a = e & (NW - 1);
             uint32_t x = X[q * HS + a];
@@ -460,14 +505,18 @@ __global__ void __launch_bounds__(32, 16) decode_scl8_kernel(const __grid_consta
             X[q * HS + a] = x;
         }
         __syncwarp();
+#pragma unroll 1
         for (int sw = 1; sw < NW; sw <<= 1) {
+#pragma unroll 1
             for (int e = lane; e < (8 << lgN); e += 32) {
                 const int q = e >> lgN, a = e & (NW - 1);
                 if (!(a & sw)) X[q * HS + a] ^= X[q * HS + a + sw];
             }
             __syncwarp();
         }
+#pragma unroll 1
         for (int q = 0; q < 8; q++) {
+#pragma unroll 1
             for (int t0 = 0; t0 < A.stride; t0 += 32) {
                 const int t = t0 + lane;
                 int bit = 0;
@@ -481,6 +530,7 @@ __global__ void __launch_bounds__(32, 16) decode_scl8_kernel(const __grid_consta
         if (A.crc && lane < 8) {
             const uint32_t* e = E + lane * EW;
             unsigned r = A.crc == 8 ? 0xFFu : 0xFFFFu;
+#pragma unroll 1
             for (int b = 0; b < A.k / 8; b++) {
                 const unsigned byte = __brev((e[b >> 2] >> (8 * (b & 3))) & 0xFFu) >> 24;
                 if (A.crc == 8) r = crc_tab[(r ^ byte) & 0xFF];

@@ -183,3 +183,25 @@ def test_sc_montecarlo_fer_matches_published():
     r = d.montecarlo(2.0, 20000, seed=11)
     fer = r["frame_errors"] / r["frames"]
     assert abs(fer - 0.1255) < 4 * np.sqrt(0.1255 * 0.8745 * (1 / 20000 + 1 / 10000)), fer
+
+
+def test_out_of_range_frames_take_the_generic_kernel(oracle):
+    """The tuned list-8 kernel hands frames with |y| outside {0} U [2^-40, 2^100] (or NaN/inf) to the
+    generic kernel; a batch that mixes both kinds must still match the oracle frame by frame."""
+    rng = np.random.default_rng(17)
+    n, k, crc, L = 1024, 512, 16, 8
+    sigma, inf, mask = oracle.make_code(n, k, crc, 2.0)
+    y = 1 + sigma * rng.standard_normal((96, n))
+    y[5] *= 1e-30            # products underflow in fp32
+    y[11] *= 1e35            # sums overflow to inf, inf - inf = NaN
+    y[12, 7] = 1e-20         # a single tiny value
+    y[40] = 0.0
+    y[41, ::3] = 0.0
+    y[63, 100] = np.inf
+    y[64, 200] = -3e38
+    d = _decoder(3, n, k, crc, L, mask, sigma)
+    got = d.decode(y)
+    want = oracle.decode(3, n, L, k, crc, sigma, y, mask)
+    bad = np.nonzero((got != want).any(axis=1))[0]
+    assert bad.size == 0, f"frames {bad.tolist()} differ"
+    assert (d.decode(y.astype(np.float32)) == oracle.decode(3, n, L, k, crc, sigma, y.astype(np.float32).astype(np.float64), mask)).all()
