@@ -186,7 +186,8 @@ pcb_handle* pcb_create(int device, int n, int k, int crc, int L, int decoder, in
     if ((e = cudaMalloc(&h->d_info_mask, NW * 4)) != cudaSuccess) return bail("cudaMalloc", e);
     if ((e = cudaMalloc(&h->d_frozen_val, NW * 4)) != cudaSuccess) return bail("cudaMalloc", e);
     if ((e = cudaMalloc(&h->d_info_pos, (size_t)n * 2)) != cudaSuccess) return bail("cudaMalloc", e);
-    const size_t sbytes = h->scratch_per_warp * (size_t)max_blocks(h) * h->wpb;
+    // sized for the full generic grid: pcb_set_code may route a mask with frozen ones to the generic kernel
+    const size_t sbytes = h->scratch_per_warp * (size_t)h->sm_count * h->bps * h->wpb;
     if (sbytes && (e = cudaMalloc(&h->d_scratch, sbytes)) != cudaSuccess) return bail("cudaMalloc(scratch)", e);
     if ((e = cudaMalloc(&h->d_counters, 16)) != cudaSuccess) return bail("cudaMalloc", e);
     return h;
@@ -236,6 +237,11 @@ int pcb_set_code(pcb_handle* h, const int* frozen_mask, double sigma) {
     CK(cudaMemcpyAsync(h->d_info_pos, pos.data(), (size_t)n * 2, cudaMemcpyHostToDevice, h->sc));
     CK(cudaStreamSynchronize(h->sc));
     h->h_info_w = im; h->h_fv_w = fv;
+    // the tuned list-8 kernel assumes all-zero frozen values (what the reference uses,
+    // PolarCodes.cpp:127); a mask with frozen ones runs on the generic kernel
+    bool any_fv = false;
+    for (uint32_t w : fv) any_fv = any_fv || w != 0;
+    h->fast8 = h->f_bps > 0 && !any_fv;
     h->sigma = sigma;
     h->code_set = true;
     return PCB_OK;

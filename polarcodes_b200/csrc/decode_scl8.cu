@@ -25,6 +25,41 @@ namespace s8 {
 
 constexpr unsigned FULL = 0xffffffffu;
 
+// Tables in constant memory, built at compile time (one warp per block: per-block shared-memory
+// copies would cost 1.5 KB of every frame's slice).
+struct LutTable { unsigned char v[1024]; };
+struct CrcTable { unsigned short v[256]; };
+// lut[mask*4 + j] = position of the j-th HIGHEST set bit of the 8-bit mask
+constexpr LutTable make_lut() {
+    LutTable t{};
+    for (int i = 0; i < 1024; i++) {
+        unsigned bm = (unsigned)i >> 2;
+        for (int j = 0; j < (i & 3); j++) {
+            if (bm) { int hb = 7; while (!((bm >> hb) & 1)) hb--; bm &= ~(1u << hb); }
+        }
+        int hb = 0;
+        if (bm) { hb = 7; while (!((bm >> hb) & 1)) hb--; }
+        t.v[i] = (unsigned char)hb;
+    }
+    return t;
+}
+// Resources.cpp:29-62 (poly 0x31) and :73-106 (poly 0x1021) regenerated from the polynomials
+constexpr CrcTable make_crc(int bits) {
+    CrcTable t{};
+    for (int i = 0; i < 256; i++) {
+        unsigned r = bits == 8 ? (unsigned)i : ((unsigned)i << 8);
+        for (int b = 0; b < 8; b++) {
+            if (bits == 8) r = (r & 0x80) ? ((r << 1) ^ 0x31) & 0xFF : (r << 1) & 0xFF;
+            else r = (r & 0x8000) ? ((r << 1) ^ 0x1021) & 0xFFFF : (r << 1) & 0xFFFF;
+        }
+        t.v[i] = (unsigned short)r;
+    }
+    return t;
+}
+__constant__ LutTable c_lut = make_lut();
+__constant__ CrcTable c_crc8 = make_crc(8);
+__constant__ CrcTable c_crc16 = make_crc(16);
+
 template <int M>
 struct Geo {
     static constexpr int N = 1 << M;
@@ -85,8 +120,7 @@ struct PathState {
 // Everything of continuePaths_UnfrozenBit (SCLDecoderMinsum.cpp:315-400) except the fast exit:
 // growth while the list is not full, else the median select; then the clones take over their
 // parents' state.  One copy in the binary (arguments and result travel in registers).
-__device__ __noinline__ PathState fork_slow(PathState s, float A0, int lane, int ninfo, uint32_t* keys,
-                                            const unsigned char* lut) {
+__device__ __noinline__ PathState fork_slow(PathState s, float A0, int lane, int ninfo, uint32_t* keys) {
     const int sub = lane >> 3, p = lane & 7;
     const float pf0 = s.met + fmaxf(-A0, 0.f);   // pen(llr,0) = |llr| iff llr < 0   (:308-313)
     const float pf1 = s.met + fmaxf(A0, 0.f);    // pen(llr,1) = |llr| iff llr > 0
@@ -123,7 +157,7 @@ __device__ __noinline__ PathState fork_slow(PathState s, float A0, int lane, int
         const unsigned nonem = ~(k0m | k1m) & 0xFF, bothm = k0m & k1m;
         // killed slots are pushed ascending (:372-376) and popped by the cloning parents in ascending
         // order (:382-389): the j-th killed slot receives the clone of the j-th HIGHEST parent
-        const uint32_t src = lut[bothm * 4 + (__popc(nonem & ((1u << p) - 1)) & 3)];
+        const uint32_t src = c_lut.v[bothm * 4 + (__popc(nonem & ((1u << p) - 1)) & 3)];
         r = ((nonem >> p) & 1) ? (3u | (src << 2)) : ((((k0m >> p) & 1) ? 0u : 1u) | ((uint32_t)p << 2));
     }
     s.u = r & 1;
@@ -148,7 +182,6 @@ struct Dec {
     float* P;          // warp slice: LLR layers
     uint32_t* H;       // partial-sum heaps
     uint32_t* keys;
-    const unsigned char* lut;
     const YT* y;
     float met;
     uint32_t pidx, cidx, w0;
@@ -323,7 +356,7 @@ struct Dec {
             if (maxlo < minhi) return A0 < 0.f ? 1 : 0;
         }
         PathState s{met, pidx, cidx, w0, A2, A1_0, A1_1, 0};
-        s = fork_slow(s, A0, lane, ninfo, keys, lut);
+        s = fork_slow(s, A0, lane, ninfo, keys);
         met = s.met; pidx = s.pidx; cidx = s.cidx; w0 = s.w0; A2 = s.A2; A1_0 = s.A1_0; A1_1 = s.A1_1;
         if (ninfo < 3) ninfo++;
         return s.u;
@@ -333,10 +366,9 @@ struct Dec {
     template <int T>
     __device__ __forceinline__ int decide(uint32_t infobyte, uint32_t fvbyte) {
         if ((infobyte >> T) & 1) return fork();
-        if (fvbyte == 0) { met += fmaxf(-A0, 0.f); return 0; }   // :413-418, frozen value 0
-        const int fv = (fvbyte >> T) & 1;
-        met += fv ? fmaxf(A0, 0.f) : fmaxf(-A0, 0.f);
-        return fv;
+        (void)fvbyte;                   // the tuned kernel is only used when every frozen value is 0
+        met += fmaxf(-A0, 0.f);         // :413-418
+        return 0;
     }
 
     // partial-sum combine at the last phase of a subtree (t = 7): d2 = 3 + ctz(blk+1)
@@ -418,41 +450,18 @@ struct Scl8Args {
 
 // One warp per block (blockDim.x == 32): the frame index depends on blockIdx only.
 template <int M, typename YT>
-__global__ void __launch_bounds__(32, 16) decode_scl8_kernel(const __grid_constant__ Scl8Args S) {
+__global__ void __launch_bounds__(32, 20) decode_scl8_kernel(const __grid_constant__ Scl8Args S) {
     const DecodeArgs& A = S.a;
     using G = s8::Geo<M>;
     extern __shared__ __align__(16) unsigned char smem_raw[];
-    __shared__ unsigned short crc_tab[256];
-    __shared__ unsigned char lut[1024];
     constexpr unsigned FULL = 0xffffffffu;
     const int lane = threadIdx.x;
-    if (A.crc) {
-#pragma unroll 1
-        for (int t = threadIdx.x; t < 256; t += blockDim.x) {
-            unsigned r = A.crc == 8 ? (unsigned)t : ((unsigned)t << 8);
-            for (int b = 0; b < 8; b++) {
-                if (A.crc == 8) r = (r & 0x80) ? ((r << 1) ^ 0x31) & 0xFF : (r << 1) & 0xFF;
-                else r = (r & 0x8000) ? ((r << 1) ^ 0x1021) & 0xFFFF : (r << 1) & 0xFFFF;
-            }
-            crc_tab[t] = (unsigned short)r;
-        }
-    }
-    // lut[mask*4 + j] = position of the j-th HIGHEST set bit of the 8-bit mask
-#pragma unroll 1
-    for (int t = threadIdx.x; t < 1024; t += blockDim.x) {
-        unsigned bm = (unsigned)t >> 2;
-        for (int j = 0; j < (t & 3); j++) if (bm) bm &= ~(0x80000000u >> __clz(bm));
-        lut[t] = bm ? (unsigned char)(31 - __clz(bm)) : 0;
-    }
-    __syncthreads();
-
     unsigned char* ws = smem_raw;
     s8::Dec<M, YT> D;
     D.lane = lane; D.sub = lane >> 3; D.p = lane & 7;
     D.P = reinterpret_cast<float*>(ws + G::OFF_P);
     D.H = reinterpret_cast<uint32_t*>(ws + G::OFF_H);
     D.keys = reinterpret_cast<uint32_t*>(ws + G::OFF_KEYS);
-    D.lut = lut;
     const int n = G::N;
     const int EW = (A.stride + 31) >> 5;
 
@@ -533,8 +542,8 @@ __global__ void __launch_bounds__(32, 16) decode_scl8_kernel(const __grid_consta
 #pragma unroll 1
             for (int b = 0; b < A.k / 8; b++) {
                 const unsigned byte = __brev((e[b >> 2] >> (8 * (b & 3))) & 0xFFu) >> 24;
-                if (A.crc == 8) r = crc_tab[(r ^ byte) & 0xFF];
-                else r = ((r << 8) ^ crc_tab[((r >> 8) ^ byte) & 0xFF]) & 0xFFFF;
+                if (A.crc == 8) r = s8::c_crc8.v[(r ^ byte) & 0xFF];
+                else r = ((r << 8) ^ s8::c_crc16.v[((r >> 8) ^ byte) & 0xFF]) & 0xFFFF;
             }
             unsigned rx = 0;
             for (int t = 0; t < A.crc; t++) { const int q = A.k + t; rx = (rx << 1) | ((e[q >> 5] >> (q & 31)) & 1); }
