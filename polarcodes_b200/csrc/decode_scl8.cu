@@ -351,9 +351,8 @@ struct Dec {
             // are exactly the L unpenalised ones (no tie possible), each path keeps its likely
             // bit and its metric.  ~85 % of the prune calls at the operating point end here.
             const float hi = met + fmaxf(fabsf(A0), 0.f);          // NaN llr -> penalty 0 (as :308-313)
-            const unsigned maxlo = __reduce_max_sync(FULL, __float_as_uint(met));
             const unsigned minhi = __reduce_min_sync(FULL, __float_as_uint(hi));
-            if (maxlo < minhi) return A0 < 0.f ? 1 : 0;
+            if (__all_sync(FULL, __float_as_uint(met) < minhi)) return A0 < 0.f ? 1 : 0;   // max met < min hi
         }
         PathState s{met, pidx, cidx, w0, A2, A1_0, A1_1, 0};
         s = fork_slow(s, A0, lane, ninfo, keys);
@@ -505,8 +504,9 @@ __global__ void __launch_bounds__(32, 20) decode_scl8_kernel(const __grid_consta
         uint32_t* X = reinterpret_cast<uint32_t*>(D.P);          // x-hat of every slot (setbit_last, d2 == M)
         uint32_t* E = X + G::XW;
         constexpr int NW = G::NW, HS = G::HS, lgN = M - 5;
+        const int q0 = A.crc ? 0 : 7;   // without a CRC the reference returns slot L-1 unconditionally
 #pragma unroll 1
-        for (int e = lane; e < (8 << lgN); e += 32) {
+        for (int e = lane + (q0 << lgN); e < (8 << lgN); e += 32) {
             const int q = e >> lgN, a = e & (NW - 1);
             uint32_t x = X[q * HS + a];
             x ^= (x >> 1) & 0x55555555u; x ^= (x >> 2) & 0x33333333u; x ^= (x >> 4) & 0x0F0F0F0Fu;
@@ -517,14 +517,14 @@ __global__ void __launch_bounds__(32, 20) decode_scl8_kernel(const __grid_consta
 #pragma unroll 1
         for (int sw = 1; sw < NW; sw <<= 1) {
 #pragma unroll 1
-            for (int e = lane; e < (8 << lgN); e += 32) {
+            for (int e = lane + (q0 << lgN); e < (8 << lgN); e += 32) {
                 const int q = e >> lgN, a = e & (NW - 1);
                 if (!(a & sw)) X[q * HS + a] ^= X[q * HS + a + sw];
             }
             __syncwarp();
         }
 #pragma unroll 1
-        for (int q = 0; q < 8; q++) {
+        for (int q = q0; q < 8; q++) {
 #pragma unroll 1
             for (int t0 = 0; t0 < A.stride; t0 += 32) {
                 const int t = t0 + lane;
