@@ -27,6 +27,10 @@ bool scl8_supported(int m);
 cudaError_t launch_decode_scl8(const DecodeArgs& a, const uint32_t* info_w, const uint32_t* fv_w, int blocks,
                                cudaStream_t st);
 cudaError_t scl8_occupancy(int m, int* bps, int* warp_bytes);
+// list-8 kernel with four frames per warp (decode_scl8q.cu)
+bool scl8q_supported(int m);
+cudaError_t launch_decode_scl8q(const DecodeArgs& a, const uint32_t* info_w, int blocks, cudaStream_t st);
+cudaError_t scl8q_occupancy(int m, int* bps, int* warp_bytes);
 }  // namespace pcb
 
 using namespace pcb;
@@ -48,6 +52,7 @@ struct pcb_handle {
     // launch shape of the tuned kernel (the fields above always describe the generic kernel, which
     // also re-decodes the frames the tuned kernel hands over)
     int f_bps = 0, f_warp_smem = 0;
+    bool quad = false;              // four-frames-per-warp variant (decode_scl8q.cu) of the tuned kernel
     int* d_redo = nullptr;          // [0] = count, [1..] = frame list
     size_t redo_cap = 0;
     size_t scratch_per_warp = 0;
@@ -92,6 +97,13 @@ static int configure(pcb_handle* h) {
         int bps = 0, wb = 0;   // one warp (= one frame) per block
         if (scl8_occupancy(h->m, &bps, &wb) != cudaSuccess || bps == 0) { cudaGetLastError(); return fail(PCB_EINVAL, "list-8 kernel does not fit one SM"); }
         h->f_bps = bps; h->f_warp_smem = wb;
+        // PCB_SCL8_VARIANT=quad selects the four-frames-per-warp kernel (default while it is the slower one: warp)
+        const char* venv = getenv("PCB_SCL8_VARIANT");
+        h->quad = scl8q_supported(h->m) && venv && !strcmp(venv, "quad");
+        if (h->quad) {
+            if (scl8q_occupancy(h->m, &bps, &wb) != cudaSuccess || bps == 0) { cudaGetLastError(); h->quad = false; }
+            else { h->f_bps = bps; h->f_warp_smem = wb; }
+        }
     }
     const char* env = getenv("PCB_WARP_SMEM");
     const int budget = env ? atoi(env) : 19200;
@@ -290,7 +302,12 @@ static cudaError_t launch(pcb_handle* h, const DecodeArgs& a, cudaStream_t st) {
         f.redo_count = h->d_redo; f.redo_list = h->d_redo + 1; f.use_redo_list = 0;
         cudaError_t e = cudaMemsetAsync(h->d_redo, 0, sizeof(int), st);
         if (e != cudaSuccess) return e;
-        e = launch_decode_scl8(f, h->h_info_w.data(), h->h_fv_w.data(), a.B < fast_blocks(h) ? a.B : fast_blocks(h), st);
+        if (h->quad) {
+            const int nq = (a.B + 3) / 4;
+            e = launch_decode_scl8q(f, h->h_info_w.data(), nq < fast_blocks(h) ? nq : fast_blocks(h), st);
+        } else {
+            e = launch_decode_scl8(f, h->h_info_w.data(), h->h_fv_w.data(), a.B < fast_blocks(h) ? a.B : fast_blocks(h), st);
+        }
         if (e != cudaSuccess) return e;
         f.use_redo_list = 1;
         h->launches++;
@@ -432,7 +449,7 @@ static size_t mc_batch(pcb_handle* h) {
     size_t b = ((size_t)256 << 20) / ((size_t)h->n * 4);
     const char* env = getenv("PCB_MC_BATCH");
     if (env) b = (size_t)atol(env);
-    const size_t minb = h->fast8 ? (size_t)fast_blocks(h) : (size_t)max_blocks(h) * h->wpb;
+    const size_t minb = h->fast8 ? (size_t)fast_blocks(h) * (h->quad ? 4 : 1) : (size_t)max_blocks(h) * h->wpb;
     if (b < minb) b = minb;
     return b;
 }

@@ -1,0 +1,631 @@
+// List-8 SCL min-sum decoder, FOUR FRAMES PER WARP (SCLDecoderMinsum.cpp:225-478 semantics,
+// bit-exact with decode_generic.cu): lane = f*8 + p, f the frame of the quad (0..3) and p the
+// path slot (0..7).  One lane owns one path of one frame from the channel values to the CRC.
+//
+// Why this mapping: every frame of a batch shares the frozen pattern, so the
+// control flow of the 1024 phases is identical for all frames and a warp can run four of them
+// in lockstep.  All per-path scalar work (leaf LLRs of the size-4/2/1 layers, metric update,
+// fork bookkeeping, partial-sum words, CRC) then uses 32 of 32 lanes instead of 8 of 32, and
+// every address computation / loop / branch of the upper layers is paid once per four frames.
+//
+//  * LLR layers 3..m-3 (sizes n/8 .. 8) live in shared memory as [frame][layer][slot][j] with a
+//    slot stride of size+4 floats: the 8 lanes of a frame (a quarter-warp of an LDS.128) hit 8
+//    distinct 16-byte bank groups for any permutation of source slots (lazy reads).
+//  * layers 0, 1, 2 are never stored: layer 3 is computed from the channel values with three
+//    fused levels every n/8 phases.  In the first half of the frame layer 1 = f(y, y') does not
+//    depend on the path, so the eight lanes of a frame compute it once, cooperatively, while
+//    staging (the staging area is the region of layers 4.., dead at those phases).
+//  * layers of size 4, 2, 1 are registers of the owning lane; a clone copies the live ones with
+//    shuffles inside its 8-lane group.
+//  * lazy copy as in decode_scl8.cu: slot p writes its own arrays, a per-path word holds the slot
+//    to read each layer from.
+#include "decode_common.cuh"
+#include "decode_launch.h"
+
+namespace pcb {
+
+namespace q8 {
+
+constexpr unsigned FULL = 0xffffffffu;
+
+template <int M>
+struct Geo {
+    static constexpr int N = 1 << M;
+    static constexpr int LTOP = 3;          // first stored LLR layer (size N/8)
+    static constexpr int LBOT = M - 3;      // last stored LLR layer (size 8); sizes 4,2,1 are registers
+    static constexpr int NW = N / 32;       // words of a full-length bit array
+    static constexpr int HS = NW + 1;       // slot stride of the partial-sum heap (layer of size S at words [S/32, 2S/32))
+    __host__ __device__ static constexpr int size(int lam) { return N >> lam; }
+    __host__ __device__ static constexpr int stride(int lam) { return size(lam) + 4; }
+    __host__ __device__ static constexpr int off(int lam) {
+        int o = 0;
+        for (int l = LTOP; l < lam; ++l) o += 8 * stride(l);
+        return o;
+    }
+    static constexpr int PFLOATS = off(LBOT + 1);
+    static constexpr int STAGE_OFF = off(LTOP + 1);          // staging area = layers 4..LBOT
+    static_assert(PFLOATS - STAGE_OFF >= N, "staging area too small");
+    static constexpr int XW = 8 * HS;                        // final codeword estimates (alias the LLR region)
+    static_assert(XW + 8 * NW <= PFLOATS, "final-stage scratch does not fit the LLR region");
+    static constexpr int FRAME_WORDS = PFLOATS + 8 * HS + 16;   // LLRs, heaps, 16 candidate keys
+    static constexpr int OFF_H = PFLOATS;
+    static constexpr int OFF_KEYS = PFLOATS + 8 * HS;
+    static constexpr int TOTAL = 4 * FRAME_WORDS * 4;
+    static_assert((FRAME_WORDS * 4) % 16 == 0 && (OFF_H * 4) % 16 == 0 && (OFF_KEYS * 4) % 16 == 0, "alignment");
+};
+
+// f for frames whose channel values are all 0 or within [2^-40, 2^100] (see decode_scl8.cu):
+// min(|a|,|b|) * (a*b < 0 ? -1 : 1) (SCLDecoderMinsum.cpp:40-42) equals fminf(|a|,|b|) with the
+// sign bit of the product.
+__device__ __forceinline__ float ff(float a, float b) {
+    const float m = fminf(fabsf(a), fabsf(b));
+    const float pr = a * b;
+    return __uint_as_float(__float_as_uint(m) | (__float_as_uint(pr) & 0x80000000u));
+}
+// g (SCLDecoderMinsum.cpp:51-53) with the partial-sum bit already at the sign position
+__device__ __forceinline__ float gs(float a, float b, uint32_t signbit) {
+    return b + __uint_as_float(__float_as_uint(a) ^ signbit);
+}
+__device__ __forceinline__ uint32_t sgn(uint32_t w, int pos) { return (w << (31 - pos)) & 0x80000000u; }
+__device__ __forceinline__ float4 ff4(float4 a, float4 b) {
+    return make_float4(ff(a.x, b.x), ff(a.y, b.y), ff(a.z, b.z), ff(a.w, b.w));
+}
+// partial-sum bits of the 4 elements at positions pos .. pos+3 of cw
+__device__ __forceinline__ float4 gs4(float4 a, float4 b, uint32_t cw, int pos) {
+    return make_float4(gs(a.x, b.x, sgn(cw, pos)), gs(a.y, b.y, sgn(cw, pos + 1)), gs(a.z, b.z, sgn(cw, pos + 2)),
+                       gs(a.w, b.w, sgn(cw, pos + 3)));
+}
+
+// max over the 8 lanes of a frame: four full-warp reductions (one uniform-datapath CREDUX each,
+// ~49 cycles for the four) instead of a three-level shuffle butterfly (~110 cycles); a
+// __reduce_*_sync with an 8-lane member mask compiles to a divergent software loop (~310 cycles).
+__device__ __forceinline__ unsigned group_max(unsigned x, int fme) {
+    unsigned r = 0;
+#pragma unroll
+    for (int g = 0; g < 4; g++) {
+        const unsigned v = __reduce_max_sync(FULL, fme == g ? x : 0u);
+        if (fme == g) r = v;
+    }
+    return r;
+}
+
+// Per-path state a fork can replace.  r = u | take << 1 | source lane << 2.
+struct PathState {
+    float met;
+    uint32_t pidx, cidx, w0, r;
+};
+
+// continuePaths_UnfrozenBit (SCLDecoderMinsum.cpp:315-400) without the fast exit, for the four
+// frames of the warp at once (every step is confined to the 8-lane group of a frame).
+__device__ __noinline__ PathState fork_slow(PathState s, float A0, int lane, int ninfo, uint32_t* keys) {
+    const int p = lane & 7, gsh = lane & 24;
+    const float pf0 = s.met + fmaxf(-A0, 0.f);   // pen(llr,0) = |llr| iff llr < 0   (:308-313)
+    const float pf1 = s.met + fmaxf(A0, 0.f);    // pen(llr,1) = |llr| iff llr > 0
+    uint32_t r;
+    if (ninfo < 3) {
+        // growth (:329-341): live slots are [8-nact, 8); parent q clones into slot 2*pbase-1-q
+        const int nact = 1 << ninfo, pbase = 8 - nact;
+        const bool take = p >= pbase - nact && p < pbase;
+        r = take ? (3u | ((uint32_t)(gsh + 2 * pbase - 1 - p) << 2)) : ((uint32_t)lane << 2);
+    } else {
+        // stable rank of both candidates among the 16 of the frame; keys are stored complemented:
+        // key < kc  <=>  carry-out of (kc + ~key)
+        *reinterpret_cast<uint2*>(keys + 2 * p) = make_uint2(~__float_as_uint(pf0), ~__float_as_uint(pf1));
+        __syncwarp();
+        const uint32_t k0 = __float_as_uint(pf0), k1 = __float_as_uint(pf1);
+        int c0 = 0, c1 = 0, d0 = 0, d1 = 0;   // two accumulators per candidate: shorter dependent chains
+#define PCB_LT(c, x, k) asm("{ .reg .u32 t; add.cc.u32 t, %1, %2; addc.u32 %0, %0, 0; }" : "+r"(c) : "r"(x), "r"(k));
+#pragma unroll
+        for (int q = 0; q < 4; q++) {
+            const uint4 kk = *reinterpret_cast<const uint4*>(keys + 4 * q);
+            PCB_LT(c0, kk.x, k0) PCB_LT(c1, kk.x, k1) PCB_LT(d0, kk.y, k0) PCB_LT(d1, kk.y, k1)
+            PCB_LT(c0, kk.z, k0) PCB_LT(c1, kk.z, k1) PCB_LT(d0, kk.w, k0) PCB_LT(d1, kk.w, k1)
+        }
+#undef PCB_LT
+        bool keep0 = c0 + d0 < 8, keep1 = c1 + d1 < 8;
+        unsigned b0 = (__ballot_sync(FULL, keep0) >> gsh) & 0xFFu, b1 = (__ballot_sync(FULL, keep1) >> gsh) & 0xFFu;
+        const bool tie = __popc(b0) + __popc(b1) != 8;        // a tie straddles the median (:362-371)
+        if (__any_sync(FULL, tie)) {
+            const unsigned top = max(keep0 ? k0 : 0u, keep1 ? k1 : 0u);
+            const unsigned tkey = group_max(top, lane >> 3);
+            const unsigned t0 = (__ballot_sync(FULL, keep0 && k0 == tkey) >> gsh) & 0xFFu;
+            const unsigned t1 = (__ballot_sync(FULL, keep1 && k1 == tkey) >> gsh) & 0xFFu;
+            const int need = 8 - (__popc(b0) + __popc(b1) - __popc(t0) - __popc(t1));
+            const unsigned lt = (1u << p) - 1;
+            const int before0 = __popc(t0 & lt) + __popc(t1 & lt), before1 = before0 + ((t0 >> p) & 1);
+            if (tie) {
+                keep0 = keep0 && (k0 < tkey || before0 < need);
+                keep1 = keep1 && (k1 < tkey || before1 < need);
+            }
+            b0 = (__ballot_sync(FULL, keep0) >> gsh) & 0xFFu;
+            b1 = (__ballot_sync(FULL, keep1) >> gsh) & 0xFFu;
+        }
+        const unsigned nonem = ~(b0 | b1) & 0xFFu, bothm = b0 & b1;
+        if ((nonem >> p) & 1) {
+            // killed slots are pushed ascending (:372-376) and popped by the cloning parents in
+            // ascending order (:382-389): the j-th killed slot receives the clone of the j-th
+            // HIGHEST parent
+            const int j = __popc(nonem & ((1u << p) - 1));
+            unsigned bm = bothm;
+            if (j > 0) bm &= ~(0x80000000u >> __clz(bm));
+            if (j > 1) bm &= ~(0x80000000u >> __clz(bm));
+            if (j > 2) bm &= ~(0x80000000u >> __clz(bm));
+            r = 3u | ((uint32_t)(gsh + 31 - __clz(bm)) << 2);
+        } else {
+            r = (keep0 ? 0u : 1u) | ((uint32_t)lane << 2);
+        }
+    }
+    s.met = (r & 1) ? pf1 : pf0;
+    // clones copy the parent's state (:145-156 without copying arrays)
+    __syncwarp();   // orders the parents' shared-memory writes before the clones' lazy reads; keys reusable
+    const int sl = (r >> 2) & 31;
+    const float m1 = __shfl_sync(FULL, pf1, sl);
+    const uint32_t pi = __shfl_sync(FULL, s.pidx, sl);
+    const uint32_t ci = __shfl_sync(FULL, s.cidx, sl);
+    const uint32_t ww = __shfl_sync(FULL, s.w0, sl);
+    if (r & 2u) { s.met = m1; s.pidx = pi; s.cidx = ci; s.w0 = ww; }
+    s.r = r;
+    return s;
+}
+
+template <int M, typename YT>
+struct Dec {
+    using G = Geo<M>;
+    int lane, p;
+    float* P;          // this frame's LLR layers
+    uint32_t* H;       // this frame's partial-sum heaps
+    uint32_t* keys;    // this frame's 16 candidate keys
+    float* W;          // the warp's whole slice (4 frames)
+    float met;
+    uint32_t maxmet;   // bit pattern of the largest metric of this frame (valid whenever the next phase is an information bit)
+    uint32_t pidx, cidx, w0;
+    float4 r4;         // size-4 layer
+    float r2_0, r2_1;  // size-2 layer
+    float A0;          // leaf LLR
+    int ninfo;         // information bits seen so far (warp-uniform): the list is full from the 4th on
+
+    __device__ __forceinline__ float* arr(int lam, int slot) const { return P + G::off(lam) + slot * G::stride(lam); }
+    __device__ __forceinline__ int pfield(int lam) const { return (pidx >> (3 * (lam - G::LTOP))) & 7; }
+    __device__ __forceinline__ int cfield(int lam) const { return (cidx >> (3 * (lam - 1))) & 7; }
+    // word w32 (32 elements each) of partial-sum layer `lam` (size >= 32), elements from `base`
+    __device__ __forceinline__ uint32_t cword(int lam, int base, int w32) const {
+        return H[cfield(lam) * G::HS + (G::size(lam) >> 5) + (base >> 5) + w32];
+    }
+
+    // ---- layer 3 straight from the channel values (layers 0, 1, 2 are virtual) ---------
+    // ev = i0 / (N/8) in 0..7: bit 2 -> layer 1 is a g-layer, bit 1 -> layer 2, bit 0 -> layer 3.
+    // L1[x] = op1(y[x], y[x+4E]), L2[x] = op2(L1[x], L1[x+2E]), L3[j] = op3(L2[j], L2[j+E]), E = N/8.
+    __device__ __forceinline__ float4 load_y4(const YT* y, int q) const {
+        if (sizeof(YT) == 8) {
+            const double2 a = *reinterpret_cast<const double2*>(y + 4 * q);
+            const double2 b = *reinterpret_cast<const double2*>(y + 4 * q + 2);
+            return make_float4((float)a.x, (float)a.y, (float)b.x, (float)b.y);   // :406-408
+        } else {
+            return *reinterpret_cast<const float4*>(y + 4 * q);
+        }
+    }
+    __device__ __forceinline__ void top3(int ev, const YT* ybase, const int (&fr)[4]) {
+        constexpr int E = G::N / 8, N4 = G::N / 4;
+        const bool g1 = ev & 4, g2 = ev & 2, g3 = ev & 1;
+        __syncwarp();                            // everyone is done with layers 4.. of the previous subtree
+        if (g1) {
+            // stage the channel values of the four frames as floats
+#pragma unroll
+            for (int f = 0; f < 4; f++) {
+                const YT* y = ybase + (size_t)fr[f] * G::N;
+                float* R = W + f * G::FRAME_WORDS + G::STAGE_OFF;
+#pragma unroll 4
+                for (int q = lane; q < N4; q += 32) *reinterpret_cast<float4*>(R + 4 * q) = load_y4(y, q);
+            }
+        } else {
+            // layer 1 = f(y[x], y[x + N/2]) is the same for every path: compute it while staging
+#pragma unroll
+            for (int f = 0; f < 4; f++) {
+                const YT* y = ybase + (size_t)fr[f] * G::N;
+                float* R = W + f * G::FRAME_WORDS + G::STAGE_OFF;
+#pragma unroll 4
+                for (int q = lane; q < N4 / 2; q += 32)
+                    *reinterpret_cast<float4*>(R + 4 * q) = ff4(load_y4(y, q), load_y4(y, q + N4 / 2));
+            }
+        }
+        __syncwarp();
+        const float* R = P + G::STAGE_OFF;
+        float* dst = arr(3, p);
+#pragma unroll 1
+        for (int k0 = 0; k0 < E / 4; k0 += 8) {          // 8 float4 = 32 outputs per round
+            uint32_t c1[4] = {0, 0, 0, 0}, c2[2] = {0, 0}, c3w = 0;
+            if (g1) {
+#pragma unroll
+                for (int t = 0; t < 4; t++) c1[t] = cword(1, t * E, k0 >> 3);
+            }
+            if (g2) { c2[0] = cword(2, 0, k0 >> 3); c2[1] = cword(2, E, k0 >> 3); }
+            if (g3) c3w = cword(3, 0, k0 >> 3);
+#pragma unroll 2
+            for (int kk = 0; kk < 8; kk++) {
+                const int k = k0 + kk;
+                float4 l1[4];
+                if (g1) {
+                    float4 yv[8];
+#pragma unroll
+                    for (int t = 0; t < 8; t++) yv[t] = *reinterpret_cast<const float4*>(R + t * E + 4 * k);
+#pragma unroll
+                    for (int t = 0; t < 4; t++) l1[t] = gs4(yv[t], yv[t + 4], c1[t], 4 * kk);
+                } else {
+#pragma unroll
+                    for (int t = 0; t < 4; t++) l1[t] = *reinterpret_cast<const float4*>(R + t * E + 4 * k);
+                }
+                float4 l2[2], o;
+                if (g2) { l2[0] = gs4(l1[0], l1[2], c2[0], 4 * kk); l2[1] = gs4(l1[1], l1[3], c2[1], 4 * kk); }
+                else { l2[0] = ff4(l1[0], l1[2]); l2[1] = ff4(l1[1], l1[3]); }
+                o = g3 ? gs4(l2[0], l2[1], c3w, 4 * kk) : ff4(l2[0], l2[1]);
+                *reinterpret_cast<float4*>(dst + 4 * k) = o;
+            }
+        }
+        __syncwarp();                            // staging area is overwritten by layer 4 next
+    }
+
+    // ---- one stored layer from the previous stored layer ------------------------------
+    // ISG: g-layer (first layer of a chain, source slot is the lazily shared one)
+    template <int LAM, bool ISG>
+    __device__ __forceinline__ void layer() {
+        constexpr int S = G::size(LAM);       // outputs
+        const int slot = ISG ? pfield(LAM - 1) : p;
+        const float* src = arr(LAM - 1, slot);
+        float* dst = arr(LAM, p);
+        if constexpr (S >= 32) {
+#pragma unroll 1
+            for (int k0 = 0; k0 < S / 4; k0 += 8) {
+                uint32_t cw = 0;
+                if (ISG) cw = cword(LAM, 0, k0 >> 3);
+#pragma unroll
+                for (int kk = 0; kk < 8; kk++) {
+                    const float4 a = *reinterpret_cast<const float4*>(src + 4 * (k0 + kk));
+                    const float4 b = *reinterpret_cast<const float4*>(src + S + 4 * (k0 + kk));
+                    *reinterpret_cast<float4*>(dst + 4 * (k0 + kk)) = ISG ? gs4(a, b, cw, 4 * kk) : ff4(a, b);
+                }
+            }
+        } else {                              // S = 16: bits [16,32) of w0; S = 8: bits [8,16)
+#pragma unroll
+            for (int kk = 0; kk < S / 4; kk++) {
+                const float4 a = *reinterpret_cast<const float4*>(src + 4 * kk);
+                const float4 b = *reinterpret_cast<const float4*>(src + S + 4 * kk);
+                *reinterpret_cast<float4*>(dst + 4 * kk) = ISG ? gs4(a, b, w0, S + 4 * kk) : ff4(a, b);
+            }
+        }
+    }
+
+    // g at layer ll (one of LTOP+1..LBOT); every g variant appears once in the binary
+    template <int LAM>
+    __device__ __forceinline__ void g_dispatch(int ll) {
+        if constexpr (LAM > G::LTOP) {
+            if (ll == LAM) layer<LAM, true>();
+            else g_dispatch<LAM - 1>(ll);
+        }
+    }
+    // f layers ll+1..LBOT; every f variant appears once in the binary
+    template <int LAM>
+    __device__ __forceinline__ void f_below(int ll) {
+        if constexpr (LAM <= G::LBOT) {
+            if (ll < LAM) layer<LAM, false>();
+            f_below<LAM + 1>(ll);
+        }
+    }
+
+    // LLR work at the first phase i0 = 8*blk of a size-8 subtree, down to layer LBOT
+    __device__ __forceinline__ void upper(int blk, const YT* ybase, const int (&fr)[4]) {
+        const int z = blk ? (__ffs(blk) - 1) : 31;
+        int ll;
+        if (z >= M - 6) { top3(blk >> (M - 6), ybase, fr); ll = G::LTOP; }     // i0 is a multiple of N/8
+        else { __syncwarp(); ll = G::LBOT - z; g_dispatch<G::LBOT>(ll); }
+        f_below<G::LTOP + 1>(ll);
+        // layers >= ll are now this slot's own
+        const uint32_t low = (1u << (3 * (ll - G::LTOP))) - 1;
+        pidx = (pidx & low) | ((0x9249249u * (uint32_t)p) & ~low);
+    }
+
+    // ---- fork / prune of one information bit (SCLDecoderMinsum.cpp:315-400) ----------
+    template <int T>
+    __device__ __forceinline__ int fork() {
+        if (ninfo >= 3) {
+            // Fast exit (no kill, no clone): the candidates of path p are {met, met + |llr|}.  If
+            // every penalised candidate of the frame is strictly above every unpenalised one, the
+            // L smallest are exactly the L unpenalised ones (no tie possible).  Taken only when
+            // all four frames of the warp agree.
+            const float hi = met + fabsf(A0);
+            if (__all_sync(FULL, __float_as_uint(hi) > maxmet)) return A0 < 0.f ? 1 : 0;   // max met < min hi
+        }
+        PathState s{met, pidx, cidx, w0, 0};
+        s = fork_slow(s, A0, lane, ninfo, keys);
+        met = s.met; pidx = s.pidx; cidx = s.cidx; w0 = s.w0;
+        const int sl = (s.r >> 2) & 31;
+        const bool take = s.r & 2u;
+        if ((T & 3) < 2) {                      // the size-4 layer is still to be read by a g
+            const float x = __shfl_sync(FULL, r4.x, sl), y = __shfl_sync(FULL, r4.y, sl);
+            const float z = __shfl_sync(FULL, r4.z, sl), w = __shfl_sync(FULL, r4.w, sl);
+            if (take) r4 = make_float4(x, y, z, w);
+        }
+        if (!(T & 1)) {                         // so is the size-2 layer
+            const float x = __shfl_sync(FULL, r2_0, sl), y = __shfl_sync(FULL, r2_1, sl);
+            if (take) { r2_0 = x; r2_1 = y; }
+        }
+        if (ninfo < 3) ninfo++;
+        maxmet = group_max(__float_as_uint(met), lane >> 3);
+        return s.r & 1;
+    }
+
+    // decision at phase i0+T with the leaf LLR in A0
+    template <int T>
+    __device__ __forceinline__ int decide(uint32_t infobyte) {
+        if ((infobyte >> T) & 1) return fork<T>();
+        met += fmaxf(-A0, 0.f);         // frozen value 0 (:413-418)
+        // the fast exit of the next information bit compares against the largest metric of the frame
+        if ((infobyte >> (T + 1)) & 1) maxmet = group_max(__float_as_uint(met), lane >> 3);
+        return 0;
+    }
+
+    // partial-sum combine at the last phase of a subtree (t = 7): d2 = 3 + ctz(blk+1)
+    __device__ __forceinline__ void setbit_last(int blk, int u) {
+        const int d2 = min(M, 3 + __ffs(blk + 1) - 1);
+        uint32_t T = (uint32_t)u;
+        T = (((w0 >> 1) ^ T) & 1u) | (T << 1);
+        T = (((w0 >> 2) ^ T) & 3u) | (T << 2);
+        T = (((w0 >> 4) ^ T) & 15u) | (T << 4);
+        if (d2 == 3) { w0 = (w0 & ~0xFF00u) | (T << 8); return; }
+        T = (((w0 >> 8) ^ T) & 0xFFu) | (T << 8);
+        if (d2 == 4) { w0 = (w0 & 0x0000FFFFu) | (T << 16); return; }
+        T = (((w0 >> 16) ^ T) & 0xFFFFu) | (T << 16);
+        const int D = 1 << d2;
+        // destination layer m-d2 sits at heap words [D/32, 2D/32); layer 0 (the final codeword
+        // estimate, written at the very last phase) goes to the then-dead LLR region instead
+        uint32_t* hp = (d2 == M) ? (reinterpret_cast<uint32_t*>(P) + p * G::HS - G::NW) : (H + p * G::HS);
+        __syncwarp();
+        hp[2 * D / 32 - 1] = T;
+        for (int w = 32; w < D; w <<= 1) {
+            const int lgw = 31 - __clz(w), layc = M - lgw, nw = w >> 5;
+            const uint32_t* cs = H + cfield(layc) * G::HS + nw;
+            for (int kk = 0; kk < nw; kk++)
+                hp[(2 * D - 2 * w) / 32 + kk] = cs[kk] ^ hp[(2 * D - w) / 32 + kk];
+        }
+        __syncwarp();
+        if (d2 < M) {
+            const int sh = 3 * (M - d2 - 1);
+            cidx = (cidx & ~(7u << sh)) | ((uint32_t)p << sh);
+        }
+    }
+
+    // the 8 phases of one size-8 subtree; layer LBOT of this subtree is already computed
+    __device__ __forceinline__ void leaf8(int blk, uint32_t ib) {
+        int u;
+        // t = 0: own arrays all the way down
+        {
+            const float* v = arr(G::LBOT, p);
+            r4 = ff4(*reinterpret_cast<const float4*>(v), *reinterpret_cast<const float4*>(v + 4));
+        }
+        r2_0 = ff(r4.x, r4.z); r2_1 = ff(r4.y, r4.w);
+        A0 = ff(r2_0, r2_1);
+        u = decide<0>(ib); w0 = (w0 & ~2u) | ((uint32_t)u << 1);
+        // t = 1
+        A0 = gs(r2_0, r2_1, sgn(w0, 1));
+        u = decide<1>(ib);
+        { uint32_t T = (((w0 >> 1) ^ u) & 1u) | ((uint32_t)u << 1); w0 = (w0 & ~0xCu) | (T << 2); }
+        // t = 2
+        r2_0 = gs(r4.x, r4.z, sgn(w0, 2)); r2_1 = gs(r4.y, r4.w, sgn(w0, 3));
+        A0 = ff(r2_0, r2_1);
+        u = decide<2>(ib); w0 = (w0 & ~2u) | ((uint32_t)u << 1);
+        // t = 3
+        A0 = gs(r2_0, r2_1, sgn(w0, 1));
+        u = decide<3>(ib);
+        { uint32_t T = (((w0 >> 1) ^ u) & 1u) | ((uint32_t)u << 1); T = (((w0 >> 2) ^ T) & 3u) | (T << 2);
+          w0 = (w0 & ~0xF0u) | (T << 4); }
+        // t = 4: the size-8 layer may be a parent's
+        {
+            __syncwarp();
+            const float* v = arr(G::LBOT, pfield(G::LBOT));
+            r4 = gs4(*reinterpret_cast<const float4*>(v), *reinterpret_cast<const float4*>(v + 4), w0, 4);
+        }
+        r2_0 = ff(r4.x, r4.z); r2_1 = ff(r4.y, r4.w);
+        A0 = ff(r2_0, r2_1);
+        u = decide<4>(ib); w0 = (w0 & ~2u) | ((uint32_t)u << 1);
+        // t = 5
+        A0 = gs(r2_0, r2_1, sgn(w0, 1));
+        u = decide<5>(ib);
+        { uint32_t T = (((w0 >> 1) ^ u) & 1u) | ((uint32_t)u << 1); w0 = (w0 & ~0xCu) | (T << 2); }
+        // t = 6
+        r2_0 = gs(r4.x, r4.z, sgn(w0, 2)); r2_1 = gs(r4.y, r4.w, sgn(w0, 3));
+        A0 = ff(r2_0, r2_1);
+        u = decide<6>(ib); w0 = (w0 & ~2u) | ((uint32_t)u << 1);
+        // t = 7
+        A0 = gs(r2_0, r2_1, sgn(w0, 1));
+        u = decide<7>(ib);
+        setbit_last(blk, u);
+    }
+};
+
+// Resources.cpp:29-62 (poly 0x31) and :73-106 (poly 0x1021) regenerated from the polynomials
+struct CrcTable { unsigned short v[256]; };
+constexpr CrcTable make_crc(int bits) {
+    CrcTable t{};
+    for (int i = 0; i < 256; i++) {
+        unsigned r = bits == 8 ? (unsigned)i : ((unsigned)i << 8);
+        for (int b = 0; b < 8; b++) {
+            if (bits == 8) r = (r & 0x80) ? ((r << 1) ^ 0x31) & 0xFF : (r << 1) & 0xFF;
+            else r = (r & 0x8000) ? ((r << 1) ^ 0x1021) & 0xFFFF : (r << 1) & 0xFFFF;
+        }
+        t.v[i] = (unsigned short)r;
+    }
+    return t;
+}
+__constant__ CrcTable c_crc8 = make_crc(8);
+__constant__ CrcTable c_crc16 = make_crc(16);
+
+}  // namespace q8
+
+// Kernel parameters: the generic arguments plus the frozen pattern itself (warp-uniform control
+// straight from the constant bank).
+struct Scl8qArgs {
+    DecodeArgs a;
+    uint32_t info_w[65];   // n <= 2048, one zero word behind the last
+};
+
+// One warp per block (blockDim.x == 32); a block decodes quads of frames.
+template <int M, typename YT>
+__global__ void __launch_bounds__(32, 5) decode_scl8q_kernel(const __grid_constant__ Scl8qArgs S) {
+    const DecodeArgs& A = S.a;
+    using G = q8::Geo<M>;
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    constexpr unsigned FULL = 0xffffffffu;
+    const int lane = threadIdx.x, fme = lane >> 3;
+    q8::Dec<M, YT> D;
+    D.lane = lane; D.p = lane & 7;
+    D.W = reinterpret_cast<float*>(smem_raw);
+    D.P = D.W + fme * G::FRAME_WORDS;
+    D.H = reinterpret_cast<uint32_t*>(D.P) + G::OFF_H;
+    D.keys = reinterpret_cast<uint32_t*>(D.P) + G::OFF_KEYS;
+    constexpr int n = G::N;
+    const int EW = (A.stride + 31) >> 5;
+    const YT* ybase = reinterpret_cast<const YT*>(A.y);
+    const int nquads = (A.B + 3) >> 2;
+
+    for (int quad = blockIdx.x; quad < nquads; quad += gridDim.x) {
+        int fr[4];
+        bool okf[4];
+#pragma unroll
+        for (int f = 0; f < 4; f++) fr[f] = min(4 * quad + f, A.B - 1);
+        // range check that licenses the arithmetic shortcuts of ff(): |y| == 0 or in [2^-40, 2^100]
+#pragma unroll
+        for (int f = 0; f < 4; f++) {
+            const YT* y = ybase + (size_t)fr[f] * n;
+            bool ok = true;
+#pragma unroll 2
+            for (int q = lane; q < n / 4; q += 32) {
+                const float4 v = D.load_y4(y, q);
+                const float a0 = fabsf(v.x), a1 = fabsf(v.y), a2 = fabsf(v.z), a3 = fabsf(v.w);
+                ok = ok && (a0 == 0.f || (a0 >= 0x1p-40f && a0 <= 0x1p100f)) && (a1 == 0.f || (a1 >= 0x1p-40f && a1 <= 0x1p100f)) &&
+                     (a2 == 0.f || (a2 >= 0x1p-40f && a2 <= 0x1p100f)) && (a3 == 0.f || (a3 >= 0x1p-40f && a3 <= 0x1p100f));
+            }
+            okf[f] = __all_sync(FULL, ok);
+            // hand the frame to the generic (reference-literal) kernel
+            if (!okf[f] && lane == 0 && 4 * quad + f < A.B) A.redo_list[atomicAdd(A.redo_count, 1)] = fr[f];
+        }
+        if (!(okf[0] || okf[1] || okf[2] || okf[3])) continue;
+        D.met = 0.f; D.maxmet = 0; D.pidx = 0; D.cidx = 0; D.w0 = 0; D.ninfo = 0;
+        D.r4 = make_float4(0.f, 0.f, 0.f, 0.f); D.r2_0 = D.r2_1 = D.A0 = 0.f;
+#pragma unroll 1
+        for (int blk = 0; blk < n / 8; ++blk) {
+            // the 8 information flags of this subtree and, as bit 8, the first one of the next
+            const uint32_t iw = S.info_w[blk >> 2], iwn = S.info_w[(blk + 1) >> 2];
+            const uint32_t ib = ((iw >> (8 * (blk & 3))) & 0xFF) | (((iwn >> (8 * ((blk + 1) & 3))) & 1) << 8);
+            D.upper(blk, ybase, fr);
+            D.leaf8(blk, ib);
+        }
+        __syncwarp();
+        // ---- final selection (:432-473): u-hat = x-hat F^(x)m per slot, CRC, first pass wins ----
+        constexpr int NW = G::NW, HS = G::HS, lgN = M - 5;
+        const int q0 = A.crc ? 0 : 7;   // without a CRC the reference returns slot L-1 unconditionally
+#pragma unroll 1
+        for (int fs = 0; fs < 4; fs++) {
+            uint32_t* X = reinterpret_cast<uint32_t*>(D.W + fs * G::FRAME_WORDS);   // x-hat of every slot (setbit_last, d2 == M)
+            uint32_t* E = X + G::XW;
+#pragma unroll 1
+            for (int e = lane + (q0 << lgN); e < (8 << lgN); e += 32) {
+                const int q = e >> lgN, a = e & (NW - 1);
+                uint32_t x = X[q * HS + a];
+                x ^= (x >> 1) & 0x55555555u; x ^= (x >> 2) & 0x33333333u; x ^= (x >> 4) & 0x0F0F0F0Fu;
+                x ^= (x >> 8) & 0x00FF00FFu; x ^= (x >> 16) & 0x0000FFFFu;
+                X[q * HS + a] = x;
+            }
+            __syncwarp();
+#pragma unroll 1
+            for (int sw = 1; sw < NW; sw <<= 1) {
+#pragma unroll 1
+                for (int e = lane + (q0 << lgN); e < (8 << lgN); e += 32) {
+                    const int q = e >> lgN, a = e & (NW - 1);
+                    if (!(a & sw)) X[q * HS + a] ^= X[q * HS + a + sw];
+                }
+                __syncwarp();
+            }
+#pragma unroll 1
+            for (int q = q0; q < 8; q++) {
+#pragma unroll 1
+                for (int t0 = 0; t0 < A.stride; t0 += 32) {
+                    const int t = t0 + lane;
+                    int bit = 0;
+                    if (t < A.stride) { const int pos = A.info_pos[t]; bit = (X[q * HS + (pos >> 5)] >> (pos & 31)) & 1; }
+                    const unsigned wd = __ballot_sync(FULL, bit);
+                    if (lane == 0) E[q * EW + (t0 >> 5)] = wd;
+                }
+            }
+            __syncwarp();
+            bool ok = false;
+            if (A.crc && lane < 8) {
+                const uint32_t* e = E + lane * EW;
+                unsigned r = A.crc == 8 ? 0xFFu : 0xFFFFu;
+#pragma unroll 1
+                for (int b = 0; b < A.k / 8; b++) {
+                    const unsigned byte = __brev((e[b >> 2] >> (8 * (b & 3))) & 0xFFu) >> 24;
+                    if (A.crc == 8) r = q8::c_crc8.v[(r ^ byte) & 0xFF];
+                    else r = ((r << 8) ^ q8::c_crc16.v[((r >> 8) ^ byte) & 0xFF]) & 0xFFFF;
+                }
+                unsigned rx = 0;
+                for (int t = 0; t < A.crc; t++) { const int q = A.k + t; rx = (rx << 1) | ((e[q >> 5] >> (q & 31)) & 1); }
+                ok = (rx == r);
+            }
+            const unsigned okm = __ballot_sync(FULL, ok);
+            const int chosen = okm ? (__ffs(okm) - 1) : 7;
+            const int frame = 4 * quad + fs;
+            if (frame < A.B && okf[fs]) {
+                if (A.sol)
+                    for (int t = lane; t < A.stride; t += 32)
+                        A.sol[(size_t)frame * A.stride + t] = (E[chosen * EW + (t >> 5)] >> (t & 31)) & 1;
+                if (A.sol_bits)
+                    for (int t = lane; t < EW; t += 32) A.sol_bits[(size_t)frame * EW + t] = E[chosen * EW + t];
+            }
+            __syncwarp();
+        }
+    }
+}
+
+template <int M, typename YT>
+static cudaError_t launch_m(const Scl8qArgs& a, int blocks, cudaStream_t st) {
+    const size_t smem = (size_t)q8::Geo<M>::TOTAL;
+    cudaError_t e = cudaFuncSetAttribute(decode_scl8q_kernel<M, YT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    decode_scl8q_kernel<M, YT><<<blocks, 32, smem, st>>>(a);
+    return cudaGetLastError();
+}
+
+template <int M, typename YT>
+static cudaError_t occ_m(int* bps, int* warp_bytes) {
+    const size_t smem = (size_t)q8::Geo<M>::TOTAL;
+    *warp_bytes = q8::Geo<M>::TOTAL;
+    cudaError_t e = cudaFuncSetAttribute(decode_scl8q_kernel<M, YT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    return cudaOccupancyMaxActiveBlocksPerMultiprocessor(bps, decode_scl8q_kernel<M, YT>, 32, smem);
+}
+
+bool scl8q_supported(int m) { return m >= 8 && m <= 11; }
+
+// info_w: host copy of the information-mask words (ceil(n/32)), passed as kernel parameters
+cudaError_t launch_decode_scl8q(const DecodeArgs& a, const uint32_t* info_w, int blocks, cudaStream_t st) {
+    Scl8qArgs s;
+    s.a = a;
+    for (int i = 0; i < 65; i++) s.info_w[i] = i < a.n / 32 ? info_w[i] : 0;
+#define PCB_CASE(MM) \
+    case MM: return a.y_f32 ? launch_m<MM, float>(s, blocks, st) : launch_m<MM, double>(s, blocks, st);
+    switch (a.m) { PCB_CASE(8) PCB_CASE(9) PCB_CASE(10) PCB_CASE(11) }
+#undef PCB_CASE
+    return cudaErrorInvalidValue;
+}
+
+// resident blocks (= warps = frame quads) per SM of the more register-hungry (double input) variant
+cudaError_t scl8q_occupancy(int m, int* bps, int* warp_bytes) {
+    switch (m) {
+        case 8: return occ_m<8, double>(bps, warp_bytes);
+        case 9: return occ_m<9, double>(bps, warp_bytes);
+        case 10: return occ_m<10, double>(bps, warp_bytes);
+        case 11: return occ_m<11, double>(bps, warp_bytes);
+    }
+    return cudaErrorInvalidValue;
+}
+
+}  // namespace pcb
