@@ -29,7 +29,8 @@ cudaError_t launch_decode_scl8(const DecodeArgs& a, const uint32_t* info_w, cons
 cudaError_t scl8_occupancy(int m, int* bps, int* warp_bytes);
 // list-8 kernel with four frames per warp (decode_scl8q.cu)
 bool scl8q_supported(int m);
-cudaError_t launch_decode_scl8q(const DecodeArgs& a, const uint32_t* info_w, int blocks, cudaStream_t st);
+cudaError_t launch_decode_scl8q(const DecodeArgs& a, const uint32_t* info_w, void* l3_scratch, int blocks, cudaStream_t st);
+size_t scl8q_scratch_per_block(int m);
 cudaError_t scl8q_occupancy(int m, int* bps, int* warp_bytes);
 }  // namespace pcb
 
@@ -53,6 +54,7 @@ struct pcb_handle {
     // also re-decodes the frames the tuned kernel hands over)
     int f_bps = 0, f_warp_smem = 0;
     bool quad = false;              // four-frames-per-warp variant (decode_scl8q.cu) of the tuned kernel
+    void* d_qscratch = nullptr;     // quad kernel: layer-3 arrays of every resident block (stays in L2)
     int* d_redo = nullptr;          // [0] = count, [1..] = frame list
     size_t redo_cap = 0;
     size_t scratch_per_warp = 0;
@@ -217,7 +219,7 @@ void pcb_destroy(pcb_handle* h) {
         if (h->ev_out[s]) cudaEventDestroy(h->ev_out[s]);
     }
     cudaFree(h->d_ymc); cudaFree(h->d_tx); cudaFree(h->d_dec); cudaFree(h->d_counters);
-    cudaFree(h->d_eu); cudaFree(h->d_ex); cudaFree(h->d_redo);
+    cudaFree(h->d_eu); cudaFree(h->d_ex); cudaFree(h->d_redo); cudaFree(h->d_qscratch);
     if (h->t0) cudaEventDestroy(h->t0);
     if (h->t1) cudaEventDestroy(h->t1);
     if (h->sc) cudaStreamDestroy(h->sc);
@@ -304,7 +306,12 @@ static cudaError_t launch(pcb_handle* h, const DecodeArgs& a, cudaStream_t st) {
         if (e != cudaSuccess) return e;
         if (h->quad) {
             const int nq = (a.B + 3) / 4;
-            e = launch_decode_scl8q(f, h->h_info_w.data(), nq < fast_blocks(h) ? nq : fast_blocks(h), st);
+            const size_t spb = scl8q_scratch_per_block(h->m);
+            if (spb && !h->d_qscratch) {
+                cudaError_t e1 = cudaMalloc(&h->d_qscratch, spb * (size_t)fast_blocks(h));
+                if (e1 != cudaSuccess) return e1;
+            }
+            e = launch_decode_scl8q(f, h->h_info_w.data(), h->d_qscratch, nq < fast_blocks(h) ? nq : fast_blocks(h), st);
         } else {
             e = launch_decode_scl8(f, h->h_info_w.data(), h->h_fv_w.data(), a.B < fast_blocks(h) ? a.B : fast_blocks(h), st);
         }

@@ -33,24 +33,31 @@ struct Geo {
     static constexpr int N = 1 << M;
     static constexpr int LTOP = 3;          // first stored LLR layer (size N/8)
     static constexpr int LBOT = M - 3;      // last stored LLR layer (size 8); sizes 4,2,1 are registers
+    // N >= 1024: layer 3 (half of all stored LLRs) lives in a per-block global scratch that stays in
+    // L2, which doubles the resident frames per SM; it is written and read 8 times per frame.
+    static constexpr bool GL3 = M >= 10;
+    static constexpr int LS = GL3 ? 4 : 3;  // first LLR layer in shared memory
     static constexpr int NW = N / 32;       // words of a full-length bit array
     static constexpr int HS = NW + 1;       // slot stride of the partial-sum heap (layer of size S at words [S/32, 2S/32))
+    static constexpr int Q3 = N / 32;       // float4s of one layer-3 array
     __host__ __device__ static constexpr int size(int lam) { return N >> lam; }
     __host__ __device__ static constexpr int stride(int lam) { return size(lam) + 4; }
     __host__ __device__ static constexpr int off(int lam) {
         int o = 0;
-        for (int l = LTOP; l < lam; ++l) o += 8 * stride(l);
+        for (int l = LS; l < lam; ++l) o += 8 * stride(l);
         return o;
     }
     static constexpr int PFLOATS = off(LBOT + 1);
-    static constexpr int STAGE_OFF = off(LTOP + 1);          // staging area = layers 4..LBOT
-    static_assert(PFLOATS - STAGE_OFF >= N, "staging area too small");
+    // staging area = the layers below the one the top stage writes (dead at those phases)
+    static constexpr int STAGE_OFF = off(LS + 1);
+    static_assert(PFLOATS - STAGE_OFF >= (GL3 ? N / 2 : N), "staging area too small");
     static constexpr int XW = 8 * HS;                        // final codeword estimates (alias the LLR region)
     static_assert(XW + 8 * NW <= PFLOATS, "final-stage scratch does not fit the LLR region");
     static constexpr int FRAME_WORDS = PFLOATS + 8 * HS + 16;   // LLRs, heaps, 16 candidate keys
     static constexpr int OFF_H = PFLOATS;
     static constexpr int OFF_KEYS = PFLOATS + 8 * HS;
     static constexpr int TOTAL = 4 * FRAME_WORDS * 4;
+    static constexpr int L3_BLOCK_FLOAT4 = GL3 ? 4 * Q3 * 8 : 0;   // global scratch per block: [frame][k][slot] float4
     static_assert((FRAME_WORDS * 4) % 16 == 0 && (OFF_H * 4) % 16 == 0 && (OFF_KEYS * 4) % 16 == 0, "alignment");
 };
 
@@ -176,6 +183,7 @@ struct Dec {
     uint32_t* H;       // this frame's partial-sum heaps
     uint32_t* keys;    // this frame's 16 candidate keys
     float* W;          // the warp's whole slice (4 frames)
+    float4* L3;        // GL3: this frame's layer-3 arrays in global memory, element (k, slot) at L3[k*8 + slot]
     float met;
     uint32_t maxmet;   // bit pattern of the largest metric of this frame (valid whenever the next phase is an information bit)
     uint32_t pidx, cidx, w0;
@@ -204,6 +212,79 @@ struct Dec {
             return *reinterpret_cast<const float4*>(y + 4 * q);
         }
     }
+    // GL3: layers 3 and 4 from the channel values.  Layer 3 goes to the global scratch, layer 4
+    // (always an f-layer here) to shared memory.  With a g-layer 1 the channel values are staged
+    // in rounds of 8+8 float4 columns (k and k + Q3/2, the two operands of a layer-4 output), so
+    // that the staging area never overlaps the layer-4 arrays being written.
+    __device__ __forceinline__ void top_gl3(int ev, const YT* ybase, const int (&fr)[4]) {
+        constexpr int E = G::N / 8, N4 = G::N / 4, Q = G::Q3, NR = Q / 16;
+        const bool g1 = ev & 4, g2 = ev & 2, g3 = ev & 1;
+        const float* R = P + G::STAGE_OFF;
+        float* dst4 = arr(4, p);
+        float4* dst3 = L3 + p;
+        __syncwarp();                            // everyone is done with the previous subtree
+        if (!g1) {
+#pragma unroll
+            for (int f = 0; f < 4; f++) {
+                const YT* y = ybase + (size_t)fr[f] * G::N;
+                float* Rf = W + f * G::FRAME_WORDS + G::STAGE_OFF;
+#pragma unroll 4
+                for (int q = lane; q < N4 / 2; q += 32)
+                    *reinterpret_cast<float4*>(Rf + 4 * q) = ff4(load_y4(y, q), load_y4(y, q + N4 / 2));
+            }
+            __syncwarp();
+        }
+#pragma unroll 1
+        for (int r = 0; r < NR; r++) {
+            if (g1) {
+                if (r) __syncwarp();
+#pragma unroll
+                for (int i = 0; i < 16; i++) {   // unit u = i*32 + lane: frame i/4, then t (8), h (2), kk (8)
+                    const int u = i * 32 + lane, t = (u >> 4) & 7, h = (u >> 3) & 1, kk = u & 7;
+                    const YT* y = ybase + (size_t)fr[i >> 2] * G::N;
+                    *reinterpret_cast<float4*>(W + (i >> 2) * G::FRAME_WORDS + G::STAGE_OFF + (u & 127) * 4) =
+                        load_y4(y, t * Q + h * (Q / 2) + r * 8 + kk);
+                }
+                __syncwarp();
+            }
+            uint32_t c1[4][2], c2[2][2], c3[2];
+#pragma unroll
+            for (int h = 0; h < 2; h++) {
+                const int w32 = h * (Q / 16) + r;
+#pragma unroll
+                for (int t = 0; t < 4; t++) c1[t][h] = g1 ? cword(1, t * E, w32) : 0u;
+                c2[0][h] = g2 ? cword(2, 0, w32) : 0u; c2[1][h] = g2 ? cword(2, E, w32) : 0u;
+                c3[h] = g3 ? cword(3, 0, w32) : 0u;
+            }
+#pragma unroll 1
+            for (int kk = 0; kk < 8; kk++) {
+                float4 o[2];
+#pragma unroll
+                for (int h = 0; h < 2; h++) {
+                    const int k = h * (Q / 2) + r * 8 + kk;
+                    float4 l1[4];
+                    if (g1) {
+                        float4 yv[8];
+#pragma unroll
+                        for (int t = 0; t < 8; t++) yv[t] = *reinterpret_cast<const float4*>(R + ((t * 2 + h) * 8 + kk) * 4);
+#pragma unroll
+                        for (int t = 0; t < 4; t++) l1[t] = gs4(yv[t], yv[t + 4], c1[t][h], 4 * kk);
+                    } else {
+#pragma unroll
+                        for (int t = 0; t < 4; t++) l1[t] = *reinterpret_cast<const float4*>(R + t * E + 4 * k);
+                    }
+                    float4 l2[2];
+                    if (g2) { l2[0] = gs4(l1[0], l1[2], c2[0][h], 4 * kk); l2[1] = gs4(l1[1], l1[3], c2[1][h], 4 * kk); }
+                    else { l2[0] = ff4(l1[0], l1[2]); l2[1] = ff4(l1[1], l1[3]); }
+                    o[h] = g3 ? gs4(l2[0], l2[1], c3[h], 4 * kk) : ff4(l2[0], l2[1]);
+                    dst3[k * 8] = o[h];
+                }
+                *reinterpret_cast<float4*>(dst4 + 4 * (r * 8 + kk)) = ff4(o[0], o[1]);
+            }
+        }
+        __syncwarp();                            // the staging area is overwritten by layer 5 next
+    }
+
     __device__ __forceinline__ void top3(int ev, const YT* ybase, const int (&fr)[4]) {
         constexpr int E = G::N / 8, N4 = G::N / 4;
         const bool g1 = ev & 4, g2 = ev & 2, g3 = ev & 1;
@@ -270,8 +351,22 @@ struct Dec {
     __device__ __forceinline__ void layer() {
         constexpr int S = G::size(LAM);       // outputs
         const int slot = ISG ? pfield(LAM - 1) : p;
-        const float* src = arr(LAM - 1, slot);
         float* dst = arr(LAM, p);
+        if constexpr (G::GL3 && LAM == 4) {   // g from the layer-3 arrays in global memory (L2)
+            static_assert(ISG, "layer 4 as an f-layer is produced by top_gl3");
+            const float4* src = L3 + slot;
+#pragma unroll 1
+            for (int k0 = 0; k0 < S / 4; k0 += 8) {
+                const uint32_t cw = cword(LAM, 0, k0 >> 3);
+                float4 a[8], b[8];
+#pragma unroll
+                for (int kk = 0; kk < 8; kk++) { a[kk] = src[(k0 + kk) * 8]; b[kk] = src[(k0 + kk + S / 4) * 8]; }
+#pragma unroll
+                for (int kk = 0; kk < 8; kk++) *reinterpret_cast<float4*>(dst + 4 * (k0 + kk)) = gs4(a[kk], b[kk], cw, 4 * kk);
+            }
+            return;
+        }
+        const float* src = arr(LAM - 1, slot);
         if constexpr (S >= 32) {
 #pragma unroll 1
             for (int k0 = 0; k0 < S / 4; k0 += 8) {
@@ -314,12 +409,15 @@ struct Dec {
     // LLR work at the first phase i0 = 8*blk of a size-8 subtree, down to layer LBOT
     __device__ __forceinline__ void upper(int blk, const YT* ybase, const int (&fr)[4]) {
         const int z = blk ? (__ffs(blk) - 1) : 31;
-        int ll;
-        if (z >= M - 6) { top3(blk >> (M - 6), ybase, fr); ll = G::LTOP; }     // i0 is a multiple of N/8
-        else { __syncwarp(); ll = G::LBOT - z; g_dispatch<G::LBOT>(ll); }
-        f_below<G::LTOP + 1>(ll);
-        // layers >= ll are now this slot's own
-        const uint32_t low = (1u << (3 * (ll - G::LTOP))) - 1;
+        int ll, own;    // layers own.. are recomputed, the f-layers below ll are still to do
+        if (z >= M - 6) {                                  // i0 is a multiple of N/8
+            if constexpr (G::GL3) { top_gl3(blk >> (M - 6), ybase, fr); ll = 4; }
+            else { top3(blk >> (M - 6), ybase, fr); ll = 3; }
+            own = G::LTOP;
+        } else { __syncwarp(); ll = own = G::LBOT - z; g_dispatch<G::LBOT>(ll); }
+        f_below<G::LS + 1>(ll);
+        // layers >= own are now this slot's own
+        const uint32_t low = (1u << (3 * (own - G::LTOP))) - 1;
         pidx = (pidx & low) | ((0x9249249u * (uint32_t)p) & ~low);
     }
 
@@ -465,11 +563,12 @@ __constant__ CrcTable c_crc16 = make_crc(16);
 struct Scl8qArgs {
     DecodeArgs a;
     uint32_t info_w[65];   // n <= 2048, one zero word behind the last
+    float4* l3;            // n >= 1024: global scratch of the layer-3 arrays, Geo::L3_BLOCK_FLOAT4 per block
 };
 
 // One warp per block (blockDim.x == 32); a block decodes quads of frames.
 template <int M, typename YT>
-__global__ void __launch_bounds__(32, 5) decode_scl8q_kernel(const __grid_constant__ Scl8qArgs S) {
+__global__ void __launch_bounds__(32, (M >= 10 ? 10 : 5)) decode_scl8q_kernel(const __grid_constant__ Scl8qArgs S) {
     const DecodeArgs& A = S.a;
     using G = q8::Geo<M>;
     extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -481,6 +580,7 @@ __global__ void __launch_bounds__(32, 5) decode_scl8q_kernel(const __grid_consta
     D.P = D.W + fme * G::FRAME_WORDS;
     D.H = reinterpret_cast<uint32_t*>(D.P) + G::OFF_H;
     D.keys = reinterpret_cast<uint32_t*>(D.P) + G::OFF_KEYS;
+    D.L3 = G::GL3 ? S.l3 + (size_t)blockIdx.x * G::L3_BLOCK_FLOAT4 + fme * (G::Q3 * 8) : nullptr;
     constexpr int n = G::N;
     const int EW = (A.stride + 31) >> 5;
     const YT* ybase = reinterpret_cast<const YT*>(A.y);
@@ -606,15 +706,25 @@ static cudaError_t occ_m(int* bps, int* warp_bytes) {
 bool scl8q_supported(int m) { return m >= 8 && m <= 11; }
 
 // info_w: host copy of the information-mask words (ceil(n/32)), passed as kernel parameters
-cudaError_t launch_decode_scl8q(const DecodeArgs& a, const uint32_t* info_w, int blocks, cudaStream_t st) {
+cudaError_t launch_decode_scl8q(const DecodeArgs& a, const uint32_t* info_w, void* l3_scratch, int blocks, cudaStream_t st) {
     Scl8qArgs s;
     s.a = a;
+    s.l3 = reinterpret_cast<float4*>(l3_scratch);
     for (int i = 0; i < 65; i++) s.info_w[i] = i < a.n / 32 ? info_w[i] : 0;
 #define PCB_CASE(MM) \
     case MM: return a.y_f32 ? launch_m<MM, float>(s, blocks, st) : launch_m<MM, double>(s, blocks, st);
     switch (a.m) { PCB_CASE(8) PCB_CASE(9) PCB_CASE(10) PCB_CASE(11) }
 #undef PCB_CASE
     return cudaErrorInvalidValue;
+}
+
+// bytes of global scratch one block needs (layer-3 arrays of its four frames)
+size_t scl8q_scratch_per_block(int m) {
+    switch (m) {
+        case 10: return (size_t)q8::Geo<10>::L3_BLOCK_FLOAT4 * 16;
+        case 11: return (size_t)q8::Geo<11>::L3_BLOCK_FLOAT4 * 16;
+    }
+    return 0;
 }
 
 // resident blocks (= warps = frame quads) per SM of the more register-hungry (double input) variant
