@@ -346,63 +346,48 @@ struct Dec {
     }
 
     // ---- one stored layer from the previous stored layer ------------------------------
-    // ISG: g-layer (first layer of a chain, source slot is the lazily shared one)
-    template <int LAM, bool ISG>
-    __device__ __forceinline__ void layer() {
-        constexpr int S = G::size(LAM);       // outputs
-        const int slot = ISG ? pfield(LAM - 1) : p;
-        float* dst = arr(LAM, p);
-        if constexpr (G::GL3 && LAM == 4) {   // g from the layer-3 arrays in global memory (L2)
-            static_assert(ISG, "layer 4 as an f-layer is produced by top_gl3");
-            const float4* src = L3 + slot;
-#pragma unroll 1
-            for (int k0 = 0; k0 < S / 4; k0 += 8) {
-                const uint32_t cw = cword(LAM, 0, k0 >> 3);
-                float4 a[8], b[8];
-#pragma unroll
-                for (int kk = 0; kk < 8; kk++) { a[kk] = src[(k0 + kk) * 8]; b[kk] = src[(k0 + kk + S / 4) * 8]; }
-#pragma unroll
-                for (int kk = 0; kk < 8; kk++) *reinterpret_cast<float4*>(dst + 4 * (k0 + kk)) = gs4(a[kk], b[kk], cw, 4 * kk);
-            }
-            return;
-        }
-        const float* src = arr(LAM - 1, slot);
-        if constexpr (S >= 32) {
-#pragma unroll 1
-            for (int k0 = 0; k0 < S / 4; k0 += 8) {
-                uint32_t cw = 0;
-                if (ISG) cw = cword(LAM, 0, k0 >> 3);
-#pragma unroll
-                for (int kk = 0; kk < 8; kk++) {
-                    const float4 a = *reinterpret_cast<const float4*>(src + 4 * (k0 + kk));
-                    const float4 b = *reinterpret_cast<const float4*>(src + S + 4 * (k0 + kk));
-                    *reinterpret_cast<float4*>(dst + 4 * (k0 + kk)) = ISG ? gs4(a, b, cw, 4 * kk) : ff4(a, b);
-                }
-            }
-        } else {                              // S = 16: bits [16,32) of w0; S = 8: bits [8,16)
-#pragma unroll
-            for (int kk = 0; kk < S / 4; kk++) {
-                const float4 a = *reinterpret_cast<const float4*>(src + 4 * kk);
-                const float4 b = *reinterpret_cast<const float4*>(src + S + 4 * kk);
-                *reinterpret_cast<float4*>(dst + 4 * kk) = ISG ? gs4(a, b, w0, S + 4 * kk) : ff4(a, b);
-            }
+    // The layer is a run-time value: one compact loop serves every size (the ten resident warps
+    // of an SM sit at different places of the program, so code size is instruction-cache traffic).
+    __device__ __forceinline__ int off_rt(int lam) const {      // == G::off(lam)
+        return 8 * ((G::N >> (G::LS - 1)) - (G::N >> (lam - 1))) + 32 * (lam - G::LS);
+    }
+    // f-layer: own arrays
+    __device__ __forceinline__ void layer_f(int lam) {
+        const int S = G::N >> lam;
+        const float* src = P + off_rt(lam - 1) + p * (2 * S + 4);
+        float* dst = P + off_rt(lam) + p * (S + 4);
+#pragma unroll 2
+        for (int k = 0; k < S; k += 4)
+            *reinterpret_cast<float4*>(dst + k) =
+                ff4(*reinterpret_cast<const float4*>(src + k), *reinterpret_cast<const float4*>(src + S + k));
+    }
+    // g-layer (first layer of a chain): the source slot is the lazily shared one; partial sums of
+    // sizes >= 32 come from the heap, smaller ones from w0 (bits [S, 2S))
+    __device__ __forceinline__ void layer_g(int lam) {
+        const int S = G::N >> lam;
+        const float* src = P + off_rt(lam - 1) + pfield(lam - 1) * (2 * S + 4);
+        float* dst = P + off_rt(lam) + p * (S + 4);
+        const uint32_t* hw = H + cfield(lam) * G::HS + (S >> 5);
+#pragma unroll 2
+        for (int k = 0; k < S; k += 4) {
+            const uint32_t cw = S >= 32 ? (hw[k >> 5] >> (k & 31)) : (w0 >> (S + k));
+            *reinterpret_cast<float4*>(dst + k) =
+                gs4(*reinterpret_cast<const float4*>(src + k), *reinterpret_cast<const float4*>(src + S + k), cw, 0);
         }
     }
-
-    // g at layer ll (one of LTOP+1..LBOT); every g variant appears once in the binary
-    template <int LAM>
-    __device__ __forceinline__ void g_dispatch(int ll) {
-        if constexpr (LAM > G::LTOP) {
-            if (ll == LAM) layer<LAM, true>();
-            else g_dispatch<LAM - 1>(ll);
-        }
-    }
-    // f layers ll+1..LBOT; every f variant appears once in the binary
-    template <int LAM>
-    __device__ __forceinline__ void f_below(int ll) {
-        if constexpr (LAM <= G::LBOT) {
-            if (ll < LAM) layer<LAM, false>();
-            f_below<LAM + 1>(ll);
+    // GL3: g at layer 4 from the layer-3 arrays in global memory (L2)
+    __device__ __forceinline__ void layer4_g_global() {
+        constexpr int S = G::size(4);
+        const float4* src = L3 + pfield(3);
+        float* dst = arr(4, p);
+#pragma unroll 1
+        for (int k0 = 0; k0 < S / 4; k0 += 8) {
+            const uint32_t cw = cword(4, 0, k0 >> 3);
+            float4 a[8], b[8];
+#pragma unroll
+            for (int kk = 0; kk < 8; kk++) { a[kk] = src[(k0 + kk) * 8]; b[kk] = src[(k0 + kk + S / 4) * 8]; }
+#pragma unroll
+            for (int kk = 0; kk < 8; kk++) *reinterpret_cast<float4*>(dst + 4 * (k0 + kk)) = gs4(a[kk], b[kk], cw, 4 * kk);
         }
     }
 
@@ -414,15 +399,20 @@ struct Dec {
             if constexpr (G::GL3) { top_gl3(blk >> (M - 6), ybase, fr); ll = 4; }
             else { top3(blk >> (M - 6), ybase, fr); ll = 3; }
             own = G::LTOP;
-        } else { __syncwarp(); ll = own = G::LBOT - z; g_dispatch<G::LBOT>(ll); }
-        f_below<G::LS + 1>(ll);
+        } else {
+            __syncwarp();
+            ll = own = G::LBOT - z;
+            if (G::GL3 && ll == 4) layer4_g_global();
+            else layer_g(ll);
+        }
+#pragma unroll 1
+        for (int lam = ll + 1; lam <= G::LBOT; lam++) layer_f(lam);
         // layers >= own are now this slot's own
         const uint32_t low = (1u << (3 * (own - G::LTOP))) - 1;
         pidx = (pidx & low) | ((0x9249249u * (uint32_t)p) & ~low);
     }
 
     // ---- fork / prune of one information bit (SCLDecoderMinsum.cpp:315-400) ----------
-    template <int T>
     __device__ __forceinline__ int fork() {
         if (ninfo >= 3) {
             // Fast exit (no kill, no clone): the candidates of path p are {met, met + |llr|}.  If
@@ -437,36 +427,30 @@ struct Dec {
         met = s.met; pidx = s.pidx; cidx = s.cidx; w0 = s.w0;
         const int sl = (s.r >> 2) & 31;
         const bool take = s.r & 2u;
-        if ((T & 3) < 2) {                      // the size-4 layer is still to be read by a g
+        {   // register layers (a dead one is copied too: cheaper than eight specialised call sites)
             const float x = __shfl_sync(FULL, r4.x, sl), y = __shfl_sync(FULL, r4.y, sl);
             const float z = __shfl_sync(FULL, r4.z, sl), w = __shfl_sync(FULL, r4.w, sl);
-            if (take) r4 = make_float4(x, y, z, w);
-        }
-        if (!(T & 1)) {                         // so is the size-2 layer
-            const float x = __shfl_sync(FULL, r2_0, sl), y = __shfl_sync(FULL, r2_1, sl);
-            if (take) { r2_0 = x; r2_1 = y; }
+            const float a = __shfl_sync(FULL, r2_0, sl), b = __shfl_sync(FULL, r2_1, sl);
+            if (take) { r4 = make_float4(x, y, z, w); r2_0 = a; r2_1 = b; }
         }
         if (ninfo < 3) ninfo++;
         maxmet = group_max(__float_as_uint(met), lane >> 3);
         return s.r & 1;
     }
 
-    // decision at phase i0+T with the leaf LLR in A0
-    template <int T>
-    __device__ __forceinline__ int decide(uint32_t infobyte) {
-        if ((infobyte >> T) & 1) return fork<T>();
+    // decision with the leaf LLR in A0
+    __device__ __forceinline__ int decide(bool isinfo, bool nextinfo) {
+        if (isinfo) return fork();
         met += fmaxf(-A0, 0.f);         // frozen value 0 (:413-418)
         // the fast exit of the next information bit compares against the largest metric of the frame
-        if ((infobyte >> (T + 1)) & 1) maxmet = group_max(__float_as_uint(met), lane >> 3);
+        if (nextinfo) maxmet = group_max(__float_as_uint(met), lane >> 3);
         return 0;
     }
 
     // partial-sum combine at the last phase of a subtree (t = 7): d2 = 3 + ctz(blk+1)
-    __device__ __forceinline__ void setbit_last(int blk, int u) {
+    // T: the size-4 partial sums of the last four phases
+    __device__ __forceinline__ void setbit_last(int blk, uint32_t T) {
         const int d2 = min(M, 3 + __ffs(blk + 1) - 1);
-        uint32_t T = (uint32_t)u;
-        T = (((w0 >> 1) ^ T) & 1u) | (T << 1);
-        T = (((w0 >> 2) ^ T) & 3u) | (T << 2);
         T = (((w0 >> 4) ^ T) & 15u) | (T << 4);
         if (d2 == 3) { w0 = (w0 & ~0xFF00u) | (T << 8); return; }
         T = (((w0 >> 8) ^ T) & 0xFFu) | (T << 8);
@@ -491,51 +475,38 @@ struct Dec {
         }
     }
 
-    // the 8 phases of one size-8 subtree; layer LBOT of this subtree is already computed
+    // the 8 phases of one size-8 subtree as four size-2 subtrees; layer LBOT is already computed.
+    // ib: information flags of the 8 phases, bit 8 = first phase of the next subtree.
     __device__ __forceinline__ void leaf8(int blk, uint32_t ib) {
-        int u;
-        // t = 0: own arrays all the way down
-        {
-            const float* v = arr(G::LBOT, p);
-            r4 = ff4(*reinterpret_cast<const float4*>(v), *reinterpret_cast<const float4*>(v + 4));
+        uint32_t T = 0;
+#pragma unroll 1
+        for (int j = 0; j < 4; j++, ib >>= 2) {
+            if (!(j & 1)) {
+                if (j == 0) {                    // own arrays all the way down
+                    const float* v = arr(G::LBOT, p);
+                    r4 = ff4(*reinterpret_cast<const float4*>(v), *reinterpret_cast<const float4*>(v + 4));
+                } else {                         // the size-8 layer may be a parent's
+                    __syncwarp();
+                    const float* v = arr(G::LBOT, pfield(G::LBOT));
+                    r4 = gs4(*reinterpret_cast<const float4*>(v), *reinterpret_cast<const float4*>(v + 4), w0, 4);
+                }
+                r2_0 = ff(r4.x, r4.z); r2_1 = ff(r4.y, r4.w);
+            } else {
+                r2_0 = gs(r4.x, r4.z, sgn(w0, 2)); r2_1 = gs(r4.y, r4.w, sgn(w0, 3));
+            }
+            A0 = ff(r2_0, r2_1);
+            int u = decide(ib & 1, ib & 2);
+            w0 = (w0 & ~2u) | ((uint32_t)u << 1);
+            A0 = gs(r2_0, r2_1, sgn(w0, 1));
+            u = decide(ib & 2, ib & 4);
+            T = (((w0 >> 1) ^ u) & 1u) | ((uint32_t)u << 1);            // size-2 partial sums
+            if (!(j & 1)) w0 = (w0 & ~0xCu) | (T << 2);
+            else {
+                T = (((w0 >> 2) ^ T) & 3u) | (T << 2);                   // size 4
+                if (j == 1) w0 = (w0 & ~0xF0u) | (T << 4);
+            }
         }
-        r2_0 = ff(r4.x, r4.z); r2_1 = ff(r4.y, r4.w);
-        A0 = ff(r2_0, r2_1);
-        u = decide<0>(ib); w0 = (w0 & ~2u) | ((uint32_t)u << 1);
-        // t = 1
-        A0 = gs(r2_0, r2_1, sgn(w0, 1));
-        u = decide<1>(ib);
-        { uint32_t T = (((w0 >> 1) ^ u) & 1u) | ((uint32_t)u << 1); w0 = (w0 & ~0xCu) | (T << 2); }
-        // t = 2
-        r2_0 = gs(r4.x, r4.z, sgn(w0, 2)); r2_1 = gs(r4.y, r4.w, sgn(w0, 3));
-        A0 = ff(r2_0, r2_1);
-        u = decide<2>(ib); w0 = (w0 & ~2u) | ((uint32_t)u << 1);
-        // t = 3
-        A0 = gs(r2_0, r2_1, sgn(w0, 1));
-        u = decide<3>(ib);
-        { uint32_t T = (((w0 >> 1) ^ u) & 1u) | ((uint32_t)u << 1); T = (((w0 >> 2) ^ T) & 3u) | (T << 2);
-          w0 = (w0 & ~0xF0u) | (T << 4); }
-        // t = 4: the size-8 layer may be a parent's
-        {
-            __syncwarp();
-            const float* v = arr(G::LBOT, pfield(G::LBOT));
-            r4 = gs4(*reinterpret_cast<const float4*>(v), *reinterpret_cast<const float4*>(v + 4), w0, 4);
-        }
-        r2_0 = ff(r4.x, r4.z); r2_1 = ff(r4.y, r4.w);
-        A0 = ff(r2_0, r2_1);
-        u = decide<4>(ib); w0 = (w0 & ~2u) | ((uint32_t)u << 1);
-        // t = 5
-        A0 = gs(r2_0, r2_1, sgn(w0, 1));
-        u = decide<5>(ib);
-        { uint32_t T = (((w0 >> 1) ^ u) & 1u) | ((uint32_t)u << 1); w0 = (w0 & ~0xCu) | (T << 2); }
-        // t = 6
-        r2_0 = gs(r4.x, r4.z, sgn(w0, 2)); r2_1 = gs(r4.y, r4.w, sgn(w0, 3));
-        A0 = ff(r2_0, r2_1);
-        u = decide<6>(ib); w0 = (w0 & ~2u) | ((uint32_t)u << 1);
-        // t = 7
-        A0 = gs(r2_0, r2_1, sgn(w0, 1));
-        u = decide<7>(ib);
-        setbit_last(blk, u);
+        setbit_last(blk, T);
     }
 };
 
