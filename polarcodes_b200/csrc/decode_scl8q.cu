@@ -475,38 +475,87 @@ struct Dec {
         }
     }
 
-    // the 8 phases of one size-8 subtree as four size-2 subtrees; layer LBOT is already computed.
+    // ---- the four phases of one size-4 subtree (its LLRs in r4, pairs (x,z) and (y,w)) --------
+    // Three routines produce the same results as four successive phases of the reference loop
+    // (SCLDecoderMinsum.cpp:409-431); each returns the size-4 partial sums [c0^d0, c1^d1, d0, d1].
+
+    // all four positions frozen (value 0): no decisions, only the four metric updates in phase order
+    __device__ __forceinline__ uint32_t rate0(bool nextinfo) {
+        const float a = ff(r4.x, r4.z), b = ff(r4.y, r4.w);
+        met += fmaxf(-ff(a, b), 0.f);
+        met += fmaxf(-(b + a), 0.f);
+        const float a2 = r4.z + r4.x, b2 = r4.w + r4.y;     // g with partial sums 0
+        met += fmaxf(-ff(a2, b2), 0.f);
+        met += fmaxf(-(b2 + a2), 0.f);
+        if (nextinfo) maxmet = group_max(__float_as_uint(met), lane >> 3);
+        return 0u;
+    }
+
+    // all four positions information bits, list full: assume every phase takes the fast exit (each
+    // path keeps its likelier bit, metrics unchanged), compute the four leaf LLRs lane-locally and
+    // verify all four exits with ONE vote: min_t (met + |A_t|) = met + min_t |A_t| must exceed the
+    // largest metric of the frame.  A zero LLR fails the test (hi == met), so below the test the
+    // sign bit of A_t IS the decision (A_t < 0).  Nothing is committed on failure.
+    __device__ __forceinline__ bool rate1(uint32_t& T4) {
+        constexpr uint32_t SB = 0x80000000u;
+        const float a = ff(r4.x, r4.z), b = ff(r4.y, r4.w);
+        const float A0 = ff(a, b);
+        const float A1 = b + __uint_as_float(__float_as_uint(a) ^ (__float_as_uint(A0) & SB));
+        const uint32_t t01 = __float_as_uint(A0) ^ __float_as_uint(A1);            // sign = c0 = u0^u1
+        const float a2 = r4.z + __uint_as_float(__float_as_uint(r4.x) ^ (t01 & SB));
+        const float b2 = r4.w + __uint_as_float(__float_as_uint(r4.y) ^ (__float_as_uint(A1) & SB));
+        const float A2 = ff(a2, b2);
+        const float A3 = b2 + __uint_as_float(__float_as_uint(a2) ^ (__float_as_uint(A2) & SB));
+        const float mn = fminf(fminf(fabsf(A0), fabsf(A1)), fminf(fabsf(A2), fabsf(A3)));
+        const float hi = met + mn;
+        if (!__all_sync(FULL, __float_as_uint(hi) > maxmet)) return false;
+        const uint32_t t23 = __float_as_uint(A2) ^ __float_as_uint(A3);             // sign = d0 = u2^u3
+        const uint32_t s1 = __float_as_uint(A1), s3 = __float_as_uint(A3);
+        T4 = ((t01 ^ t23) >> 31) | (((s1 ^ s3) >> 31) << 1) | ((t23 >> 31) << 2) | ((s3 >> 31) << 3);
+        return true;
+    }
+
+    // any pattern, phase by phase; ib: information flags of the four phases, bit 4 = next phase
+    __device__ __forceinline__ uint32_t seq4(uint32_t ib) {
+        r2_0 = ff(r4.x, r4.z); r2_1 = ff(r4.y, r4.w);
+        A0 = ff(r2_0, r2_1);
+        int u = decide(ib & 1, ib & 2);
+        w0 = (w0 & ~2u) | ((uint32_t)u << 1);
+        A0 = gs(r2_0, r2_1, sgn(w0, 1));
+        u = decide(ib & 2, ib & 4);
+        uint32_t T = (((w0 >> 1) ^ u) & 1u) | ((uint32_t)u << 1);            // size-2 partial sums
+        w0 = (w0 & ~0xCu) | (T << 2);
+        r2_0 = gs(r4.x, r4.z, sgn(w0, 2)); r2_1 = gs(r4.y, r4.w, sgn(w0, 3));
+        A0 = ff(r2_0, r2_1);
+        u = decide(ib & 4, ib & 8);
+        w0 = (w0 & ~2u) | ((uint32_t)u << 1);
+        A0 = gs(r2_0, r2_1, sgn(w0, 1));
+        u = decide(ib & 8, ib & 16);
+        T = (((w0 >> 1) ^ u) & 1u) | ((uint32_t)u << 1);
+        return (((w0 >> 2) ^ T) & 3u) | (T << 2);                            // size 4
+    }
+
+    // the 8 phases of one size-8 subtree as two size-4 subtrees; layer LBOT is already computed.
     // ib: information flags of the 8 phases, bit 8 = first phase of the next subtree.
     __device__ __forceinline__ void leaf8(int blk, uint32_t ib) {
-        uint32_t T = 0;
+        uint32_t T4 = 0;
 #pragma unroll 1
-        for (int j = 0; j < 4; j++, ib >>= 2) {
-            if (!(j & 1)) {
-                if (j == 0) {                    // own arrays all the way down
-                    const float* v = arr(G::LBOT, p);
-                    r4 = ff4(*reinterpret_cast<const float4*>(v), *reinterpret_cast<const float4*>(v + 4));
-                } else {                         // the size-8 layer may be a parent's
-                    __syncwarp();
-                    const float* v = arr(G::LBOT, pfield(G::LBOT));
-                    r4 = gs4(*reinterpret_cast<const float4*>(v), *reinterpret_cast<const float4*>(v + 4), w0, 4);
-                }
-                r2_0 = ff(r4.x, r4.z); r2_1 = ff(r4.y, r4.w);
-            } else {
-                r2_0 = gs(r4.x, r4.z, sgn(w0, 2)); r2_1 = gs(r4.y, r4.w, sgn(w0, 3));
+        for (int h = 0; h < 2; h++, ib >>= 4) {
+            if (h == 0) {                    // own arrays all the way down
+                const float* v = arr(G::LBOT, p);
+                r4 = ff4(*reinterpret_cast<const float4*>(v), *reinterpret_cast<const float4*>(v + 4));
+            } else {                         // the size-8 layer may be a parent's
+                __syncwarp();
+                const float* v = arr(G::LBOT, pfield(G::LBOT));
+                r4 = gs4(*reinterpret_cast<const float4*>(v), *reinterpret_cast<const float4*>(v + 4), w0, 4);
             }
-            A0 = ff(r2_0, r2_1);
-            int u = decide(ib & 1, ib & 2);
-            w0 = (w0 & ~2u) | ((uint32_t)u << 1);
-            A0 = gs(r2_0, r2_1, sgn(w0, 1));
-            u = decide(ib & 2, ib & 4);
-            T = (((w0 >> 1) ^ u) & 1u) | ((uint32_t)u << 1);            // size-2 partial sums
-            if (!(j & 1)) w0 = (w0 & ~0xCu) | (T << 2);
-            else {
-                T = (((w0 >> 2) ^ T) & 3u) | (T << 2);                   // size 4
-                if (j == 1) w0 = (w0 & ~0xF0u) | (T << 4);
-            }
+            const uint32_t pat = ib & 15u;
+            if (pat == 0u) T4 = rate0(ib & 16u);
+            else if (pat == 15u && ninfo >= 3 && rate1(T4)) {}
+            else T4 = seq4(ib);
+            if (h == 0) w0 = (w0 & ~0xF0u) | (T4 << 4);
         }
-        setbit_last(blk, T);
+        setbit_last(blk, T4);
     }
 };
 
