@@ -242,6 +242,24 @@ __global__ void count_errors_kernel(const uint32_t* __restrict__ dec, const uint
     }
 }
 
+// HBM-bound pre-pass of the list-8 quad kernel: 12 bytes per value, 128-bit accesses
+__global__ void __launch_bounds__(256) convert_f64_f32_kernel(const double* __restrict__ y64, float* __restrict__ y32, size_t count4) {
+    const size_t stride = (size_t)gridDim.x * blockDim.x;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < count4; i += stride) {
+        const double2 a = reinterpret_cast<const double2*>(y64)[2 * i];
+        const double2 b = reinterpret_cast<const double2*>(y64)[2 * i + 1];
+        reinterpret_cast<float4*>(y32)[i] = make_float4((float)a.x, (float)a.y, (float)b.x, (float)b.y);
+    }
+}
+
+cudaError_t launch_convert_f64_f32(const double* y64, float* y32, size_t count, int sm_count, cudaStream_t st) {
+    const size_t count4 = count / 4;    // count is a multiple of n >= 256
+    size_t blocks = (count4 + 255) / 256;
+    if (blocks > (size_t)sm_count * 8) blocks = (size_t)sm_count * 8;
+    convert_f64_f32_kernel<<<(unsigned)blocks, 256, 0, st>>>(y64, y32, count4);
+    return cudaGetLastError();
+}
+
 cudaError_t launch_count(const uint32_t* dec, const uint32_t* tx, int words, int nbits, int B,
                          unsigned long long* counters, cudaStream_t st) {
     count_errors_kernel<<<(B + 127) / 128, 128, 0, st>>>(dec, tx, words, nbits, B, counters);

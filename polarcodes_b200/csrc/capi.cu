@@ -55,6 +55,8 @@ struct pcb_handle {
     int f_bps = 0, f_warp_smem = 0;
     bool quad = false;              // four-frames-per-warp variant (decode_scl8q.cu) of the tuned kernel
     void* d_qscratch = nullptr;     // quad kernel: layer-3 arrays of every resident block (stays in L2)
+    float* d_y32 = nullptr;         // quad kernel: double channel values converted once per batch
+    size_t y32_cap = 0;
     int* d_redo = nullptr;          // [0] = count, [1..] = frame list
     size_t redo_cap = 0;
     size_t scratch_per_warp = 0;
@@ -219,7 +221,7 @@ void pcb_destroy(pcb_handle* h) {
         if (h->ev_out[s]) cudaEventDestroy(h->ev_out[s]);
     }
     cudaFree(h->d_ymc); cudaFree(h->d_tx); cudaFree(h->d_dec); cudaFree(h->d_counters);
-    cudaFree(h->d_eu); cudaFree(h->d_ex); cudaFree(h->d_redo); cudaFree(h->d_qscratch);
+    cudaFree(h->d_eu); cudaFree(h->d_ex); cudaFree(h->d_redo); cudaFree(h->d_qscratch); cudaFree(h->d_y32);
     if (h->t0) cudaEventDestroy(h->t0);
     if (h->t1) cudaEventDestroy(h->t1);
     if (h->sc) cudaStreamDestroy(h->sc);
@@ -305,6 +307,21 @@ static cudaError_t launch(pcb_handle* h, const DecodeArgs& a, cudaStream_t st) {
         cudaError_t e = cudaMemsetAsync(h->d_redo, 0, sizeof(int), st);
         if (e != cudaSuccess) return e;
         if (h->quad) {
+            if (!f.y_f32) {
+                // the decoder works in float (SCLDecoderMinsum.cpp:406-408): convert the batch once
+                // instead of at each of the 8 top-stage events of every frame
+                const size_t cnt = (size_t)a.B * h->n;
+                if (h->y32_cap < cnt) {
+                    cudaFree(h->d_y32); h->d_y32 = nullptr; h->y32_cap = 0;
+                    cudaError_t e1 = cudaMalloc(&h->d_y32, cnt * sizeof(float));
+                    if (e1 != cudaSuccess) return e1;
+                    h->y32_cap = cnt;
+                }
+                e = launch_convert_f64_f32(reinterpret_cast<const double*>(a.y), h->d_y32, cnt, h->sm_count, st);
+                if (e != cudaSuccess) return e;
+                h->launches++;
+                f.y = h->d_y32; f.y_f32 = 1;
+            }
             const int nq = (a.B + 3) / 4;
             const size_t spb = scl8q_scratch_per_block(h->m);
             if (spb && !h->d_qscratch) {

@@ -22,6 +22,14 @@
 #include "decode_common.cuh"
 #include "decode_launch.h"
 
+// Layer 4 in the global scratch as well (16 resident quads per SM): measured SLOWER on B200
+// (16.1 vs 17.6 Mframes/s) — the 57 MB of scratch plus the in-flight channel values no longer
+// stay in L2 (DRAM traffic x10) and 16 independent warps thrash the instruction cache.  Kept as
+// a compile-time experiment.
+#ifndef PCB_Q_GL4
+#define PCB_Q_GL4 0
+#endif
+
 namespace pcb {
 
 namespace q8 {
@@ -36,7 +44,9 @@ struct Geo {
     // N >= 1024: layer 3 (half of all stored LLRs) lives in a per-block global scratch that stays in
     // L2, which doubles the resident frames per SM; it is written and read 8 times per frame.
     static constexpr bool GL3 = M >= 10;
-    static constexpr int LS = GL3 ? 4 : 3;  // first LLR layer in shared memory
+    // optional experiment: layer 4 there too (see PCB_Q_GL4)
+    static constexpr bool GL4 = GL3 && PCB_Q_GL4;
+    static constexpr int LS = GL4 ? 5 : GL3 ? 4 : 3;  // first LLR layer in shared memory
     static constexpr int NW = N / 32;       // words of a full-length bit array
     static constexpr int HS = NW + 1;       // slot stride of the partial-sum heap (layer of size S at words [S/32, 2S/32))
     static constexpr int Q3 = N / 32;       // float4s of one layer-3 array
@@ -49,7 +59,7 @@ struct Geo {
     }
     static constexpr int PFLOATS = off(LBOT + 1);
     // staging area = the layers below the one the top stage writes (dead at those phases)
-    static constexpr int STAGE_OFF = off(LS + 1);
+    static constexpr int STAGE_OFF = GL4 ? 0 : off(LS + 1);
     static_assert(PFLOATS - STAGE_OFF >= (GL3 ? N / 2 : N), "staging area too small");
     static constexpr int XW = 8 * HS;                        // final codeword estimates (alias the LLR region)
     static_assert(XW + 8 * NW <= PFLOATS, "final-stage scratch does not fit the LLR region");
@@ -58,6 +68,8 @@ struct Geo {
     static constexpr int OFF_KEYS = PFLOATS + 8 * HS;
     static constexpr int TOTAL = 4 * FRAME_WORDS * 4;
     static constexpr int L3_BLOCK_FLOAT4 = GL3 ? 4 * Q3 * 8 : 0;   // global scratch per block: [frame][k][slot] float4
+    static constexpr int L4_BLOCK_FLOAT4 = GL4 ? 4 * (Q3 / 2) * 8 : 0;
+    static constexpr int SCRATCH_BLOCK_FLOAT4 = L3_BLOCK_FLOAT4 + L4_BLOCK_FLOAT4;
     static_assert((FRAME_WORDS * 4) % 16 == 0 && (OFF_H * 4) % 16 == 0 && (OFF_KEYS * 4) % 16 == 0, "alignment");
 };
 
@@ -184,6 +196,7 @@ struct Dec {
     uint32_t* keys;    // this frame's 16 candidate keys
     float* W;          // the warp's whole slice (4 frames)
     float4* L3;        // GL3: this frame's layer-3 arrays in global memory, element (k, slot) at L3[k*8 + slot]
+    float4* L4;        // GL4: same for layer 4
     float met;
     uint32_t maxmet;   // bit pattern of the largest metric of this frame (valid whenever the next phase is an information bit)
     uint32_t pidx, cidx, w0;
@@ -220,7 +233,7 @@ struct Dec {
         constexpr int E = G::N / 8, N4 = G::N / 4, Q = G::Q3, NR = Q / 16;
         const bool g1 = ev & 4, g2 = ev & 2, g3 = ev & 1;
         const float* R = P + G::STAGE_OFF;
-        float* dst4 = arr(4, p);
+        float* dst4 = G::GL4 ? nullptr : arr(4, p);
         float4* dst3 = L3 + p;
         __syncwarp();                            // everyone is done with the previous subtree
         if (!g1) {
@@ -279,7 +292,8 @@ struct Dec {
                     o[h] = g3 ? gs4(l2[0], l2[1], c3[h], 4 * kk) : ff4(l2[0], l2[1]);
                     dst3[k * 8] = o[h];
                 }
-                *reinterpret_cast<float4*>(dst4 + 4 * (r * 8 + kk)) = ff4(o[0], o[1]);
+                if constexpr (G::GL4) L4[(r * 8 + kk) * 8 + p] = ff4(o[0], o[1]);
+                else *reinterpret_cast<float4*>(dst4 + 4 * (r * 8 + kk)) = ff4(o[0], o[1]);
             }
         }
         __syncwarp();                            // the staging area is overwritten by layer 5 next
@@ -379,7 +393,7 @@ struct Dec {
     __device__ __forceinline__ void layer4_g_global() {
         constexpr int S = G::size(4);
         const float4* src = L3 + pfield(3);
-        float* dst = arr(4, p);
+        float* dst = G::GL4 ? nullptr : arr(4, p);
 #pragma unroll 1
         for (int k0 = 0; k0 < S / 4; k0 += 8) {
             const uint32_t cw = cword(4, 0, k0 >> 3);
@@ -387,7 +401,31 @@ struct Dec {
 #pragma unroll
             for (int kk = 0; kk < 8; kk++) { a[kk] = src[(k0 + kk) * 8]; b[kk] = src[(k0 + kk + S / 4) * 8]; }
 #pragma unroll
-            for (int kk = 0; kk < 8; kk++) *reinterpret_cast<float4*>(dst + 4 * (k0 + kk)) = gs4(a[kk], b[kk], cw, 4 * kk);
+            for (int kk = 0; kk < 8; kk++) {
+                const float4 o = gs4(a[kk], b[kk], cw, 4 * kk);
+                if constexpr (G::GL4) L4[(k0 + kk) * 8 + p] = o;
+                else *reinterpret_cast<float4*>(dst + 4 * (k0 + kk)) = o;
+            }
+        }
+    }
+    // GL4: layer 5 (shared memory) from the layer-4 arrays in global memory
+    __device__ __forceinline__ void layer5_global(bool isg) {
+        constexpr int S = G::size(5);
+        const float4* src = L4 + (isg ? pfield(4) : p);
+        float* dst = arr(5, p);
+#pragma unroll 1
+        for (int k0 = 0; k0 < S / 4; k0 += 8) {
+            const uint32_t cw = isg ? cword(5, 0, k0 >> 3) : 0u;
+            float4 a[8], b[8];
+#pragma unroll
+            for (int kk = 0; kk < 8; kk++) { a[kk] = src[(k0 + kk) * 8]; b[kk] = src[(k0 + kk + S / 4) * 8]; }
+            if (isg) {
+#pragma unroll
+                for (int kk = 0; kk < 8; kk++) *reinterpret_cast<float4*>(dst + 4 * (k0 + kk)) = gs4(a[kk], b[kk], cw, 4 * kk);
+            } else {
+#pragma unroll
+                for (int kk = 0; kk < 8; kk++) *reinterpret_cast<float4*>(dst + 4 * (k0 + kk)) = ff4(a[kk], b[kk]);
+            }
         }
     }
 
@@ -403,10 +441,14 @@ struct Dec {
             __syncwarp();
             ll = own = G::LBOT - z;
             if (G::GL3 && ll == 4) layer4_g_global();
+            else if (G::GL4 && ll == 5) layer5_global(true);
             else layer_g(ll);
         }
 #pragma unroll 1
-        for (int lam = ll + 1; lam <= G::LBOT; lam++) layer_f(lam);
+        for (int lam = ll + 1; lam <= G::LBOT; lam++) {
+            if (G::GL4 && lam == 5) layer5_global(false);
+            else layer_f(lam);
+        }
         // layers >= own are now this slot's own
         const uint32_t low = (1u << (3 * (own - G::LTOP))) - 1;
         pidx = (pidx & low) | ((0x9249249u * (uint32_t)p) & ~low);
@@ -588,7 +630,7 @@ struct Scl8qArgs {
 
 // One warp per block (blockDim.x == 32); a block decodes quads of frames.
 template <int M, typename YT>
-__global__ void __launch_bounds__(32, (M >= 10 ? 10 : 5)) decode_scl8q_kernel(const __grid_constant__ Scl8qArgs S) {
+__global__ void __launch_bounds__(32, (q8::Geo<M>::GL4 ? 16 : M >= 10 ? 10 : 5)) decode_scl8q_kernel(const __grid_constant__ Scl8qArgs S) {
     const DecodeArgs& A = S.a;
     using G = q8::Geo<M>;
     extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -600,7 +642,8 @@ __global__ void __launch_bounds__(32, (M >= 10 ? 10 : 5)) decode_scl8q_kernel(co
     D.P = D.W + fme * G::FRAME_WORDS;
     D.H = reinterpret_cast<uint32_t*>(D.P) + G::OFF_H;
     D.keys = reinterpret_cast<uint32_t*>(D.P) + G::OFF_KEYS;
-    D.L3 = G::GL3 ? S.l3 + (size_t)blockIdx.x * G::L3_BLOCK_FLOAT4 + fme * (G::Q3 * 8) : nullptr;
+    D.L3 = G::GL3 ? S.l3 + (size_t)blockIdx.x * G::SCRATCH_BLOCK_FLOAT4 + fme * (G::Q3 * 8) : nullptr;
+    D.L4 = G::GL4 ? S.l3 + (size_t)blockIdx.x * G::SCRATCH_BLOCK_FLOAT4 + G::L3_BLOCK_FLOAT4 + fme * (G::Q3 / 2 * 8) : nullptr;
     constexpr int n = G::N;
     const int EW = (A.stride + 31) >> 5;
     const YT* ybase = reinterpret_cast<const YT*>(A.y);
@@ -732,7 +775,8 @@ cudaError_t launch_decode_scl8q(const DecodeArgs& a, const uint32_t* info_w, voi
     s.l3 = reinterpret_cast<float4*>(l3_scratch);
     for (int i = 0; i < 65; i++) s.info_w[i] = i < a.n / 32 ? info_w[i] : 0;
 #define PCB_CASE(MM) \
-    case MM: return a.y_f32 ? launch_m<MM, float>(s, blocks, st) : launch_m<MM, double>(s, blocks, st);
+    case MM: return launch_m<MM, float>(s, blocks, st);
+    if (!a.y_f32) return cudaErrorInvalidValue;   // the caller converts double batches first (capi.cu)
     switch (a.m) { PCB_CASE(8) PCB_CASE(9) PCB_CASE(10) PCB_CASE(11) }
 #undef PCB_CASE
     return cudaErrorInvalidValue;
@@ -741,19 +785,19 @@ cudaError_t launch_decode_scl8q(const DecodeArgs& a, const uint32_t* info_w, voi
 // bytes of global scratch one block needs (layer-3 arrays of its four frames)
 size_t scl8q_scratch_per_block(int m) {
     switch (m) {
-        case 10: return (size_t)q8::Geo<10>::L3_BLOCK_FLOAT4 * 16;
-        case 11: return (size_t)q8::Geo<11>::L3_BLOCK_FLOAT4 * 16;
+        case 10: return (size_t)q8::Geo<10>::SCRATCH_BLOCK_FLOAT4 * 16;
+        case 11: return (size_t)q8::Geo<11>::SCRATCH_BLOCK_FLOAT4 * 16;
     }
     return 0;
 }
 
-// resident blocks (= warps = frame quads) per SM of the more register-hungry (double input) variant
+// resident blocks (= warps = frame quads) per SM
 cudaError_t scl8q_occupancy(int m, int* bps, int* warp_bytes) {
     switch (m) {
-        case 8: return occ_m<8, double>(bps, warp_bytes);
-        case 9: return occ_m<9, double>(bps, warp_bytes);
-        case 10: return occ_m<10, double>(bps, warp_bytes);
-        case 11: return occ_m<11, double>(bps, warp_bytes);
+        case 8: return occ_m<8, float>(bps, warp_bytes);
+        case 9: return occ_m<9, float>(bps, warp_bytes);
+        case 10: return occ_m<10, float>(bps, warp_bytes);
+        case 11: return occ_m<11, float>(bps, warp_bytes);
     }
     return cudaErrorInvalidValue;
 }
