@@ -106,7 +106,11 @@ static int configure(pcb_handle* h) {
         h->quad = scl8q_supported(h->m) && venv && !strcmp(venv, "quad");
         if (h->quad) {
             if (scl8q_occupancy(h->m, &bps, &wb) != cudaSuccess || bps == 0) { cudaGetLastError(); h->quad = false; }
-            else { h->f_bps = bps; h->f_warp_smem = wb; }
+            else {
+                const char* benv = getenv("PCB_Q_BPS");     // experiment: fewer resident quads per SM
+                if (benv && atoi(benv) > 0 && atoi(benv) < bps) bps = atoi(benv);
+                h->f_bps = bps; h->f_warp_smem = wb;
+            }
         }
     }
     const char* env = getenv("PCB_WARP_SMEM");

@@ -26,6 +26,10 @@
 // (16.1 vs 17.6 Mframes/s) — the 57 MB of scratch plus the in-flight channel values no longer
 // stay in L2 (DRAM traffic x10) and 16 independent warps thrash the instruction cache.  Kept as
 // a compile-time experiment.
+// register chains cover the last PCB_Q_CHAIN + 1 stored layers (sizes 8 .. 8 << PCB_Q_CHAIN)
+#ifndef PCB_Q_CHAIN
+#define PCB_Q_CHAIN 1
+#endif
 #ifndef PCB_Q_GL4
 #define PCB_Q_GL4 0
 #endif
@@ -200,6 +204,7 @@ struct Dec {
     float met;
     uint32_t maxmet;   // bit pattern of the largest metric of this frame (valid whenever the next phase is an information bit)
     uint32_t pidx, cidx, w0;
+    float4 vA, vB;     // layer LBOT (size 8) of the current subtree, handed from upper() to leaf8()
     float4 r4;         // size-4 layer
     float r2_0, r2_1;  // size-2 layer
     float A0;          // leaf LLR
@@ -429,8 +434,60 @@ struct Dec {
         }
     }
 
+    // ---- register chains: layers of size <= 32 --------------------------------------
+    // From the first layer with at most 8 float4 (LR) down to LBOT a chain is computed in
+    // registers: every layer is stored once (a g reads it later, maybe from a clone) but never
+    // re-read, and layer LBOT is handed to the leaf in vA/vB.
+    static constexpr int LR = (G::LBOT - PCB_Q_CHAIN > G::LS) ? G::LBOT - PCB_Q_CHAIN : G::LS + 1;  // size(LR) = 8 << PCB_Q_CHAIN
+    template <int LAM, int NF4>
+    __device__ __forceinline__ void f_down(float4 (&v)[NF4]) {
+        float* dst = arr(LAM, p);
+#pragma unroll
+        for (int k = 0; k < NF4; k++) *reinterpret_cast<float4*>(dst + 4 * k) = v[k];
+        if constexpr (LAM < G::LBOT) {
+            float4 w[NF4 / 2];
+#pragma unroll
+            for (int k = 0; k < NF4 / 2; k++) w[k] = ff4(v[k], v[k + NF4 / 2]);
+            f_down<LAM + 1, NF4 / 2>(w);
+        } else {
+            vA = v[0]; vB = v[1];
+        }
+    }
+    // g at layer LAM (LR..LBOT) from the lazily shared layer LAM-1 in shared memory, then f down
+    template <int LAM>
+    __device__ __forceinline__ void chain_g() {
+        constexpr int S = G::size(LAM), NF4 = S / 4;
+        const float* src = arr(LAM - 1, pfield(LAM - 1));
+        uint32_t cw;
+        if constexpr (S >= 32) cw = cword(LAM, 0, 0);
+        else cw = w0 >> S;
+        float4 v[NF4];
+#pragma unroll
+        for (int k = 0; k < NF4; k++)
+            v[k] = gs4(*reinterpret_cast<const float4*>(src + 4 * k), *reinterpret_cast<const float4*>(src + S + 4 * k), cw, 4 * k);
+        f_down<LAM, NF4>(v);
+    }
+    // f at layer LR from this slot's own layer LR-1 in shared memory, then f down
+    __device__ __forceinline__ void chain_f() {
+        constexpr int S = G::size(LR), NF4 = S / 4;
+        const float* src = arr(LR - 1, p);
+        float4 v[NF4];
+#pragma unroll
+        for (int k = 0; k < NF4; k++)
+            v[k] = ff4(*reinterpret_cast<const float4*>(src + 4 * k), *reinterpret_cast<const float4*>(src + S + 4 * k));
+        f_down<LR, NF4>(v);
+    }
+    template <int LAM>
+    __device__ __forceinline__ void chain_g_dispatch(int ll) {
+        if constexpr (LAM <= G::LBOT) {
+            if (ll == LAM) chain_g<LAM>();
+            else chain_g_dispatch<LAM + 1>(ll);
+        }
+    }
+
     // LLR work at the first phase i0 = 8*blk of a size-8 subtree, down to layer LBOT
     __device__ __forceinline__ void upper(int blk, const YT* ybase, const int (&fr)[4]) {
+        static_assert(!G::GL4 && LR > G::LS, "register chains start below the first shared-memory layer");
         const int z = blk ? (__ffs(blk) - 1) : 31;
         int ll, own;    // layers own.. are recomputed, the f-layers below ll are still to do
         if (z >= M - 6) {                                  // i0 is a multiple of N/8
@@ -440,14 +497,14 @@ struct Dec {
         } else {
             __syncwarp();
             ll = own = G::LBOT - z;
-            if (G::GL3 && ll == 4) layer4_g_global();
-            else if (G::GL4 && ll == 5) layer5_global(true);
+            if (ll >= LR) { chain_g_dispatch<LR>(ll); ll = G::LBOT; }
+            else if (G::GL3 && ll == 4) layer4_g_global();
             else layer_g(ll);
         }
+        if (ll < G::LBOT) {
 #pragma unroll 1
-        for (int lam = ll + 1; lam <= G::LBOT; lam++) {
-            if (G::GL4 && lam == 5) layer5_global(false);
-            else layer_f(lam);
+            for (int lam = ll + 1; lam < LR; lam++) layer_f(lam);
+            chain_f();
         }
         // layers >= own are now this slot's own
         const uint32_t low = (1u << (3 * (own - G::LTOP))) - 1;
@@ -583,9 +640,8 @@ struct Dec {
         uint32_t T4 = 0;
 #pragma unroll 1
         for (int h = 0; h < 2; h++, ib >>= 4) {
-            if (h == 0) {                    // own arrays all the way down
-                const float* v = arr(G::LBOT, p);
-                r4 = ff4(*reinterpret_cast<const float4*>(v), *reinterpret_cast<const float4*>(v + 4));
+            if (h == 0) {                    // own arrays all the way down: layer LBOT comes in registers
+                r4 = ff4(vA, vB);
             } else {                         // the size-8 layer may be a parent's
                 __syncwarp();
                 const float* v = arr(G::LBOT, pfield(G::LBOT));
