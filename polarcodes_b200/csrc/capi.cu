@@ -101,9 +101,10 @@ static int configure(pcb_handle* h) {
         int bps = 0, wb = 0;   // one warp (= one frame) per block
         if (scl8_occupancy(h->m, &bps, &wb) != cudaSuccess || bps == 0) { cudaGetLastError(); return fail(PCB_EINVAL, "list-8 kernel does not fit one SM"); }
         h->f_bps = bps; h->f_warp_smem = wb;
-        // PCB_SCL8_VARIANT=quad selects the four-frames-per-warp kernel (default while it is the slower one: warp)
+        // default: four frames per warp (decode_scl8q.cu); PCB_SCL8_VARIANT=warp selects the
+        // one-frame-per-warp kernel (decode_scl8.cu)
         const char* venv = getenv("PCB_SCL8_VARIANT");
-        h->quad = scl8q_supported(h->m) && venv && !strcmp(venv, "quad");
+        h->quad = scl8q_supported(h->m) && !(venv && !strcmp(venv, "warp"));
         if (h->quad) {
             if (scl8q_occupancy(h->m, &bps, &wb) != cudaSuccess || bps == 0) { cudaGetLastError(); h->quad = false; }
             else {

@@ -112,10 +112,36 @@ __device__ __forceinline__ unsigned group_max(unsigned x, int fme) {
     return r;
 }
 
+// Partial-sum combine into a layer of size D = 2^d2 >= 32 (SCLDecoderMinsum.cpp:287-305), one
+// lane per path: T holds the last 32 bits; the destination layer m-d2 sits at heap words
+// [D/32, 2D/32) of this slot; layer 0 (the final codeword estimate, written at the very last
+// phase) goes to the then-dead LLR region instead.  Out of line: taken once per four subtrees.
+__device__ __noinline__ uint32_t heap_combine(uint32_t* Pw, uint32_t* H, int p, uint32_t cidx, int d2, uint32_t T, int m) {
+    const int D = 1 << d2, NW = 1 << (m - 5), HS = NW + 1;
+    uint32_t* hp = (d2 == m) ? (Pw + p * HS - NW) : (H + p * HS);
+    __syncwarp();
+    hp[2 * D / 32 - 1] = T;
+    for (int w = 32; w < D; w <<= 1) {
+        const int lgw = 31 - __clz(w), layc = m - lgw, nw = w >> 5;
+        const uint32_t* cs = H + ((cidx >> (3 * (layc - 1))) & 7) * HS + nw;
+        for (int kk = 0; kk < nw; kk++)
+            hp[(2 * D - 2 * w) / 32 + kk] = cs[kk] ^ hp[(2 * D - w) / 32 + kk];
+    }
+    __syncwarp();
+    if (d2 < m) {
+        const int sh = 3 * (m - d2 - 1);
+        cidx = (cidx & ~(7u << sh)) | ((uint32_t)p << sh);
+    }
+    return cidx;
+}
+
 // Per-path state a fork can replace.  r = u | take << 1 | source lane << 2.
 struct PathState {
     float met;
     uint32_t pidx, cidx, w0, r;
+    float4 r4;          // register LLR layers (a dead one is copied too: one code path for all phases)
+    float r2_0, r2_1;
+    uint32_t maxmet;    // out: largest metric of the frame after the fork
 };
 
 // continuePaths_UnfrozenBit (SCLDecoderMinsum.cpp:315-400) without the fast exit, for the four
@@ -186,8 +212,15 @@ __device__ __noinline__ PathState fork_slow(PathState s, float A0, int lane, int
     const uint32_t pi = __shfl_sync(FULL, s.pidx, sl);
     const uint32_t ci = __shfl_sync(FULL, s.cidx, sl);
     const uint32_t ww = __shfl_sync(FULL, s.w0, sl);
-    if (r & 2u) { s.met = m1; s.pidx = pi; s.cidx = ci; s.w0 = ww; }
+    const float x4 = __shfl_sync(FULL, s.r4.x, sl), y4 = __shfl_sync(FULL, s.r4.y, sl);
+    const float z4 = __shfl_sync(FULL, s.r4.z, sl), w4 = __shfl_sync(FULL, s.r4.w, sl);
+    const float a2 = __shfl_sync(FULL, s.r2_0, sl), b2 = __shfl_sync(FULL, s.r2_1, sl);
+    if (r & 2u) {
+        s.met = m1; s.pidx = pi; s.cidx = ci; s.w0 = ww;
+        s.r4 = make_float4(x4, y4, z4, w4); s.r2_0 = a2; s.r2_1 = b2;
+    }
     s.r = r;
+    s.maxmet = group_max(__float_as_uint(s.met), lane >> 3);
     return s;
 }
 
@@ -195,6 +228,7 @@ template <int M, typename YT>
 struct Dec {
     using G = Geo<M>;
     int lane, p;
+    int fbase, Bm1;    // first frame of the quad, last frame of the batch (tail quads repeat it)
     float* P;          // this frame's LLR layers
     uint32_t* H;       // this frame's partial-sum heaps
     uint32_t* keys;    // this frame's 16 candidate keys
@@ -242,11 +276,11 @@ struct Dec {
         float4* dst3 = L3 + p;
         __syncwarp();                            // everyone is done with the previous subtree
         if (!g1) {
-#pragma unroll
+#pragma unroll 1
             for (int f = 0; f < 4; f++) {
-                const YT* y = ybase + (size_t)fr[f] * G::N;
+                const YT* y = ybase + (size_t)min(fbase + f, Bm1) * G::N;
                 float* Rf = W + f * G::FRAME_WORDS + G::STAGE_OFF;
-#pragma unroll 4
+#pragma unroll 2
                 for (int q = lane; q < N4 / 2; q += 32)
                     *reinterpret_cast<float4*>(Rf + 4 * q) = ff4(load_y4(y, q), load_y4(y, q + N4 / 2));
             }
@@ -256,10 +290,10 @@ struct Dec {
         for (int r = 0; r < NR; r++) {
             if (g1) {
                 if (r) __syncwarp();
-#pragma unroll
+#pragma unroll 4
                 for (int i = 0; i < 16; i++) {   // unit u = i*32 + lane: frame i/4, then t (8), h (2), kk (8)
                     const int u = i * 32 + lane, t = (u >> 4) & 7, h = (u >> 3) & 1, kk = u & 7;
-                    const YT* y = ybase + (size_t)fr[i >> 2] * G::N;
+                    const YT* y = ybase + (size_t)min(fbase + (i >> 2), Bm1) * G::N;
                     *reinterpret_cast<float4*>(W + (i >> 2) * G::FRAME_WORDS + G::STAGE_OFF + (u & 127) * 4) =
                         load_y4(y, t * Q + h * (Q / 2) + r * 8 + kk);
                 }
@@ -521,19 +555,11 @@ struct Dec {
             const float hi = met + fabsf(A0);
             if (__all_sync(FULL, __float_as_uint(hi) > maxmet)) return A0 < 0.f ? 1 : 0;   // max met < min hi
         }
-        PathState s{met, pidx, cidx, w0, 0};
+        PathState s{met, pidx, cidx, w0, 0, r4, r2_0, r2_1, 0};
         s = fork_slow(s, A0, lane, ninfo, keys);
         met = s.met; pidx = s.pidx; cidx = s.cidx; w0 = s.w0;
-        const int sl = (s.r >> 2) & 31;
-        const bool take = s.r & 2u;
-        {   // register layers (a dead one is copied too: cheaper than eight specialised call sites)
-            const float x = __shfl_sync(FULL, r4.x, sl), y = __shfl_sync(FULL, r4.y, sl);
-            const float z = __shfl_sync(FULL, r4.z, sl), w = __shfl_sync(FULL, r4.w, sl);
-            const float a = __shfl_sync(FULL, r2_0, sl), b = __shfl_sync(FULL, r2_1, sl);
-            if (take) { r4 = make_float4(x, y, z, w); r2_0 = a; r2_1 = b; }
-        }
+        r4 = s.r4; r2_0 = s.r2_0; r2_1 = s.r2_1; maxmet = s.maxmet;
         if (ninfo < 3) ninfo++;
-        maxmet = group_max(__float_as_uint(met), lane >> 3);
         return s.r & 1;
     }
 
@@ -555,23 +581,7 @@ struct Dec {
         T = (((w0 >> 8) ^ T) & 0xFFu) | (T << 8);
         if (d2 == 4) { w0 = (w0 & 0x0000FFFFu) | (T << 16); return; }
         T = (((w0 >> 16) ^ T) & 0xFFFFu) | (T << 16);
-        const int D = 1 << d2;
-        // destination layer m-d2 sits at heap words [D/32, 2D/32); layer 0 (the final codeword
-        // estimate, written at the very last phase) goes to the then-dead LLR region instead
-        uint32_t* hp = (d2 == M) ? (reinterpret_cast<uint32_t*>(P) + p * G::HS - G::NW) : (H + p * G::HS);
-        __syncwarp();
-        hp[2 * D / 32 - 1] = T;
-        for (int w = 32; w < D; w <<= 1) {
-            const int lgw = 31 - __clz(w), layc = M - lgw, nw = w >> 5;
-            const uint32_t* cs = H + cfield(layc) * G::HS + nw;
-            for (int kk = 0; kk < nw; kk++)
-                hp[(2 * D - 2 * w) / 32 + kk] = cs[kk] ^ hp[(2 * D - w) / 32 + kk];
-        }
-        __syncwarp();
-        if (d2 < M) {
-            const int sh = 3 * (M - d2 - 1);
-            cidx = (cidx & ~(7u << sh)) | ((uint32_t)p << sh);
-        }
+        cidx = heap_combine(reinterpret_cast<uint32_t*>(P), H, p, cidx, d2, T, M);
     }
 
     // ---- the four phases of one size-4 subtree (its LLRs in r4, pairs (x,z) and (y,w)) --------
@@ -686,7 +696,7 @@ struct Scl8qArgs {
 
 // One warp per block (blockDim.x == 32); a block decodes quads of frames.
 template <int M, typename YT>
-__global__ void __launch_bounds__(32, (q8::Geo<M>::GL4 ? 16 : M >= 10 ? 10 : 5)) decode_scl8q_kernel(const __grid_constant__ Scl8qArgs S) {
+__global__ void __launch_bounds__(32, (q8::Geo<M>::GL4 && M == 10 ? 16 : M == 10 ? 10 : 5)) decode_scl8q_kernel(const __grid_constant__ Scl8qArgs S) {
     const DecodeArgs& A = S.a;
     using G = q8::Geo<M>;
     extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -708,6 +718,7 @@ __global__ void __launch_bounds__(32, (q8::Geo<M>::GL4 ? 16 : M >= 10 ? 10 : 5))
     for (int quad = blockIdx.x; quad < nquads; quad += gridDim.x) {
         int fr[4];
         bool okf[4];
+        D.fbase = 4 * quad; D.Bm1 = A.B - 1;
 #pragma unroll
         for (int f = 0; f < 4; f++) fr[f] = min(4 * quad + f, A.B - 1);
         // range check that licenses the arithmetic shortcuts of ff(): |y| == 0 or in [2^-40, 2^100]
