@@ -229,6 +229,7 @@ struct Dec {
     using G = Geo<M>;
     int lane, p;
     int fbase, Bm1;    // first frame of the quad, last frame of the batch (tail quads repeat it)
+    uint32_t badmask;  // frames of the quad with a channel value outside the safe range of ff()
     float* P;          // this frame's LLR layers
     uint32_t* H;       // this frame's partial-sum heaps
     uint32_t* keys;    // this frame's 16 candidate keys
@@ -268,6 +269,37 @@ struct Dec {
     // (always an f-layer here) to shared memory.  With a g-layer 1 the channel values are staged
     // in rounds of 8+8 float4 columns (k and k + Q3/2, the two operands of a layer-4 output), so
     // that the staging area never overlaps the layer-4 arrays being written.
+    // range check that licenses the arithmetic shortcuts of ff(): |y| == 0 or in [2^-40, 2^100]
+    // (2^-40 = 0x2B800000, 2^100 = 0x71800000 as bit patterns; NaN and inf are above)
+    __device__ __forceinline__ static bool in_range(float4 v) {
+        bool ok = true;
+        const float e[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+        for (int i = 0; i < 4; i++) {
+            const uint32_t a = __float_as_uint(e[i]) & 0x7fffffffu;
+            ok = ok && (a == 0u || (a - 0x2B800000u) <= (0x71800000u - 0x2B800000u));
+        }
+        return ok;
+    }
+    // Stage layer 1 = f(y[x], y[x + N/2]) (the same for every path) of the four frames; at the
+    // first event of a quad this is also the first touch of its channel values: range-check them.
+    __device__ __forceinline__ void stage_l1f(int ev, const YT* ybase) {
+        constexpr int N4 = G::N / 4;
+#pragma unroll 1
+        for (int f = 0; f < 4; f++) {
+            const YT* y = ybase + (size_t)min(fbase + f, Bm1) * G::N;
+            float* Rf = W + f * G::FRAME_WORDS + G::STAGE_OFF;
+            bool ok = true;
+#pragma unroll 4
+            for (int q = lane; q < N4 / 2; q += 32) {
+                const float4 a = load_y4(y, q), b = load_y4(y, q + N4 / 2);
+                if (ev == 0) ok = ok && in_range(a) && in_range(b);
+                *reinterpret_cast<float4*>(Rf + 4 * q) = ff4(a, b);
+            }
+            if (ev == 0 && !__all_sync(FULL, ok)) badmask |= 1u << f;
+        }
+    }
+
     __device__ __forceinline__ void top_gl3(int ev, const YT* ybase, const int (&fr)[4]) {
         constexpr int E = G::N / 8, N4 = G::N / 4, Q = G::Q3, NR = Q / 16;
         const bool g1 = ev & 4, g2 = ev & 2, g3 = ev & 1;
@@ -276,14 +308,7 @@ struct Dec {
         float4* dst3 = L3 + p;
         __syncwarp();                            // everyone is done with the previous subtree
         if (!g1) {
-#pragma unroll 1
-            for (int f = 0; f < 4; f++) {
-                const YT* y = ybase + (size_t)min(fbase + f, Bm1) * G::N;
-                float* Rf = W + f * G::FRAME_WORDS + G::STAGE_OFF;
-#pragma unroll 2
-                for (int q = lane; q < N4 / 2; q += 32)
-                    *reinterpret_cast<float4*>(Rf + 4 * q) = ff4(load_y4(y, q), load_y4(y, q + N4 / 2));
-            }
+            stage_l1f(ev, ybase);
             __syncwarp();
         }
 #pragma unroll 1
@@ -344,23 +369,15 @@ struct Dec {
         __syncwarp();                            // everyone is done with layers 4.. of the previous subtree
         if (g1) {
             // stage the channel values of the four frames as floats
-#pragma unroll
+#pragma unroll 1
             for (int f = 0; f < 4; f++) {
-                const YT* y = ybase + (size_t)fr[f] * G::N;
+                const YT* y = ybase + (size_t)min(fbase + f, Bm1) * G::N;
                 float* R = W + f * G::FRAME_WORDS + G::STAGE_OFF;
 #pragma unroll 4
                 for (int q = lane; q < N4; q += 32) *reinterpret_cast<float4*>(R + 4 * q) = load_y4(y, q);
             }
         } else {
-            // layer 1 = f(y[x], y[x + N/2]) is the same for every path: compute it while staging
-#pragma unroll
-            for (int f = 0; f < 4; f++) {
-                const YT* y = ybase + (size_t)fr[f] * G::N;
-                float* R = W + f * G::FRAME_WORDS + G::STAGE_OFF;
-#pragma unroll 4
-                for (int q = lane; q < N4 / 2; q += 32)
-                    *reinterpret_cast<float4*>(R + 4 * q) = ff4(load_y4(y, q), load_y4(y, q + N4 / 2));
-            }
+            stage_l1f(ev, ybase);
         }
         __syncwarp();
         const float* R = P + G::STAGE_OFF;
@@ -717,27 +734,17 @@ __global__ void __launch_bounds__(32, (q8::Geo<M>::GL4 && M == 10 ? 16 : M == 10
 
     for (int quad = blockIdx.x; quad < nquads; quad += gridDim.x) {
         int fr[4];
-        bool okf[4];
         D.fbase = 4 * quad; D.Bm1 = A.B - 1;
 #pragma unroll
         for (int f = 0; f < 4; f++) fr[f] = min(4 * quad + f, A.B - 1);
-        // range check that licenses the arithmetic shortcuts of ff(): |y| == 0 or in [2^-40, 2^100]
-#pragma unroll
-        for (int f = 0; f < 4; f++) {
-            const YT* y = ybase + (size_t)fr[f] * n;
-            bool ok = true;
-#pragma unroll 2
-            for (int q = lane; q < n / 4; q += 32) {
-                const float4 v = D.load_y4(y, q);
-                const float a0 = fabsf(v.x), a1 = fabsf(v.y), a2 = fabsf(v.z), a3 = fabsf(v.w);
-                ok = ok && (a0 == 0.f || (a0 >= 0x1p-40f && a0 <= 0x1p100f)) && (a1 == 0.f || (a1 >= 0x1p-40f && a1 <= 0x1p100f)) &&
-                     (a2 == 0.f || (a2 >= 0x1p-40f && a2 <= 0x1p100f)) && (a3 == 0.f || (a3 >= 0x1p-40f && a3 <= 0x1p100f));
-            }
-            okf[f] = __all_sync(FULL, ok);
-            // hand the frame to the generic (reference-literal) kernel
-            if (!okf[f] && lane == 0 && 4 * quad + f < A.B) A.redo_list[atomicAdd(A.redo_count, 1)] = fr[f];
+        D.badmask = 0;
+        // pull the next quad of this block into L2 while this one is decoded (its first touch is
+        // otherwise a DRAM-latency stall with nothing else to do)
+        if (4 * (quad + (int)gridDim.x) + 4 <= A.B) {
+            const char* nx = reinterpret_cast<const char*>(ybase + (size_t)4 * (quad + gridDim.x) * n);
+            for (int ln = lane; ln < (int)(4 * n * sizeof(YT) / 128); ln += 32)
+                asm volatile("prefetch.global.L2 [%0];" ::"l"(nx + (size_t)ln * 128));
         }
-        if (!(okf[0] || okf[1] || okf[2] || okf[3])) continue;
         D.met = 0.f; D.maxmet = 0; D.pidx = 0; D.cidx = 0; D.w0 = 0; D.ninfo = 0;
         D.r4 = make_float4(0.f, 0.f, 0.f, 0.f); D.r2_0 = D.r2_1 = D.A0 = 0.f;
 #pragma unroll 1
@@ -749,6 +756,9 @@ __global__ void __launch_bounds__(32, (q8::Geo<M>::GL4 && M == 10 ? 16 : M == 10
             D.leaf8(blk, ib);
         }
         __syncwarp();
+        // frames outside the safe range go to the generic (reference-literal) kernel
+        if (D.badmask && lane < 4 && ((D.badmask >> lane) & 1) && 4 * quad + lane < A.B)
+            A.redo_list[atomicAdd(A.redo_count, 1)] = 4 * quad + lane;
         // ---- final selection (:432-473): u-hat = x-hat F^(x)m per slot, CRC, first pass wins ----
         constexpr int NW = G::NW, HS = G::HS, lgN = M - 5;
         const int q0 = A.crc ? 0 : 7;   // without a CRC the reference returns slot L-1 unconditionally
@@ -803,7 +813,7 @@ __global__ void __launch_bounds__(32, (q8::Geo<M>::GL4 && M == 10 ? 16 : M == 10
             const unsigned okm = __ballot_sync(FULL, ok);
             const int chosen = okm ? (__ffs(okm) - 1) : 7;
             const int frame = 4 * quad + fs;
-            if (frame < A.B && okf[fs]) {
+            if (frame < A.B && !((D.badmask >> fs) & 1)) {
                 if (A.sol)
                     for (int t = lane; t < A.stride; t += 32)
                         A.sol[(size_t)frame * A.stride + t] = (E[chosen * EW + (t >> 5)] >> (t & 31)) & 1;
