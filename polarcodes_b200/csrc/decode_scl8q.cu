@@ -141,8 +141,29 @@ struct PathState {
     uint32_t pidx, cidx, w0, r;
     float4 r4;          // register LLR layers (a dead one is copied too: one code path for all phases)
     float r2_0, r2_1;
-    uint32_t maxmet;    // out: largest metric of the frame after the fork
+    uint32_t maxmet;    // largest metric of the frame: in before, out after the fork
 };
+
+// Shortcut of the median select for the commonest non-trivial outcome.  Per frame, B = the paths
+// whose penalised candidate hi = met + |llr| is not above the largest metric maxmet.  If B is
+// empty the frame takes its fast exit; if B = {q0}, hi(q0) < maxmet strictly and exactly one path
+// p0 holds maxmet, then the 8 smallest of the 16 candidates are the 7 other unpenalised ones plus
+// both candidates of q0, with a strict gap on either side of the cut (no tie for pass 2 to
+// break): p0 is killed and its slot receives the clone of q0 (:372-389).  Returns false (and the
+// caller runs the full select) unless every frame of the warp is in one of the two cases.
+__device__ __forceinline__ bool single_swap(const PathState& s, float A0, int lane, uint32_t& r) {
+    const int gsh = lane & 24;
+    const uint32_t lo = __float_as_uint(s.met), hi = __float_as_uint(s.met + fabsf(A0));
+    const unsigned gB = (__ballot_sync(FULL, !(hi > s.maxmet)) >> gsh) & 0xFFu;
+    const unsigned gE = (__ballot_sync(FULL, lo == s.maxmet) >> gsh) & 0xFFu;
+    const unsigned gS = (__ballot_sync(FULL, hi == s.maxmet) >> gsh) & 0xFFu;
+    const bool cond = gB == 0u || (__popc(gB) == 1 && __popc(gE) == 1 && gS == 0u);
+    if (!__all_sync(FULL, cond)) return false;
+    const int q0 = gsh + __ffs(gB) - 1, p0 = gsh + __ffs(gE) - 1;
+    if (gB != 0u && lane == p0) r = 3u | ((uint32_t)q0 << 2);                       // clone of q0, bit 1
+    else r = ((gB != 0u && lane == q0) ? 0u : (A0 < 0.f ? 1u : 0u)) | ((uint32_t)lane << 2);   // q0 keeps bit 0
+    return true;
+}
 
 // continuePaths_UnfrozenBit (SCLDecoderMinsum.cpp:315-400) without the fast exit, for the four
 // frames of the warp at once (every step is confined to the 8-lane group of a frame).
@@ -156,6 +177,7 @@ __device__ __noinline__ PathState fork_slow(PathState s, float A0, int lane, int
         const int nact = 1 << ninfo, pbase = 8 - nact;
         const bool take = p >= pbase - nact && p < pbase;
         r = take ? (3u | ((uint32_t)(gsh + 2 * pbase - 1 - p) << 2)) : ((uint32_t)lane << 2);
+    } else if (single_swap(s, A0, lane, r)) {
     } else {
         // stable rank of both candidates among the 16 of the frame; keys are stored complemented:
         // key < kc  <=>  carry-out of (kc + ~key)
@@ -572,7 +594,7 @@ struct Dec {
             const float hi = met + fabsf(A0);
             if (__all_sync(FULL, __float_as_uint(hi) > maxmet)) return A0 < 0.f ? 1 : 0;   // max met < min hi
         }
-        PathState s{met, pidx, cidx, w0, 0, r4, r2_0, r2_1, 0};
+        PathState s{met, pidx, cidx, w0, 0, r4, r2_0, r2_1, maxmet};
         s = fork_slow(s, A0, lane, ninfo, keys);
         met = s.met; pidx = s.pidx; cidx = s.cidx; w0 = s.w0;
         r4 = s.r4; r2_0 = s.r2_0; r2_1 = s.r2_1; maxmet = s.maxmet;
