@@ -73,7 +73,9 @@ struct Geo {
     static constexpr int TOTAL = 4 * FRAME_WORDS * 4;
     static constexpr int L3_BLOCK_FLOAT4 = GL3 ? 4 * Q3 * 8 : 0;   // global scratch per block: [frame][k][slot] float4
     static constexpr int L4_BLOCK_FLOAT4 = GL4 ? 4 * (Q3 / 2) * 8 : 0;
-    static constexpr int SCRATCH_BLOCK_FLOAT4 = L3_BLOCK_FLOAT4 + L4_BLOCK_FLOAT4;
+    // layer 2 of the even top-stage events, re-used by the following odd event: [frame][k (2*Q3)][slot]
+    static constexpr int L2C_BLOCK_FLOAT4 = GL3 ? 4 * 2 * Q3 * 8 : 0;
+    static constexpr int SCRATCH_BLOCK_FLOAT4 = L3_BLOCK_FLOAT4 + L4_BLOCK_FLOAT4 + L2C_BLOCK_FLOAT4;
     static_assert((FRAME_WORDS * 4) % 16 == 0 && (OFF_H * 4) % 16 == 0 && (OFF_KEYS * 4) % 16 == 0, "alignment");
 };
 
@@ -258,6 +260,7 @@ struct Dec {
     float* W;          // the warp's whole slice (4 frames)
     float4* L3;        // GL3: this frame's layer-3 arrays in global memory, element (k, slot) at L3[k*8 + slot]
     float4* L4;        // GL4: same for layer 4
+    float4* L2c;       // GL3: layer 2 as computed at the last even top-stage event
     float met;
     uint32_t maxmet;   // bit pattern of the largest metric of this frame (valid whenever the next phase is an information bit)
     uint32_t pidx, cidx, w0;
@@ -329,6 +332,38 @@ struct Dec {
         float* dst4 = G::GL4 ? nullptr : arr(4, p);
         float4* dst3 = L3 + p;
         __syncwarp();                            // everyone is done with the previous subtree
+        if (g3) {
+            // Odd event: layers 1 and 2 are those of the previous (even) event, whose layer 2 is in
+            // the global scratch (of this path or of the ancestor it was cloned from since):
+            // layer 3 = g(layer 2, partial sums of layer 3), no channel values needed.
+            const float4* src = L2c + ((pidx >> 24) & 7);
+#pragma unroll 1
+            for (int k0 = 0; k0 < Q / 2; k0 += 8) {
+                const uint32_t ca = cword(3, 0, k0 >> 3), cb = cword(3, 0, (k0 + Q / 2) >> 3);
+#pragma unroll 1
+                for (int k4 = 0; k4 < 8; k4 += 4) {          // 16 loads in flight: the scratch may have left L2
+                    float4 a0[4], b0[4], a1[4], b1[4];
+#pragma unroll
+                    for (int i = 0; i < 4; i++) {
+                        const int k = k0 + k4 + i;
+                        a0[i] = __ldcg(src + k * 8); b0[i] = __ldcg(src + (k + Q) * 8);
+                        a1[i] = __ldcg(src + (k + Q / 2) * 8); b1[i] = __ldcg(src + (k + Q / 2 + Q) * 8);
+                    }
+#pragma unroll
+                    for (int i = 0; i < 4; i++) {
+                        const int k = k0 + k4 + i;
+                        const float4 o0 = gs4(a0[i], b0[i], ca, 4 * (k4 + i));
+                        const float4 o1 = gs4(a1[i], b1[i], cb, 4 * (k4 + i));
+                        dst3[k * 8] = o0;
+                        dst3[(k + Q / 2) * 8] = o1;
+                        if constexpr (G::GL4) L4[k * 8 + p] = ff4(o0, o1);
+                        else *reinterpret_cast<float4*>(dst4 + 4 * k) = ff4(o0, o1);
+                    }
+                }
+            }
+            __syncwarp();
+            return;
+        }
         if (!g1) {
             stage_l1f(ev, ybase);
             __syncwarp();
@@ -346,14 +381,13 @@ struct Dec {
                 }
                 __syncwarp();
             }
-            uint32_t c1[4][2], c2[2][2], c3[2];
+            uint32_t c1[4][2], c2[2][2];
 #pragma unroll
             for (int h = 0; h < 2; h++) {
                 const int w32 = h * (Q / 16) + r;
 #pragma unroll
                 for (int t = 0; t < 4; t++) c1[t][h] = g1 ? cword(1, t * E, w32) : 0u;
                 c2[0][h] = g2 ? cword(2, 0, w32) : 0u; c2[1][h] = g2 ? cword(2, E, w32) : 0u;
-                c3[h] = g3 ? cword(3, 0, w32) : 0u;
             }
 #pragma unroll 1
             for (int kk = 0; kk < 8; kk++) {
@@ -375,13 +409,16 @@ struct Dec {
                     float4 l2[2];
                     if (g2) { l2[0] = gs4(l1[0], l1[2], c2[0][h], 4 * kk); l2[1] = gs4(l1[1], l1[3], c2[1][h], 4 * kk); }
                     else { l2[0] = ff4(l1[0], l1[2]); l2[1] = ff4(l1[1], l1[3]); }
-                    o[h] = g3 ? gs4(l2[0], l2[1], c3[h], 4 * kk) : ff4(l2[0], l2[1]);
+                    L2c[k * 8 + p] = l2[0];             // for the odd event that follows
+                    L2c[(k + Q) * 8 + p] = l2[1];
+                    o[h] = ff4(l2[0], l2[1]);
                     dst3[k * 8] = o[h];
                 }
                 if constexpr (G::GL4) L4[(r * 8 + kk) * 8 + p] = ff4(o[0], o[1]);
                 else *reinterpret_cast<float4*>(dst4 + 4 * (r * 8 + kk)) = ff4(o[0], o[1]);
             }
         }
+        pidx = (pidx & ~(7u << 24)) | ((uint32_t)p << 24);   // the cached layer 2 is this slot's own
         __syncwarp();                            // the staging area is overwritten by layer 5 next
     }
 
@@ -581,7 +618,7 @@ struct Dec {
         }
         // layers >= own are now this slot's own
         const uint32_t low = (1u << (3 * (own - G::LTOP))) - 1;
-        pidx = (pidx & low) | ((0x9249249u * (uint32_t)p) & ~low);
+        pidx = (pidx & (low | 0xFF000000u)) | ((0x249249u * (uint32_t)p) & ~low);   // bits 24.. hold the layer-2 field
     }
 
     // ---- fork / prune of one information bit (SCLDecoderMinsum.cpp:315-400) ----------
@@ -749,6 +786,7 @@ __global__ void __launch_bounds__(32, (q8::Geo<M>::GL4 && M == 10 ? 16 : M == 10
     D.keys = reinterpret_cast<uint32_t*>(D.P) + G::OFF_KEYS;
     D.L3 = G::GL3 ? S.l3 + (size_t)blockIdx.x * G::SCRATCH_BLOCK_FLOAT4 + fme * (G::Q3 * 8) : nullptr;
     D.L4 = G::GL4 ? S.l3 + (size_t)blockIdx.x * G::SCRATCH_BLOCK_FLOAT4 + G::L3_BLOCK_FLOAT4 + fme * (G::Q3 / 2 * 8) : nullptr;
+    D.L2c = G::GL3 ? S.l3 + (size_t)blockIdx.x * G::SCRATCH_BLOCK_FLOAT4 + G::L3_BLOCK_FLOAT4 + G::L4_BLOCK_FLOAT4 + fme * (2 * G::Q3 * 8) : nullptr;
     constexpr int n = G::N;
     const int EW = (A.stride + 31) >> 5;
     const YT* ybase = reinterpret_cast<const YT*>(A.y);

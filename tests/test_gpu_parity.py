@@ -205,3 +205,53 @@ def test_out_of_range_frames_take_the_generic_kernel(oracle):
     bad = np.nonzero((got != want).any(axis=1))[0]
     assert bad.size == 0, f"frames {bad.tolist()} differ"
     assert (d.decode(y.astype(np.float32)) == oracle.decode(3, n, L, k, crc, sigma, y.astype(np.float32).astype(np.float64), mask)).all()
+
+
+@pytest.mark.parametrize("frames", [1, 2, 3, 5, 7, 130])
+def test_quad_kernel_ragged_batches(oracle, frames):
+    """The list-8 kernel decodes four frames per warp: batches that are not a multiple of four
+    (the last quad repeats the final frame and must not write it twice or out of bounds)."""
+    rng = np.random.default_rng(100 + frames)
+    n, k, crc, L = 1024, 512, 16, 8
+    sigma, inf, mask = oracle.make_code(n, k, crc, 1.5)
+    y = 1 + sigma * rng.standard_normal((frames, n))
+    d = _decoder(3, n, k, crc, L, mask, sigma)
+    want = oracle.decode(3, n, L, k, crc, sigma, y, mask)
+    assert (d.decode(y) == want).all()
+    import polarcodes_b200 as pb
+    assert (pb.unpack_bits(d.decode_packed(y.astype(np.float32)), k + crc) ==
+            oracle.decode(3, n, L, k, crc, sigma, y.astype(np.float32).astype(np.float64), mask)).all()
+
+
+def test_quad_kernel_one_bad_frame_per_quad(oracle):
+    """A quad with one out-of-range frame: the other three come from the quad kernel, the bad one
+    from the generic kernel; also a quad whose four frames are all out of range."""
+    rng = np.random.default_rng(23)
+    n, k, crc, L = 1024, 512, 0, 8
+    sigma, inf, mask = oracle.make_code(n, k, crc, 2.0)
+    y = 1 + sigma * rng.standard_normal((24, n))
+    y[1] *= 1e-30
+    y[6, 3] = np.nan
+    y[8:12] *= 1e36
+    y[23, -1] = 1e-25
+    d = _decoder(3, n, k, crc, L, mask, sigma)
+    got, want = d.decode(y), oracle.decode(3, n, L, k, crc, sigma, y, mask)
+    bad = np.nonzero((got != want).any(axis=1))[0]
+    assert bad.size == 0, f"frames {bad.tolist()} differ"
+
+
+@pytest.mark.parametrize("n,k,crc,snr", [(1024, 512, 16, 1.0), (256, 128, 8, 1.5), (2048, 1024, 0, 2.0)])
+def test_one_frame_per_warp_variant_agrees(oracle, n, k, crc, snr):
+    """PCB_SCL8_VARIANT=warp keeps the one-frame-per-warp list-8 kernel selectable; both tuned
+    kernels and the oracle agree."""
+    rng = np.random.default_rng(7 + n)
+    sigma, inf, mask = oracle.make_code(n, k, crc, snr)
+    y = 1 + sigma * rng.standard_normal((40, n))
+    want = oracle.decode(3, n, 8, k, crc, sigma, y, mask)
+    quad = _decoder(3, n, k, crc, 8, mask, sigma).decode(y)
+    os.environ["PCB_SCL8_VARIANT"] = "warp"
+    try:
+        warp = _decoder(3, n, k, crc, 8, mask, sigma).decode(y)
+    finally:
+        del os.environ["PCB_SCL8_VARIANT"]
+    assert (quad == want).all() and (warp == want).all()
