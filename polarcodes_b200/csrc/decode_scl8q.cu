@@ -676,6 +676,18 @@ struct Dec {
         return 0u;
     }
 
+    // three frozen positions, then one information bit (the commonest mixed pattern)
+    __device__ __forceinline__ uint32_t rep4() {
+        const float a = ff(r4.x, r4.z), b = ff(r4.y, r4.w);
+        met += fmaxf(-ff(a, b), 0.f);
+        met += fmaxf(-(b + a), 0.f);
+        r2_0 = r4.z + r4.x; r2_1 = r4.w + r4.y;             // g with partial sums 0
+        met += fmaxf(-ff(r2_0, r2_1), 0.f);
+        A0 = r2_1 + r2_0;                                   // g with u2 = 0
+        maxmet = group_max(__float_as_uint(met), lane >> 3);
+        return fork() ? 0xFu : 0u;                          // [u3, u3, u3, u3]
+    }
+
     // all four positions information bits, list full: assume every phase takes the fast exit (each
     // path keeps its likelier bit, metrics unchanged), compute the four leaf LLRs lane-locally and
     // verify all four exits with ONE vote: min_t (met + |A_t|) = met + min_t |A_t| must exceed the
@@ -735,6 +747,7 @@ struct Dec {
             }
             const uint32_t pat = ib & 15u;
             if (pat == 0u) T4 = rate0(ib & 16u);
+            else if (pat == 8u) T4 = rep4();
             else if (pat == 15u && ninfo >= 3 && rate1(T4)) {}
             else T4 = seq4(ib);
             if (h == 0) w0 = (w0 & ~0xF0u) | (T4 << 4);
