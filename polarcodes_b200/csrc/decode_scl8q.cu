@@ -123,9 +123,11 @@ __device__ __noinline__ uint32_t heap_combine(uint32_t* Pw, uint32_t* H, int p, 
     uint32_t* hp = (d2 == m) ? (Pw + p * HS - NW) : (H + p * HS);
     __syncwarp();
     hp[2 * D / 32 - 1] = T;
+#pragma unroll 1
     for (int w = 32; w < D; w <<= 1) {
         const int lgw = 31 - __clz(w), layc = m - lgw, nw = w >> 5;
         const uint32_t* cs = H + ((cidx >> (3 * (layc - 1))) & 7) * HS + nw;
+#pragma unroll 1
         for (int kk = 0; kk < nw; kk++)
             hp[(2 * D - 2 * w) / 32 + kk] = cs[kk] ^ hp[(2 * D - w) / 32 + kk];
     }
@@ -510,13 +512,13 @@ struct Dec {
         const float4* src = L3 + pfield(3);
         float* dst = G::GL4 ? nullptr : arr(4, p);
 #pragma unroll 1
-        for (int k0 = 0; k0 < S / 4; k0 += 8) {
-            const uint32_t cw = cword(4, 0, k0 >> 3);
-            float4 a[8], b[8];
+        for (int k0 = 0; k0 < S / 4; k0 += 4) {          // 8 loads in flight; compact code
+            const uint32_t cw = cword(4, 0, k0 >> 3) >> (4 * (k0 & 7));
+            float4 a[4], b[4];
 #pragma unroll
-            for (int kk = 0; kk < 8; kk++) { a[kk] = src[(k0 + kk) * 8]; b[kk] = src[(k0 + kk + S / 4) * 8]; }
+            for (int kk = 0; kk < 4; kk++) { a[kk] = src[(k0 + kk) * 8]; b[kk] = src[(k0 + kk + S / 4) * 8]; }
 #pragma unroll
-            for (int kk = 0; kk < 8; kk++) {
+            for (int kk = 0; kk < 4; kk++) {
                 const float4 o = gs4(a[kk], b[kk], cw, 4 * kk);
                 if constexpr (G::GL4) L4[(k0 + kk) * 8 + p] = o;
                 else *reinterpret_cast<float4*>(dst + 4 * (k0 + kk)) = o;
