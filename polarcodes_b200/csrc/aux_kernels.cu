@@ -242,21 +242,45 @@ __global__ void count_errors_kernel(const uint32_t* __restrict__ dec, const uint
     }
 }
 
-// HBM-bound pre-pass of the list-8 quad kernel: 12 bytes per value, 128-bit accesses
-__global__ void __launch_bounds__(256) convert_f64_f32_kernel(const double* __restrict__ y64, float* __restrict__ y32, size_t count4) {
-    const size_t stride = (size_t)gridDim.x * blockDim.x;
-    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < count4; i += stride) {
-        const double2 a = reinterpret_cast<const double2*>(y64)[2 * i];
-        const double2 b = reinterpret_cast<const double2*>(y64)[2 * i + 1];
-        reinterpret_cast<float4*>(y32)[i] = make_float4((float)a.x, (float)a.y, (float)b.x, (float)b.y);
+// HBM-bound pre-pass of the list-8 quad kernel, one warp per frame: converts double channel
+// values to float (what SCLDecoderMinsum.cpp:406-408 does per frame; y64 may be null: the values
+// are already float) and appends every frame with a value outside the safe input range of the
+// tuned kernel's arithmetic, |y| == 0 or 2^-40 <= |y| <= 2^100 (NaN / inf are outside), to the
+// redo list: the generic kernel re-decodes those after the tuned one.
+__global__ void __launch_bounds__(256) scl8_prepass_kernel(const double* __restrict__ y64, float* __restrict__ y32, int n, int B,
+                                                           int* redo_count, int* redo_list) {
+    const int lane = threadIdx.x & 31;
+    const int wpb = blockDim.x >> 5;
+    for (int frame = blockIdx.x * wpb + (threadIdx.x >> 5); frame < B; frame += gridDim.x * wpb) {
+        bool ok = true;
+        float4* o = reinterpret_cast<float4*>(y32 + (size_t)frame * n);
+#pragma unroll 4
+        for (int q = lane; q < n / 4; q += 32) {
+            float4 v;
+            if (y64) {
+                const double2 a = reinterpret_cast<const double2*>(y64 + (size_t)frame * n)[2 * q];
+                const double2 b = reinterpret_cast<const double2*>(y64 + (size_t)frame * n)[2 * q + 1];
+                v = make_float4((float)a.x, (float)a.y, (float)b.x, (float)b.y);
+                o[q] = v;
+            } else {
+                v = o[q];
+            }
+            const float e[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+            for (int i = 0; i < 4; i++) {
+                const uint32_t a = __float_as_uint(e[i]) & 0x7fffffffu;      // 2^-40 = 0x2B800000, 2^100 = 0x71800000
+                ok = ok && (a == 0u || (a - 0x2B800000u) <= (0x71800000u - 0x2B800000u));
+            }
+        }
+        if (!__all_sync(0xffffffffu, ok) && lane == 0) redo_list[atomicAdd(redo_count, 1)] = frame;
     }
 }
 
-cudaError_t launch_convert_f64_f32(const double* y64, float* y32, size_t count, int sm_count, cudaStream_t st) {
-    const size_t count4 = count / 4;    // count is a multiple of n >= 256
-    size_t blocks = (count4 + 255) / 256;
-    if (blocks > (size_t)sm_count * 8) blocks = (size_t)sm_count * 8;
-    convert_f64_f32_kernel<<<(unsigned)blocks, 256, 0, st>>>(y64, y32, count4);
+cudaError_t launch_scl8_prepass(const double* y64, float* y32, int n, int B, int* redo_count, int* redo_list, int sm_count,
+                                cudaStream_t st) {
+    int blocks = (B + 7) / 8;
+    if (blocks > sm_count * 8) blocks = sm_count * 8;
+    scl8_prepass_kernel<<<blocks, 256, 0, st>>>(y64, y32, n, B, redo_count, redo_list);
     return cudaGetLastError();
 }
 

@@ -312,9 +312,12 @@ static cudaError_t launch(pcb_handle* h, const DecodeArgs& a, cudaStream_t st) {
         cudaError_t e = cudaMemsetAsync(h->d_redo, 0, sizeof(int), st);
         if (e != cudaSuccess) return e;
         if (h->quad) {
+            // Pre-pass (HBM-bound): the decoder works in float (SCLDecoderMinsum.cpp:406-408), so a
+            // double batch is converted once instead of at each top-stage event of every frame, and
+            // frames outside the tuned kernel's safe input range are put on the redo list.
+            float* y32 = const_cast<float*>(reinterpret_cast<const float*>(a.y));
+            const double* y64 = nullptr;
             if (!f.y_f32) {
-                // the decoder works in float (SCLDecoderMinsum.cpp:406-408): convert the batch once
-                // instead of at each of the 8 top-stage events of every frame
                 const size_t cnt = (size_t)a.B * h->n;
                 if (h->y32_cap < cnt) {
                     cudaFree(h->d_y32); h->d_y32 = nullptr; h->y32_cap = 0;
@@ -322,11 +325,13 @@ static cudaError_t launch(pcb_handle* h, const DecodeArgs& a, cudaStream_t st) {
                     if (e1 != cudaSuccess) return e1;
                     h->y32_cap = cnt;
                 }
-                e = launch_convert_f64_f32(reinterpret_cast<const double*>(a.y), h->d_y32, cnt, h->sm_count, st);
-                if (e != cudaSuccess) return e;
-                h->launches++;
-                f.y = h->d_y32; f.y_f32 = 1;
+                y64 = reinterpret_cast<const double*>(a.y);
+                y32 = h->d_y32;
             }
+            e = launch_scl8_prepass(y64, y32, h->n, a.B, f.redo_count, f.redo_list, h->sm_count, st);
+            if (e != cudaSuccess) return e;
+            h->launches++;
+            f.y = y32; f.y_f32 = 1;
             const int nq = (a.B + 3) / 4;
             const size_t spb = scl8q_scratch_per_block(h->m);
             if (spb && !h->d_qscratch) {

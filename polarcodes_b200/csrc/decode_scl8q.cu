@@ -255,7 +255,6 @@ struct Dec {
     using G = Geo<M>;
     int lane, p;
     int fbase, Bm1;    // first frame of the quad, last frame of the batch (tail quads repeat it)
-    uint32_t badmask;  // frames of the quad with a channel value outside the safe range of ff()
     float* P;          // this frame's LLR layers
     uint32_t* H;       // this frame's partial-sum heaps
     uint32_t* keys;    // this frame's 16 candidate keys
@@ -296,34 +295,16 @@ struct Dec {
     // (always an f-layer here) to shared memory.  With a g-layer 1 the channel values are staged
     // in rounds of 8+8 float4 columns (k and k + Q3/2, the two operands of a layer-4 output), so
     // that the staging area never overlaps the layer-4 arrays being written.
-    // range check that licenses the arithmetic shortcuts of ff(): |y| == 0 or in [2^-40, 2^100]
-    // (2^-40 = 0x2B800000, 2^100 = 0x71800000 as bit patterns; NaN and inf are above)
-    __device__ __forceinline__ static bool in_range(float4 v) {
-        bool ok = true;
-        const float e[4] = {v.x, v.y, v.z, v.w};
-#pragma unroll
-        for (int i = 0; i < 4; i++) {
-            const uint32_t a = __float_as_uint(e[i]) & 0x7fffffffu;
-            ok = ok && (a == 0u || (a - 0x2B800000u) <= (0x71800000u - 0x2B800000u));
-        }
-        return ok;
-    }
-    // Stage layer 1 = f(y[x], y[x + N/2]) (the same for every path) of the four frames; at the
-    // first event of a quad this is also the first touch of its channel values: range-check them.
-    __device__ __forceinline__ void stage_l1f(int ev, const YT* ybase) {
+    // Stage layer 1 = f(y[x], y[x + N/2]) (the same for every path) of the four frames.
+    __device__ __forceinline__ void stage_l1f(const YT* ybase) {
         constexpr int N4 = G::N / 4;
 #pragma unroll 1
         for (int f = 0; f < 4; f++) {
             const YT* y = ybase + (size_t)min(fbase + f, Bm1) * G::N;
             float* Rf = W + f * G::FRAME_WORDS + G::STAGE_OFF;
-            bool ok = true;
-#pragma unroll 4
-            for (int q = lane; q < N4 / 2; q += 32) {
-                const float4 a = load_y4(y, q), b = load_y4(y, q + N4 / 2);
-                if (ev == 0) ok = ok && in_range(a) && in_range(b);
-                *reinterpret_cast<float4*>(Rf + 4 * q) = ff4(a, b);
-            }
-            if (ev == 0 && !__all_sync(FULL, ok)) badmask |= 1u << f;
+#pragma unroll 2
+            for (int q = lane; q < N4 / 2; q += 32)
+                *reinterpret_cast<float4*>(Rf + 4 * q) = ff4(load_y4(y, q), load_y4(y, q + N4 / 2));
         }
     }
 
@@ -367,7 +348,7 @@ struct Dec {
             return;
         }
         if (!g1) {
-            stage_l1f(ev, ybase);
+            stage_l1f(ybase);
             __syncwarp();
         }
 #pragma unroll 1
@@ -438,7 +419,7 @@ struct Dec {
                 for (int q = lane; q < N4; q += 32) *reinterpret_cast<float4*>(R + 4 * q) = load_y4(y, q);
             }
         } else {
-            stage_l1f(ev, ybase);
+            stage_l1f(ybase);
         }
         __syncwarp();
         const float* R = P + G::STAGE_OFF;
@@ -812,7 +793,6 @@ __global__ void __launch_bounds__(32, (q8::Geo<M>::GL4 && M == 10 ? 16 : M == 10
         D.fbase = 4 * quad; D.Bm1 = A.B - 1;
 #pragma unroll
         for (int f = 0; f < 4; f++) fr[f] = min(4 * quad + f, A.B - 1);
-        D.badmask = 0;
         // pull the next quad of this block into L2 while this one is decoded (its first touch is
         // otherwise a DRAM-latency stall with nothing else to do)
         if (4 * (quad + (int)gridDim.x) + 4 <= A.B) {
@@ -831,9 +811,6 @@ __global__ void __launch_bounds__(32, (q8::Geo<M>::GL4 && M == 10 ? 16 : M == 10
             D.leaf8(blk, ib);
         }
         __syncwarp();
-        // frames outside the safe range go to the generic (reference-literal) kernel
-        if (D.badmask && lane < 4 && ((D.badmask >> lane) & 1) && 4 * quad + lane < A.B)
-            A.redo_list[atomicAdd(A.redo_count, 1)] = 4 * quad + lane;
         // ---- final selection (:432-473): u-hat = x-hat F^(x)m per slot, CRC, first pass wins ----
         constexpr int NW = G::NW, HS = G::HS, lgN = M - 5;
         const int q0 = A.crc ? 0 : 7;   // without a CRC the reference returns slot L-1 unconditionally
@@ -888,7 +865,7 @@ __global__ void __launch_bounds__(32, (q8::Geo<M>::GL4 && M == 10 ? 16 : M == 10
             const unsigned okm = __ballot_sync(FULL, ok);
             const int chosen = okm ? (__ffs(okm) - 1) : 7;
             const int frame = 4 * quad + fs;
-            if (frame < A.B && !((D.badmask >> fs) & 1)) {
+            if (frame < A.B) {
                 if (A.sol)
                     for (int t = lane; t < A.stride; t += 32)
                         A.sol[(size_t)frame * A.stride + t] = (E[chosen * EW + (t >> 5)] >> (t & 31)) & 1;
