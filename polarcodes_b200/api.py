@@ -12,7 +12,8 @@ import os
 import numpy as np
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libpolar_b200.so")
+# PCB_LIB_PATH: another build of the same library (kernel experiments), never a different implementation
+LIB_PATH = os.environ.get("PCB_LIB_PATH") or os.path.join(HERE, "libpolar_b200.so")
 
 SC, SCMINSUM, SCLMINSUM = 1, 2, 3
 STRICT, FP32 = 0, 1

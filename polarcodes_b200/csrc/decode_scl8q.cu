@@ -797,6 +797,7 @@ __global__ void __launch_bounds__(32, (q8::Geo<M>::GL4 && M == 10 ? 16 : M == 10
         // otherwise a DRAM-latency stall with nothing else to do)
         if (4 * (quad + (int)gridDim.x) + 4 <= A.B) {
             const char* nx = reinterpret_cast<const char*>(ybase + (size_t)4 * (quad + gridDim.x) * n);
+#pragma unroll 1
             for (int ln = lane; ln < (int)(4 * n * sizeof(YT) / 128); ln += 32)
                 asm volatile("prefetch.global.L2 [%0];" ::"l"(nx + (size_t)ln * 128));
         }
@@ -859,6 +860,7 @@ __global__ void __launch_bounds__(32, (q8::Geo<M>::GL4 && M == 10 ? 16 : M == 10
                     else r = ((r << 8) ^ q8::c_crc16.v[((r >> 8) ^ byte) & 0xFF]) & 0xFFFF;
                 }
                 unsigned rx = 0;
+#pragma unroll 1
                 for (int t = 0; t < A.crc; t++) { const int q = A.k + t; rx = (rx << 1) | ((e[q >> 5] >> (q & 31)) & 1); }
                 ok = (rx == r);
             }
@@ -867,9 +869,11 @@ __global__ void __launch_bounds__(32, (q8::Geo<M>::GL4 && M == 10 ? 16 : M == 10
             const int frame = 4 * quad + fs;
             if (frame < A.B) {
                 if (A.sol)
+#pragma unroll 1
                     for (int t = lane; t < A.stride; t += 32)
                         A.sol[(size_t)frame * A.stride + t] = (E[chosen * EW + (t >> 5)] >> (t & 31)) & 1;
                 if (A.sol_bits)
+#pragma unroll 1
                     for (int t = lane; t < EW; t += 32) A.sol_bits[(size_t)frame * EW + t] = E[chosen * EW + t];
             }
             __syncwarp();

@@ -1,0 +1,12 @@
+#!/bin/bash
+# Builds a variant of the library with extra -D flags for decode_scl8q.cu:
+#   tools/variant.sh NAME -DPCB_Q_ODDCOLS=4 ...   ->  polarcodes_b200/build/var_NAME.so
+# Run it on the GPU box with PCB_LIB_PATH=polarcodes_b200/build/var_NAME.so python bench.py ...
+set -e
+R=$(cd "$(dirname "$0")/.." && pwd); N=$1; shift
+B=$R/polarcodes_b200/build
+nvcc -gencode arch=compute_100a,code=sm_100a -O3 -std=c++17 -lineinfo -fmad=false -Xcompiler -fPIC -Xcompiler -ffp-contract=off \
+  "$@" -I $R/polarcodes_b200/csrc -I $R/include -c ${SRC:-$R/polarcodes_b200/csrc/decode_scl8q.cu} -o $B/var_$N.o
+OBJS=$(ls $B/*.o | grep -v "var_\|decode_scl8q.cu.o")
+nvcc -gencode arch=compute_100a,code=sm_100a -shared -o $B/var_$N.so $OBJS $B/var_$N.o -lcudart
+echo $B/var_$N.so
