@@ -22,16 +22,22 @@
 #include "decode_common.cuh"
 #include "decode_launch.h"
 
-// Layer 4 in the global scratch as well (16 resident quads per SM): measured SLOWER on B200
-// (16.1 vs 17.6 Mframes/s) — the 57 MB of scratch plus the in-flight channel values no longer
-// stay in L2 (DRAM traffic x10) and 16 independent warps thrash the instruction cache.  Kept as
-// a compile-time experiment.
+// Compile-time switches, each measured on the same B200 box (tools/variant.sh + tools/ab.sh):
 // register chains cover the last PCB_Q_CHAIN + 1 stored layers (sizes 8 .. 8 << PCB_Q_CHAIN)
 #ifndef PCB_Q_CHAIN
 #define PCB_Q_CHAIN 1
 #endif
+// PCB_Q_GL4: layer 4 lives in the global scratch next to layer 3, which leaves 13 KB of shared
+// memory per quad and 16 resident quads per SM instead of 10 (25.5 vs 22.0 Mframes/s).  The
+// scratch is then 24 KB per quad, 57 MB for the whole grid: it has to stay in L2, so ...
 #ifndef PCB_Q_GL4
-#define PCB_Q_GL4 0
+#define PCB_Q_GL4 1
+#endif
+// ... PCB_Q_L2C (layer 2 of an even top-stage event cached in the scratch for the odd event that
+// follows, +32 KB per quad) is off: with it the footprint is 132 MB and half of the scratch
+// stores end up in DRAM (21.6 Mframes/s).  With 10 quads per SM it is a 4 % gain.
+#ifndef PCB_Q_L2C
+#define PCB_Q_L2C 0
 #endif
 
 namespace pcb {
@@ -74,7 +80,7 @@ struct Geo {
     static constexpr int L3_BLOCK_FLOAT4 = GL3 ? 4 * Q3 * 8 : 0;   // global scratch per block: [frame][k][slot] float4
     static constexpr int L4_BLOCK_FLOAT4 = GL4 ? 4 * (Q3 / 2) * 8 : 0;
     // layer 2 of the even top-stage events, re-used by the following odd event: [frame][k (2*Q3)][slot]
-    static constexpr int L2C_BLOCK_FLOAT4 = GL3 ? 4 * 2 * Q3 * 8 : 0;
+    static constexpr int L2C_BLOCK_FLOAT4 = (GL3 && PCB_Q_L2C) ? 4 * 2 * Q3 * 8 : 0;
     static constexpr int SCRATCH_BLOCK_FLOAT4 = L3_BLOCK_FLOAT4 + L4_BLOCK_FLOAT4 + L2C_BLOCK_FLOAT4;
     static_assert((FRAME_WORDS * 4) % 16 == 0 && (OFF_H * 4) % 16 == 0 && (OFF_KEYS * 4) % 16 == 0, "alignment");
 };
@@ -315,7 +321,7 @@ struct Dec {
         float* dst4 = G::GL4 ? nullptr : arr(4, p);
         float4* dst3 = L3 + p;
         __syncwarp();                            // everyone is done with the previous subtree
-        if (g3) {
+        if (PCB_Q_L2C && g3) {
             // Odd event: layers 1 and 2 are those of the previous (even) event, whose layer 2 is in
             // the global scratch (of this path or of the ancestor it was cloned from since):
             // layer 3 = g(layer 2, partial sums of layer 3), no channel values needed.
@@ -364,10 +370,11 @@ struct Dec {
                 }
                 __syncwarp();
             }
-            uint32_t c1[4][2], c2[2][2];
+            uint32_t c1[4][2], c2[2][2], c3[2];
 #pragma unroll
             for (int h = 0; h < 2; h++) {
                 const int w32 = h * (Q / 16) + r;
+                c3[h] = (!PCB_Q_L2C && g3) ? cword(3, 0, w32) : 0u;
 #pragma unroll
                 for (int t = 0; t < 4; t++) c1[t][h] = g1 ? cword(1, t * E, w32) : 0u;
                 c2[0][h] = g2 ? cword(2, 0, w32) : 0u; c2[1][h] = g2 ? cword(2, E, w32) : 0u;
@@ -392,9 +399,13 @@ struct Dec {
                     float4 l2[2];
                     if (g2) { l2[0] = gs4(l1[0], l1[2], c2[0][h], 4 * kk); l2[1] = gs4(l1[1], l1[3], c2[1][h], 4 * kk); }
                     else { l2[0] = ff4(l1[0], l1[2]); l2[1] = ff4(l1[1], l1[3]); }
-                    L2c[k * 8 + p] = l2[0];             // for the odd event that follows
-                    L2c[(k + Q) * 8 + p] = l2[1];
-                    o[h] = ff4(l2[0], l2[1]);
+                    if (PCB_Q_L2C) {
+                        L2c[k * 8 + p] = l2[0];         // for the odd event that follows
+                        L2c[(k + Q) * 8 + p] = l2[1];
+                        o[h] = ff4(l2[0], l2[1]);
+                    } else {
+                        o[h] = g3 ? gs4(l2[0], l2[1], c3[h], 4 * kk) : ff4(l2[0], l2[1]);
+                    }
                     dst3[k * 8] = o[h];
                 }
                 if constexpr (G::GL4) L4[(r * 8 + kk) * 8 + p] = ff4(o[0], o[1]);
@@ -580,7 +591,7 @@ struct Dec {
 
     // LLR work at the first phase i0 = 8*blk of a size-8 subtree, down to layer LBOT
     __device__ __forceinline__ void upper(int blk, const YT* ybase, const int (&fr)[4]) {
-        static_assert(!G::GL4 && LR > G::LS, "register chains start below the first shared-memory layer");
+        static_assert(LR > G::LS, "register chains start below the first shared-memory layer");
         const int z = blk ? (__ffs(blk) - 1) : 31;
         int ll, own;    // layers own.. are recomputed, the f-layers below ll are still to do
         if (z >= M - 6) {                                  // i0 is a multiple of N/8
@@ -592,11 +603,14 @@ struct Dec {
             ll = own = G::LBOT - z;
             if (ll >= LR) { chain_g_dispatch<LR>(ll); ll = G::LBOT; }
             else if (G::GL3 && ll == 4) layer4_g_global();
+            else if (G::GL4 && ll == 5) layer5_global(true);
             else layer_g(ll);
         }
         if (ll < G::LBOT) {
+            int lam = ll + 1;
+            if (G::GL4 && ll == 4) { layer5_global(false); lam = 6; }
 #pragma unroll 1
-            for (int lam = ll + 1; lam < LR; lam++) layer_f(lam);
+            for (; lam < LR; lam++) layer_f(lam);
             chain_f();
         }
         // layers >= own are now this slot's own
