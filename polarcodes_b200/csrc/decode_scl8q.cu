@@ -30,6 +30,18 @@
 // PCB_Q_GL4: layer 4 lives in the global scratch next to layer 3, which leaves 13 KB of shared
 // memory per quad and 16 resident quads per SM instead of 10 (25.5 vs 22.0 Mframes/s).  The
 // scratch is then 24 KB per quad, 57 MB for the whole grid: it has to stay in L2, so ...
+#ifndef PCB_Q_L5N
+#define PCB_Q_L5N 4   // float4 column pairs per iteration of the layer-5 loop (GL4)
+#endif
+#ifndef PCB_Q_STU
+#define PCB_Q_STU 4    // unroll factors of the two staging loops of the top stage
+#endif
+#ifndef PCB_Q_STG
+#define PCB_Q_STG 16
+#endif
+#ifndef PCB_Q_TOPU
+#define PCB_Q_TOPU 1   // unroll factor of the top-stage column loop
+#endif
 #ifndef PCB_Q_GL4
 #define PCB_Q_GL4 1
 #endif
@@ -303,19 +315,19 @@ struct Dec {
     // that the staging area never overlaps the layer-4 arrays being written.
     // Stage layer 1 = f(y[x], y[x + N/2]) (the same for every path) of the four frames.
     __device__ __forceinline__ void stage_l1f(const YT* ybase) {
-        constexpr int N4 = G::N / 4;
+        constexpr int N4 = G::N / 4, SU = PCB_Q_STU;
 #pragma unroll 1
         for (int f = 0; f < 4; f++) {
             const YT* y = ybase + (size_t)min(fbase + f, Bm1) * G::N;
             float* Rf = W + f * G::FRAME_WORDS + G::STAGE_OFF;
-#pragma unroll 2
+#pragma unroll SU
             for (int q = lane; q < N4 / 2; q += 32)
                 *reinterpret_cast<float4*>(Rf + 4 * q) = ff4(load_y4(y, q), load_y4(y, q + N4 / 2));
         }
     }
 
     __device__ __forceinline__ void top_gl3(int ev, const YT* ybase, const int (&fr)[4]) {
-        constexpr int E = G::N / 8, N4 = G::N / 4, Q = G::Q3, NR = Q / 16;
+        constexpr int E = G::N / 8, N4 = G::N / 4, Q = G::Q3, NR = Q / 16, TU = PCB_Q_TOPU, SG = PCB_Q_STG;
         const bool g1 = ev & 4, g2 = ev & 2, g3 = ev & 1;
         const float* R = P + G::STAGE_OFF;
         float* dst4 = G::GL4 ? nullptr : arr(4, p);
@@ -361,7 +373,7 @@ struct Dec {
         for (int r = 0; r < NR; r++) {
             if (g1) {
                 if (r) __syncwarp();
-#pragma unroll 4
+#pragma unroll SG
                 for (int i = 0; i < 16; i++) {   // unit u = i*32 + lane: frame i/4, then t (8), h (2), kk (8)
                     const int u = i * 32 + lane, t = (u >> 4) & 7, h = (u >> 3) & 1, kk = u & 7;
                     const YT* y = ybase + (size_t)min(fbase + (i >> 2), Bm1) * G::N;
@@ -379,7 +391,7 @@ struct Dec {
                 for (int t = 0; t < 4; t++) c1[t][h] = g1 ? cword(1, t * E, w32) : 0u;
                 c2[0][h] = g2 ? cword(2, 0, w32) : 0u; c2[1][h] = g2 ? cword(2, E, w32) : 0u;
             }
-#pragma unroll 1
+#pragma unroll TU
             for (int kk = 0; kk < 8; kk++) {
                 float4 o[2];
 #pragma unroll
@@ -519,21 +531,21 @@ struct Dec {
     }
     // GL4: layer 5 (shared memory) from the layer-4 arrays in global memory
     __device__ __forceinline__ void layer5_global(bool isg) {
-        constexpr int S = G::size(5);
+        constexpr int S = G::size(5), NL = PCB_Q_L5N;
         const float4* src = L4 + (isg ? pfield(4) : p);
         float* dst = arr(5, p);
 #pragma unroll 1
-        for (int k0 = 0; k0 < S / 4; k0 += 8) {
-            const uint32_t cw = isg ? cword(5, 0, k0 >> 3) : 0u;
-            float4 a[8], b[8];
+        for (int k0 = 0; k0 < S / 4; k0 += NL) {
+            const uint32_t cw = isg ? cword(5, 0, k0 >> 3) >> (4 * (k0 & 7)) : 0u;
+            float4 a[NL], b[NL];
 #pragma unroll
-            for (int kk = 0; kk < 8; kk++) { a[kk] = src[(k0 + kk) * 8]; b[kk] = src[(k0 + kk + S / 4) * 8]; }
+            for (int kk = 0; kk < NL; kk++) { a[kk] = src[(k0 + kk) * 8]; b[kk] = src[(k0 + kk + S / 4) * 8]; }
             if (isg) {
 #pragma unroll
-                for (int kk = 0; kk < 8; kk++) *reinterpret_cast<float4*>(dst + 4 * (k0 + kk)) = gs4(a[kk], b[kk], cw, 4 * kk);
+                for (int kk = 0; kk < NL; kk++) *reinterpret_cast<float4*>(dst + 4 * (k0 + kk)) = gs4(a[kk], b[kk], cw, 4 * kk);
             } else {
 #pragma unroll
-                for (int kk = 0; kk < 8; kk++) *reinterpret_cast<float4*>(dst + 4 * (k0 + kk)) = ff4(a[kk], b[kk]);
+                for (int kk = 0; kk < NL; kk++) *reinterpret_cast<float4*>(dst + 4 * (k0 + kk)) = ff4(a[kk], b[kk]);
             }
         }
     }
