@@ -29,7 +29,7 @@ cudaError_t launch_decode_scl8(const DecodeArgs& a, const uint32_t* info_w, cons
 cudaError_t scl8_occupancy(int m, int* bps, int* warp_bytes);
 // list-8 kernel with four frames per warp (decode_scl8q.cu)
 bool scl8q_supported(int m);
-cudaError_t launch_decode_scl8q(const DecodeArgs& a, const uint32_t* info_w, void* l3_scratch, int blocks, cudaStream_t st);
+cudaError_t launch_decode_scl8q(const DecodeArgs& a, const uint32_t* info_w, void* l3_scratch, int* next_quad, int blocks, cudaStream_t st);
 size_t scl8q_scratch_per_block(int m);
 cudaError_t scl8q_occupancy(int m, int* bps, int* warp_bytes);
 }  // namespace pcb
@@ -57,7 +57,7 @@ struct pcb_handle {
     void* d_qscratch = nullptr;     // quad kernel: layer-3 arrays of every resident block (stays in L2)
     float* d_y32 = nullptr;         // quad kernel: double channel values converted once per batch
     size_t y32_cap = 0;
-    int* d_redo = nullptr;          // [0] = count, [1..] = frame list
+    int* d_redo = nullptr;          // [0] = count, [1] = work counter of the quad kernel, [2..] = frame list
     size_t redo_cap = 0;
     size_t scratch_per_warp = 0;
     cudaStream_t sc = nullptr, sin = nullptr, sout = nullptr;
@@ -299,17 +299,17 @@ static DecodeArgs make_args(pcb_handle* h, const void* d_y, int y_f32, int* d_so
 static cudaError_t launch(pcb_handle* h, const DecodeArgs& a, cudaStream_t st) {
     h->launches++;
     if (h->fast8) {
-        if (h->redo_cap < (size_t)a.B + 1) {   // (re)allocation synchronises the device: safe, and rare
+        if (h->redo_cap < (size_t)a.B + 2) {   // (re)allocation synchronises the device: safe, and rare
             cudaFree(h->d_redo); h->d_redo = nullptr; h->redo_cap = 0;
-            cudaError_t e0 = cudaMalloc(&h->d_redo, ((size_t)a.B + 1) * sizeof(int));
+            cudaError_t e0 = cudaMalloc(&h->d_redo, ((size_t)a.B + 2) * sizeof(int));
             if (e0 != cudaSuccess) return e0;
-            h->redo_cap = (size_t)a.B + 1;
+            h->redo_cap = (size_t)a.B + 2;
         }
         // tuned kernel first; frames outside its safe input range come back in the redo list and
         // are decoded by the generic kernel right behind it (normally an empty launch)
         DecodeArgs f = a;
-        f.redo_count = h->d_redo; f.redo_list = h->d_redo + 1; f.use_redo_list = 0;
-        cudaError_t e = cudaMemsetAsync(h->d_redo, 0, sizeof(int), st);
+        f.redo_count = h->d_redo; f.redo_list = h->d_redo + 2; f.use_redo_list = 0;
+        cudaError_t e = cudaMemsetAsync(h->d_redo, 0, 2 * sizeof(int), st);
         if (e != cudaSuccess) return e;
         if (h->quad) {
             // Pre-pass (HBM-bound): the decoder works in float (SCLDecoderMinsum.cpp:406-408), so a
@@ -338,7 +338,7 @@ static cudaError_t launch(pcb_handle* h, const DecodeArgs& a, cudaStream_t st) {
                 cudaError_t e1 = cudaMalloc(&h->d_qscratch, spb * (size_t)fast_blocks(h));
                 if (e1 != cudaSuccess) return e1;
             }
-            e = launch_decode_scl8q(f, h->h_info_w.data(), h->d_qscratch, nq < fast_blocks(h) ? nq : fast_blocks(h), st);
+            e = launch_decode_scl8q(f, h->h_info_w.data(), h->d_qscratch, h->d_redo + 1, nq < fast_blocks(h) ? nq : fast_blocks(h), st);
         } else {
             e = launch_decode_scl8(f, h->h_info_w.data(), h->h_fv_w.data(), a.B < fast_blocks(h) ? a.B : fast_blocks(h), st);
         }

@@ -789,6 +789,7 @@ __constant__ CrcTable c_crc16 = make_crc(16);
 struct Scl8qArgs {
     DecodeArgs a;
     uint32_t info_w[65];   // n <= 2048, one zero word behind the last
+    int* next_quad;        // work counter (zero at launch): quad gridDim.x + counter is the next one not yet taken
     float4* l3;            // n >= 1024: global scratch of the layer-3 arrays, Geo::L3_BLOCK_FLOAT4 per block
 };
 
@@ -814,15 +815,25 @@ __global__ void __launch_bounds__(32, (q8::Geo<M>::GL4 && M == 10 ? 16 : M == 10
     const YT* ybase = reinterpret_cast<const YT*>(A.y);
     const int nquads = (A.B + 3) >> 2;
 
-    for (int quad = blockIdx.x; quad < nquads; quad += gridDim.x) {
+    // The first quad of a block is its index, the following ones come from a work counter: decode
+    // times differ from quad to quad, and a static stride leaves SMs idle at the end of the batch.
+    int quad = blockIdx.x;
+    while (quad < nquads) {
         int fr[4];
         D.fbase = 4 * quad; D.Bm1 = A.B - 1;
 #pragma unroll
         for (int f = 0; f < 4; f++) fr[f] = min(4 * quad + f, A.B - 1);
-        // pull the next quad of this block into L2 while this one is decoded (its first touch is
+        // take the next quad now and pull it into L2 while this one is decoded (its first touch is
         // otherwise a DRAM-latency stall with nothing else to do)
-        if (4 * (quad + (int)gridDim.x) + 4 <= A.B) {
-            const char* nx = reinterpret_cast<const char*>(ybase + (size_t)4 * (quad + gridDim.x) * n);
+        int next_quad = 0;
+#ifdef PCB_Q_STATIC
+        next_quad = quad + (int)gridDim.x;
+#else
+        if (lane == 0) next_quad = (int)gridDim.x + atomicAdd(S.next_quad, 1);
+        next_quad = __shfl_sync(FULL, next_quad, 0);
+#endif
+        if (4 * next_quad + 4 <= A.B) {
+            const char* nx = reinterpret_cast<const char*>(ybase + (size_t)4 * next_quad * n);
 #pragma unroll 1
             for (int ln = lane; ln < (int)(4 * n * sizeof(YT) / 128); ln += 32)
                 asm volatile("prefetch.global.L2 [%0];" ::"l"(nx + (size_t)ln * 128));
@@ -904,6 +915,7 @@ __global__ void __launch_bounds__(32, (q8::Geo<M>::GL4 && M == 10 ? 16 : M == 10
             }
             __syncwarp();
         }
+        quad = next_quad;
     }
 }
 
@@ -928,9 +940,10 @@ static cudaError_t occ_m(int* bps, int* warp_bytes) {
 bool scl8q_supported(int m) { return m >= 8 && m <= 11; }
 
 // info_w: host copy of the information-mask words (ceil(n/32)), passed as kernel parameters
-cudaError_t launch_decode_scl8q(const DecodeArgs& a, const uint32_t* info_w, void* l3_scratch, int blocks, cudaStream_t st) {
+cudaError_t launch_decode_scl8q(const DecodeArgs& a, const uint32_t* info_w, void* l3_scratch, int* next_quad, int blocks, cudaStream_t st) {
     Scl8qArgs s;
     s.a = a;
+    s.next_quad = next_quad;
     s.l3 = reinterpret_cast<float4*>(l3_scratch);
     for (int i = 0; i < 65; i++) s.info_w[i] = i < a.n / 32 ? info_w[i] : 0;
 #define PCB_CASE(MM) \
