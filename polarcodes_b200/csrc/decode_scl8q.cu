@@ -98,12 +98,14 @@ struct Geo {
 };
 
 // f for frames whose channel values are all 0 or within [2^-40, 2^100] (see decode_scl8.cu):
-// min(|a|,|b|) * (a*b < 0 ? -1 : 1) (SCLDecoderMinsum.cpp:40-42) equals fminf(|a|,|b|) with the
-// sign bit of the product.
+// min(|a|,|b|) * (a*b < 0 ? -1 : 1) (SCLDecoderMinsum.cpp:40-42) equals min(|a|,|b|) with the
+// XOR of the two sign bits there (the product neither underflows nor overflows), which is one
+// instruction: FMNMX.XORSIGN |a|, |b|.  A zero result may carry a minus sign where the reference
+// has +0; no decision, metric update or later f/g distinguishes the two.
 __device__ __forceinline__ float ff(float a, float b) {
-    const float m = fminf(fabsf(a), fabsf(b));
-    const float pr = a * b;
-    return __uint_as_float(__float_as_uint(m) | (__float_as_uint(pr) & 0x80000000u));
+    float r;
+    asm("min.xorsign.abs.f32 %0, %1, %2;" : "=f"(r) : "f"(a), "f"(b));
+    return r;
 }
 // g (SCLDecoderMinsum.cpp:51-53) with the partial-sum bit already at the sign position
 __device__ __forceinline__ float gs(float a, float b, uint32_t signbit) {
