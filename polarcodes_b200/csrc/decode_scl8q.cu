@@ -39,6 +39,9 @@
 #ifndef PCB_Q_STG
 #define PCB_Q_STG 16
 #endif
+#ifndef PCB_Q_FADD2
+#define PCB_Q_FADD2 1   // g on a float4 with two packed adds
+#endif
 #ifndef PCB_Q_TOPU
 #define PCB_Q_TOPU 1   // unroll factor of the top-stage column loop
 #endif
@@ -115,10 +118,33 @@ __device__ __forceinline__ uint32_t sgn(uint32_t w, int pos) { return (w << (31 
 __device__ __forceinline__ float4 ff4(float4 a, float4 b) {
     return make_float4(ff(a.x, b.x), ff(a.y, b.y), ff(a.z, b.z), ff(a.w, b.w));
 }
-// partial-sum bits of the 4 elements at positions pos .. pos+3 of cw
+// b + a as two packed adds (FADD2: one issue slot for two lanes of the float4)
+__device__ __forceinline__ float4 add4(float4 b, float4 a) {
+    unsigned long long a0, a1, b0, b1, r0, r1;
+    asm("mov.b64 %0, {%1,%2};" : "=l"(a0) : "f"(a.x), "f"(a.y));
+    asm("mov.b64 %0, {%1,%2};" : "=l"(a1) : "f"(a.z), "f"(a.w));
+    asm("mov.b64 %0, {%1,%2};" : "=l"(b0) : "f"(b.x), "f"(b.y));
+    asm("mov.b64 %0, {%1,%2};" : "=l"(b1) : "f"(b.z), "f"(b.w));
+    asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r0) : "l"(b0), "l"(a0));
+    asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r1) : "l"(b1), "l"(a1));
+    float4 r;
+    asm("mov.b64 {%0,%1}, %2;" : "=f"(r.x), "=f"(r.y) : "l"(r0));
+    asm("mov.b64 {%0,%1}, %2;" : "=f"(r.z), "=f"(r.w) : "l"(r1));
+    return r;
+}
+// partial-sum bits of the 4 elements at positions pos .. pos+3 of cw (pos <= 28)
 __device__ __forceinline__ float4 gs4(float4 a, float4 b, uint32_t cw, int pos) {
+#if PCB_Q_FADD2
+    const uint32_t t = cw << (28 - pos);       // bit of element 3 at the sign position
+    a.x = __uint_as_float(__float_as_uint(a.x) ^ ((t << 3) & 0x80000000u));
+    a.y = __uint_as_float(__float_as_uint(a.y) ^ ((t << 2) & 0x80000000u));
+    a.z = __uint_as_float(__float_as_uint(a.z) ^ ((t << 1) & 0x80000000u));
+    a.w = __uint_as_float(__float_as_uint(a.w) ^ (t & 0x80000000u));
+    return add4(b, a);
+#else
     return make_float4(gs(a.x, b.x, sgn(cw, pos)), gs(a.y, b.y, sgn(cw, pos + 1)), gs(a.z, b.z, sgn(cw, pos + 2)),
                        gs(a.w, b.w, sgn(cw, pos + 3)));
+#endif
 }
 
 // max over the 8 lanes of a frame: four full-warp reductions (one uniform-datapath CREDUX each,
