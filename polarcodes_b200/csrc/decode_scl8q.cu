@@ -878,39 +878,68 @@ __global__ void __launch_bounds__(32, (q8::Geo<M>::GL4 && M == 10 ? 16 : M == 10
         }
         __syncwarp();
         // ---- final selection (:432-473): u-hat = x-hat F^(x)m per slot, CRC, first pass wins ----
-        constexpr int NW = G::NW, HS = G::HS, lgN = M - 5;
+        // Lane l owns words l (and l + 32) of a codeword estimate: the transform inside a word is
+        // five shift-xor steps, across words five shuffles, and the information bits of a word are
+        // compressed (Hacker's Delight 7-4) and OR-ed into the packed output at the bit offset that
+        // the information counts of the words before it give.
+        constexpr int NW = G::NW, HS = G::HS, WPL = NW > 32 ? NW / 32 : 1;
         const int q0 = A.crc ? 0 : 7;   // without a CRC the reference returns slot L-1 unconditionally
+        uint32_t mk[WPL];
+        int off[WPL];
+        {
+            int base = 0;
+#pragma unroll
+            for (int w = 0; w < WPL; w++) {
+                mk[w] = lane + 32 * w < NW ? S.info_w[lane + 32 * w] : 0u;
+                const int c = __popc(mk[w]);
+                int inc = c;
+#pragma unroll
+                for (int d = 1; d < 32; d <<= 1) { const int v = __shfl_up_sync(FULL, inc, d); if (lane >= d) inc += v; }
+                off[w] = base + inc - c;
+                base += __shfl_sync(FULL, inc, 31);
+            }
+        }
 #pragma unroll 1
         for (int fs = 0; fs < 4; fs++) {
             uint32_t* X = reinterpret_cast<uint32_t*>(D.W + fs * G::FRAME_WORDS);   // x-hat of every slot (setbit_last, d2 == M)
             uint32_t* E = X + G::XW;
 #pragma unroll 1
-            for (int e = lane + (q0 << lgN); e < (8 << lgN); e += 32) {
-                const int q = e >> lgN, a = e & (NW - 1);
-                uint32_t x = X[q * HS + a];
-                x ^= (x >> 1) & 0x55555555u; x ^= (x >> 2) & 0x33333333u; x ^= (x >> 4) & 0x0F0F0F0Fu;
-                x ^= (x >> 8) & 0x00FF00FFu; x ^= (x >> 16) & 0x0000FFFFu;
-                X[q * HS + a] = x;
-            }
+            for (int t = lane + q0 * EW; t < 8 * EW; t += 32) E[t] = 0;
             __syncwarp();
 #pragma unroll 1
-            for (int sw = 1; sw < NW; sw <<= 1) {
-#pragma unroll 1
-                for (int e = lane + (q0 << lgN); e < (8 << lgN); e += 32) {
-                    const int q = e >> lgN, a = e & (NW - 1);
-                    if (!(a & sw)) X[q * HS + a] ^= X[q * HS + a + sw];
-                }
-                __syncwarp();
-            }
-#pragma unroll 1
             for (int q = q0; q < 8; q++) {
+                uint32_t xs[WPL];
+#pragma unroll
+                for (int w = 0; w < WPL; w++) {
+                    uint32_t x = lane + 32 * w < NW ? X[q * HS + lane + 32 * w] : 0u;
+                    x ^= (x >> 1) & 0x55555555u; x ^= (x >> 2) & 0x33333333u; x ^= (x >> 4) & 0x0F0F0F0Fu;
+                    x ^= (x >> 8) & 0x00FF00FFu; x ^= (x >> 16) & 0x0000FFFFu;
+#pragma unroll
+                    for (int sw = 1; sw < 32 && sw < NW; sw <<= 1) {
+                        const uint32_t y = __shfl_xor_sync(FULL, x, sw);
+                        if (!(lane & sw)) x ^= y;
+                    }
+                    xs[w] = x;
+                }
+                if constexpr (WPL == 2) xs[0] ^= xs[1];
+#pragma unroll
+                for (int w = 0; w < WPL; w++) {
+                    uint32_t m = mk[w], x = xs[w] & m, mkk = ~m << 1;
 #pragma unroll 1
-                for (int t0 = 0; t0 < A.stride; t0 += 32) {
-                    const int t = t0 + lane;
-                    int bit = 0;
-                    if (t < A.stride) { const int pos = A.info_pos[t]; bit = (X[q * HS + (pos >> 5)] >> (pos & 31)) & 1; }
-                    const unsigned wd = __ballot_sync(FULL, bit);
-                    if (lane == 0) E[q * EW + (t0 >> 5)] = wd;
+                    for (int i = 0; i < 5; i++) {
+                        uint32_t mp = mkk ^ (mkk << 1);
+                        mp ^= mp << 2; mp ^= mp << 4; mp ^= mp << 8; mp ^= mp << 16;
+                        const uint32_t mv = mp & m;
+                        m = (m ^ mv) | (mv >> (1 << i));
+                        const uint32_t t = x & mv;
+                        x = (x ^ t) | (t >> (1 << i));
+                        mkk &= ~mp;
+                    }
+                    const int c = __popc(mk[w]), o = off[w];
+                    if (c) {
+                        atomicOr(&E[q * EW + (o >> 5)], x << (o & 31));
+                        if ((o & 31) + c > 32) atomicOr(&E[q * EW + (o >> 5) + 1], x >> (32 - (o & 31)));
+                    }
                 }
             }
             __syncwarp();
