@@ -542,18 +542,40 @@ struct Dec {
     __device__ __forceinline__ void layer4_g_global() {
         constexpr int S = G::size(4);
         const float4* src = L3 + pfield(3);
-        float* dst = G::GL4 ? nullptr : arr(4, p);
+        if constexpr (G::GL4) {
+            // layer 4 goes back to the scratch and, as layer 5 = f(layer 4) comes next for this
+            // slot, columns j and j + S/8 are produced together and combined on the spot
+            float* dst5 = arr(5, p);
 #pragma unroll 1
-        for (int k0 = 0; k0 < S / 4; k0 += 4) {          // 8 loads in flight; compact code
-            const uint32_t cw = cword(4, 0, k0 >> 3) >> (4 * (k0 & 7));
-            float4 a[4], b[4];
+            for (int j0 = 0; j0 < S / 8; j0 += 2) {       // 8 loads in flight
+                const uint32_t cw0 = cword(4, 0, j0 >> 3) >> (4 * (j0 & 7)), cw1 = cword(4, 0, (j0 + S / 8) >> 3) >> (4 * (j0 & 7));
+                float4 a[2][2], b[2][2];
 #pragma unroll
-            for (int kk = 0; kk < 4; kk++) { a[kk] = src[(k0 + kk) * 8]; b[kk] = src[(k0 + kk + S / 4) * 8]; }
+                for (int i = 0; i < 2; i++)
 #pragma unroll
-            for (int kk = 0; kk < 4; kk++) {
-                const float4 o = gs4(a[kk], b[kk], cw, 4 * kk);
-                if constexpr (G::GL4) L4[(k0 + kk) * 8 + p] = o;
-                else *reinterpret_cast<float4*>(dst + 4 * (k0 + kk)) = o;
+                    for (int hh = 0; hh < 2; hh++) {
+                        const int c = j0 + i + hh * (S / 8);
+                        a[i][hh] = src[c * 8]; b[i][hh] = src[(c + S / 4) * 8];
+                    }
+#pragma unroll
+                for (int i = 0; i < 2; i++) {
+                    const float4 lo = gs4(a[i][0], b[i][0], cw0, 4 * i), hi = gs4(a[i][1], b[i][1], cw1, 4 * i);
+                    L4[(j0 + i) * 8 + p] = lo;
+                    L4[(j0 + i + S / 8) * 8 + p] = hi;
+                    *reinterpret_cast<float4*>(dst5 + 4 * (j0 + i)) = ff4(lo, hi);
+                }
+            }
+        } else {
+            float* dst = arr(4, p);
+#pragma unroll 1
+            for (int k0 = 0; k0 < S / 4; k0 += 4) {          // 8 loads in flight; compact code
+                const uint32_t cw = cword(4, 0, k0 >> 3) >> (4 * (k0 & 7));
+                float4 a[4], b[4];
+#pragma unroll
+                for (int kk = 0; kk < 4; kk++) { a[kk] = src[(k0 + kk) * 8]; b[kk] = src[(k0 + kk + S / 4) * 8]; }
+#pragma unroll
+                for (int kk = 0; kk < 4; kk++)
+                    *reinterpret_cast<float4*>(dst + 4 * (k0 + kk)) = gs4(a[kk], b[kk], cw, 4 * kk);
             }
         }
     }
@@ -642,7 +664,7 @@ struct Dec {
             __syncwarp();
             ll = own = G::LBOT - z;
             if (ll >= LR) { chain_g_dispatch<LR>(ll); ll = G::LBOT; }
-            else if (G::GL3 && ll == 4) layer4_g_global();
+            else if (G::GL3 && ll == 4) { layer4_g_global(); if (G::GL4) ll = 5; }   // GL4: layer 5 done as well
             else if (G::GL4 && ll == 5) layer5_global(true);
             else layer_g(ll);
         }
