@@ -306,6 +306,15 @@ def main():
         peak_lane = info["sm_count"] * 128 * sm_max * 1e6 / 1e12         # T lane-ops/s
         ach = (B / (kms * 1e-3)) * ops["lane_ops"] / 1e12
         hbm_bytes = B * (N * 8 + words * 4)
+        # DRAM bytes of the dominant kernel per launch, from the committed ncu capture of this
+        # command (scaled to this batch size); algorithmic bytes are hbm_bytes
+        traffic, traffic_src = None, None
+        try:
+            tj = json.load(open(os.path.join(ROOT, "profiles", "r1_scl8q_traffic.json")))
+            traffic = (tj["dram_bytes_read"] + tj["dram_bytes_write"]) * B / tj["frames_per_launch"]
+            traffic_src = tj["source"]
+        except Exception:
+            pass
         line = {
             "metric": METRIC, "value": fps * K / 1e9, "unit": "Gbit/s", "frames_per_s": fps, "n_gpus": world,
             "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": 1e3 * elapsed / args.steps,
@@ -314,7 +323,8 @@ def main():
                        "frames_per_step_per_gpu": B, "input": "double y[B][n] resident in HBM (1 GiB/step > L2, no flush needed)",
                        "launch": info},
             "roofline": {"bound": "alu", "achieved": ach, "peak": peak_lane, "unit": "Tlane-op/s", "frac": ach / peak_lane,
-                         "traffic": None, "lane_ops_per_frame": ops, "kernel_ms": kms,
+                         "traffic": traffic, "traffic_source": traffic_src, "lane_ops_per_frame": ops, "kernel_ms": kms,
+                         "kernel_ms_covers": "scl8_prepass + decode_scl8q + decode_generic (empty redo list), CUDA events on the launch stream",
                          "peak_source": f"{info['sm_count']} SMs x 128 fp32/int lanes x {sm_max:.0f} MHz (SURVEY.md §8(d)); no tensor/HBM bound applies",
                          "hbm": {"algorithmic_GBps": hbm_bytes / (kms * 1e-3) / 1e9, "peak_GBps": peaks.get("hbm_gbs"),
                                  "frac": (hbm_bytes / (kms * 1e-3) / 1e9) / peaks["hbm_gbs"] if peaks.get("hbm_gbs") else None}},
