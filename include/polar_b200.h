@@ -81,7 +81,12 @@ int pcb_encode_batch(pcb_handle* h, const int* u, int* x, int with_shuffle, int 
 
 /* Decode B frames. y[B][n] are the raw channel values the reference passes to *::Decode
  * (PolarCodes.cpp:162,171,180).  sol is [B][n] for decoders 1,2 (full u-hat incl. frozen
- * positions) and [B][k+crc] for decoder 3 (info + crc bits), one int per bit. */
+ * positions) and [B][k+crc] for decoder 3 (info + crc bits), one int per bit.
+ * Host buffers (pinned ones overlap best), chunked H2D / kernel / D2H pipeline.  For the float
+ * decoders (2 non-strict, 3) the (float) narrowing the reference applies to y is done on the way:
+ * part of each chunk on the host cores (PCB_HOST_THREADS, default = usable CPUs / ranks of the
+ * node - 2), the rest on the device, split so that the cores and the PCIe link finish together
+ * (PCB_NO_HOST_NARROW=1: every value crosses the link as a double). */
 int pcb_decode_batch(pcb_handle* h, const double* y, int* sol, int B);
 /* Same with fp32 channel values. Bit-exact with pcb_decode_batch for decoder 3 when
  * yf[i] == (float)y[i] (SCLDecoderMinsum.cpp:406-408 does that conversion itself). */

@@ -247,8 +247,9 @@ __global__ void count_errors_kernel(const uint32_t* __restrict__ dec, const uint
 // are already float) and appends every frame with a value outside the safe input range of the
 // tuned kernel's arithmetic, |y| == 0 or 2^-40 <= |y| <= 2^100 (NaN / inf are outside), to the
 // redo list: the generic kernel re-decodes those after the tuned one.
+// Frames below `nf` are already float in y32; frame f >= nf is converted from y64[(f - nf) * n].
 __global__ void __launch_bounds__(256) scl8_prepass_kernel(const double* __restrict__ y64, float* __restrict__ y32, int n, int B,
-                                                           int* redo_count, int* redo_list) {
+                                                           int nf, int* redo_count, int* redo_list) {
     const int lane = threadIdx.x & 31;
     const int wpb = blockDim.x >> 5;
     for (int frame = blockIdx.x * wpb + (threadIdx.x >> 5); frame < B; frame += gridDim.x * wpb) {
@@ -257,9 +258,9 @@ __global__ void __launch_bounds__(256) scl8_prepass_kernel(const double* __restr
 #pragma unroll 4
         for (int q = lane; q < n / 4; q += 32) {
             float4 v;
-            if (y64) {
-                const double2 a = reinterpret_cast<const double2*>(y64 + (size_t)frame * n)[2 * q];
-                const double2 b = reinterpret_cast<const double2*>(y64 + (size_t)frame * n)[2 * q + 1];
+            if (frame >= nf) {
+                const double2 a = reinterpret_cast<const double2*>(y64 + (size_t)(frame - nf) * n)[2 * q];
+                const double2 b = reinterpret_cast<const double2*>(y64 + (size_t)(frame - nf) * n)[2 * q + 1];
                 v = make_float4((float)a.x, (float)a.y, (float)b.x, (float)b.y);
                 o[q] = v;
             } else {
@@ -276,11 +277,11 @@ __global__ void __launch_bounds__(256) scl8_prepass_kernel(const double* __restr
     }
 }
 
-cudaError_t launch_scl8_prepass(const double* y64, float* y32, int n, int B, int* redo_count, int* redo_list, int sm_count,
-                                cudaStream_t st) {
+cudaError_t launch_scl8_prepass(const double* y64, float* y32, int n, int B, int nf, int* redo_count, int* redo_list,
+                                int sm_count, cudaStream_t st) {
     int blocks = (B + 7) / 8;
     if (blocks > sm_count * 8) blocks = sm_count * 8;
-    scl8_prepass_kernel<<<blocks, 256, 0, st>>>(y64, y32, n, B, redo_count, redo_list);
+    scl8_prepass_kernel<<<blocks, 256, 0, st>>>(y64, y32, n, B, y64 ? nf : B, redo_count, redo_list);
     return cudaGetLastError();
 }
 

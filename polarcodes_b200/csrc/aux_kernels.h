@@ -24,8 +24,8 @@ cudaError_t launch_encode(const int* d_u, int* d_x, int n, int m, int with_shuff
 cudaError_t launch_generate(const GenArgs& g, int sm_count, cudaStream_t st);
 // pre-pass of the list-8 quad kernel: y64 (may be null) -> y32 conversion and the range check that
 // fills the redo list (see aux_kernels.cu)
-cudaError_t launch_scl8_prepass(const double* y64, float* y32, int n, int B, int* redo_count, int* redo_list, int sm_count,
-                                cudaStream_t st);
+cudaError_t launch_scl8_prepass(const double* y64, float* y32, int n, int B, int nf, int* redo_count, int* redo_list,
+                                int sm_count, cudaStream_t st);
 cudaError_t launch_count(const uint32_t* dec, const uint32_t* tx, int words, int nbits, int B,
                          unsigned long long* counters, cudaStream_t st);
 

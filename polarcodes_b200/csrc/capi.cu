@@ -5,7 +5,13 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <chrono>
+#include <condition_variable>
+#include <mutex>
+#include <thread>
 #include <vector>
+#include <immintrin.h>
+#include <sched.h>
 
 #include "../../include/polar_b200.h"
 #include "aux_kernels.h"
@@ -43,6 +49,90 @@ using namespace pcb;
             return fail(PCB_ECUDA, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__); \
     } while (0)
 
+// Host side of pcb_decode_batch for the float decoders: the reference narrows every channel value
+// to float before it decodes (SCLDecoderMinsum.cpp:406-408), so the narrowing is done on the host
+// cores, chunk by chunk into pinned staging buffers, and only 4 bytes per value cross PCIe (the
+// link, not the GPU, bounds this call).  Same rounding as the device cast (round to nearest even,
+// denormals kept).  This is data movement of the product path, not a decoder: no CPU fallback.
+struct HostNarrow {
+    std::vector<std::thread> th;
+    std::mutex m;
+    std::condition_variable cv, done_cv;
+    const double* src = nullptr;
+    float* dst = nullptr;
+    size_t cnt = 0;
+    int gen = 0, pending = 0, T = 0;
+    bool stop = false;
+
+    static int usable_cpus() {     // the CPUs this process may run on (a container sees fewer than the host has)
+        cpu_set_t set;
+        CPU_ZERO(&set);
+        if (sched_getaffinity(0, sizeof(set), &set) == 0 && CPU_COUNT(&set) > 0) return CPU_COUNT(&set);
+        return (int)std::thread::hardware_concurrency();
+    }
+    __attribute__((target("avx"))) static size_t narrow_avx(const double* s, float* d, size_t n) {   // d 32-byte aligned
+        size_t i = 0;
+        for (; i + 8 <= n; i += 8) {
+            const __m128 lo = _mm256_cvtpd_ps(_mm256_loadu_pd(s + i)), hi = _mm256_cvtpd_ps(_mm256_loadu_pd(s + i + 4));
+            _mm256_stream_ps(d + i, _mm256_insertf128_ps(_mm256_castps128_ps256(lo), hi, 1));
+        }
+        return i;
+    }
+    static void narrow(const double* s, float* d, size_t n) {   // d 32-byte aligned; the host never reads the staging buffer
+        size_t i = 0;
+        if (__builtin_cpu_supports("avx")) i = narrow_avx(s, d, n);
+        for (; i + 4 <= n; i += 4) {
+            const __m128 lo = _mm_cvtpd_ps(_mm_loadu_pd(s + i)), hi = _mm_cvtpd_ps(_mm_loadu_pd(s + i + 2));
+            _mm_stream_ps(d + i, _mm_movelh_ps(lo, hi));
+        }
+        for (; i < n; i++) d[i] = (float)s[i];
+        _mm_sfence();
+    }
+    void worker(int id) {
+        int seen = 0;
+        for (;;) {
+            std::unique_lock<std::mutex> lk(m);
+            cv.wait(lk, [&] { return stop || gen != seen; });
+            if (stop) return;
+            seen = gen;
+            const double* s = src; float* d = dst; const size_t n = cnt;
+            lk.unlock();
+            const size_t per = ((n + T - 1) / T + 15) & ~(size_t)15;
+            const size_t a = std::min(n, (size_t)id * per), b = std::min(n, a + per);
+            if (b > a) narrow(s + a, d + a, b - a);
+            lk.lock();
+            if (--pending == 0) done_cv.notify_one();
+        }
+    }
+    void start() {
+        if (T) return;
+        const char* e = getenv("PCB_HOST_THREADS");
+        int t;
+        if (e && *e) {
+            t = atoi(e);
+        } else {
+            // the ranks of one node (torchrun) share its CPUs; one CPU per rank stays with the calling
+            // thread and the driver
+            const char* lw = getenv("LOCAL_WORLD_SIZE");
+            const int ranks = (lw && atoi(lw) > 0) ? atoi(lw) : 1;
+            t = usable_cpus() / ranks - (ranks > 1 ? 1 : 2);
+        }
+        T = t < 1 ? 1 : t > 64 ? 64 : t;
+        for (int i = 0; i < T; i++) th.emplace_back([this, i] { worker(i); });
+    }
+    void run(const double* s, float* d, size_t n) {
+        std::unique_lock<std::mutex> lk(m);
+        src = s; dst = d; cnt = n; pending = T; gen++;
+        cv.notify_all();
+        done_cv.wait(lk, [&] { return pending == 0; });
+    }
+    ~HostNarrow() {
+        { std::lock_guard<std::mutex> lk(m); stop = true; }
+        cv.notify_all();
+        for (auto& t : th) t.join();
+    }
+};
+
 struct pcb_handle {
     int device = 0, n = 0, m = 0, k = 0, crc = 0, L = 1, decoder = 0, precision = 0;
     int stride = 0, EW = 0, fp64 = 0, sizeofT = 4;
@@ -70,6 +160,15 @@ struct pcb_handle {
     void* d_y[2] = {};
     int* d_sol[2] = {};
     uint32_t* d_solb[2] = {};
+    float* h_stage[2] = {};         // pinned staging of the narrowed channel values (host pipeline, float decoders)
+    size_t stage_frames = 0;
+    HostNarrow* narrow = nullptr;
+    const double* mix_tail = nullptr;   // set by decode_host for one launch(): frames >= mix_nf of the batch are still
+    int mix_nf = 0;                     // double, at this device address (the list-8 pre-pass converts them)
+    double narrow_frac = 0.75;          // share of a chunk narrowed on the host; adapted to the measured rates
+    double rate_cpu = 0, rate_h2d = 0;  // values/s narrowed by the host cores, bytes/s of the H2D copies
+    cudaEvent_t ev_c0[2] = {}, ev_c1[2] = {};
+    size_t copy_bytes[2] = {};
     // Monte-Carlo buffers
     size_t mc_frames = 0;
     float* d_ymc = nullptr;
@@ -200,6 +299,8 @@ pcb_handle* pcb_create(int device, int n, int k, int crc, int L, int decoder, in
         if ((e = cudaEventCreateWithFlags(&h->ev_in[s], cudaEventDisableTiming)) != cudaSuccess) return bail("event", e);
         if ((e = cudaEventCreateWithFlags(&h->ev_k[s], cudaEventDisableTiming)) != cudaSuccess) return bail("event", e);
         if ((e = cudaEventCreateWithFlags(&h->ev_out[s], cudaEventDisableTiming)) != cudaSuccess) return bail("event", e);
+        if ((e = cudaEventCreate(&h->ev_c0[s])) != cudaSuccess) return bail("event", e);
+        if ((e = cudaEventCreate(&h->ev_c1[s])) != cudaSuccess) return bail("event", e);
     }
     if ((e = cudaEventCreate(&h->t0)) != cudaSuccess) return bail("event", e);
     if ((e = cudaEventCreate(&h->t1)) != cudaSuccess) return bail("event", e);
@@ -222,11 +323,14 @@ void pcb_destroy(pcb_handle* h) {
     for (int s = 0; s < 2; s++) {
         cudaFree(h->d_y[s]); cudaFree(h->d_sol[s]); cudaFree(h->d_solb[s]);
         if (h->ev_in[s]) cudaEventDestroy(h->ev_in[s]);
+        if (h->ev_c0[s]) cudaEventDestroy(h->ev_c0[s]);
+        if (h->ev_c1[s]) cudaEventDestroy(h->ev_c1[s]);
         if (h->ev_k[s]) cudaEventDestroy(h->ev_k[s]);
         if (h->ev_out[s]) cudaEventDestroy(h->ev_out[s]);
     }
     cudaFree(h->d_ymc); cudaFree(h->d_tx); cudaFree(h->d_dec); cudaFree(h->d_counters);
     cudaFree(h->d_eu); cudaFree(h->d_ex); cudaFree(h->d_redo); cudaFree(h->d_qscratch); cudaFree(h->d_y32);
+    cudaFreeHost(h->h_stage[0]); cudaFreeHost(h->h_stage[1]); delete h->narrow;
     if (h->t0) cudaEventDestroy(h->t0);
     if (h->t1) cudaEventDestroy(h->t1);
     if (h->sc) cudaStreamDestroy(h->sc);
@@ -317,6 +421,7 @@ static cudaError_t launch(pcb_handle* h, const DecodeArgs& a, cudaStream_t st) {
             // frames outside the tuned kernel's safe input range are put on the redo list.
             float* y32 = const_cast<float*>(reinterpret_cast<const float*>(a.y));
             const double* y64 = nullptr;
+            int nf = 0;                      // frames below nf are float already
             if (!f.y_f32) {
                 const size_t cnt = (size_t)a.B * h->n;
                 if (h->y32_cap < cnt) {
@@ -327,8 +432,11 @@ static cudaError_t launch(pcb_handle* h, const DecodeArgs& a, cudaStream_t st) {
                 }
                 y64 = reinterpret_cast<const double*>(a.y);
                 y32 = h->d_y32;
+            } else if (h->mix_tail) {        // host pipeline: the tail of the chunk came over as doubles
+                y64 = h->mix_tail; nf = h->mix_nf;
             }
-            e = launch_scl8_prepass(y64, y32, h->n, a.B, f.redo_count, f.redo_list, h->sm_count, st);
+            h->mix_tail = nullptr;
+            e = launch_scl8_prepass(y64, y32, h->n, a.B, nf, f.redo_count, f.redo_list, h->sm_count, st);
             if (e != cudaSuccess) return e;
             h->launches++;
             f.y = y32; f.y_f32 = 1;
@@ -360,7 +468,9 @@ static int ensure_slots(pcb_handle* h, size_t frames, size_t ybytes_per_frame) {
     }
     h->slot_frames = 0;
     for (int s = 0; s < 2; s++) {
-        CK(cudaMalloc(&h->d_y[s], frames * (size_t)h->n * 8));
+        // 12 bytes per value: a chunk of the host pipeline may arrive as floats (narrowed on the host)
+        // followed by a tail of doubles, [frames*n floats][frames*n doubles]
+        CK(cudaMalloc(&h->d_y[s], frames * (size_t)h->n * 12));
         CK(cudaMalloc(&h->d_sol[s], frames * (size_t)h->stride * 4));
         CK(cudaMalloc(&h->d_solb[s], frames * (size_t)h->EW * 4));
     }
@@ -383,16 +493,69 @@ static int decode_host(pcb_handle* h, const void* y, int y_f32, int* sol, uint32
     if (chunk < 1) chunk = 1;
     if (chunk > (size_t)B) chunk = (size_t)B;
     if (int r = ensure_slots(h, chunk, ybpf)) return r;
+    // float decoders fed with doubles: narrow on the host cores, copy 4 bytes per value
+    const bool narrow = !y_f32 && !h->fp64 && !getenv("PCB_NO_HOST_NARROW");
+    const bool mixed = narrow && h->fast8 && h->quad && !getenv("PCB_NO_MIXED_INPUT");
+    const double* mix_tail = nullptr;
+    int mix_nf = 0;
+    if (narrow) {
+        if (h->stage_frames < chunk) {
+            cudaFreeHost(h->h_stage[0]); cudaFreeHost(h->h_stage[1]);
+            h->h_stage[0] = h->h_stage[1] = nullptr; h->stage_frames = 0;
+            for (int s = 0; s < 2; s++) CK(cudaHostAlloc(&h->h_stage[s], chunk * (size_t)h->n * 4, cudaHostAllocDefault));
+            h->stage_frames = chunk;
+        }
+        if (!h->narrow) h->narrow = new HostNarrow();
+        h->narrow->start();
+    }
     int c = 0;
     for (size_t f0 = 0; f0 < (size_t)B; f0 += chunk, c++) {
         const int s = c & 1;
         const int nb = (int)((size_t)B - f0 < chunk ? (size_t)B - f0 : chunk);
         if (c >= 2) CK(cudaStreamWaitEvent(h->sin, h->ev_k[s], 0));      // slot input consumed
-        CK(cudaMemcpyAsync(h->d_y[s], (const char*)y + f0 * ybpf, (size_t)nb * ybpf, cudaMemcpyHostToDevice, h->sin));
+        if (narrow) {
+            if (c >= 2) {
+                CK(cudaEventSynchronize(h->ev_in[s]));                   // staging slot copied out
+                float ms = 0.f;                                          // H2D rate of the chunk that used this slot
+                if (h->copy_bytes[s] && cudaEventElapsedTime(&ms, h->ev_c0[s], h->ev_c1[s]) == cudaSuccess && ms > 0.f) {
+                    const double r = (double)h->copy_bytes[s] / (ms * 1e-3);
+                    h->rate_h2d = h->rate_h2d > 0 ? 0.5 * h->rate_h2d + 0.5 * r : r;
+                }
+            }
+            // The list-8 pre-pass can convert on the device, so the chunk is split: the head is
+            // narrowed here (4 bytes per value over PCIe), the tail goes over as doubles while the
+            // host cores work.  With R values/s narrowed and W bytes/s copied, both finish together
+            // when the head is 8R / (W + 4R) of the chunk.
+            int nf = nb;
+            if (mixed) {
+                if (h->rate_cpu > 0 && h->rate_h2d > 0) h->narrow_frac = 8.0 * h->rate_cpu / (h->rate_h2d + 4.0 * h->rate_cpu);
+                if (h->narrow_frac < 0.1) h->narrow_frac = 0.1;          // keeps the host rate measured
+                if (h->narrow_frac > 1.0) h->narrow_frac = 1.0;
+                const char* fe = getenv("PCB_NARROW_FRAC");              // experiment: fixed split
+                const double frac = (fe && *fe) ? atof(fe) : h->narrow_frac;
+                nf = ((int)(frac * nb) + 3) & ~3;
+                if (nf > nb) nf = nb;
+            }
+            const int nd = nb - nf;
+            double* d_tail = reinterpret_cast<double*>(reinterpret_cast<char*>(h->d_y[s]) + chunk * (size_t)h->n * 4);
+            CK(cudaEventRecord(h->ev_c0[s], h->sin));
+            if (nd) CK(cudaMemcpyAsync(d_tail, (const double*)y + (f0 + nf) * h->n, (size_t)nd * h->n * 8, cudaMemcpyHostToDevice, h->sin));
+            CK(cudaEventRecord(h->ev_c1[s], h->sin));                    // the tail copy alone times the link (no host work inside)
+            h->copy_bytes[s] = (size_t)nd * h->n * 8;
+            const auto t0 = std::chrono::steady_clock::now();
+            if (nf) h->narrow->run((const double*)y + f0 * h->n, h->h_stage[s], (size_t)nf * h->n);
+            const double dt = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+            if (nf && dt > 0) { const double r = (double)nf * h->n / dt; h->rate_cpu = h->rate_cpu > 0 ? 0.5 * h->rate_cpu + 0.5 * r : r; }
+            if (nf) CK(cudaMemcpyAsync(h->d_y[s], h->h_stage[s], (size_t)nf * h->n * 4, cudaMemcpyHostToDevice, h->sin));
+            mix_tail = nd ? d_tail : nullptr; mix_nf = nf;
+        } else {
+            CK(cudaMemcpyAsync(h->d_y[s], (const char*)y + f0 * ybpf, (size_t)nb * ybpf, cudaMemcpyHostToDevice, h->sin));
+        }
         CK(cudaEventRecord(h->ev_in[s], h->sin));
         CK(cudaStreamWaitEvent(h->sc, h->ev_in[s], 0));
         if (c >= 2) CK(cudaStreamWaitEvent(h->sc, h->ev_out[s], 0));     // slot output drained
-        DecodeArgs a = make_args(h, h->d_y[s], y_f32, sol ? h->d_sol[s] : nullptr, solb ? h->d_solb[s] : nullptr, nb);
+        DecodeArgs a = make_args(h, h->d_y[s], y_f32 || narrow, sol ? h->d_sol[s] : nullptr, solb ? h->d_solb[s] : nullptr, nb);
+        h->mix_tail = mix_tail; h->mix_nf = mix_nf; mix_tail = nullptr;
         CK(launch(h, a, h->sc));
         CK(cudaEventRecord(h->ev_k[s], h->sc));
         CK(cudaStreamWaitEvent(h->sout, h->ev_k[s], 0));
@@ -405,6 +568,9 @@ static int decode_host(pcb_handle* h, const void* y, int y_f32, int* sol, uint32
     CK(cudaStreamSynchronize(h->sout));
     CK(cudaStreamSynchronize(h->sc));
     CK(cudaStreamSynchronize(h->sin));
+    if (narrow && getenv("PCB_DEBUG_PIPE"))
+        fprintf(stderr, "polar_b200 host pipeline: %d threads, %.2f Gvalues/s narrowed, %.1f GB/s H2D, head share %.2f\n",
+                h->narrow->T, h->rate_cpu / 1e9, h->rate_h2d / 1e9, h->narrow_frac);
     return PCB_OK;
 }
 
