@@ -165,7 +165,10 @@ struct pcb_handle {
     HostNarrow* narrow = nullptr;
     const double* mix_tail = nullptr;   // set by decode_host for one launch(): frames >= mix_nf of the batch are still
     int mix_nf = 0;                     // double, at this device address (the list-8 pre-pass converts them)
-    double narrow_frac = 0.75;          // share of a chunk narrowed on the host; adapted to the measured rates
+    double narrow_frac = 0.75;          // share of a chunk narrowed on the host (see decode_host)
+    bool shared_host = false;           // other ranks of the job run on this host (LOCAL_WORLD_SIZE > 1)
+    double pc_dir = 1.0, pc_prev = 0, pc_frames = 0, pc_time = 0;
+    int pc_chunks = 0;
     double rate_cpu = 0, rate_h2d = 0;  // values/s narrowed by the host cores, bytes/s of the H2D copies
     cudaEvent_t ev_c0[2] = {}, ev_c1[2] = {};
     size_t copy_bytes[2] = {};
@@ -498,6 +501,7 @@ static int decode_host(pcb_handle* h, const void* y, int y_f32, int* sol, uint32
     const bool mixed = narrow && h->fast8 && h->quad && !getenv("PCB_NO_MIXED_INPUT");
     const double* mix_tail = nullptr;
     int mix_nf = 0;
+    auto t_iter = std::chrono::steady_clock::now();
     if (narrow) {
         if (h->stage_frames < chunk) {
             cudaFreeHost(h->h_stage[0]); cudaFreeHost(h->h_stage[1]);
@@ -505,7 +509,12 @@ static int decode_host(pcb_handle* h, const void* y, int y_f32, int* sol, uint32
             for (int s = 0; s < 2; s++) CK(cudaHostAlloc(&h->h_stage[s], chunk * (size_t)h->n * 4, cudaHostAllocDefault));
             h->stage_frames = chunk;
         }
-        if (!h->narrow) h->narrow = new HostNarrow();
+        if (!h->narrow) {
+            h->narrow = new HostNarrow();
+            const char* lw = getenv("LOCAL_WORLD_SIZE");
+            h->shared_host = lw && atoi(lw) > 1;
+            if (h->shared_host) h->narrow_frac = 0.3;
+        }
         h->narrow->start();
     }
     int c = 0;
@@ -524,13 +533,33 @@ static int decode_host(pcb_handle* h, const void* y, int y_f32, int* sol, uint32
             }
             // The list-8 pre-pass can convert on the device, so the chunk is split: the head is
             // narrowed here (4 bytes per value over PCIe), the tail goes over as doubles while the
-            // host cores work.  With R values/s narrowed and W bytes/s copied, both finish together
-            // when the head is 8R / (W + 4R) of the chunk.
+            // host cores work.  A process that has the host to itself uses the split at which cores
+            // and link finish together, 8R / (W + 4R) for R values/s narrowed and W bytes/s copied
+            // (both measured per chunk).  Ranks that share a host also share its memory system, R
+            // and W then depend on what the others do: there the share of the head follows the
+            // measured chunk rate (every three chunks it moves by 0.08, and turns round when the
+            // rate dropped), starting low.
             int nf = nb;
             if (mixed) {
-                if (h->rate_cpu > 0 && h->rate_h2d > 0) h->narrow_frac = 8.0 * h->rate_cpu / (h->rate_h2d + 4.0 * h->rate_cpu);
-                if (h->narrow_frac < 0.1) h->narrow_frac = 0.1;          // keeps the host rate measured
-                if (h->narrow_frac > 1.0) h->narrow_frac = 1.0;
+                const auto now = std::chrono::steady_clock::now();
+                if (!h->shared_host) {
+                    if (h->rate_cpu > 0 && h->rate_h2d > 0) h->narrow_frac = 8.0 * h->rate_cpu / (h->rate_h2d + 4.0 * h->rate_cpu);
+                    if (h->narrow_frac < 0.1) h->narrow_frac = 0.1;      // keeps the host rate measured
+                    if (h->narrow_frac > 1.0) h->narrow_frac = 1.0;
+                } else if (c >= 2) {                                     // steady state: this loop paces the pipeline
+                    h->pc_time += std::chrono::duration<double>(now - t_iter).count();
+                    h->pc_frames += (double)chunk;
+                    if (++h->pc_chunks == 3) {
+                        const double tp = h->pc_frames / h->pc_time;
+                        if (h->pc_prev > 0 && tp < 0.99 * h->pc_prev) h->pc_dir = -h->pc_dir;
+                        h->pc_prev = tp;
+                        h->narrow_frac += 0.08 * h->pc_dir;
+                        if (h->narrow_frac >= 1.0) { h->narrow_frac = 1.0; h->pc_dir = -1.0; }
+                        if (h->narrow_frac <= 0.0) { h->narrow_frac = 0.0; h->pc_dir = 1.0; }
+                        h->pc_frames = h->pc_time = 0; h->pc_chunks = 0;
+                    }
+                }
+                t_iter = now;
                 const char* fe = getenv("PCB_NARROW_FRAC");              // experiment: fixed split
                 const double frac = (fe && *fe) ? atof(fe) : h->narrow_frac;
                 nf = ((int)(frac * nb) + 3) & ~3;
