@@ -255,3 +255,39 @@ def test_one_frame_per_warp_variant_agrees(oracle, n, k, crc, snr):
     finally:
         del os.environ["PCB_SCL8_VARIANT"]
     assert (quad == want).all() and (warp == want).all()
+
+
+@pytest.mark.parametrize("frac", ["0", "0.5", "1", "auto", "off"])
+def test_host_pipeline_splits(oracle, frac):
+    """pcb_decode_batch with double host buffers: every chunk is split into a head narrowed to float
+    by the host thread pool and a tail narrowed by the device pre-pass.  Any split, ragged chunks and
+    out-of-range frames on either side of the split give the reference's bits."""
+    rng = np.random.default_rng(99)
+    n, k, crc, L = 256, 128, 8, 8
+    sigma, inf, mask = oracle.make_code(n, k, crc, 1.5)
+    y = 1 + sigma * rng.standard_normal((203, n))
+    y[3] *= 1e-30            # head of chunk 0
+    y[36, 5] = np.inf        # tail of chunk 0
+    y[100:104] *= 1e37
+    y[202, 0] = 1e-44
+    want = oracle.decode(3, n, L, k, crc, sigma, y, mask)
+    env = {"PCB_CHUNK_FRAMES": "37"}
+    if frac == "off":
+        env["PCB_NO_HOST_NARROW"] = "1"
+    elif frac != "auto":
+        env["PCB_NARROW_FRAC"] = frac
+    old = {key: os.environ.get(key) for key in env}
+    os.environ.update(env)
+    try:
+        d = _decoder(3, n, k, crc, L, mask, sigma)
+        got = d.decode(y)
+        got2 = d.decode(y)       # second call: staging slots and rates re-used
+    finally:
+        for key, v in old.items():
+            if v is None:
+                del os.environ[key]
+            else:
+                os.environ[key] = v
+    for g in (got, got2):
+        bad = np.nonzero((g != want).any(axis=1))[0]
+        assert bad.size == 0, f"frames {bad.tolist()} differ"
