@@ -189,7 +189,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours")
     ap.add_argument("--crc", type=int, default=0)
-    ap.add_argument("--frames", type=int, default=1 << 17, help="frames per step per GPU")
+    ap.add_argument("--frames", type=int, default=1 << 18, help="frames per step per GPU (SURVEY.md 8(d): >= 2^18 per launch)")
     ap.add_argument("--e2e-frames", type=int, default=1 << 16)
     ap.add_argument("--no-cpu", action="store_true")
     args = ap.parse_args()
@@ -320,7 +320,7 @@ def main():
             "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": 1e3 * elapsed / args.steps,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": f"SCLDecoderMinsum L={LIST} N={N} K={K} crc={args.crc} AWGN-construction {SNR_DB} dB",
-                       "frames_per_step_per_gpu": B, "input": "double y[B][n] resident in HBM (1 GiB/step > L2, no flush needed)",
+                       "frames_per_step_per_gpu": B, "input": f"double y[B][n] resident in HBM ({B * N * 8 / 2**30:.0f} GiB/step > L2, no flush needed)",
                        "launch": info},
             "roofline": {"bound": "alu", "achieved": ach, "peak": peak_lane, "unit": "Tlane-op/s", "frac": ach / peak_lane,
                          "traffic": traffic, "traffic_source": traffic_src, "lane_ops_per_frame": ops, "kernel_ms": kms,
