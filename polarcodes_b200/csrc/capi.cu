@@ -33,6 +33,12 @@ bool scl8_supported(int m);
 cudaError_t launch_decode_scl8(const DecodeArgs& a, const uint32_t* info_w, const uint32_t* fv_w, int blocks,
                                cudaStream_t st);
 cudaError_t scl8_occupancy(int m, int* bps, int* warp_bytes);
+// min-sum SC kernel with 32 frames per warp (decode_sc32.cu)
+bool sc32_supported(int m);
+cudaError_t sc32_occupancy(int m, int fp64, int* bps, int* bytes);
+size_t sc32_yt_bytes(int n, int B, int fp64);
+cudaError_t launch_decode_sc32(const DecodeArgs& a, const uint32_t* info_w, const uint32_t* fv_w, void* yt, int fp64,
+                               int blocks, int sm_count, cudaStream_t st);
 // list-8 kernel with four frames per warp (decode_scl8q.cu)
 bool scl8q_supported(int m);
 cudaError_t launch_decode_scl8q(const DecodeArgs& a, const uint32_t* info_w, void* l3_scratch, int* next_quad, int blocks, cudaStream_t st);
@@ -144,6 +150,10 @@ struct pcb_handle {
     // also re-decodes the frames the tuned kernel hands over)
     int f_bps = 0, f_warp_smem = 0;
     bool quad = false;              // four-frames-per-warp variant (decode_scl8q.cu) of the tuned kernel
+    bool sc32 = false;              // min-sum SC: lane-per-frame kernel (decode_sc32.cu) instead of the generic one
+    int sc32_bps = 0, sc32_smem = 0;
+    void* d_yt = nullptr;           // sc32: transposed channel values of the batch
+    size_t yt_cap = 0;
     void* d_qscratch = nullptr;     // quad kernel: layer-3 arrays of every resident block (stays in L2)
     float* d_y32 = nullptr;         // quad kernel: double channel values converted once per batch
     size_t y32_cap = 0;
@@ -215,6 +225,10 @@ static int configure(pcb_handle* h) {
                 h->f_bps = bps; h->f_warp_smem = wb;
             }
         }
+    }
+    h->sc32 = h->decoder == 2 && sc32_supported(h->m) && !getenv("PCB_FORCE_GENERIC");
+    if (h->sc32 && (sc32_occupancy(h->m, h->fp64, &h->sc32_bps, &h->sc32_smem) != cudaSuccess || h->sc32_bps == 0)) {
+        cudaGetLastError(); h->sc32 = false;
     }
     const char* env = getenv("PCB_WARP_SMEM");
     const int budget = env ? atoi(env) : 19200;
@@ -332,7 +346,7 @@ void pcb_destroy(pcb_handle* h) {
         if (h->ev_out[s]) cudaEventDestroy(h->ev_out[s]);
     }
     cudaFree(h->d_ymc); cudaFree(h->d_tx); cudaFree(h->d_dec); cudaFree(h->d_counters);
-    cudaFree(h->d_eu); cudaFree(h->d_ex); cudaFree(h->d_redo); cudaFree(h->d_qscratch); cudaFree(h->d_y32);
+    cudaFree(h->d_eu); cudaFree(h->d_ex); cudaFree(h->d_redo); cudaFree(h->d_qscratch); cudaFree(h->d_y32); cudaFree(h->d_yt);
     cudaFreeHost(h->h_stage[0]); cudaFreeHost(h->h_stage[1]); delete h->narrow;
     if (h->t0) cudaEventDestroy(h->t0);
     if (h->t1) cudaEventDestroy(h->t1);
@@ -457,6 +471,17 @@ static cudaError_t launch(pcb_handle* h, const DecodeArgs& a, cudaStream_t st) {
         f.use_redo_list = 1;
         h->launches++;
         return launch_decode_generic(f, h->L, h->decoder, h->fp64, max_blocks(h), h->wpb, st);
+    }
+    if (h->sc32) {
+        const size_t need = sc32_yt_bytes(h->n, a.B, h->fp64);
+        if (h->yt_cap < need) {               // (re)allocation synchronises the device: safe, and rare
+            cudaFree(h->d_yt); h->d_yt = nullptr; h->yt_cap = 0;
+            cudaError_t e0 = cudaMalloc(&h->d_yt, need);
+            if (e0 != cudaSuccess) return e0;
+            h->yt_cap = need;
+        }
+        h->launches++;                        // transposition + decoder
+        return launch_decode_sc32(a, h->h_info_w.data(), h->h_fv_w.data(), h->d_yt, h->fp64, h->sm_count * h->sc32_bps, h->sm_count, st);
     }
     int blocks = (a.B + h->wpb - 1) / h->wpb;
     if (blocks > max_blocks(h)) blocks = max_blocks(h);

@@ -1,0 +1,257 @@
+// Min-sum SC decoder (SCDecoderMinsum.cpp:14-76), thirty-two frames per warp: lane = frame.
+//
+// An SC decoder is one dependent walk over the code tree; inside a frame only the f/g updates of
+// one node are independent, and half of all updates belong to nodes of size <= 16.  Frames are
+// independent, so a lane owns a whole frame: every update, decision and partial-sum word is
+// lane-local, the warp needs no shuffle, vote or __syncwarp, and control (the frozen pattern, the
+// tree walk) is warp-uniform.  The price is memory: a frame's LLR tree is n values.  Layout:
+//  * the channel values are transposed once per batch into [tile of 32 frames][x][lane]
+//    (sc32_transpose_kernel, HBM-bound), already gathered through the bit reversal that maps the
+//    reference's adjacent pairing (SCDecoderMinsum.cpp:32-66) onto half-split pairing (DESIGN.md
+//    section 3), so that every load of the decoder is one coalesced row;
+//  * the layers of sizes n/2 .. 128 are never stored: every 64 phases the size-64 layer is
+//    produced straight from the channel values through log2(n) - 6 fused levels (the partial sums
+//    of those levels come from the lane's bit heap);
+//  * sizes 64, 32, 16, 8 live in shared memory as rows of 32 lanes ([row][lane]: conflict-free);
+//    a size-8 subtree is decoded in registers by a fully unrolled recursion;
+//  * partial sums are bit-packed per lane: sizes < 32 in one register word (size S at bits
+//    [S, 2S)), larger ones in a shared-memory heap with the same rule (SCLDecoderMinsum.cpp:287-305
+//    is the same combine; the SC decoder's decTree2 holds the same bits one int each).
+// Arithmetic is the reference's, operation for operation, in its own precision (double; float when
+// the handle was created with the fp32 precision): bit-exact decisions.
+#include "decode_common.cuh"
+#include "decode_launch.h"
+
+namespace pcb {
+namespace s32 {
+
+template <int M, typename T>
+struct Geo {
+    static constexpr int N = 1 << M, V = M - 6, NW = N / 32;
+    static constexpr int PROWS = 64 + 32 + 16 + 8;
+    __host__ __device__ static constexpr int off(int e) { return e == 6 ? 0 : e == 5 ? 64 : e == 4 ? 96 : 112; }
+    static constexpr int ESTRIDE = 33;     // decisions: word w of lane f at E[w * 33 + f]
+    static constexpr int BYTES = 32 * PROWS * (int)sizeof(T) + 32 * NW * 4 + ESTRIDE * NW * 4;
+};
+
+struct Args {
+    DecodeArgs a;
+    const void* yt;          // transposed channel values
+    int ntiles;
+    uint32_t info_w[64];     // n <= 2048
+    uint32_t fv_w[64];
+};
+
+// value of virtual level v (0 = channel values, level v has n >> v elements) at element x
+template <int v, int M, typename T>
+__device__ __forceinline__ T topval(const T* yt, const uint32_t* H, int lane, int gmask, int x) {
+    if constexpr (v == 0) {
+        return yt[(size_t)x * 32];
+    } else {
+        constexpr int V = M - 6, S = (1 << M) >> v;
+        const T a = topval<v - 1, M, T>(yt, H, lane, gmask, x), b = topval<v - 1, M, T>(yt, H, lane, gmask, x + S);
+        if ((gmask >> (V - v)) & 1) {
+            const int c = (H[((S + x) >> 5) * 32 + lane] >> (x & 31)) & 1;
+            return g_minsum<T>(a, b, c);
+        }
+        return f_minsum<T>(a, b);
+    }
+}
+
+// SC decoding of a subtree of S leaves held in registers (SCDecoderMinsum.cpp:32-66): returns its
+// partial sums, the decisions in phase order in ub.  ib/fb: information flags / frozen values.
+template <int S, typename T>
+__device__ __forceinline__ uint32_t sc_node(const T (&a)[S], uint32_t ib, uint32_t fb, uint32_t& ub) {
+    if constexpr (S == 1) {
+        const uint32_t u = (ib & 1u) ? (a[0] > (T)0 ? 0u : 1u) : (fb & 1u);   // :33-47, an LLR of exactly 0 decodes to 1
+        ub = u;
+        return u;
+    } else {
+        constexpr int Hf = S / 2;
+        T l[Hf], r[Hf];
+#pragma unroll
+        for (int j = 0; j < Hf; j++) l[j] = f_minsum<T>(a[j], a[j + Hf]);
+        uint32_t uL, uR;
+        const uint32_t pL = sc_node<Hf, T>(l, ib, fb, uL);
+#pragma unroll
+        for (int j = 0; j < Hf; j++) r[j] = g_minsum<T>(a[j], a[j + Hf], (int)((pL >> j) & 1u));
+        const uint32_t pR = sc_node<Hf, T>(r, ib >> Hf, fb >> Hf, uR);
+        ub = uL | (uR << Hf);
+        return (pL ^ pR) | (pR << Hf);
+    }
+}
+
+template <int M, typename T>
+__global__ void __launch_bounds__(32) decode_sc32_kernel(const __grid_constant__ Args S) {
+    using G = Geo<M, T>;
+    const DecodeArgs& A = S.a;
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    const int lane = threadIdx.x;
+    T* P = reinterpret_cast<T*>(smem_raw);
+    uint32_t* H = reinterpret_cast<uint32_t*>(P + G::PROWS * 32);
+    uint32_t* E = H + G::NW * 32;
+    constexpr int N = G::N;
+
+    for (int tile = blockIdx.x; tile < S.ntiles; tile += gridDim.x) {
+        const T* yt = reinterpret_cast<const T*>(S.yt) + (size_t)tile * N * 32 + lane;
+        uint32_t w0 = 0, uacc = 0;
+#pragma unroll 1
+        for (int b64 = 0; b64 < N / 64; ++b64) {
+            // size-64 layer from the channel values through V fused levels
+#pragma unroll 1
+            for (int j = 0; j < 64; ++j) P[(G::off(6) + j) * 32 + lane] = topval<G::V, M, T>(yt, H, lane, b64, j);
+#pragma unroll 1
+            for (int b8 = 0; b8 < 8; ++b8) {
+                const int blk = b64 * 8 + b8;
+                int e;
+                if (b8 == 0) {
+                    e = 5;
+                    T* dst = P + G::off(5) * 32 + lane;
+                    const T* src = P + G::off(6) * 32 + lane;
+#pragma unroll 4
+                    for (int j = 0; j < 32; ++j) dst[j * 32] = f_minsum<T>(src[j * 32], src[(j + 32) * 32]);
+                } else {
+                    e = 3 + __ffs(b8) - 1;
+                    const int Sz = 1 << e;
+                    T* dst = P + G::off(e) * 32 + lane;
+                    const T* src = P + G::off(e + 1) * 32 + lane;
+                    const uint32_t cw = Sz == 32 ? H[32 + lane] : (w0 >> Sz);
+#pragma unroll 4
+                    for (int j = 0; j < Sz; ++j) dst[j * 32] = g_minsum<T>(src[j * 32], src[(j + Sz) * 32], (int)((cw >> j) & 1u));
+                }
+#pragma unroll 1
+                for (int ee = e - 1; ee >= 3; --ee) {
+                    const int Sz = 1 << ee;
+                    T* dst = P + G::off(ee) * 32 + lane;
+                    const T* src = P + G::off(ee + 1) * 32 + lane;
+#pragma unroll 4
+                    for (int j = 0; j < Sz; ++j) dst[j * 32] = f_minsum<T>(src[j * 32], src[(j + Sz) * 32]);
+                }
+                // the size-8 subtree in registers
+                T a[8];
+#pragma unroll
+                for (int j = 0; j < 8; ++j) a[j] = P[(G::off(3) + j) * 32 + lane];
+                const uint32_t ib = (S.info_w[blk >> 2] >> (8 * (blk & 3))) & 0xFFu;
+                const uint32_t fb = (S.fv_w[blk >> 2] >> (8 * (blk & 3))) & 0xFFu;
+                uint32_t ub;
+                uint32_t Tps = sc_node<8, T>(a, ib, fb, ub);
+                uacc |= ub << (8 * (blk & 3));
+                if ((blk & 3) == 3) { E[(blk >> 2) * G::ESTRIDE + lane] = uacc; uacc = 0; }
+                // partial sums of the subtree that ends here, size 2^d2 (SCLDecoderMinsum.cpp:287-305)
+                const int d2 = min(M, 3 + __ffs(blk + 1) - 1);
+                if (d2 == 3) { w0 = (w0 & ~0xFF00u) | (Tps << 8); continue; }
+                Tps = (((w0 >> 8) ^ Tps) & 0xFFu) | (Tps << 8);
+                if (d2 == 4) { w0 = (w0 & 0x0000FFFFu) | (Tps << 16); continue; }
+                Tps = (((w0 >> 16) ^ Tps) & 0xFFFFu) | (Tps << 16);
+                if (d2 == M) continue;                     // the whole codeword: nobody reads it
+                const int D = 1 << d2;
+                H[(2 * D / 32 - 1) * 32 + lane] = Tps;
+#pragma unroll 1
+                for (int w = 32; w < D; w <<= 1) {
+                    const int nw = w >> 5;
+#pragma unroll 1
+                    for (int kk = 0; kk < nw; kk++)
+                        H[((2 * D - 2 * w) / 32 + kk) * 32 + lane] = H[(nw + kk) * 32 + lane] ^ H[((2 * D - w) / 32 + kk) * 32 + lane];
+                }
+            }
+        }
+        __syncwarp();
+        // decisions of the 32 frames, coalesced (sol: one int per bit, the reference's layout)
+#pragma unroll 1
+        for (int f = 0; f < 32; ++f) {
+            const int frame = tile * 32 + f;
+            if (frame >= A.B) break;
+            if (A.sol_bits)
+                for (int w = lane; w < G::NW; w += 32) A.sol_bits[(size_t)frame * G::NW + w] = E[w * G::ESTRIDE + f];
+            if (A.sol)
+                for (int t = lane; t < N; t += 32) A.sol[(size_t)frame * N + t] = (E[(t >> 5) * G::ESTRIDE + f] >> lane) & 1;
+        }
+        __syncwarp();
+    }
+}
+
+// y[B][n] -> yt[tile][x][lane] = y[tile * 32 + lane][bitrev_m(x)], converted to T; the frames behind
+// B in the last tile repeat frame B - 1.  One warp per (tile, 32 consecutive source indexes).
+template <typename TI, typename T>
+__global__ void __launch_bounds__(128) sc32_transpose_kernel(const TI* __restrict__ y, T* __restrict__ yt, int n, int m, int B, int ntiles) {
+    __shared__ T sm[4][32][33];
+    const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+    const int chunks = n >> 5;
+    const long long total = (long long)ntiles * chunks;
+    for (long long wid = (long long)blockIdx.x * 4 + wib; wid < total; wid += (long long)gridDim.x * 4) {
+        const int tile = (int)(wid / chunks), c = (int)(wid % chunks);
+        for (int f = 0; f < 32; f++) {
+            const int frame = min(tile * 32 + f, B - 1);
+            sm[wib][f][lane] = (T)y[(size_t)frame * n + c * 32 + lane];
+        }
+        __syncwarp();
+        for (int i = 0; i < 32; i++) {
+            const int x = (int)(__brev((unsigned)(c * 32 + i)) >> (32 - m));
+            yt[((size_t)tile * n + x) * 32 + lane] = sm[wib][lane][i];
+        }
+        __syncwarp();
+    }
+}
+
+template <int M, typename T>
+static cudaError_t launch_m(const Args& s, int blocks, cudaStream_t st) {
+    const int smem = Geo<M, T>::BYTES;
+    cudaError_t e = cudaFuncSetAttribute(decode_sc32_kernel<M, T>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    if (e != cudaSuccess) return e;
+    decode_sc32_kernel<M, T><<<blocks, 32, smem, st>>>(s);
+    return cudaGetLastError();
+}
+template <int M, typename T>
+static cudaError_t occ_m(int* bps, int* bytes) {
+    const int smem = Geo<M, T>::BYTES;
+    *bytes = smem;
+    cudaError_t e = cudaFuncSetAttribute(decode_sc32_kernel<M, T>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    if (e != cudaSuccess) return e;
+    return cudaOccupancyMaxActiveBlocksPerMultiprocessor(bps, decode_sc32_kernel<M, T>, 32, smem);
+}
+
+}  // namespace s32
+
+bool sc32_supported(int m) { return m >= 7 && m <= 11; }
+
+#define PCB_SC32_DISPATCH(FN, ...)                                                    \
+    switch (m) {                                                                     \
+        case 7: return fp64 ? s32::FN<7, double>(__VA_ARGS__) : s32::FN<7, float>(__VA_ARGS__);     \
+        case 8: return fp64 ? s32::FN<8, double>(__VA_ARGS__) : s32::FN<8, float>(__VA_ARGS__);     \
+        case 9: return fp64 ? s32::FN<9, double>(__VA_ARGS__) : s32::FN<9, float>(__VA_ARGS__);     \
+        case 10: return fp64 ? s32::FN<10, double>(__VA_ARGS__) : s32::FN<10, float>(__VA_ARGS__);  \
+        case 11: return fp64 ? s32::FN<11, double>(__VA_ARGS__) : s32::FN<11, float>(__VA_ARGS__);  \
+    }                                                                                \
+    return cudaErrorInvalidValue;
+
+cudaError_t sc32_occupancy(int m, int fp64, int* bps, int* bytes) { PCB_SC32_DISPATCH(occ_m, bps, bytes) }
+
+// bytes of the transposed copy of a batch
+size_t sc32_yt_bytes(int n, int B, int fp64) { return (size_t)((B + 31) / 32) * 32 * (size_t)n * (fp64 ? 8 : 4); }
+
+// transposes the batch into yt (sc32_yt_bytes) and decodes it
+cudaError_t launch_decode_sc32(const DecodeArgs& a, const uint32_t* info_w, const uint32_t* fv_w, void* yt, int fp64,
+                               int blocks, int sm_count, cudaStream_t st) {
+    s32::Args s;
+    s.a = a;
+    s.yt = yt;
+    s.ntiles = (a.B + 31) / 32;
+    for (int i = 0; i < 64; i++) { s.info_w[i] = i < a.n / 32 ? info_w[i] : 0; s.fv_w[i] = i < a.n / 32 ? fv_w[i] : 0; }
+    const long long warps = (long long)s.ntiles * (a.n / 32);
+    int tb = (int)((warps + 3) / 4);
+    if (tb > sm_count * 32) tb = sm_count * 32;
+    if (fp64) {
+        if (a.y_f32) s32::sc32_transpose_kernel<float, double><<<tb, 128, 0, st>>>((const float*)a.y, (double*)yt, a.n, a.m, a.B, s.ntiles);
+        else s32::sc32_transpose_kernel<double, double><<<tb, 128, 0, st>>>((const double*)a.y, (double*)yt, a.n, a.m, a.B, s.ntiles);
+    } else {
+        if (a.y_f32) s32::sc32_transpose_kernel<float, float><<<tb, 128, 0, st>>>((const float*)a.y, (float*)yt, a.n, a.m, a.B, s.ntiles);
+        else s32::sc32_transpose_kernel<double, float><<<tb, 128, 0, st>>>((const double*)a.y, (float*)yt, a.n, a.m, a.B, s.ntiles);
+    }
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return e;
+    if (blocks > s.ntiles) blocks = s.ntiles;
+    const int m = a.m;
+    PCB_SC32_DISPATCH(launch_m, s, blocks, st)
+}
+
+}  // namespace pcb
