@@ -37,8 +37,9 @@ cudaError_t scl8_occupancy(int m, int* bps, int* warp_bytes);
 bool sc32_supported(int m);
 cudaError_t sc32_occupancy(int m, int fp64, int* bps, int* bytes);
 size_t sc32_yt_bytes(int n, int B, int fp64);
-cudaError_t launch_decode_sc32(const DecodeArgs& a, const uint32_t* info_w, const uint32_t* fv_w, void* yt, int fp64,
-                               int blocks, int sm_count, cudaStream_t st);
+size_t sc32_scratch_bytes(int blocks, int fp64);
+cudaError_t launch_decode_sc32(const DecodeArgs& a, const uint32_t* info_w, const uint32_t* fv_w, void* yt, void* scratch,
+                               int fp64, int blocks, int sm_count, cudaStream_t st);
 // list-8 kernel with four frames per warp (decode_scl8q.cu)
 bool scl8q_supported(int m);
 cudaError_t launch_decode_scl8q(const DecodeArgs& a, const uint32_t* info_w, void* l3_scratch, int* next_quad, int blocks, cudaStream_t st);
@@ -153,6 +154,7 @@ struct pcb_handle {
     bool sc32 = false;              // min-sum SC: lane-per-frame kernel (decode_sc32.cu) instead of the generic one
     int sc32_bps = 0, sc32_smem = 0;
     void* d_yt = nullptr;           // sc32: transposed channel values of the batch
+    void* d_sc32_scratch = nullptr; // sc32: size-256 level of every resident block (stays in L2)
     size_t yt_cap = 0;
     void* d_qscratch = nullptr;     // quad kernel: layer-3 arrays of every resident block (stays in L2)
     float* d_y32 = nullptr;         // quad kernel: double channel values converted once per batch
@@ -346,7 +348,7 @@ void pcb_destroy(pcb_handle* h) {
         if (h->ev_out[s]) cudaEventDestroy(h->ev_out[s]);
     }
     cudaFree(h->d_ymc); cudaFree(h->d_tx); cudaFree(h->d_dec); cudaFree(h->d_counters);
-    cudaFree(h->d_eu); cudaFree(h->d_ex); cudaFree(h->d_redo); cudaFree(h->d_qscratch); cudaFree(h->d_y32); cudaFree(h->d_yt);
+    cudaFree(h->d_eu); cudaFree(h->d_ex); cudaFree(h->d_redo); cudaFree(h->d_qscratch); cudaFree(h->d_y32); cudaFree(h->d_yt); cudaFree(h->d_sc32_scratch);
     cudaFreeHost(h->h_stage[0]); cudaFreeHost(h->h_stage[1]); delete h->narrow;
     if (h->t0) cudaEventDestroy(h->t0);
     if (h->t1) cudaEventDestroy(h->t1);
@@ -480,8 +482,13 @@ static cudaError_t launch(pcb_handle* h, const DecodeArgs& a, cudaStream_t st) {
             if (e0 != cudaSuccess) return e0;
             h->yt_cap = need;
         }
+        if (!h->d_sc32_scratch) {
+            cudaError_t e0 = cudaMalloc(&h->d_sc32_scratch, sc32_scratch_bytes(h->sm_count * h->sc32_bps, h->fp64));
+            if (e0 != cudaSuccess) return e0;
+        }
         h->launches++;                        // transposition + decoder
-        return launch_decode_sc32(a, h->h_info_w.data(), h->h_fv_w.data(), h->d_yt, h->fp64, h->sm_count * h->sc32_bps, h->sm_count, st);
+        return launch_decode_sc32(a, h->h_info_w.data(), h->h_fv_w.data(), h->d_yt, h->d_sc32_scratch, h->fp64,
+                                  h->sm_count * h->sc32_bps, h->sm_count, st);
     }
     int blocks = (a.B + h->wpb - 1) / h->wpb;
     if (blocks > max_blocks(h)) blocks = max_blocks(h);

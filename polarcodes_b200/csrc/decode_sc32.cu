@@ -22,6 +22,10 @@
 #include "decode_common.cuh"
 #include "decode_launch.h"
 
+#ifndef PCB_S_TOPU
+#define PCB_S_TOPU 8     // outputs of the fused top stage per loop iteration (16 << log2 of it channel loads in flight)
+#endif
+
 namespace pcb {
 namespace s32 {
 
@@ -37,24 +41,43 @@ struct Geo {
 struct Args {
     DecodeArgs a;
     const void* yt;          // transposed channel values
+    void* scratch;           // n >= 512: 256 rows of 32 lanes per block
     int ntiles;
     uint32_t info_w[64];     // n <= 2048
     uint32_t fv_w[64];
 };
 
-// value of virtual level v (0 = channel values, level v has n >> v elements) at element x
-template <int v, int M, typename T>
-__device__ __forceinline__ T topval(const T* yt, const uint32_t* H, int lane, int gmask, int x) {
-    if constexpr (v == 0) {
-        return yt[(size_t)x * 32];
-    } else {
-        constexpr int V = M - 6, S = (1 << M) >> v;
-        const T a = topval<v - 1, M, T>(yt, H, lane, gmask, x), b = topval<v - 1, M, T>(yt, H, lane, gmask, x + S);
-        if ((gmask >> (V - v)) & 1) {
-            const int c = (H[((S + x) >> 5) * 32 + lane] >> (x & 31)) & 1;
-            return g_minsum<T>(a, b, c);
+// Element x of level BASE + LEVELS from the 2^LEVELS elements of level BASE it depends on (level v
+// has n >> v elements, level 0 = channel values; element x of level v pairs x and x + (n >> v) of
+// level v - 1, its partial-sum bit sits at heap bit (n >> v) + x).  All loads first (one basic
+// block: they are in flight together), then the levels in registers; level BASE + l is a g-level
+// iff bit LEVELS - l of `path` is set (warp-uniform), chosen by select so that nothing separates
+// the loads.
+template <int M, int BASE, int LEVELS, int NOUT, typename T>
+__device__ __forceinline__ void fuse(const T* __restrict__ src, const uint32_t* H, int lane, int path, int x0, T (&out)[NOUT]) {
+    constexpr int C = 1 << LEVELS, UNIT = ((1 << M) >> BASE) >> LEVELS;
+    T v[NOUT][C];
+#pragma unroll
+    for (int o = 0; o < NOUT; o++)
+#pragma unroll
+        for (int t = 0; t < C; t++) v[o][t] = src[(size_t)(x0 + o + UNIT * t) * 32];
+#pragma unroll
+    for (int o = 0; o < NOUT; o++) {
+#pragma unroll
+        for (int l = 1; l <= LEVELS; l++) {
+            const int half = C >> l;
+            const bool isg = (path >> (LEVELS - l)) & 1;
+            const int S = (1 << M) >> (BASE + l);
+#pragma unroll
+            for (int t = 0; t < half; t++) {
+                const int xx = x0 + o + UNIT * t;
+                const T a = v[o][t], b = v[o][t + half];
+                const int c = isg ? (int)((H[((S + xx) >> 5) * 32 + lane] >> (xx & 31)) & 1u) : 0;
+                const T gv = g_minsum<T>(a, b, c), fv = f_minsum<T>(a, b);
+                v[o][t] = isg ? gv : fv;
+            }
         }
-        return f_minsum<T>(a, b);
+        out[o] = v[o][0];
     }
 }
 
@@ -90,16 +113,41 @@ __global__ void __launch_bounds__(32) decode_sc32_kernel(const __grid_constant__
     T* P = reinterpret_cast<T*>(smem_raw);
     uint32_t* H = reinterpret_cast<uint32_t*>(P + G::PROWS * 32);
     uint32_t* E = H + G::NW * 32;
-    constexpr int N = G::N;
+    constexpr int N = G::N, TU = PCB_S_TOPU;
+    T* LB = reinterpret_cast<T*>(S.scratch) + (size_t)blockIdx.x * 256 * 32 + lane;   // size-256 level of this block's tile
 
     for (int tile = blockIdx.x; tile < S.ntiles; tile += gridDim.x) {
         const T* yt = reinterpret_cast<const T*>(S.yt) + (size_t)tile * N * 32 + lane;
         uint32_t w0 = 0, uacc = 0;
 #pragma unroll 1
         for (int b64 = 0; b64 < N / 64; ++b64) {
-            // size-64 layer from the channel values through V fused levels
+            // size-64 layer from the channel values through V fused levels; with V > 2 the size-256
+            // level is kept in a per-block global buffer (64 KB, stays in L2) and refreshed every
+            // fourth block, which cuts the passes over the channel values from n/64 to n/256
+            T o[TU];
+            if constexpr (G::V > 2) {
+                if ((b64 & 3) == 0) {
 #pragma unroll 1
-            for (int j = 0; j < 64; ++j) P[(G::off(6) + j) * 32 + lane] = topval<G::V, M, T>(yt, H, lane, b64, j);
+                    for (int x = 0; x < 256; x += TU) {
+                        fuse<M, 0, G::V - 2, TU, T>(yt, H, lane, b64 >> 2, x, o);
+#pragma unroll
+                        for (int i = 0; i < TU; i++) LB[(size_t)(x + i) * 32] = o[i];
+                    }
+                }
+#pragma unroll 1
+                for (int j = 0; j < 64; j += TU) {
+                    fuse<M, G::V - 2, 2, TU, T>(LB, H, lane, b64 & 3, j, o);
+#pragma unroll
+                    for (int i = 0; i < TU; i++) P[(G::off(6) + j + i) * 32 + lane] = o[i];
+                }
+            } else {
+#pragma unroll 1
+                for (int j = 0; j < 64; j += TU) {
+                    fuse<M, 0, G::V, TU, T>(yt, H, lane, b64, j, o);
+#pragma unroll
+                    for (int i = 0; i < TU; i++) P[(G::off(6) + j + i) * 32 + lane] = o[i];
+                }
+            }
 #pragma unroll 1
             for (int b8 = 0; b8 < 8; ++b8) {
                 const int blk = b64 * 8 + b8;
@@ -230,11 +278,15 @@ cudaError_t sc32_occupancy(int m, int fp64, int* bps, int* bytes) { PCB_SC32_DIS
 size_t sc32_yt_bytes(int n, int B, int fp64) { return (size_t)((B + 31) / 32) * 32 * (size_t)n * (fp64 ? 8 : 4); }
 
 // transposes the batch into yt (sc32_yt_bytes) and decodes it
-cudaError_t launch_decode_sc32(const DecodeArgs& a, const uint32_t* info_w, const uint32_t* fv_w, void* yt, int fp64,
-                               int blocks, int sm_count, cudaStream_t st) {
+// bytes of the per-block buffer of the size-256 level
+size_t sc32_scratch_bytes(int blocks, int fp64) { return (size_t)blocks * 256 * 32 * (fp64 ? 8 : 4); }
+
+cudaError_t launch_decode_sc32(const DecodeArgs& a, const uint32_t* info_w, const uint32_t* fv_w, void* yt, void* scratch,
+                               int fp64, int blocks, int sm_count, cudaStream_t st) {
     s32::Args s;
     s.a = a;
     s.yt = yt;
+    s.scratch = scratch;
     s.ntiles = (a.B + 31) / 32;
     for (int i = 0; i < 64; i++) { s.info_w[i] = i < a.n / 32 ? info_w[i] : 0; s.fv_w[i] = i < a.n / 32 ? fv_w[i] : 0; }
     const long long warps = (long long)s.ntiles * (a.n / 32);

@@ -17,7 +17,12 @@ CONFIGS = [
     ("D  SCL-32    N=2048  K=1024 crc=0", 2048, 1024, 0, 32, pb.SCLMINSUM, pb.STRICT, 1 << 14),
     ("E  SCMinsum  N=32768 K=16384 (fp64 strict)", 32768, 16384, 0, 1, pb.SCMINSUM, pb.STRICT, 1 << 13),
 ]
+SCALE = float(os.environ.get("PCB_SWEEP_SCALE", "1"))   # batch-size multiplier
+ONLY = os.environ.get("PCB_SWEEP_ONLY")                # first letters of the configs to run
 for name, N, K, crc, L, dec, prec, B in CONFIGS:
+    if ONLY and name[0] not in ONLY:
+        continue
+    B = max(32, int(B * SCALE))
     code = pb.Code(N, K, crc, 2.0)
     d = pb.Decoder(N, K, crc, L, dec, prec, device=0)
     d.set_code(code.mask, code.sigma)
