@@ -39,7 +39,7 @@ cudaError_t sc32_occupancy(int m, int fp64, int* bps, int* bytes);
 size_t sc32_yt_bytes(int n, int B, int fp64);
 size_t sc32_scratch_bytes(int blocks, int fp64);
 cudaError_t launch_decode_sc32(const DecodeArgs& a, const uint32_t* info_w, const uint32_t* fv_w, void* yt, void* scratch,
-                               int fp64, int blocks, int sm_count, cudaStream_t st);
+                               uint32_t* tmp_bits, int fp64, int blocks, int sm_count, cudaStream_t st);
 // list-8 kernel with four frames per warp (decode_scl8q.cu)
 bool scl8q_supported(int m);
 cudaError_t launch_decode_scl8q(const DecodeArgs& a, const uint32_t* info_w, void* l3_scratch, int* next_quad, int blocks, cudaStream_t st);
@@ -155,6 +155,8 @@ struct pcb_handle {
     int sc32_bps = 0, sc32_smem = 0;
     void* d_yt = nullptr;           // sc32: transposed channel values of the batch
     void* d_sc32_scratch = nullptr; // sc32: size-256 level of every resident block (stays in L2)
+    uint32_t* d_sc32_bits = nullptr; // sc32: packed decisions when the caller wants one int per bit
+    size_t sc32_bits_cap = 0;
     size_t yt_cap = 0;
     void* d_qscratch = nullptr;     // quad kernel: layer-3 arrays of every resident block (stays in L2)
     float* d_y32 = nullptr;         // quad kernel: double channel values converted once per batch
@@ -231,6 +233,14 @@ static int configure(pcb_handle* h) {
     h->sc32 = h->decoder == 2 && sc32_supported(h->m) && !getenv("PCB_FORCE_GENERIC");
     if (h->sc32 && (sc32_occupancy(h->m, h->fp64, &h->sc32_bps, &h->sc32_smem) != cudaSuccess || h->sc32_bps == 0)) {
         cudaGetLastError(); h->sc32 = false;
+    }
+    if (h->sc32) {
+        // every resident warp keeps a 64 KB (fp64) / 32 KB (fp32) level buffer that has to stay in L2:
+        // measured optimum 8 / 14 warps per SM (more warps spill it to DRAM)
+        const int cap = h->fp64 ? 8 : 14;
+        if (h->sc32_bps > cap) h->sc32_bps = cap;
+        const char* benv = getenv("PCB_S_BPS");         // experiment: fewer resident warps per SM
+        if (benv && atoi(benv) > 0 && atoi(benv) < h->sc32_bps) h->sc32_bps = atoi(benv);
     }
     const char* env = getenv("PCB_WARP_SMEM");
     const int budget = env ? atoi(env) : 19200;
@@ -348,7 +358,7 @@ void pcb_destroy(pcb_handle* h) {
         if (h->ev_out[s]) cudaEventDestroy(h->ev_out[s]);
     }
     cudaFree(h->d_ymc); cudaFree(h->d_tx); cudaFree(h->d_dec); cudaFree(h->d_counters);
-    cudaFree(h->d_eu); cudaFree(h->d_ex); cudaFree(h->d_redo); cudaFree(h->d_qscratch); cudaFree(h->d_y32); cudaFree(h->d_yt); cudaFree(h->d_sc32_scratch);
+    cudaFree(h->d_eu); cudaFree(h->d_ex); cudaFree(h->d_redo); cudaFree(h->d_qscratch); cudaFree(h->d_y32); cudaFree(h->d_yt); cudaFree(h->d_sc32_scratch); cudaFree(h->d_sc32_bits);
     cudaFreeHost(h->h_stage[0]); cudaFreeHost(h->h_stage[1]); delete h->narrow;
     if (h->t0) cudaEventDestroy(h->t0);
     if (h->t1) cudaEventDestroy(h->t1);
@@ -486,8 +496,14 @@ static cudaError_t launch(pcb_handle* h, const DecodeArgs& a, cudaStream_t st) {
             cudaError_t e0 = cudaMalloc(&h->d_sc32_scratch, sc32_scratch_bytes(h->sm_count * h->sc32_bps, h->fp64));
             if (e0 != cudaSuccess) return e0;
         }
+        if (!a.sol_bits && h->sc32_bits_cap < (size_t)a.B * (h->n / 32)) {
+            cudaFree(h->d_sc32_bits); h->d_sc32_bits = nullptr; h->sc32_bits_cap = 0;
+            cudaError_t e0 = cudaMalloc(&h->d_sc32_bits, (size_t)a.B * (h->n / 32) * 4);
+            if (e0 != cudaSuccess) return e0;
+            h->sc32_bits_cap = (size_t)a.B * (h->n / 32);
+        }
         h->launches++;                        // transposition + decoder
-        return launch_decode_sc32(a, h->h_info_w.data(), h->h_fv_w.data(), h->d_yt, h->d_sc32_scratch, h->fp64,
+        return launch_decode_sc32(a, h->h_info_w.data(), h->h_fv_w.data(), h->d_yt, h->d_sc32_scratch, h->d_sc32_bits, h->fp64,
                                   h->sm_count * h->sc32_bps, h->sm_count, st);
     }
     int blocks = (a.B + h->wpb - 1) / h->wpb;

@@ -22,6 +22,9 @@
 #include "decode_common.cuh"
 #include "decode_launch.h"
 
+#ifndef PCB_S_FE
+#define PCB_S_FE 5       // log2 of the largest stored layer (64); 5 halves the shared memory per warp and doubles the fused work
+#endif
 #ifndef PCB_S_TOPU
 #define PCB_S_TOPU 8     // outputs of the fused top stage per loop iteration (16 << log2 of it channel loads in flight)
 #endif
@@ -31,17 +34,19 @@ namespace s32 {
 
 template <int M, typename T>
 struct Geo {
-    static constexpr int N = 1 << M, V = M - 6, NW = N / 32;
-    static constexpr int PROWS = 64 + 32 + 16 + 8;
-    __host__ __device__ static constexpr int off(int e) { return e == 6 ? 0 : e == 5 ? 64 : e == 4 ? 96 : 112; }
-    static constexpr int ESTRIDE = 33;     // decisions: word w of lane f at E[w * 33 + f]
-    static constexpr int BYTES = 32 * PROWS * (int)sizeof(T) + 32 * NW * 4 + ESTRIDE * NW * 4;
+    static constexpr int FE = PCB_S_FE, F = 1 << FE;        // largest stored layer
+    static constexpr int N = 1 << M, V = M - FE, NW = N / 32;
+    static constexpr int CL = 8 - FE;                        // levels between the cached size-256 level and size F
+    static constexpr int PROWS = 2 * F - 8;                  // sizes F, F/2, .., 8
+    __host__ __device__ static constexpr int off(int e) { return 2 * F - (2 << e); }
+    static constexpr int BYTES = 32 * PROWS * (int)sizeof(T) + 32 * NW * 4;
 };
 
 struct Args {
     DecodeArgs a;
     const void* yt;          // transposed channel values
     void* scratch;           // n >= 512: 256 rows of 32 lanes per block
+    uint32_t* bits;          // [B][n/32] packed decisions
     int ntiles;
     uint32_t info_w[64];     // n <= 2048
     uint32_t fv_w[64];
@@ -112,52 +117,51 @@ __global__ void __launch_bounds__(32) decode_sc32_kernel(const __grid_constant__
     const int lane = threadIdx.x;
     T* P = reinterpret_cast<T*>(smem_raw);
     uint32_t* H = reinterpret_cast<uint32_t*>(P + G::PROWS * 32);
-    uint32_t* E = H + G::NW * 32;
     constexpr int N = G::N, TU = PCB_S_TOPU;
     T* LB = reinterpret_cast<T*>(S.scratch) + (size_t)blockIdx.x * 256 * 32 + lane;   // size-256 level of this block's tile
 
     for (int tile = blockIdx.x; tile < S.ntiles; tile += gridDim.x) {
         const T* yt = reinterpret_cast<const T*>(S.yt) + (size_t)tile * N * 32 + lane;
+        const int frame = tile * 32 + lane;
+        uint32_t* bits = S.bits + (size_t)min(frame, A.B - 1) * G::NW;   // this lane's packed decisions
         uint32_t w0 = 0, uacc = 0;
 #pragma unroll 1
-        for (int b64 = 0; b64 < N / 64; ++b64) {
+        for (int b64 = 0; b64 < N / G::F; ++b64) {
             // size-64 layer from the channel values through V fused levels; with V > 2 the size-256
             // level is kept in a per-block global buffer (64 KB, stays in L2) and refreshed every
             // fourth block, which cuts the passes over the channel values from n/64 to n/256
+            constexpr int TUB = G::CL > 2 ? (TU >> (G::CL - 2) > 0 ? TU >> (G::CL - 2) : 1) : TU;   // same number of loads in flight
             T o[TU];
-            if constexpr (G::V > 2) {
-                if ((b64 & 3) == 0) {
+            if constexpr (G::V > G::CL) {
+                if ((b64 & ((1 << G::CL) - 1)) == 0) {
 #pragma unroll 1
                     for (int x = 0; x < 256; x += TU) {
-                        fuse<M, 0, G::V - 2, TU, T>(yt, H, lane, b64 >> 2, x, o);
+                        fuse<M, 0, G::V - G::CL, TU, T>(yt, H, lane, b64 >> G::CL, x, o);
 #pragma unroll
                         for (int i = 0; i < TU; i++) LB[(size_t)(x + i) * 32] = o[i];
                     }
                 }
 #pragma unroll 1
-                for (int j = 0; j < 64; j += TU) {
-                    fuse<M, G::V - 2, 2, TU, T>(LB, H, lane, b64 & 3, j, o);
+                for (int j = 0; j < G::F; j += TUB) {
+                    T ob[TUB];
+                    fuse<M, G::V - G::CL, G::CL, TUB, T>(LB, H, lane, b64 & ((1 << G::CL) - 1), j, ob);
 #pragma unroll
-                    for (int i = 0; i < TU; i++) P[(G::off(6) + j + i) * 32 + lane] = o[i];
+                    for (int i = 0; i < TUB; i++) P[(G::off(G::FE) + j + i) * 32 + lane] = ob[i];
                 }
             } else {
 #pragma unroll 1
-                for (int j = 0; j < 64; j += TU) {
+                for (int j = 0; j < G::F; j += TU) {
                     fuse<M, 0, G::V, TU, T>(yt, H, lane, b64, j, o);
 #pragma unroll
-                    for (int i = 0; i < TU; i++) P[(G::off(6) + j + i) * 32 + lane] = o[i];
+                    for (int i = 0; i < TU; i++) P[(G::off(G::FE) + j + i) * 32 + lane] = o[i];
                 }
             }
 #pragma unroll 1
-            for (int b8 = 0; b8 < 8; ++b8) {
-                const int blk = b64 * 8 + b8;
+            for (int b8 = 0; b8 < G::F / 8; ++b8) {
+                const int blk = b64 * (G::F / 8) + b8;
                 int e;
                 if (b8 == 0) {
-                    e = 5;
-                    T* dst = P + G::off(5) * 32 + lane;
-                    const T* src = P + G::off(6) * 32 + lane;
-#pragma unroll 4
-                    for (int j = 0; j < 32; ++j) dst[j * 32] = f_minsum<T>(src[j * 32], src[(j + 32) * 32]);
+                    e = G::FE;                    // the f-layers below start from the size-F layer itself
                 } else {
                     e = 3 + __ffs(b8) - 1;
                     const int Sz = 1 << e;
@@ -184,7 +188,10 @@ __global__ void __launch_bounds__(32) decode_sc32_kernel(const __grid_constant__
                 uint32_t ub;
                 uint32_t Tps = sc_node<8, T>(a, ib, fb, ub);
                 uacc |= ub << (8 * (blk & 3));
-                if ((blk & 3) == 3) { E[(blk >> 2) * G::ESTRIDE + lane] = uacc; uacc = 0; }
+                if ((blk & 3) == 3) {
+                    if (frame < A.B) bits[blk >> 2] = uacc;
+                    uacc = 0;
+                }
                 // partial sums of the subtree that ends here, size 2^d2 (SCLDecoderMinsum.cpp:287-305)
                 const int d2 = min(M, 3 + __ffs(blk + 1) - 1);
                 if (d2 == 3) { w0 = (w0 & ~0xFF00u) | (Tps << 8); continue; }
@@ -203,19 +210,13 @@ __global__ void __launch_bounds__(32) decode_sc32_kernel(const __grid_constant__
                 }
             }
         }
-        __syncwarp();
-        // decisions of the 32 frames, coalesced (sol: one int per bit, the reference's layout)
-#pragma unroll 1
-        for (int f = 0; f < 32; ++f) {
-            const int frame = tile * 32 + f;
-            if (frame >= A.B) break;
-            if (A.sol_bits)
-                for (int w = lane; w < G::NW; w += 32) A.sol_bits[(size_t)frame * G::NW + w] = E[w * G::ESTRIDE + f];
-            if (A.sol)
-                for (int t = lane; t < N; t += 32) A.sol[(size_t)frame * N + t] = (E[(t >> 5) * G::ESTRIDE + f] >> lane) & 1;
-        }
-        __syncwarp();
     }
+}
+
+// packed decisions -> one int per bit (the reference's layout)
+__global__ void __launch_bounds__(256) sc32_expand_kernel(const uint32_t* __restrict__ bits, int* __restrict__ sol, size_t total) {
+    for (size_t t = (size_t)blockIdx.x * 256 + threadIdx.x; t < total; t += (size_t)gridDim.x * 256)
+        sol[t] = (bits[t >> 5] >> (t & 31)) & 1;
 }
 
 // y[B][n] -> yt[tile][x][lane] = y[tile * 32 + lane][bitrev_m(x)], converted to T; the frames behind
@@ -278,15 +279,19 @@ cudaError_t sc32_occupancy(int m, int fp64, int* bps, int* bytes) { PCB_SC32_DIS
 size_t sc32_yt_bytes(int n, int B, int fp64) { return (size_t)((B + 31) / 32) * 32 * (size_t)n * (fp64 ? 8 : 4); }
 
 // transposes the batch into yt (sc32_yt_bytes) and decodes it
+static cudaError_t launch_dispatch(const s32::Args& s, int m, int fp64, int blocks, cudaStream_t st) { PCB_SC32_DISPATCH(launch_m, s, blocks, st) }
+
 // bytes of the per-block buffer of the size-256 level
 size_t sc32_scratch_bytes(int blocks, int fp64) { return (size_t)blocks * 256 * 32 * (fp64 ? 8 : 4); }
 
+// tmp_bits: [B][n/32] words, used when the caller wants one int per bit (a.sol) and no packed output
 cudaError_t launch_decode_sc32(const DecodeArgs& a, const uint32_t* info_w, const uint32_t* fv_w, void* yt, void* scratch,
-                               int fp64, int blocks, int sm_count, cudaStream_t st) {
+                               uint32_t* tmp_bits, int fp64, int blocks, int sm_count, cudaStream_t st) {
     s32::Args s;
     s.a = a;
     s.yt = yt;
     s.scratch = scratch;
+    s.bits = a.sol_bits ? a.sol_bits : tmp_bits;
     s.ntiles = (a.B + 31) / 32;
     for (int i = 0; i < 64; i++) { s.info_w[i] = i < a.n / 32 ? info_w[i] : 0; s.fv_w[i] = i < a.n / 32 ? fv_w[i] : 0; }
     const long long warps = (long long)s.ntiles * (a.n / 32);
@@ -302,8 +307,16 @@ cudaError_t launch_decode_sc32(const DecodeArgs& a, const uint32_t* info_w, cons
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return e;
     if (blocks > s.ntiles) blocks = s.ntiles;
-    const int m = a.m;
-    PCB_SC32_DISPATCH(launch_m, s, blocks, st)
+    e = launch_dispatch(s, a.m, fp64, blocks, st);
+    if (e != cudaSuccess) return e;
+    if (a.sol) {
+        const size_t total = (size_t)a.B * a.n;          // n is a multiple of 32: frame * n / 32 = frame * NW
+        size_t eb = (total + 255) / 256;
+        if (eb > (size_t)sm_count * 32) eb = (size_t)sm_count * 32;
+        s32::sc32_expand_kernel<<<(unsigned)eb, 256, 0, st>>>(s.bits, a.sol, total);
+        e = cudaGetLastError();
+    }
+    return e;
 }
 
 }  // namespace pcb
