@@ -39,7 +39,7 @@ cudaError_t sc32_occupancy(int m, int fp64, int* bps, int* bytes);
 size_t sc32_yt_bytes(int n, int B, int fp64);
 size_t sc32_scratch_bytes(int blocks, int fp64);
 cudaError_t launch_decode_sc32(const DecodeArgs& a, const uint32_t* info_w, const uint32_t* fv_w, void* yt, void* scratch,
-                               uint32_t* tmp_bits, int fp64, int blocks, int sm_count, cudaStream_t st);
+                               uint32_t* tmp_bits, int fp64, int exact, int blocks, int sm_count, cudaStream_t st);
 // list-8 kernel with four frames per warp (decode_scl8q.cu)
 bool scl8q_supported(int m);
 cudaError_t launch_decode_scl8q(const DecodeArgs& a, const uint32_t* info_w, void* l3_scratch, int* next_quad, int blocks, cudaStream_t st);
@@ -230,7 +230,7 @@ static int configure(pcb_handle* h) {
             }
         }
     }
-    h->sc32 = h->decoder == 2 && sc32_supported(h->m) && !getenv("PCB_FORCE_GENERIC");
+    h->sc32 = (h->decoder == 2 || h->decoder == 1) && sc32_supported(h->m) && !getenv("PCB_FORCE_GENERIC");
     if (h->sc32 && (sc32_occupancy(h->m, h->fp64, &h->sc32_bps, &h->sc32_smem) != cudaSuccess || h->sc32_bps == 0)) {
         cudaGetLastError(); h->sc32 = false;
     }
@@ -503,7 +503,7 @@ static cudaError_t launch(pcb_handle* h, const DecodeArgs& a, cudaStream_t st) {
             h->sc32_bits_cap = (size_t)a.B * (h->n / 32);
         }
         h->launches++;                        // transposition + decoder
-        return launch_decode_sc32(a, h->h_info_w.data(), h->h_fv_w.data(), h->d_yt, h->d_sc32_scratch, h->d_sc32_bits, h->fp64,
+        return launch_decode_sc32(a, h->h_info_w.data(), h->h_fv_w.data(), h->d_yt, h->d_sc32_scratch, h->d_sc32_bits, h->fp64, h->decoder == 1,
                                   h->sm_count * h->sc32_bps, h->sm_count, st);
     }
     int blocks = (a.B + h->wpb - 1) / h->wpb;

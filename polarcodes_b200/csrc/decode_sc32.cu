@@ -19,6 +19,8 @@
 //    is the same combine; the SC decoder's decTree2 holds the same bits one int each).
 // Arithmetic is the reference's, operation for operation, in its own precision (double; float when
 // the handle was created with the fp32 precision): bit-exact decisions.
+#include <cfloat>
+
 #include "decode_common.cuh"
 #include "decode_launch.h"
 
@@ -52,13 +54,25 @@ struct Args {
     uint32_t fv_w[64];
 };
 
+// f and g of the decoder: min-sum (SCDecoderMinsum.cpp:14-26) or exact (SCDecoder.cpp:19-36, double only)
+template <bool EXACT, typename T>
+__device__ __forceinline__ T opf(T a, T b) {
+    if constexpr (EXACT) return (T)f_exact((double)a, (double)b);
+    else return f_minsum<T>(a, b);
+}
+template <bool EXACT, typename T>
+__device__ __forceinline__ T opg(T a, T b, int c) {
+    if constexpr (EXACT) return (T)g_exact((double)a, (double)b, c);
+    else return g_minsum<T>(a, b, c);
+}
+
 // Element x of level BASE + LEVELS from the 2^LEVELS elements of level BASE it depends on (level v
 // has n >> v elements, level 0 = channel values; element x of level v pairs x and x + (n >> v) of
 // level v - 1, its partial-sum bit sits at heap bit (n >> v) + x).  All loads first (one basic
 // block: they are in flight together), then the levels in registers; level BASE + l is a g-level
 // iff bit LEVELS - l of `path` is set (warp-uniform), chosen by select so that nothing separates
 // the loads.
-template <int M, int BASE, int LEVELS, int NOUT, typename T>
+template <int M, int BASE, int LEVELS, int NOUT, bool EXACT, typename T>
 __device__ __forceinline__ void fuse(const T* __restrict__ src, const uint32_t* H, int lane, int path, int x0, T (&out)[NOUT]) {
     constexpr int C = 1 << LEVELS, UNIT = ((1 << M) >> BASE) >> LEVELS;
     T v[NOUT][C];
@@ -78,8 +92,12 @@ __device__ __forceinline__ void fuse(const T* __restrict__ src, const uint32_t* 
                 const int xx = x0 + o + UNIT * t;
                 const T a = v[o][t], b = v[o][t + half];
                 const int c = isg ? (int)((H[((S + xx) >> 5) * 32 + lane] >> (xx & 31)) & 1u) : 0;
-                const T gv = g_minsum<T>(a, b, c), fv = f_minsum<T>(a, b);
-                v[o][t] = isg ? gv : fv;
+                if constexpr (EXACT) {       // three transcendentals per f: a (warp-uniform) branch is cheaper than a select
+                    v[o][t] = isg ? opg<EXACT, T>(a, b, c) : opf<EXACT, T>(a, b);
+                } else {
+                    const T gv = opg<EXACT, T>(a, b, c), fv = opf<EXACT, T>(a, b);
+                    v[o][t] = isg ? gv : fv;
+                }
             }
         }
         out[o] = v[o][0];
@@ -88,7 +106,7 @@ __device__ __forceinline__ void fuse(const T* __restrict__ src, const uint32_t* 
 
 // SC decoding of a subtree of S leaves held in registers (SCDecoderMinsum.cpp:32-66): returns its
 // partial sums, the decisions in phase order in ub.  ib/fb: information flags / frozen values.
-template <int S, typename T>
+template <int S, bool EXACT, typename T>
 __device__ __forceinline__ uint32_t sc_node(const T (&a)[S], uint32_t ib, uint32_t fb, uint32_t& ub) {
     if constexpr (S == 1) {
         const uint32_t u = (ib & 1u) ? (a[0] > (T)0 ? 0u : 1u) : (fb & 1u);   // :33-47, an LLR of exactly 0 decodes to 1
@@ -98,18 +116,18 @@ __device__ __forceinline__ uint32_t sc_node(const T (&a)[S], uint32_t ib, uint32
         constexpr int Hf = S / 2;
         T l[Hf], r[Hf];
 #pragma unroll
-        for (int j = 0; j < Hf; j++) l[j] = f_minsum<T>(a[j], a[j + Hf]);
+        for (int j = 0; j < Hf; j++) l[j] = opf<EXACT, T>(a[j], a[j + Hf]);
         uint32_t uL, uR;
-        const uint32_t pL = sc_node<Hf, T>(l, ib, fb, uL);
+        const uint32_t pL = sc_node<Hf, EXACT, T>(l, ib, fb, uL);
 #pragma unroll
-        for (int j = 0; j < Hf; j++) r[j] = g_minsum<T>(a[j], a[j + Hf], (int)((pL >> j) & 1u));
-        const uint32_t pR = sc_node<Hf, T>(r, ib >> Hf, fb >> Hf, uR);
+        for (int j = 0; j < Hf; j++) r[j] = opg<EXACT, T>(a[j], a[j + Hf], (int)((pL >> j) & 1u));
+        const uint32_t pR = sc_node<Hf, EXACT, T>(r, ib >> Hf, fb >> Hf, uR);
         ub = uL | (uR << Hf);
         return (pL ^ pR) | (pR << Hf);
     }
 }
 
-template <int M, typename T>
+template <int M, typename T, bool EXACT>
 __global__ void __launch_bounds__(32) decode_sc32_kernel(const __grid_constant__ Args S) {
     using G = Geo<M, T>;
     const DecodeArgs& A = S.a;
@@ -136,7 +154,7 @@ __global__ void __launch_bounds__(32) decode_sc32_kernel(const __grid_constant__
                 if ((b64 & ((1 << G::CL) - 1)) == 0) {
 #pragma unroll 1
                     for (int x = 0; x < 256; x += TU) {
-                        fuse<M, 0, G::V - G::CL, TU, T>(yt, H, lane, b64 >> G::CL, x, o);
+                        fuse<M, 0, G::V - G::CL, TU, EXACT, T>(yt, H, lane, b64 >> G::CL, x, o);
 #pragma unroll
                         for (int i = 0; i < TU; i++) LB[(size_t)(x + i) * 32] = o[i];
                     }
@@ -144,14 +162,14 @@ __global__ void __launch_bounds__(32) decode_sc32_kernel(const __grid_constant__
 #pragma unroll 1
                 for (int j = 0; j < G::F; j += TUB) {
                     T ob[TUB];
-                    fuse<M, G::V - G::CL, G::CL, TUB, T>(LB, H, lane, b64 & ((1 << G::CL) - 1), j, ob);
+                    fuse<M, G::V - G::CL, G::CL, TUB, EXACT, T>(LB, H, lane, b64 & ((1 << G::CL) - 1), j, ob);
 #pragma unroll
                     for (int i = 0; i < TUB; i++) P[(G::off(G::FE) + j + i) * 32 + lane] = ob[i];
                 }
             } else {
 #pragma unroll 1
                 for (int j = 0; j < G::F; j += TU) {
-                    fuse<M, 0, G::V, TU, T>(yt, H, lane, b64, j, o);
+                    fuse<M, 0, G::V, TU, EXACT, T>(yt, H, lane, b64, j, o);
 #pragma unroll
                     for (int i = 0; i < TU; i++) P[(G::off(G::FE) + j + i) * 32 + lane] = o[i];
                 }
@@ -169,7 +187,7 @@ __global__ void __launch_bounds__(32) decode_sc32_kernel(const __grid_constant__
                     const T* src = P + G::off(e + 1) * 32 + lane;
                     const uint32_t cw = Sz == 32 ? H[32 + lane] : (w0 >> Sz);
 #pragma unroll 4
-                    for (int j = 0; j < Sz; ++j) dst[j * 32] = g_minsum<T>(src[j * 32], src[(j + Sz) * 32], (int)((cw >> j) & 1u));
+                    for (int j = 0; j < Sz; ++j) dst[j * 32] = opg<EXACT, T>(src[j * 32], src[(j + Sz) * 32], (int)((cw >> j) & 1u));
                 }
 #pragma unroll 1
                 for (int ee = e - 1; ee >= 3; --ee) {
@@ -177,7 +195,7 @@ __global__ void __launch_bounds__(32) decode_sc32_kernel(const __grid_constant__
                     T* dst = P + G::off(ee) * 32 + lane;
                     const T* src = P + G::off(ee + 1) * 32 + lane;
 #pragma unroll 4
-                    for (int j = 0; j < Sz; ++j) dst[j * 32] = f_minsum<T>(src[j * 32], src[(j + Sz) * 32]);
+                    for (int j = 0; j < Sz; ++j) dst[j * 32] = opf<EXACT, T>(src[j * 32], src[(j + Sz) * 32]);
                 }
                 // the size-8 subtree in registers
                 T a[8];
@@ -186,7 +204,7 @@ __global__ void __launch_bounds__(32) decode_sc32_kernel(const __grid_constant__
                 const uint32_t ib = (S.info_w[blk >> 2] >> (8 * (blk & 3))) & 0xFFu;
                 const uint32_t fb = (S.fv_w[blk >> 2] >> (8 * (blk & 3))) & 0xFFu;
                 uint32_t ub;
-                uint32_t Tps = sc_node<8, T>(a, ib, fb, ub);
+                uint32_t Tps = sc_node<8, EXACT, T>(a, ib, fb, ub);
                 uacc |= ub << (8 * (blk & 3));
                 if ((blk & 3) == 3) {
                     if (frame < A.B) bits[blk >> 2] = uacc;
@@ -222,7 +240,8 @@ __global__ void __launch_bounds__(256) sc32_expand_kernel(const uint32_t* __rest
 // y[B][n] -> yt[tile][x][lane] = y[tile * 32 + lane][bitrev_m(x)], converted to T; the frames behind
 // B in the last tile repeat frame B - 1.  One warp per (tile, 32 consecutive source indexes).
 template <typename TI, typename T>
-__global__ void __launch_bounds__(128) sc32_transpose_kernel(const TI* __restrict__ y, T* __restrict__ yt, int n, int m, int B, int ntiles) {
+__global__ void __launch_bounds__(128) sc32_transpose_kernel(const TI* __restrict__ y, T* __restrict__ yt, int n, int m, int B, int ntiles,
+                                                             double sigma2 /* > 0: exact SC, LLR = 2y/sigma^2 (SCDecoder.cpp:15-17, :77-79) */) {
     __shared__ T sm[4][32][33];
     const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
     const int chunks = n >> 5;
@@ -231,7 +250,12 @@ __global__ void __launch_bounds__(128) sc32_transpose_kernel(const TI* __restric
         const int tile = (int)(wid / chunks), c = (int)(wid % chunks);
         for (int f = 0; f < 32; f++) {
             const int frame = min(tile * 32 + f, B - 1);
-            sm[wib][f][lane] = (T)y[(size_t)frame * n + c * 32 + lane];
+            T v = (T)y[(size_t)frame * n + c * 32 + lane];
+            if (sigma2 > 0.) {
+                v = (T)((double)v * 2. / sigma2);
+                if (isinf((double)v)) v = (T)DBL_MAX;
+            }
+            sm[wib][f][lane] = v;
         }
         __syncwarp();
         for (int i = 0; i < 32; i++) {
@@ -243,20 +267,28 @@ __global__ void __launch_bounds__(128) sc32_transpose_kernel(const TI* __restric
 }
 
 template <int M, typename T>
-static cudaError_t launch_m(const Args& s, int blocks, cudaStream_t st) {
+static cudaError_t launch_m(const Args& s, int blocks, bool exact, cudaStream_t st) {
     const int smem = Geo<M, T>::BYTES;
-    cudaError_t e = cudaFuncSetAttribute(decode_sc32_kernel<M, T>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    if constexpr (sizeof(T) == 8) {
+        if (exact) {
+            cudaError_t e = cudaFuncSetAttribute(decode_sc32_kernel<M, T, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+            if (e != cudaSuccess) return e;
+            decode_sc32_kernel<M, T, true><<<blocks, 32, smem, st>>>(s);
+            return cudaGetLastError();
+        }
+    }
+    cudaError_t e = cudaFuncSetAttribute(decode_sc32_kernel<M, T, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     if (e != cudaSuccess) return e;
-    decode_sc32_kernel<M, T><<<blocks, 32, smem, st>>>(s);
+    decode_sc32_kernel<M, T, false><<<blocks, 32, smem, st>>>(s);
     return cudaGetLastError();
 }
 template <int M, typename T>
 static cudaError_t occ_m(int* bps, int* bytes) {
     const int smem = Geo<M, T>::BYTES;
     *bytes = smem;
-    cudaError_t e = cudaFuncSetAttribute(decode_sc32_kernel<M, T>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    cudaError_t e = cudaFuncSetAttribute(decode_sc32_kernel<M, T, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     if (e != cudaSuccess) return e;
-    return cudaOccupancyMaxActiveBlocksPerMultiprocessor(bps, decode_sc32_kernel<M, T>, 32, smem);
+    return cudaOccupancyMaxActiveBlocksPerMultiprocessor(bps, decode_sc32_kernel<M, T, false>, 32, smem);
 }
 
 }  // namespace s32
@@ -279,14 +311,16 @@ cudaError_t sc32_occupancy(int m, int fp64, int* bps, int* bytes) { PCB_SC32_DIS
 size_t sc32_yt_bytes(int n, int B, int fp64) { return (size_t)((B + 31) / 32) * 32 * (size_t)n * (fp64 ? 8 : 4); }
 
 // transposes the batch into yt (sc32_yt_bytes) and decodes it
-static cudaError_t launch_dispatch(const s32::Args& s, int m, int fp64, int blocks, cudaStream_t st) { PCB_SC32_DISPATCH(launch_m, s, blocks, st) }
+static cudaError_t launch_dispatch(const s32::Args& s, int m, int fp64, int blocks, bool exact, cudaStream_t st) {
+    PCB_SC32_DISPATCH(launch_m, s, blocks, exact, st)
+}
 
 // bytes of the per-block buffer of the size-256 level
 size_t sc32_scratch_bytes(int blocks, int fp64) { return (size_t)blocks * 256 * 32 * (fp64 ? 8 : 4); }
 
 // tmp_bits: [B][n/32] words, used when the caller wants one int per bit (a.sol) and no packed output
 cudaError_t launch_decode_sc32(const DecodeArgs& a, const uint32_t* info_w, const uint32_t* fv_w, void* yt, void* scratch,
-                               uint32_t* tmp_bits, int fp64, int blocks, int sm_count, cudaStream_t st) {
+                               uint32_t* tmp_bits, int fp64, int exact, int blocks, int sm_count, cudaStream_t st) {
     s32::Args s;
     s.a = a;
     s.yt = yt;
@@ -294,20 +328,21 @@ cudaError_t launch_decode_sc32(const DecodeArgs& a, const uint32_t* info_w, cons
     s.bits = a.sol_bits ? a.sol_bits : tmp_bits;
     s.ntiles = (a.B + 31) / 32;
     for (int i = 0; i < 64; i++) { s.info_w[i] = i < a.n / 32 ? info_w[i] : 0; s.fv_w[i] = i < a.n / 32 ? fv_w[i] : 0; }
+    const double sigma2 = exact ? a.sigma * a.sigma : 0.;
     const long long warps = (long long)s.ntiles * (a.n / 32);
     int tb = (int)((warps + 3) / 4);
     if (tb > sm_count * 32) tb = sm_count * 32;
     if (fp64) {
-        if (a.y_f32) s32::sc32_transpose_kernel<float, double><<<tb, 128, 0, st>>>((const float*)a.y, (double*)yt, a.n, a.m, a.B, s.ntiles);
-        else s32::sc32_transpose_kernel<double, double><<<tb, 128, 0, st>>>((const double*)a.y, (double*)yt, a.n, a.m, a.B, s.ntiles);
+        if (a.y_f32) s32::sc32_transpose_kernel<float, double><<<tb, 128, 0, st>>>((const float*)a.y, (double*)yt, a.n, a.m, a.B, s.ntiles, sigma2);
+        else s32::sc32_transpose_kernel<double, double><<<tb, 128, 0, st>>>((const double*)a.y, (double*)yt, a.n, a.m, a.B, s.ntiles, sigma2);
     } else {
-        if (a.y_f32) s32::sc32_transpose_kernel<float, float><<<tb, 128, 0, st>>>((const float*)a.y, (float*)yt, a.n, a.m, a.B, s.ntiles);
-        else s32::sc32_transpose_kernel<double, float><<<tb, 128, 0, st>>>((const double*)a.y, (float*)yt, a.n, a.m, a.B, s.ntiles);
+        if (a.y_f32) s32::sc32_transpose_kernel<float, float><<<tb, 128, 0, st>>>((const float*)a.y, (float*)yt, a.n, a.m, a.B, s.ntiles, sigma2);
+        else s32::sc32_transpose_kernel<double, float><<<tb, 128, 0, st>>>((const double*)a.y, (float*)yt, a.n, a.m, a.B, s.ntiles, sigma2);
     }
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return e;
     if (blocks > s.ntiles) blocks = s.ntiles;
-    e = launch_dispatch(s, a.m, fp64, blocks, st);
+    e = launch_dispatch(s, a.m, fp64, blocks, exact != 0, st);
     if (e != cudaSuccess) return e;
     if (a.sol) {
         const size_t total = (size_t)a.B * a.n;          // n is a multiple of 32: frame * n / 32 = frame * NW
