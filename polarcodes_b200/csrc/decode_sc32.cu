@@ -9,10 +9,11 @@
 //    (sc32_transpose_kernel, HBM-bound), already gathered through the bit reversal that maps the
 //    reference's adjacent pairing (SCDecoderMinsum.cpp:32-66) onto half-split pairing (DESIGN.md
 //    section 3), so that every load of the decoder is one coalesced row;
-//  * the layers of sizes n/2 .. 128 are never stored: every 64 phases the size-64 layer is
-//    produced straight from the channel values through log2(n) - 6 fused levels (the partial sums
-//    of those levels come from the lane's bit heap);
-//  * sizes 64, 32, 16, 8 live in shared memory as rows of 32 lanes ([row][lane]: conflict-free);
+//  * layers larger than 32 are never stored: every 32 phases the size-32 layer is produced through
+//    fused levels (the partial sums of those levels come from the lane's bit heap); for n >= 512
+//    the size-256 level is kept in a per-block global buffer that stays in L2 and is refreshed
+//    every 256 phases, so the channel values are read n/256 times instead of n/32;
+//  * sizes 32, 16, 8 live in shared memory as rows of 32 lanes ([row][lane]: conflict-free);
 //    a size-8 subtree is decoded in registers by a fully unrolled recursion;
 //  * partial sums are bit-packed per lane: sizes < 32 in one register word (size S at bits
 //    [S, 2S)), larger ones in a shared-memory heap with the same rule (SCLDecoderMinsum.cpp:287-305
@@ -25,7 +26,7 @@
 #include "decode_launch.h"
 
 #ifndef PCB_S_FE
-#define PCB_S_FE 5       // log2 of the largest stored layer (64); 5 halves the shared memory per warp and doubles the fused work
+#define PCB_S_FE 5       // log2 of the largest stored layer: 32 (6: twice the shared memory per warp, half the fused work)
 #endif
 #ifndef PCB_S_TOPU
 #define PCB_S_TOPU 8     // outputs of the fused top stage per loop iteration (16 << log2 of it channel loads in flight)
@@ -145,9 +146,9 @@ __global__ void __launch_bounds__(32) decode_sc32_kernel(const __grid_constant__
         uint32_t w0 = 0, uacc = 0;
 #pragma unroll 1
         for (int b64 = 0; b64 < N / G::F; ++b64) {
-            // size-64 layer from the channel values through V fused levels; with V > 2 the size-256
-            // level is kept in a per-block global buffer (64 KB, stays in L2) and refreshed every
-            // fourth block, which cuts the passes over the channel values from n/64 to n/256
+            // size-F layer from the channel values through V fused levels; when more than CL levels
+            // are fused the size-256 level is kept in a per-block global buffer (64 KB in fp64, stays
+            // in L2) and refreshed every 256 phases: n/256 passes over the channel values, not n/F
             constexpr int TUB = G::CL > 2 ? (TU >> (G::CL - 2) > 0 ? TU >> (G::CL - 2) : 1) : TU;   // same number of loads in flight
             T o[TU];
             if constexpr (G::V > G::CL) {
