@@ -38,6 +38,8 @@ bool sc32_supported(int m);
 cudaError_t sc32_occupancy(int m, int fp64, int* bps, int* bytes);
 size_t sc32_yt_bytes(int n, int B, int fp64);
 size_t sc32_scratch_bytes(int blocks, int fp64);
+bool sc32_is_big(int m);
+size_t sc32_big_scratch_bytes(int n, int blocks, int fp64);
 cudaError_t launch_decode_sc32(const DecodeArgs& a, const uint32_t* info_w, const uint32_t* fv_w, void* yt, void* scratch,
                                uint32_t* tmp_bits, int fp64, int exact, int blocks, int sm_count, cudaStream_t st);
 // list-8 kernel with four frames per warp (decode_scl8q.cu)
@@ -237,7 +239,7 @@ static int configure(pcb_handle* h) {
     if (h->sc32) {
         // every resident warp keeps a 64 KB (fp64) / 32 KB (fp32) level buffer that has to stay in L2:
         // measured optimum 8 / 14 warps per SM (more warps spill it to DRAM)
-        const int cap = h->fp64 ? 8 : 14;
+        const int cap = sc32_is_big(h->m) ? 6 : h->fp64 ? 8 : 14;   // n > 2048: DRAM-bound, each warp owns n * 32 values of scratch
         if (h->sc32_bps > cap) h->sc32_bps = cap;
         const char* benv = getenv("PCB_S_BPS");         // experiment: fewer resident warps per SM
         if (benv && atoi(benv) > 0 && atoi(benv) < h->sc32_bps) h->sc32_bps = atoi(benv);
@@ -493,7 +495,9 @@ static cudaError_t launch(pcb_handle* h, const DecodeArgs& a, cudaStream_t st) {
             h->yt_cap = need;
         }
         if (!h->d_sc32_scratch) {
-            cudaError_t e0 = cudaMalloc(&h->d_sc32_scratch, sc32_scratch_bytes(h->sm_count * h->sc32_bps, h->fp64));
+            const int nb = h->sm_count * h->sc32_bps;
+            cudaError_t e0 = cudaMalloc(&h->d_sc32_scratch, sc32_is_big(h->m) ? sc32_big_scratch_bytes(h->n, nb, h->fp64)
+                                                                              : sc32_scratch_bytes(nb, h->fp64));
             if (e0 != cudaSuccess) return e0;
         }
         if (!a.sol_bits && h->sc32_bits_cap < (size_t)a.B * (h->n / 32)) {

@@ -232,6 +232,113 @@ __global__ void __launch_bounds__(32) decode_sc32_kernel(const __grid_constant__
     }
 }
 
+// ---- n > 2048 (SC min-sum at N = 32768, SURVEY config E): same lane = frame mapping, but every
+// level above size 32 is stored, in a per-block global store LV[level][x][lane] (n - 32 rows of 32
+// lanes), and so is the partial-sum heap (n/32 rows of 32 words).  A level is written once and read
+// once or twice, always as whole coalesced rows; the decoder is DRAM-bound (about 3n values moved
+// per level and frame).  Frozen pattern from global memory (warp-uniform loads).
+struct BigArgs {
+    DecodeArgs a;
+    const void* yt;
+    void* lv;                // per block: (n - 32) * 32 values
+    uint32_t* heap;          // per block: (n / 32) * 32 words
+    uint32_t* bits;
+    int ntiles;
+};
+
+template <typename T, bool EXACT>
+__global__ void __launch_bounds__(32) decode_sc32big_kernel(const __grid_constant__ BigArgs S) {
+    const DecodeArgs& A = S.a;
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    const int lane = threadIdx.x;
+    const int n = A.n, m = A.m, NW = n >> 5, LT = m - 5;       // level LT has 32 elements
+    T* P = reinterpret_cast<T*>(smem_raw);                       // sizes 32, 16, 8: rows 0, 32, 48
+    T* LV = reinterpret_cast<T*>(S.lv) + (size_t)blockIdx.x * (n - 32) * 32 + lane;
+    uint32_t* H = S.heap + (size_t)blockIdx.x * NW * 32 + lane;
+    constexpr int TU = 8;
+    auto lvl = [&](int v) -> T* { return LV + (size_t)(n - (n >> (v - 1))) * 32; };   // level v >= 1, n >> v rows
+
+    for (int tile = blockIdx.x; tile < S.ntiles; tile += gridDim.x) {
+        const T* yt = reinterpret_cast<const T*>(S.yt) + (size_t)tile * n * 32 + lane;
+        const int frame = tile * 32 + lane;
+        uint32_t* bits = S.bits + (size_t)min(frame, A.B - 1) * NW;
+        uint32_t w0 = 0, uacc = 0;
+#pragma unroll 1
+        for (int b32 = 0; b32 < NW; ++b32) {
+            // levels v0 .. LT: the first one is a g-level (except at the very start), the rest f-levels
+            const int v0 = b32 ? LT - (__ffs(b32) - 1) : 1;
+#pragma unroll 1
+            for (int v = v0; v <= LT; ++v) {
+                const int Sz = n >> v;
+                const bool isg = b32 && v == v0;
+                const T* src = v == 1 ? yt : lvl(v - 1);
+                T* dl = v == LT ? P + lane : lvl(v);          // rows of 32 lanes either way
+#pragma unroll 1
+                for (int x = 0; x < Sz; x += TU) {
+                    T a[TU], b[TU];
+#pragma unroll
+                    for (int i = 0; i < TU; i++) { a[i] = src[(size_t)(x + i) * 32]; b[i] = src[(size_t)(x + i + Sz) * 32]; }
+                    const uint32_t cw = isg ? H[(size_t)((Sz + x) >> 5) * 32] >> (x & 31) : 0u;
+#pragma unroll
+                    for (int i = 0; i < TU; i++) {
+                        const T o = isg ? opg<EXACT, T>(a[i], b[i], (int)((cw >> i) & 1u)) : opf<EXACT, T>(a[i], b[i]);
+                        dl[(size_t)(x + i) * 32] = o;
+                    }
+                }
+            }
+#pragma unroll 1
+            for (int b8 = 0; b8 < 4; ++b8) {
+                const int blk = b32 * 4 + b8;
+                int e = 5;
+                if (b8) {
+                    e = 3 + __ffs(b8) - 1;
+                    const int Sz = 1 << e;
+                    T* dst = P + (64 - (2 << e)) * 32 + lane;
+                    const T* src = P + (64 - (4 << e)) * 32 + lane;
+                    const uint32_t cw = w0 >> Sz;
+#pragma unroll 4
+                    for (int j = 0; j < Sz; ++j) dst[j * 32] = opg<EXACT, T>(src[j * 32], src[(j + Sz) * 32], (int)((cw >> j) & 1u));
+                }
+#pragma unroll 1
+                for (int ee = e - 1; ee >= 3; --ee) {
+                    const int Sz = 1 << ee;
+                    T* dst = P + (64 - (2 << ee)) * 32 + lane;
+                    const T* src = P + (64 - (4 << ee)) * 32 + lane;
+#pragma unroll 4
+                    for (int j = 0; j < Sz; ++j) dst[j * 32] = opf<EXACT, T>(src[j * 32], src[(j + Sz) * 32]);
+                }
+                T a[8];
+#pragma unroll
+                for (int j = 0; j < 8; ++j) a[j] = P[(48 + j) * 32 + lane];
+                const uint32_t ib = (__ldg(A.info_mask + b32) >> (8 * b8)) & 0xFFu;
+                const uint32_t fb = (__ldg(A.frozen_val + b32) >> (8 * b8)) & 0xFFu;
+                uint32_t ub;
+                uint32_t Tps = sc_node<8, EXACT, T>(a, ib, fb, ub);
+                uacc |= ub << (8 * b8);
+                if (b8 == 3) {
+                    if (frame < A.B) bits[b32] = uacc;
+                    uacc = 0;
+                }
+                const int d2 = min(m, 3 + __ffs(blk + 1) - 1);
+                if (d2 == 3) { w0 = (w0 & ~0xFF00u) | (Tps << 8); continue; }
+                Tps = (((w0 >> 8) ^ Tps) & 0xFFu) | (Tps << 8);
+                if (d2 == 4) { w0 = (w0 & 0x0000FFFFu) | (Tps << 16); continue; }
+                Tps = (((w0 >> 16) ^ Tps) & 0xFFFFu) | (Tps << 16);
+                if (d2 == m) continue;
+                const int D = 1 << d2;
+                H[(size_t)(2 * D / 32 - 1) * 32] = Tps;
+#pragma unroll 1
+                for (int w = 32; w < D; w <<= 1) {
+                    const int nw = w >> 5;
+#pragma unroll 1
+                    for (int kk = 0; kk < nw; kk++)
+                        H[(size_t)((2 * D - 2 * w) / 32 + kk) * 32] = H[(size_t)(nw + kk) * 32] ^ H[(size_t)((2 * D - w) / 32 + kk) * 32];
+                }
+            }
+        }
+    }
+}
+
 // packed decisions -> one int per bit (the reference's layout)
 __global__ void __launch_bounds__(256) sc32_expand_kernel(const uint32_t* __restrict__ bits, int* __restrict__ sol, size_t total) {
     for (size_t t = (size_t)blockIdx.x * 256 + threadIdx.x; t < total; t += (size_t)gridDim.x * 256)
@@ -294,7 +401,8 @@ static cudaError_t occ_m(int* bps, int* bytes) {
 
 }  // namespace s32
 
-bool sc32_supported(int m) { return m >= 7 && m <= 11; }
+bool sc32_supported(int m) { return m >= 7 && m <= 16; }
+bool sc32_is_big(int m) { return m > 11; }
 
 #define PCB_SC32_DISPATCH(FN, ...)                                                    \
     switch (m) {                                                                     \
@@ -306,7 +414,14 @@ bool sc32_supported(int m) { return m >= 7 && m <= 11; }
     }                                                                                \
     return cudaErrorInvalidValue;
 
-cudaError_t sc32_occupancy(int m, int fp64, int* bps, int* bytes) { PCB_SC32_DISPATCH(occ_m, bps, bytes) }
+cudaError_t sc32_occupancy(int m, int fp64, int* bps, int* bytes) {
+    if (sc32_is_big(m)) {
+        *bytes = 56 * 32 * (fp64 ? 8 : 4);
+        return fp64 ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(bps, s32::decode_sc32big_kernel<double, false>, 32, *bytes)
+                    : cudaOccupancyMaxActiveBlocksPerMultiprocessor(bps, s32::decode_sc32big_kernel<float, false>, 32, *bytes);
+    }
+    PCB_SC32_DISPATCH(occ_m, bps, bytes)
+}
 
 // bytes of the transposed copy of a batch
 size_t sc32_yt_bytes(int n, int B, int fp64) { return (size_t)((B + 31) / 32) * 32 * (size_t)n * (fp64 ? 8 : 4); }
@@ -318,11 +433,16 @@ static cudaError_t launch_dispatch(const s32::Args& s, int m, int fp64, int bloc
 
 // bytes of the per-block buffer of the size-256 level
 size_t sc32_scratch_bytes(int blocks, int fp64) { return (size_t)blocks * 256 * 32 * (fp64 ? 8 : 4); }
+// n > 2048: the per-block level store followed by the per-block heap
+size_t sc32_big_scratch_bytes(int n, int blocks, int fp64) {
+    return (size_t)blocks * ((size_t)(n - 32) * 32 * (fp64 ? 8 : 4) + (size_t)(n / 32) * 32 * 4);
+}
 
 // tmp_bits: [B][n/32] words, used when the caller wants one int per bit (a.sol) and no packed output
 cudaError_t launch_decode_sc32(const DecodeArgs& a, const uint32_t* info_w, const uint32_t* fv_w, void* yt, void* scratch,
                                uint32_t* tmp_bits, int fp64, int exact, int blocks, int sm_count, cudaStream_t st) {
     s32::Args s;
+    const int all_blocks = blocks;     // the scratch was sized for this many
     s.a = a;
     s.yt = yt;
     s.scratch = scratch;
@@ -343,7 +463,22 @@ cudaError_t launch_decode_sc32(const DecodeArgs& a, const uint32_t* info_w, cons
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return e;
     if (blocks > s.ntiles) blocks = s.ntiles;
-    e = launch_dispatch(s, a.m, fp64, blocks, exact != 0, st);
+    if (sc32_is_big(a.m)) {
+        s32::BigArgs g;
+        g.a = a; g.yt = yt; g.bits = s.bits; g.ntiles = s.ntiles;
+        g.lv = scratch;
+        g.heap = reinterpret_cast<uint32_t*>(reinterpret_cast<char*>(scratch) + (size_t)all_blocks * (size_t)(a.n - 32) * 32 * (fp64 ? 8 : 4));
+        const int smem = 56 * 32 * (fp64 ? 8 : 4);
+        if (fp64) {
+            if (exact) s32::decode_sc32big_kernel<double, true><<<blocks, 32, smem, st>>>(g);
+            else s32::decode_sc32big_kernel<double, false><<<blocks, 32, smem, st>>>(g);
+        } else {
+            s32::decode_sc32big_kernel<float, false><<<blocks, 32, smem, st>>>(g);
+        }
+        e = cudaGetLastError();
+    } else {
+        e = launch_dispatch(s, a.m, fp64, blocks, exact != 0, st);
+    }
     if (e != cudaSuccess) return e;
     if (a.sol) {
         const size_t total = (size_t)a.B * a.n;          // n is a multiple of 32: frame * n / 32 = frame * NW
