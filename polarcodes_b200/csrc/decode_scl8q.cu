@@ -48,6 +48,13 @@
 #ifndef PCB_Q_GL4
 #define PCB_Q_GL4 1
 #endif
+// g-layer 1 of the top stage staged with cp.async, two chunks ahead of the arithmetic
+#ifndef PCB_Q_CPA
+#define PCB_Q_CPA 1
+#endif
+#ifndef PCB_Q_CPU
+#define PCB_Q_CPU 4    // unroll factor of the cp.async issue loop
+#endif
 // ... PCB_Q_L2C (layer 2 of an even top-stage event cached in the scratch for the odd event that
 // follows, +32 KB per quad) is off: with it the footprint is 132 MB and half of the scratch
 // stores end up in DRAM (21.6 Mframes/s).  With 10 quads per SM it is a 4 % gain.
@@ -354,8 +361,26 @@ struct Dec {
         }
     }
 
+    // chunk c of the channel values of the four frames (columns 4c .. 4c+3 of each half, 8 rows):
+    // 256 float4 per warp, one cp.async group (an empty one behind the last chunk)
+    __device__ __forceinline__ void stage_chunk(const YT* ybase, int c) {
+        constexpr int Q = G::Q3, CU = PCB_Q_CPU;
+        static_assert(sizeof(YT) == 4, "cp.async staging copies float channel values");
+        if (c < Q / 8) {
+#pragma unroll CU
+            for (int i = 0; i < 8; i++) {    // unit v = i*32 + lane: frame i/2, then t (8), h (2), k4 (4)
+                const int v = i * 32 + lane, w = v & 63, t = w >> 3, h = (w >> 2) & 1, kk = (c & 1) * 4 + (w & 3);
+                const YT* y = ybase + (size_t)min(fbase + (i >> 1), Bm1) * G::N;
+                const unsigned sa = (unsigned)__cvta_generic_to_shared(W + (i >> 1) * G::FRAME_WORDS + G::STAGE_OFF + ((t * 2 + h) * 8 + kk) * 4);
+                asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(sa), "l"(y + 4 * (t * Q + h * (Q / 2) + (c >> 1) * 8 + kk)) : "memory");
+            }
+        }
+        asm volatile("cp.async.commit_group;" ::: "memory");
+    }
+
     __device__ __forceinline__ void top_gl3(int ev, const YT* ybase, const int (&fr)[4]) {
-        constexpr int E = G::N / 8, N4 = G::N / 4, Q = G::Q3, NR = Q / 16, TU = PCB_Q_TOPU, SG = PCB_Q_STG;
+        constexpr int E = G::N / 8, N4 = G::N / 4, Q = G::Q3, NR = Q / 16, TU = PCB_Q_TOPU;
+        [[maybe_unused]] constexpr int SG = PCB_Q_STG;
         const bool g1 = ev & 4, g2 = ev & 2, g3 = ev & 1;
         const float* R = P + G::STAGE_OFF;
         float* dst4 = G::GL4 ? nullptr : arr(4, p);
@@ -397,8 +422,18 @@ struct Dec {
             stage_l1f(ybase);
             __syncwarp();
         }
+#if PCB_Q_CPA
+        // g-layer 1: the channel values go straight from L2 to the staging area with cp.async, in
+        // chunks of 4 columns x 2 halves x 8 rows per frame (chunk c = columns c*4 .. c*4+3); chunk
+        // c+2 is in flight while chunk c is consumed, so the L2 latency hides behind the arithmetic.
+        if (g1) {
+#pragma unroll 1
+            for (int c = 0; c < 2; c++) stage_chunk(ybase, c);
+        }
+#endif
 #pragma unroll 1
         for (int r = 0; r < NR; r++) {
+#if !PCB_Q_CPA
             if (g1) {
                 if (r) __syncwarp();
 #pragma unroll SG
@@ -410,6 +445,7 @@ struct Dec {
                 }
                 __syncwarp();
             }
+#endif
             uint32_t c1[4][2], c2[2][2], c3[2];
 #pragma unroll
             for (int h = 0; h < 2; h++) {
@@ -419,8 +455,19 @@ struct Dec {
                 for (int t = 0; t < 4; t++) c1[t][h] = g1 ? cword(1, t * E, w32) : 0u;
                 c2[0][h] = g2 ? cword(2, 0, w32) : 0u; c2[1][h] = g2 ? cword(2, E, w32) : 0u;
             }
+#if PCB_Q_CPA
+#pragma unroll 1
+            for (int hf = 0; hf < 2; hf++) {
+            if (g1) {
+                asm volatile("cp.async.wait_group 1;" ::: "memory");
+                __syncwarp();
+            }
+#pragma unroll TU
+            for (int kk = 4 * hf; kk < 4 * hf + 4; kk++) {
+#else
 #pragma unroll TU
             for (int kk = 0; kk < 8; kk++) {
+#endif
                 float4 o[2];
 #pragma unroll
                 for (int h = 0; h < 2; h++) {
@@ -451,6 +498,13 @@ struct Dec {
                 if constexpr (G::GL4) L4[(r * 8 + kk) * 8 + p] = ff4(o[0], o[1]);
                 else *reinterpret_cast<float4*>(dst4 + 4 * (r * 8 + kk)) = ff4(o[0], o[1]);
             }
+#if PCB_Q_CPA
+            if (g1) {
+                __syncwarp();                    // the chunk is consumed: its slots take chunk c + 2
+                stage_chunk(ybase, 2 * r + hf + 2);
+            }
+            }
+#endif
         }
         pidx = (pidx & ~(7u << 24)) | ((uint32_t)p << 24);   // the cached layer 2 is this slot's own
         __syncwarp();                            // the staging area is overwritten by layer 5 next
