@@ -42,11 +42,12 @@ bool sc32_is_big(int m);
 size_t sc32_big_scratch_bytes(int n, int blocks, int fp64);
 cudaError_t launch_decode_sc32(const DecodeArgs& a, const uint32_t* info_w, const uint32_t* fv_w, void* yt, void* scratch,
                                uint32_t* tmp_bits, int fp64, int exact, int blocks, int sm_count, cudaStream_t st);
-// list-8 kernel with four frames per warp (decode_scl8q.cu)
-bool scl8q_supported(int m);
-cudaError_t launch_decode_scl8q(const DecodeArgs& a, const uint32_t* info_w, void* l3_scratch, int* next_quad, int blocks, cudaStream_t st);
-size_t scl8q_scratch_per_block(int m);
-cudaError_t scl8q_occupancy(int m, int* bps, int* warp_bytes);
+// lane-per-path list kernel, 32 / L frames per warp (decode_scl8q.cu): L = 8 and L = 32
+bool scl8q_supported(int m, int L);
+int scl8q_frames_per_warp(int L);
+cudaError_t launch_decode_scl8q(const DecodeArgs& a, int L, const uint32_t* info_w, void* l3_scratch, int* next_quad, int blocks, cudaStream_t st);
+size_t scl8q_scratch_per_block(int m, int L);
+cudaError_t scl8q_occupancy(int m, int L, int* bps, int* warp_bytes);
 }  // namespace pcb
 
 using namespace pcb;
@@ -214,23 +215,28 @@ static int ensure_device(pcb_handle* h) {
 // per-warp slice fits the budget, then the warps-per-block with the best occupancy.
 static int configure(pcb_handle* h) {
     const char* wenv = getenv("PCB_WPB");
-    h->fast8 = h->decoder == 3 && h->L == 8 && scl8_supported(h->m) && !getenv("PCB_FORCE_GENERIC");
+    const bool l8 = h->L == 8 && scl8_supported(h->m);
+    h->fast8 = h->decoder == 3 && (l8 || scl8q_supported(h->m, h->L)) && !getenv("PCB_FORCE_GENERIC");
+    h->quad = false;
     if (h->fast8) {
         int bps = 0, wb = 0;   // one warp (= one frame) per block
-        if (scl8_occupancy(h->m, &bps, &wb) != cudaSuccess || bps == 0) { cudaGetLastError(); return fail(PCB_EINVAL, "list-8 kernel does not fit one SM"); }
-        h->f_bps = bps; h->f_warp_smem = wb;
-        // default: four frames per warp (decode_scl8q.cu); PCB_SCL8_VARIANT=warp selects the
-        // one-frame-per-warp kernel (decode_scl8.cu)
+        if (l8) {
+            if (scl8_occupancy(h->m, &bps, &wb) != cudaSuccess || bps == 0) { cudaGetLastError(); return fail(PCB_EINVAL, "list-8 kernel does not fit one SM"); }
+            h->f_bps = bps; h->f_warp_smem = wb;
+        }
+        // default: one lane per path, 32 / L frames per warp (decode_scl8q.cu); for L = 8
+        // PCB_SCL8_VARIANT=warp selects the one-frame-per-warp kernel (decode_scl8.cu)
         const char* venv = getenv("PCB_SCL8_VARIANT");
-        h->quad = scl8q_supported(h->m) && !(venv && !strcmp(venv, "warp"));
+        h->quad = scl8q_supported(h->m, h->L) && !(l8 && venv && !strcmp(venv, "warp"));
         if (h->quad) {
-            if (scl8q_occupancy(h->m, &bps, &wb) != cudaSuccess || bps == 0) { cudaGetLastError(); h->quad = false; }
+            if (scl8q_occupancy(h->m, h->L, &bps, &wb) != cudaSuccess || bps == 0) { cudaGetLastError(); h->quad = false; }
             else {
                 const char* benv = getenv("PCB_Q_BPS");     // experiment: fewer resident quads per SM
                 if (benv && atoi(benv) > 0 && atoi(benv) < bps) bps = atoi(benv);
                 h->f_bps = bps; h->f_warp_smem = wb;
             }
         }
+        if (!h->quad && !l8) h->fast8 = false;
     }
     h->sc32 = (h->decoder == 2 || h->decoder == 1) && sc32_supported(h->m) && !getenv("PCB_FORCE_GENERIC");
     if (h->sc32 && (sc32_occupancy(h->m, h->fp64, &h->sc32_bps, &h->sc32_smem) != cudaSuccess || h->sc32_bps == 0)) {
@@ -471,13 +477,14 @@ static cudaError_t launch(pcb_handle* h, const DecodeArgs& a, cudaStream_t st) {
             if (e != cudaSuccess) return e;
             h->launches++;
             f.y = y32; f.y_f32 = 1;
-            const int nq = (a.B + 3) / 4;
-            const size_t spb = scl8q_scratch_per_block(h->m);
+            const int fpw = scl8q_frames_per_warp(h->L);
+            const int nq = (a.B + fpw - 1) / fpw;
+            const size_t spb = scl8q_scratch_per_block(h->m, h->L);
             if (spb && !h->d_qscratch) {
                 cudaError_t e1 = cudaMalloc(&h->d_qscratch, spb * (size_t)fast_blocks(h));
                 if (e1 != cudaSuccess) return e1;
             }
-            e = launch_decode_scl8q(f, h->h_info_w.data(), h->d_qscratch, h->d_redo + 1, nq < fast_blocks(h) ? nq : fast_blocks(h), st);
+            e = launch_decode_scl8q(f, h->L, h->h_info_w.data(), h->d_qscratch, h->d_redo + 1, nq < fast_blocks(h) ? nq : fast_blocks(h), st);
         } else {
             e = launch_decode_scl8(f, h->h_info_w.data(), h->h_fv_w.data(), a.B < fast_blocks(h) ? a.B : fast_blocks(h), st);
         }
@@ -730,7 +737,7 @@ static size_t mc_batch(pcb_handle* h) {
     size_t b = ((size_t)256 << 20) / ((size_t)h->n * 4);
     const char* env = getenv("PCB_MC_BATCH");
     if (env) b = (size_t)atol(env);
-    const size_t minb = h->fast8 ? (size_t)fast_blocks(h) * (h->quad ? 4 : 1) : (size_t)max_blocks(h) * h->wpb;
+    const size_t minb = h->fast8 ? (size_t)fast_blocks(h) * (h->quad ? scl8q_frames_per_warp(h->L) : 1) : (size_t)max_blocks(h) * h->wpb;
     if (b < minb) b = minb;
     return b;
 }

@@ -55,12 +55,8 @@
 #ifndef PCB_Q_CPU
 #define PCB_Q_CPU 4    // unroll factor of the cp.async issue loop
 #endif
-// ... PCB_Q_L2C (layer 2 of an even top-stage event cached in the scratch for the odd event that
-// follows, +32 KB per quad) is off: with it the footprint is 132 MB and half of the scratch
-// stores end up in DRAM (21.6 Mframes/s).  With 10 quads per SM it is a 4 % gain.
-#ifndef PCB_Q_L2C
-#define PCB_Q_L2C 0
-#endif
+// ... (caching layer 2 of an even top-stage event in the scratch for the odd event that follows,
+// +32 KB per quad, was a 4 % gain with 10 quads per SM and a 15 % loss with 16: removed.)
 
 namespace pcb {
 
@@ -68,8 +64,12 @@ namespace q8 {
 
 constexpr unsigned FULL = 0xffffffffu;
 
-template <int M>
+template <int M, int LL>
 struct Geo {
+    static_assert(LL == 4 || LL == 8 || LL == 16 || LL == 32, "list size");
+    static constexpr int FPW = 32 / LL;     // frames per warp: lane = frame * LL + path slot
+    static constexpr int LB = LL == 4 ? 2 : LL == 8 ? 3 : LL == 16 ? 4 : 5;   // bits of a slot number
+    static constexpr unsigned GM = LL == 32 ? 0xffffffffu : (1u << LL) - 1;   // lane mask of one frame (shifted down)
     static constexpr int N = 1 << M;
     static constexpr int LTOP = 3;          // first stored LLR layer (size N/8)
     static constexpr int LBOT = M - 3;      // last stored LLR layer (size 8); sizes 4,2,1 are registers
@@ -86,24 +86,29 @@ struct Geo {
     __host__ __device__ static constexpr int stride(int lam) { return size(lam) + 4; }
     __host__ __device__ static constexpr int off(int lam) {
         int o = 0;
-        for (int l = LS; l < lam; ++l) o += 8 * stride(l);
+        for (int l = LS; l < lam; ++l) o += LL * stride(l);
         return o;
     }
     static constexpr int PFLOATS = off(LBOT + 1);
     // staging area = the layers below the one the top stage writes (dead at those phases)
     static constexpr int STAGE_OFF = GL4 ? 0 : off(LS + 1);
     static_assert(PFLOATS - STAGE_OFF >= (GL3 ? N / 2 : N), "staging area too small");
-    static constexpr int XW = 8 * HS;                        // final codeword estimates (alias the LLR region)
-    static_assert(XW + 8 * NW <= PFLOATS, "final-stage scratch does not fit the LLR region");
-    static constexpr int FRAME_WORDS = PFLOATS + 8 * HS + 16;   // LLRs, heaps, 16 candidate keys
+    static constexpr int XW = LL * HS;                       // final codeword estimates (alias the LLR region)
+    static_assert(XW + LL * NW <= PFLOATS, "final-stage scratch does not fit the LLR region");
+    static constexpr int FRAME_WORDS = PFLOATS + LL * HS + 2 * LL;   // LLRs, heaps, 2L candidate keys
     static constexpr int OFF_H = PFLOATS;
-    static constexpr int OFF_KEYS = PFLOATS + 8 * HS;
-    static constexpr int TOTAL = 4 * FRAME_WORDS * 4;
-    static constexpr int L3_BLOCK_FLOAT4 = GL3 ? 4 * Q3 * 8 : 0;   // global scratch per block: [frame][k][slot] float4
-    static constexpr int L4_BLOCK_FLOAT4 = GL4 ? 4 * (Q3 / 2) * 8 : 0;
-    // layer 2 of the even top-stage events, re-used by the following odd event: [frame][k (2*Q3)][slot]
-    static constexpr int L2C_BLOCK_FLOAT4 = (GL3 && PCB_Q_L2C) ? 4 * 2 * Q3 * 8 : 0;
-    static constexpr int SCRATCH_BLOCK_FLOAT4 = L3_BLOCK_FLOAT4 + L4_BLOCK_FLOAT4 + L2C_BLOCK_FLOAT4;
+    static constexpr int OFF_KEYS = PFLOATS + LL * HS;
+    static constexpr int TOTAL = FPW * FRAME_WORDS * 4;
+    static constexpr int L3_BLOCK_FLOAT4 = GL3 ? FPW * Q3 * LL : 0;   // global scratch per block: [frame][k][slot] float4
+    static constexpr int L4_BLOCK_FLOAT4 = GL4 ? FPW * (Q3 / 2) * LL : 0;
+    static constexpr int SCRATCH_BLOCK_FLOAT4 = L3_BLOCK_FLOAT4 + L4_BLOCK_FLOAT4;
+    // one slot number per layer: LLR layers LTOP..LBOT in pidx, partial-sum layers 1..M-5 in cidx
+    static_assert(LB * (M - 5) <= 32, "slot fields do not fit one word");
+    __host__ __device__ static constexpr unsigned rep_field() {   // 1 at the lowest bit of every field
+        unsigned r = 0;
+        for (int i = 0; i < M - 5; ++i) r |= 1u << (LB * i);
+        return r;
+    }
     static_assert((FRAME_WORDS * 4) % 16 == 0 && (OFF_H * 4) % 16 == 0 && (OFF_KEYS * 4) % 16 == 0, "alignment");
 };
 
@@ -157,10 +162,12 @@ __device__ __forceinline__ float4 gs4(float4 a, float4 b, uint32_t cw, int pos) 
 // max over the 8 lanes of a frame: four full-warp reductions (one uniform-datapath CREDUX each,
 // ~49 cycles for the four) instead of a three-level shuffle butterfly (~110 cycles); a
 // __reduce_*_sync with an 8-lane member mask compiles to a divergent software loop (~310 cycles).
+template <int FPW>
 __device__ __forceinline__ unsigned group_max(unsigned x, int fme) {
+    if constexpr (FPW == 1) return __reduce_max_sync(FULL, x);
     unsigned r = 0;
 #pragma unroll
-    for (int g = 0; g < 4; g++) {
+    for (int g = 0; g < FPW; g++) {
         const unsigned v = __reduce_max_sync(FULL, fme == g ? x : 0u);
         if (fme == g) r = v;
     }
@@ -171,6 +178,7 @@ __device__ __forceinline__ unsigned group_max(unsigned x, int fme) {
 // lane per path: T holds the last 32 bits; the destination layer m-d2 sits at heap words
 // [D/32, 2D/32) of this slot; layer 0 (the final codeword estimate, written at the very last
 // phase) goes to the then-dead LLR region instead.  Out of line: taken once per four subtrees.
+template <int LB>
 __device__ __noinline__ uint32_t heap_combine(uint32_t* Pw, uint32_t* H, int p, uint32_t cidx, int d2, uint32_t T, int m) {
     const int D = 1 << d2, NW = 1 << (m - 5), HS = NW + 1;
     uint32_t* hp = (d2 == m) ? (Pw + p * HS - NW) : (H + p * HS);
@@ -179,15 +187,15 @@ __device__ __noinline__ uint32_t heap_combine(uint32_t* Pw, uint32_t* H, int p, 
 #pragma unroll 1
     for (int w = 32; w < D; w <<= 1) {
         const int lgw = 31 - __clz(w), layc = m - lgw, nw = w >> 5;
-        const uint32_t* cs = H + ((cidx >> (3 * (layc - 1))) & 7) * HS + nw;
+        const uint32_t* cs = H + ((cidx >> (LB * (layc - 1))) & ((1u << LB) - 1)) * HS + nw;
 #pragma unroll 1
         for (int kk = 0; kk < nw; kk++)
             hp[(2 * D - 2 * w) / 32 + kk] = cs[kk] ^ hp[(2 * D - w) / 32 + kk];
     }
     __syncwarp();
     if (d2 < m) {
-        const int sh = 3 * (m - d2 - 1);
-        cidx = (cidx & ~(7u << sh)) | ((uint32_t)p << sh);
+        const int sh = LB * (m - d2 - 1);
+        cidx = (cidx & ~(((1u << LB) - 1) << sh)) | ((uint32_t)p << sh);
     }
     return cidx;
 }
@@ -208,12 +216,14 @@ struct PathState {
 // both candidates of q0, with a strict gap on either side of the cut (no tie for pass 2 to
 // break): p0 is killed and its slot receives the clone of q0 (:372-389).  Returns false (and the
 // caller runs the full select) unless every frame of the warp is in one of the two cases.
+template <int LL>
 __device__ __forceinline__ bool single_swap(const PathState& s, float A0, int lane, uint32_t& r) {
-    const int gsh = lane & 24;
+    constexpr unsigned GM = LL == 32 ? 0xffffffffu : (1u << LL) - 1;
+    const int gsh = lane & (32 - LL);
     const uint32_t lo = __float_as_uint(s.met), hi = __float_as_uint(s.met + fabsf(A0));
-    const unsigned gB = (__ballot_sync(FULL, !(hi > s.maxmet)) >> gsh) & 0xFFu;
-    const unsigned gE = (__ballot_sync(FULL, lo == s.maxmet) >> gsh) & 0xFFu;
-    const unsigned gS = (__ballot_sync(FULL, hi == s.maxmet) >> gsh) & 0xFFu;
+    const unsigned gB = (__ballot_sync(FULL, !(hi > s.maxmet)) >> gsh) & GM;
+    const unsigned gE = (__ballot_sync(FULL, lo == s.maxmet) >> gsh) & GM;
+    const unsigned gS = (__ballot_sync(FULL, hi == s.maxmet) >> gsh) & GM;
     const bool cond = gB == 0u || (__popc(gB) == 1 && __popc(gE) == 1 && gS == 0u);
     if (!__all_sync(FULL, cond)) return false;
     const int q0 = gsh + __ffs(gB) - 1, p0 = gsh + __ffs(gE) - 1;
@@ -224,17 +234,20 @@ __device__ __forceinline__ bool single_swap(const PathState& s, float A0, int la
 
 // continuePaths_UnfrozenBit (SCLDecoderMinsum.cpp:315-400) without the fast exit, for the four
 // frames of the warp at once (every step is confined to the 8-lane group of a frame).
+template <int LL>
 __device__ __noinline__ PathState fork_slow(PathState s, float A0, int lane, int ninfo, uint32_t* keys) {
-    const int p = lane & 7, gsh = lane & 24;
+    constexpr int FPW = 32 / LL, LB = LL == 4 ? 2 : LL == 8 ? 3 : LL == 16 ? 4 : 5;
+    constexpr unsigned GM = LL == 32 ? 0xffffffffu : (1u << LL) - 1;
+    const int p = lane & (LL - 1), gsh = lane & (32 - LL);
     const float pf0 = s.met + fmaxf(-A0, 0.f);   // pen(llr,0) = |llr| iff llr < 0   (:308-313)
     const float pf1 = s.met + fmaxf(A0, 0.f);    // pen(llr,1) = |llr| iff llr > 0
     uint32_t r;
-    if (ninfo < 3) {
-        // growth (:329-341): live slots are [8-nact, 8); parent q clones into slot 2*pbase-1-q
-        const int nact = 1 << ninfo, pbase = 8 - nact;
+    if (ninfo < LB) {
+        // growth (:329-341): live slots are [L-nact, L); parent q clones into slot 2*pbase-1-q
+        const int nact = 1 << ninfo, pbase = LL - nact;
         const bool take = p >= pbase - nact && p < pbase;
         r = take ? (3u | ((uint32_t)(gsh + 2 * pbase - 1 - p) << 2)) : ((uint32_t)lane << 2);
-    } else if (single_swap(s, A0, lane, r)) {
+    } else if (single_swap<LL>(s, A0, lane, r)) {
     } else {
         // stable rank of both candidates among the 16 of the frame; keys are stored complemented:
         // key < kc  <=>  carry-out of (kc + ~key)
@@ -243,41 +256,46 @@ __device__ __noinline__ PathState fork_slow(PathState s, float A0, int lane, int
         const uint32_t k0 = __float_as_uint(pf0), k1 = __float_as_uint(pf1);
         int c0 = 0, c1 = 0, d0 = 0, d1 = 0;   // two accumulators per candidate: shorter dependent chains
 #define PCB_LT(c, x, k) asm("{ .reg .u32 t; add.cc.u32 t, %1, %2; addc.u32 %0, %0, 0; }" : "+r"(c) : "r"(x), "r"(k));
-#pragma unroll
-        for (int q = 0; q < 4; q++) {
+#pragma unroll 4
+        for (int q = 0; q < LL / 2; q++) {
             const uint4 kk = *reinterpret_cast<const uint4*>(keys + 4 * q);
             PCB_LT(c0, kk.x, k0) PCB_LT(c1, kk.x, k1) PCB_LT(d0, kk.y, k0) PCB_LT(d1, kk.y, k1)
             PCB_LT(c0, kk.z, k0) PCB_LT(c1, kk.z, k1) PCB_LT(d0, kk.w, k0) PCB_LT(d1, kk.w, k1)
         }
 #undef PCB_LT
-        bool keep0 = c0 + d0 < 8, keep1 = c1 + d1 < 8;
-        unsigned b0 = (__ballot_sync(FULL, keep0) >> gsh) & 0xFFu, b1 = (__ballot_sync(FULL, keep1) >> gsh) & 0xFFu;
-        const bool tie = __popc(b0) + __popc(b1) != 8;        // a tie straddles the median (:362-371)
+        bool keep0 = c0 + d0 < LL, keep1 = c1 + d1 < LL;
+        unsigned b0 = (__ballot_sync(FULL, keep0) >> gsh) & GM, b1 = (__ballot_sync(FULL, keep1) >> gsh) & GM;
+        const bool tie = __popc(b0) + __popc(b1) != LL;        // a tie straddles the median (:362-371)
         if (__any_sync(FULL, tie)) {
             const unsigned top = max(keep0 ? k0 : 0u, keep1 ? k1 : 0u);
-            const unsigned tkey = group_max(top, lane >> 3);
-            const unsigned t0 = (__ballot_sync(FULL, keep0 && k0 == tkey) >> gsh) & 0xFFu;
-            const unsigned t1 = (__ballot_sync(FULL, keep1 && k1 == tkey) >> gsh) & 0xFFu;
-            const int need = 8 - (__popc(b0) + __popc(b1) - __popc(t0) - __popc(t1));
+            const unsigned tkey = group_max<FPW>(top, lane / LL);
+            const unsigned t0 = (__ballot_sync(FULL, keep0 && k0 == tkey) >> gsh) & GM;
+            const unsigned t1 = (__ballot_sync(FULL, keep1 && k1 == tkey) >> gsh) & GM;
+            const int need = LL - (__popc(b0) + __popc(b1) - __popc(t0) - __popc(t1));
             const unsigned lt = (1u << p) - 1;
             const int before0 = __popc(t0 & lt) + __popc(t1 & lt), before1 = before0 + ((t0 >> p) & 1);
             if (tie) {
                 keep0 = keep0 && (k0 < tkey || before0 < need);
                 keep1 = keep1 && (k1 < tkey || before1 < need);
             }
-            b0 = (__ballot_sync(FULL, keep0) >> gsh) & 0xFFu;
-            b1 = (__ballot_sync(FULL, keep1) >> gsh) & 0xFFu;
+            b0 = (__ballot_sync(FULL, keep0) >> gsh) & GM;
+            b1 = (__ballot_sync(FULL, keep1) >> gsh) & GM;
         }
-        const unsigned nonem = ~(b0 | b1) & 0xFFu, bothm = b0 & b1;
+        const unsigned nonem = ~(b0 | b1) & GM, bothm = b0 & b1;
         if ((nonem >> p) & 1) {
             // killed slots are pushed ascending (:372-376) and popped by the cloning parents in
             // ascending order (:382-389): the j-th killed slot receives the clone of the j-th
             // HIGHEST parent
             const int j = __popc(nonem & ((1u << p) - 1));
             unsigned bm = bothm;
-            if (j > 0) bm &= ~(0x80000000u >> __clz(bm));
-            if (j > 1) bm &= ~(0x80000000u >> __clz(bm));
-            if (j > 2) bm &= ~(0x80000000u >> __clz(bm));
+            if constexpr (LL <= 8) {       // at most L/2 slots are killed
+                if (j > 0) bm &= ~(0x80000000u >> __clz(bm));
+                if (j > 1) bm &= ~(0x80000000u >> __clz(bm));
+                if (j > 2) bm &= ~(0x80000000u >> __clz(bm));
+            } else {
+#pragma unroll 1
+                for (int jj = 0; jj < j; jj++) bm &= ~(0x80000000u >> __clz(bm));
+            }
             r = 3u | ((uint32_t)(gsh + 31 - __clz(bm)) << 2);
         } else {
             r = (keep0 ? 0u : 1u) | ((uint32_t)lane << 2);
@@ -299,13 +317,14 @@ __device__ __noinline__ PathState fork_slow(PathState s, float A0, int lane, int
         s.r4 = make_float4(x4, y4, z4, w4); s.r2_0 = a2; s.r2_1 = b2;
     }
     s.r = r;
-    s.maxmet = group_max(__float_as_uint(s.met), lane >> 3);
+    s.maxmet = group_max<FPW>(__float_as_uint(s.met), lane / LL);
     return s;
 }
 
-template <int M, typename YT>
+template <int M, int LL, typename YT>
 struct Dec {
-    using G = Geo<M>;
+    using G = Geo<M, LL>;
+    static constexpr int FPW = G::FPW, LB = G::LB;
     int lane, p;
     int fbase, Bm1;    // first frame of the quad, last frame of the batch (tail quads repeat it)
     float* P;          // this frame's LLR layers
@@ -314,7 +333,6 @@ struct Dec {
     float* W;          // the warp's whole slice (4 frames)
     float4* L3;        // GL3: this frame's layer-3 arrays in global memory, element (k, slot) at L3[k*8 + slot]
     float4* L4;        // GL4: same for layer 4
-    float4* L2c;       // GL3: layer 2 as computed at the last even top-stage event
     float met;
     uint32_t maxmet;   // bit pattern of the largest metric of this frame (valid whenever the next phase is an information bit)
     uint32_t pidx, cidx, w0;
@@ -325,8 +343,8 @@ struct Dec {
     int ninfo;         // information bits seen so far (warp-uniform): the list is full from the 4th on
 
     __device__ __forceinline__ float* arr(int lam, int slot) const { return P + G::off(lam) + slot * G::stride(lam); }
-    __device__ __forceinline__ int pfield(int lam) const { return (pidx >> (3 * (lam - G::LTOP))) & 7; }
-    __device__ __forceinline__ int cfield(int lam) const { return (cidx >> (3 * (lam - 1))) & 7; }
+    __device__ __forceinline__ int pfield(int lam) const { return (pidx >> (LB * (lam - G::LTOP))) & (LL - 1); }
+    __device__ __forceinline__ int cfield(int lam) const { return (cidx >> (LB * (lam - 1))) & (LL - 1); }
     // word w32 (32 elements each) of partial-sum layer `lam` (size >= 32), elements from `base`
     __device__ __forceinline__ uint32_t cword(int lam, int base, int w32) const {
         return H[cfield(lam) * G::HS + (G::size(lam) >> 5) + (base >> 5) + w32];
@@ -352,7 +370,7 @@ struct Dec {
     __device__ __forceinline__ void stage_l1f(const YT* ybase) {
         constexpr int N4 = G::N / 4, SU = PCB_Q_STU;
 #pragma unroll 1
-        for (int f = 0; f < 4; f++) {
+        for (int f = 0; f < FPW; f++) {
             const YT* y = ybase + (size_t)min(fbase + f, Bm1) * G::N;
             float* Rf = W + f * G::FRAME_WORDS + G::STAGE_OFF;
 #pragma unroll SU
@@ -362,13 +380,13 @@ struct Dec {
     }
 
     // chunk c of the channel values of the four frames (columns 4c .. 4c+3 of each half, 8 rows):
-    // 256 float4 per warp, one cp.async group (an empty one behind the last chunk)
+    // 64 float4 per frame, one cp.async group (an empty one behind the last chunk)
     __device__ __forceinline__ void stage_chunk(const YT* ybase, int c) {
         constexpr int Q = G::Q3, CU = PCB_Q_CPU;
         static_assert(sizeof(YT) == 4, "cp.async staging copies float channel values");
         if (c < Q / 8) {
 #pragma unroll CU
-            for (int i = 0; i < 8; i++) {    // unit v = i*32 + lane: frame i/2, then t (8), h (2), k4 (4)
+            for (int i = 0; i < 2 * FPW; i++) {    // unit v = i*32 + lane: frame i/2, then t (8), h (2), k4 (4)
                 const int v = i * 32 + lane, w = v & 63, t = w >> 3, h = (w >> 2) & 1, kk = (c & 1) * 4 + (w & 3);
                 const YT* y = ybase + (size_t)min(fbase + (i >> 1), Bm1) * G::N;
                 const unsigned sa = (unsigned)__cvta_generic_to_shared(W + (i >> 1) * G::FRAME_WORDS + G::STAGE_OFF + ((t * 2 + h) * 8 + kk) * 4);
@@ -386,38 +404,6 @@ struct Dec {
         float* dst4 = G::GL4 ? nullptr : arr(4, p);
         float4* dst3 = L3 + p;
         __syncwarp();                            // everyone is done with the previous subtree
-        if (PCB_Q_L2C && g3) {
-            // Odd event: layers 1 and 2 are those of the previous (even) event, whose layer 2 is in
-            // the global scratch (of this path or of the ancestor it was cloned from since):
-            // layer 3 = g(layer 2, partial sums of layer 3), no channel values needed.
-            const float4* src = L2c + ((pidx >> 24) & 7);
-#pragma unroll 1
-            for (int k0 = 0; k0 < Q / 2; k0 += 8) {
-                const uint32_t ca = cword(3, 0, k0 >> 3), cb = cword(3, 0, (k0 + Q / 2) >> 3);
-#pragma unroll 1
-                for (int k4 = 0; k4 < 8; k4 += 4) {          // 16 loads in flight: the scratch may have left L2
-                    float4 a0[4], b0[4], a1[4], b1[4];
-#pragma unroll
-                    for (int i = 0; i < 4; i++) {
-                        const int k = k0 + k4 + i;
-                        a0[i] = __ldcg(src + k * 8); b0[i] = __ldcg(src + (k + Q) * 8);
-                        a1[i] = __ldcg(src + (k + Q / 2) * 8); b1[i] = __ldcg(src + (k + Q / 2 + Q) * 8);
-                    }
-#pragma unroll
-                    for (int i = 0; i < 4; i++) {
-                        const int k = k0 + k4 + i;
-                        const float4 o0 = gs4(a0[i], b0[i], ca, 4 * (k4 + i));
-                        const float4 o1 = gs4(a1[i], b1[i], cb, 4 * (k4 + i));
-                        dst3[k * 8] = o0;
-                        dst3[(k + Q / 2) * 8] = o1;
-                        if constexpr (G::GL4) L4[k * 8 + p] = ff4(o0, o1);
-                        else *reinterpret_cast<float4*>(dst4 + 4 * k) = ff4(o0, o1);
-                    }
-                }
-            }
-            __syncwarp();
-            return;
-        }
         if (!g1) {
             stage_l1f(ybase);
             __syncwarp();
@@ -437,7 +423,7 @@ struct Dec {
             if (g1) {
                 if (r) __syncwarp();
 #pragma unroll SG
-                for (int i = 0; i < 16; i++) {   // unit u = i*32 + lane: frame i/4, then t (8), h (2), kk (8)
+                for (int i = 0; i < 4 * FPW; i++) {   // unit u = i*32 + lane: frame i/4, then t (8), h (2), kk (8)
                     const int u = i * 32 + lane, t = (u >> 4) & 7, h = (u >> 3) & 1, kk = u & 7;
                     const YT* y = ybase + (size_t)min(fbase + (i >> 2), Bm1) * G::N;
                     *reinterpret_cast<float4*>(W + (i >> 2) * G::FRAME_WORDS + G::STAGE_OFF + (u & 127) * 4) =
@@ -450,7 +436,7 @@ struct Dec {
 #pragma unroll
             for (int h = 0; h < 2; h++) {
                 const int w32 = h * (Q / 16) + r;
-                c3[h] = (!PCB_Q_L2C && g3) ? cword(3, 0, w32) : 0u;
+                c3[h] = g3 ? cword(3, 0, w32) : 0u;
 #pragma unroll
                 for (int t = 0; t < 4; t++) c1[t][h] = g1 ? cword(1, t * E, w32) : 0u;
                 c2[0][h] = g2 ? cword(2, 0, w32) : 0u; c2[1][h] = g2 ? cword(2, E, w32) : 0u;
@@ -486,16 +472,10 @@ struct Dec {
                     float4 l2[2];
                     if (g2) { l2[0] = gs4(l1[0], l1[2], c2[0][h], 4 * kk); l2[1] = gs4(l1[1], l1[3], c2[1][h], 4 * kk); }
                     else { l2[0] = ff4(l1[0], l1[2]); l2[1] = ff4(l1[1], l1[3]); }
-                    if (PCB_Q_L2C) {
-                        L2c[k * 8 + p] = l2[0];         // for the odd event that follows
-                        L2c[(k + Q) * 8 + p] = l2[1];
-                        o[h] = ff4(l2[0], l2[1]);
-                    } else {
-                        o[h] = g3 ? gs4(l2[0], l2[1], c3[h], 4 * kk) : ff4(l2[0], l2[1]);
-                    }
-                    dst3[k * 8] = o[h];
+                    o[h] = g3 ? gs4(l2[0], l2[1], c3[h], 4 * kk) : ff4(l2[0], l2[1]);
+                    dst3[k * LL] = o[h];
                 }
-                if constexpr (G::GL4) L4[(r * 8 + kk) * 8 + p] = ff4(o[0], o[1]);
+                if constexpr (G::GL4) L4[(r * 8 + kk) * LL + p] = ff4(o[0], o[1]);
                 else *reinterpret_cast<float4*>(dst4 + 4 * (r * 8 + kk)) = ff4(o[0], o[1]);
             }
 #if PCB_Q_CPA
@@ -506,7 +486,6 @@ struct Dec {
             }
 #endif
         }
-        pidx = (pidx & ~(7u << 24)) | ((uint32_t)p << 24);   // the cached layer 2 is this slot's own
         __syncwarp();                            // the staging area is overwritten by layer 5 next
     }
 
@@ -517,7 +496,7 @@ struct Dec {
         if (g1) {
             // stage the channel values of the four frames as floats
 #pragma unroll 1
-            for (int f = 0; f < 4; f++) {
+            for (int f = 0; f < FPW; f++) {
                 const YT* y = ybase + (size_t)min(fbase + f, Bm1) * G::N;
                 float* R = W + f * G::FRAME_WORDS + G::STAGE_OFF;
 #pragma unroll 4
@@ -566,7 +545,7 @@ struct Dec {
     // The layer is a run-time value: one compact loop serves every size (the ten resident warps
     // of an SM sit at different places of the program, so code size is instruction-cache traffic).
     __device__ __forceinline__ int off_rt(int lam) const {      // == G::off(lam)
-        return 8 * ((G::N >> (G::LS - 1)) - (G::N >> (lam - 1))) + 32 * (lam - G::LS);
+        return LL * ((G::N >> (G::LS - 1)) - (G::N >> (lam - 1))) + 4 * LL * (lam - G::LS);
     }
     // f-layer: own arrays
     __device__ __forceinline__ void layer_f(int lam) {
@@ -609,13 +588,13 @@ struct Dec {
 #pragma unroll
                     for (int hh = 0; hh < 2; hh++) {
                         const int c = j0 + i + hh * (S / 8);
-                        a[i][hh] = src[c * 8]; b[i][hh] = src[(c + S / 4) * 8];
+                        a[i][hh] = src[c * LL]; b[i][hh] = src[(c + S / 4) * LL];
                     }
 #pragma unroll
                 for (int i = 0; i < 2; i++) {
                     const float4 lo = gs4(a[i][0], b[i][0], cw0, 4 * i), hi = gs4(a[i][1], b[i][1], cw1, 4 * i);
-                    L4[(j0 + i) * 8 + p] = lo;
-                    L4[(j0 + i + S / 8) * 8 + p] = hi;
+                    L4[(j0 + i) * LL + p] = lo;
+                    L4[(j0 + i + S / 8) * LL + p] = hi;
                     *reinterpret_cast<float4*>(dst5 + 4 * (j0 + i)) = ff4(lo, hi);
                 }
             }
@@ -626,7 +605,7 @@ struct Dec {
                 const uint32_t cw = cword(4, 0, k0 >> 3) >> (4 * (k0 & 7));
                 float4 a[4], b[4];
 #pragma unroll
-                for (int kk = 0; kk < 4; kk++) { a[kk] = src[(k0 + kk) * 8]; b[kk] = src[(k0 + kk + S / 4) * 8]; }
+                for (int kk = 0; kk < 4; kk++) { a[kk] = src[(k0 + kk) * LL]; b[kk] = src[(k0 + kk + S / 4) * LL]; }
 #pragma unroll
                 for (int kk = 0; kk < 4; kk++)
                     *reinterpret_cast<float4*>(dst + 4 * (k0 + kk)) = gs4(a[kk], b[kk], cw, 4 * kk);
@@ -643,7 +622,7 @@ struct Dec {
             const uint32_t cw = isg ? cword(5, 0, k0 >> 3) >> (4 * (k0 & 7)) : 0u;
             float4 a[NL], b[NL];
 #pragma unroll
-            for (int kk = 0; kk < NL; kk++) { a[kk] = src[(k0 + kk) * 8]; b[kk] = src[(k0 + kk + S / 4) * 8]; }
+            for (int kk = 0; kk < NL; kk++) { a[kk] = src[(k0 + kk) * LL]; b[kk] = src[(k0 + kk + S / 4) * LL]; }
             if (isg) {
 #pragma unroll
                 for (int kk = 0; kk < NL; kk++) *reinterpret_cast<float4*>(dst + 4 * (k0 + kk)) = gs4(a[kk], b[kk], cw, 4 * kk);
@@ -730,13 +709,13 @@ struct Dec {
             chain_f();
         }
         // layers >= own are now this slot's own
-        const uint32_t low = (1u << (3 * (own - G::LTOP))) - 1;
-        pidx = (pidx & (low | 0xFF000000u)) | ((0x249249u * (uint32_t)p) & ~low);   // bits 24.. hold the layer-2 field
+        const uint32_t low = (1u << (LB * (own - G::LTOP))) - 1;
+        pidx = (pidx & low) | ((G::rep_field() * (uint32_t)p) & ~low);
     }
 
     // ---- fork / prune of one information bit (SCLDecoderMinsum.cpp:315-400) ----------
     __device__ __forceinline__ int fork() {
-        if (ninfo >= 3) {
+        if (ninfo >= LB) {
             // Fast exit (no kill, no clone): the candidates of path p are {met, met + |llr|}.  If
             // every penalised candidate of the frame is strictly above every unpenalised one, the
             // L smallest are exactly the L unpenalised ones (no tie possible).  Taken only when
@@ -745,10 +724,10 @@ struct Dec {
             if (__all_sync(FULL, __float_as_uint(hi) > maxmet)) return A0 < 0.f ? 1 : 0;   // max met < min hi
         }
         PathState s{met, pidx, cidx, w0, 0, r4, r2_0, r2_1, maxmet};
-        s = fork_slow(s, A0, lane, ninfo, keys);
+        s = fork_slow<LL>(s, A0, lane, ninfo, keys);
         met = s.met; pidx = s.pidx; cidx = s.cidx; w0 = s.w0;
         r4 = s.r4; r2_0 = s.r2_0; r2_1 = s.r2_1; maxmet = s.maxmet;
-        if (ninfo < 3) ninfo++;
+        if (ninfo < LB) ninfo++;
         return s.r & 1;
     }
 
@@ -757,7 +736,7 @@ struct Dec {
         if (isinfo) return fork();
         met += fmaxf(-A0, 0.f);         // frozen value 0 (:413-418)
         // the fast exit of the next information bit compares against the largest metric of the frame
-        if (nextinfo) maxmet = group_max(__float_as_uint(met), lane >> 3);
+        if (nextinfo) maxmet = group_max<FPW>(__float_as_uint(met), lane / LL);
         return 0;
     }
 
@@ -770,7 +749,7 @@ struct Dec {
         T = (((w0 >> 8) ^ T) & 0xFFu) | (T << 8);
         if (d2 == 4) { w0 = (w0 & 0x0000FFFFu) | (T << 16); return; }
         T = (((w0 >> 16) ^ T) & 0xFFFFu) | (T << 16);
-        cidx = heap_combine(reinterpret_cast<uint32_t*>(P), H, p, cidx, d2, T, M);
+        cidx = heap_combine<LB>(reinterpret_cast<uint32_t*>(P), H, p, cidx, d2, T, M);
     }
 
     // ---- the four phases of one size-4 subtree (its LLRs in r4, pairs (x,z) and (y,w)) --------
@@ -785,7 +764,7 @@ struct Dec {
         const float a2 = r4.z + r4.x, b2 = r4.w + r4.y;     // g with partial sums 0
         met += fmaxf(-ff(a2, b2), 0.f);
         met += fmaxf(-(b2 + a2), 0.f);
-        if (nextinfo) maxmet = group_max(__float_as_uint(met), lane >> 3);
+        if (nextinfo) maxmet = group_max<FPW>(__float_as_uint(met), lane / LL);
         return 0u;
     }
 
@@ -797,7 +776,7 @@ struct Dec {
         r2_0 = r4.z + r4.x; r2_1 = r4.w + r4.y;             // g with partial sums 0
         met += fmaxf(-ff(r2_0, r2_1), 0.f);
         A0 = r2_1 + r2_0;                                   // g with u2 = 0
-        maxmet = group_max(__float_as_uint(met), lane >> 3);
+        maxmet = group_max<FPW>(__float_as_uint(met), lane / LL);
         return fork() ? 0xFu : 0u;                          // [u3, u3, u3, u3]
     }
 
@@ -861,7 +840,7 @@ struct Dec {
             const uint32_t pat = ib & 15u;
             if (pat == 0u) T4 = rate0(ib & 16u);
             else if (pat == 8u) T4 = rep4();
-            else if (pat == 15u && ninfo >= 3 && rate1(T4)) {}
+            else if (pat == 15u && ninfo >= LB && rate1(T4)) {}
             else T4 = seq4(ib);
             if (h == 0) w0 = (w0 & ~0xF0u) | (T4 << 4);
         }
@@ -898,35 +877,35 @@ struct Scl8qArgs {
 };
 
 // One warp per block (blockDim.x == 32); a block decodes quads of frames.
-template <int M, typename YT>
-__global__ void __launch_bounds__(32, (q8::Geo<M>::GL4 && M == 10 ? 16 : M == 10 ? 10 : 5)) decode_scl8q_kernel(const __grid_constant__ Scl8qArgs S) {
+template <int M, int LL, typename YT>
+__global__ void __launch_bounds__(32, (LL != 8 ? 1 : q8::Geo<M, LL>::GL4 && M == 10 ? 16 : M == 10 ? 10 : 5)) decode_scl8q_kernel(const __grid_constant__ Scl8qArgs S) {
     const DecodeArgs& A = S.a;
-    using G = q8::Geo<M>;
+    using G = q8::Geo<M, LL>;
+    constexpr int FPW = G::FPW;
     extern __shared__ __align__(16) unsigned char smem_raw[];
     constexpr unsigned FULL = 0xffffffffu;
-    const int lane = threadIdx.x, fme = lane >> 3;
-    q8::Dec<M, YT> D;
-    D.lane = lane; D.p = lane & 7;
+    const int lane = threadIdx.x, fme = lane / LL;
+    q8::Dec<M, LL, YT> D;
+    D.lane = lane; D.p = lane & (LL - 1);
     D.W = reinterpret_cast<float*>(smem_raw);
     D.P = D.W + fme * G::FRAME_WORDS;
     D.H = reinterpret_cast<uint32_t*>(D.P) + G::OFF_H;
     D.keys = reinterpret_cast<uint32_t*>(D.P) + G::OFF_KEYS;
-    D.L3 = G::GL3 ? S.l3 + (size_t)blockIdx.x * G::SCRATCH_BLOCK_FLOAT4 + fme * (G::Q3 * 8) : nullptr;
-    D.L4 = G::GL4 ? S.l3 + (size_t)blockIdx.x * G::SCRATCH_BLOCK_FLOAT4 + G::L3_BLOCK_FLOAT4 + fme * (G::Q3 / 2 * 8) : nullptr;
-    D.L2c = G::GL3 ? S.l3 + (size_t)blockIdx.x * G::SCRATCH_BLOCK_FLOAT4 + G::L3_BLOCK_FLOAT4 + G::L4_BLOCK_FLOAT4 + fme * (2 * G::Q3 * 8) : nullptr;
+    D.L3 = G::GL3 ? S.l3 + (size_t)blockIdx.x * G::SCRATCH_BLOCK_FLOAT4 + fme * (G::Q3 * LL) : nullptr;
+    D.L4 = G::GL4 ? S.l3 + (size_t)blockIdx.x * G::SCRATCH_BLOCK_FLOAT4 + G::L3_BLOCK_FLOAT4 + fme * (G::Q3 / 2 * LL) : nullptr;
     constexpr int n = G::N;
     const int EW = (A.stride + 31) >> 5;
     const YT* ybase = reinterpret_cast<const YT*>(A.y);
-    const int nquads = (A.B + 3) >> 2;
+    const int nquads = (A.B + FPW - 1) / FPW;
 
     // The first quad of a block is its index, the following ones come from a work counter: decode
     // times differ from quad to quad, and a static stride leaves SMs idle at the end of the batch.
     int quad = blockIdx.x;
     while (quad < nquads) {
         int fr[4];
-        D.fbase = 4 * quad; D.Bm1 = A.B - 1;
+        D.fbase = FPW * quad; D.Bm1 = A.B - 1;
 #pragma unroll
-        for (int f = 0; f < 4; f++) fr[f] = min(4 * quad + f, A.B - 1);
+        for (int f = 0; f < 4; f++) fr[f] = min(FPW * quad + f, A.B - 1);
         // take the next quad now and pull it into L2 while this one is decoded (its first touch is
         // otherwise a DRAM-latency stall with nothing else to do)
         int next_quad = 0;
@@ -936,10 +915,10 @@ __global__ void __launch_bounds__(32, (q8::Geo<M>::GL4 && M == 10 ? 16 : M == 10
         if (lane == 0) next_quad = (int)gridDim.x + atomicAdd(S.next_quad, 1);
         next_quad = __shfl_sync(FULL, next_quad, 0);
 #endif
-        if (4 * next_quad + 4 <= A.B) {
-            const char* nx = reinterpret_cast<const char*>(ybase + (size_t)4 * next_quad * n);
+        if (FPW * next_quad + FPW <= A.B) {
+            const char* nx = reinterpret_cast<const char*>(ybase + (size_t)FPW * next_quad * n);
 #pragma unroll 1
-            for (int ln = lane; ln < (int)(4 * n * sizeof(YT) / 128); ln += 32)
+            for (int ln = lane; ln < (int)(FPW * n * sizeof(YT) / 128); ln += 32)
                 asm volatile("prefetch.global.L2 [%0];" ::"l"(nx + (size_t)ln * 128));
         }
         D.met = 0.f; D.maxmet = 0; D.pidx = 0; D.cidx = 0; D.w0 = 0; D.ninfo = 0;
@@ -959,7 +938,7 @@ __global__ void __launch_bounds__(32, (q8::Geo<M>::GL4 && M == 10 ? 16 : M == 10
         // compressed (Hacker's Delight 7-4) and OR-ed into the packed output at the bit offset that
         // the information counts of the words before it give.
         constexpr int NW = G::NW, HS = G::HS, WPL = NW > 32 ? NW / 32 : 1;
-        const int q0 = A.crc ? 0 : 7;   // without a CRC the reference returns slot L-1 unconditionally
+        const int q0 = A.crc ? 0 : LL - 1;   // without a CRC the reference returns slot L-1 unconditionally
         uint32_t mk[WPL];
         int off[WPL];
         {
@@ -976,14 +955,14 @@ __global__ void __launch_bounds__(32, (q8::Geo<M>::GL4 && M == 10 ? 16 : M == 10
             }
         }
 #pragma unroll 1
-        for (int fs = 0; fs < 4; fs++) {
+        for (int fs = 0; fs < FPW; fs++) {
             uint32_t* X = reinterpret_cast<uint32_t*>(D.W + fs * G::FRAME_WORDS);   // x-hat of every slot (setbit_last, d2 == M)
             uint32_t* E = X + G::XW;
 #pragma unroll 1
-            for (int t = lane + q0 * EW; t < 8 * EW; t += 32) E[t] = 0;
+            for (int t = lane + q0 * EW; t < LL * EW; t += 32) E[t] = 0;
             __syncwarp();
 #pragma unroll 1
-            for (int q = q0; q < 8; q++) {
+            for (int q = q0; q < LL; q++) {
                 uint32_t xs[WPL];
 #pragma unroll
                 for (int w = 0; w < WPL; w++) {
@@ -1020,7 +999,7 @@ __global__ void __launch_bounds__(32, (q8::Geo<M>::GL4 && M == 10 ? 16 : M == 10
             }
             __syncwarp();
             bool ok = false;
-            if (A.crc && lane < 8) {
+            if (A.crc && lane < LL) {
                 const uint32_t* e = E + lane * EW;
                 unsigned r = A.crc == 8 ? 0xFFu : 0xFFFFu;
 #pragma unroll 1
@@ -1035,8 +1014,8 @@ __global__ void __launch_bounds__(32, (q8::Geo<M>::GL4 && M == 10 ? 16 : M == 10
                 ok = (rx == r);
             }
             const unsigned okm = __ballot_sync(FULL, ok);
-            const int chosen = okm ? (__ffs(okm) - 1) : 7;
-            const int frame = 4 * quad + fs;
+            const int chosen = okm ? (__ffs(okm) - 1) : LL - 1;
+            const int frame = FPW * quad + fs;
             if (frame < A.B) {
                 if (A.sol)
 #pragma unroll 1
@@ -1052,58 +1031,58 @@ __global__ void __launch_bounds__(32, (q8::Geo<M>::GL4 && M == 10 ? 16 : M == 10
     }
 }
 
-template <int M, typename YT>
+template <int M, int LL, typename YT>
 static cudaError_t launch_m(const Scl8qArgs& a, int blocks, cudaStream_t st) {
-    const size_t smem = (size_t)q8::Geo<M>::TOTAL;
-    cudaError_t e = cudaFuncSetAttribute(decode_scl8q_kernel<M, YT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    const size_t smem = (size_t)q8::Geo<M, LL>::TOTAL;
+    cudaError_t e = cudaFuncSetAttribute(decode_scl8q_kernel<M, LL, YT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
-    decode_scl8q_kernel<M, YT><<<blocks, 32, smem, st>>>(a);
+    decode_scl8q_kernel<M, LL, YT><<<blocks, 32, smem, st>>>(a);
     return cudaGetLastError();
 }
 
-template <int M, typename YT>
+template <int M, int LL, typename YT>
 static cudaError_t occ_m(int* bps, int* warp_bytes) {
-    const size_t smem = (size_t)q8::Geo<M>::TOTAL;
-    *warp_bytes = q8::Geo<M>::TOTAL;
-    cudaError_t e = cudaFuncSetAttribute(decode_scl8q_kernel<M, YT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    const size_t smem = (size_t)q8::Geo<M, LL>::TOTAL;
+    *warp_bytes = q8::Geo<M, LL>::TOTAL;
+    cudaError_t e = cudaFuncSetAttribute(decode_scl8q_kernel<M, LL, YT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
-    return cudaOccupancyMaxActiveBlocksPerMultiprocessor(bps, decode_scl8q_kernel<M, YT>, 32, smem);
+    return cudaOccupancyMaxActiveBlocksPerMultiprocessor(bps, decode_scl8q_kernel<M, LL, YT>, 32, smem);
 }
 
-bool scl8q_supported(int m) { return m >= 8 && m <= 11; }
+// list sizes with a lane-per-path kernel: 32 / L frames per warp
+bool scl8q_supported(int m, int L) { return m >= 8 && m <= 11 && (L == 8 || L == 16 || L == 32); }
+int scl8q_frames_per_warp(int L) { return 32 / L; }
+
+#define PCB_FOR_ALL(X) \
+    X(8, 8) X(9, 8) X(10, 8) X(11, 8) X(8, 16) X(9, 16) X(10, 16) X(11, 16) X(8, 32) X(9, 32) X(10, 32) X(11, 32)
 
 // info_w: host copy of the information-mask words (ceil(n/32)), passed as kernel parameters
-cudaError_t launch_decode_scl8q(const DecodeArgs& a, const uint32_t* info_w, void* l3_scratch, int* next_quad, int blocks, cudaStream_t st) {
+cudaError_t launch_decode_scl8q(const DecodeArgs& a, int L, const uint32_t* info_w, void* l3_scratch, int* next_quad, int blocks, cudaStream_t st) {
     Scl8qArgs s;
     s.a = a;
     s.next_quad = next_quad;
     s.l3 = reinterpret_cast<float4*>(l3_scratch);
     for (int i = 0; i < 65; i++) s.info_w[i] = i < a.n / 32 ? info_w[i] : 0;
-#define PCB_CASE(MM) \
-    case MM: return launch_m<MM, float>(s, blocks, st);
     if (!a.y_f32) return cudaErrorInvalidValue;   // the caller converts double batches first (capi.cu)
-    switch (a.m) { PCB_CASE(8) PCB_CASE(9) PCB_CASE(10) PCB_CASE(11) }
+#define PCB_CASE(MM, LLL) if (a.m == MM && L == LLL) return launch_m<MM, LLL, float>(s, blocks, st);
+    PCB_FOR_ALL(PCB_CASE)
 #undef PCB_CASE
     return cudaErrorInvalidValue;
 }
 
-// bytes of global scratch one block needs (layer-3 arrays of its four frames)
-size_t scl8q_scratch_per_block(int m) {
-    switch (m) {
-        case 10: return (size_t)q8::Geo<10>::SCRATCH_BLOCK_FLOAT4 * 16;
-        case 11: return (size_t)q8::Geo<11>::SCRATCH_BLOCK_FLOAT4 * 16;
-    }
+// bytes of global scratch one block needs (layer-3/4 arrays of its frames)
+size_t scl8q_scratch_per_block(int m, int L) {
+#define PCB_CASE(MM, LLL) if (m == MM && L == LLL) return (size_t)q8::Geo<MM, LLL>::SCRATCH_BLOCK_FLOAT4 * 16;
+    PCB_FOR_ALL(PCB_CASE)
+#undef PCB_CASE
     return 0;
 }
 
-// resident blocks (= warps = frame quads) per SM
-cudaError_t scl8q_occupancy(int m, int* bps, int* warp_bytes) {
-    switch (m) {
-        case 8: return occ_m<8, float>(bps, warp_bytes);
-        case 9: return occ_m<9, float>(bps, warp_bytes);
-        case 10: return occ_m<10, float>(bps, warp_bytes);
-        case 11: return occ_m<11, float>(bps, warp_bytes);
-    }
+// resident blocks (= warps) per SM
+cudaError_t scl8q_occupancy(int m, int L, int* bps, int* warp_bytes) {
+#define PCB_CASE(MM, LLL) if (m == MM && L == LLL) return occ_m<MM, LLL, float>(bps, warp_bytes);
+    PCB_FOR_ALL(PCB_CASE)
+#undef PCB_CASE
     return cudaErrorInvalidValue;
 }
 
