@@ -49,6 +49,9 @@
 #define PCB_Q_GL4 1
 #endif
 // g-layer 1 of the top stage staged with cp.async, two chunks ahead of the arithmetic
+#ifndef PCB_Q_GL5
+#define PCB_Q_GL5 1
+#endif
 #ifndef PCB_Q_CPA
 #define PCB_Q_CPA 1
 #endif
@@ -78,7 +81,11 @@ struct Geo {
     static constexpr bool GL3 = M >= 10;
     // optional experiment: layer 4 there too (see PCB_Q_GL4)
     static constexpr bool GL4 = GL3 && PCB_Q_GL4;
-    static constexpr int LS = GL4 ? 5 : GL3 ? 4 : 3;  // first LLR layer in shared memory
+    // N = 2048 with 16 or 32 paths per frame: layer 5 (size 64) as well, 17 KB instead of 26 KB of
+    // shared memory per warp (12 resident warps per SM instead of 8; the throughput follows the
+    // number of resident warps).  With 8 paths the staging area of the top stage would not fit.
+    static constexpr bool GL5 = GL4 && M >= 11 && LL >= 16 && PCB_Q_GL5;
+    static constexpr int LS = GL5 ? 6 : GL4 ? 5 : GL3 ? 4 : 3;  // first LLR layer in shared memory
     static constexpr int NW = N / 32;       // words of a full-length bit array
     static constexpr int HS = NW + 1;       // slot stride of the partial-sum heap (layer of size S at words [S/32, 2S/32))
     static constexpr int Q3 = N / 32;       // float4s of one layer-3 array
@@ -94,14 +101,15 @@ struct Geo {
     static constexpr int STAGE_OFF = GL4 ? 0 : off(LS + 1);
     static_assert(PFLOATS - STAGE_OFF >= (GL3 ? N / 2 : N), "staging area too small");
     static constexpr int XW = LL * HS;                       // final codeword estimates (alias the LLR region)
-    static_assert(XW + LL * NW <= PFLOATS, "final-stage scratch does not fit the LLR region");
+    static_assert(XW <= PFLOATS, "final codeword estimates do not fit the LLR region");
     static constexpr int FRAME_WORDS = PFLOATS + LL * HS + 2 * LL;   // LLRs, heaps, 2L candidate keys
     static constexpr int OFF_H = PFLOATS;
     static constexpr int OFF_KEYS = PFLOATS + LL * HS;
     static constexpr int TOTAL = FPW * FRAME_WORDS * 4;
     static constexpr int L3_BLOCK_FLOAT4 = GL3 ? FPW * Q3 * LL : 0;   // global scratch per block: [frame][k][slot] float4
     static constexpr int L4_BLOCK_FLOAT4 = GL4 ? FPW * (Q3 / 2) * LL : 0;
-    static constexpr int SCRATCH_BLOCK_FLOAT4 = L3_BLOCK_FLOAT4 + L4_BLOCK_FLOAT4;
+    static constexpr int L5_BLOCK_FLOAT4 = GL5 ? FPW * (Q3 / 4) * LL : 0;
+    static constexpr int SCRATCH_BLOCK_FLOAT4 = L3_BLOCK_FLOAT4 + L4_BLOCK_FLOAT4 + L5_BLOCK_FLOAT4;
     // one slot number per layer: LLR layers LTOP..LBOT in pidx, partial-sum layers 1..M-5 in cidx
     static_assert(LB * (M - 5) <= 32, "slot fields do not fit one word");
     __host__ __device__ static constexpr unsigned rep_field() {   // 1 at the lowest bit of every field
@@ -333,6 +341,7 @@ struct Dec {
     float* W;          // the warp's whole slice (4 frames)
     float4* L3;        // GL3: this frame's layer-3 arrays in global memory, element (k, slot) at L3[k*8 + slot]
     float4* L4;        // GL4: same for layer 4
+    float4* L5;        // GL5: same for layer 5
     float met;
     uint32_t maxmet;   // bit pattern of the largest metric of this frame (valid whenever the next phase is an information bit)
     uint32_t pidx, cidx, w0;
@@ -571,6 +580,64 @@ struct Dec {
                 gs4(*reinterpret_cast<const float4*>(src + k), *reinterpret_cast<const float4*>(src + S + k), cw, 0);
         }
     }
+    // ---- GL5: layers 3, 4, 5 in the global scratch -----------------------------------------
+    __device__ __forceinline__ float4* glayer(int lam) const { return lam == 3 ? L3 : lam == 4 ? L4 : L5; }
+    // Layer LAM (global) from the global layer LAM-1: g from the lazily shared source slot, or f
+    // from this slot's own arrays.  Layer LAM+1 = f(layer LAM) comes next for this slot, so columns
+    // j and j + S/8 are produced together and combined on the spot; it goes to the scratch when it is
+    // a global layer too, else to shared memory.
+    template <int LAM>
+    __device__ __forceinline__ void global_fused(bool isg) {
+        constexpr int S = G::size(LAM);
+        const float4* src = glayer(LAM - 1) + (isg ? pfield(LAM - 1) : p);
+        float4* dstg = glayer(LAM);
+        float* dsts = LAM + 1 >= G::LS ? arr(LAM + 1 >= G::LS ? LAM + 1 : G::LS, p) : nullptr;
+#pragma unroll 1
+        for (int j0 = 0; j0 < S / 8; j0 += 2) {       // 8 loads in flight
+            uint32_t cw0 = 0, cw1 = 0;
+            if (isg) { cw0 = cword(LAM, 0, j0 >> 3) >> (4 * (j0 & 7)); cw1 = cword(LAM, 0, (j0 + S / 8) >> 3) >> (4 * (j0 & 7)); }
+            float4 a[2][2], b[2][2];
+#pragma unroll
+            for (int i = 0; i < 2; i++)
+#pragma unroll
+                for (int hh = 0; hh < 2; hh++) {
+                    const int c = j0 + i + hh * (S / 8);
+                    a[i][hh] = src[c * LL]; b[i][hh] = src[(c + S / 4) * LL];
+                }
+#pragma unroll
+            for (int i = 0; i < 2; i++) {
+                float4 lo, hi;
+                if (isg) { lo = gs4(a[i][0], b[i][0], cw0, 4 * i); hi = gs4(a[i][1], b[i][1], cw1, 4 * i); }
+                else { lo = ff4(a[i][0], b[i][0]); hi = ff4(a[i][1], b[i][1]); }
+                dstg[(j0 + i) * LL + p] = lo;
+                dstg[(j0 + i + S / 8) * LL + p] = hi;
+                if constexpr (LAM + 1 >= G::LS) *reinterpret_cast<float4*>(dsts + 4 * (j0 + i)) = ff4(lo, hi);
+                else glayer(LAM + 1)[(j0 + i) * LL + p] = ff4(lo, hi);
+            }
+        }
+    }
+    // shared-memory layer LAM from the global layer LAM-1
+    template <int LAM>
+    __device__ __forceinline__ void from_global(bool isg) {
+        constexpr int S = G::size(LAM), NL = PCB_Q_L5N;
+        const float4* src = glayer(LAM - 1) + (isg ? pfield(LAM - 1) : p);
+        float* dst = arr(LAM, p);
+#pragma unroll 1
+        for (int k0 = 0; k0 < S / 4; k0 += NL) {
+            const uint32_t cw = isg ? cword(LAM, 0, k0 >> 3) >> (4 * (k0 & 7)) : 0u;
+            float4 a[NL], b[NL];
+#pragma unroll
+            for (int kk = 0; kk < NL; kk++) { a[kk] = src[(k0 + kk) * LL]; b[kk] = src[(k0 + kk + S / 4) * LL]; }
+            if (isg) {
+#pragma unroll
+                for (int kk = 0; kk < NL; kk++) *reinterpret_cast<float4*>(dst + 4 * (k0 + kk)) = gs4(a[kk], b[kk], cw, 4 * kk);
+            } else {
+#pragma unroll
+                for (int kk = 0; kk < NL; kk++) *reinterpret_cast<float4*>(dst + 4 * (k0 + kk)) = ff4(a[kk], b[kk]);
+            }
+        }
+    }
+
     // GL3: g at layer 4 from the layer-3 arrays in global memory (L2)
     __device__ __forceinline__ void layer4_g_global() {
         constexpr int S = G::size(4);
@@ -697,13 +764,17 @@ struct Dec {
             __syncwarp();
             ll = own = G::LBOT - z;
             if (ll >= LR) { chain_g_dispatch<LR>(ll); ll = G::LBOT; }
+            else if (G::GL5 && ll == 4) { global_fused<4>(true); from_global<6>(false); ll = 6; }   // layers 4, 5, 6
+            else if (G::GL5 && ll == 5) { global_fused<5>(true); ll = 6; }
+            else if (G::GL5 && ll == 6) from_global<6>(true);
             else if (G::GL3 && ll == 4) { layer4_g_global(); if (G::GL4) ll = 5; }   // GL4: layer 5 done as well
             else if (G::GL4 && ll == 5) layer5_global(true);
             else layer_g(ll);
         }
         if (ll < G::LBOT) {
             int lam = ll + 1;
-            if (G::GL4 && ll == 4) { layer5_global(false); lam = 6; }
+            if (G::GL5 && ll == 4) { global_fused<5>(false); lam = 7; }      // after the top stage
+            else if (G::GL4 && ll == 4) { layer5_global(false); lam = 6; }
 #pragma unroll 1
             for (; lam < LR; lam++) layer_f(lam);
             chain_f();
@@ -893,6 +964,7 @@ __global__ void __launch_bounds__(32, (LL != 8 ? 1 : q8::Geo<M, LL>::GL4 && M ==
     D.keys = reinterpret_cast<uint32_t*>(D.P) + G::OFF_KEYS;
     D.L3 = G::GL3 ? S.l3 + (size_t)blockIdx.x * G::SCRATCH_BLOCK_FLOAT4 + fme * (G::Q3 * LL) : nullptr;
     D.L4 = G::GL4 ? S.l3 + (size_t)blockIdx.x * G::SCRATCH_BLOCK_FLOAT4 + G::L3_BLOCK_FLOAT4 + fme * (G::Q3 / 2 * LL) : nullptr;
+    D.L5 = G::GL5 ? S.l3 + (size_t)blockIdx.x * G::SCRATCH_BLOCK_FLOAT4 + G::L3_BLOCK_FLOAT4 + G::L4_BLOCK_FLOAT4 + fme * (G::Q3 / 4 * LL) : nullptr;
     constexpr int n = G::N;
     const int EW = (A.stride + 31) >> 5;
     const YT* ybase = reinterpret_cast<const YT*>(A.y);
@@ -957,7 +1029,7 @@ __global__ void __launch_bounds__(32, (LL != 8 ? 1 : q8::Geo<M, LL>::GL4 && M ==
 #pragma unroll 1
         for (int fs = 0; fs < FPW; fs++) {
             uint32_t* X = reinterpret_cast<uint32_t*>(D.W + fs * G::FRAME_WORDS);   // x-hat of every slot (setbit_last, d2 == M)
-            uint32_t* E = X + G::XW;
+            uint32_t* E = X + G::OFF_H;    // the partial-sum heaps are dead by now
 #pragma unroll 1
             for (int t = lane + q0 * EW; t < LL * EW; t += 32) E[t] = 0;
             __syncwarp();
