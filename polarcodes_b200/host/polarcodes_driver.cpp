@@ -14,6 +14,14 @@
 //   PCB_SEED=<s>     Philox seed (default 0x5EED0000 + SNR index as SURVEY.md §8(d))
 //   PCB_CSV=<file>   extra CSV with BER, frames/s, info Gbit/s per SNR point
 //   PCB_CONF=<file>  configuration file (default conf.txt in the CWD, like the reference)
+//   PCB_CKPT=<file>  checkpoint of a long run: after every slice of
+//                    PCB_SLICE frames (default 2^22) the per-point counters and the frame-id
+//                    cursor are written (tmp + rename); a later run with the same configuration
+//                    resumes behind the cursor.  The Philox stream is keyed by the global frame
+//                    id, so a resumed run ends with exactly the counters of an uninterrupted one.
+//   PCB_MAX_ERRORS=<e>  error budget: an SNR point stops at the first slice boundary with at
+//                    least e frame errors (FER = errors / frames decoded so far)
+//   PCB_STOP_AFTER_SLICES=<s>  exit with status 3 after s slices (interruption drill for the tests)
 // testType 2 (throughput) follows the reference semantics of timing the decoder only: the value
 // written is the decode-kernel time in clock ticks (CLOCKS_PER_SEC) accumulated over SNR points
 // (the reference never resets tAll, :118,243), for `loop` distinct frames.
@@ -34,7 +42,51 @@
 struct Point {
     uint64_t frames = 0, frame_errors = 0, bit_errors = 0;
     double seconds = 0;
+    uint64_t cursor = 0;   // global frame ids below the cursor are accounted for
+    int done = 0;
 };
+
+// Checkpoint: one header line that identifies the run, then one line per SNR point.
+static std::string ckpt_header(int testType, int n, int k, int loop, int decoder, int zComputer, int L, int crc,
+                               const std::vector<double>& snr, const char* seed_env) {
+    char buf[256];
+    std::snprintf(buf, sizeof buf, "pcb_ckpt 1 %d %d %d %d %d %d %d %d %s %zu", testType, n, k, loop, decoder, zComputer, L, crc,
+                  seed_env ? seed_env : "default", snr.size());
+    std::string h = buf;
+    for (double v : snr) { std::snprintf(buf, sizeof buf, " %.17g", v); h += buf; }
+    return h;
+}
+
+static bool ckpt_load(const char* path, const std::string& header, std::vector<Point>& pts) {
+    std::ifstream f(path);
+    if (!f) return false;
+    std::string h;
+    std::getline(f, h);
+    if (h != header) {
+        std::fprintf(stderr, "polarcodes_driver: checkpoint %s belongs to another configuration, ignored\n", path);
+        return false;
+    }
+    std::vector<Point> tmp(pts.size());
+    for (auto& p : tmp)
+        if (!(f >> p.cursor >> p.frames >> p.frame_errors >> p.bit_errors >> p.seconds >> p.done)) return false;
+    pts = tmp;
+    return true;
+}
+
+static void ckpt_save(const char* path, const std::string& header, const std::vector<Point>& pts) {
+    const std::string tmp = std::string(path) + ".tmp";
+    {
+        std::ofstream f(tmp);
+        f << header << '\n';
+        for (const auto& p : pts) {
+            char buf[200];
+            std::snprintf(buf, sizeof buf, "%llu %llu %llu %llu %.17g %d\n", (unsigned long long)p.cursor, (unsigned long long)p.frames,
+                          (unsigned long long)p.frame_errors, (unsigned long long)p.bit_errors, p.seconds, p.done);
+            f << buf;
+        }
+    }
+    std::rename(tmp.c_str(), path);
+}
 
 static void fail(const char* what) {
     std::fprintf(stderr, "polarcodes_driver: %s: %s\n", what, pcb_last_error());
@@ -93,6 +145,14 @@ int main() {
 
     std::vector<std::pair<double, double>> res;
     std::vector<Point> points(nth);
+    const char* ckpt = std::getenv("PCB_CKPT");
+    const std::string header = ckpt_header(testType, n, k, loop, decoder, zComputer, L, crc, snr, seed_env);
+    if (ckpt && ckpt_load(ckpt, header, points)) std::cout << "Resuming from " << ckpt << "\n";
+    uint64_t slice = 1ull << 22;
+    if (const char* e = std::getenv("PCB_SLICE")) slice = std::max<uint64_t>(1, std::strtoull(e, nullptr, 0));
+    uint64_t max_errors = 0, stop_after = 0, slices_done = 0;
+    if (const char* e = std::getenv("PCB_MAX_ERRORS")) max_errors = std::strtoull(e, nullptr, 0);
+    if (const char* e = std::getenv("PCB_STOP_AFTER_SLICES")) stop_after = std::strtoull(e, nullptr, 0);
     const clock_t startT = clock();
     double tAll = 0;
     for (int si = 0; si < nth; si++) {
@@ -105,23 +165,43 @@ int main() {
         if (pcb_frozen_mask(n, inf.data(), ninf, mask.data()) != PCB_OK) fail("pcb_frozen_mask");
         const uint64_t seed = seed_env ? std::strtoull(seed_env, nullptr, 0) : (0x5EED0000ull + (uint64_t)si);
         const uint64_t total = (uint64_t)std::max(loop, 0);
-        std::vector<Point> part(gpus);
-        std::vector<std::thread> th;
-        for (int g = 0; g < gpus; g++) {
-            th.emplace_back([&, g]() {
-                if (pcb_set_code(hs[g], mask.data(), sigma) != PCB_OK) fail("pcb_set_code");
-                const uint64_t lo = total * g / gpus, hi = total * (g + 1) / gpus;   // shard by global frame id
-                if (hi > lo &&
-                    pcb_montecarlo(hs[g], snr[si], hi - lo, seed, lo, &part[g].frames, &part[g].frame_errors,
-                                   &part[g].bit_errors, &part[g].seconds) != PCB_OK)
-                    fail("pcb_montecarlo");
-            });
-        }
-        for (auto& t : th) t.join();
         Point& p = points[si];
-        for (int g = 0; g < gpus; g++) {
-            p.frames += part[g].frames; p.frame_errors += part[g].frame_errors; p.bit_errors += part[g].bit_errors;
-            p.seconds = std::max(p.seconds, part[g].seconds);
+        bool code_set = false;
+        while (!p.done) {
+            if (p.cursor >= total || (max_errors && p.frame_errors >= max_errors)) {
+                p.done = 1;
+                if (ckpt) ckpt_save(ckpt, header, points);
+                break;
+            }
+            if (stop_after && slices_done >= stop_after) {
+                std::cout << "\nStopped after " << slices_done << " slices\n";
+                return 3;
+            }
+            // one slice of global frame ids [base, base + len), sharded over the GPUs
+            const uint64_t base = p.cursor, len = std::min(slice, total - base);
+            std::vector<Point> part(gpus);
+            std::vector<std::thread> th;
+            for (int g = 0; g < gpus; g++) {
+                th.emplace_back([&, g]() {
+                    if (!code_set && pcb_set_code(hs[g], mask.data(), sigma) != PCB_OK) fail("pcb_set_code");
+                    const uint64_t lo = base + len * g / gpus, hi = base + len * (g + 1) / gpus;
+                    if (hi > lo &&
+                        pcb_montecarlo(hs[g], snr[si], hi - lo, seed, lo, &part[g].frames, &part[g].frame_errors,
+                                       &part[g].bit_errors, &part[g].seconds) != PCB_OK)
+                        fail("pcb_montecarlo");
+                });
+            }
+            for (auto& t : th) t.join();
+            code_set = true;
+            double sec = 0;
+            for (int g = 0; g < gpus; g++) {
+                p.frames += part[g].frames; p.frame_errors += part[g].frame_errors; p.bit_errors += part[g].bit_errors;
+                sec = std::max(sec, part[g].seconds);
+            }
+            p.seconds += sec;
+            p.cursor = base + len;
+            slices_done++;
+            if (ckpt) ckpt_save(ckpt, header, points);
         }
         if (testType == 1) {
             const double fer = p.frames ? (double)p.frame_errors / (double)p.frames : 0.0;

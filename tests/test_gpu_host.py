@@ -92,3 +92,41 @@ def test_driver_scl_crc16_and_throughput_mode(tmp_path):
     assert len(files) == 1
     ticks = float(open(files[0]).read().split("\n")[1].split("\t")[1])
     assert ticks > 0   # decode time of 20000 frames in clock ticks
+
+
+def _csv_rows(path):
+    rows = open(path).read().strip().split("\n")[1:]
+    return [tuple(int(v) for v in r.split(",")[1:4]) for r in rows]   # frames, frame errors, bit errors
+
+
+def test_driver_checkpoint_resume_and_error_budget(tmp_path):
+    """an interrupted run resumed from its checkpoint ends with exactly the counters
+    of an uninterrupted one (Philox is keyed by the global frame id); PCB_MAX_ERRORS stops a point early."""
+    subprocess.check_call(["make", "-s", "-C", HOST])
+    exe = os.path.join(HOST, "polarcodes_driver")
+    (tmp_path / "conf.txt").write_text("1\n1024\n512\n30000\n2\n2\n1\n0\n2\n2\n1.5 2.5\n")
+    base = dict(os.environ, PCB_SLICE="8192")
+    r = subprocess.run([exe], cwd=tmp_path, capture_output=True, text=True, env=dict(base, PCB_CSV=str(tmp_path / "a.csv")))
+    assert r.returncode == 0, r.stderr
+    want = _csv_rows(tmp_path / "a.csv")
+    assert [w[0] for w in want] == [30000, 30000]
+    ck = dict(base, PCB_CKPT=str(tmp_path / "run.ckpt"), PCB_CSV=str(tmp_path / "b.csv"))
+    r = subprocess.run([exe], cwd=tmp_path, capture_output=True, text=True, env=dict(ck, PCB_STOP_AFTER_SLICES="2"))
+    assert r.returncode == 3 and os.path.exists(tmp_path / "run.ckpt")
+    r = subprocess.run([exe], cwd=tmp_path, capture_output=True, text=True, env=dict(ck, PCB_STOP_AFTER_SLICES="3"))
+    assert r.returncode == 3                      # second interruption, inside the second SNR point
+    r = subprocess.run([exe], cwd=tmp_path, capture_output=True, text=True, env=ck)
+    assert r.returncode == 0 and "Resuming" in r.stdout, r.stderr
+    assert _csv_rows(tmp_path / "b.csv") == want
+    # a checkpoint of another configuration is ignored
+    (tmp_path / "conf.txt").write_text("1\n1024\n512\n30000\n2\n2\n1\n0\n2\n1\n1.5\n")
+    r = subprocess.run([exe], cwd=tmp_path, capture_output=True, text=True, env=dict(ck, PCB_CSV=str(tmp_path / "c.csv")))
+    assert r.returncode == 0 and "another configuration" in r.stderr
+    assert _csv_rows(tmp_path / "c.csv") == want[:1]
+    # error budget
+    os.remove(tmp_path / "run.ckpt")
+    r = subprocess.run([exe], cwd=tmp_path, capture_output=True, text=True,
+                       env=dict(base, PCB_MAX_ERRORS="100", PCB_CSV=str(tmp_path / "d.csv")))
+    assert r.returncode == 0, r.stderr
+    (frames, ferr, _), = _csv_rows(tmp_path / "d.csv")
+    assert frames == 8192 and ferr >= 100       # FER ~ 0.36 at 1.5 dB: the first slice is enough
