@@ -52,6 +52,12 @@
 #ifndef PCB_Q_GL5
 #define PCB_Q_GL5 1
 #endif
+#ifndef PCB_Q_GH
+#define PCB_Q_GH 1         // N = 2048, 16/32 paths: the two largest partial-sum layers in the global scratch
+#endif
+#ifndef PCB_Q_GH_SMALL
+#define PCB_Q_GH_SMALL 0   // the same for the other N >= 1024 variants
+#endif
 #ifndef PCB_Q_CPA
 #define PCB_Q_CPA 1
 #endif
@@ -87,7 +93,13 @@ struct Geo {
     static constexpr bool GL5 = GL4 && M >= 11 && LL >= 16 && PCB_Q_GL5;
     static constexpr int LS = GL5 ? 6 : GL4 ? 5 : GL3 ? 4 : 3;  // first LLR layer in shared memory
     static constexpr int NW = N / 32;       // words of a full-length bit array
-    static constexpr int HS = NW + 1;       // slot stride of the partial-sum heap (layer of size S at words [S/32, 2S/32))
+    // Partial-sum heap of a slot: the layer of size S at words [S/32, 2S/32).  GH: the two largest
+    // layers (words >= SPLITW, three quarters of the heap) live in the global scratch as
+    // [word][slot]; they are touched at the top-stage events and by the rare big combines only.
+    static constexpr bool GH = M >= 10 && ((M >= 11 && LL >= 16) ? PCB_Q_GH : PCB_Q_GH_SMALL);
+    static constexpr int SPLITW = GH ? NW / 4 : (1 << 20);
+    static constexpr int HS = GH ? SPLITW + 1 : NW + 1;       // slot stride of the shared-memory part
+    static constexpr int XHS = NW + 1;      // slot stride of the final codeword estimates
     static constexpr int Q3 = N / 32;       // float4s of one layer-3 array
     __host__ __device__ static constexpr int size(int lam) { return N >> lam; }
     __host__ __device__ static constexpr int stride(int lam) { return size(lam) + 4; }
@@ -100,7 +112,7 @@ struct Geo {
     // staging area = the layers below the one the top stage writes (dead at those phases)
     static constexpr int STAGE_OFF = GL4 ? 0 : off(LS + 1);
     static_assert(PFLOATS - STAGE_OFF >= (GL3 ? N / 2 : N), "staging area too small");
-    static constexpr int XW = LL * HS;                       // final codeword estimates (alias the LLR region)
+    static constexpr int XW = LL * XHS;                      // final codeword estimates (alias the LLR region)
     static_assert(XW <= PFLOATS, "final codeword estimates do not fit the LLR region");
     static constexpr int FRAME_WORDS = PFLOATS + LL * HS + 2 * LL;   // LLRs, heaps, 2L candidate keys
     static constexpr int OFF_H = PFLOATS;
@@ -109,7 +121,8 @@ struct Geo {
     static constexpr int L3_BLOCK_FLOAT4 = GL3 ? FPW * Q3 * LL : 0;   // global scratch per block: [frame][k][slot] float4
     static constexpr int L4_BLOCK_FLOAT4 = GL4 ? FPW * (Q3 / 2) * LL : 0;
     static constexpr int L5_BLOCK_FLOAT4 = GL5 ? FPW * (Q3 / 4) * LL : 0;
-    static constexpr int SCRATCH_BLOCK_FLOAT4 = L3_BLOCK_FLOAT4 + L4_BLOCK_FLOAT4 + L5_BLOCK_FLOAT4;
+    static constexpr int HG_BLOCK_FLOAT4 = GH ? FPW * (NW - NW / 4) * LL / 4 : 0;
+    static constexpr int SCRATCH_BLOCK_FLOAT4 = L3_BLOCK_FLOAT4 + L4_BLOCK_FLOAT4 + L5_BLOCK_FLOAT4 + HG_BLOCK_FLOAT4;
     // one slot number per layer: LLR layers LTOP..LBOT in pidx, partial-sum layers 1..M-5 in cidx
     static_assert(LB * (M - 5) <= 32, "slot fields do not fit one word");
     __host__ __device__ static constexpr unsigned rep_field() {   // 1 at the lowest bit of every field
@@ -187,18 +200,29 @@ __device__ __forceinline__ unsigned group_max(unsigned x, int fme) {
 // [D/32, 2D/32) of this slot; layer 0 (the final codeword estimate, written at the very last
 // phase) goes to the then-dead LLR region instead.  Out of line: taken once per four subtrees.
 template <int LB>
-__device__ __noinline__ uint32_t heap_combine(uint32_t* Pw, uint32_t* H, int p, uint32_t cidx, int d2, uint32_t T, int m) {
-    const int D = 1 << d2, NW = 1 << (m - 5), HS = NW + 1;
-    uint32_t* hp = (d2 == m) ? (Pw + p * HS - NW) : (H + p * HS);
+__device__ __noinline__ uint32_t heap_combine(uint32_t* Pw, uint32_t* H, uint32_t* HG, int hs, int splitw, int p, uint32_t cidx, int d2, uint32_t T, int m) {
+    constexpr int LL = 1 << LB;
+    const int D = 1 << d2, NW = 1 << (m - 5);
+    // word i of the destination layer's slot is dp[i * ds]: the then-dead LLR region for layer 0,
+    // the global part of the heap ([word][slot]) for the big layers, shared memory otherwise
+    uint32_t* dp;
+    int ds = 1;
+    if (d2 == m) dp = Pw + p * (NW + 1) - NW;
+    else if (D / 32 >= splitw) { dp = HG + p - splitw * LL; ds = LL; }
+    else dp = H + p * hs;
     __syncwarp();
-    hp[2 * D / 32 - 1] = T;
+    dp[(2 * D / 32 - 1) * ds] = T;
 #pragma unroll 1
     for (int w = 32; w < D; w <<= 1) {
         const int lgw = 31 - __clz(w), layc = m - lgw, nw = w >> 5;
-        const uint32_t* cs = H + ((cidx >> (LB * (layc - 1))) & ((1u << LB) - 1)) * HS + nw;
+        const int sc = (cidx >> (LB * (layc - 1))) & (LL - 1);
+        const uint32_t* sp;
+        int ss = 1;
+        if (nw >= splitw) { sp = HG + sc + (nw - splitw) * LL; ss = LL; }
+        else sp = H + sc * hs + nw;
 #pragma unroll 1
         for (int kk = 0; kk < nw; kk++)
-            hp[(2 * D - 2 * w) / 32 + kk] = cs[kk] ^ hp[(2 * D - w) / 32 + kk];
+            dp[((2 * D - 2 * w) / 32 + kk) * ds] = sp[kk * ss] ^ dp[((2 * D - w) / 32 + kk) * ds];
     }
     __syncwarp();
     if (d2 < m) {
@@ -337,6 +361,7 @@ struct Dec {
     int fbase, Bm1;    // first frame of the quad, last frame of the batch (tail quads repeat it)
     float* P;          // this frame's LLR layers
     uint32_t* H;       // this frame's partial-sum heaps
+    uint32_t* HG;      // GH: their big layers in global memory, word w of slot s at HG[(w - SPLITW) * LL + s]
     uint32_t* keys;    // this frame's 16 candidate keys
     float* W;          // the warp's whole slice (4 frames)
     float4* L3;        // GL3: this frame's layer-3 arrays in global memory, element (k, slot) at L3[k*8 + slot]
@@ -356,7 +381,9 @@ struct Dec {
     __device__ __forceinline__ int cfield(int lam) const { return (cidx >> (LB * (lam - 1))) & (LL - 1); }
     // word w32 (32 elements each) of partial-sum layer `lam` (size >= 32), elements from `base`
     __device__ __forceinline__ uint32_t cword(int lam, int base, int w32) const {
-        return H[cfield(lam) * G::HS + (G::size(lam) >> 5) + (base >> 5) + w32];
+        const int w = (G::size(lam) >> 5) + (base >> 5) + w32;
+        if (G::GH && (G::size(lam) >> 5) >= G::SPLITW) return HG[(w - G::SPLITW) * LL + cfield(lam)];
+        return H[cfield(lam) * G::HS + w];
     }
 
     // ---- layer 3 straight from the channel values (layers 0, 1, 2 are virtual) ---------
@@ -820,7 +847,7 @@ struct Dec {
         T = (((w0 >> 8) ^ T) & 0xFFu) | (T << 8);
         if (d2 == 4) { w0 = (w0 & 0x0000FFFFu) | (T << 16); return; }
         T = (((w0 >> 16) ^ T) & 0xFFFFu) | (T << 16);
-        cidx = heap_combine<LB>(reinterpret_cast<uint32_t*>(P), H, p, cidx, d2, T, M);
+        cidx = heap_combine<LB>(reinterpret_cast<uint32_t*>(P), H, HG, G::HS, G::SPLITW, p, cidx, d2, T, M);
     }
 
     // ---- the four phases of one size-4 subtree (its LLRs in r4, pairs (x,z) and (y,w)) --------
@@ -961,6 +988,9 @@ __global__ void __launch_bounds__(32, (LL != 8 ? 1 : q8::Geo<M, LL>::GL4 && M ==
     D.W = reinterpret_cast<float*>(smem_raw);
     D.P = D.W + fme * G::FRAME_WORDS;
     D.H = reinterpret_cast<uint32_t*>(D.P) + G::OFF_H;
+    D.HG = G::GH ? reinterpret_cast<uint32_t*>(S.l3 + (size_t)blockIdx.x * G::SCRATCH_BLOCK_FLOAT4 + G::L3_BLOCK_FLOAT4 + G::L4_BLOCK_FLOAT4 +
+                                               G::L5_BLOCK_FLOAT4) + fme * ((G::NW - G::NW / 4) * LL)
+                   : nullptr;
     D.keys = reinterpret_cast<uint32_t*>(D.P) + G::OFF_KEYS;
     D.L3 = G::GL3 ? S.l3 + (size_t)blockIdx.x * G::SCRATCH_BLOCK_FLOAT4 + fme * (G::Q3 * LL) : nullptr;
     D.L4 = G::GL4 ? S.l3 + (size_t)blockIdx.x * G::SCRATCH_BLOCK_FLOAT4 + G::L3_BLOCK_FLOAT4 + fme * (G::Q3 / 2 * LL) : nullptr;
@@ -1009,7 +1039,7 @@ __global__ void __launch_bounds__(32, (LL != 8 ? 1 : q8::Geo<M, LL>::GL4 && M ==
         // five shift-xor steps, across words five shuffles, and the information bits of a word are
         // compressed (Hacker's Delight 7-4) and OR-ed into the packed output at the bit offset that
         // the information counts of the words before it give.
-        constexpr int NW = G::NW, HS = G::HS, WPL = NW > 32 ? NW / 32 : 1;
+        constexpr int NW = G::NW, XHS = G::XHS, WPL = NW > 32 ? NW / 32 : 1;
         const int q0 = A.crc ? 0 : LL - 1;   // without a CRC the reference returns slot L-1 unconditionally
         uint32_t mk[WPL];
         int off[WPL];
@@ -1029,16 +1059,15 @@ __global__ void __launch_bounds__(32, (LL != 8 ? 1 : q8::Geo<M, LL>::GL4 && M ==
 #pragma unroll 1
         for (int fs = 0; fs < FPW; fs++) {
             uint32_t* X = reinterpret_cast<uint32_t*>(D.W + fs * G::FRAME_WORDS);   // x-hat of every slot (setbit_last, d2 == M)
-            uint32_t* E = X + G::OFF_H;    // the partial-sum heaps are dead by now
-#pragma unroll 1
-            for (int t = lane + q0 * EW; t < LL * EW; t += 32) E[t] = 0;
-            __syncwarp();
+            // packed output words of slot q: over the (dead) heaps for slot 0, over the codeword
+            // estimate of slot q - 1 (consumed one iteration earlier) for the others
+            auto eptr = [&](int q) { return q == 0 ? X + G::OFF_H : X + (q - 1) * XHS; };
 #pragma unroll 1
             for (int q = q0; q < LL; q++) {
                 uint32_t xs[WPL];
 #pragma unroll
                 for (int w = 0; w < WPL; w++) {
-                    uint32_t x = lane + 32 * w < NW ? X[q * HS + lane + 32 * w] : 0u;
+                    uint32_t x = lane + 32 * w < NW ? X[q * XHS + lane + 32 * w] : 0u;
                     x ^= (x >> 1) & 0x55555555u; x ^= (x >> 2) & 0x33333333u; x ^= (x >> 4) & 0x0F0F0F0Fu;
                     x ^= (x >> 8) & 0x00FF00FFu; x ^= (x >> 16) & 0x0000FFFFu;
 #pragma unroll
@@ -1049,6 +1078,11 @@ __global__ void __launch_bounds__(32, (LL != 8 ? 1 : q8::Geo<M, LL>::GL4 && M ==
                     xs[w] = x;
                 }
                 if constexpr (WPL == 2) xs[0] ^= xs[1];
+                uint32_t* Eq = eptr(q);
+                __syncwarp();                    // every lane has read its words of slot q
+#pragma unroll 1
+                for (int t = lane; t < EW; t += 32) Eq[t] = 0;
+                __syncwarp();
 #pragma unroll
                 for (int w = 0; w < WPL; w++) {
                     uint32_t m = mk[w], x = xs[w] & m, mkk = ~m << 1;
@@ -1064,15 +1098,15 @@ __global__ void __launch_bounds__(32, (LL != 8 ? 1 : q8::Geo<M, LL>::GL4 && M ==
                     }
                     const int c = __popc(mk[w]), o = off[w];
                     if (c) {
-                        atomicOr(&E[q * EW + (o >> 5)], x << (o & 31));
-                        if ((o & 31) + c > 32) atomicOr(&E[q * EW + (o >> 5) + 1], x >> (32 - (o & 31)));
+                        atomicOr(&Eq[o >> 5], x << (o & 31));
+                        if ((o & 31) + c > 32) atomicOr(&Eq[(o >> 5) + 1], x >> (32 - (o & 31)));
                     }
                 }
             }
             __syncwarp();
             bool ok = false;
             if (A.crc && lane < LL) {
-                const uint32_t* e = E + lane * EW;
+                const uint32_t* e = eptr(lane);
                 unsigned r = A.crc == 8 ? 0xFFu : 0xFFFFu;
 #pragma unroll 1
                 for (int b = 0; b < A.k / 8; b++) {
@@ -1088,14 +1122,15 @@ __global__ void __launch_bounds__(32, (LL != 8 ? 1 : q8::Geo<M, LL>::GL4 && M ==
             const unsigned okm = __ballot_sync(FULL, ok);
             const int chosen = okm ? (__ffs(okm) - 1) : LL - 1;
             const int frame = FPW * quad + fs;
+            const uint32_t* Ec = eptr(chosen);
             if (frame < A.B) {
                 if (A.sol)
 #pragma unroll 1
                     for (int t = lane; t < A.stride; t += 32)
-                        A.sol[(size_t)frame * A.stride + t] = (E[chosen * EW + (t >> 5)] >> (t & 31)) & 1;
+                        A.sol[(size_t)frame * A.stride + t] = (Ec[t >> 5] >> (t & 31)) & 1;
                 if (A.sol_bits)
 #pragma unroll 1
-                    for (int t = lane; t < EW; t += 32) A.sol_bits[(size_t)frame * EW + t] = E[chosen * EW + t];
+                    for (int t = lane; t < EW; t += 32) A.sol_bits[(size_t)frame * EW + t] = Ec[t];
             }
             __syncwarp();
         }
