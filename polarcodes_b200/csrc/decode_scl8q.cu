@@ -58,6 +58,9 @@
 #ifndef PCB_Q_GH_SMALL
 #define PCB_Q_GH_SMALL 0   // the same for the other N >= 1024 variants
 #endif
+#ifndef PCB_Q_R1FAST
+#define PCB_Q_R1FAST 1     // rate-1 nodes of size 4 and 8 from the signs and the smallest magnitude of their inputs
+#endif
 #ifndef PCB_Q_CPA
 #define PCB_Q_CPA 1
 #endif
@@ -878,6 +881,40 @@ struct Dec {
         return fork() ? 0xFu : 0u;                          // [u3, u3, u3, u3]
     }
 
+    // Rate-1 node (all positions information bits) with the list full.  If every phase of the node
+    // takes the fast exit, each path keeps its likelier bit at every phase and no metric changes, so
+    // the node is an SC decode with hard decisions per path, and for those (min-sum, no zero LLR):
+    //   * the node's partial sums are the signs of its input LLRs (u0 = sa^sb, u1 = sb for a pair;
+    //     induction over the sizes), and
+    //   * every g is a sum of two same-signed values (|g| = fl(|a|+|b|) >= max), every f a min, so
+    //     the smallest leaf magnitude is the first leaf's, min_i |alpha_i|, exactly.
+    // All fast exits of the node hold iff met + min_i |alpha_i| exceeds the largest metric of the
+    // frame (fl(met + x) is monotone in x): ONE vote, no leaf LLR computed.  A zero input fails the
+    // test (hi == met <= maxmet).  Nothing is committed on failure.
+#if PCB_Q_R1FAST
+    __device__ __forceinline__ static uint32_t signs4(float4 v) {
+        return (__float_as_uint(v.x) >> 31) | ((__float_as_uint(v.y) >> 31) << 1) | ((__float_as_uint(v.z) >> 31) << 2) |
+               ((__float_as_uint(v.w) >> 31) << 3);
+    }
+    __device__ __forceinline__ bool rate1(uint32_t& T4) {
+        const float mn = fminf(fminf(fabsf(r4.x), fabsf(r4.y)), fminf(fabsf(r4.z), fabsf(r4.w)));
+        const float hi = met + mn;
+        if (!__all_sync(FULL, __float_as_uint(hi) > maxmet)) return false;
+        T4 = signs4(r4);
+        return true;
+    }
+    // the same for a whole size-8 subtree (its input LLRs in vA, vB): partial sums [sA ^ sB, sB]
+    __device__ __forceinline__ bool rate1_8(uint32_t& T4) {
+        const float ma = fminf(fminf(fabsf(vA.x), fabsf(vA.y)), fminf(fabsf(vA.z), fabsf(vA.w)));
+        const float mb = fminf(fminf(fabsf(vB.x), fabsf(vB.y)), fminf(fabsf(vB.z), fabsf(vB.w)));
+        const float hi = met + fminf(ma, mb);
+        if (!__all_sync(FULL, __float_as_uint(hi) > maxmet)) return false;
+        const uint32_t sA = signs4(vA), sB = signs4(vB);
+        w0 = (w0 & ~0xF0u) | ((sA ^ sB) << 4);
+        T4 = sB;
+        return true;
+    }
+#else
     // all four positions information bits, list full: assume every phase takes the fast exit (each
     // path keeps its likelier bit, metrics unchanged), compute the four leaf LLRs lane-locally and
     // verify all four exits with ONE vote: min_t (met + |A_t|) = met + min_t |A_t| must exceed the
@@ -901,6 +938,7 @@ struct Dec {
         T4 = ((t01 ^ t23) >> 31) | (((s1 ^ s3) >> 31) << 1) | ((t23 >> 31) << 2) | ((s3 >> 31) << 3);
         return true;
     }
+#endif
 
     // any pattern, phase by phase; ib: information flags of the four phases, bit 4 = next phase
     __device__ __forceinline__ uint32_t seq4(uint32_t ib) {
@@ -926,8 +964,12 @@ struct Dec {
     // ib: information flags of the 8 phases, bit 8 = first phase of the next subtree.
     __device__ __forceinline__ void leaf8(int blk, uint32_t ib) {
         uint32_t T4 = 0;
+        int h = 0;
+#if PCB_Q_R1FAST
+        if ((ib & 0xFFu) == 0xFFu && ninfo >= LB && rate1_8(T4)) h = 2;
+#endif
 #pragma unroll 1
-        for (int h = 0; h < 2; h++, ib >>= 4) {
+        for (; h < 2; h++, ib >>= 4) {
             if (h == 0) {                    // own arrays all the way down: layer LBOT comes in registers
                 r4 = ff4(vA, vB);
             } else {                         // the size-8 layer may be a parent's
