@@ -61,6 +61,12 @@
 #ifndef PCB_Q_R1FAST
 #define PCB_Q_R1FAST 1     // rate-1 nodes of size 4 and 8 from the signs and the smallest magnitude of their inputs
 #endif
+#ifndef PCB_Q_MERGE
+#define PCB_Q_MERGE 1
+#endif
+#ifndef PCB_Q_MERGE_SMALL
+#define PCB_Q_MERGE_SMALL 0
+#endif
 #ifndef PCB_Q_CPA
 #define PCB_Q_CPA 1
 #endif
@@ -117,7 +123,9 @@ struct Geo {
     static_assert(PFLOATS - STAGE_OFF >= (GL3 ? N / 2 : N), "staging area too small");
     static constexpr int XW = LL * XHS;                      // final codeword estimates (alias the LLR region)
     static_assert(XW <= PFLOATS, "final codeword estimates do not fit the LLR region");
-    static constexpr int FRAME_WORDS = PFLOATS + LL * HS + 2 * LL;   // LLRs, heaps, 2L candidate keys
+    // select by merging two sorted lists of L (fork_slow): 4L words of key scratch instead of 2L
+    static constexpr bool MERGE = LL >= 16 ? PCB_Q_MERGE : PCB_Q_MERGE_SMALL;
+    static constexpr int FRAME_WORDS = PFLOATS + LL * HS + (MERGE ? 4 : 2) * LL;   // LLRs, heaps, candidate keys
     static constexpr int OFF_H = PFLOATS;
     static constexpr int OFF_KEYS = PFLOATS + LL * HS;
     static constexpr int TOTAL = FPW * FRAME_WORDS * 4;
@@ -269,7 +277,7 @@ __device__ __forceinline__ bool single_swap(const PathState& s, float A0, int la
 
 // continuePaths_UnfrozenBit (SCLDecoderMinsum.cpp:315-400) without the fast exit, for the four
 // frames of the warp at once (every step is confined to the 8-lane group of a frame).
-template <int LL>
+template <int LL, bool MERGE>
 __device__ __noinline__ PathState fork_slow(PathState s, float A0, int lane, int ninfo, uint32_t* keys) {
     constexpr int FPW = 32 / LL, LB = LL == 4 ? 2 : LL == 8 ? 3 : LL == 16 ? 4 : 5;
     constexpr unsigned GM = LL == 32 ? 0xffffffffu : (1u << LL) - 1;
@@ -284,22 +292,66 @@ __device__ __noinline__ PathState fork_slow(PathState s, float A0, int lane, int
         r = take ? (3u | ((uint32_t)(gsh + 2 * pbase - 1 - p) << 2)) : ((uint32_t)lane << 2);
     } else if (single_swap<LL>(s, A0, lane, r)) {
     } else {
-        // stable rank of both candidates among the 16 of the frame; keys are stored complemented:
-        // key < kc  <=>  carry-out of (kc + ~key)
-        *reinterpret_cast<uint2*>(keys + 2 * p) = make_uint2(~__float_as_uint(pf0), ~__float_as_uint(pf1));
-        __syncwarp();
         const uint32_t k0 = __float_as_uint(pf0), k1 = __float_as_uint(pf1);
-        int c0 = 0, c1 = 0, d0 = 0, d1 = 0;   // two accumulators per candidate: shorter dependent chains
+        bool keep0, keep1;
+        unsigned b0, b1;
 #define PCB_LT(c, x, k) asm("{ .reg .u32 t; add.cc.u32 t, %1, %2; addc.u32 %0, %0, 0; }" : "+r"(c) : "r"(x), "r"(k));
+        if constexpr (MERGE) {
+        // The survivors are the L smallest of the 2L candidates in the order (value, candidate number
+        // 2p + b) (:342-371: everything below the median, then ties at the median in candidate
+        // order).  Every path has a smaller candidate lo (its metric) and a larger one hi; sort the
+        // L lo's and the L hi's separately (ties inside a list fall in path order, which is the
+        // candidate order) and merge: with a_0 < .. < a_L-1 the lo's and b_0 < .. the hi's, exactly
+        // c = #{i : b_i < a_(L-1-i)} hi's survive (the predicate is monotone in i), together with
+        // the L - c smallest lo's.  2 x L x L compares per frame instead of 2L x 2L.
+        const bool lob = k1 < k0;                 // bit of the smaller candidate (bit 0 when equal)
+        const uint32_t lov = lob ? k1 : k0, hiv = lob ? k0 : k1;
+        keys[p] = ~lov;                           // complemented: key < kc <=> carry-out of (kc + ~key)
+        keys[LL + p] = ~hiv;
+        __syncwarp();
+        int ca = 0, cb = 0, da = 0, db = 0;
+#pragma unroll 4
+        for (int q = 0; q < LL / 4; q++) {
+            const uint4 ka = *reinterpret_cast<const uint4*>(keys + 4 * q);
+            const uint4 kb = *reinterpret_cast<const uint4*>(keys + LL + 4 * q);
+            PCB_LT(ca, ka.x, lov) PCB_LT(cb, kb.x, hiv) PCB_LT(da, ka.y, lov) PCB_LT(db, kb.y, hiv)
+            PCB_LT(ca, ka.z, lov) PCB_LT(cb, kb.z, hiv) PCB_LT(da, ka.w, lov) PCB_LT(db, kb.w, hiv)
+        }
+        int ra = ca + da, rb = cb + db;           // ranks inside the two lists, so far without the ties
+        // the strict ranks of a list are a permutation unless two of its values are equal (rare)
+        if ((__reduce_or_sync(FULL, 1u << (gsh + ra)) & __reduce_or_sync(FULL, 1u << (gsh + rb))) != FULL) {
+            const unsigned below = (1u << p) - 1;
+            ra += __popc((__match_any_sync(FULL, lov) >> gsh) & GM & below);
+            rb += __popc((__match_any_sync(FULL, hiv) >> gsh) & GM & below);
+        }
+        __syncwarp();                             // the keys are consumed
+        uint2* SA = reinterpret_cast<uint2*>(keys);
+        uint2* SB = SA + LL;
+        SA[LL - 1 - ra] = make_uint2(lov, 2u * p + (lob ? 1u : 0u));      // lo's, descending
+        SB[rb] = make_uint2(hiv, 2u * p + (lob ? 0u : 1u));               // hi's, ascending
+        __syncwarp();
+        const uint2 av = SA[p], bv = SB[p];
+        const bool hi_first = bv.x < av.x || (bv.x == av.x && bv.y < av.y);
+        const int c = __popc((__ballot_sync(FULL, hi_first) >> gsh) & GM);
+        const bool keep_lo = ra < LL - c, keep_hi = rb < c;
+        keep0 = lob ? keep_hi : keep_lo;
+        keep1 = lob ? keep_lo : keep_hi;
+        b0 = (__ballot_sync(FULL, keep0) >> gsh) & GM;
+        b1 = (__ballot_sync(FULL, keep1) >> gsh) & GM;
+        } else {
+        // stable rank of both candidates among the 2L of the frame; keys are stored complemented:
+        // key < kc  <=>  carry-out of (kc + ~key)
+        *reinterpret_cast<uint2*>(keys + 2 * p) = make_uint2(~k0, ~k1);
+        __syncwarp();
+        int c0 = 0, c1 = 0, d0 = 0, d1 = 0;   // two accumulators per candidate: shorter dependent chains
 #pragma unroll 4
         for (int q = 0; q < LL / 2; q++) {
             const uint4 kk = *reinterpret_cast<const uint4*>(keys + 4 * q);
             PCB_LT(c0, kk.x, k0) PCB_LT(c1, kk.x, k1) PCB_LT(d0, kk.y, k0) PCB_LT(d1, kk.y, k1)
             PCB_LT(c0, kk.z, k0) PCB_LT(c1, kk.z, k1) PCB_LT(d0, kk.w, k0) PCB_LT(d1, kk.w, k1)
         }
-#undef PCB_LT
-        bool keep0 = c0 + d0 < LL, keep1 = c1 + d1 < LL;
-        unsigned b0 = (__ballot_sync(FULL, keep0) >> gsh) & GM, b1 = (__ballot_sync(FULL, keep1) >> gsh) & GM;
+        keep0 = c0 + d0 < LL; keep1 = c1 + d1 < LL;
+        b0 = (__ballot_sync(FULL, keep0) >> gsh) & GM; b1 = (__ballot_sync(FULL, keep1) >> gsh) & GM;
         const bool tie = __popc(b0) + __popc(b1) != LL;        // a tie straddles the median (:362-371)
         if (__any_sync(FULL, tie)) {
             const unsigned top = max(keep0 ? k0 : 0u, keep1 ? k1 : 0u);
@@ -316,6 +368,8 @@ __device__ __noinline__ PathState fork_slow(PathState s, float A0, int lane, int
             b0 = (__ballot_sync(FULL, keep0) >> gsh) & GM;
             b1 = (__ballot_sync(FULL, keep1) >> gsh) & GM;
         }
+        }
+#undef PCB_LT
         const unsigned nonem = ~(b0 | b1) & GM, bothm = b0 & b1;
         if ((nonem >> p) & 1) {
             // killed slots are pushed ascending (:372-376) and popped by the cloning parents in
@@ -825,7 +879,7 @@ struct Dec {
             if (__all_sync(FULL, __float_as_uint(hi) > maxmet)) return A0 < 0.f ? 1 : 0;   // max met < min hi
         }
         PathState s{met, pidx, cidx, w0, 0, r4, r2_0, r2_1, maxmet};
-        s = fork_slow<LL>(s, A0, lane, ninfo, keys);
+        s = fork_slow<LL, G::MERGE>(s, A0, lane, ninfo, keys);
         met = s.met; pidx = s.pidx; cidx = s.cidx; w0 = s.w0;
         r4 = s.r4; r2_0 = s.r2_0; r2_1 = s.r2_1; maxmet = s.maxmet;
         if (ninfo < LB) ninfo++;
