@@ -1104,8 +1104,8 @@ __global__ void __launch_bounds__(32, (LL != 8 ? 1 : q8::Geo<M, LL>::GL4 && M ==
         D.fbase = FPW * quad; D.Bm1 = A.B - 1;
 #pragma unroll
         for (int f = 0; f < 4; f++) fr[f] = min(FPW * quad + f, A.B - 1);
-        // take the next quad now and pull it into L2 while this one is decoded (its first touch is
-        // otherwise a DRAM-latency stall with nothing else to do)
+        // take the next quad now (an L2 prefetch of its channel values here, or late in the frame,
+        // stopped paying once the top stage staged them with cp.async: 34.15 / 33.0 vs 34.23 M)
         int next_quad = 0;
 #ifdef PCB_Q_STATIC
         next_quad = quad + (int)gridDim.x;
@@ -1113,12 +1113,6 @@ __global__ void __launch_bounds__(32, (LL != 8 ? 1 : q8::Geo<M, LL>::GL4 && M ==
         if (lane == 0) next_quad = (int)gridDim.x + atomicAdd(S.next_quad, 1);
         next_quad = __shfl_sync(FULL, next_quad, 0);
 #endif
-        if (FPW * next_quad + FPW <= A.B) {
-            const char* nx = reinterpret_cast<const char*>(ybase + (size_t)FPW * next_quad * n);
-#pragma unroll 1
-            for (int ln = lane; ln < (int)(FPW * n * sizeof(YT) / 128); ln += 32)
-                asm volatile("prefetch.global.L2 [%0];" ::"l"(nx + (size_t)ln * 128));
-        }
         D.met = 0.f; D.maxmet = 0; D.pidx = 0; D.cidx = 0; D.w0 = 0; D.ninfo = 0;
         D.r4 = make_float4(0.f, 0.f, 0.f, 0.f); D.r2_0 = D.r2_1 = D.A0 = 0.f;
 #pragma unroll 1
