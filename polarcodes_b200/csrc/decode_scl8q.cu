@@ -1,24 +1,30 @@
-// List-8 SCL min-sum decoder, FOUR FRAMES PER WARP (SCLDecoderMinsum.cpp:225-478 semantics,
-// bit-exact with decode_generic.cu): lane = f*8 + p, f the frame of the quad (0..3) and p the
-// path slot (0..7).  One lane owns one path of one frame from the channel values to the CRC.
+// SCL min-sum decoder with ONE LANE PER PATH (SCLDecoderMinsum.cpp:225-478 semantics, bit-exact
+// with decode_generic.cu), templated on the list size L = 8, 16, 32: a frame takes L lanes and a
+// warp decodes 32 / L frames in lockstep, lane = f*L + p with f the frame of the group and p the
+// path slot.  One lane owns one path of one frame from the channel values to the CRC.  The
+// comments below are written for the headline case L = 8 (four frames per warp, a "quad").
 //
 // Why this mapping: every frame of a batch shares the frozen pattern, so the
-// control flow of the 1024 phases is identical for all frames and a warp can run four of them
+// control flow of the n phases is identical for all frames and a warp can run several of them
 // in lockstep.  All per-path scalar work (leaf LLRs of the size-4/2/1 layers, metric update,
-// fork bookkeeping, partial-sum words, CRC) then uses 32 of 32 lanes instead of 8 of 32, and
-// every address computation / loop / branch of the upper layers is paid once per four frames.
+// fork bookkeeping, partial-sum words, CRC) then uses 32 of 32 lanes instead of L of 32, and
+// every address computation / loop / branch of the upper layers is paid once per warp.
 //
-//  * LLR layers 3..m-3 (sizes n/8 .. 8) live in shared memory as [frame][layer][slot][j] with a
-//    slot stride of size+4 floats: the 8 lanes of a frame (a quarter-warp of an LDS.128) hit 8
-//    distinct 16-byte bank groups for any permutation of source slots (lazy reads).
+//  * LLR layers LS..m-3 (sizes .. 8) live in shared memory as [frame][layer][slot][j] with a
+//    slot stride of size+4 floats: the 8 lanes of a quarter-warp LDS.128 hit 8 distinct 16-byte
+//    bank groups for any permutation of 8 source slots (lazy reads).  For n >= 1024 the layers
+//    3, 4 (and 5 for n = 2048 with L >= 16) live in a per-block global scratch that stays in L2.
 //  * layers 0, 1, 2 are never stored: layer 3 is computed from the channel values with three
 //    fused levels every n/8 phases.  In the first half of the frame layer 1 = f(y, y') does not
-//    depend on the path, so the eight lanes of a frame compute it once, cooperatively, while
-//    staging (the staging area is the region of layers 4.., dead at those phases).
+//    depend on the path, so the lanes of a frame compute it once, cooperatively, while staging
+//    (the staging area is the region of the shared-memory layers, dead at those phases); in the
+//    second half the channel values are staged with cp.async two chunks ahead of the arithmetic.
 //  * layers of size 4, 2, 1 are registers of the owning lane; a clone copies the live ones with
-//    shuffles inside its 8-lane group.
+//    shuffles inside its group of L lanes.
 //  * lazy copy as in decode_scl8.cu: slot p writes its own arrays, a per-path word holds the slot
-//    to read each layer from.
+//    to read each layer from (log2 L bits per layer).
+//  * rate-0, repetition and rate-1 nodes of size 4 (rate-1 also of size 8) have routines that
+//    produce the results of the reference's phase-by-phase loop without running it.
 #include "decode_common.cuh"
 #include "decode_launch.h"
 
