@@ -245,7 +245,8 @@ static int configure(pcb_handle* h) {
     if (h->sc32) {
         // every resident warp keeps a 64 KB (fp64) / 32 KB (fp32) level buffer that has to stay in L2:
         // measured optimum 8 / 14 warps per SM (more warps spill it to DRAM)
-        const int cap = sc32_is_big(h->m) ? 6 : h->fp64 ? 8 : 14;   // n > 2048: DRAM-bound, each warp owns n * 32 values of scratch
+        int cap = sc32_is_big(h->m) ? 9 : h->fp64 ? 8 : 14;   // n > 2048: DRAM-bound, each warp owns n * 32 values of scratch (measured: 4/6/9/12 warps -> 0.54/0.64/0.78/0.72 M frames/s)
+        if (const char* cenv = getenv("PCB_S_CAP")) { if (atoi(cenv) > 0) cap = atoi(cenv); }   // experiment: another cap
         if (h->sc32_bps > cap) h->sc32_bps = cap;
         const char* benv = getenv("PCB_S_BPS");         // experiment: fewer resident warps per SM
         if (benv && atoi(benv) > 0 && atoi(benv) < h->sc32_bps) h->sc32_bps = atoi(benv);

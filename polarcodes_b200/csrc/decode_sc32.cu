@@ -28,6 +28,12 @@
 #ifndef PCB_S_FE
 #define PCB_S_FE 5       // log2 of the largest stored layer: 32 (6: twice the shared memory per warp, half the fused work)
 #endif
+#ifndef PCB_S_BIGFUSE
+#define PCB_S_BIGFUSE 1  // n > 2048: two levels per pass (the f that follows a level never re-reads it; three per pass: slower)
+#endif
+#ifndef PCB_S_BIGTU
+#define PCB_S_BIGTU 32   // n > 2048: outputs per loop iteration of a level (twice as many loads in flight)
+#endif
 #ifndef PCB_S_TOPU
 #define PCB_S_TOPU 8     // outputs of the fused top stage per loop iteration (16 << log2 of it channel loads in flight)
 #endif
@@ -235,8 +241,10 @@ __global__ void __launch_bounds__(32) decode_sc32_kernel(const __grid_constant__
 // ---- n > 2048 (SC min-sum at N = 32768, SURVEY config E): same lane = frame mapping, but every
 // level above size 32 is stored, in a per-block global store LV[level][x][lane] (n - 32 rows of 32
 // lanes), and so is the partial-sum heap (n/32 rows of 32 words).  A level is written once and read
-// once or twice, always as whole coalesced rows; the decoder is DRAM-bound (about 3n values moved
-// per level and frame).  Frozen pattern from global memory (warp-uniform loads).
+// once or twice, always as whole coalesced rows; the decoder is DRAM-bound.  Two levels are produced
+// per pass (the f-level that follows a level takes it from registers, so a level is read back only
+// by the g of its right child: about 2.25 n values moved per level and frame instead of 3 n), with
+// 64 loads in flight per lane.  Frozen pattern from global memory (warp-uniform loads).
 struct BigArgs {
     DecodeArgs a;
     const void* yt;
@@ -255,7 +263,7 @@ __global__ void __launch_bounds__(32) decode_sc32big_kernel(const __grid_constan
     T* P = reinterpret_cast<T*>(smem_raw);                       // sizes 32, 16, 8: rows 0, 32, 48
     T* LV = reinterpret_cast<T*>(S.lv) + (size_t)blockIdx.x * (n - 32) * 32 + lane;
     uint32_t* H = S.heap + (size_t)blockIdx.x * NW * 32 + lane;
-    constexpr int TU = 8;
+    constexpr int TU = PCB_S_BIGTU;
     auto lvl = [&](int v) -> T* { return LV + (size_t)(n - (n >> (v - 1))) * 32; };   // level v >= 1, n >> v rows
 
     for (int tile = blockIdx.x; tile < S.ntiles; tile += gridDim.x) {
@@ -268,10 +276,42 @@ __global__ void __launch_bounds__(32) decode_sc32big_kernel(const __grid_constan
             // levels v0 .. LT: the first one is a g-level (except at the very start), the rest f-levels
             const int v0 = b32 ? LT - (__ffs(b32) - 1) : 1;
 #pragma unroll 1
-            for (int v = v0; v <= LT; ++v) {
+            for (int v = v0; v <= LT;) {
                 const int Sz = n >> v;
                 const bool isg = b32 && v == v0;
                 const T* src = v == 1 ? yt : lvl(v - 1);
+#if PCB_S_BIGFUSE
+                if (v < LT) {
+                    // levels v and v+1 in one pass: outputs x and x + Sz/2 of level v are produced
+                    // together, stored (the g of the right child reads them later) and combined on the
+                    // spot into output x of level v+1, which is therefore never read back for its f
+                    constexpr int TF = TU / 2;
+                    const int Hs = Sz >> 1;
+                    T* d1 = lvl(v);
+                    T* d2 = v + 1 == LT ? P + lane : lvl(v + 1);
+#pragma unroll 1
+                    for (int x = 0; x < Hs; x += TF) {
+                        T a0[TF], b0[TF], a1[TF], b1[TF];
+#pragma unroll
+                        for (int i = 0; i < TF; i++) {
+                            a0[i] = src[(size_t)(x + i) * 32]; b0[i] = src[(size_t)(x + i + Sz) * 32];
+                            a1[i] = src[(size_t)(x + i + Hs) * 32]; b1[i] = src[(size_t)(x + i + Hs + Sz) * 32];
+                        }
+                        const uint32_t cw0 = isg ? H[(size_t)((Sz + x) >> 5) * 32] >> (x & 31) : 0u;
+                        const uint32_t cw1 = isg ? H[(size_t)((Sz + x + Hs) >> 5) * 32] >> (x & 31) : 0u;
+#pragma unroll
+                        for (int i = 0; i < TF; i++) {
+                            const T o0 = isg ? opg<EXACT, T>(a0[i], b0[i], (int)((cw0 >> i) & 1u)) : opf<EXACT, T>(a0[i], b0[i]);
+                            const T o1 = isg ? opg<EXACT, T>(a1[i], b1[i], (int)((cw1 >> i) & 1u)) : opf<EXACT, T>(a1[i], b1[i]);
+                            d1[(size_t)(x + i) * 32] = o0;
+                            d1[(size_t)(x + i + Hs) * 32] = o1;
+                            d2[(size_t)(x + i) * 32] = opf<EXACT, T>(o0, o1);
+                        }
+                    }
+                    v += 2;
+                    continue;
+                }
+#endif
                 T* dl = v == LT ? P + lane : lvl(v);          // rows of 32 lanes either way
 #pragma unroll 1
                 for (int x = 0; x < Sz; x += TU) {
@@ -285,6 +325,7 @@ __global__ void __launch_bounds__(32) decode_sc32big_kernel(const __grid_constan
                         dl[(size_t)(x + i) * 32] = o;
                     }
                 }
+                ++v;
             }
 #pragma unroll 1
             for (int b8 = 0; b8 < 4; ++b8) {
