@@ -740,6 +740,12 @@ static size_t mc_batch(pcb_handle* h) {
     if (env) b = (size_t)atol(env);
     const size_t minb = h->fast8 ? (size_t)fast_blocks(h) * (h->quad ? scl8q_frames_per_warp(h->L) : 1) : (size_t)max_blocks(h) * h->wpb;
     if (b < minb) b = minb;
+    if (h->sc32 && !env) {
+        // lane-per-frame kernels walk the tiles of 32 frames with a static stride: whole waves of
+        // the resident grid (one tile per warp and wave), at least one (n = 32768: 42 624 frames)
+        const size_t wave = (size_t)h->sm_count * h->sc32_bps * 32;
+        b = (b + wave - 1) / wave * wave;
+    }
     return b;
 }
 

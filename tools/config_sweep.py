@@ -14,7 +14,7 @@ CONFIGS = [
     ("B  SC exact  N=256   K=128", 256, 128, 0, 1, pb.SC, pb.STRICT, 1 << 18),
     ("C  SCL-8     N=1024  K=512 crc=0", 1024, 512, 0, 8, pb.SCLMINSUM, pb.STRICT, 1 << 18),
     ("C' SCL-8     N=1024  K=512 crc=16", 1024, 512, 16, 8, pb.SCLMINSUM, pb.STRICT, 1 << 18),
-    ("D  SCL-32    N=2048  K=1024 crc=0", 2048, 1024, 0, 32, pb.SCLMINSUM, pb.STRICT, 1 << 14),
+    ("D  SCL-32    N=2048  K=1024 crc=0", 2048, 1024, 0, 32, pb.SCLMINSUM, pb.STRICT, 1 << 16),
     ("E  SCMinsum  N=32768 K=16384 (fp64 strict)", 32768, 16384, 0, 1, pb.SCMINSUM, pb.STRICT, 1 << 16),
 ]
 SCALE = float(os.environ.get("PCB_SWEEP_SCALE", "1"))   # batch-size multiplier
