@@ -1124,8 +1124,7 @@ __global__ void __launch_bounds__(32, (LL != 8 ? 1 : q8::Geo<M, LL>::GL4 && M ==
 #pragma unroll 1
         for (int blk = 0; blk < n / 8; ++blk) {
             // the 8 information flags of this subtree and, as bit 8, the first one of the next
-            const uint32_t iw = S.info_w[blk >> 2], iwn = S.info_w[(blk + 1) >> 2];
-            const uint32_t ib = ((iw >> (8 * (blk & 3))) & 0xFF) | (((iwn >> (8 * ((blk + 1) & 3))) & 1) << 8);
+            const uint32_t ib = __funnelshift_r(S.info_w[blk >> 2], S.info_w[(blk >> 2) + 1], 8 * (blk & 3)) & 0x1FFu;
             D.upper(blk, ybase, fr);
             D.leaf8(blk, ib);
         }
