@@ -216,7 +216,7 @@ __device__ __forceinline__ unsigned group_max(unsigned x, int fme) {
 // lane per path: T holds the last 32 bits; the destination layer m-d2 sits at heap words
 // [D/32, 2D/32) of this slot; layer 0 (the final codeword estimate, written at the very last
 // phase) goes to the then-dead LLR region instead.  Out of line: taken once per four subtrees.
-template <int LB>
+template <int LB, bool GH>
 __device__ __noinline__ uint32_t heap_combine(uint32_t* Pw, uint32_t* H, uint32_t* HG, int hs, int splitw, int p, uint32_t cidx, int d2, uint32_t T, int m) {
     constexpr int LL = 1 << LB;
     const int D = 1 << d2, NW = 1 << (m - 5);
@@ -225,7 +225,7 @@ __device__ __noinline__ uint32_t heap_combine(uint32_t* Pw, uint32_t* H, uint32_
     uint32_t* dp;
     int ds = 1;
     if (d2 == m) dp = Pw + p * (NW + 1) - NW;
-    else if (D / 32 >= splitw) { dp = HG + p - splitw * LL; ds = LL; }
+    else if (GH && D / 32 >= splitw) { dp = HG + p - splitw * LL; ds = LL; }
     else dp = H + p * hs;
     __syncwarp();
     dp[(2 * D / 32 - 1) * ds] = T;
@@ -235,7 +235,7 @@ __device__ __noinline__ uint32_t heap_combine(uint32_t* Pw, uint32_t* H, uint32_
         const int sc = (cidx >> (LB * (layc - 1))) & (LL - 1);
         const uint32_t* sp;
         int ss = 1;
-        if (nw >= splitw) { sp = HG + sc + (nw - splitw) * LL; ss = LL; }
+        if (GH && nw >= splitw) { sp = HG + sc + (nw - splitw) * LL; ss = LL; }
         else sp = H + sc * hs + nw;
 #pragma unroll 1
         for (int kk = 0; kk < nw; kk++)
@@ -910,7 +910,7 @@ struct Dec {
         T = (((w0 >> 8) ^ T) & 0xFFu) | (T << 8);
         if (d2 == 4) { w0 = (w0 & 0x0000FFFFu) | (T << 16); return; }
         T = (((w0 >> 16) ^ T) & 0xFFFFu) | (T << 16);
-        cidx = heap_combine<LB>(reinterpret_cast<uint32_t*>(P), H, HG, G::HS, G::SPLITW, p, cidx, d2, T, M);
+        cidx = heap_combine<LB, G::GH>(reinterpret_cast<uint32_t*>(P), H, HG, G::HS, G::SPLITW, p, cidx, d2, T, M);
     }
 
     // ---- the four phases of one size-4 subtree (its LLRs in r4, pairs (x,z) and (y,w)) --------
