@@ -45,7 +45,8 @@ cudaError_t launch_decode_sc32(const DecodeArgs& a, const uint32_t* info_w, cons
 // lane-per-path list kernel, 32 / L frames per warp (decode_scl8q.cu): L = 8 and L = 32
 bool scl8q_supported(int m, int L);
 int scl8q_frames_per_warp(int L);
-cudaError_t launch_decode_scl8q(const DecodeArgs& a, int L, const uint32_t* info_w, void* l3_scratch, int* next_quad, int blocks, cudaStream_t st);
+cudaError_t launch_decode_scl8q(const DecodeArgs& a, int L, const uint32_t* info_w, const uint32_t* synd, uint32_t synd_c0, void* l3_scratch, int* next_quad,
+                                int blocks, cudaStream_t st);
 size_t scl8q_scratch_per_block(int m, int L);
 cudaError_t scl8q_occupancy(int m, int L, int* bps, int* warp_bytes);
 }  // namespace pcb
@@ -162,6 +163,8 @@ struct pcb_handle {
     size_t sc32_bits_cap = 0;
     size_t yt_cap = 0;
     void* d_qscratch = nullptr;     // quad kernel: layer-3 arrays of every resident block (stays in L2)
+    uint32_t* d_synd = nullptr;     // quad kernel: rows of the CRC syndrome matrix (16 x n/32 words), see pcb_set_code
+    uint32_t synd_c0 = 0;
     float* d_y32 = nullptr;         // quad kernel: double channel values converted once per batch
     size_t y32_cap = 0;
     int* d_redo = nullptr;          // [0] = count, [1] = work counter of the quad kernel, [2..] = frame list
@@ -367,7 +370,7 @@ void pcb_destroy(pcb_handle* h) {
         if (h->ev_out[s]) cudaEventDestroy(h->ev_out[s]);
     }
     cudaFree(h->d_ymc); cudaFree(h->d_tx); cudaFree(h->d_dec); cudaFree(h->d_counters);
-    cudaFree(h->d_eu); cudaFree(h->d_ex); cudaFree(h->d_redo); cudaFree(h->d_qscratch); cudaFree(h->d_y32); cudaFree(h->d_yt); cudaFree(h->d_sc32_scratch); cudaFree(h->d_sc32_bits);
+    cudaFree(h->d_eu); cudaFree(h->d_ex); cudaFree(h->d_redo); cudaFree(h->d_qscratch); cudaFree(h->d_synd); cudaFree(h->d_y32); cudaFree(h->d_yt); cudaFree(h->d_sc32_scratch); cudaFree(h->d_sc32_bits);
     cudaFreeHost(h->h_stage[0]); cudaFreeHost(h->h_stage[1]); delete h->narrow;
     if (h->t0) cudaEventDestroy(h->t0);
     if (h->t1) cudaEventDestroy(h->t1);
@@ -400,6 +403,33 @@ int pcb_set_code(pcb_handle* h, const int* frozen_mask, double sigma) {
     CK(cudaMemcpyAsync(h->d_info_pos, pos.data(), (size_t)n * 2, cudaMemcpyHostToDevice, h->sc));
     CK(cudaStreamSynchronize(h->sc));
     h->h_info_w = im; h->h_fv_w = fv;
+    if (h->decoder == 3 && h->crc > 0 && h->quad) {
+        // The final selection (SCLDecoderMinsum.cpp:442-472) keeps the first slot whose CRC passes:
+        // crc(sol[0..k)) == the bits sol[k..k+crc), with sol the information positions of
+        // u = x F^(x)m.  Both sides are GF(2)-linear in the codeword estimate x up to the constant
+        // the CRC register's initial value contributes, so the test is a syndrome: slot passes
+        // iff S x == c0, c0 = f(0), column i of S = f(e_i) ^ f(0) for
+        // f(x) = crc(sol(x)[0..k)) ^ (sol(x)[k..k+crc) read MSB first).  u(e_i)_j = 1 iff j is a
+        // bitwise subset of i.  The list kernel evaluates S x with 16 parities per word.
+        const int K = h->k, C = h->crc, KC = K + C;
+        std::vector<int> sol(KC, 0);
+        auto fval = [&]() {
+            unsigned r = C == 8 ? pcb_crc8(sol.data(), K) : pcb_crc16(sol.data(), K), rx = 0;
+            for (int t = 0; t < C; t++) rx = (rx << 1) | (unsigned)sol[K + t];
+            return r ^ rx;
+        };
+        const unsigned c0 = fval();
+        std::vector<uint32_t> S((size_t)16 * NW, 0);
+        for (int i = 0; i < n; i++) {
+            for (int j = 0; j < KC; j++) sol[j] = ((int)pos[j] & i) == (int)pos[j];
+            const unsigned col = fval() ^ c0;
+            for (int t = 0; t < C; t++)
+                if ((col >> t) & 1) S[(size_t)t * NW + (i >> 5)] |= 1u << (i & 31);
+        }
+        if (!h->d_synd) CK(cudaMalloc(&h->d_synd, (size_t)16 * NW * 4));
+        CK(cudaMemcpy(h->d_synd, S.data(), (size_t)16 * NW * 4, cudaMemcpyHostToDevice));
+        h->synd_c0 = c0;
+    }
     // the tuned list-8 kernel assumes all-zero frozen values (what the reference uses,
     // PolarCodes.cpp:127); a mask with frozen ones runs on the generic kernel
     bool any_fv = false;
@@ -485,7 +515,7 @@ static cudaError_t launch(pcb_handle* h, const DecodeArgs& a, cudaStream_t st) {
                 cudaError_t e1 = cudaMalloc(&h->d_qscratch, spb * (size_t)fast_blocks(h));
                 if (e1 != cudaSuccess) return e1;
             }
-            e = launch_decode_scl8q(f, h->L, h->h_info_w.data(), h->d_qscratch, h->d_redo + 1, nq < fast_blocks(h) ? nq : fast_blocks(h), st);
+            e = launch_decode_scl8q(f, h->L, h->h_info_w.data(), h->d_synd, h->synd_c0, h->d_qscratch, h->d_redo + 1, nq < fast_blocks(h) ? nq : fast_blocks(h), st);
         } else {
             e = launch_decode_scl8(f, h->h_info_w.data(), h->h_fv_w.data(), a.B < fast_blocks(h) ? a.B : fast_blocks(h), st);
         }

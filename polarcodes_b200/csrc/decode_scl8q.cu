@@ -1048,23 +1048,6 @@ struct Dec {
     }
 };
 
-// Resources.cpp:29-62 (poly 0x31) and :73-106 (poly 0x1021) regenerated from the polynomials
-struct CrcTable { unsigned short v[256]; };
-constexpr CrcTable make_crc(int bits) {
-    CrcTable t{};
-    for (int i = 0; i < 256; i++) {
-        unsigned r = bits == 8 ? (unsigned)i : ((unsigned)i << 8);
-        for (int b = 0; b < 8; b++) {
-            if (bits == 8) r = (r & 0x80) ? ((r << 1) ^ 0x31) & 0xFF : (r << 1) & 0xFF;
-            else r = (r & 0x8000) ? ((r << 1) ^ 0x1021) & 0xFFFF : (r << 1) & 0xFFFF;
-        }
-        t.v[i] = (unsigned short)r;
-    }
-    return t;
-}
-__constant__ CrcTable c_crc8 = make_crc(8);
-__constant__ CrcTable c_crc16 = make_crc(16);
-
 }  // namespace q8
 
 // Kernel parameters: the generic arguments plus the frozen pattern itself (warp-uniform control
@@ -1074,6 +1057,11 @@ struct Scl8qArgs {
     uint32_t info_w[65];   // n <= 2048, one zero word behind the last
     int* next_quad;        // work counter (zero at launch): quad gridDim.x + counter is the next one not yet taken
     float4* l3;            // n >= 1024: global scratch of the layer-3 arrays, Geo::L3_BLOCK_FLOAT4 per block
+    // CRC check as a syndrome of the codeword estimate: crc(info bits of x F) ^ (appended CRC bits of
+    // x F) is affine in x, so slot q passes iff S x_q == c0 with S a crc x n bit matrix that depends
+    // on the code only (row t as n/32 words at synd[t * n/32 ..)) and c0 the CRC of the zero message.
+    const uint32_t* synd;
+    uint32_t synd_c0;
 };
 
 // One warp per block (blockDim.x == 32); a block decodes quads of frames.
@@ -1135,7 +1123,11 @@ __global__ void __launch_bounds__(32, (LL != 8 ? 1 : q8::Geo<M, LL>::GL4 && M ==
         // compressed (Hacker's Delight 7-4) and OR-ed into the packed output at the bit offset that
         // the information counts of the words before it give.
         constexpr int NW = G::NW, XHS = G::XHS, WPL = NW > 32 ? NW / 32 : 1;
-        const int q0 = A.crc ? 0 : LL - 1;   // without a CRC the reference returns slot L-1 unconditionally
+        uint32_t sm[WPL][16];                // this lane's words of the syndrome rows (zero rows above crc)
+#pragma unroll
+        for (int w = 0; w < WPL; w++)
+#pragma unroll
+            for (int t = 0; t < 16; t++) sm[w][t] = (A.crc > t && lane + 32 * w < NW) ? __ldg(S.synd + t * NW + lane + 32 * w) : 0u;
         uint32_t mk[WPL];
         int off[WPL];
         {
@@ -1154,11 +1146,27 @@ __global__ void __launch_bounds__(32, (LL != 8 ? 1 : q8::Geo<M, LL>::GL4 && M ==
 #pragma unroll 1
         for (int fs = 0; fs < FPW; fs++) {
             uint32_t* X = reinterpret_cast<uint32_t*>(D.W + fs * G::FRAME_WORDS);   // x-hat of every slot (setbit_last, d2 == M)
-            // packed output words of slot q: over the (dead) heaps for slot 0, over the codeword
-            // estimate of slot q - 1 (consumed one iteration earlier) for the others
-            auto eptr = [&](int q) { return q == 0 ? X + G::OFF_H : X + (q - 1) * XHS; };
+            // (:442-472) the first slot, in slot order, whose CRC passes; slot L-1 if none does or
+            // there is no CRC.  The check needs no u-hat: 16 (8) parities of x-hat per lane and word,
+            // one XOR reduction per slot, and it stops at the first slot that passes.
+            int chosen = LL - 1;
+            if (A.crc) {
 #pragma unroll 1
-            for (int q = q0; q < LL; q++) {
+                for (int q = 0; q < LL; q++) {
+                    uint32_t acc = 0;
+#pragma unroll
+                    for (int w = 0; w < WPL; w++) {
+                        const uint32_t x = lane + 32 * w < NW ? X[q * XHS + lane + 32 * w] : 0u;
+#pragma unroll
+                        for (int t = 0; t < 16; t++) acc ^= (uint32_t)(__popc(x & sm[w][t]) & 1) << t;
+                    }
+                    if (__reduce_xor_sync(FULL, acc) == S.synd_c0) { chosen = q; break; }
+                }
+            }
+            // u-hat of the chosen slot: transform, then the information bits compressed into E
+            uint32_t* Ec = X + G::OFF_H;         // the partial-sum heaps are dead by now
+            {
+                const int q = chosen;
                 uint32_t xs[WPL];
 #pragma unroll
                 for (int w = 0; w < WPL; w++) {
@@ -1173,10 +1181,8 @@ __global__ void __launch_bounds__(32, (LL != 8 ? 1 : q8::Geo<M, LL>::GL4 && M ==
                     xs[w] = x;
                 }
                 if constexpr (WPL == 2) xs[0] ^= xs[1];
-                uint32_t* Eq = eptr(q);
-                __syncwarp();                    // every lane has read its words of slot q
 #pragma unroll 1
-                for (int t = lane; t < EW; t += 32) Eq[t] = 0;
+                for (int t = lane; t < EW; t += 32) Ec[t] = 0;
                 __syncwarp();
 #pragma unroll
                 for (int w = 0; w < WPL; w++) {
@@ -1193,31 +1199,13 @@ __global__ void __launch_bounds__(32, (LL != 8 ? 1 : q8::Geo<M, LL>::GL4 && M ==
                     }
                     const int c = __popc(mk[w]), o = off[w];
                     if (c) {
-                        atomicOr(&Eq[o >> 5], x << (o & 31));
-                        if ((o & 31) + c > 32) atomicOr(&Eq[(o >> 5) + 1], x >> (32 - (o & 31)));
+                        atomicOr(&Ec[o >> 5], x << (o & 31));
+                        if ((o & 31) + c > 32) atomicOr(&Ec[(o >> 5) + 1], x >> (32 - (o & 31)));
                     }
                 }
             }
             __syncwarp();
-            bool ok = false;
-            if (A.crc && lane < LL) {
-                const uint32_t* e = eptr(lane);
-                unsigned r = A.crc == 8 ? 0xFFu : 0xFFFFu;
-#pragma unroll 1
-                for (int b = 0; b < A.k / 8; b++) {
-                    const unsigned byte = __brev((e[b >> 2] >> (8 * (b & 3))) & 0xFFu) >> 24;
-                    if (A.crc == 8) r = q8::c_crc8.v[(r ^ byte) & 0xFF];
-                    else r = ((r << 8) ^ q8::c_crc16.v[((r >> 8) ^ byte) & 0xFF]) & 0xFFFF;
-                }
-                unsigned rx = 0;
-#pragma unroll 1
-                for (int t = 0; t < A.crc; t++) { const int q = A.k + t; rx = (rx << 1) | ((e[q >> 5] >> (q & 31)) & 1); }
-                ok = (rx == r);
-            }
-            const unsigned okm = __ballot_sync(FULL, ok);
-            const int chosen = okm ? (__ffs(okm) - 1) : LL - 1;
             const int frame = FPW * quad + fs;
-            const uint32_t* Ec = eptr(chosen);
             if (frame < A.B) {
                 if (A.sol)
 #pragma unroll 1
@@ -1259,11 +1247,14 @@ int scl8q_frames_per_warp(int L) { return 32 / L; }
     X(8, 8) X(9, 8) X(10, 8) X(11, 8) X(8, 16) X(9, 16) X(10, 16) X(11, 16) X(8, 32) X(9, 32) X(10, 32) X(11, 32)
 
 // info_w: host copy of the information-mask words (ceil(n/32)), passed as kernel parameters
-cudaError_t launch_decode_scl8q(const DecodeArgs& a, int L, const uint32_t* info_w, void* l3_scratch, int* next_quad, int blocks, cudaStream_t st) {
+cudaError_t launch_decode_scl8q(const DecodeArgs& a, int L, const uint32_t* info_w, const uint32_t* synd, uint32_t synd_c0, void* l3_scratch, int* next_quad,
+                                int blocks, cudaStream_t st) {
     Scl8qArgs s;
     s.a = a;
     s.next_quad = next_quad;
     s.l3 = reinterpret_cast<float4*>(l3_scratch);
+    s.synd = synd; s.synd_c0 = synd_c0;
+    if (a.crc && !synd) return cudaErrorInvalidValue;
     for (int i = 0; i < 65; i++) s.info_w[i] = i < a.n / 32 ? info_w[i] : 0;
     if (!a.y_f32) return cudaErrorInvalidValue;   // the caller converts double batches first (capi.cu)
 #define PCB_CASE(MM, LLL) if (a.m == MM && L == LLL) return launch_m<MM, LLL, float>(s, blocks, st);
