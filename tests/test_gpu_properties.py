@@ -90,3 +90,21 @@ def test_noiseless_round_trip(n, k, crc, L, dec):
         assert r["frame_errors"] <= 2
     else:
         assert r["frame_errors"] == 0 and r["bit_errors"] == 0
+
+
+def test_double_device_batch_equals_float_batch():
+    """A device-resident double batch goes through the float pre-pass (the reference narrows first,
+    SCLDecoderMinsum.cpp:406-408): same result as the float batch, including the frames the pre-pass
+    sends to the generic kernel."""
+    n, k, crc, L, B = 1024, 512, 16, 8, (1 << 18) + 6
+    d = _handle(n, k, crc, L, pb.SCLMINSUM)
+    y, _ = _batch(d, n, B)
+    y[5, 17] = 1e-42                      # denormal: outside the tuned kernel's range
+    y[B - 9, 3] = float("inf")
+    ref = _decode(d, y)
+    y64 = y.double()
+    out = torch.zeros((B, d.words), dtype=torch.int32, device="cuda")
+    for _ in range(2):
+        d.decode_dev(y64.data_ptr(), False, out.data_ptr(), B)
+    torch.cuda.synchronize()
+    assert torch.equal(out, ref)
