@@ -1,6 +1,7 @@
 #!/usr/bin/env python
 """Device-resident throughput of the BASELINE.json configs A-E, float channel
-values in HBM, packed output.  Config C is the bench.py headline; the others run on the generic kernel."""
+values in HBM, packed output.  Config C is the bench.py headline.  PCB_SWEEP_ONLY=<letters> selects
+configs, PCB_SWEEP_SCALE=<x> scales the batch sizes, PCB_FORCE_GENERIC=1 runs the generic kernel."""
 import os
 import sys
 
