@@ -45,6 +45,7 @@ cudaError_t launch_decode_sc32(const DecodeArgs& a, const uint32_t* info_w, cons
 // lane-per-path list kernel, 32 / L frames per warp (decode_scl8q.cu): L = 8 and L = 32
 bool scl8q_supported(int m, int L);
 int scl8q_frames_per_warp(int L);
+int scl8q_warps_per_block(int m, int L);
 cudaError_t launch_decode_scl8q(const DecodeArgs& a, int L, const uint32_t* info_w, const uint32_t* synd, uint32_t synd_c0, void* l3_scratch, int* next_quad,
                                 int blocks, cudaStream_t st);
 size_t scl8q_scratch_per_block(int m, int L);
@@ -444,9 +445,10 @@ int pcb_info(pcb_handle* h, int* sm_count, int* warps_per_block, int* blocks, in
              int* first_smem_layer, uint64_t* kernel_launches) {
     if (!h) return fail(PCB_EINVAL, "pcb_info: null handle");
     if (sm_count) *sm_count = h->sm_count;
-    if (warps_per_block) *warps_per_block = h->fast8 ? 1 : h->wpb;
-    if (blocks) *blocks = h->fast8 ? fast_blocks(h) : max_blocks(h);
-    if (smem_per_block) *smem_per_block = h->fast8 ? h->f_warp_smem : h->warp_smem * h->wpb;
+    const int fw = h->fast8 && h->quad ? scl8q_warps_per_block(h->m, h->L) : 1;
+    if (warps_per_block) *warps_per_block = h->fast8 ? fw : h->wpb;
+    if (blocks) *blocks = h->fast8 ? fast_blocks(h) / fw : max_blocks(h);
+    if (smem_per_block) *smem_per_block = h->fast8 ? h->f_warp_smem * fw : h->warp_smem * h->wpb;
     if (first_smem_layer) *first_smem_layer = h->ls;
     if (kernel_launches) *kernel_launches = h->launches;
     return PCB_OK;

@@ -73,6 +73,17 @@
 #ifndef PCB_Q_MERGE_SMALL
 #define PCB_Q_MERGE_SMALL 0
 #endif
+// PCB_Q_MW: all resident warps of an SM in ONE block (each warp still decodes its own frames and
+// never synchronises with the others): the 1 KB of shared memory the system reserves per block is
+// paid once, which makes room for a 17th warp at n = 1024, L = 8 -- where it loses 0.9 % (the
+// compiler keeps 88 instead of 106 registers under the 544-thread bound); with one frame per warp
+// (L = 32, 18 warps either way) it gains 3 %, so it is on for L >= 16 only.
+#ifndef PCB_Q_MW
+#define PCB_Q_MW 0
+#endif
+#ifndef PCB_Q_MW_BIG
+#define PCB_Q_MW_BIG 1
+#endif
 #ifndef PCB_Q_CPA
 #define PCB_Q_CPA 1
 #endif
@@ -148,6 +159,9 @@ struct Geo {
         return r;
     }
     static_assert((FRAME_WORDS * 4) % 16 == 0 && (OFF_H * 4) % 16 == 0 && (OFF_KEYS * 4) % 16 == 0, "alignment");
+    // PCB_Q_MW: warps of the one block of an SM (227 KB minus the reserved 1 KB; 18 warps keep 113 registers)
+    static constexpr int WMAX = (232448 - 1024) / TOTAL < 18 ? (232448 - 1024) / TOTAL : 18;
+    static constexpr bool MW = LL >= 16 ? PCB_Q_MW_BIG : PCB_Q_MW;
 };
 
 // f for frames whose channel values are all 0 or within [2^-40, 2^100] (see decode_scl8.cu):
@@ -1066,25 +1080,31 @@ struct Scl8qArgs {
 
 // One warp per block (blockDim.x == 32); a block decodes quads of frames.
 template <int M, int LL, typename YT>
-__global__ void __launch_bounds__(32, (LL != 8 ? 1 : q8::Geo<M, LL>::GL4 && M == 10 ? 16 : M == 10 ? 10 : 5)) decode_scl8q_kernel(const __grid_constant__ Scl8qArgs S) {
+__global__ void __launch_bounds__(q8::Geo<M, LL>::MW ? 32 * q8::Geo<M, LL>::WMAX : 32,
+                                  q8::Geo<M, LL>::MW ? 1 : (LL != 8 ? 1 : q8::Geo<M, LL>::GL4 && M == 10 ? 16 : M == 10 ? 10 : 5))
+    decode_scl8q_kernel(const __grid_constant__ Scl8qArgs S) {
     const DecodeArgs& A = S.a;
     using G = q8::Geo<M, LL>;
     constexpr int FPW = G::FPW;
     extern __shared__ __align__(16) unsigned char smem_raw[];
     constexpr unsigned FULL = 0xffffffffu;
-    const int lane = threadIdx.x, fme = lane / LL;
+    // a warp is a virtual block (G::MW: several of them in one block)
+    const int lane = G::MW ? threadIdx.x & 31 : threadIdx.x, wib = G::MW ? threadIdx.x >> 5 : 0, wpb = G::MW ? blockDim.x >> 5 : 1;
+    const int vblock = blockIdx.x * wpb + wib, nvblocks = gridDim.x * wpb;
+    unsigned char* const smem_warp = smem_raw + (size_t)wib * G::TOTAL;
+    const int fme = lane / LL;
     q8::Dec<M, LL, YT> D;
     D.lane = lane; D.p = lane & (LL - 1);
-    D.W = reinterpret_cast<float*>(smem_raw);
+    D.W = reinterpret_cast<float*>(smem_warp);
     D.P = D.W + fme * G::FRAME_WORDS;
     D.H = reinterpret_cast<uint32_t*>(D.P) + G::OFF_H;
-    D.HG = G::GH ? reinterpret_cast<uint32_t*>(S.l3 + (size_t)blockIdx.x * G::SCRATCH_BLOCK_FLOAT4 + G::L3_BLOCK_FLOAT4 + G::L4_BLOCK_FLOAT4 +
+    D.HG = G::GH ? reinterpret_cast<uint32_t*>(S.l3 + (size_t)vblock * G::SCRATCH_BLOCK_FLOAT4 + G::L3_BLOCK_FLOAT4 + G::L4_BLOCK_FLOAT4 +
                                                G::L5_BLOCK_FLOAT4) + fme * ((G::NW - G::NW / 4) * LL)
                    : nullptr;
     D.keys = reinterpret_cast<uint32_t*>(D.P) + G::OFF_KEYS;
-    D.L3 = G::GL3 ? S.l3 + (size_t)blockIdx.x * G::SCRATCH_BLOCK_FLOAT4 + fme * (G::Q3 * LL) : nullptr;
-    D.L4 = G::GL4 ? S.l3 + (size_t)blockIdx.x * G::SCRATCH_BLOCK_FLOAT4 + G::L3_BLOCK_FLOAT4 + fme * (G::Q3 / 2 * LL) : nullptr;
-    D.L5 = G::GL5 ? S.l3 + (size_t)blockIdx.x * G::SCRATCH_BLOCK_FLOAT4 + G::L3_BLOCK_FLOAT4 + G::L4_BLOCK_FLOAT4 + fme * (G::Q3 / 4 * LL) : nullptr;
+    D.L3 = G::GL3 ? S.l3 + (size_t)vblock * G::SCRATCH_BLOCK_FLOAT4 + fme * (G::Q3 * LL) : nullptr;
+    D.L4 = G::GL4 ? S.l3 + (size_t)vblock * G::SCRATCH_BLOCK_FLOAT4 + G::L3_BLOCK_FLOAT4 + fme * (G::Q3 / 2 * LL) : nullptr;
+    D.L5 = G::GL5 ? S.l3 + (size_t)vblock * G::SCRATCH_BLOCK_FLOAT4 + G::L3_BLOCK_FLOAT4 + G::L4_BLOCK_FLOAT4 + fme * (G::Q3 / 4 * LL) : nullptr;
     constexpr int n = G::N;
     const int EW = (A.stride + 31) >> 5;
     const YT* ybase = reinterpret_cast<const YT*>(A.y);
@@ -1092,7 +1112,7 @@ __global__ void __launch_bounds__(32, (LL != 8 ? 1 : q8::Geo<M, LL>::GL4 && M ==
 
     // The first quad of a block is its index, the following ones come from a work counter: decode
     // times differ from quad to quad, and a static stride leaves SMs idle at the end of the batch.
-    int quad = blockIdx.x;
+    int quad = vblock;
     while (quad < nquads) {
         int fr[4];
         D.fbase = FPW * quad; D.Bm1 = A.B - 1;
@@ -1102,9 +1122,9 @@ __global__ void __launch_bounds__(32, (LL != 8 ? 1 : q8::Geo<M, LL>::GL4 && M ==
         // stopped paying once the top stage staged them with cp.async: 34.15 / 33.0 vs 34.23 M)
         int next_quad = 0;
 #ifdef PCB_Q_STATIC
-        next_quad = quad + (int)gridDim.x;
+        next_quad = quad + nvblocks;
 #else
-        if (lane == 0) next_quad = (int)gridDim.x + atomicAdd(S.next_quad, 1);
+        if (lane == 0) next_quad = nvblocks + atomicAdd(S.next_quad, 1);
         next_quad = __shfl_sync(FULL, next_quad, 0);
 #endif
         D.met = 0.f; D.maxmet = 0; D.pidx = 0; D.cidx = 0; D.w0 = 0; D.ninfo = 0;
@@ -1223,10 +1243,11 @@ __global__ void __launch_bounds__(32, (LL != 8 ? 1 : q8::Geo<M, LL>::GL4 && M ==
 
 template <int M, int LL, typename YT>
 static cudaError_t launch_m(const Scl8qArgs& a, int blocks, cudaStream_t st) {
-    const size_t smem = (size_t)q8::Geo<M, LL>::TOTAL;
+    const int W = q8::Geo<M, LL>::MW ? q8::Geo<M, LL>::WMAX : 1;      // `blocks` counts warps
+    const size_t smem = (size_t)q8::Geo<M, LL>::TOTAL * W;
     cudaError_t e = cudaFuncSetAttribute(decode_scl8q_kernel<M, LL, YT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
-    decode_scl8q_kernel<M, LL, YT><<<blocks, 32, smem, st>>>(a);
+    decode_scl8q_kernel<M, LL, YT><<<(blocks + W - 1) / W, 32 * W, smem, st>>>(a);
     return cudaGetLastError();
 }
 
@@ -1234,9 +1255,13 @@ template <int M, int LL, typename YT>
 static cudaError_t occ_m(int* bps, int* warp_bytes) {
     const size_t smem = (size_t)q8::Geo<M, LL>::TOTAL;
     *warp_bytes = q8::Geo<M, LL>::TOTAL;
-    cudaError_t e = cudaFuncSetAttribute(decode_scl8q_kernel<M, LL, YT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    const int W = q8::Geo<M, LL>::MW ? q8::Geo<M, LL>::WMAX : 1;
+    cudaError_t e = cudaFuncSetAttribute(decode_scl8q_kernel<M, LL, YT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(smem * W));
     if (e != cudaSuccess) return e;
-    return cudaOccupancyMaxActiveBlocksPerMultiprocessor(bps, decode_scl8q_kernel<M, LL, YT>, 32, smem);
+    int nb = 0;
+    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, decode_scl8q_kernel<M, LL, YT>, 32 * W, smem * W);
+    *bps = nb * W;                           // warps per SM
+    return e;
 }
 
 // list sizes with a lane-per-path kernel: 32 / L frames per warp
@@ -1271,7 +1296,15 @@ size_t scl8q_scratch_per_block(int m, int L) {
     return 0;
 }
 
-// resident blocks (= warps) per SM
+// warps per block: all resident warps of an SM for the variants with several warps per block, else one
+int scl8q_warps_per_block(int m, int L) {
+#define PCB_CASE(MM, LLL) if (m == MM && L == LLL) return q8::Geo<MM, LLL>::MW ? q8::Geo<MM, LLL>::WMAX : 1;
+    PCB_FOR_ALL(PCB_CASE)
+#undef PCB_CASE
+    return 1;
+}
+
+// resident warps per SM
 cudaError_t scl8q_occupancy(int m, int L, int* bps, int* warp_bytes) {
 #define PCB_CASE(MM, LLL) if (m == MM && L == LLL) return occ_m<MM, LLL, float>(bps, warp_bytes);
     PCB_FOR_ALL(PCB_CASE)

@@ -53,7 +53,7 @@ def _decode(d, y):
 @pytest.mark.parametrize("name,n,k,crc,L,dec,B", FULL, ids=[c[0].strip() for c in FULL])
 def test_tuned_kernel_equals_generic_kernel_at_full_size(name, n, k, crc, L, dec, B):
     fast, slow = _handle(n, k, crc, L, dec), _handle(n, k, crc, L, dec, generic=True)
-    assert fast.info()["warps_per_block"] == 1 and slow.info()["blocks"] > 0
+    assert fast.info()["blocks"] > 0 and slow.info()["blocks"] > 0
     y, _ = _batch(fast, n, B)
     a, b = _decode(fast, y), _decode(slow, y)
     if dec == pb.SC:   # tanh/atanh: same CUDA libm on both sides, still bit-exact between the two kernels
