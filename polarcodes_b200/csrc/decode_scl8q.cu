@@ -84,6 +84,9 @@
 #ifndef PCB_Q_MW_BIG
 #define PCB_Q_MW_BIG 1
 #endif
+#ifndef PCB_Q_WCAP
+#define PCB_Q_WCAP 18      // most warps of such a block (18 warps keep 113 registers each)
+#endif
 #ifndef PCB_Q_CPA
 #define PCB_Q_CPA 1
 #endif
@@ -160,7 +163,7 @@ struct Geo {
     }
     static_assert((FRAME_WORDS * 4) % 16 == 0 && (OFF_H * 4) % 16 == 0 && (OFF_KEYS * 4) % 16 == 0, "alignment");
     // PCB_Q_MW: warps of the one block of an SM (227 KB minus the reserved 1 KB; 18 warps keep 113 registers)
-    static constexpr int WMAX = (232448 - 1024) / TOTAL < 18 ? (232448 - 1024) / TOTAL : 18;
+    static constexpr int WMAX = (232448 - 1024) / TOTAL < PCB_Q_WCAP ? (232448 - 1024) / TOTAL : PCB_Q_WCAP;
     static constexpr bool MW = LL >= 16 ? PCB_Q_MW_BIG : PCB_Q_MW;
 };
 
