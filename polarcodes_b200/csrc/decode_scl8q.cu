@@ -37,7 +37,7 @@
 // memory per quad and 16 resident quads per SM instead of 10 (25.5 vs 22.0 Mframes/s).  The
 // scratch is then 24 KB per quad, 57 MB for the whole grid: it has to stay in L2, so ...
 #ifndef PCB_Q_L5N
-#define PCB_Q_L5N 4   // float4 column pairs per iteration of the layer-5 loop (GL4)
+#define PCB_Q_L5N 8   // float4 column pairs per iteration of the layer-5 loop (GL4): 16 loads in flight (4: -0.8 %, 2: -2.6 %)
 #endif
 #ifndef PCB_Q_STU
 #define PCB_Q_STU 4    // unroll factors of the two staging loops of the top stage
@@ -726,7 +726,7 @@ struct Dec {
     // shared-memory layer LAM from the global layer LAM-1
     template <int LAM>
     __device__ __forceinline__ void from_global(bool isg) {
-        constexpr int S = G::size(LAM), NL = PCB_Q_L5N;
+        constexpr int S = G::size(LAM), NL = 4;      // (8 columns per iteration: -1.6 % at L = 32)
         const float4* src = glayer(LAM - 1) + (isg ? pfield(LAM - 1) : p);
         float* dst = arr(LAM, p);
 #pragma unroll 1
@@ -788,7 +788,7 @@ struct Dec {
     }
     // GL4: layer 5 (shared memory) from the layer-4 arrays in global memory
     __device__ __forceinline__ void layer5_global(bool isg) {
-        constexpr int S = G::size(5), NL = PCB_Q_L5N;
+        constexpr int S = G::size(5), NL = PCB_Q_L5N < S / 4 ? PCB_Q_L5N : S / 4;
         const float4* src = L4 + (isg ? pfield(4) : p);
         float* dst = arr(5, p);
 #pragma unroll 1
