@@ -39,6 +39,9 @@
 #ifndef PCB_Q_L5N
 #define PCB_Q_L5N 8   // float4 column pairs per iteration of the layer-5 loop (GL4): 16 loads in flight (4: -0.8 %, 2: -2.6 %)
 #endif
+#ifndef PCB_Q_L4N
+#define PCB_Q_L4N 2   // column pairs per iteration of the layer-4 g loop, 4 float4 loads each (4 pairs: 117 registers, -0.8 %)
+#endif
 #ifndef PCB_Q_STU
 #define PCB_Q_STU 4    // unroll factors of the two staging loops of the top stage
 #endif
@@ -747,25 +750,25 @@ struct Dec {
 
     // GL3: g at layer 4 from the layer-3 arrays in global memory (L2)
     __device__ __forceinline__ void layer4_g_global() {
-        constexpr int S = G::size(4);
+        constexpr int S = G::size(4), NJ = PCB_Q_L4N;
         const float4* src = L3 + pfield(3);
         if constexpr (G::GL4) {
             // layer 4 goes back to the scratch and, as layer 5 = f(layer 4) comes next for this
             // slot, columns j and j + S/8 are produced together and combined on the spot
             float* dst5 = arr(5, p);
 #pragma unroll 1
-            for (int j0 = 0; j0 < S / 8; j0 += 2) {       // 8 loads in flight
+            for (int j0 = 0; j0 < S / 8; j0 += NJ) {      // 4 * NJ loads in flight
                 const uint32_t cw0 = cword(4, 0, j0 >> 3) >> (4 * (j0 & 7)), cw1 = cword(4, 0, (j0 + S / 8) >> 3) >> (4 * (j0 & 7));
-                float4 a[2][2], b[2][2];
+                float4 a[NJ][2], b[NJ][2];
 #pragma unroll
-                for (int i = 0; i < 2; i++)
+                for (int i = 0; i < NJ; i++)
 #pragma unroll
                     for (int hh = 0; hh < 2; hh++) {
                         const int c = j0 + i + hh * (S / 8);
                         a[i][hh] = src[c * LL]; b[i][hh] = src[(c + S / 4) * LL];
                     }
 #pragma unroll
-                for (int i = 0; i < 2; i++) {
+                for (int i = 0; i < NJ; i++) {
                     const float4 lo = gs4(a[i][0], b[i][0], cw0, 4 * i), hi = gs4(a[i][1], b[i][1], cw1, 4 * i);
                     L4[(j0 + i) * LL + p] = lo;
                     L4[(j0 + i + S / 8) * LL + p] = hi;
