@@ -63,16 +63,27 @@ unsigned pcb_crc16(const int* bits, int len);
 /* PolarCodes.cpp:136-155 — append the crc (0/8/16) MSB first at xinf[k..k+crc) */
 int pcb_append_crc(int* xinf, int k, int crc);
 
+/* Algorithmic ALU lane-ops of one frame (the roofline numerator): counted from the frozen mask with the
+ * fixed weights f = 4, g = 2, metric update = 2, compare-exchange = 3 (bitonic convention over 2L
+ * candidates), 1 per packed word of partial-sum XORs; decoders 1,2: L = 1, no metric, no select.
+ * llr_updates (may be NULL) receives the number of f + g updates. */
+int pcb_lane_ops_per_frame(const int* frozen_mask, int n, int L, int decoder, double* lane_ops, double* llr_updates);
+
 /* ---- handle -------------------------------------------------------------------------- */
 /* Replaces the per-run allocations of PolarCodes.cpp:99-121 and
  * SCLDecoderMinsum::InitializeDataStructures (SCLDecoderMinsum.cpp:60-118).
  * n: power of two in [2, 65536]; L: power of two in [1, 32] (decoder 3; ignored otherwise);
- * crc in {0, 8, 16} (decoder 3); device: CUDA ordinal. Returns NULL on failure. */
+ * crc in {0, 8, 16}: checked by decoder 3 (:442-472); for decoders 1,2 it only tells the frame
+ * generator to append it to the payload, as the loop does for every decoder (PolarCodes.cpp:136-155).
+ * k is the payload size: sigma / the rate use k, never k + crc (PolarCodes.cpp:123).
+ * device: CUDA ordinal. Returns NULL on failure. */
 pcb_handle* pcb_create(int device, int n, int k, int crc, int L, int decoder, int precision);
 void pcb_destroy(pcb_handle* h);
 
-/* Uploads the frozen mask (the vector FrozenBits() returns, Encoder.cpp:43) and sigma.
- * The number of -1 entries must be k + crc (decoder 3) — decoders 1,2 accept any count. */
+/* Uploads the frozen mask (the vector FrozenBits() returns, Encoder.cpp:43) and sigma (used by
+ * decoder 1 only: LLR = 2y/sigma^2, SCDecoder.cpp:15-17).  The number of -1 entries must be k + crc
+ * for decoder 3; decoders 1,2 decode a mask with any count, but pcb_montecarlo / pcb_generate_*
+ * need k + crc positions to scatter the payload into (PCB_ESTATE otherwise). */
 int pcb_set_code(pcb_handle* h, const int* frozen_mask, double sigma);
 
 /* Encode (Encoder.cpp:77-83), batched: u[B][n] one int per bit -> x[B][n].
@@ -104,7 +115,11 @@ int pcb_decode_batch_dev(pcb_handle* h, const void* y_dev, int y_is_f32, uint32_
  * frames [first_frame_id, first_frame_id + frames) of the stream keyed by `seed`; results do
  * not depend on batch size or GPU count. Counters are ADDED to *frame_errors / *bit_errors
  * (bit errors over the k info bits for decoder 3, over all n u-bits for decoders 1,2 — the
- * reference counts frame errors only, PolarCodes.cpp:163-186). seconds = decode-kernel time. */
+ * reference counts frame errors only, PolarCodes.cpp:163-186). seconds = decode-kernel time.
+ * The channel values are fp32 (s + sigma z with z from Philox4x32-10 + Box-Muller in fp32, |z| up to
+ * 6.76: a 2^-33 floor on the uniform); the reference draws N(0, sigma) in double from mt19937.  Parity
+ * of this mode is statistical by construction; FER points below ~1e-9 per bit would
+ * feel the truncated tail.  The handle's own sigma (pcb_set_code) is not touched. */
 int pcb_montecarlo(pcb_handle* h, double snr_db, uint64_t frames, uint64_t seed, uint64_t first_frame_id,
                    uint64_t* frames_done, uint64_t* frame_errors, uint64_t* bit_errors, double* seconds);
 
@@ -118,6 +133,26 @@ int pcb_generate_batch(pcb_handle* h, double snr_db, uint64_t seed, uint64_t fir
  * packed (may be NULL). Synchronises before returning. */
 int pcb_generate_batch_dev(pcb_handle* h, double snr_db, uint64_t seed, uint64_t first_frame_id, int B,
                            float* y_dev, uint32_t* tx_bits_dev);
+
+/* ---- error counters and their reduction across GPUs ------------------------------------------
+ * Frame-error compare of the loop (PolarCodes.cpp:163-168,172-177,181-186) on packed DEVICE words:
+ * dec_bits_dev / tx_bits_dev are [B][ceil(stride/32)] (what pcb_decode_batch_dev writes and
+ * pcb_generate_batch_dev hands out).  counters[3] += {B, frame errors, bit errors} (bit errors over
+ * the k info bits for decoder 3, all n u-bits for decoders 1,2).  allreduce != 0: the three numbers
+ * are first summed over the ranks of the communicator (ncclAllReduce on the handle's stream). */
+int pcb_count_errors_dev(pcb_handle* h, const uint32_t* dec_bits_dev, const uint32_t* tx_bits_dev, int B, int allreduce,
+                         uint64_t* counters);
+/* One process per GPU: rank 0 obtains a 128-byte NCCL unique id, hands it to the other ranks by any
+ * means (a file, MPI, torch.distributed), and every rank binds a communicator to its handle.  The
+ * `er` counter of the reference loop (PolarCodes.cpp:129,193) then becomes
+ * pcb_comm_allreduce(SUM, uint64[count <= 8]).  NCCL is opened at run time (libnccl.so.2). */
+int pcb_comm_unique_id(void* id128);
+int pcb_comm_init(pcb_handle* h, const void* id128, int rank, int world);
+int pcb_comm_allreduce(pcb_handle* h, uint64_t* counters, int count);
+
+/* ALU roofline of this handle's device for this decoder's arithmetic: SMs x lanes x max SM clock, lanes =
+ * 128 per SM (fp32 / int32) or 64 (fp64: decoders 1,2 in strict precision).  lane-ops per second. */
+int pcb_alu_peak(pcb_handle* h, double* lane_ops_per_s);
 
 /* introspection for bench / roofline accounting */
 int pcb_info(pcb_handle* h, int* sm_count, int* warps_per_block, int* blocks, int* smem_per_block,

@@ -22,11 +22,19 @@ _ip = np.ctypeslib.ndpointer(dtype=np.int32, flags="C_CONTIGUOUS")
 _dp = np.ctypeslib.ndpointer(dtype=np.float64, flags="C_CONTIGUOUS")
 
 
+SHIM_MAIN = os.path.join(HERE, "_ref", "PolarCodes_shim")
+
+
 def build(force=False):
-    """Compile liboracle.so (always possible) and oracle/_ref (only where /root/reference exists)."""
-    need = force or not os.path.exists(ORACLE_SO) or (
-        os.path.getmtime(ORACLE_SO) < os.path.getmtime(os.path.join(HERE, "polar_oracle.c")))
-    if need or (os.path.isdir("/root/reference/PolarCodes") and not os.path.exists(REF_SO)):
+    """Compile liboracle.so (always possible) and, only where /root/reference exists, oracle/_ref:
+    libpolar_ref.so (the unmodified reference) and PolarCodes_shim (its main() against the shim header)."""
+    def stale(out, src):
+        return not os.path.exists(out) or os.path.getmtime(out) < os.path.getmtime(src)
+    need = force or stale(ORACLE_SO, os.path.join(HERE, "polar_oracle.c"))
+    if os.path.isdir("/root/reference/PolarCodes"):
+        shim_h = os.path.join(HERE, "..", "polarcodes_b200", "host", "polar_b200_shim.h")
+        need = need or stale(REF_SO, os.path.join(HERE, "ref_wrap.cpp")) or stale(SHIM_MAIN, shim_h)
+    if need:
         subprocess.check_call(["make", "-C", HERE, "all"], stdout=subprocess.DEVNULL)
 
 
@@ -162,6 +170,7 @@ class Ref(_Base):
         L.ref_gen_frame.argtypes = [C.c_int, C.c_int, C.c_int, _ip, C.c_double, C.c_int, _ip, _ip, _ip, _dp]
         L.ref_time_decode.restype = C.c_double
         L.ref_time_decode.argtypes = [C.c_int] * 5 + [_dp, _ip, C.c_double, C.c_int, C.c_int, C.c_void_p]
+        L.ref_decode_batch.argtypes = [C.c_int] * 5 + [C.c_double, _dp, _ip, _ip, C.c_int]
         L.ref_fer_point.restype = C.c_int
         L.ref_fer_point.argtypes = [C.c_int] * 6 + [C.c_double, C.c_int]
 
@@ -212,19 +221,10 @@ class Ref(_Base):
 
     def decode(self, decoder, n, L, k, crc, sigma, y, mask):
         y = _f64(y).reshape(-1, n)
-        mask = _i32(mask)
         stride = k + crc if decoder == 3 else n
-        sol = np.zeros((y.shape[0], max(stride, n)), np.int32)
-        if decoder == 3:
-            self.lib.ref_scl_init(n, L, k, crc)
-        for f in range(y.shape[0]):
-            if decoder == 1:
-                self.lib.ref_sc_decode(n, y[f], mask, sigma, sol[f])
-            elif decoder == 2:
-                self.lib.ref_scms_decode(n, y[f], mask, sol[f])
-            else:
-                self.lib.ref_scl_decode(n, L, y[f], mask, sol[f])
-        return np.ascontiguousarray(sol[:, :stride])
+        sol = np.zeros((y.shape[0], stride), np.int32)
+        self.lib.ref_decode_batch(decoder, n, L, k, crc, float(sigma), y, _i32(mask), sol, y.shape[0])
+        return sol
 
     def gen_frames(self, n, k, crc, inf, sigma, with_shuffle, frames):
         """frames iterations of PolarCodes.cpp:133-158 drawing from the (seeded) global engine."""
@@ -243,6 +243,25 @@ class Ref(_Base):
 
     def fer_point(self, n, k, crc, L, decoder, zcomputer, snr_db, loop):
         return self.lib.ref_fer_point(n, k, crc, L, decoder, zcomputer, snr_db, loop)
+
+
+def _ref_worker(args):
+    decoder, n, L, k, crc, sigma, y, mask = args
+    return Ref().decode(decoder, n, L, k, crc, sigma, y, mask)
+
+
+def ref_decode_parallel(decoder, n, L, k, crc, sigma, y, mask, procs=None):
+    """The unmodified reference over a large batch, split over host processes (its list decoder keeps
+    namespace-global state: processes, not threads).  Frame order is preserved."""
+    import multiprocessing as mp
+    y = _f64(y).reshape(-1, n)
+    procs = max(1, min(procs or (os.cpu_count() or 1), y.shape[0] // 8 or 1))
+    if procs == 1:
+        return Ref().decode(decoder, n, L, k, crc, sigma, y, mask)
+    parts = np.array_split(y, procs)
+    with mp.get_context("fork").Pool(procs) as pool:
+        out = pool.map(_ref_worker, [(decoder, n, L, k, crc, sigma, p, mask) for p in parts])
+    return np.concatenate(out, axis=0)
 
 
 def best_cpu():

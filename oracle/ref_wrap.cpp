@@ -125,6 +125,25 @@ void ref_scl_decode(int n, int L, const double* y, const int* mask, int* sol) {
     SCLDecoderMinsum::Decode(n, L, const_cast<double*>(y), g_buf.decTree2, sol, fb, 2);
 }
 
+// B frames through the reference decoders, one call per frame exactly as the loop makes them
+// (PolarCodes.cpp:162,171,180); sol is [B][n] for decoders 1,2 and [B][k+crc] for decoder 3.
+void ref_decode_batch(int decoder, int n, int L, int k, int crc, double sigma, const double* y, const int* mask, int* sol, int B) {
+    ensure_buffers(n);
+    std::vector<int> fb(mask, mask + n);
+    std::vector<int> tmp(n);
+    if (decoder == 3) ref_scl_init(n, L, k, crc);
+    const int stride = decoder == 3 ? k + crc : n;
+    for (int f = 0; f < B; f++) {
+        double* c = const_cast<double*>(y) + (size_t)f * n;
+        switch (decoder) {
+            case 1: SCDecoder::Decode(n, c, g_buf.decTree1, g_buf.decTree2, tmp.data(), fb, sigma); break;
+            case 2: SCDecoderMinsum::Decode(n, c, g_buf.decTree1, g_buf.decTree2, tmp.data(), fb); break;
+            default: SCLDecoderMinsum::Decode(n, L, c, g_buf.decTree2, tmp.data(), fb, 2); break;
+        }
+        std::memcpy(sol + (size_t)f * stride, tmp.data(), sizeof(int) * stride);
+    }
+}
+
 // One iteration of the frame-generation part of the FER loop, PolarCodes.cpp:133-158:
 // uniform info bits, CRC append (MSB first), AddFrozenBits, Encode, Transform (BPSK+AWGN).
 // Draws from the global `eng` exactly as the reference does.

@@ -37,6 +37,8 @@ SIGNATURES = {
     "pcb_crc8": (C.c_uint, [_ip, C.c_int]),
     "pcb_crc16": (C.c_uint, [_ip, C.c_int]),
     "pcb_append_crc": (C.c_int, [_ip, C.c_int, C.c_int]),
+    "pcb_lane_ops_per_frame": (C.c_int, [_ip, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_double)]),
+    "pcb_alu_peak": (C.c_int, [C.c_void_p, C.POINTER(C.c_double)]),
     "pcb_create": (C.c_void_p, [C.c_int] * 7),
     "pcb_destroy": (None, [C.c_void_p]),
     "pcb_set_code": (C.c_int, [C.c_void_p, _ip, C.c_double]),
@@ -49,6 +51,10 @@ SIGNATURES = {
                                  C.POINTER(C.c_double)]),
     "pcb_generate_batch": (C.c_int, [C.c_void_p, C.c_double, C.c_uint64, C.c_uint64, C.c_int, _fp, _ip]),
     "pcb_generate_batch_dev": (C.c_int, [C.c_void_p, C.c_double, C.c_uint64, C.c_uint64, C.c_int, C.c_void_p, C.c_void_p]),
+    "pcb_count_errors_dev": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, _u64p]),
+    "pcb_comm_unique_id": (C.c_int, [C.c_void_p]),
+    "pcb_comm_init": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int]),
+    "pcb_comm_allreduce": (C.c_int, [C.c_void_p, _u64p, C.c_int]),
     "pcb_info": (C.c_int, [C.c_void_p] + [C.POINTER(C.c_int)] * 5 + [_u64p]),
 }
 
@@ -100,6 +106,14 @@ class Code:
         _check(L.pcb_frozen_mask(n, self.inf, len(self.inf), self.mask))
 
 
+def lane_ops_per_frame(mask, L, decoder):
+    """(ALU lane-ops, LLR updates) of one frame under the SURVEY.md section 8(d) convention."""
+    mask = _i32(mask)
+    ops, upd = C.c_double(0), C.c_double(0)
+    _check(lib().pcb_lane_ops_per_frame(mask, len(mask), L, decoder, C.byref(ops), C.byref(upd)))
+    return ops.value, upd.value
+
+
 def crc8(bits):
     b = _i32(bits)
     return lib().pcb_crc8(b, len(b))
@@ -133,9 +147,9 @@ class Decoder:
             raise PolarError(f"pcb_create failed: {lib().pcb_last_error().decode()}")
         self._h = h
         self.n, self.k, self.decoder = n, k, decoder
-        self.crc = crc if decoder == SCLMINSUM else 0
+        self.crc = crc      # decoder 3 checks it; decoders 1, 2 only see it in the generated payload (PolarCodes.cpp:136-155)
         self.L = L if decoder == SCLMINSUM else 1
-        self.stride = k + self.crc if decoder == SCLMINSUM else n
+        self.stride = k + crc if decoder == SCLMINSUM else n
         self.words = (self.stride + 31) // 32
 
     def close(self):
@@ -202,6 +216,27 @@ class Decoder:
         _check(lib().pcb_generate_batch_dev(self._h, float(snr_db), int(seed), int(first_frame_id), B, y_dev_ptr,
                                             tx_dev_ptr))
 
+    def count_errors_dev(self, dec_bits_dev_ptr, tx_bits_dev_ptr, B, allreduce=False):
+        """{frames, frame_errors, bit_errors} of a device-resident batch (summed over the ranks when allreduce)."""
+        c = (C.c_uint64 * 3)(0, 0, 0)
+        _check(lib().pcb_count_errors_dev(self._h, dec_bits_dev_ptr, tx_bits_dev_ptr, B, int(bool(allreduce)), c))
+        return dict(frames=c[0], frame_errors=c[1], bit_errors=c[2])
+
+    def comm_init(self, id128, rank, world):
+        """Binds an NCCL communicator (one process per GPU); id128 = unique_id() of rank 0."""
+        buf = (C.c_char * 128).from_buffer_copy(bytes(id128))
+        _check(lib().pcb_comm_init(self._h, buf, rank, world))
+
+    def comm_allreduce(self, counters):
+        c = (C.c_uint64 * len(counters))(*[int(v) for v in counters])
+        _check(lib().pcb_comm_allreduce(self._h, c, len(counters)))
+        return [int(v) for v in c]
+
+    def alu_peak(self):
+        v = C.c_double(0)
+        _check(lib().pcb_alu_peak(self._h, C.byref(v)))
+        return v.value
+
     def info(self):
         v = [C.c_int(0) for _ in range(5)]
         launches = C.c_uint64(0)
@@ -210,6 +245,13 @@ class Decoder:
         d = {k: x.value for k, x in zip(keys, v)}
         d["kernel_launches"] = launches.value
         return d
+
+
+def comm_unique_id():
+    """128-byte NCCL unique id (rank 0 creates it, every rank passes it to Decoder.comm_init)."""
+    buf = (C.c_char * 128)()
+    _check(lib().pcb_comm_unique_id(buf))
+    return bytes(buf)
 
 
 def unpack_bits(words, nbits):

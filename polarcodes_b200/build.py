@@ -17,7 +17,7 @@ ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
 # -fmad=false: no mul+add contraction anywhere on the decode path (bit-exact LLR arithmetic);
 # no --use_fast_math, denormals kept (ftz off is the default).
 NVCC_FLAGS = ["-O3", "-std=c++17", "-lineinfo", "-fmad=false", "-Xcompiler", "-fPIC", "-Xcompiler", "-ffp-contract=off"]
-CUDA_SOURCES = ["decode_generic.cu", "decode_scl8.cu", "decode_scl8q.cu", "decode_sc32.cu", "aux_kernels.cu", "capi.cu"]
+CUDA_SOURCES = ["decode_generic.cu", "decode_scl8q.cu", "decode_sc32.cu", "aux_kernels.cu", "capi.cu"]
 CXX_SOURCES = ["construct.cpp"]
 
 
@@ -46,7 +46,7 @@ def build(force=False, verbose=False):
             cmd = [_nvcc()] + ARCH + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-c", sp, "-o", op]
             subprocess.check_call(cmd)
     if force or _stale(OUT, objs):
-        subprocess.check_call([_nvcc()] + ARCH + ["-shared", "-o", OUT] + objs + ["-lcudart"])
+        subprocess.check_call([_nvcc()] + ARCH + ["-shared", "-o", OUT] + objs + ["-lcudart", "-ldl"])
     return OUT
 
 

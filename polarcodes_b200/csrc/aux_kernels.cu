@@ -89,7 +89,9 @@ struct Philox {
 };
 
 __device__ __forceinline__ void box_muller(uint32_t a, uint32_t b, float& z0, float& z1) {
-    const float u1 = ((float)(a >> 8) + 0.5f) * (1.0f / 16777216.0f);   // (0,1), 24-bit grid
+    // u1 in (0, 1] on the full 32-bit grid near zero ((float)a is exact for a < 2^24, which is where the
+    // tail of the normal lives): the smallest value 2^-33 gives |z| up to 6.76; u2 on a 24-bit grid
+    const float u1 = a ? __uint2float_rn(a) * (1.0f / 4294967296.0f) : (0.5f / 4294967296.0f);
     const float u2 = ((float)(b >> 8) + 0.5f) * (1.0f / 16777216.0f);
     const float r = sqrtf(-2.0f * logf(u1));
     float sn, cs;

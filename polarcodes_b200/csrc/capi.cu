@@ -17,6 +17,7 @@
 #include "aux_kernels.h"
 #include "decode_launch.h"
 #include "errors.h"
+#include "nccl_dl.h"
 
 namespace pcb {
 static thread_local char g_err[512] = "";
@@ -28,11 +29,6 @@ int fail(int code, const char* fmt, ...) {
     return code;
 }
 cudaError_t decode_generic_occupancy(int L, int mode, int fp64, int wpb, size_t smem, int* bps);
-// tuned list-8 kernel (decode_scl8.cu)
-bool scl8_supported(int m);
-cudaError_t launch_decode_scl8(const DecodeArgs& a, const uint32_t* info_w, const uint32_t* fv_w, int blocks,
-                               cudaStream_t st);
-cudaError_t scl8_occupancy(int m, int* bps, int* warp_bytes);
 // min-sum SC kernel with 32 frames per warp (decode_sc32.cu)
 bool sc32_supported(int m);
 cudaError_t sc32_occupancy(int m, int fp64, int* bps, int* bytes);
@@ -148,14 +144,15 @@ struct HostNarrow {
 struct pcb_handle {
     int device = 0, n = 0, m = 0, k = 0, crc = 0, L = 1, decoder = 0, precision = 0;
     int stride = 0, EW = 0, fp64 = 0, sizeofT = 4;
+    int ninfo = 0;                  // information positions of the uploaded mask (decoders 1, 2: any count)
     bool code_set = false;
     double sigma = 1.0;
     int sm_count = 0, wpb = 4, bps = 1, ls = 1, warp_smem = 0;
-    bool fast8 = false;             // tuned list-8 kernel (decode_scl8.cu) instead of the generic one
+    bool fast8 = false;             // tuned lane-per-path list kernel (decode_scl8q.cu) instead of the generic one
     // launch shape of the tuned kernel (the fields above always describe the generic kernel, which
     // also re-decodes the frames the tuned kernel hands over)
     int f_bps = 0, f_warp_smem = 0;
-    bool quad = false;              // four-frames-per-warp variant (decode_scl8q.cu) of the tuned kernel
+    bool quad = false;              // same as fast8 (kept: the launch code reads better with both names)
     bool sc32 = false;              // min-sum SC: lane-per-frame kernel (decode_sc32.cu) instead of the generic one
     int sc32_bps = 0, sc32_smem = 0;
     void* d_yt = nullptr;           // sc32: transposed channel values of the batch
@@ -202,6 +199,11 @@ struct pcb_handle {
     size_t enc_frames = 0;
     int *d_eu = nullptr, *d_ex = nullptr;
     uint64_t launches = 0;
+    // counter reduction across the ranks of a box (pcb_comm_init): NCCL communicator + device buffer
+    void* comm = nullptr;
+    int comm_rank = 0, comm_world = 1;
+    unsigned long long* d_red = nullptr;   // [8]: frames, frame errors, bit errors (+ caller's extras)
+    uint64_t collectives = 0;
     std::vector<uint32_t> h_info_w, h_fv_w;   // host copies of the mask words (kernel parameters of the list-8 kernel)
 };
 
@@ -219,28 +221,17 @@ static int ensure_device(pcb_handle* h) {
 // per-warp slice fits the budget, then the warps-per-block with the best occupancy.
 static int configure(pcb_handle* h) {
     const char* wenv = getenv("PCB_WPB");
-    const bool l8 = h->L == 8 && scl8_supported(h->m);
-    h->fast8 = h->decoder == 3 && (l8 || scl8q_supported(h->m, h->L)) && !getenv("PCB_FORCE_GENERIC");
+    h->fast8 = h->decoder == 3 && scl8q_supported(h->m, h->L) && !getenv("PCB_FORCE_GENERIC");
     h->quad = false;
     if (h->fast8) {
-        int bps = 0, wb = 0;   // one warp (= one frame) per block
-        if (l8) {
-            if (scl8_occupancy(h->m, &bps, &wb) != cudaSuccess || bps == 0) { cudaGetLastError(); return fail(PCB_EINVAL, "list-8 kernel does not fit one SM"); }
-            h->f_bps = bps; h->f_warp_smem = wb;
+        // one lane per path, 32 / L frames per warp (decode_scl8q.cu)
+        int bps = 0, wb = 0;
+        if (scl8q_occupancy(h->m, h->L, &bps, &wb) != cudaSuccess || bps == 0) { cudaGetLastError(); h->fast8 = false; }
+        else {
+            const char* benv = getenv("PCB_Q_BPS");     // experiment: fewer resident warps per SM
+            if (benv && atoi(benv) > 0 && atoi(benv) < bps) bps = atoi(benv);
+            h->f_bps = bps; h->f_warp_smem = wb; h->quad = true;
         }
-        // default: one lane per path, 32 / L frames per warp (decode_scl8q.cu); for L = 8
-        // PCB_SCL8_VARIANT=warp selects the one-frame-per-warp kernel (decode_scl8.cu)
-        const char* venv = getenv("PCB_SCL8_VARIANT");
-        h->quad = scl8q_supported(h->m, h->L) && !(l8 && venv && !strcmp(venv, "warp"));
-        if (h->quad) {
-            if (scl8q_occupancy(h->m, h->L, &bps, &wb) != cudaSuccess || bps == 0) { cudaGetLastError(); h->quad = false; }
-            else {
-                const char* benv = getenv("PCB_Q_BPS");     // experiment: fewer resident quads per SM
-                if (benv && atoi(benv) > 0 && atoi(benv) < bps) bps = atoi(benv);
-                h->f_bps = bps; h->f_warp_smem = wb;
-            }
-        }
-        if (!h->quad && !l8) h->fast8 = false;
     }
     h->sc32 = (h->decoder == 2 || h->decoder == 1) && sc32_supported(h->m) && !getenv("PCB_FORCE_GENERIC");
     if (h->sc32 && (sc32_occupancy(h->m, h->fp64, &h->sc32_bps, &h->sc32_smem) != cudaSuccess || h->sc32_bps == 0)) {
@@ -300,7 +291,7 @@ pcb_handle* pcb_create(int device, int n, int k, int crc, int L, int decoder, in
     while ((1 << m) < n) m++;
     if (n < 2 || n > 65536 || (1 << m) != n) { fail(PCB_EINVAL, "n must be a power of two in [2, 65536]"); return nullptr; }
     if (decoder < 1 || decoder > 3) { fail(PCB_EINVAL, "decoder must be 1 (SC), 2 (SCMinsum) or 3 (SCLMinsum)"); return nullptr; }
-    if (decoder != 3) { L = 1; crc = 0; }
+    if (decoder != 3) L = 1;   // the CRC still matters to decoders 1, 2: the loop appends it for every decoder (PolarCodes.cpp:136-155)
     if (L < 1 || L > 32 || (L & (L - 1))) { fail(PCB_EINVAL, "L must be a power of two in [1, 32]"); return nullptr; }
     if (crc != 0 && crc != 8 && crc != 16) { fail(PCB_EINVAL, "crc must be 0, 8 or 16"); return nullptr; }
     if (k < 1 || k + crc > n) { fail(PCB_EINVAL, "need 1 <= k and k + crc <= n"); return nullptr; }
@@ -372,6 +363,8 @@ void pcb_destroy(pcb_handle* h) {
     }
     cudaFree(h->d_ymc); cudaFree(h->d_tx); cudaFree(h->d_dec); cudaFree(h->d_counters);
     cudaFree(h->d_eu); cudaFree(h->d_ex); cudaFree(h->d_redo); cudaFree(h->d_qscratch); cudaFree(h->d_synd); cudaFree(h->d_y32); cudaFree(h->d_yt); cudaFree(h->d_sc32_scratch); cudaFree(h->d_sc32_bits);
+    if (h->comm) nccl_api().CommDestroy(h->comm);
+    cudaFree(h->d_red);
     cudaFreeHost(h->h_stage[0]); cudaFreeHost(h->h_stage[1]); delete h->narrow;
     if (h->t0) cudaEventDestroy(h->t0);
     if (h->t1) cudaEventDestroy(h->t1);
@@ -396,8 +389,7 @@ int pcb_set_code(pcb_handle* h, const int* frozen_mask, double sigma) {
     if (h->decoder == 3 && (int)pos.size() != h->k + h->crc)
         return fail(PCB_EINVAL, "frozen mask has %d information positions, expected k + crc = %d", (int)pos.size(),
                     h->k + h->crc);
-    if (h->decoder != 3 && (int)pos.size() != h->k)
-        return fail(PCB_EINVAL, "frozen mask has %d information positions, expected k = %d", (int)pos.size(), h->k);
+    h->ninfo = (int)pos.size();     // decoders 1, 2 decode any mask; pcb_montecarlo / pcb_generate_* want k + crc positions
     pos.resize(n, 0);
     CK(cudaMemcpyAsync(h->d_info_mask, im.data(), NW * 4, cudaMemcpyHostToDevice, h->sc));
     CK(cudaMemcpyAsync(h->d_frozen_val, fv.data(), NW * 4, cudaMemcpyHostToDevice, h->sc));
@@ -428,7 +420,8 @@ int pcb_set_code(pcb_handle* h, const int* frozen_mask, double sigma) {
                 if ((col >> t) & 1) S[(size_t)t * NW + (i >> 5)] |= 1u << (i & 31);
         }
         if (!h->d_synd) CK(cudaMalloc(&h->d_synd, (size_t)16 * NW * 4));
-        CK(cudaMemcpy(h->d_synd, S.data(), (size_t)16 * NW * 4, cudaMemcpyHostToDevice));
+        CK(cudaMemcpyAsync(h->d_synd, S.data(), (size_t)16 * NW * 4, cudaMemcpyHostToDevice, h->sc));
+        CK(cudaStreamSynchronize(h->sc));   // S is a local: the copy has landed before it goes away; ordered before any decode on h->sc
         h->synd_c0 = c0;
     }
     // the tuned list-8 kernel assumes all-zero frozen values (what the reference uses,
@@ -438,6 +431,14 @@ int pcb_set_code(pcb_handle* h, const int* frozen_mask, double sigma) {
     h->fast8 = h->f_bps > 0 && !any_fv;
     h->sigma = sigma;
     h->code_set = true;
+    return PCB_OK;
+}
+
+int pcb_alu_peak(pcb_handle* h, double* lane_ops_per_s) {
+    if (!h || !lane_ops_per_s) return fail(PCB_EINVAL, "pcb_alu_peak: null argument");
+    int khz = 0;
+    CK(cudaDeviceGetAttribute(&khz, cudaDevAttrClockRate, h->device));
+    *lane_ops_per_s = (double)h->sm_count * (h->fp64 ? 64.0 : 128.0) * (double)khz * 1e3;
     return PCB_OK;
 }
 
@@ -459,7 +460,7 @@ int pcb_info(pcb_handle* h, int* sm_count, int* warps_per_block, int* blocks, in
 // ------------------------------------------------------------------ decode plumbing ------
 static DecodeArgs make_args(pcb_handle* h, const void* d_y, int y_f32, int* d_sol, uint32_t* d_solb, int B) {
     DecodeArgs a;
-    a.n = h->n; a.m = h->m; a.k = h->k; a.crc = h->crc; a.B = B;
+    a.n = h->n; a.m = h->m; a.k = h->k; a.crc = h->decoder == 3 ? h->crc : 0; a.B = B;   // the SC decoders never look at the CRC
     a.first_smem_layer = h->ls; a.warp_smem_bytes = h->warp_smem; a.stride = h->stride;
     a.y = d_y; a.y_f32 = y_f32;
     a.info_mask = h->d_info_mask; a.frozen_val = h->d_frozen_val; a.info_pos = h->d_info_pos;
@@ -519,7 +520,7 @@ static cudaError_t launch(pcb_handle* h, const DecodeArgs& a, cudaStream_t st) {
             }
             e = launch_decode_scl8q(f, h->L, h->h_info_w.data(), h->d_synd, h->synd_c0, h->d_qscratch, h->d_redo + 1, nq < fast_blocks(h) ? nq : fast_blocks(h), st);
         } else {
-            e = launch_decode_scl8(f, h->h_info_w.data(), h->h_fv_w.data(), a.B < fast_blocks(h) ? a.B : fast_blocks(h), st);
+            return cudaErrorInvalidValue;
         }
         if (e != cudaSuccess) return e;
         f.use_redo_list = 1;
@@ -596,7 +597,9 @@ static int decode_host(pcb_handle* h, const void* y, int y_f32, int* sol, uint32
     auto t_iter = std::chrono::steady_clock::now();
     if (narrow) {
         if (h->stage_frames < chunk) {
-            cudaFreeHost(h->h_stage[0]); cudaFreeHost(h->h_stage[1]);
+            if (h->comm) nccl_api().CommDestroy(h->comm);
+    cudaFree(h->d_red);
+    cudaFreeHost(h->h_stage[0]); cudaFreeHost(h->h_stage[1]);
             h->h_stage[0] = h->h_stage[1] = nullptr; h->stage_frames = 0;
             for (int s = 0; s < 2; s++) CK(cudaHostAlloc(&h->h_stage[s], chunk * (size_t)h->n * 4, cudaHostAllocDefault));
             h->stage_frames = chunk;
@@ -753,6 +756,14 @@ static int ensure_mc(pcb_handle* h, size_t frames) {
     return PCB_OK;
 }
 
+// frame generation scatters k + crc payload bits (PolarCodes.cpp:133-156): the mask must have as many positions
+static int check_gen(const pcb_handle* h, const char* who) {
+    if (h->ninfo != h->k + h->crc)
+        return fail(PCB_ESTATE, "%s: the frozen mask has %d information positions, frame generation needs k + crc = %d", who,
+                    h->ninfo, h->k + h->crc);
+    return PCB_OK;
+}
+
 static GenArgs gen_args(pcb_handle* h, double snr_db, uint64_t seed, uint64_t first, int B) {
     GenArgs g;
     g.n = h->n; g.m = h->m; g.k = h->k; g.crc = h->crc; g.B = B;
@@ -785,6 +796,7 @@ int pcb_montecarlo(pcb_handle* h, double snr_db, uint64_t frames, uint64_t seed,
                    uint64_t* frames_done, uint64_t* frame_errors, uint64_t* bit_errors, double* seconds) {
     if (!h) return fail(PCB_EINVAL, "pcb_montecarlo: null handle");
     if (!h->code_set) return fail(PCB_ESTATE, "pcb_montecarlo: call pcb_set_code first");
+    if (int r = check_gen(h, "pcb_montecarlo")) return r;
     if (int r = ensure_device(h)) return r;
     size_t batch = mc_batch(h);
     if (batch > frames) batch = (size_t)frames;
@@ -793,12 +805,13 @@ int pcb_montecarlo(pcb_handle* h, double snr_db, uint64_t frames, uint64_t seed,
     CK(cudaMemsetAsync(h->d_counters, 0, 16, h->sc));
     double secs = 0;
     const int nbits = h->decoder == 3 ? h->k : h->n;
-    h->sigma = pcb_sigma(h->n, h->k, snr_db);
+    const double mc_sigma = pcb_sigma(h->n, h->k, snr_db);   // exact SC scales by 2/sigma^2 (SCDecoder.cpp:15-17); the handle's sigma stays the caller's
     for (uint64_t f0 = 0; f0 < frames; f0 += batch) {
         const int nb = (int)(frames - f0 < batch ? frames - f0 : batch);
         GenArgs g = gen_args(h, snr_db, seed, first_frame_id + f0, nb);
         CK(launch_generate(g, h->sm_count, h->sc));
         DecodeArgs a = make_args(h, h->d_ymc, 1, nullptr, h->d_dec, nb);
+        a.sigma = mc_sigma;
         CK(cudaEventRecord(h->t0, h->sc));
         CK(launch(h, a, h->sc));
         CK(cudaEventRecord(h->t1, h->sc));
@@ -822,6 +835,7 @@ int pcb_generate_batch_dev(pcb_handle* h, double snr_db, uint64_t seed, uint64_t
                            float* y_dev, uint32_t* tx_bits_dev) {
     if (!h || !y_dev) return fail(PCB_EINVAL, "pcb_generate_batch_dev: null argument");
     if (!h->code_set) return fail(PCB_ESTATE, "pcb_generate_batch_dev: call pcb_set_code first");
+    if (int r = check_gen(h, "pcb_generate_batch_dev")) return r;
     if (B <= 0) return B == 0 ? PCB_OK : fail(PCB_EINVAL, "B < 0");
     if (int r = ensure_device(h)) return r;
     GenArgs g = gen_args(h, snr_db, seed, first_frame_id, B);
@@ -836,6 +850,7 @@ int pcb_generate_batch(pcb_handle* h, double snr_db, uint64_t seed, uint64_t fir
                        int* tx_bits) {
     if (!h || !y) return fail(PCB_EINVAL, "pcb_generate_batch: null argument");
     if (!h->code_set) return fail(PCB_ESTATE, "pcb_generate_batch: call pcb_set_code first");
+    if (int r = check_gen(h, "pcb_generate_batch")) return r;
     if (B <= 0) return B == 0 ? PCB_OK : fail(PCB_EINVAL, "B < 0");
     if (int r = ensure_device(h)) return r;
     if (int r = ensure_mc(h, (size_t)B)) return r;
@@ -850,6 +865,75 @@ int pcb_generate_batch(pcb_handle* h, double snr_db, uint64_t seed, uint64_t fir
         for (int f = 0; f < B; f++)
             for (int t = 0; t < h->stride; t++)
                 tx_bits[(size_t)f * h->stride + t] = (tx[(size_t)f * h->EW + (t >> 5)] >> (t & 31)) & 1;
+    return PCB_OK;
+}
+
+
+// ---- error counting and the counter reduction (the path's only collective) --------------------
+int pcb_count_errors_dev(pcb_handle* h, const uint32_t* dec_bits_dev, const uint32_t* tx_bits_dev, int B, int allreduce,
+                         uint64_t* counters) {
+    if (!h || !dec_bits_dev || !tx_bits_dev || !counters) return fail(PCB_EINVAL, "pcb_count_errors_dev: null argument");
+    if (B < 0) return fail(PCB_EINVAL, "pcb_count_errors_dev: B < 0");
+    if (allreduce && !h->comm) return fail(PCB_ESTATE, "pcb_count_errors_dev: allreduce without pcb_comm_init");
+    if (int r = ensure_device(h)) return r;
+    if (!h->d_red) CK(cudaMalloc(&h->d_red, 8 * sizeof(unsigned long long)));
+    const unsigned long long init[3] = {(unsigned long long)B, 0ull, 0ull};
+    CK(cudaMemcpyAsync(h->d_red, init, sizeof init, cudaMemcpyHostToDevice, h->sc));
+    if (B) {
+        CK(launch_count(dec_bits_dev, tx_bits_dev, h->EW, h->decoder == 3 ? h->k : h->n, B, h->d_red + 1, h->sc));
+        h->launches++;
+    }
+    if (allreduce) {
+        NcclApi& nc = nccl_api();
+        const int rc = nc.AllReduce(h->d_red, h->d_red, 3, NcclApi::kUint64, NcclApi::kSum, h->comm, h->sc);
+        if (rc) return fail(PCB_ECUDA, "ncclAllReduce: %s", nc.GetErrorString(rc));
+        h->collectives++;
+    }
+    unsigned long long out[3];
+    CK(cudaMemcpyAsync(out, h->d_red, sizeof out, cudaMemcpyDeviceToHost, h->sc));
+    CK(cudaStreamSynchronize(h->sc));
+    for (int i = 0; i < 3; i++) counters[i] += out[i];
+    return PCB_OK;
+}
+
+int pcb_comm_unique_id(void* id128) {
+    if (!id128) return fail(PCB_EINVAL, "pcb_comm_unique_id: null argument");
+    NcclApi& nc = nccl_api();
+    if (const char* why = nc.load()) return fail(PCB_ESTATE, "NCCL unavailable: %s", why);
+    NcclApi::UniqueId id;
+    const int rc = nc.GetUniqueId(&id);
+    if (rc) return fail(PCB_ECUDA, "ncclGetUniqueId: %s", nc.GetErrorString(rc));
+    memcpy(id128, &id, sizeof id);
+    return PCB_OK;
+}
+
+int pcb_comm_init(pcb_handle* h, const void* id128, int rank, int world) {
+    if (!h || !id128) return fail(PCB_EINVAL, "pcb_comm_init: null argument");
+    if (world < 1 || rank < 0 || rank >= world) return fail(PCB_EINVAL, "pcb_comm_init: rank %d of %d", rank, world);
+    if (h->comm) return fail(PCB_ESTATE, "pcb_comm_init: the handle already has a communicator");
+    if (int r = ensure_device(h)) return r;
+    NcclApi& nc = nccl_api();
+    if (const char* why = nc.load()) return fail(PCB_ESTATE, "NCCL unavailable: %s", why);
+    NcclApi::UniqueId id;
+    memcpy(&id, id128, sizeof id);
+    const int rc = nc.CommInitRank(&h->comm, world, id, rank);
+    if (rc) { h->comm = nullptr; return fail(PCB_ECUDA, "ncclCommInitRank: %s", nc.GetErrorString(rc)); }
+    h->comm_rank = rank; h->comm_world = world;
+    if (!h->d_red) CK(cudaMalloc(&h->d_red, 8 * sizeof(unsigned long long)));
+    return PCB_OK;
+}
+
+int pcb_comm_allreduce(pcb_handle* h, uint64_t* counters, int count) {
+    if (!h || !counters || count < 1 || count > 8) return fail(PCB_EINVAL, "pcb_comm_allreduce: bad argument");
+    if (!h->comm) return fail(PCB_ESTATE, "pcb_comm_allreduce: call pcb_comm_init first");
+    if (int r = ensure_device(h)) return r;
+    NcclApi& nc = nccl_api();
+    CK(cudaMemcpyAsync(h->d_red, counters, count * sizeof(uint64_t), cudaMemcpyHostToDevice, h->sc));
+    const int rc = nc.AllReduce(h->d_red, h->d_red, (size_t)count, NcclApi::kUint64, NcclApi::kSum, h->comm, h->sc);
+    if (rc) return fail(PCB_ECUDA, "ncclAllReduce: %s", nc.GetErrorString(rc));
+    h->collectives++;
+    CK(cudaMemcpyAsync(counters, h->d_red, count * sizeof(uint64_t), cudaMemcpyDeviceToHost, h->sc));
+    CK(cudaStreamSynchronize(h->sc));
     return PCB_OK;
 }
 

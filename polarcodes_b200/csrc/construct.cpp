@@ -122,4 +122,36 @@ int pcb_append_crc(int* xinf, int k, int crc) {
     return PCB_OK;
 }
 
+
+// Algorithmic ALU work of one frame under the SURVEY.md section 8(d) convention, counted exactly from the
+// frozen mask: f = 4 lane-ops, g = 2, path-metric update 2 per live path and phase, one compare-exchange
+// of the (bitonic-convention) median select 3, one per packed 32-bit word of partial-sum XORs.  The list
+// is a_i = min(L, 2^(information positions before i)) paths wide at phase i; phase i recomputes layers
+// m-d..m with d = min(m-1, ctz i) (d = m-1 at i = 0), the first one a g-layer iff bit d of i is set.
+int pcb_lane_ops_per_frame(const int* frozen_mask, int n, int L, int decoder, double* lane_ops, double* llr_updates) {
+    const bool list = decoder == PCB_DEC_SCLMINSUM;     // the SC decoders keep no metric and select nothing
+    if (!list) L = 1;
+    if (!frozen_mask || !pow2(n) || n < 2 || L < 1 || !lane_ops) return pcb::fail(PCB_EINVAL, "pcb_lane_ops_per_frame: bad argument");
+    int m = 0;
+    while ((1 << m) < n) m++;
+    double f = 0, g = 0, sa = 0;
+    int seen = 0, ninfo = 0;
+    for (int i = 0; i < n; i++) {
+        const double a = seen >= 30 ? L : std::min<double>(L, (double)(1u << seen));
+        const int d = i == 0 ? m - 1 : std::min(m - 1, __builtin_ctz((unsigned)i));
+        const double size = (double)(1u << d);
+        if ((i >> d) & 1) { g += a * size; f += a * (size - 1); }
+        else f += a * (2 * size - 1);
+        sa += a;
+        if (frozen_mask[i] == -1) { seen++; ninfo++; }
+    }
+    int l2 = 0;
+    while ((1 << l2) < 2 * L) l2++;
+    const double ce = list ? (double)ninfo * L * l2 * (l2 + 1) / 2 : 0;
+    const double x = std::floor((f + g) / 2 / 32);
+    *lane_ops = 4 * f + 2 * g + (list ? 2 * sa : 0) + 3 * ce + x;
+    if (llr_updates) *llr_updates = f + g;
+    return PCB_OK;
+}
+
 }  // extern "C"

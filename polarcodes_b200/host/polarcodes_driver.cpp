@@ -11,6 +11,15 @@
 //   PCB_GPUS=<g>     use GPUs 0..g-1 of this box (one host thread + handle per GPU); frames are
 //                    sharded by global frame id, counters summed on the host (24 bytes per SNR
 //                    point; bench.py does the same reduction with NCCL across processes)
+//   one process per GPU (torchrun --no-python, mpirun, or a shell loop): with WORLD_SIZE > 1 in the
+//                    environment (RANK, LOCAL_RANK as torchrun sets them) every process drives GPU
+//                    LOCAL_RANK, decodes its share of each slice and the ranks sum
+//                    {frames, frame errors, bit errors} with ncclAllReduce after every slice — that
+//                    is also the poll of the cross-rank error budget (PCB_MAX_ERRORS).  Rank 0 hands
+//                    the NCCL unique id to the others through the file PCB_NCCL_ID_FILE (default
+//                    /tmp/pcb_nccl_id.<parent pid>.<MASTER_PORT>), prints, checkpoints and writes the
+//                    result file; the counters equal those of a one-GPU run (Philox is keyed by the
+//                    global frame id).
 //   PCB_SEED=<s>     Philox seed (default 0x5EED0000 + SNR index as SURVEY.md §8(d))
 //   PCB_CSV=<file>   extra CSV with BER, frames/s, info Gbit/s per SNR point
 //   PCB_CONF=<file>  configuration file (default conf.txt in the CWD, like the reference)
@@ -34,12 +43,16 @@
 #include <fstream>
 #include <iostream>
 #include <string>
+#include <chrono>
+#include <sys/stat.h>
 #include <thread>
+#include <unistd.h>
 #include <vector>
 
 #include "../../include/polar_b200.h"
 
 struct Point {
+    double lane_ops = 0;   // algorithmic ALU lane-ops per frame of this point's mask (not checkpointed: recomputed)
     uint64_t frames = 0, frame_errors = 0, bit_errors = 0;
     double seconds = 0;
     uint64_t cursor = 0;   // global frame ids below the cursor are accounted for
@@ -93,8 +106,43 @@ static void fail(const char* what) {
     std::exit(2);
 }
 
+static int env_int(const char* name, int dflt) {
+    const char* e = std::getenv(name);
+    return e && *e ? std::atoi(e) : dflt;
+}
+
+// Rank 0 publishes the NCCL unique id in a file (tmp + rename); the other ranks wait for a fresh one.
+static void exchange_id(int rank, char (&id)[128]) {
+    std::string path;
+    if (const char* e = std::getenv("PCB_NCCL_ID_FILE")) path = e;
+    else {
+        const char* port = std::getenv("MASTER_PORT");
+        path = "/tmp/pcb_nccl_id." + std::to_string((long)getppid()) + "." + (port ? port : "0");
+    }
+    if (rank == 0) {
+        if (pcb_comm_unique_id(id) != PCB_OK) fail("pcb_comm_unique_id");
+        const std::string tmp = path + ".tmp";
+        { std::ofstream f(tmp, std::ios::binary); f.write(id, 128); }
+        std::rename(tmp.c_str(), path.c_str());
+        return;
+    }
+    const time_t started = time(nullptr);
+    for (int tries = 0; tries < 6000; tries++) {      // up to ten minutes
+        struct stat st;
+        if (stat(path.c_str(), &st) == 0 && st.st_size == 128 && st.st_mtime >= started - 30) {
+            std::ifstream f(path, std::ios::binary);
+            if (f.read(id, 128)) return;
+        }
+        std::this_thread::sleep_for(std::chrono::milliseconds(100));
+    }
+    std::fprintf(stderr, "polarcodes_driver: rank %d never saw the NCCL id file %s\n", rank, path.c_str());
+    std::exit(2);
+}
+
 int main() {
     int testType, n, k, decoder, zComputer, L, crc, loop, nth, qFraction;
+    const int world = std::max(1, env_int("WORLD_SIZE", 1)), rank = env_int("RANK", 0), local_rank = env_int("LOCAL_RANK", rank);
+    if (rank != 0) std::cout.setstate(std::ios::failbit);      // one voice: rank 0 prints, checkpoints and writes the files
     const char* conf = std::getenv("PCB_CONF");
     std::ifstream fin(conf ? conf : "conf.txt");
     if (!fin) { std::fprintf(stderr, "polarcodes_driver: cannot open %s\n", conf ? conf : "conf.txt"); return 2; }
@@ -134,20 +182,30 @@ int main() {
     int gpus = 1;
     if (const char* g = std::getenv("PCB_GPUS")) gpus = std::max(1, std::atoi(g));
     gpus = std::min(gpus, std::max(1, pcb_device_count()));
+    if (world > 1) gpus = 1;                                   // one process per GPU
     const char* seed_env = std::getenv("PCB_SEED");
-    const int ecrc = decoder == 3 ? crc : 0;   // only the list decoder appends/uses the CRC (:136-155,:442-472)
+    // The loop appends the CRC to the payload and builds InfIndexesAWGN(n, k + crc) for EVERY decoder
+    // (:125, :136-155); only the list decoder checks it (:442-472).  The BEC construction ignores crc
+    // (InfIndexesBEC(n, k), :125): with crc > 0 the reference then over-reads its frozen vector (:127,
+    // Encoder.cpp:17-33) — undefined there; here decoders 1, 2 run the k-position code and decoder 3 is refused.
+    const int ecrc = zComputer == 1 && decoder != 3 ? 0 : crc;
 
     std::vector<pcb_handle*> hs(gpus, nullptr);
     for (int g = 0; g < gpus; g++) {
-        hs[g] = pcb_create(g, n, k, ecrc, L, decoder, PCB_PREC_STRICT);
+        hs[g] = pcb_create(world > 1 ? local_rank : g, n, k, ecrc, L, decoder, PCB_PREC_STRICT);
         if (!hs[g]) fail("pcb_create");
+    }
+    if (world > 1) {
+        char id[128];
+        exchange_id(rank, id);
+        if (pcb_comm_init(hs[0], id, rank, world) != PCB_OK) fail("pcb_comm_init");
     }
 
     std::vector<std::pair<double, double>> res;
     std::vector<Point> points(nth);
     const char* ckpt = std::getenv("PCB_CKPT");
     const std::string header = ckpt_header(testType, n, k, loop, decoder, zComputer, L, crc, snr, seed_env);
-    if (ckpt && ckpt_load(ckpt, header, points)) std::cout << "Resuming from " << ckpt << "\n";
+    if (ckpt && ckpt_load(ckpt, header, points)) std::cout << "Resuming from " << ckpt << "\n";   // every rank reads the same file
     uint64_t slice = 1ull << 22;
     if (const char* e = std::getenv("PCB_SLICE")) slice = std::max<uint64_t>(1, std::strtoull(e, nullptr, 0));
     uint64_t max_errors = 0, stop_after = 0, slices_done = 0;
@@ -166,11 +224,12 @@ int main() {
         const uint64_t seed = seed_env ? std::strtoull(seed_env, nullptr, 0) : (0x5EED0000ull + (uint64_t)si);
         const uint64_t total = (uint64_t)std::max(loop, 0);
         Point& p = points[si];
+        if (pcb_lane_ops_per_frame(mask.data(), n, L, decoder, &p.lane_ops, nullptr) != PCB_OK) fail("pcb_lane_ops_per_frame");
         bool code_set = false;
         while (!p.done) {
             if (p.cursor >= total || (max_errors && p.frame_errors >= max_errors)) {
                 p.done = 1;
-                if (ckpt) ckpt_save(ckpt, header, points);
+                if (ckpt && rank == 0) ckpt_save(ckpt, header, points);
                 break;
             }
             if (stop_after && slices_done >= stop_after) {
@@ -184,7 +243,8 @@ int main() {
             for (int g = 0; g < gpus; g++) {
                 th.emplace_back([&, g]() {
                     if (!code_set && pcb_set_code(hs[g], mask.data(), sigma) != PCB_OK) fail("pcb_set_code");
-                    const uint64_t lo = base + len * g / gpus, hi = base + len * (g + 1) / gpus;
+                    const int part_i = world > 1 ? rank : g, parts = world > 1 ? world : gpus;
+                    const uint64_t lo = base + len * part_i / parts, hi = base + len * (part_i + 1) / parts;
                     if (hi > lo &&
                         pcb_montecarlo(hs[g], snr[si], hi - lo, seed, lo, &part[g].frames, &part[g].frame_errors,
                                        &part[g].bit_errors, &part[g].seconds) != PCB_OK)
@@ -194,14 +254,23 @@ int main() {
             for (auto& t : th) t.join();
             code_set = true;
             double sec = 0;
-            for (int g = 0; g < gpus; g++) {
-                p.frames += part[g].frames; p.frame_errors += part[g].frame_errors; p.bit_errors += part[g].bit_errors;
-                sec = std::max(sec, part[g].seconds);
+            if (world > 1) {
+                // the reference's `er` counter (:129,165,174,183,193) summed over the ranks; every rank gets the
+                // totals, so every rank takes the same stop decision at the next slice boundary
+                uint64_t c[4] = {part[0].frames, part[0].frame_errors, part[0].bit_errors, (uint64_t)(part[0].seconds * 1e9)};
+                if (pcb_comm_allreduce(hs[0], c, 4) != PCB_OK) fail("pcb_comm_allreduce");
+                p.frames += c[0]; p.frame_errors += c[1]; p.bit_errors += c[2];
+                sec = (double)c[3] * 1e-9 / world;              // mean decode-kernel time of the ranks
+            } else {
+                for (int g = 0; g < gpus; g++) {
+                    p.frames += part[g].frames; p.frame_errors += part[g].frame_errors; p.bit_errors += part[g].bit_errors;
+                    sec = std::max(sec, part[g].seconds);
+                }
             }
             p.seconds += sec;
             p.cursor = base + len;
             slices_done++;
-            if (ckpt) ckpt_save(ckpt, header, points);
+            if (ckpt && rank == 0) ckpt_save(ckpt, header, points);
         }
         if (testType == 1) {
             const double fer = p.frames ? (double)p.frame_errors / (double)p.frames : 0.0;
@@ -214,6 +283,10 @@ int main() {
         }
     }
     const clock_t endT = clock();
+    if (rank != 0) {                                           // rank 0 alone writes the result file and the CSV
+        for (auto h : hs) pcb_destroy(h);
+        return 0;
+    }
     std::sort(res.begin(), res.end());
     std::ofstream fout("SC_" + std::to_string(testType) + "_" + std::to_string(n) + "_" + std::to_string(k) + "_L" +
                        std::to_string(L) + "_CRC" + std::to_string(crc) + "_" + std::to_string(time(0)) + ".txt");
@@ -222,15 +295,18 @@ int main() {
 
     if (const char* csv = std::getenv("PCB_CSV")) {
         std::ofstream c(csv);
-        c << "snr_db,frames,frame_errors,bit_errors,fer,ber,decode_seconds,frames_per_s,info_gbit_per_s\n";
+        c << "snr_db,frames,frame_errors,bit_errors,fer,ber,decode_seconds,frames_per_s,info_gbit_per_s,lane_ops_per_frame,alu_roofline_frac\n";
         const double bits = decoder == 3 ? k : n;
+        double peak = 0;                                        // SMs x lanes x max SM clock of GPU 0, times the GPUs
+        if (pcb_alu_peak(hs[0], &peak) != PCB_OK) fail("pcb_alu_peak");
+        peak *= world > 1 ? world : gpus;
         for (int si = 0; si < nth; si++) {
             const Point& p = points[si];
             const double fps = p.seconds > 0 ? p.frames / p.seconds : 0;
             c << snr[si] << ',' << p.frames << ',' << p.frame_errors << ',' << p.bit_errors << ','
               << (p.frames ? (double)p.frame_errors / p.frames : 0) << ','
               << (p.frames ? (double)p.bit_errors / (p.frames * bits) : 0) << ',' << p.seconds << ',' << fps << ','
-              << fps * k / 1e9 << '\n';
+              << fps * k / 1e9 << ',' << p.lane_ops << ',' << (peak > 0 ? fps * p.lane_ops / peak : 0) << '\n';
         }
     }
     for (auto h : hs) pcb_destroy(h);

@@ -179,11 +179,7 @@ def test_montecarlo_consistency(oracle):
     b = d.montecarlo(snr, 312, seed=77, first_frame_id=200)
     assert a["frame_errors"] + b["frame_errors"] == r["frame_errors"]
     assert a["bit_errors"] + b["bit_errors"] == r["bit_errors"]
-    # noise statistics of the generator
-    s = pb.lib().pcb_sigma(n, k, snr)
-    cw = np.where(y > 0, 1.0, -1.0)
-    noise = (y - cw)[np.abs(y) > 1.0]
-    assert abs(np.std(y - np.sign(y) * 1.0) / s - 1) < 0.2
+    # (the noise statistics of the generator are tested in test_gpu_ref_parity.py::test_channel_noise_statistics)
 
 
 def test_sc_montecarlo_fer_matches_published():
@@ -249,23 +245,6 @@ def test_quad_kernel_one_bad_frame_per_quad(oracle):
     got, want = d.decode(y), oracle.decode(3, n, L, k, crc, sigma, y, mask)
     bad = np.nonzero((got != want).any(axis=1))[0]
     assert bad.size == 0, f"frames {bad.tolist()} differ"
-
-
-@pytest.mark.parametrize("n,k,crc,snr", [(1024, 512, 16, 1.0), (256, 128, 8, 1.5), (2048, 1024, 0, 2.0)])
-def test_one_frame_per_warp_variant_agrees(oracle, n, k, crc, snr):
-    """PCB_SCL8_VARIANT=warp keeps the one-frame-per-warp list-8 kernel selectable; both tuned
-    kernels and the oracle agree."""
-    rng = np.random.default_rng(7 + n)
-    sigma, inf, mask = oracle.make_code(n, k, crc, snr)
-    y = 1 + sigma * rng.standard_normal((40, n))
-    want = oracle.decode(3, n, 8, k, crc, sigma, y, mask)
-    quad = _decoder(3, n, k, crc, 8, mask, sigma).decode(y)
-    os.environ["PCB_SCL8_VARIANT"] = "warp"
-    try:
-        warp = _decoder(3, n, k, crc, 8, mask, sigma).decode(y)
-    finally:
-        del os.environ["PCB_SCL8_VARIANT"]
-    assert (quad == want).all() and (warp == want).all()
 
 
 @pytest.mark.parametrize("frac", ["0", "0.5", "1", "auto", "off"])
