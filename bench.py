@@ -3,17 +3,24 @@
 
   python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
 
-A "step" is one pass of the decoder over one batch of synthetic frames (on-device Philox
-BPSK/AWGN codewords of the AWGN-constructed code, 2.0 dB).  Workload: SCLDecoderMinsum L=8,
-N=1024, K=512 (BASELINE.json configs[2], the configuration the metric is quoted on).
-  value     decoded info Gbit/s with the channel values already resident in HBM (kernel path)
-  e2e       same metric through the reference-facing C-ABI call pcb_decode_batch with HOST
-            (pinned) double buffers: H2D + kernel + D2H inside the timed region
-  roofline  ALU lane-ops (SURVEY.md §8(d) convention, counted exactly from the frozen mask)
-            / kernel time from CUDA events / (SMs * 128 lanes * max SM clock)
-  cpu_baseline  the unmodified reference (oracle/_ref) or the C port timed on the host cores
-Multi-GPU: one process per GPU (torchrun), frames sharded, no data-path collective; NCCL
-only sums the error counters (weak scaling).
+A "step" is one pass of the decoder over one batch of synthetic frames (on-device Philox BPSK/AWGN
+codewords of the AWGN-constructed code, 2.0 dB) followed by the error count of that batch and — at
+N > 1 — the NCCL all-reduce of the three counters through the product's own communicator
+(pcb_count_errors_dev), i.e. the loop body of PolarCodes.cpp:132-193 for a whole batch.  Workload:
+SCLDecoderMinsum L=8, N=1024, K=512 (BASELINE.json configs[2], the configuration the metric is quoted on).
+  value     decoded info Gbit/s with the channel values (double, the reference's type) resident in HBM
+  e2e       same metric through the reference-facing C-ABI call pcb_decode_batch with HOST (pinned) double
+            buffers: H2D + kernels + D2H inside the timed region; `bound` = what the measured PCIe and
+            host-narrowing rates allow
+  roofline  ALU lane-ops (SURVEY.md 8(d) convention, counted exactly from the frozen mask) / kernel time
+            from CUDA events on the launch stream / (SMs * 128 lanes * max SM clock)
+  configs   the other BASELINE.json configurations (A double / A' fp32, B, C crc16, D, E): frames/s, Gbit/s,
+            their own ALU-roofline fraction (fp64 decoders against 64 lanes per SM) and DRAM bytes per
+            algorithmic byte from the committed ncu capture — N = 1 only
+  montecarlo  the drop-in for the reference loop: pcb_montecarlo (Philox -> CRC -> encode -> decode -> count
+            on the device, nothing crosses PCIe), wall clock of the call — N = 1 only
+  cpu_baseline  the unmodified reference (oracle/_ref) or the C port timed on the host cores — N = 1 only
+Multi-GPU: one process per GPU (torchrun), frames sharded, no data-path collective (weak scaling).
 """
 import argparse
 import json
@@ -32,9 +39,17 @@ N, K, LIST, SNR_DB = 1024, 512, 8, 2.0
 METRIC = "decoded info Gbit/s, SCL-8 N=1024 K=512"
 
 
+def workload_config(crc):
+    """Identical in both arms (ours / --impl reference): the driver compares the two `config` objects."""
+    return {"workload": f"SCLDecoderMinsum L={LIST} N={N} K={K} crc={crc} AWGN-construction {SNR_DB} dB",
+            "decoder": "SCLDecoderMinsum", "n": N, "k": K, "L": LIST, "crc": crc, "snr_db": SNR_DB,
+            "construction": "AWGN (InfIndexesAWGN at the operating SNR)", "input": "double y[B][n], BPSK + AWGN"}
+
+
 def lane_ops_per_frame(mask, L):
     """f=4, g=2 lane-ops per LLR update, PM update 2, one compare-exchange of
-    the (bitonic-convention) median select 3, one partial-sum XOR per packed 32-bit word."""
+    the (bitonic-convention) median select 3, one partial-sum XOR per packed 32-bit word.
+    (Python twin of pcb_lane_ops_per_frame, kept for the breakdown it returns.)"""
     n = len(mask)
     m = n.bit_length() - 1
     f = g = sa = 0
@@ -59,8 +74,7 @@ def lane_ops_per_frame(mask, L):
 
 
 class ClockSampler(threading.Thread):
-    """Samples SM clock and throttle reasons DURING the timed region: NVML every ~2 ms (the timed
-    region of a default run is only ~50 ms), nvidia-smi as a fallback."""
+    """Samples SM clock and throttle reasons DURING the timed region: NVML every ~5 ms, nvidia-smi as a fallback."""
     Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap,power.draw")
     REASONS = (("hw_slowdown", 0x8), ("hw_thermal_slowdown", 0x40), ("sw_thermal_slowdown", 0x20), ("sw_power_cap", 0x4))
@@ -109,7 +123,7 @@ class ClockSampler(threading.Thread):
                 self._sample_nvml() if self.nvml else self._sample_smi()
             except Exception:
                 pass
-            self._halt.wait(0.002 if self.nvml else 0.2)
+            self._halt.wait(0.005 if self.nvml else 0.2)
 
     def stop(self):
         self._halt.set()
@@ -122,7 +136,7 @@ class ClockSampler(threading.Thread):
 def cpu_reference_run(frames_total, procs, crc, kind_pref="reference"):
     """Times the reference's own SCL decoder (oracle/_ref) — or the C port when _ref is absent —
     on `procs` host processes (the decoder keeps namespace-global state: processes, not threads).
-    Returns (frames/s, kind, seconds)."""
+    Returns (frames/s, kind, seconds, frames)."""
     from oracle.pyoracle import Oracle, Ref
     use_ref = kind_pref == "reference" and Ref.available()
     o = Oracle()
@@ -174,24 +188,104 @@ def run_reference_arm(args, rank, world):
     line = {"impl": "reference", "metric": METRIC, "value": gbps, "unit": "Gbit/s", "frames_per_s": fps,
             "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * t_sum / args.steps,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": f"SCLDecoderMinsum L={LIST} N={N} K={K} crc={crc} AWGN-construction {SNR_DB} dB",
-                       "frames_per_step": per_step},
+            "config": workload_config(crc),
+            "sample": {"frames_per_step": per_step},
             "cpu_baseline": {"value": gbps, "unit": "Gbit/s", "cores": cores, "kind": kind,
                              "sample": f"{per_step} distinct frames per step, {cores} processes, decode-only"},
             "e2e": {"value": gbps, "unit": "Gbit/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line), flush=True)
 
 
+# ---- the other BASELINE.json configurations: device-resident throughput, N = 1 ---------------
+def sweep_configs(pb, torch, dev, peaks, traffic):
+    cfgs = [  # key, label, decoder, n, k, crc, L, precision, double input, frames
+        ("A", "SCDecoderMinsum N=1024 K=512 fp64 (double y)", pb.SCMINSUM, 1024, 512, 0, 1, pb.STRICT, True, 1 << 20),
+        ("A_fp32", "SCDecoderMinsum N=1024 K=512 fp32 fast mode (float y; not bit-exact by contract)", pb.SCMINSUM, 1024, 512, 0, 1, pb.FP32, False, 1 << 20),
+        ("B", "exact SCDecoder N=256 K=128 fp64 (double y)", pb.SC, 256, 128, 0, 1, pb.STRICT, True, 1 << 20),
+        ("C_crc16", "SCLDecoderMinsum L=8 N=1024 K=512 crc=16 (double y)", pb.SCLMINSUM, 1024, 512, 16, 8, pb.STRICT, True, 1 << 20),
+        ("conf_txt", "SCLDecoderMinsum L=4 N=2048 K=1024 crc=16 (the reference's shipped conf.txt; double y)", pb.SCLMINSUM, 2048, 1024, 16, 4, pb.STRICT, True, 1 << 18),
+        ("D", "SCLDecoderMinsum L=32 N=2048 K=1024 crc=0 (double y)", pb.SCLMINSUM, 2048, 1024, 0, 32, pb.STRICT, True, 1 << 16),
+        ("E", "SCDecoderMinsum N=32768 K=16384 fp64 (double y)", pb.SCMINSUM, 32768, 16384, 0, 1, pb.STRICT, True, 1 << 15),
+    ]
+    out = []
+    for key, label, decoder, n, k, crc, L, prec, dbl, B in cfgs:
+        torch.cuda.empty_cache()
+        code = pb.Code(n, k, crc, SNR_DB)
+        dec = pb.Decoder(n, k, crc, L, decoder, prec, device=dev.index)
+        dec.set_code(code.mask, code.sigma)
+        y = torch.empty((B, n), dtype=torch.float32, device=dev)
+        tx = torch.empty((B, dec.words), dtype=torch.int32, device=dev)
+        dec.generate_dev(SNR_DB, B, y.data_ptr(), tx.data_ptr(), seed=0x5EED0000, first_frame_id=0)
+        if dbl:
+            y = y.double()
+        sol = torch.empty((B, dec.words), dtype=torch.int32, device=dev)
+        for _ in range(2):
+            dec.decode_dev(y.data_ptr(), not dbl, sol.data_ptr(), B)
+        ms, t_budget = [], time.perf_counter() + 1.5
+        while len(ms) < 3 or (time.perf_counter() < t_budget and len(ms) < 50):
+            ms.append(dec.decode_dev(y.data_ptr(), not dbl, sol.data_ptr(), B))
+        cnt = dec.count_errors_dev(sol.data_ptr(), tx.data_ptr(), B)
+        kms = float(np.mean(ms))
+        fps = B / (kms * 1e-3)
+        ops, upd = pb.lane_ops_per_frame(code.mask, L, decoder)
+        peak = dec.alu_peak()
+        alg_bytes = n * (8 if dbl else 4) + dec.words * 4
+        row = {"config": key, "workload": label, "frames_per_launch": B, "launches_timed": len(ms), "kernel_ms": kms,
+               "frames_per_s": fps, "info_gbit_per_s": fps * k / 1e9, "lane_ops_per_frame": ops, "llr_updates_per_frame": upd,
+               "alu_peak_tlane_ops": peak / 1e12, "alu_lanes_per_sm": 64 if dec_is_fp64(pb, decoder, prec) else 128,
+               "alu_frac": fps * ops / peak, "algorithmic_bytes_per_frame": alg_bytes,
+               "hbm_frac_algorithmic": (fps * alg_bytes / 1e9) / peaks["hbm_gbs"] if peaks.get("hbm_gbs") else None,
+               "fer": cnt["frame_errors"] / B, "ber": cnt["bit_errors"] / (B * (k if decoder == pb.SCLMINSUM else n))}
+        t = (traffic or {}).get(key)
+        if t:
+            per_frame = (t["dram_bytes_read"] + t["dram_bytes_write"]) / t["frames_per_launch"]
+            row["dram_bytes_per_frame"] = per_frame
+            row["dram_over_algorithmic"] = per_frame / alg_bytes
+            row["traffic_source"] = t.get("source")
+        out.append(row)
+        dec.close()
+        del y, tx, sol
+    torch.cuda.empty_cache()
+    return out
+
+
+def dec_is_fp64(pb, decoder, prec):
+    return decoder == pb.SC or (decoder == pb.SCMINSUM and prec == pb.STRICT)
+
+
+def montecarlo_leg(pb, dev):
+    """pcb_montecarlo: what replaces the reference's loop body (PolarCodes.cpp:132-192) — wall clock of the call."""
+    out = []
+    for key, decoder, n, k, crc, L, frames in (("C_crc16", pb.SCLMINSUM, 1024, 512, 16, 8, 1 << 24),
+                                               ("C_crc0", pb.SCLMINSUM, 1024, 512, 0, 8, 1 << 23),
+                                               ("A", pb.SCMINSUM, 1024, 512, 0, 1, 1 << 24)):
+        code = pb.Code(n, k, crc, SNR_DB)
+        dec = pb.Decoder(n, k, crc, L, decoder, device=dev.index)
+        dec.set_code(code.mask, code.sigma)
+        dec.montecarlo(SNR_DB, 1 << 20, seed=1)                      # buffers, first launches
+        t0 = time.perf_counter()
+        r = dec.montecarlo(SNR_DB, frames, seed=0x5EED0000)
+        wall = time.perf_counter() - t0
+        out.append({"config": key, "frames": r["frames"], "frame_errors": r["frame_errors"], "bit_errors": r["bit_errors"],
+                    "fer": r["frame_errors"] / r["frames"], "wall_s": wall, "frames_per_s_wall": r["frames"] / wall,
+                    "info_gbit_per_s_wall": r["frames"] / wall * k / 1e9,
+                    "frames_per_s_decode_kernels_only": r["frames"] / r["seconds"] if r["seconds"] else None})
+        dec.close()
+    return out
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours")
     ap.add_argument("--crc", type=int, default=0)
-    ap.add_argument("--frames", type=int, default=1 << 18, help="frames per step per GPU (SURVEY.md 8(d): >= 2^18 per launch)")
-    ap.add_argument("--e2e-frames", type=int, default=1 << 16)
+    ap.add_argument("--frames", type=int, default=1 << 23,
+                    help="frames per step per GPU (SURVEY.md 8(d): >= 2^18 per launch, >= 2 s timed: 2^23 frames ~ 0.2 s)")
+    ap.add_argument("--e2e-frames", type=int, default=1 << 20)
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-extras", action="store_true", help="skip the configs sweep and the Monte-Carlo leg")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -199,28 +293,40 @@ def main():
     if args.impl == "reference":
         run_reference_arm(args, rank, world)
         return
+    if args.warmup < 3:
+        print(f"bench.py: --warmup {args.warmup} < 3 breaks the timing rules (taken as given)", file=sys.stderr)
 
     import torch
     import torch.distributed as dist
     import polarcodes_b200 as pb
 
     torch.cuda.set_device(local)
-    if world > 1:
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
     code = pb.Code(N, K, args.crc, SNR_DB)
     dec = pb.Decoder(N, K, args.crc, LIST, pb.SCLMINSUM, device=local)
     dec.set_code(code.mask, code.sigma)
+    if world > 1:
+        # the product's own communicator: rank 0 draws the NCCL id, torch.distributed only carries the 128 bytes
+        idt = torch.zeros(128, dtype=torch.uint8, device=dev)
+        if rank == 0:
+            idt = torch.frombuffer(bytearray(pb.comm_unique_id()), dtype=torch.uint8).to(dev)
+        dist.broadcast(idt, 0)
+        dec.comm_init(bytes(idt.cpu().numpy().tobytes()), rank, world)
     B = args.frames
     words = dec.words
 
     # synthetic inputs, generated on the device (frame ids disjoint across ranks), widened to the
-    # reference's input type (double).  8 KiB/frame * 131072 = 1 GiB per step: far larger than L2.
+    # reference's input type (double).  8 KiB/frame * 2^23 = 64 GiB per step: far larger than L2.
     y32 = torch.empty((B, N), dtype=torch.float32, device=dev)
     tx = torch.empty((B, words), dtype=torch.int32, device=dev)
     dec.generate_dev(SNR_DB, B, y32.data_ptr(), tx.data_ptr(), seed=0x5EED0000, first_frame_id=rank * B)
-    y64 = y32.double()
+    y64 = torch.empty((B, N), dtype=torch.float64, device=dev)
+    for a in range(0, B, 1 << 20):                           # widen in slices: no third full-size temporary
+        y64[a:a + (1 << 20)].copy_(y32[a:a + (1 << 20)])
     del y32
+    torch.cuda.empty_cache()
     out = torch.empty((B, words), dtype=torch.int32, device=dev)
 
     def barrier():
@@ -229,8 +335,12 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
-    for _ in range(max(args.warmup, 3)):
-        dec.decode_dev(y64.data_ptr(), False, out.data_ptr(), B)
+    def step():
+        ms = dec.decode_dev(y64.data_ptr(), False, out.data_ptr(), B)         # CUDA events on the launch stream
+        return ms, dec.count_errors_dev(out.data_ptr(), tx.data_ptr(), B, allreduce=world > 1)
+
+    for _ in range(args.warmup):
+        step()
     sampler = ClockSampler(local)
     sampler.start()
     barrier()
@@ -238,29 +348,25 @@ def main():
     launches0 = dec.info()["kernel_launches"]
     t0 = time.perf_counter()
     for _ in range(args.steps):
-        kernel_ms.append(dec.decode_dev(y64.data_ptr(), False, out.data_ptr(), B))   # CUDA events on the launch stream
+        ms, counters = step()
+        kernel_ms.append(ms)
     barrier()
     elapsed = time.perf_counter() - t0
-    gpu_launches = dec.info()["kernel_launches"] - launches0   # tuned kernel + its (normally empty) generic follow-up
+    gpu_launches = dec.info()["kernel_launches"] - launches0   # prepass + list kernel + (empty) generic follow-up + error count
     clocks = sampler.stop()
-    # error counters of the last step, summed over ranks with NCCL (the path's only collective)
-    kmask = torch.ones(words * 32, dtype=torch.bool, device=dev)
-    diff = (out ^ tx)
-    bits = ((diff.unsqueeze(-1) >> torch.arange(32, device=dev, dtype=torch.int32)) & 1).reshape(B, -1)[:, :K]
-    counters = torch.stack([torch.tensor(B, device=dev, dtype=torch.int64), bits.any(dim=1).sum(), bits.sum()])
     el = torch.tensor([elapsed, float(np.mean(kernel_ms))], device=dev, dtype=torch.float64)
     if world > 1:
-        dist.all_reduce(counters, op=dist.ReduceOp.SUM)
         dist.all_reduce(el, op=dist.ReduceOp.MAX)
     elapsed, kms = float(el[0]), float(el[1])
-    del kmask, diff, bits
 
-    # end-to-end through the reference-facing call with pinned HOST double buffers
+    # ---- end to end through the reference-facing call with pinned HOST double buffers -------------------
     Be = min(args.e2e_frames, B)
-    hy = torch.empty((Be, N), dtype=torch.float64).pin_memory()
+    hy = torch.empty((Be, N), dtype=torch.float64, pin_memory=True)
     hy.copy_(y64[:Be])
-    hsol = torch.empty((Be, dec.stride), dtype=torch.int32).pin_memory()
+    ref_bits = out[:4096].cpu()
     del y64
+    torch.cuda.empty_cache()
+    hsol = torch.empty((Be, dec.stride), dtype=torch.int32, pin_memory=True)
     for _ in range(2):
         dec.decode_ptr(hy.data_ptr(), hsol.data_ptr(), Be)
     barrier()
@@ -271,14 +377,19 @@ def main():
     e2e_t = torch.tensor([time.perf_counter() - t0], device=dev, dtype=torch.float64)
     if world > 1:
         dist.all_reduce(e2e_t, op=dist.ReduceOp.MAX)
-    e2e_fps = world * Be * args.steps / float(e2e_t[0])
-    # e2e output equals the kernel-path output (same frames)
-    e2e_ok = bool((torch.from_numpy(pb.unpack_bits(out[:256].cpu().numpy().view(np.uint32), dec.stride)) == hsol[:256]).all())
+    e2e_s = float(e2e_t[0])
+    e2e_fps = world * Be * args.steps / e2e_s
+    e2e_ok = bool((torch.from_numpy(pb.unpack_bits(ref_bits.numpy().view(np.uint32), dec.stride)) == hsol[:4096]).all())
+    # what the link and the host cores allow: pinned H2D rate of this GPU and the narrowing rate of this rank's
+    # thread pool, both measured with every rank busy (pcb_host_probe), combined as the pipeline combines them
+    probe = dec.host_probe(hy.data_ptr(), Be)
+    barrier()
     # production variant of the same call: float inputs (the decoder works in fp32, SCLDecoderMinsum.cpp:406-408)
     # and packed output bits — 4 KiB in, 64 B out per frame instead of 8 KiB / 2 KiB
-    hy32 = torch.empty((Be, N), dtype=torch.float32).pin_memory()
+    hy32 = torch.empty((Be, N), dtype=torch.float32, pin_memory=True)
     hy32.copy_(hy)
-    hbits = torch.empty((Be, words), dtype=torch.int32).pin_memory()
+    del hy, hsol
+    hbits = torch.empty((Be, words), dtype=torch.int32, pin_memory=True)
     lib = pb.lib()
     for _ in range(2):
         lib.pcb_decode_batch_f32_packed(dec._h, hy32.data_ptr(), hbits.data_ptr(), Be)
@@ -288,15 +399,23 @@ def main():
         assert lib.pcb_decode_batch_f32_packed(dec._h, hy32.data_ptr(), hbits.data_ptr(), Be) == 0
     barrier()
     e2e32_t = torch.tensor([time.perf_counter() - t0], device=dev, dtype=torch.float64)
+    pr = torch.tensor([probe["h2d_GBps"], probe["narrow_Gvalues_per_s"], probe["bound_frames_per_s"]], device=dev, dtype=torch.float64)
     if world > 1:
         dist.all_reduce(e2e32_t, op=dist.ReduceOp.MAX)
+        dist.all_reduce(pr, op=dist.ReduceOp.SUM)
     e2e32_fps = world * Be * args.steps / float(e2e32_t[0])
-    e2e32_ok = bool((hbits[:256] == out[:256].cpu()).all())
+    e2e32_ok = bool((hbits[:4096] == ref_bits).all())
+    del hy32, hbits
 
     if rank == 0:
         peaks = {}
         try:
             peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        except Exception:
+            pass
+        traffic_all = {}
+        try:
+            traffic_all = json.load(open(os.path.join(ROOT, "profiles", "r2_traffic.json")))
         except Exception:
             pass
         info = dec.info()
@@ -306,39 +425,56 @@ def main():
         peak_lane = info["sm_count"] * 128 * sm_max * 1e6 / 1e12         # T lane-ops/s
         ach = (B / (kms * 1e-3)) * ops["lane_ops"] / 1e12
         hbm_bytes = B * (N * 8 + words * 4)
-        # DRAM bytes of the dominant kernel per launch, from the committed ncu capture of this
-        # command (scaled to this batch size); algorithmic bytes are hbm_bytes
-        traffic, traffic_src = None, None
-        try:
-            tj = json.load(open(os.path.join(ROOT, "profiles", "r1_scl8q_traffic.json")))
+        # DRAM bytes of the dominant kernel per launch, from the committed ncu capture of this workload
+        # (scaled to this batch size); algorithmic bytes are hbm_bytes
+        traffic, traffic_src, executed = None, None, None
+        tj = traffic_all.get("C")
+        if tj:
             traffic = (tj["dram_bytes_read"] + tj["dram_bytes_write"]) * B / tj["frames_per_launch"]
-            traffic_src = tj["source"]
-        except Exception:
-            pass
+            traffic_src = tj.get("source")
+            if tj.get("warp_instructions"):
+                wi = tj["warp_instructions"] / tj["frames_per_launch"]
+                executed = {"warp_instructions_per_frame": wi, "lane_instr_per_frame": 32 * wi,
+                            "lane_instr_rate_frac_of_peak": (B / (kms * 1e-3)) * 32 * wi / 1e12 / peak_lane,
+                            "note": "executed instructions (ncu smsp__inst_executed.sum) x 32 lanes against the same 128-lane peak; the convention figure above charges 3*CE for a bitonic select the kernel mostly skips"}
         line = {
             "metric": METRIC, "value": fps * K / 1e9, "unit": "Gbit/s", "frames_per_s": fps, "n_gpus": world,
-            "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": 1e3 * elapsed / args.steps,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * elapsed / args.steps,
+            "timed_region_s": elapsed,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": f"SCLDecoderMinsum L={LIST} N={N} K={K} crc={args.crc} AWGN-construction {SNR_DB} dB",
-                       "frames_per_step_per_gpu": B, "input": f"double y[B][n] resident in HBM ({B * N * 8 / 2**30:.0f} GiB/step > L2, no flush needed)",
-                       "launch": info},
+            "config": workload_config(args.crc),
+            "setup": {"frames_per_step_per_gpu": B,
+                      "input": f"double y[B][n] resident in HBM ({B * N * 8 / 2**30:.0f} GiB/step > L2, no flush needed)",
+                      "step": "pcb_decode_batch_dev + pcb_count_errors_dev" + (" (ncclAllReduce of the 3 counters inside)" if world > 1 else ""),
+                      "collectives_per_step": 1 if world > 1 else 0, "launch": info},
             "roofline": {"bound": "alu", "achieved": ach, "peak": peak_lane, "unit": "Tlane-op/s", "frac": ach / peak_lane,
                          "traffic": traffic, "traffic_source": traffic_src, "lane_ops_per_frame": ops, "kernel_ms": kms,
                          "kernel_ms_covers": "scl8_prepass + decode_scl8q + decode_generic (empty redo list), CUDA events on the launch stream",
                          "peak_source": f"{info['sm_count']} SMs x 128 fp32/int lanes x {sm_max:.0f} MHz (SURVEY.md §8(d)); no tensor/HBM bound applies",
+                         "executed": executed,
                          "hbm": {"algorithmic_GBps": hbm_bytes / (kms * 1e-3) / 1e9, "peak_GBps": peaks.get("hbm_gbs"),
                                  "frac": (hbm_bytes / (kms * 1e-3) / 1e9) / peaks["hbm_gbs"] if peaks.get("hbm_gbs") else None}},
             "e2e": {"value": e2e_fps * K / 1e9, "unit": "Gbit/s", "frames_per_s": e2e_fps,
                     "h2d_bytes_per_step": Be * N * 8, "d2h_bytes_per_step": Be * dec.stride * 4,
+                    "frames_per_step_per_gpu": Be, "timed_region_s": e2e_s,
                     "matches_kernel_path": e2e_ok,
                     "input": "pinned host double y[B][n] -> int sol[B][k+crc] (the reference's types)",
+                    "bound": {"h2d_GBps_sum": float(pr[0]), "host_narrow_Gvalues_per_s_sum": float(pr[1]),
+                              "bound_frames_per_s": float(pr[2]), "frac_of_bound": e2e_fps / float(pr[2]) if float(pr[2]) > 0 else None,
+                              "how": "pcb_host_probe on every rank at once: pinned H2D copy rate W and thread-pool double->float rate R; "
+                                     "a chunk with head share x narrowed on the host costs max(x/R, (4x + 8(1-x))/W) per value, minimised over x"},
                     "f32_packed_variant": {"value": e2e32_fps * K / 1e9, "unit": "Gbit/s", "frames_per_s": e2e32_fps,
                                            "h2d_bytes_per_step": Be * N * 4, "d2h_bytes_per_step": Be * words * 4,
                                            "matches_kernel_path": e2e32_ok}},
             "gpu_launches": gpu_launches, "clocks": clocks,
-            "errors": {"frames": int(counters[0]), "frame_errors": int(counters[1]), "bit_errors": int(counters[2])},
+            "errors": {"frames": int(counters["frames"]), "frame_errors": int(counters["frame_errors"]),
+                       "bit_errors": int(counters["bit_errors"]), "summed_over_ranks_by": "ncclAllReduce (pcb_count_errors_dev)" if world > 1 else "one rank"},
         }
-        if not args.no_cpu:
+        dec.close()
+        if world == 1 and not args.no_extras:
+            line["configs"] = sweep_configs(pb, torch, dev, peaks, traffic_all)
+            line["montecarlo"] = montecarlo_leg(pb, dev)
+        if not args.no_cpu and world == 1:
             cores = os.cpu_count() or 1
             sample = int(cores * 1300 * 12)
             cfps, kind, wall, nf = cpu_reference_run(sample, cores, args.crc)

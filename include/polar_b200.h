@@ -154,6 +154,13 @@ int pcb_comm_allreduce(pcb_handle* h, uint64_t* counters, int count);
  * 128 per SM (fp32 / int32) or 64 (fp64: decoders 1,2 in strict precision).  lane-ops per second. */
 int pcb_alu_peak(pcb_handle* h, double* lane_ops_per_s);
 
+/* The two rates that bound pcb_decode_batch with double host input on a float decoder: the pinned H2D rate of
+ * this GPU and the double->float narrowing rate of the handle's host thread pool (y_host: `frames` frames of
+ * pinned doubles, read only), and the frames/s they allow when combined as the pipeline combines them.
+ * Call after a pcb_decode_batch; ranks that share a host call it together. */
+int pcb_host_probe(pcb_handle* h, const double* y_host, int frames, double* h2d_GBps, double* narrow_Gvalues_per_s,
+                   double* bound_frames_per_s);
+
 /* introspection for bench / roofline accounting */
 int pcb_info(pcb_handle* h, int* sm_count, int* warps_per_block, int* blocks, int* smem_per_block,
              int* first_smem_layer, uint64_t* kernel_launches);

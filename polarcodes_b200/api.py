@@ -55,6 +55,7 @@ SIGNATURES = {
     "pcb_comm_unique_id": (C.c_int, [C.c_void_p]),
     "pcb_comm_init": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int]),
     "pcb_comm_allreduce": (C.c_int, [C.c_void_p, _u64p, C.c_int]),
+    "pcb_host_probe": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int] + [C.POINTER(C.c_double)] * 3),
     "pcb_info": (C.c_int, [C.c_void_p] + [C.POINTER(C.c_int)] * 5 + [_u64p]),
 }
 
@@ -231,6 +232,12 @@ class Decoder:
         c = (C.c_uint64 * len(counters))(*[int(v) for v in counters])
         _check(lib().pcb_comm_allreduce(self._h, c, len(counters)))
         return [int(v) for v in c]
+
+    def host_probe(self, y_host_ptr, frames):
+        """Pinned H2D rate, host narrowing rate and the frames/s bound they give pcb_decode_batch."""
+        a, b, c = C.c_double(0), C.c_double(0), C.c_double(0)
+        _check(lib().pcb_host_probe(self._h, y_host_ptr, frames, C.byref(a), C.byref(b), C.byref(c)))
+        return {"h2d_GBps": a.value, "narrow_Gvalues_per_s": b.value, "bound_frames_per_s": c.value}
 
     def alu_peak(self):
         v = C.c_double(0)

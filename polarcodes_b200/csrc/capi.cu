@@ -5,6 +5,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <algorithm>
 #include <chrono>
 #include <condition_variable>
 #include <mutex>
@@ -934,6 +935,43 @@ int pcb_comm_allreduce(pcb_handle* h, uint64_t* counters, int count) {
     h->collectives++;
     CK(cudaMemcpyAsync(counters, h->d_red, count * sizeof(uint64_t), cudaMemcpyDeviceToHost, h->sc));
     CK(cudaStreamSynchronize(h->sc));
+    return PCB_OK;
+}
+
+
+// What bounds pcb_decode_batch (host doubles in): the pinned H2D rate W of this GPU's link and the rate R at
+// which this handle's thread pool narrows doubles to floats, measured on the caller's own buffer with the chunk
+// size and staging buffers of the pipeline (call it after a pcb_decode_batch; ranks that share a host call it
+// together to see the contended figures).  A chunk whose head share x is narrowed on the host costs
+// max(x / R, (4x + 8(1 - x)) / W) seconds per value; the bound is that at the best x.
+int pcb_host_probe(pcb_handle* h, const double* y_host, int frames, double* h2d_GBps, double* narrow_Gvalues_per_s,
+                   double* bound_frames_per_s) {
+    if (!h || !y_host || frames < 1) return fail(PCB_EINVAL, "pcb_host_probe: bad argument");
+    if (int r = ensure_device(h)) return r;
+    if (!h->slot_frames || !h->stage_frames || !h->narrow) return fail(PCB_ESTATE, "pcb_host_probe: run pcb_decode_batch (double input, float decoder) first");
+    const size_t chunk = std::min<size_t>({h->slot_frames, h->stage_frames, (size_t)frames});
+    const size_t vals = chunk * (size_t)h->n;
+    const int reps = (int)std::max<size_t>(1, std::min<size_t>(32, (size_t)frames / chunk));
+    h->narrow->start();
+    // link: back-to-back copies of distinct chunks, CUDA events around all of them
+    CK(cudaEventRecord(h->ev_c0[0], h->sin));
+    for (int i = 0; i < reps; i++)
+        CK(cudaMemcpyAsync(h->d_y[i & 1], y_host + (size_t)i * vals, vals * 8, cudaMemcpyHostToDevice, h->sin));
+    CK(cudaEventRecord(h->ev_c1[0], h->sin));
+    // cores: at the same time, as in the pipeline
+    const auto t0 = std::chrono::steady_clock::now();
+    for (int i = 0; i < reps; i++) h->narrow->run(y_host + (size_t)i * vals, h->h_stage[i & 1], vals);
+    const double dt = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+    CK(cudaStreamSynchronize(h->sin));
+    float ms = 0.f;
+    CK(cudaEventElapsedTime(&ms, h->ev_c0[0], h->ev_c1[0]));
+    const double W = (double)reps * vals * 8 / (ms * 1e-3), R = (double)reps * vals / dt;
+    double x = 8.0 * R / (W + 4.0 * R);
+    x = x > 1.0 ? 1.0 : x;
+    const double per_value = std::max(x / R, (4.0 * x + 8.0 * (1.0 - x)) / W);
+    if (h2d_GBps) *h2d_GBps = W / 1e9;
+    if (narrow_Gvalues_per_s) *narrow_Gvalues_per_s = R / 1e9;
+    if (bound_frames_per_s) *bound_frames_per_s = 1.0 / (per_value * h->n);
     return PCB_OK;
 }
 
