@@ -286,6 +286,7 @@ def main():
     ap.add_argument("--e2e-frames", type=int, default=1 << 20)
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-extras", action="store_true", help="skip the configs sweep and the Monte-Carlo leg")
+    ap.add_argument("--kernel-only", action="store_true", help="A/B of kernel variants: the device-resident leg only, short JSON")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -359,6 +360,15 @@ def main():
         dist.all_reduce(el, op=dist.ReduceOp.MAX)
     elapsed, kms = float(el[0]), float(el[1])
 
+    if args.kernel_only:
+        if rank == 0:
+            ops = lane_ops_per_frame(code.mask, LIST)
+            info = dec.info()
+            peak_lane = info["sm_count"] * 128 * (clocks.get("sm_max_mhz") or 1965.0) * 1e6 / 1e12
+            ach = (B / (kms * 1e-3)) * ops["lane_ops"] / 1e12
+            print(json.dumps({"frames_per_s": world * B * args.steps / elapsed, "kernel_ms": kms, "roofline": {"frac": ach / peak_lane, "kernel_ms": kms},
+                              "clocks": clocks}), flush=True)
+        return
     # ---- end to end through the reference-facing call with pinned HOST double buffers -------------------
     Be = min(args.e2e_frames, B)
     hy = torch.empty((Be, N), dtype=torch.float64, pin_memory=True)

@@ -88,15 +88,17 @@ struct Philox {
     }
 };
 
+// Box-Muller on the SFU: lg2 / sqrt / sin / cos approximations (relative error ~1e-6, far below the
+// 24-bit grid of u2).  The channel of the Monte-Carlo mode is statistical by construction (the reference
+// draws from mt19937 + std::normal_distribution); its moments and tails are tested on the GPU.
 __device__ __forceinline__ void box_muller(uint32_t a, uint32_t b, float& z0, float& z1) {
     // u1 in (0, 1] on the full 32-bit grid near zero ((float)a is exact for a < 2^24, which is where the
     // tail of the normal lives): the smallest value 2^-33 gives |z| up to 6.76; u2 on a 24-bit grid
     const float u1 = a ? __uint2float_rn(a) * (1.0f / 4294967296.0f) : (0.5f / 4294967296.0f);
-    const float u2 = ((float)(b >> 8) + 0.5f) * (1.0f / 16777216.0f);
-    const float r = sqrtf(-2.0f * logf(u1));
-    float sn, cs;
-    sincospif(2.0f * u2, &sn, &cs);
-    z0 = r * cs; z1 = r * sn;
+    const float ang = ((float)(b >> 8) + 0.5f) * (6.283185307179586f / 16777216.0f);   // in (0, 2 pi)
+    float r;
+    asm("sqrt.approx.f32 %0, %1;" : "=f"(r) : "f"(-1.3862943611198906f * __log2f(u1)));   // sqrt(-2 ln u1)
+    z0 = r * __cosf(ang); z1 = r * __sinf(ang);
 }
 
 // One warp generates one frame: random info bits -> CRC -> scatter by the info positions ->
@@ -190,22 +192,46 @@ __global__ void __launch_bounds__(128) generate_kernel(GenArgs G) {
         }
         __syncwarp();
         warp_transform(W, n, lane);
-        // Transform (Encoder.cpp:35-41)
+        // Transform (Encoder.cpp:35-41); the range check of the tuned list kernel rides along (redo list):
+        // |y| must be 0 or within [2^-40, 2^100], see scl8_prepass_kernel
         float* y = G.y + (size_t)f * n;
-        for (int q = lane; q < (n + 3) / 4; q += 32) {
-            const uint4 r = ph(f_lo, f_hi, (uint32_t)q, 0x6E6F6973u);
-            float z[4];
-            box_muller(r.x, r.y, z[0], z[1]);
-            box_muller(r.z, r.w, z[2], z[3]);
+        bool ok = true;
+        if ((n & 3) == 0) {
+            for (int q = lane; q < n / 4; q += 32) {
+                const uint4 r = ph(f_lo, f_hi, (uint32_t)q, 0x6E6F6973u);
+                float z[4];
+                box_muller(r.x, r.y, z[0], z[1]);
+                box_muller(r.z, r.w, z[2], z[3]);
+                const uint32_t bits = W[q >> 3] >> (4 * (q & 7));
+                float4 v;
+                v.x = ((bits & 1u) ? -1.f : 1.f) + G.sigma * z[0];
+                v.y = ((bits & 2u) ? -1.f : 1.f) + G.sigma * z[1];
+                v.z = ((bits & 4u) ? -1.f : 1.f) + G.sigma * z[2];
+                v.w = ((bits & 8u) ? -1.f : 1.f) + G.sigma * z[3];
+                reinterpret_cast<float4*>(y)[q] = v;
+                if (G.redo_count) {
+                    const float e[4] = {v.x, v.y, v.z, v.w};
 #pragma unroll
-            for (int t = 0; t < 4; t++) {
-                const int i = q * 4 + t;
-                if (i < n) {
-                    const float s = ((W[i >> 5] >> (i & 31)) & 1u) ? -1.f : 1.f;
-                    y[i] = s + G.sigma * z[t];
+                    for (int i = 0; i < 4; i++) {
+                        const uint32_t a = __float_as_uint(e[i]) & 0x7fffffffu;
+                        ok = ok && (a == 0u || (a - 0x2B800000u) <= (0x71800000u - 0x2B800000u));
+                    }
+                }
+            }
+        } else {                                            // n = 2
+            for (int q = lane; q < (n + 3) / 4; q += 32) {
+                const uint4 r = ph(f_lo, f_hi, (uint32_t)q, 0x6E6F6973u);
+                float z[4];
+                box_muller(r.x, r.y, z[0], z[1]);
+                box_muller(r.z, r.w, z[2], z[3]);
+#pragma unroll
+                for (int t = 0; t < 4; t++) {
+                    const int i = q * 4 + t;
+                    if (i < n) y[i] = (((W[i >> 5] >> (i & 31)) & 1u) ? -1.f : 1.f) + G.sigma * z[t];
                 }
             }
         }
+        if (G.redo_count && !__all_sync(0xffffffffu, ok) && lane == 0) G.redo_list[atomicAdd(G.redo_count, 1)] = f;
         __syncwarp();
     }
 }

@@ -17,6 +17,8 @@ struct GenArgs {
     const uint16_t* info_pos;
     float* y;                    // [B][n]
     uint32_t* tx_bits;           // [B][tx_words]
+    int* redo_count;             // not null: range check for the tuned list kernel (what scl8_prepass_kernel does), frames
+    int* redo_list;              // outside the safe input range are appended here
 };
 
 cudaError_t launch_encode(const int* d_u, int* d_x, int n, int m, int with_shuffle, int B, int sm_count,

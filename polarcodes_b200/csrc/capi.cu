@@ -44,7 +44,7 @@ bool scl8q_supported(int m, int L);
 int scl8q_frames_per_warp(int L);
 int scl8q_warps_per_block(int m, int L);
 cudaError_t launch_decode_scl8q(const DecodeArgs& a, int L, const uint32_t* info_w, const uint32_t* synd, uint32_t synd_c0, void* l3_scratch, int* next_quad,
-                                int blocks, cudaStream_t st);
+                                const double* y64, int nf, float* yscr, int check_range, int blocks, cudaStream_t st);
 size_t scl8q_scratch_per_block(int m, int L);
 cudaError_t scl8q_occupancy(int m, int L, int* bps, int* warp_bytes);
 }  // namespace pcb
@@ -164,7 +164,8 @@ struct pcb_handle {
     void* d_qscratch = nullptr;     // quad kernel: layer-3 arrays of every resident block (stays in L2)
     uint32_t* d_synd = nullptr;     // quad kernel: rows of the CRC syndrome matrix (16 x n/32 words), see pcb_set_code
     uint32_t synd_c0 = 0;
-    float* d_y32 = nullptr;         // quad kernel: double channel values converted once per batch
+    float* d_y32 = nullptr;         // PCB_SEPARATE_PREPASS only: double channel values converted once per batch
+    float* d_yscr = nullptr;        // quad kernel: the float rows of every resident warp's frames (narrowed by the warp itself)
     size_t y32_cap = 0;
     int* d_redo = nullptr;          // [0] = count, [1] = work counter of the quad kernel, [2..] = frame list
     size_t redo_cap = 0;
@@ -363,7 +364,7 @@ void pcb_destroy(pcb_handle* h) {
         if (h->ev_out[s]) cudaEventDestroy(h->ev_out[s]);
     }
     cudaFree(h->d_ymc); cudaFree(h->d_tx); cudaFree(h->d_dec); cudaFree(h->d_counters);
-    cudaFree(h->d_eu); cudaFree(h->d_ex); cudaFree(h->d_redo); cudaFree(h->d_qscratch); cudaFree(h->d_synd); cudaFree(h->d_y32); cudaFree(h->d_yt); cudaFree(h->d_sc32_scratch); cudaFree(h->d_sc32_bits);
+    cudaFree(h->d_eu); cudaFree(h->d_ex); cudaFree(h->d_redo); cudaFree(h->d_qscratch); cudaFree(h->d_synd); cudaFree(h->d_y32); cudaFree(h->d_yscr); cudaFree(h->d_yt); cudaFree(h->d_sc32_scratch); cudaFree(h->d_sc32_bits);
     if (h->comm) nccl_api().CommDestroy(h->comm);
     cudaFree(h->d_red);
     cudaFreeHost(h->h_stage[0]); cudaFreeHost(h->h_stage[1]); delete h->narrow;
@@ -463,7 +464,7 @@ static DecodeArgs make_args(pcb_handle* h, const void* d_y, int y_f32, int* d_so
     DecodeArgs a;
     a.n = h->n; a.m = h->m; a.k = h->k; a.crc = h->decoder == 3 ? h->crc : 0; a.B = B;   // the SC decoders never look at the CRC
     a.first_smem_layer = h->ls; a.warp_smem_bytes = h->warp_smem; a.stride = h->stride;
-    a.y = d_y; a.y_f32 = y_f32;
+    a.y = d_y; a.y_f32 = y_f32; a.y64_tail = nullptr; a.y64_first = 0;
     a.info_mask = h->d_info_mask; a.frozen_val = h->d_frozen_val; a.info_pos = h->d_info_pos;
     a.sol = d_sol; a.sol_bits = d_solb;
     a.scratch = h->d_scratch; a.scratch_per_warp = h->scratch_per_warp;
@@ -472,54 +473,75 @@ static DecodeArgs make_args(pcb_handle* h, const void* d_y, int y_f32, int* d_so
     return a;
 }
 
-static cudaError_t launch(pcb_handle* h, const DecodeArgs& a, cudaStream_t st) {
+static cudaError_t ensure_redo(pcb_handle* h, size_t B) {
+    if (h->redo_cap >= B + 2) return cudaSuccess;
+    cudaFree(h->d_redo); h->d_redo = nullptr; h->redo_cap = 0;     // (re)allocation synchronises the device: safe, and rare
+    cudaError_t e0 = cudaMalloc(&h->d_redo, (B + 2) * sizeof(int));
+    if (e0 != cudaSuccess) return e0;
+    h->redo_cap = B + 2;
+    return cudaSuccess;
+}
+
+// prechecked: the producer of the (float) batch has already zeroed the redo header and listed the frames
+// outside the tuned list kernel's safe input range (the on-device generator does): no pre-pass
+static cudaError_t launch(pcb_handle* h, const DecodeArgs& a, cudaStream_t st, bool prechecked = false) {
     h->launches++;
     if (h->fast8) {
-        if (h->redo_cap < (size_t)a.B + 2) {   // (re)allocation synchronises the device: safe, and rare
-            cudaFree(h->d_redo); h->d_redo = nullptr; h->redo_cap = 0;
-            cudaError_t e0 = cudaMalloc(&h->d_redo, ((size_t)a.B + 2) * sizeof(int));
-            if (e0 != cudaSuccess) return e0;
-            h->redo_cap = (size_t)a.B + 2;
-        }
+        cudaError_t e = ensure_redo(h, (size_t)a.B);
+        if (e != cudaSuccess) return e;
         // tuned kernel first; frames outside its safe input range come back in the redo list and
         // are decoded by the generic kernel right behind it (normally an empty launch)
         DecodeArgs f = a;
         f.redo_count = h->d_redo; f.redo_list = h->d_redo + 2; f.use_redo_list = 0;
-        cudaError_t e = cudaMemsetAsync(h->d_redo, 0, 2 * sizeof(int), st);
-        if (e != cudaSuccess) return e;
+        if (!prechecked) {
+            e = cudaMemsetAsync(h->d_redo, 0, 2 * sizeof(int), st);
+            if (e != cudaSuccess) return e;
+        }
         if (h->quad) {
-            // Pre-pass (HBM-bound): the decoder works in float (SCLDecoderMinsum.cpp:406-408), so a
-            // double batch is converted once instead of at each top-stage event of every frame, and
-            // frames outside the tuned kernel's safe input range are put on the redo list.
-            float* y32 = const_cast<float*>(reinterpret_cast<const float*>(a.y));
+            // The decoder works in float (SCLDecoderMinsum.cpp:406-408 narrows every value first).  The warp that
+            // decodes a quad narrows its doubles itself (into the block's rows of d_yscr, which stay in L2) and
+            // range-checks its frames for the redo list: no pre-pass over the batch, no float copy in HBM.
+            // PCB_SEPARATE_PREPASS=1 keeps the old HBM-bound pre-pass kernel (A/B).
+            const float* y32 = reinterpret_cast<const float*>(a.y);
             const double* y64 = nullptr;
             int nf = 0;                      // frames below nf are float already
-            if (!f.y_f32) {
-                const size_t cnt = (size_t)a.B * h->n;
-                if (h->y32_cap < cnt) {
-                    cudaFree(h->d_y32); h->d_y32 = nullptr; h->y32_cap = 0;
-                    cudaError_t e1 = cudaMalloc(&h->d_y32, cnt * sizeof(float));
-                    if (e1 != cudaSuccess) return e1;
-                    h->y32_cap = cnt;
-                }
-                y64 = reinterpret_cast<const double*>(a.y);
-                y32 = h->d_y32;
-            } else if (h->mix_tail) {        // host pipeline: the tail of the chunk came over as doubles
-                y64 = h->mix_tail; nf = h->mix_nf;
-            }
+            if (!f.y_f32) { y64 = reinterpret_cast<const double*>(a.y); y32 = nullptr; }
+            else if (h->mix_tail) { y64 = h->mix_tail; nf = h->mix_nf; }   // host pipeline: the tail of the chunk came over as doubles
             h->mix_tail = nullptr;
-            e = launch_scl8_prepass(y64, y32, h->n, a.B, nf, f.redo_count, f.redo_list, h->sm_count, st);
-            if (e != cudaSuccess) return e;
-            h->launches++;
-            f.y = y32; f.y_f32 = 1;
             const int fpw = scl8q_frames_per_warp(h->L);
+            int check = prechecked ? 0 : 1;
+            static const bool separate = getenv("PCB_SEPARATE_PREPASS") != nullptr;
+            if (separate && !prechecked) {
+                float* dst = const_cast<float*>(y32);
+                if (!f.y_f32) {
+                    const size_t cnt = (size_t)a.B * h->n;
+                    if (h->y32_cap < cnt) {
+                        cudaFree(h->d_y32); h->d_y32 = nullptr; h->y32_cap = 0;
+                        cudaError_t e1 = cudaMalloc(&h->d_y32, cnt * sizeof(float));
+                        if (e1 != cudaSuccess) return e1;
+                        h->y32_cap = cnt;
+                    }
+                    dst = h->d_y32;
+                }
+                e = launch_scl8_prepass(y64, dst, h->n, a.B, nf, f.redo_count, f.redo_list, h->sm_count, st);
+                if (e != cudaSuccess) return e;
+                h->launches++;
+                y32 = dst; y64 = nullptr; check = 0;
+            }
+            if (y64 && !h->d_yscr) {
+                cudaError_t e1 = cudaMalloc(&h->d_yscr, (size_t)fast_blocks(h) * fpw * h->n * sizeof(float));
+                if (e1 != cudaSuccess) return e1;
+            }
+            f.y = y32; f.y_f32 = 1;
+            f.y64_tail = y64; f.y64_first = nf;      // the generic kernel finds the redo frames where the list kernel found them
             const int nq = (a.B + fpw - 1) / fpw;
             const size_t spb = scl8q_scratch_per_block(h->m, h->L);
             if (spb && !h->d_qscratch) {
                 cudaError_t e1 = cudaMalloc(&h->d_qscratch, spb * (size_t)fast_blocks(h));
                 if (e1 != cudaSuccess) return e1;
             }
-            e = launch_decode_scl8q(f, h->L, h->h_info_w.data(), h->d_synd, h->synd_c0, h->d_qscratch, h->d_redo + 1, nq < fast_blocks(h) ? nq : fast_blocks(h), st);
+            e = launch_decode_scl8q(f, h->L, h->h_info_w.data(), h->d_synd, h->synd_c0, h->d_qscratch, h->d_redo + 1, y64, nf, h->d_yscr, check,
+                                    nq < fast_blocks(h) ? nq : fast_blocks(h), st);
         } else {
             return cudaErrorInvalidValue;
         }
@@ -775,11 +797,12 @@ static GenArgs gen_args(pcb_handle* h, double snr_db, uint64_t seed, uint64_t fi
     g.seed = seed; g.first_frame = first;
     g.info_mask = h->d_info_mask; g.frozen_val = h->d_frozen_val; g.info_pos = h->d_info_pos;
     g.y = h->d_ymc; g.tx_bits = h->d_tx;
+    g.redo_count = nullptr; g.redo_list = nullptr;
     return g;
 }
 
 static size_t mc_batch(pcb_handle* h) {
-    size_t b = ((size_t)256 << 20) / ((size_t)h->n * 4);
+    size_t b = ((size_t)1 << 30) / ((size_t)h->n * 4);     // 1 GiB of channel values: many waves of the resident grid per launch
     const char* env = getenv("PCB_MC_BATCH");
     if (env) b = (size_t)atol(env);
     const size_t minb = h->fast8 ? (size_t)fast_blocks(h) * (h->quad ? scl8q_frames_per_warp(h->L) : 1) : (size_t)max_blocks(h) * h->wpb;
@@ -807,22 +830,40 @@ int pcb_montecarlo(pcb_handle* h, double snr_db, uint64_t frames, uint64_t seed,
     double secs = 0;
     const int nbits = h->decoder == 3 ? h->k : h->n;
     const double mc_sigma = pcb_sigma(h->n, h->k, snr_db);   // exact SC scales by 2/sigma^2 (SCDecoder.cpp:15-17); the handle's sigma stays the caller's
+    // the tuned list kernel wants its input range-checked: the generator does that on the way (no pre-pass)
+    const bool precheck = h->fast8 && h->quad;
+    if (precheck) CK(ensure_redo(h, batch));
+    // everything of a batch is enqueued on one stream and nothing waits for the host between batches; the
+    // decode-kernel time comes from one pair of events per batch, read at the end
+    std::vector<cudaEvent_t> ev;
+    auto cleanup = [&]() { for (auto e : ev) cudaEventDestroy(e); };
     for (uint64_t f0 = 0; f0 < frames; f0 += batch) {
         const int nb = (int)(frames - f0 < batch ? frames - f0 : batch);
         GenArgs g = gen_args(h, snr_db, seed, first_frame_id + f0, nb);
+        if (precheck) {
+            CK(cudaMemsetAsync(h->d_redo, 0, 2 * sizeof(int), h->sc));
+            g.redo_count = h->d_redo; g.redo_list = h->d_redo + 2;
+        }
         CK(launch_generate(g, h->sm_count, h->sc));
         DecodeArgs a = make_args(h, h->d_ymc, 1, nullptr, h->d_dec, nb);
         a.sigma = mc_sigma;
-        CK(cudaEventRecord(h->t0, h->sc));
-        CK(launch(h, a, h->sc));
-        CK(cudaEventRecord(h->t1, h->sc));
+        cudaEvent_t e0, e1;
+        if (cudaEventCreate(&e0) != cudaSuccess || cudaEventCreate(&e1) != cudaSuccess) { cleanup(); return fail(PCB_ECUDA, "cudaEventCreate failed"); }
+        ev.push_back(e0); ev.push_back(e1);
+        CK(cudaEventRecord(e0, h->sc));
+        CK(launch(h, a, h->sc, precheck));
+        CK(cudaEventRecord(e1, h->sc));
         CK(launch_count(h->d_dec, h->d_tx, h->EW, nbits, nb, h->d_counters, h->sc));
         h->launches += 2;
-        CK(cudaStreamSynchronize(h->sc));
-        float ms = 0;
-        CK(cudaEventElapsedTime(&ms, h->t0, h->t1));
-        secs += ms * 1e-3;
+        if (ev.size() >= 512) {                              // bounded number of live events on very long runs
+            CK(cudaStreamSynchronize(h->sc));
+            for (size_t i = 0; i < ev.size(); i += 2) { float ms = 0; CK(cudaEventElapsedTime(&ms, ev[i], ev[i + 1])); secs += ms * 1e-3; }
+            cleanup(); ev.clear();
+        }
     }
+    CK(cudaStreamSynchronize(h->sc));
+    for (size_t i = 0; i < ev.size(); i += 2) { float ms = 0; CK(cudaEventElapsedTime(&ms, ev[i], ev[i + 1])); secs += ms * 1e-3; }
+    cleanup();
     unsigned long long cnt[2];
     CK(cudaMemcpy(cnt, h->d_counters, 16, cudaMemcpyDeviceToHost));
     if (frames_done) *frames_done += frames;

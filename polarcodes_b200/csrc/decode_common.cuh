@@ -22,6 +22,8 @@ struct DecodeArgs {
     int stride;                 // solution bits per frame: n (SC) or k+crc (SCL)
     const void* y;              // [B][n] channel values
     int y_f32;                  // 1: float, 0: double
+    const double* y64_tail;     // not null (with y_f32 = 1): frame f >= y64_first is doubles at y64_tail + (f - y64_first) * n
+    int y64_first;
     const uint32_t* info_mask;  // ceil(n/32) words, bit i set = information position
     const uint32_t* frozen_val; // ceil(n/32) words, frozen value at frozen positions
     const uint16_t* info_pos;   // [k+crc] ascending information positions (SCL)

@@ -88,11 +88,14 @@ __global__ void __launch_bounds__(256) decode_generic_kernel(const DecodeArgs A)
     const int nframes = A.use_redo_list ? *A.redo_count : A.B;
     for (int fidx = gwarp; fidx < nframes; fidx += total_warps) {
         const int frame = A.use_redo_list ? A.redo_list[fidx] : fidx;
+        // a batch may be floats for the frames below y64_first and doubles behind (host pipeline of the list decoder)
+        const bool is_f32 = A.y_f32 && !(A.y64_tail && frame >= A.y64_first);
         const float* yf = reinterpret_cast<const float*>(A.y) + (size_t)frame * n;
-        const double* yd = reinterpret_cast<const double*>(A.y) + (size_t)frame * n;
+        const double* yd = A.y64_tail ? A.y64_tail + (size_t)(frame - A.y64_first) * n
+                                      : reinterpret_cast<const double*>(A.y) + (size_t)frame * n;
         auto ch = [&](int j) -> T {
             const int idx = (MODE == MODE_SCL) ? j : (int)(__brev((unsigned)j) >> (32 - m));
-            T v = A.y_f32 ? (T)yf[idx] : (T)yd[idx];
+            T v = is_f32 ? (T)yf[idx] : (T)yd[idx];
             if (MODE == MODE_SC_EXACT) {  // SCDecoder.cpp:15-17, :77-79
                 v = (T)((double)v * 2. / inv_s2);
                 if (isinf((double)v)) v = (T)DBL_MAX;

@@ -93,6 +93,9 @@
 #ifndef PCB_Q_CPA
 #define PCB_Q_CPA 1
 #endif
+#ifndef PCB_Q_PF64
+#define PCB_Q_PF64 0   // L2 prefetch of the next quad's double rows, late in the current quad: 33.5 vs 35.7 M frames/s, off
+#endif
 #ifndef PCB_Q_CPU
 #define PCB_Q_CPU 4    // unroll factor of the cp.async issue loop
 #endif
@@ -107,9 +110,9 @@ constexpr unsigned FULL = 0xffffffffu;
 
 template <int M, int LL>
 struct Geo {
-    static_assert(LL == 4 || LL == 8 || LL == 16 || LL == 32, "list size");
+    static_assert(LL == 2 || LL == 4 || LL == 8 || LL == 16 || LL == 32, "list size");
     static constexpr int FPW = 32 / LL;     // frames per warp: lane = frame * LL + path slot
-    static constexpr int LB = LL == 4 ? 2 : LL == 8 ? 3 : LL == 16 ? 4 : 5;   // bits of a slot number
+    static constexpr int LB = LL == 2 ? 1 : LL == 4 ? 2 : LL == 8 ? 3 : LL == 16 ? 4 : 5;   // bits of a slot number
     static constexpr unsigned GM = LL == 32 ? 0xffffffffu : (1u << LL) - 1;   // lane mask of one frame (shifted down)
     static constexpr int N = 1 << M;
     static constexpr int LTOP = 3;          // first stored LLR layer (size N/8)
@@ -140,17 +143,28 @@ struct Geo {
         for (int l = LS; l < lam; ++l) o += LL * stride(l);
         return o;
     }
-    static constexpr int PFLOATS = off(LBOT + 1);
-    // staging area = the layers below the one the top stage writes (dead at those phases)
+    static constexpr int LFLOATS = off(LBOT + 1);             // the shared-memory LLR layers
+    // staging area of the top stage = the layers below the one it writes (dead at those phases): one frame's
+    // layer 1 (N/2 floats) or, for N < 1024, its channel values.  With 2 or 4 paths per frame the layers are
+    // smaller than that and the region is extended (a frame then costs about what it costs with 8 paths).
     static constexpr int STAGE_OFF = GL4 ? 0 : off(LS + 1);
-    static_assert(PFLOATS - STAGE_OFF >= (GL3 ? N / 2 : N), "staging area too small");
+    // CHUNKF (2 or 4 paths, N >= 1024): layer 1 is never staged whole; the channel values go through the
+    // chunked cp.async staging at every top-stage event (512 floats per frame) and an f-layer 1 is
+    // computed from them per path.  That costs some redundant f's and saves the shared memory that
+    // decides how many warps are resident.
+    // Only where it buys resident warps: N = 2048 (8 instead of 5 per SM at L = 4: 17.5 vs 14.8 M frames/s); at
+    // N = 1024 the frame needs 512 floats either way and the redundant f's cost 4 % (L = 4) to 15 % (L = 2).
+    static constexpr bool CHUNKF = GL3 && M >= 11 && LL <= 4 && PCB_Q_CPA;
+    static constexpr int STAGE_NEED = CHUNKF ? 512 : GL3 ? N / 2 : N;
+    static constexpr int PFLOATS = LFLOATS - STAGE_OFF >= STAGE_NEED ? LFLOATS : STAGE_OFF + STAGE_NEED;
+    static_assert(LL <= 4 || PFLOATS == LFLOATS, "staging area too small");
     static constexpr int XW = LL * XHS;                      // final codeword estimates (alias the LLR region)
     static_assert(XW <= PFLOATS, "final codeword estimates do not fit the LLR region");
     // select by merging two sorted lists of L (fork_slow): 4L words of key scratch instead of 2L
     static constexpr bool MERGE = LL >= 16 ? PCB_Q_MERGE : PCB_Q_MERGE_SMALL;
-    static constexpr int FRAME_WORDS = PFLOATS + LL * HS + (MERGE ? 4 : 2) * LL;   // LLRs, heaps, candidate keys
     static constexpr int OFF_H = PFLOATS;
-    static constexpr int OFF_KEYS = PFLOATS + LL * HS;
+    static constexpr int OFF_KEYS = (PFLOATS + LL * HS + 3) & ~3;
+    static constexpr int FRAME_WORDS = (OFF_KEYS + (MERGE ? 4 : 2) * LL + 3) & ~3;   // LLRs, heaps, candidate keys
     static constexpr int TOTAL = FPW * FRAME_WORDS * 4;
     static constexpr int L3_BLOCK_FLOAT4 = GL3 ? FPW * Q3 * LL : 0;   // global scratch per block: [frame][k][slot] float4
     static constexpr int L4_BLOCK_FLOAT4 = GL4 ? FPW * (Q3 / 2) * LL : 0;
@@ -223,6 +237,11 @@ __device__ __forceinline__ float4 gs4(float4 a, float4 b, uint32_t cw, int pos) 
 template <int FPW>
 __device__ __forceinline__ unsigned group_max(unsigned x, int fme) {
     if constexpr (FPW == 1) return __reduce_max_sync(FULL, x);
+    if constexpr (FPW >= 8) {     // 2 or 4 lanes per frame: a shuffle butterfly beats 8 or 16 reductions
+#pragma unroll
+        for (int o = 16 / FPW; o; o >>= 1) x = max(x, __shfl_xor_sync(FULL, x, o));
+        return x;
+    }
     unsigned r = 0;
 #pragma unroll
     for (int g = 0; g < FPW; g++) {
@@ -305,7 +324,7 @@ __device__ __forceinline__ bool single_swap(const PathState& s, float A0, int la
 // frames of the warp at once (every step is confined to the 8-lane group of a frame).
 template <int LL, bool MERGE>
 __device__ __noinline__ PathState fork_slow(PathState s, float A0, int lane, int ninfo, uint32_t* keys) {
-    constexpr int FPW = 32 / LL, LB = LL == 4 ? 2 : LL == 8 ? 3 : LL == 16 ? 4 : 5;
+    constexpr int FPW = 32 / LL, LB = LL == 2 ? 1 : LL == 4 ? 2 : LL == 8 ? 3 : LL == 16 ? 4 : 5;
     constexpr unsigned GM = LL == 32 ? 0xffffffffu : (1u << LL) - 1;
     const int p = lane & (LL - 1), gsh = lane & (32 - LL);
     const float pf0 = s.met + fmaxf(-A0, 0.f);   // pen(llr,0) = |llr| iff llr < 0   (:308-313)
@@ -436,11 +455,18 @@ __device__ __noinline__ PathState fork_slow(PathState s, float A0, int lane, int
     return s;
 }
 
-template <int M, int LL, typename YT>
+template <int M, int LL, typename YT, bool CONV>
 struct Dec {
     using G = Geo<M, LL>;
     static constexpr int FPW = G::FPW, LB = G::LB;
     int lane, p;
+    // channel values of the frames of this quad: CONV: the block's own converted copy (frame f of the quad at
+    // ysrc + f * N, written by the quad prologue), else the batch itself (frame id * N)
+    const YT* ysrc;
+    __device__ __forceinline__ const YT* yrow(int f) const {
+        if constexpr (CONV) return ysrc + f * G::N;
+        else return ysrc + (size_t)min(fbase + f, Bm1) * G::N;
+    }
     int fbase, Bm1;    // first frame of the quad, last frame of the batch (tail quads repeat it)
     float* P;          // this frame's LLR layers
     uint32_t* H;       // this frame's partial-sum heaps
@@ -490,7 +516,7 @@ struct Dec {
         constexpr int N4 = G::N / 4, SU = PCB_Q_STU;
 #pragma unroll 1
         for (int f = 0; f < FPW; f++) {
-            const YT* y = ybase + (size_t)min(fbase + f, Bm1) * G::N;
+            const YT* y = yrow(f);
             float* Rf = W + f * G::FRAME_WORDS + G::STAGE_OFF;
 #pragma unroll SU
             for (int q = lane; q < N4 / 2; q += 32)
@@ -507,7 +533,7 @@ struct Dec {
 #pragma unroll CU
             for (int i = 0; i < 2 * FPW; i++) {    // unit v = i*32 + lane: frame i/2, then t (8), h (2), k4 (4)
                 const int v = i * 32 + lane, w = v & 63, t = w >> 3, h = (w >> 2) & 1, kk = (c & 1) * 4 + (w & 3);
-                const YT* y = ybase + (size_t)min(fbase + (i >> 1), Bm1) * G::N;
+                const YT* y = yrow((i >> 1));
                 const unsigned sa = (unsigned)__cvta_generic_to_shared(W + (i >> 1) * G::FRAME_WORDS + G::STAGE_OFF + ((t * 2 + h) * 8 + kk) * 4);
                 asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(sa), "l"(y + 4 * (t * Q + h * (Q / 2) + (c >> 1) * 8 + kk)) : "memory");
             }
@@ -515,7 +541,7 @@ struct Dec {
         asm volatile("cp.async.commit_group;" ::: "memory");
     }
 
-    __device__ __forceinline__ void top_gl3(int ev, const YT* ybase, const int (&fr)[4]) {
+    __device__ __forceinline__ void top_gl3(int ev, const YT* ybase) {
         constexpr int E = G::N / 8, N4 = G::N / 4, Q = G::Q3, NR = Q / 16, TU = PCB_Q_TOPU;
         [[maybe_unused]] constexpr int SG = PCB_Q_STG;
         const bool g1 = ev & 4, g2 = ev & 2, g3 = ev & 1;
@@ -523,7 +549,8 @@ struct Dec {
         float* dst4 = G::GL4 ? nullptr : arr(4, p);
         float4* dst3 = L3 + p;
         __syncwarp();                            // everyone is done with the previous subtree
-        if (!g1) {
+        const bool chunked = g1 || G::CHUNKF;    // channel values staged chunk by chunk (else: layer 1 = f staged whole)
+        if (!chunked) {
             stage_l1f(ybase);
             __syncwarp();
         }
@@ -531,7 +558,7 @@ struct Dec {
         // g-layer 1: the channel values go straight from L2 to the staging area with cp.async, in
         // chunks of 4 columns x 2 halves x 8 rows per frame (chunk c = columns c*4 .. c*4+3); chunk
         // c+2 is in flight while chunk c is consumed, so the L2 latency hides behind the arithmetic.
-        if (g1) {
+        if (chunked) {
 #pragma unroll 1
             for (int c = 0; c < 2; c++) stage_chunk(ybase, c);
         }
@@ -544,7 +571,7 @@ struct Dec {
 #pragma unroll SG
                 for (int i = 0; i < 4 * FPW; i++) {   // unit u = i*32 + lane: frame i/4, then t (8), h (2), kk (8)
                     const int u = i * 32 + lane, t = (u >> 4) & 7, h = (u >> 3) & 1, kk = u & 7;
-                    const YT* y = ybase + (size_t)min(fbase + (i >> 2), Bm1) * G::N;
+                    const YT* y = yrow((i >> 2));
                     *reinterpret_cast<float4*>(W + (i >> 2) * G::FRAME_WORDS + G::STAGE_OFF + (u & 127) * 4) =
                         load_y4(y, t * Q + h * (Q / 2) + r * 8 + kk);
                 }
@@ -563,7 +590,7 @@ struct Dec {
 #if PCB_Q_CPA
 #pragma unroll 1
             for (int hf = 0; hf < 2; hf++) {
-            if (g1) {
+            if (chunked) {
                 asm volatile("cp.async.wait_group 1;" ::: "memory");
                 __syncwarp();
             }
@@ -578,12 +605,17 @@ struct Dec {
                 for (int h = 0; h < 2; h++) {
                     const int k = h * (Q / 2) + r * 8 + kk;
                     float4 l1[4];
-                    if (g1) {
+                    if (chunked) {
                         float4 yv[8];
 #pragma unroll
                         for (int t = 0; t < 8; t++) yv[t] = *reinterpret_cast<const float4*>(R + ((t * 2 + h) * 8 + kk) * 4);
+                        if (g1) {
 #pragma unroll
-                        for (int t = 0; t < 4; t++) l1[t] = gs4(yv[t], yv[t + 4], c1[t][h], 4 * kk);
+                            for (int t = 0; t < 4; t++) l1[t] = gs4(yv[t], yv[t + 4], c1[t][h], 4 * kk);
+                        } else if constexpr (G::CHUNKF) {
+#pragma unroll
+                            for (int t = 0; t < 4; t++) l1[t] = ff4(yv[t], yv[t + 4]);
+                        }
                     } else {
 #pragma unroll
                         for (int t = 0; t < 4; t++) l1[t] = *reinterpret_cast<const float4*>(R + t * E + 4 * k);
@@ -598,7 +630,7 @@ struct Dec {
                 else *reinterpret_cast<float4*>(dst4 + 4 * (r * 8 + kk)) = ff4(o[0], o[1]);
             }
 #if PCB_Q_CPA
-            if (g1) {
+            if (chunked) {
                 __syncwarp();                    // the chunk is consumed: its slots take chunk c + 2
                 stage_chunk(ybase, 2 * r + hf + 2);
             }
@@ -608,7 +640,7 @@ struct Dec {
         __syncwarp();                            // the staging area is overwritten by layer 5 next
     }
 
-    __device__ __forceinline__ void top3(int ev, const YT* ybase, const int (&fr)[4]) {
+    __device__ __forceinline__ void top3(int ev, const YT* ybase) {
         constexpr int E = G::N / 8, N4 = G::N / 4;
         const bool g1 = ev & 4, g2 = ev & 2, g3 = ev & 1;
         __syncwarp();                            // everyone is done with layers 4.. of the previous subtree
@@ -616,7 +648,7 @@ struct Dec {
             // stage the channel values of the four frames as floats
 #pragma unroll 1
             for (int f = 0; f < FPW; f++) {
-                const YT* y = ybase + (size_t)min(fbase + f, Bm1) * G::N;
+                const YT* y = yrow(f);
                 float* R = W + f * G::FRAME_WORDS + G::STAGE_OFF;
 #pragma unroll 4
                 for (int q = lane; q < N4; q += 32) *reinterpret_cast<float4*>(R + 4 * q) = load_y4(y, q);
@@ -862,13 +894,13 @@ struct Dec {
     }
 
     // LLR work at the first phase i0 = 8*blk of a size-8 subtree, down to layer LBOT
-    __device__ __forceinline__ void upper(int blk, const YT* ybase, const int (&fr)[4]) {
+    __device__ __forceinline__ void upper(int blk, const YT* ybase) {
         static_assert(LR > G::LS, "register chains start below the first shared-memory layer");
         const int z = blk ? (__ffs(blk) - 1) : 31;
         int ll, own;    // layers own.. are recomputed, the f-layers below ll are still to do
         if (z >= M - 6) {                                  // i0 is a multiple of N/8
-            if constexpr (G::GL3) { top_gl3(blk >> (M - 6), ybase, fr); ll = 4; }
-            else { top3(blk >> (M - 6), ybase, fr); ll = 3; }
+            if constexpr (G::GL3) { top_gl3(blk >> (M - 6), ybase); ll = 4; }
+            else { top3(blk >> (M - 6), ybase); ll = 3; }
             own = G::LTOP;
         } else {
             __syncwarp();
@@ -1082,10 +1114,19 @@ struct Scl8qArgs {
     // on the code only (row t as n/32 words at synd[t * n/32 ..)) and c0 the CRC of the zero message.
     const uint32_t* synd;
     uint32_t synd_c0;
+    // Quad prologue (replaces the separate pre-pass): every frame is range-checked by the warp that decodes
+    // it (frames outside the safe input range of the arithmetic go on the redo list of the generic kernel).
+    // CONV kernels also narrow: frames below nf are floats at a.y, frame f >= nf is doubles at
+    // y64 + (f - nf) * n (SCLDecoderMinsum.cpp:406-408 narrows every value first); the float rows of the
+    // quad go to the block's slice of yscr (FPW * n floats, stays in L2) and the decoder reads them there.
+    const double* y64;
+    int nf;
+    float* yscr;
+    int check_range;       // 0: the producer of the batch has already range-checked it (on-device generator)
 };
 
 // One warp per block (blockDim.x == 32); a block decodes quads of frames.
-template <int M, int LL, typename YT>
+template <int M, int LL, typename YT, bool CONV>
 __global__ void __launch_bounds__(q8::Geo<M, LL>::MW ? 32 * q8::Geo<M, LL>::WMAX : 32,
                                   q8::Geo<M, LL>::MW ? 1 : (LL != 8 ? 1 : q8::Geo<M, LL>::GL4 && M == 10 ? 16 : M == 10 ? 10 : 5))
     decode_scl8q_kernel(const __grid_constant__ Scl8qArgs S) {
@@ -1099,7 +1140,7 @@ __global__ void __launch_bounds__(q8::Geo<M, LL>::MW ? 32 * q8::Geo<M, LL>::WMAX
     const int vblock = blockIdx.x * wpb + wib, nvblocks = gridDim.x * wpb;
     unsigned char* const smem_warp = smem_raw + (size_t)wib * G::TOTAL;
     const int fme = lane / LL;
-    q8::Dec<M, LL, YT> D;
+    q8::Dec<M, LL, YT, CONV> D;
     D.lane = lane; D.p = lane & (LL - 1);
     D.W = reinterpret_cast<float*>(smem_warp);
     D.P = D.W + fme * G::FRAME_WORDS;
@@ -1114,16 +1155,15 @@ __global__ void __launch_bounds__(q8::Geo<M, LL>::MW ? 32 * q8::Geo<M, LL>::WMAX
     constexpr int n = G::N;
     const int EW = (A.stride + 31) >> 5;
     const YT* ybase = reinterpret_cast<const YT*>(A.y);
+    float* const yscr = CONV ? S.yscr + (size_t)vblock * (FPW * G::N) : nullptr;
+    D.ysrc = CONV ? yscr : ybase;
     const int nquads = (A.B + FPW - 1) / FPW;
 
     // The first quad of a block is its index, the following ones come from a work counter: decode
     // times differ from quad to quad, and a static stride leaves SMs idle at the end of the batch.
     int quad = vblock;
     while (quad < nquads) {
-        int fr[4];
         D.fbase = FPW * quad; D.Bm1 = A.B - 1;
-#pragma unroll
-        for (int f = 0; f < 4; f++) fr[f] = min(FPW * quad + f, A.B - 1);
         // take the next quad now (an L2 prefetch of its channel values here, or late in the frame,
         // stopped paying once the top stage staged them with cp.async: 34.15 / 33.0 vs 34.23 M)
         int next_quad = 0;
@@ -1135,11 +1175,66 @@ __global__ void __launch_bounds__(q8::Geo<M, LL>::MW ? 32 * q8::Geo<M, LL>::WMAX
 #endif
         D.met = 0.f; D.maxmet = 0; D.pidx = 0; D.cidx = 0; D.w0 = 0; D.ninfo = 0;
         D.r4 = make_float4(0.f, 0.f, 0.f, 0.f); D.r2_0 = D.r2_1 = D.A0 = 0.f;
+        // ---- quad prologue: range check (and narrowing) of the quad's frames --------------------------
+        if (CONV || S.check_range) {
+            if constexpr (CONV) __syncwarp();          // the previous quad is done with the block's rows
+#pragma unroll 1
+            for (int f = 0; f < FPW; f++) {
+                const int frame = min(FPW * quad + f, A.B - 1);
+                bool ok = true;
+                auto chk = [&](float4 v) {
+                    const float e[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+                    for (int i = 0; i < 4; i++) {
+                        const uint32_t a = __float_as_uint(e[i]) & 0x7fffffffu;      // 2^-40 = 0x2B800000, 2^100 = 0x71800000
+                        ok = ok && (a == 0u || (a - 0x2B800000u) <= (0x71800000u - 0x2B800000u));
+                    }
+                };
+                if (CONV && frame >= S.nf) {
+                    const double2* src = reinterpret_cast<const double2*>(S.y64 + (size_t)(frame - S.nf) * n);
+                    float4* dst = reinterpret_cast<float4*>(yscr + f * n);
+#pragma unroll 4
+                    for (int q = lane; q < n / 4; q += 32) {
+                        const double2 a = __ldcs(src + 2 * q), b = __ldcs(src + 2 * q + 1);   // streamed: read once
+                        const float4 v = make_float4((float)a.x, (float)a.y, (float)b.x, (float)b.y);   // :406-408
+                        dst[q] = v;
+                        chk(v);
+                    }
+                } else {
+                    const float4* src = reinterpret_cast<const float4*>(reinterpret_cast<const float*>(A.y) + (size_t)frame * n);
+                    [[maybe_unused]] float4* dst = reinterpret_cast<float4*>(yscr + f * n);
+#pragma unroll 4
+                    for (int q = lane; q < n / 4; q += 32) {
+                        const float4 v = CONV ? __ldcs(src + q) : src[q];
+                        if constexpr (CONV) dst[q] = v;
+                        chk(v);
+                    }
+                }
+                if (S.check_range && !__all_sync(FULL, ok) && lane == 0 && FPW * quad + f < A.B)
+                    A.redo_list[atomicAdd(A.redo_count, 1)] = frame;
+            }
+            if constexpr (CONV) __syncwarp();          // the rows are written before anyone stages them
+        }
 #pragma unroll 1
         for (int blk = 0; blk < n / 8; ++blk) {
+#if PCB_Q_PF64
+            // CONV: the doubles of the next quad are on their way from DRAM to L2 during the last eighth of
+            // this one (its prologue then waits for L2, not for DRAM; earlier they would only crowd L2)
+            if (CONV && blk == n / 8 - n / 64 && next_quad < nquads) {
+#pragma unroll 1
+                for (int f = 0; f < FPW; f++) {
+                    const int frame = min(FPW * next_quad + f, A.B - 1);
+                    if (frame >= S.nf) {
+                        const char* row = reinterpret_cast<const char*>(S.y64 + (size_t)(frame - S.nf) * n);
+#pragma unroll 2
+                        for (int l = lane; l < n / 16; l += 32) asm volatile("prefetch.global.L2 [%0];" ::"l"(row + 128 * l));
+                    }
+                }
+            }
+#endif
             // the 8 information flags of this subtree and, as bit 8, the first one of the next
             const uint32_t ib = __funnelshift_r(S.info_w[blk >> 2], S.info_w[(blk >> 2) + 1], 8 * (blk & 3)) & 0x1FFu;
-            D.upper(blk, ybase, fr);
+            D.upper(blk, ybase);
             D.leaf8(blk, ib);
         }
         __syncwarp();
@@ -1247,14 +1342,18 @@ __global__ void __launch_bounds__(q8::Geo<M, LL>::MW ? 32 * q8::Geo<M, LL>::WMAX
     }
 }
 
-template <int M, int LL, typename YT>
-static cudaError_t launch_m(const Scl8qArgs& a, int blocks, cudaStream_t st) {
+template <int M, int LL, typename YT, bool CONV>
+static cudaError_t launch_mc(const Scl8qArgs& a, int blocks, cudaStream_t st) {
     const int W = q8::Geo<M, LL>::MW ? q8::Geo<M, LL>::WMAX : 1;      // `blocks` counts warps
     const size_t smem = (size_t)q8::Geo<M, LL>::TOTAL * W;
-    cudaError_t e = cudaFuncSetAttribute(decode_scl8q_kernel<M, LL, YT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    cudaError_t e = cudaFuncSetAttribute(decode_scl8q_kernel<M, LL, YT, CONV>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
-    decode_scl8q_kernel<M, LL, YT><<<(blocks + W - 1) / W, 32 * W, smem, st>>>(a);
+    decode_scl8q_kernel<M, LL, YT, CONV><<<(blocks + W - 1) / W, 32 * W, smem, st>>>(a);
     return cudaGetLastError();
+}
+template <int M, int LL, typename YT>
+static cudaError_t launch_m(const Scl8qArgs& a, int blocks, cudaStream_t st) {
+    return a.y64 ? launch_mc<M, LL, YT, true>(a, blocks, st) : launch_mc<M, LL, YT, false>(a, blocks, st);
 }
 
 template <int M, int LL, typename YT>
@@ -1262,32 +1361,42 @@ static cudaError_t occ_m(int* bps, int* warp_bytes) {
     const size_t smem = (size_t)q8::Geo<M, LL>::TOTAL;
     *warp_bytes = q8::Geo<M, LL>::TOTAL;
     const int W = q8::Geo<M, LL>::MW ? q8::Geo<M, LL>::WMAX : 1;
-    cudaError_t e = cudaFuncSetAttribute(decode_scl8q_kernel<M, LL, YT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(smem * W));
+    cudaError_t e = cudaFuncSetAttribute(decode_scl8q_kernel<M, LL, YT, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(smem * W));
     if (e != cudaSuccess) return e;
-    int nb = 0;
-    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, decode_scl8q_kernel<M, LL, YT>, 32 * W, smem * W);
+    int nb = 0, nb2 = 0;
+    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, decode_scl8q_kernel<M, LL, YT, true>, 32 * W, smem * W);
+    if (e != cudaSuccess) return e;
+    e = cudaFuncSetAttribute(decode_scl8q_kernel<M, LL, YT, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(smem * W));
+    if (e != cudaSuccess) return e;
+    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb2, decode_scl8q_kernel<M, LL, YT, false>, 32 * W, smem * W);
+    if (nb2 < nb) nb = nb2;                  // one grid size (and scratch size) for both input paths
     *bps = nb * W;                           // warps per SM
     return e;
 }
 
 // list sizes with a lane-per-path kernel: 32 / L frames per warp
-bool scl8q_supported(int m, int L) { return m >= 8 && m <= 11 && (L == 8 || L == 16 || L == 32); }
+bool scl8q_supported(int m, int L) { return m >= 8 && m <= 11 && (L == 2 || L == 4 || L == 8 || L == 16 || L == 32); }
 int scl8q_frames_per_warp(int L) { return 32 / L; }
 
 #define PCB_FOR_ALL(X) \
-    X(8, 8) X(9, 8) X(10, 8) X(11, 8) X(8, 16) X(9, 16) X(10, 16) X(11, 16) X(8, 32) X(9, 32) X(10, 32) X(11, 32)
+    X(8, 8) X(9, 8) X(10, 8) X(11, 8) X(8, 16) X(9, 16) X(10, 16) X(11, 16) X(8, 32) X(9, 32) X(10, 32) X(11, 32) \
+    X(8, 4) X(9, 4) X(10, 4) X(11, 4) X(8, 2) X(9, 2) X(10, 2) X(11, 2)
 
 // info_w: host copy of the information-mask words (ceil(n/32)), passed as kernel parameters
+// y64 != null: frames >= nf of the batch are doubles at y64 + (frame - nf) * n and yscr holds blocks * (32 / L) * n
+// floats; check_range: fill the redo list (a.redo_count / a.redo_list) with the frames outside the safe input range
 cudaError_t launch_decode_scl8q(const DecodeArgs& a, int L, const uint32_t* info_w, const uint32_t* synd, uint32_t synd_c0, void* l3_scratch, int* next_quad,
-                                int blocks, cudaStream_t st) {
+                                const double* y64, int nf, float* yscr, int check_range, int blocks, cudaStream_t st) {
     Scl8qArgs s;
     s.a = a;
+    s.y64 = y64; s.nf = y64 ? nf : a.B; s.yscr = yscr; s.check_range = check_range;
+    if (y64 && !yscr) return cudaErrorInvalidValue;
     s.next_quad = next_quad;
     s.l3 = reinterpret_cast<float4*>(l3_scratch);
     s.synd = synd; s.synd_c0 = synd_c0;
     if (a.crc && !synd) return cudaErrorInvalidValue;
     for (int i = 0; i < 65; i++) s.info_w[i] = i < a.n / 32 ? info_w[i] : 0;
-    if (!a.y_f32) return cudaErrorInvalidValue;   // the caller converts double batches first (capi.cu)
+    if (!a.y_f32 && !y64) return cudaErrorInvalidValue;   // a.y is float; doubles come in through y64
 #define PCB_CASE(MM, LLL) if (a.m == MM && L == LLL) return launch_m<MM, LLL, float>(s, blocks, st);
     PCB_FOR_ALL(PCB_CASE)
 #undef PCB_CASE

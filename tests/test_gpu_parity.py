@@ -88,6 +88,15 @@ CASES = [  # decoder, n, k, crc, L, snr, frames
     (3, 512, 256, 8, 32, 1.5, 64),
     (3, 256, 128, 0, 32, 1.0, 96),
     (3, 1024, 128, 8, 32, 0.0, 33),
+    # list 4 and 2 on the lane-per-path kernel (8 / 16 frames per warp)
+    (3, 2048, 1024, 16, 4, 2.0, 67),
+    (3, 1024, 512, 8, 4, 1.0, 131),
+    (3, 512, 256, 0, 4, 1.5, 64),
+    (3, 256, 128, 16, 4, 1.0, 250),
+    (3, 1024, 512, 16, 2, 1.5, 97),
+    (3, 2048, 1024, 0, 2, 2.0, 40),
+    (3, 256, 128, 8, 2, 1.0, 129),
+    (3, 512, 64, 8, 2, 0.0, 33),
     # list 16: two frames per warp
     (3, 1024, 512, 16, 16, 1.5, 65),
     (3, 2048, 1024, 0, 16, 2.0, 31),
@@ -119,7 +128,8 @@ def test_quantised_inputs_force_ties(oracle):
     SCLDecoderMinsum.cpp:362-371) and exercise the slot-order discipline."""
     rng = np.random.default_rng(5)
     for n, k, crc, L in ((128, 64, 0, 8), (256, 128, 8, 8), (2048, 1024, 0, 8), (256, 128, 8, 4), (64, 32, 0, 16), (1024, 512, 16, 8), (256, 128, 0, 32),
-                         (2048, 1024, 16, 32), (1024, 512, 0, 32), (512, 256, 0, 16), (1024, 512, 16, 16), (64, 32, 0, 1), (64, 32, 0, 2)):
+                         (2048, 1024, 16, 32), (1024, 512, 0, 32), (512, 256, 0, 16), (1024, 512, 16, 16), (64, 32, 0, 1), (64, 32, 0, 2),
+                         (1024, 512, 0, 4), (2048, 1024, 16, 4), (256, 128, 8, 2), (1024, 512, 16, 2), (512, 256, 0, 4)):
         sigma, inf, mask = oracle.make_code(n, k, crc, 2.0)
         y = rng.integers(-3, 4, (48, n)).astype(np.float64)
         d = _decoder(3, n, k, crc, L, mask, sigma)

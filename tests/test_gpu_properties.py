@@ -18,6 +18,8 @@ FULL = [  # name, n, k, crc, L, decoder, frames
     ("C  SCL-8 1024 crc16", 1024, 512, 16, 8, pb.SCLMINSUM, 1 << 18),
     ("C  SCL-8 1024 crc0", 1024, 512, 0, 8, pb.SCLMINSUM, 1 << 17),
     ("   SCL-16 1024 crc8", 1024, 512, 8, 16, pb.SCLMINSUM, 1 << 15),
+    ("conf.txt SCL-4 2048 crc16", 2048, 1024, 16, 4, pb.SCLMINSUM, 1 << 14),
+    ("   SCL-2 1024 crc8", 1024, 512, 8, 2, pb.SCLMINSUM, (1 << 14) + 7),
     ("D  SCL-32 2048", 2048, 1024, 0, 32, pb.SCLMINSUM, 1 << 13),
     ("D  SCL-32 2048 crc16", 2048, 1024, 16, 32, pb.SCLMINSUM, (1 << 12) + 5),
     ("E  SC min-sum 32768", 32768, 16384, 0, 1, pb.SCMINSUM, 1 << 10),
@@ -64,7 +66,8 @@ def test_tuned_kernel_equals_generic_kernel_at_full_size(name, n, k, crc, L, dec
 
 
 @pytest.mark.parametrize("n,k,crc,L,dec,B", [(1024, 512, 16, 8, pb.SCLMINSUM, 1 << 16), (2048, 1024, 0, 32, pb.SCLMINSUM, 1 << 11),
-                                             (1024, 512, 0, 16, pb.SCLMINSUM, 1 << 13), (1024, 512, 0, 1, pb.SCMINSUM, 1 << 15)])
+                                             (1024, 512, 0, 16, pb.SCLMINSUM, 1 << 13), (1024, 512, 0, 1, pb.SCMINSUM, 1 << 15),
+                                             (2048, 1024, 16, 4, pb.SCLMINSUM, 1 << 12), (1024, 512, 0, 2, pb.SCLMINSUM, 1 << 12)])
 def test_frames_do_not_depend_on_their_position(n, k, crc, L, dec, B):
     d = _handle(n, k, crc, L, dec)
     y, _ = _batch(d, n, B)
