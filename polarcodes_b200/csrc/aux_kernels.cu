@@ -10,6 +10,7 @@
 // Bits are packed 32 per word; butterfly stages with stride < 32 are in-word shifts/XORs,
 // larger strides are word XORs in shared memory.
 #include "aux_kernels.h"
+#include "gen_common.cuh"
 
 namespace pcb {
 
@@ -71,36 +72,6 @@ cudaError_t launch_encode(const int* d_u, int* d_x, int n, int m, int with_shuff
     return cudaGetLastError();
 }
 
-// ---------------------------------------------------------------- Philox4x32-10 ---------
-struct Philox {
-    uint32_t k0, k1;
-    __device__ __forceinline__ uint4 operator()(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3) const {
-        uint32_t a = k0, b = k1;
-#pragma unroll
-        for (int r = 0; r < 10; r++) {
-            const uint32_t hi0 = __umulhi(0xD2511F53u, c0), lo0 = 0xD2511F53u * c0;
-            const uint32_t hi1 = __umulhi(0xCD9E8D57u, c2), lo1 = 0xCD9E8D57u * c2;
-            const uint32_t n0 = hi1 ^ c1 ^ a, n1 = lo1, n2 = hi0 ^ c3 ^ b, n3 = lo0;
-            c0 = n0; c1 = n1; c2 = n2; c3 = n3;
-            a += 0x9E3779B9u; b += 0xBB67AE85u;
-        }
-        return make_uint4(c0, c1, c2, c3);
-    }
-};
-
-// Box-Muller on the SFU: lg2 / sqrt / sin / cos approximations (relative error ~1e-6, far below the
-// 24-bit grid of u2).  The channel of the Monte-Carlo mode is statistical by construction (the reference
-// draws from mt19937 + std::normal_distribution); its moments and tails are tested on the GPU.
-__device__ __forceinline__ void box_muller(uint32_t a, uint32_t b, float& z0, float& z1) {
-    // u1 in (0, 1] on the full 32-bit grid near zero ((float)a is exact for a < 2^24, which is where the
-    // tail of the normal lives): the smallest value 2^-33 gives |z| up to 6.76; u2 on a 24-bit grid
-    const float u1 = a ? __uint2float_rn(a) * (1.0f / 4294967296.0f) : (0.5f / 4294967296.0f);
-    const float ang = ((float)(b >> 8) + 0.5f) * (6.283185307179586f / 16777216.0f);   // in (0, 2 pi)
-    float r;
-    asm("sqrt.approx.f32 %0, %1;" : "=f"(r) : "f"(-1.3862943611198906f * __log2f(u1)));   // sqrt(-2 ln u1)
-    z0 = r * __cosf(ang); z1 = r * __sinf(ang);
-}
-
 // One warp generates one frame: random info bits -> CRC -> scatter by the info positions ->
 // encode -> BPSK + AWGN.  The random stream is a function of (seed, global frame id, index)
 // only, so results do not depend on the batch size or the number of GPUs.
@@ -131,11 +102,7 @@ __global__ void __launch_bounds__(128) generate_kernel(GenArgs G) {
         const uint32_t f_lo = (uint32_t)fid, f_hi = (uint32_t)(fid >> 32);
         // information bits (PolarCodes.cpp:133-135)
         for (int w = lane; w < IW; w += 32) {
-            const uint4 r = ph(f_lo, f_hi, (uint32_t)(w >> 2), 0x696E666Fu);
-            uint32_t v = (w & 3) == 0 ? r.x : (w & 3) == 1 ? r.y : (w & 3) == 2 ? r.z : r.w;
-            const int hi = G.k - w * 32;
-            if (hi < 32) v = hi > 0 ? (v & ((1u << hi) - 1)) : 0u;
-            XI[w] = v;
+            XI[w] = payload_word(ph, f_lo, f_hi, w, G.k);
         }
         for (int w = lane; w < NW; w += 32) W[w] = 0;
         __syncwarp();
@@ -198,16 +165,7 @@ __global__ void __launch_bounds__(128) generate_kernel(GenArgs G) {
         bool ok = true;
         if ((n & 3) == 0) {
             for (int q = lane; q < n / 4; q += 32) {
-                const uint4 r = ph(f_lo, f_hi, (uint32_t)q, 0x6E6F6973u);
-                float z[4];
-                box_muller(r.x, r.y, z[0], z[1]);
-                box_muller(r.z, r.w, z[2], z[3]);
-                const uint32_t bits = W[q >> 3] >> (4 * (q & 7));
-                float4 v;
-                v.x = ((bits & 1u) ? -1.f : 1.f) + G.sigma * z[0];
-                v.y = ((bits & 2u) ? -1.f : 1.f) + G.sigma * z[1];
-                v.z = ((bits & 4u) ? -1.f : 1.f) + G.sigma * z[2];
-                v.w = ((bits & 8u) ? -1.f : 1.f) + G.sigma * z[3];
+                const float4 v = channel4(ph, f_lo, f_hi, q, W[q >> 3] >> (4 * (q & 7)), G.sigma);
                 reinterpret_cast<float4*>(y)[q] = v;
                 if (G.redo_count) {
                     const float e[4] = {v.x, v.y, v.z, v.w};

@@ -43,8 +43,8 @@ cudaError_t launch_decode_sc32(const DecodeArgs& a, const uint32_t* info_w, cons
 bool scl8q_supported(int m, int L);
 int scl8q_frames_per_warp(int L);
 int scl8q_warps_per_block(int m, int L);
-cudaError_t launch_decode_scl8q(const DecodeArgs& a, int L, const uint32_t* info_w, const uint32_t* synd, uint32_t synd_c0, void* l3_scratch, int* next_quad,
-                                const double* y64, int nf, float* yscr, int check_range, int blocks, cudaStream_t st);
+cudaError_t launch_decode_scl8q(const DecodeArgs& a, int L, const uint32_t* info_w, uint32_t* xhat, void* l3_scratch, int* next_quad,
+                                const double* y64, int nf, float* yscr, int check_range, const Scl8qGen* gen, int blocks, cudaStream_t st);
 size_t scl8q_scratch_per_block(int m, int L);
 cudaError_t scl8q_occupancy(int m, int L, int* bps, int* warp_bytes);
 }  // namespace pcb
@@ -164,6 +164,13 @@ struct pcb_handle {
     void* d_qscratch = nullptr;     // quad kernel: layer-3 arrays of every resident block (stays in L2)
     uint32_t* d_synd = nullptr;     // quad kernel: rows of the CRC syndrome matrix (16 x n/32 words), see pcb_set_code
     uint32_t synd_c0 = 0;
+    uint32_t* d_gcrc = nullptr;     // quad kernel, Monte-Carlo mode: payload -> CRC map, [ceil((k+crc)/32)][16] words
+    uint32_t gcrc_c0 = 0;
+    uint32_t* d_xhat = nullptr;     // quad kernel: codeword estimates of every slot of the batch, the input of scl_select_kernel
+    size_t xhat_cap = 0;            // (frames)
+    uint32_t* d_skip = nullptr;     // Monte-Carlo mode: frames the select kernel must not count
+    size_t skip_cap = 0;
+    unsigned long long* d_mc_redo = nullptr;   // [0] count + ids of generated frames outside the tuned kernel's input range
     float* d_y32 = nullptr;         // PCB_SEPARATE_PREPASS only: double channel values converted once per batch
     float* d_yscr = nullptr;        // quad kernel: the float rows of every resident warp's frames (narrowed by the warp itself)
     size_t y32_cap = 0;
@@ -364,7 +371,7 @@ void pcb_destroy(pcb_handle* h) {
         if (h->ev_out[s]) cudaEventDestroy(h->ev_out[s]);
     }
     cudaFree(h->d_ymc); cudaFree(h->d_tx); cudaFree(h->d_dec); cudaFree(h->d_counters);
-    cudaFree(h->d_eu); cudaFree(h->d_ex); cudaFree(h->d_redo); cudaFree(h->d_qscratch); cudaFree(h->d_synd); cudaFree(h->d_y32); cudaFree(h->d_yscr); cudaFree(h->d_yt); cudaFree(h->d_sc32_scratch); cudaFree(h->d_sc32_bits);
+    cudaFree(h->d_eu); cudaFree(h->d_ex); cudaFree(h->d_redo); cudaFree(h->d_qscratch); cudaFree(h->d_synd); cudaFree(h->d_gcrc); cudaFree(h->d_mc_redo); cudaFree(h->d_xhat); cudaFree(h->d_skip); cudaFree(h->d_y32); cudaFree(h->d_yscr); cudaFree(h->d_yt); cudaFree(h->d_sc32_scratch); cudaFree(h->d_sc32_bits);
     if (h->comm) nccl_api().CommDestroy(h->comm);
     cudaFree(h->d_red);
     cudaFreeHost(h->h_stage[0]); cudaFreeHost(h->h_stage[1]); delete h->narrow;
@@ -425,6 +432,24 @@ int pcb_set_code(pcb_handle* h, const int* frozen_mask, double sigma) {
         CK(cudaMemcpyAsync(h->d_synd, S.data(), (size_t)16 * NW * 4, cudaMemcpyHostToDevice, h->sc));
         CK(cudaStreamSynchronize(h->sc));   // S is a local: the copy has landed before it goes away; ordered before any decode on h->sc
         h->synd_c0 = c0;
+        // The generating prologue of the list kernel (Monte-Carlo mode) computes the CRC the loop appends
+        // (PolarCodes.cpp:136-155) the same way: crc(payload) = crc(0) ^ XOR of the columns of the set payload bits.
+        const int IW = (KC + 31) / 32;
+        std::vector<int> msg(K, 0);
+        const unsigned g0 = C == 8 ? pcb_crc8(msg.data(), K) : pcb_crc16(msg.data(), K);
+        std::vector<uint32_t> Gm((size_t)16 * IW, 0);
+        for (int j = 0; j < K; j++) {
+            msg[j] = 1;
+            const unsigned col = (C == 8 ? pcb_crc8(msg.data(), K) : pcb_crc16(msg.data(), K)) ^ g0;
+            msg[j] = 0;
+            for (int t = 0; t < C; t++)
+                if ((col >> t) & 1) Gm[(size_t)(j >> 5) * 16 + t] |= 1u << (j & 31);      // [word][crc bit]: 16 consecutive words per payload word
+        }
+        if (h->d_gcrc) { CK(cudaFree(h->d_gcrc)); h->d_gcrc = nullptr; }
+        CK(cudaMalloc(&h->d_gcrc, Gm.size() * 4));
+        CK(cudaMemcpyAsync(h->d_gcrc, Gm.data(), Gm.size() * 4, cudaMemcpyHostToDevice, h->sc));
+        CK(cudaStreamSynchronize(h->sc));
+        h->gcrc_c0 = g0;
     }
     // the tuned list-8 kernel assumes all-zero frozen values (what the reference uses,
     // PolarCodes.cpp:127); a mask with frozen ones runs on the generic kernel
@@ -480,6 +505,24 @@ static cudaError_t ensure_redo(pcb_handle* h, size_t B) {
     if (e0 != cudaSuccess) return e0;
     h->redo_cap = B + 2;
     return cudaSuccess;
+}
+
+static cudaError_t ensure_xhat(pcb_handle* h, size_t B) {
+    if (h->xhat_cap >= B) return cudaSuccess;
+    cudaFree(h->d_xhat); h->d_xhat = nullptr; h->xhat_cap = 0;
+    cudaError_t e0 = cudaMalloc(&h->d_xhat, B * (size_t)h->L * (h->n / 32) * sizeof(uint32_t));
+    if (e0 != cudaSuccess) return e0;
+    h->xhat_cap = B;
+    return cudaSuccess;
+}
+
+static SelectArgs select_args(pcb_handle* h, const DecodeArgs& a) {
+    SelectArgs s;
+    s.xhat = h->d_xhat; s.B = a.B; s.L = h->L; s.n = h->n; s.k = h->k; s.crc = h->crc; s.stride = h->stride;
+    s.info_mask = h->d_info_mask; s.synd = h->d_synd; s.synd_c0 = h->synd_c0;
+    s.sol = a.sol; s.sol_bits = a.sol_bits;
+    s.count = 0; s.skip = nullptr; s.counters = nullptr; s.seed = 0; s.first_frame = 0;
+    return s;
 }
 
 // prechecked: the producer of the (float) batch has already zeroed the redo header and listed the frames
@@ -540,8 +583,13 @@ static cudaError_t launch(pcb_handle* h, const DecodeArgs& a, cudaStream_t st, b
                 cudaError_t e1 = cudaMalloc(&h->d_qscratch, spb * (size_t)fast_blocks(h));
                 if (e1 != cudaSuccess) return e1;
             }
-            e = launch_decode_scl8q(f, h->L, h->h_info_w.data(), h->d_synd, h->synd_c0, h->d_qscratch, h->d_redo + 1, y64, nf, h->d_yscr, check,
-                                    nq < fast_blocks(h) ? nq : fast_blocks(h), st);
+            e = ensure_xhat(h, (size_t)a.B);
+            if (e != cudaSuccess) return e;
+            e = launch_decode_scl8q(f, h->L, h->h_info_w.data(), h->d_xhat, h->d_qscratch, h->d_redo + 1, y64, nf, h->d_yscr, check,
+                                    nullptr, nq < fast_blocks(h) ? nq : fast_blocks(h), st);
+            if (e != cudaSuccess) return e;
+            e = launch_scl_select(select_args(h, f), h->sm_count, st);     // the generic kernel behind it overrides the redo frames
+            h->launches++;
         } else {
             return cudaErrorInvalidValue;
         }
@@ -823,20 +871,95 @@ int pcb_montecarlo(pcb_handle* h, double snr_db, uint64_t frames, uint64_t seed,
     if (int r = check_gen(h, "pcb_montecarlo")) return r;
     if (int r = ensure_device(h)) return r;
     size_t batch = mc_batch(h);
+    if (h->fast8 && h->quad && getenv("PCB_MC_FUSED") && !getenv("PCB_MC_UNFUSED") && !getenv("PCB_MC_BATCH")) batch = (size_t)1 << 21;   // fused: no channel values in HBM; the launch is the unit (its codeword estimates are L n / 8 bytes per frame)
     if (batch > frames) batch = (size_t)frames;
     if (frames == 0) return PCB_OK;
-    if (int r = ensure_mc(h, batch)) return r;
     CK(cudaMemsetAsync(h->d_counters, 0, 16, h->sc));
     double secs = 0;
     const int nbits = h->decoder == 3 ? h->k : h->n;
     const double mc_sigma = pcb_sigma(h->n, h->k, snr_db);   // exact SC scales by 2/sigma^2 (SCDecoder.cpp:15-17); the handle's sigma stays the caller's
+    // generate_kernel -> decoder -> count_errors_kernel, three launches over a float batch in HBM.  For the list decoder
+    // on the tuned kernel there is also a one-kernel form: the warp that decodes a quad generates its frames into its
+    // rows of d_yscr (they never reach HBM) and scl_select_kernel counts.
+    // Measured (config C, crc 16): the generating prologue costs 13.7 % more instructions (it is rolled and out of line:
+    // every SASS row of the decode kernel competes for the instruction cache) and still drops the instruction-cache hit
+    // rate to 89 %: 25.4 M frames/s against 31.8 M for the three launches.  So the one-kernel path is opt-in (PCB_MC_FUSED=1).
+    const bool unfused = getenv("PCB_MC_FUSED") == nullptr || getenv("PCB_MC_UNFUSED") != nullptr;
+    const bool fused = h->fast8 && h->quad && !unfused;
     // the tuned list kernel wants its input range-checked: the generator does that on the way (no pre-pass)
     const bool precheck = h->fast8 && h->quad;
     if (precheck) CK(ensure_redo(h, batch));
+    const int MC_REDO_CAP = 4096;
+    std::vector<cudaEvent_t> ev;
+    auto cleanup = [&]() { for (auto e : ev) cudaEventDestroy(e); ev.clear(); };
+    auto drain = [&]() -> int {
+        CK(cudaStreamSynchronize(h->sc));
+        for (size_t i = 0; i < ev.size(); i += 2) { float ms = 0; CK(cudaEventElapsedTime(&ms, ev[i], ev[i + 1])); secs += ms * 1e-3; }
+        cleanup();
+        return PCB_OK;
+    };
+    if (fused) {
+        const int fpw = scl8q_frames_per_warp(h->L);
+        if (!h->d_yscr) CK(cudaMalloc(&h->d_yscr, (size_t)fast_blocks(h) * fpw * h->n * sizeof(float)));
+        const size_t spb = scl8q_scratch_per_block(h->m, h->L);
+        if (spb && !h->d_qscratch) CK(cudaMalloc(&h->d_qscratch, spb * (size_t)fast_blocks(h)));
+        if (!h->d_mc_redo) CK(cudaMalloc(&h->d_mc_redo, (size_t)(MC_REDO_CAP + 1) * sizeof(unsigned long long)));
+        CK(cudaMemsetAsync(h->d_mc_redo, 0, sizeof(unsigned long long), h->sc));
+        Scl8qGen g;
+        g.seed = seed; g.sigma = (float)mc_sigma; g.gcrc = h->d_gcrc; g.gcrc_c0 = h->gcrc_c0;
+        g.mc_redo = h->d_mc_redo; g.mc_redo_cap = MC_REDO_CAP;
+        CK(ensure_xhat(h, batch));
+        if (h->skip_cap < (batch + 31) / 32) {
+            cudaFree(h->d_skip); h->d_skip = nullptr; h->skip_cap = 0;
+            CK(cudaMalloc(&h->d_skip, ((batch + 31) / 32) * sizeof(uint32_t)));
+            h->skip_cap = (batch + 31) / 32;
+        }
+        g.skip = h->d_skip;
+        const char* fenv = getenv("PCB_TEST_FORCE_REDO_MOD");       // test hook: these frame ids take the redo path
+        g.force_redo_mod = fenv ? atoi(fenv) : 0;
+        for (uint64_t f0 = 0; f0 < frames; f0 += batch) {
+            const int nb = (int)(frames - f0 < batch ? frames - f0 : batch);
+            g.first_frame = first_frame_id + f0;
+            DecodeArgs a = make_args(h, nullptr, 1, nullptr, nullptr, nb);
+            CK(cudaMemsetAsync(h->d_redo, 0, 2 * sizeof(int), h->sc));    // [1] is the work counter of the launch
+            cudaEvent_t e0, e1;
+            if (cudaEventCreate(&e0) != cudaSuccess || cudaEventCreate(&e1) != cudaSuccess) { cleanup(); return fail(PCB_ECUDA, "cudaEventCreate failed"); }
+            ev.push_back(e0); ev.push_back(e1);
+            const int nq = (nb + fpw - 1) / fpw;
+            CK(cudaEventRecord(e0, h->sc));
+            CK(cudaMemsetAsync(h->d_skip, 0, (((size_t)nb + 31) / 32) * sizeof(uint32_t), h->sc));
+            CK(launch_decode_scl8q(a, h->L, h->h_info_w.data(), h->d_xhat, h->d_qscratch, h->d_redo + 1, nullptr, 0, h->d_yscr, 0, &g,
+                                   nq < fast_blocks(h) ? nq : fast_blocks(h), h->sc));
+            SelectArgs sa = select_args(h, a);
+            sa.count = 1; sa.skip = h->d_skip; sa.counters = h->d_counters; sa.seed = seed; sa.first_frame = g.first_frame;
+            CK(launch_scl_select(sa, h->sm_count, h->sc));
+            CK(cudaEventRecord(e1, h->sc));
+            h->launches += 2;
+            if (ev.size() >= 512) { if (int r = drain()) return r; }
+        }
+        if (int r = drain()) return r;
+        // frames outside the safe input range of the tuned kernel's arithmetic (|y| tiny or huge: ~1e-9 per frame):
+        // the three-launch path decodes them one by one, the generic kernel behind the tuned one
+        unsigned long long nredo = 0;
+        CK(cudaMemcpy(&nredo, h->d_mc_redo, sizeof nredo, cudaMemcpyDeviceToHost));
+        if (nredo > (unsigned long long)MC_REDO_CAP)
+            return fail(PCB_ECUDA, "pcb_montecarlo: %llu frames outside the tuned kernel's input range (limit %d per call)", nredo, MC_REDO_CAP);
+        std::vector<unsigned long long> ids((size_t)nredo);
+        if (nredo) CK(cudaMemcpy(ids.data(), h->d_mc_redo + 1, (size_t)nredo * sizeof(unsigned long long), cudaMemcpyDeviceToHost));
+        if (nredo) { if (int r = ensure_mc(h, 1)) return r; }
+        for (unsigned long long id : ids) {
+            GenArgs gg = gen_args(h, snr_db, seed, id, 1);
+            CK(launch_generate(gg, h->sm_count, h->sc));
+            DecodeArgs a = make_args(h, h->d_ymc, 1, nullptr, h->d_dec, 1);
+            CK(launch(h, a, h->sc));
+            CK(launch_count(h->d_dec, h->d_tx, h->EW, nbits, 1, h->d_counters, h->sc));
+            h->launches += 2;
+        }
+        CK(cudaStreamSynchronize(h->sc));
+    } else {
+    if (int r = ensure_mc(h, batch)) return r;
     // everything of a batch is enqueued on one stream and nothing waits for the host between batches; the
     // decode-kernel time comes from one pair of events per batch, read at the end
-    std::vector<cudaEvent_t> ev;
-    auto cleanup = [&]() { for (auto e : ev) cudaEventDestroy(e); };
     for (uint64_t f0 = 0; f0 < frames; f0 += batch) {
         const int nb = (int)(frames - f0 < batch ? frames - f0 : batch);
         GenArgs g = gen_args(h, snr_db, seed, first_frame_id + f0, nb);
@@ -855,15 +978,10 @@ int pcb_montecarlo(pcb_handle* h, double snr_db, uint64_t frames, uint64_t seed,
         CK(cudaEventRecord(e1, h->sc));
         CK(launch_count(h->d_dec, h->d_tx, h->EW, nbits, nb, h->d_counters, h->sc));
         h->launches += 2;
-        if (ev.size() >= 512) {                              // bounded number of live events on very long runs
-            CK(cudaStreamSynchronize(h->sc));
-            for (size_t i = 0; i < ev.size(); i += 2) { float ms = 0; CK(cudaEventElapsedTime(&ms, ev[i], ev[i + 1])); secs += ms * 1e-3; }
-            cleanup(); ev.clear();
-        }
+        if (ev.size() >= 512) { if (int r = drain()) return r; }
     }
-    CK(cudaStreamSynchronize(h->sc));
-    for (size_t i = 0; i < ev.size(); i += 2) { float ms = 0; CK(cudaEventElapsedTime(&ms, ev[i], ev[i + 1])); secs += ms * 1e-3; }
-    cleanup();
+    if (int r = drain()) return r;
+    }
     unsigned long long cnt[2];
     CK(cudaMemcpy(cnt, h->d_counters, 16, cudaMemcpyDeviceToHost));
     if (frames_done) *frames_done += frames;

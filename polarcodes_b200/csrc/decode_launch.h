@@ -35,6 +35,35 @@ inline size_t warp_scratch_bytes(int sizeofT, int L, int n, int ls) {
     return (size_t)sizeofT * L * (size_t)(n - (n >> (ls - 1)));
 }
 
+// Monte-Carlo mode of the list kernel (decode_scl8q.cu): the kernel generates, decodes and counts
+struct Scl8qGen {
+    uint64_t seed, first_frame;        // Philox key, global id of frame 0 of the launch
+    float sigma;
+    const uint32_t* gcrc;              // device: [ceil((k+crc)/32)][16] words of the payload -> CRC map (crc > 0)
+    uint32_t gcrc_c0;                  // CRC of the all-zero payload
+    uint32_t* skip;                    // device: ceil(B/32) zeroed words; the kernel sets the bit of every frame it puts on mc_redo
+    unsigned long long* mc_redo;       // device: [0] count, [1..] global ids of the frames the kernel could not decode itself
+    int mc_redo_cap;
+    int force_redo_mod;                // test hook
+};
+
+// Final selection of the lane-per-path list kernel (scl_select.cu)
+struct SelectArgs {
+    const uint32_t* xhat;              // [B][L][n/32] codeword estimates of every slot (written by decode_scl8q_kernel)
+    int B, L, n, k, crc, stride;
+    const uint32_t* info_mask;         // n/32 words, device
+    const uint32_t* synd;              // crc > 0: 16 rows of n/32 words, see pcb_set_code
+    uint32_t synd_c0;
+    int* sol;                          // [B][stride] one int per bit, or null
+    uint32_t* sol_bits;                // [B][ceil(stride/32)] packed, or null
+    // Monte-Carlo mode: count the errors of the k information bits against the regenerated payload
+    int count;
+    const uint32_t* skip;              // frames with their bit set are not counted (they are decoded again elsewhere)
+    unsigned long long* counters;      // [0] += frame errors, [1] += bit errors
+    uint64_t seed, first_frame;
+};
+cudaError_t launch_scl_select(const SelectArgs& a, int sm_count, cudaStream_t st);
+
 cudaError_t launch_decode_generic(const DecodeArgs& a, int L, int mode, int fp64, int blocks, int wpb,
                                   cudaStream_t st);
 

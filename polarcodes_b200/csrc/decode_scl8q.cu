@@ -27,6 +27,8 @@
 //    produce the results of the reference's phase-by-phase loop without running it.
 #include "decode_common.cuh"
 #include "decode_launch.h"
+#define PCB_PHILOX_COMPACT 1
+#include "gen_common.cuh"
 
 // Compile-time switches, each measured on the same B200 box (tools/variant.sh + tools/ab.sh):
 // register chains cover the last PCB_Q_CHAIN + 1 stored layers (sizes 8 .. 8 << PCB_Q_CHAIN)
@@ -92,6 +94,9 @@
 #endif
 #ifndef PCB_Q_CPA
 #define PCB_Q_CPA 1
+#endif
+#ifndef PCB_Q_PROU
+#define PCB_Q_PROU 1   // unroll factor of the prologue loops (narrowing / range check): code size beats loads in flight (1: 35.9, 2: 35.8, 4: 35.4 M frames/s)
 #endif
 #ifndef PCB_Q_PF64
 #define PCB_Q_PF64 0   // L2 prefetch of the next quad's double rows, late in the current quad: 33.5 vs 35.7 M frames/s, off
@@ -455,16 +460,16 @@ __device__ __noinline__ PathState fork_slow(PathState s, float A0, int lane, int
     return s;
 }
 
-template <int M, int LL, typename YT, bool CONV>
+template <int M, int LL, typename YT, bool ROWS>
 struct Dec {
     using G = Geo<M, LL>;
     static constexpr int FPW = G::FPW, LB = G::LB;
     int lane, p;
-    // channel values of the frames of this quad: CONV: the block's own converted copy (frame f of the quad at
-    // ysrc + f * N, written by the quad prologue), else the batch itself (frame id * N)
+    // channel values of the frames of this quad: ROWS: the block's own float rows (frame f of the quad at
+    // ysrc + f * N, written by the quad prologue: narrowed doubles or generated frames), else the batch itself
     const YT* ysrc;
     __device__ __forceinline__ const YT* yrow(int f) const {
-        if constexpr (CONV) return ysrc + f * G::N;
+        if constexpr (ROWS) return ysrc + f * G::N;
         else return ysrc + (size_t)min(fbase + f, Bm1) * G::N;
     }
     int fbase, Bm1;    // first frame of the quad, last frame of the batch (tail quads repeat it)
@@ -1109,11 +1114,7 @@ struct Scl8qArgs {
     uint32_t info_w[65];   // n <= 2048, one zero word behind the last
     int* next_quad;        // work counter (zero at launch): quad gridDim.x + counter is the next one not yet taken
     float4* l3;            // n >= 1024: global scratch of the layer-3 arrays, Geo::L3_BLOCK_FLOAT4 per block
-    // CRC check as a syndrome of the codeword estimate: crc(info bits of x F) ^ (appended CRC bits of
-    // x F) is affine in x, so slot q passes iff S x_q == c0 with S a crc x n bit matrix that depends
-    // on the code only (row t as n/32 words at synd[t * n/32 ..)) and c0 the CRC of the zero message.
-    const uint32_t* synd;
-    uint32_t synd_c0;
+    uint32_t* xhat;        // out: [B][L][n/32] codeword estimates of every slot, the input of scl_select_kernel
     // Quad prologue (replaces the separate pre-pass): every frame is range-checked by the warp that decodes
     // it (frames outside the safe input range of the arithmetic go on the redo list of the generic kernel).
     // CONV kernels also narrow: frames below nf are floats at a.y, frame f >= nf is doubles at
@@ -1123,16 +1124,123 @@ struct Scl8qArgs {
     int nf;
     float* yscr;
     int check_range;       // 0: the producer of the batch has already range-checked it (on-device generator)
+    // SRC = 2, the Monte-Carlo loop body in one kernel (PolarCodes.cpp:132-192): the warp GENERATES the frames of
+    // its quad (payload, CRC, frozen bits, encoder, BPSK + AWGN: gen_common.cuh, the same functions and the same
+    // Philox stream as generate_kernel) into its rows of yscr, decodes them, and counts frame / bit errors of
+    // the k information bits against the payload it regenerates — no channel value ever reaches HBM.
+    uint64_t seed, first_frame;
+    float sigma;
+    const uint32_t* gcrc;  // [16][IW] rows of the payload -> CRC map (crc = gcrc_c0 ^ XOR of the columns of the set bits)
+    uint32_t gcrc_c0;
+    uint32_t* skip;                    // bit f set: frame f is on the redo list, scl_select_kernel must not count it
+    unsigned long long* mc_redo;       // [0] = count, then global frame ids of frames outside the safe input range
+    int mc_redo_cap;
+    int force_redo_mod;    // test hook: frames whose id is a multiple of this take the redo path
+    int gen;               // 1: SRC = 2
 };
 
+namespace q8 {
+// One frame of the Monte-Carlo loop body up to Transform (PolarCodes.cpp:133-158), made by the warp that will
+// decode it: payload bits, CRC (GF(2)-affine in the payload: 16 parities per word), AddFrozenBits (frozen values
+// 0), x = u F^(x)m, BPSK + AWGN into `row` (n floats, the block's own rows: they stay in L2).  Same device functions
+// and the same Philox stream as generate_kernel.  SM: n/32 + (k+crc)/32 + 1 words of scratch (the frame's LLR region,
+// dead between quads).  Returns false in the lanes that saw a value outside the safe input range of the kernel's arithmetic.
+// Out of line and rolled on purpose: it runs once per frame, and every SASS row of this kernel competes for the
+// instruction cache with the decoding loop of the 15 other warps of the SM.
+template <int M>
+__device__ __forceinline__ bool gen_frame(const Scl8qArgs& S, const Philox& ph, uint64_t fid, uint32_t* SM, float* row, int lane) {
+    constexpr int n = 1 << M, NW = n / 32;
+    const DecodeArgs& A = S.a;
+    const int ninf = A.k + A.crc, IW = (ninf + 31) >> 5;
+    const uint32_t f_lo = (uint32_t)fid, f_hi = (uint32_t)(fid >> 32);
+    uint32_t* Wd = SM;            // u, then the codeword
+    uint32_t* XI = SM + NW;       // payload + CRC
+    // (loops with warp-uniform bounds and a lane predicate inside: the compiler then still knows that the warp is
+    // converged everywhere in the kernel; lane-dependent trip counts here cost 40 % more SASS in the whole kernel)
+#pragma unroll 1
+    for (int w0 = 0; w0 < IW; w0 += 32) {                                                 // PolarCodes.cpp:133-135
+        const int w = w0 + lane;
+        const uint32_t v = payload_word(ph, f_lo, f_hi, min(w, IW - 1), A.k);
+        if (w < IW) XI[w] = v;
+    }
+#pragma unroll 1
+    for (int w0 = 0; w0 < NW; w0 += 32) { if (w0 + lane < NW) Wd[w0 + lane] = 0; }
+    __syncwarp();
+    if (A.crc) {                  // PolarCodes.cpp:136-155
+        uint32_t acc = 0;
+#pragma unroll 1
+        for (int w0 = 0; w0 < IW; w0 += 32) {
+            const int w = min(w0 + lane, IW - 1);
+            const uint32_t x = w0 + lane < IW ? XI[w] : 0u;
+            const uint4* g = reinterpret_cast<const uint4*>(S.gcrc + 16 * w);              // the 16 rows of word w
+#pragma unroll 1
+            for (int t4 = 0; t4 < 4; t4++) {
+                const uint4 gv = __ldg(g + t4);
+                acc ^= ((uint32_t)(__popc(x & gv.x) & 1) | ((uint32_t)(__popc(x & gv.y) & 1) << 1) | ((uint32_t)(__popc(x & gv.z) & 1) << 2) |
+                        ((uint32_t)(__popc(x & gv.w) & 1) << 3)) << (4 * t4);
+            }
+        }
+        const uint32_t r = __reduce_xor_sync(FULL, acc) ^ S.gcrc_c0;
+        if (lane < A.crc && ((r >> (A.crc - 1 - lane)) & 1u)) atomicOr(&XI[(A.k + lane) >> 5], 1u << ((A.k + lane) & 31));   // MSB first
+        __syncwarp();
+    }
+#pragma unroll 1
+    for (int t0 = 0; t0 < ninf; t0 += 32) {                                                // AddFrozenBits, Encoder.cpp:17-33
+        const int t = min(t0 + lane, ninf - 1);
+        const int pos = A.info_pos[t];
+        if (t0 + lane < ninf && ((XI[t >> 5] >> (t & 31)) & 1u)) atomicOr(&Wd[pos >> 5], 1u << (pos & 31));
+    }
+    __syncwarp();
+    // x = u F^(x)m (Encoder.cpp:57-83): inside the words, then across them
+#pragma unroll 1
+    for (int w0 = 0; w0 < NW; w0 += 32) {
+        const int w = w0 + lane;
+        if (w < NW) {
+            uint32_t x = Wd[w];
+            x ^= (x >> 1) & 0x55555555u; x ^= (x >> 2) & 0x33333333u; x ^= (x >> 4) & 0x0F0F0F0Fu;
+            x ^= (x >> 8) & 0x00FF00FFu; x ^= (x >> 16) & 0x0000FFFFu;
+            Wd[w] = x;
+        }
+    }
+    __syncwarp();
+#pragma unroll 1
+    for (int sw = 1; sw < NW; sw <<= 1) {
+#pragma unroll 1
+        for (int w0 = 0; w0 < NW; w0 += 32) {
+            const int w = w0 + lane;
+            if (w < NW && !(w & sw)) Wd[w] ^= Wd[w + sw];
+        }
+        __syncwarp();
+    }
+    // Transform (Encoder.cpp:35-41); the range check of the arithmetic rides along
+    bool ok = true;
+#pragma unroll 1
+    for (int q0 = 0; q0 < n / 4; q0 += 32) {
+        const int q = q0 + lane;
+        const float4 v = channel4(ph, f_lo, f_hi, q, Wd[q >> 3] >> (4 * (q & 7)), S.sigma);
+        reinterpret_cast<float4*>(row)[q] = v;
+        const uint32_t ax = __float_as_uint(v.x) & 0x7fffffffu, ay = __float_as_uint(v.y) & 0x7fffffffu;
+        const uint32_t az = __float_as_uint(v.z) & 0x7fffffffu, aw = __float_as_uint(v.w) & 0x7fffffffu;
+        // |y| == 0 or 2^-40 (0x2B800000) <= |y| <= 2^100 (0x71800000)
+        ok = ok && (ax == 0u || ax - 0x2B800000u <= 0x46000000u) && (ay == 0u || ay - 0x2B800000u <= 0x46000000u) &&
+             (az == 0u || az - 0x2B800000u <= 0x46000000u) && (aw == 0u || aw - 0x2B800000u <= 0x46000000u);
+    }
+    if (S.force_redo_mod && (uint32_t)fid % (uint32_t)S.force_redo_mod == 0u) ok = false;      // (32-bit: a 64-bit modulo is 300 SASS rows)
+    __syncwarp();
+    return ok;                    // this lane's values; the caller votes (a vote in the kernel body keeps its control flow provably uniform)
+}
+}  // namespace q8
+
 // One warp per block (blockDim.x == 32); a block decodes quads of frames.
-template <int M, int LL, typename YT, bool CONV>
+template <int M, int LL, typename YT, int SRC>
 __global__ void __launch_bounds__(q8::Geo<M, LL>::MW ? 32 * q8::Geo<M, LL>::WMAX : 32,
                                   q8::Geo<M, LL>::MW ? 1 : (LL != 8 ? 1 : q8::Geo<M, LL>::GL4 && M == 10 ? 16 : M == 10 ? 10 : 5))
     decode_scl8q_kernel(const __grid_constant__ Scl8qArgs S) {
     const DecodeArgs& A = S.a;
     using G = q8::Geo<M, LL>;
     constexpr int FPW = G::FPW;
+    constexpr bool CONV = SRC == 1, GEN = SRC == 2, ROWS = SRC != 0;
+    [[maybe_unused]] constexpr int PROU = PCB_Q_PROU;
     extern __shared__ __align__(16) unsigned char smem_raw[];
     constexpr unsigned FULL = 0xffffffffu;
     // a warp is a virtual block (G::MW: several of them in one block)
@@ -1140,7 +1248,7 @@ __global__ void __launch_bounds__(q8::Geo<M, LL>::MW ? 32 * q8::Geo<M, LL>::WMAX
     const int vblock = blockIdx.x * wpb + wib, nvblocks = gridDim.x * wpb;
     unsigned char* const smem_warp = smem_raw + (size_t)wib * G::TOTAL;
     const int fme = lane / LL;
-    q8::Dec<M, LL, YT, CONV> D;
+    q8::Dec<M, LL, YT, ROWS> D;
     D.lane = lane; D.p = lane & (LL - 1);
     D.W = reinterpret_cast<float*>(smem_warp);
     D.P = D.W + fme * G::FRAME_WORDS;
@@ -1153,11 +1261,12 @@ __global__ void __launch_bounds__(q8::Geo<M, LL>::MW ? 32 * q8::Geo<M, LL>::WMAX
     D.L4 = G::GL4 ? S.l3 + (size_t)vblock * G::SCRATCH_BLOCK_FLOAT4 + G::L3_BLOCK_FLOAT4 + fme * (G::Q3 / 2 * LL) : nullptr;
     D.L5 = G::GL5 ? S.l3 + (size_t)vblock * G::SCRATCH_BLOCK_FLOAT4 + G::L3_BLOCK_FLOAT4 + G::L4_BLOCK_FLOAT4 + fme * (G::Q3 / 4 * LL) : nullptr;
     constexpr int n = G::N;
-    const int EW = (A.stride + 31) >> 5;
     const YT* ybase = reinterpret_cast<const YT*>(A.y);
-    float* const yscr = CONV ? S.yscr + (size_t)vblock * (FPW * G::N) : nullptr;
-    D.ysrc = CONV ? yscr : ybase;
+    float* const yscr = ROWS ? S.yscr + (size_t)vblock * (FPW * G::N) : nullptr;
+    D.ysrc = ROWS ? yscr : ybase;
     const int nquads = (A.B + FPW - 1) / FPW;
+    [[maybe_unused]] const Philox ph{(uint32_t)S.seed, (uint32_t)(S.seed >> 32)};
+    [[maybe_unused]] unsigned redo_mask = 0;                        // GEN: frames of the quad that scl_select_kernel must not count
 
     // The first quad of a block is its index, the following ones come from a work counter: decode
     // times differ from quad to quad, and a static stride leaves SMs idle at the end of the batch.
@@ -1175,8 +1284,26 @@ __global__ void __launch_bounds__(q8::Geo<M, LL>::MW ? 32 * q8::Geo<M, LL>::WMAX
 #endif
         D.met = 0.f; D.maxmet = 0; D.pidx = 0; D.cidx = 0; D.w0 = 0; D.ninfo = 0;
         D.r4 = make_float4(0.f, 0.f, 0.f, 0.f); D.r2_0 = D.r2_1 = D.A0 = 0.f;
+        // ---- generating prologue: the Monte-Carlo loop body up to Transform (PolarCodes.cpp:133-158) ----
+        if constexpr (GEN) {
+            redo_mask = 0;
+            __syncwarp();                              // the previous quad is done with the block's rows and the LLR region
+#pragma unroll 1
+            for (int f = 0; f < FPW; f++) {
+                const uint64_t fid = S.first_frame + (uint64_t)min(FPW * quad + f, A.B - 1);
+                const bool ok = q8::gen_frame<M>(S, ph, fid, reinterpret_cast<uint32_t*>(D.W + f * G::FRAME_WORDS), yscr + f * n, lane);
+                if (!__all_sync(FULL, ok)) {
+                    redo_mask |= 1u << f;
+                    if (lane == 0 && FPW * quad + f < A.B) {
+                        const unsigned long long slot = atomicAdd(S.mc_redo, 1ull);
+                        if (slot < (unsigned long long)S.mc_redo_cap) S.mc_redo[1 + slot] = fid;
+                    }
+                }
+            }
+            __syncwarp();                              // the rows are written before anyone stages them
+        }
         // ---- quad prologue: range check (and narrowing) of the quad's frames --------------------------
-        if (CONV || S.check_range) {
+        if (!GEN && (CONV || S.check_range)) {
             if constexpr (CONV) __syncwarp();          // the previous quad is done with the block's rows
 #pragma unroll 1
             for (int f = 0; f < FPW; f++) {
@@ -1193,8 +1320,9 @@ __global__ void __launch_bounds__(q8::Geo<M, LL>::MW ? 32 * q8::Geo<M, LL>::WMAX
                 if (CONV && frame >= S.nf) {
                     const double2* src = reinterpret_cast<const double2*>(S.y64 + (size_t)(frame - S.nf) * n);
                     float4* dst = reinterpret_cast<float4*>(yscr + f * n);
-#pragma unroll 4
-                    for (int q = lane; q < n / 4; q += 32) {
+#pragma unroll PROU
+                    for (int q0 = 0; q0 < n / 4; q0 += 32) {
+                        const int q = q0 + lane;
                         const double2 a = __ldcs(src + 2 * q), b = __ldcs(src + 2 * q + 1);   // streamed: read once
                         const float4 v = make_float4((float)a.x, (float)a.y, (float)b.x, (float)b.y);   // :406-408
                         dst[q] = v;
@@ -1203,8 +1331,9 @@ __global__ void __launch_bounds__(q8::Geo<M, LL>::MW ? 32 * q8::Geo<M, LL>::WMAX
                 } else {
                     const float4* src = reinterpret_cast<const float4*>(reinterpret_cast<const float*>(A.y) + (size_t)frame * n);
                     [[maybe_unused]] float4* dst = reinterpret_cast<float4*>(yscr + f * n);
-#pragma unroll 4
-                    for (int q = lane; q < n / 4; q += 32) {
+#pragma unroll PROU
+                    for (int q0 = 0; q0 < n / 4; q0 += 32) {
+                        const int q = q0 + lane;
                         const float4 v = CONV ? __ldcs(src + q) : src[q];
                         if constexpr (CONV) dst[q] = v;
                         chk(v);
@@ -1238,122 +1367,44 @@ __global__ void __launch_bounds__(q8::Geo<M, LL>::MW ? 32 * q8::Geo<M, LL>::WMAX
             D.leaf8(blk, ib);
         }
         __syncwarp();
-        // ---- final selection (:432-473): u-hat = x-hat F^(x)m per slot, CRC, first pass wins ----
-        // Lane l owns words l (and l + 32) of a codeword estimate: the transform inside a word is
-        // five shift-xor steps, across words five shuffles, and the information bits of a word are
-        // compressed (Hacker's Delight 7-4) and OR-ed into the packed output at the bit offset that
-        // the information counts of the words before it give.
-        constexpr int NW = G::NW, XHS = G::XHS, WPL = NW > 32 ? NW / 32 : 1;
-        uint32_t sm[WPL][16];                // this lane's words of the syndrome rows (zero rows above crc)
-#pragma unroll
-        for (int w = 0; w < WPL; w++)
-#pragma unroll
-            for (int t = 0; t < 16; t++) sm[w][t] = (A.crc > t && lane + 32 * w < NW) ? __ldg(S.synd + t * NW + lane + 32 * w) : 0u;
-        uint32_t mk[WPL];
-        int off[WPL];
-        {
-            int base = 0;
-#pragma unroll
-            for (int w = 0; w < WPL; w++) {
-                mk[w] = lane + 32 * w < NW ? S.info_w[lane + 32 * w] : 0u;
-                const int c = __popc(mk[w]);
-                int inc = c;
-#pragma unroll
-                for (int d = 1; d < 32; d <<= 1) { const int v = __shfl_up_sync(FULL, inc, d); if (lane >= d) inc += v; }
-                off[w] = base + inc - c;
-                base += __shfl_sync(FULL, inc, 31);
-            }
-        }
+        // ---- the codeword estimates of every slot leave the kernel (setbit_last, d2 == M, put them in the LLR
+        // region); the final selection (:432-473) is scl_select_kernel's (scl_select.cu): it runs once per frame, and
+        // every SASS row of THIS kernel competes with the decoding loop for the instruction cache.
+        constexpr int NW = G::NW, XHS = G::XHS;
 #pragma unroll 1
         for (int fs = 0; fs < FPW; fs++) {
-            uint32_t* X = reinterpret_cast<uint32_t*>(D.W + fs * G::FRAME_WORDS);   // x-hat of every slot (setbit_last, d2 == M)
-            // (:442-472) the first slot, in slot order, whose CRC passes; slot L-1 if none does or
-            // there is no CRC.  The check needs no u-hat: 16 (8) parities of x-hat per lane and word,
-            // one XOR reduction per slot, and it stops at the first slot that passes.
-            int chosen = LL - 1;
-            if (A.crc) {
-#pragma unroll 1
-                for (int q = 0; q < LL; q++) {
-                    uint32_t acc = 0;
-#pragma unroll
-                    for (int w = 0; w < WPL; w++) {
-                        const uint32_t x = lane + 32 * w < NW ? X[q * XHS + lane + 32 * w] : 0u;
-#pragma unroll
-                        for (int t = 0; t < 16; t++) acc ^= (uint32_t)(__popc(x & sm[w][t]) & 1) << t;
-                    }
-                    if (__reduce_xor_sync(FULL, acc) == S.synd_c0) { chosen = q; break; }
-                }
-            }
-            // u-hat of the chosen slot: transform, then the information bits compressed into E
-            uint32_t* Ec = X + G::OFF_H;         // the partial-sum heaps are dead by now
-            {
-                const int q = chosen;
-                uint32_t xs[WPL];
-#pragma unroll
-                for (int w = 0; w < WPL; w++) {
-                    uint32_t x = lane + 32 * w < NW ? X[q * XHS + lane + 32 * w] : 0u;
-                    x ^= (x >> 1) & 0x55555555u; x ^= (x >> 2) & 0x33333333u; x ^= (x >> 4) & 0x0F0F0F0Fu;
-                    x ^= (x >> 8) & 0x00FF00FFu; x ^= (x >> 16) & 0x0000FFFFu;
-#pragma unroll
-                    for (int sw = 1; sw < 32 && sw < NW; sw <<= 1) {
-                        const uint32_t y = __shfl_xor_sync(FULL, x, sw);
-                        if (!(lane & sw)) x ^= y;
-                    }
-                    xs[w] = x;
-                }
-                if constexpr (WPL == 2) xs[0] ^= xs[1];
-#pragma unroll 1
-                for (int t = lane; t < EW; t += 32) Ec[t] = 0;
-                __syncwarp();
-#pragma unroll
-                for (int w = 0; w < WPL; w++) {
-                    uint32_t m = mk[w], x = xs[w] & m, mkk = ~m << 1;
-#pragma unroll 1
-                    for (int i = 0; i < 5; i++) {
-                        uint32_t mp = mkk ^ (mkk << 1);
-                        mp ^= mp << 2; mp ^= mp << 4; mp ^= mp << 8; mp ^= mp << 16;
-                        const uint32_t mv = mp & m;
-                        m = (m ^ mv) | (mv >> (1 << i));
-                        const uint32_t t = x & mv;
-                        x = (x ^ t) | (t >> (1 << i));
-                        mkk &= ~mp;
-                    }
-                    const int c = __popc(mk[w]), o = off[w];
-                    if (c) {
-                        atomicOr(&Ec[o >> 5], x << (o & 31));
-                        if ((o & 31) + c > 32) atomicOr(&Ec[(o >> 5) + 1], x >> (32 - (o & 31)));
-                    }
-                }
-            }
-            __syncwarp();
             const int frame = FPW * quad + fs;
-            if (frame < A.B) {
-                if (A.sol)
-#pragma unroll 1
-                    for (int t = lane; t < A.stride; t += 32)
-                        A.sol[(size_t)frame * A.stride + t] = (Ec[t >> 5] >> (t & 31)) & 1;
-                if (A.sol_bits)
-#pragma unroll 1
-                    for (int t = lane; t < EW; t += 32) A.sol_bits[(size_t)frame * EW + t] = Ec[t];
+            if (frame < A.B) {                          // (warp-uniform)
+                const uint32_t* X = reinterpret_cast<const uint32_t*>(D.W + fs * G::FRAME_WORDS);
+                uint32_t* dst = S.xhat + (size_t)frame * (LL * NW);
+#pragma unroll 2
+                for (int i0 = 0; i0 < LL * NW; i0 += 32) {
+                    const int i = i0 + lane;
+                    if (LL * NW >= 32 || i < LL * NW) dst[i] = X[(i / NW) * XHS + (i & (NW - 1))];
+                }
+                if constexpr (GEN) {
+                    if (lane == 0 && ((redo_mask >> fs) & 1u)) atomicOr(&S.skip[frame >> 5], 1u << (frame & 31));
+                }
             }
-            __syncwarp();
         }
+        __syncwarp();
         quad = next_quad;
     }
 }
 
-template <int M, int LL, typename YT, bool CONV>
+template <int M, int LL, typename YT, int SRC>
 static cudaError_t launch_mc(const Scl8qArgs& a, int blocks, cudaStream_t st) {
     const int W = q8::Geo<M, LL>::MW ? q8::Geo<M, LL>::WMAX : 1;      // `blocks` counts warps
     const size_t smem = (size_t)q8::Geo<M, LL>::TOTAL * W;
-    cudaError_t e = cudaFuncSetAttribute(decode_scl8q_kernel<M, LL, YT, CONV>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    cudaError_t e = cudaFuncSetAttribute(decode_scl8q_kernel<M, LL, YT, SRC>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
-    decode_scl8q_kernel<M, LL, YT, CONV><<<(blocks + W - 1) / W, 32 * W, smem, st>>>(a);
+    decode_scl8q_kernel<M, LL, YT, SRC><<<(blocks + W - 1) / W, 32 * W, smem, st>>>(a);
     return cudaGetLastError();
 }
 template <int M, int LL, typename YT>
 static cudaError_t launch_m(const Scl8qArgs& a, int blocks, cudaStream_t st) {
-    return a.y64 ? launch_mc<M, LL, YT, true>(a, blocks, st) : launch_mc<M, LL, YT, false>(a, blocks, st);
+    if (a.gen) return launch_mc<M, LL, YT, 2>(a, blocks, st);
+    return a.y64 ? launch_mc<M, LL, YT, 1>(a, blocks, st) : launch_mc<M, LL, YT, 0>(a, blocks, st);
 }
 
 template <int M, int LL, typename YT>
@@ -1361,14 +1412,14 @@ static cudaError_t occ_m(int* bps, int* warp_bytes) {
     const size_t smem = (size_t)q8::Geo<M, LL>::TOTAL;
     *warp_bytes = q8::Geo<M, LL>::TOTAL;
     const int W = q8::Geo<M, LL>::MW ? q8::Geo<M, LL>::WMAX : 1;
-    cudaError_t e = cudaFuncSetAttribute(decode_scl8q_kernel<M, LL, YT, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(smem * W));
+    cudaError_t e = cudaFuncSetAttribute(decode_scl8q_kernel<M, LL, YT, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(smem * W));
     if (e != cudaSuccess) return e;
     int nb = 0, nb2 = 0;
-    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, decode_scl8q_kernel<M, LL, YT, true>, 32 * W, smem * W);
+    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, decode_scl8q_kernel<M, LL, YT, 1>, 32 * W, smem * W);
     if (e != cudaSuccess) return e;
-    e = cudaFuncSetAttribute(decode_scl8q_kernel<M, LL, YT, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(smem * W));
+    e = cudaFuncSetAttribute(decode_scl8q_kernel<M, LL, YT, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(smem * W));
     if (e != cudaSuccess) return e;
-    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb2, decode_scl8q_kernel<M, LL, YT, false>, 32 * W, smem * W);
+    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb2, decode_scl8q_kernel<M, LL, YT, 0>, 32 * W, smem * W);
     if (nb2 < nb) nb = nb2;                  // one grid size (and scratch size) for both input paths
     *bps = nb * W;                           // warps per SM
     return e;
@@ -1378,25 +1429,38 @@ static cudaError_t occ_m(int* bps, int* warp_bytes) {
 bool scl8q_supported(int m, int L) { return m >= 8 && m <= 11 && (L == 2 || L == 4 || L == 8 || L == 16 || L == 32); }
 int scl8q_frames_per_warp(int L) { return 32 / L; }
 
+#ifdef PCB_Q_ONLY          // kernel experiments: one instantiation compiles in seconds
+#define PCB_FOR_ALL(X) X(10, 8)
+#else
 #define PCB_FOR_ALL(X) \
     X(8, 8) X(9, 8) X(10, 8) X(11, 8) X(8, 16) X(9, 16) X(10, 16) X(11, 16) X(8, 32) X(9, 32) X(10, 32) X(11, 32) \
     X(8, 4) X(9, 4) X(10, 4) X(11, 4) X(8, 2) X(9, 2) X(10, 2) X(11, 2)
+#endif
 
 // info_w: host copy of the information-mask words (ceil(n/32)), passed as kernel parameters
 // y64 != null: frames >= nf of the batch are doubles at y64 + (frame - nf) * n and yscr holds blocks * (32 / L) * n
 // floats; check_range: fill the redo list (a.redo_count / a.redo_list) with the frames outside the safe input range
-cudaError_t launch_decode_scl8q(const DecodeArgs& a, int L, const uint32_t* info_w, const uint32_t* synd, uint32_t synd_c0, void* l3_scratch, int* next_quad,
-                                const double* y64, int nf, float* yscr, int check_range, int blocks, cudaStream_t st) {
+// gen != null: the frames are generated by the kernel itself (Scl8qGen, decode_launch.h) and counted, a.y is unused
+cudaError_t launch_decode_scl8q(const DecodeArgs& a, int L, const uint32_t* info_w, uint32_t* xhat, void* l3_scratch, int* next_quad,
+                                const double* y64, int nf, float* yscr, int check_range, const Scl8qGen* gen, int blocks, cudaStream_t st) {
     Scl8qArgs s;
     s.a = a;
     s.y64 = y64; s.nf = y64 ? nf : a.B; s.yscr = yscr; s.check_range = check_range;
-    if (y64 && !yscr) return cudaErrorInvalidValue;
+    if ((y64 || gen) && !yscr) return cudaErrorInvalidValue;
+    s.seed = 0; s.first_frame = 0; s.sigma = 0.f; s.gcrc = nullptr; s.gcrc_c0 = 0; s.skip = nullptr; s.mc_redo = nullptr; s.gen = gen ? 1 : 0;
+    s.mc_redo_cap = 0; s.force_redo_mod = 0;
+    if (gen) {
+        if (!gen->skip || !gen->mc_redo || (a.crc && !gen->gcrc)) return cudaErrorInvalidValue;
+        s.seed = gen->seed; s.first_frame = gen->first_frame; s.sigma = gen->sigma; s.gcrc = gen->gcrc; s.gcrc_c0 = gen->gcrc_c0;
+        s.skip = gen->skip; s.mc_redo = gen->mc_redo; s.mc_redo_cap = gen->mc_redo_cap; s.force_redo_mod = gen->force_redo_mod;
+        s.y64 = nullptr; s.check_range = 0;
+    }
     s.next_quad = next_quad;
     s.l3 = reinterpret_cast<float4*>(l3_scratch);
-    s.synd = synd; s.synd_c0 = synd_c0;
-    if (a.crc && !synd) return cudaErrorInvalidValue;
+    s.xhat = xhat;
+    if (!xhat) return cudaErrorInvalidValue;
     for (int i = 0; i < 65; i++) s.info_w[i] = i < a.n / 32 ? info_w[i] : 0;
-    if (!a.y_f32 && !y64) return cudaErrorInvalidValue;   // a.y is float; doubles come in through y64
+    if (!a.y_f32 && !y64 && !gen) return cudaErrorInvalidValue;   // a.y is float; doubles come in through y64
 #define PCB_CASE(MM, LLL) if (a.m == MM && L == LLL) return launch_m<MM, LLL, float>(s, blocks, st);
     PCB_FOR_ALL(PCB_CASE)
 #undef PCB_CASE

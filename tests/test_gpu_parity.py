@@ -192,6 +192,30 @@ def test_montecarlo_consistency(oracle):
     # (the noise statistics of the generator are tested in test_gpu_ref_parity.py::test_channel_noise_statistics)
 
 
+@pytest.mark.parametrize("n,k,crc,L,snr,frames", [(1024, 512, 16, 8, 1.5, 40003), (1024, 512, 0, 8, 2.0, 9999), (2048, 1024, 16, 32, 1.5, 3001),
+                                                  (2048, 1024, 16, 4, 2.0, 20000), (512, 256, 8, 16, 1.0, 7777), (256, 128, 8, 2, 1.0, 30001)])
+def test_fused_montecarlo_equals_three_launch_path(n, k, crc, L, snr, frames):
+    """PCB_MC_FUSED=1: pcb_montecarlo on the tuned list kernel generates the frames inside the warp that decodes
+    them (no channel value in HBM) and scl_select_kernel counts; the default runs generate_kernel / list kernel /
+    count_errors_kernel over a float batch in HBM.  Same Philox stream, same device functions: identical counters.
+    PCB_TEST_FORCE_REDO_MOD pushes every 97th frame through the path for frames outside the tuned kernel's input range."""
+    import polarcodes_b200 as pb
+    code = pb.Code(n, k, crc, snr)
+    d = _decoder(3, n, k, crc, L, code.mask, code.sigma)
+    plain = d.montecarlo(snr, frames, seed=5, first_frame_id=123456789012)
+    os.environ["PCB_MC_FUSED"] = "1"
+    try:
+        fused = d.montecarlo(snr, frames, seed=5, first_frame_id=123456789012)
+        os.environ["PCB_TEST_FORCE_REDO_MOD"] = "97"
+        forced = d.montecarlo(snr, frames, seed=5, first_frame_id=123456789012)
+    finally:
+        os.environ.pop("PCB_TEST_FORCE_REDO_MOD", None)
+        del os.environ["PCB_MC_FUSED"]
+    for key in ("frames", "frame_errors", "bit_errors"):
+        assert fused[key] == plain[key] == forced[key], (key, fused, plain, forced)
+    assert fused["frame_errors"] > 0 or snr >= 2.0
+
+
 def test_sc_montecarlo_fer_matches_published():
     """pc.txt:3 (SC min-sum (1024,512), BEC construction, 2 dB): FER 0.1255 with 10 000 frames."""
     import polarcodes_b200 as pb
