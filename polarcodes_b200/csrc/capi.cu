@@ -668,9 +668,7 @@ static int decode_host(pcb_handle* h, const void* y, int y_f32, int* sol, uint32
     auto t_iter = std::chrono::steady_clock::now();
     if (narrow) {
         if (h->stage_frames < chunk) {
-            if (h->comm) nccl_api().CommDestroy(h->comm);
-    cudaFree(h->d_red);
-    cudaFreeHost(h->h_stage[0]); cudaFreeHost(h->h_stage[1]);
+            cudaFreeHost(h->h_stage[0]); cudaFreeHost(h->h_stage[1]);
             h->h_stage[0] = h->h_stage[1] = nullptr; h->stage_frames = 0;
             for (int s = 0; s < 2; s++) CK(cudaHostAlloc(&h->h_stage[s], chunk * (size_t)h->n * 4, cudaHostAllocDefault));
             h->stage_frames = chunk;
