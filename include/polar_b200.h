@@ -111,6 +111,21 @@ int pcb_decode_batch_f32_packed(pcb_handle* h, const float* y, uint32_t* sol_bit
 int pcb_decode_batch_dev(pcb_handle* h, const void* y_dev, int y_is_f32, uint32_t* sol_bits_dev, int B,
                          float* ms);
 
+/* No-allocation variant of pcb_decode_batch_dev.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving
+ * loops, harnesses that forbid it).  Same arguments and the same (bit-identical) output, but the call makes
+ * no cudaMalloc / cudaFree / allocating library call: it runs the reference-literal kernel (one warp per
+ * frame) with its per-warp LLR scratch in a static device array of PCB_NOALLOC_SCRATCH_BYTES that every GPU
+ * which loads the library holds until exit.  Limits: B <= PCB_NOALLOC_MAX_FRAMES per call, and one block's
+ * scratch (about 4 n L bytes per warp, 8 n for the fp64 decoders) must fit the array — every code a handle
+ * can be created for does today (at most 3.5 MiB), the check guards later changes; beyond either limit the
+ * call returns PCB_EINVAL with the numbers in pcb_last_error().  The grid is the number of blocks whose
+ * scratch fits the array, so the call is slower than pcb_decode_batch_dev.  All calls on a GPU share the array (whatever the handle): calls that
+ * overlap on the GPU race; serialise them.  Synchronises before returning. */
+#define PCB_NOALLOC_SCRATCH_BYTES (8u << 20)
+#define PCB_NOALLOC_MAX_FRAMES (1 << 20)
+int pcb_decode_batch_dev_noalloc(pcb_handle* h, const void* y_dev, int y_is_f32, uint32_t* sol_bits_dev, int B);
+
 /* Batched Monte-Carlo body (PolarCodes.cpp:132-192) with on-device Philox4x32-10 BPSK/AWGN:
  * frames [first_frame_id, first_frame_id + frames) of the stream keyed by `seed`; results do
  * not depend on batch size or GPU count. Counters are ADDED to *frame_errors / *bit_errors

@@ -47,6 +47,7 @@ SIGNATURES = {
     "pcb_decode_batch_f32": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int]),
     "pcb_decode_batch_f32_packed": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int]),
     "pcb_decode_batch_dev": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.POINTER(C.c_float)]),
+    "pcb_decode_batch_dev_noalloc": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_int]),
     "pcb_montecarlo": (C.c_int, [C.c_void_p, C.c_double, C.c_uint64, C.c_uint64, C.c_uint64, _u64p, _u64p, _u64p,
                                  C.POINTER(C.c_double)]),
     "pcb_generate_batch": (C.c_int, [C.c_void_p, C.c_double, C.c_uint64, C.c_uint64, C.c_int, _fp, _ip]),
@@ -200,6 +201,10 @@ class Decoder:
         ms = C.c_float(0)
         _check(lib().pcb_decode_batch_dev(self._h, y_dev_ptr, int(y_is_f32), sol_bits_dev_ptr, B, C.byref(ms)))
         return ms.value
+
+    def decode_dev_noalloc(self, y_dev_ptr, y_is_f32, sol_bits_dev_ptr, B):
+        """pcb_decode_batch_dev without any allocation (static device scratch; see include/polar_b200.h)."""
+        _check(lib().pcb_decode_batch_dev_noalloc(self._h, y_dev_ptr, int(y_is_f32), sol_bits_dev_ptr, B))
 
     def montecarlo(self, snr_db, frames, seed=0x5EED0000, first_frame_id=0):
         done, fe, be, sec = C.c_uint64(0), C.c_uint64(0), C.c_uint64(0), C.c_double(0)

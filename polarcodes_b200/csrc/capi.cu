@@ -182,6 +182,8 @@ struct pcb_handle {
     uint32_t *d_info_mask = nullptr, *d_frozen_val = nullptr;
     uint16_t* d_info_pos = nullptr;
     unsigned char* d_scratch = nullptr;
+    unsigned char* d_noalloc = nullptr;   // pcb_decode_batch_dev_noalloc: device address of decode_generic.cu's file-scope scratch array
+    size_t noalloc_bytes = 0;
     // host-buffer pipeline (two slots)
     size_t slot_frames = 0;
     void* d_y[2] = {};
@@ -354,6 +356,8 @@ pcb_handle* pcb_create(int device, int n, int k, int crc, int L, int decoder, in
     const size_t sbytes = h->scratch_per_warp * (size_t)h->sm_count * h->bps * h->wpb;
     if (sbytes && (e = cudaMalloc(&h->d_scratch, sbytes)) != cudaSuccess) return bail("cudaMalloc(scratch)", e);
     if ((e = cudaMalloc(&h->d_counters, 16)) != cudaSuccess) return bail("cudaMalloc", e);
+    // set-up for the no-allocation entry point: the static scratch array's address on THIS device (current since cudaSetDevice above)
+    if ((e = noalloc_scratch_address(&h->d_noalloc, &h->noalloc_bytes)) != cudaSuccess) return bail("cudaGetSymbolAddress(noalloc scratch)", e);
     return h;
 }
 
@@ -786,6 +790,37 @@ int pcb_decode_batch_dev(pcb_handle* h, const void* y_dev, int y_is_f32, uint32_
     CK(cudaEventRecord(h->t1, h->sc));
     CK(cudaStreamSynchronize(h->sc));
     if (ms) CK(cudaEventElapsedTime(ms, h->t0, h->t1));
+    return PCB_OK;
+}
+
+// No-allocation variant of pcb_decode_batch_dev: the generic (reference-literal) kernel with its per-warp LLR scratch
+// in the static device array of decode_generic.cu instead of the handle's cudaMalloc'ed one.  Nothing here allocates:
+// no cudaMalloc / cudaFree, no lazily grown handle buffer (the tuned kernels' redo list, codeword estimates and
+// transposed batch are what pcb_decode_batch_dev grows on demand, so this call does not use them).
+int pcb_decode_batch_dev_noalloc(pcb_handle* h, const void* y_dev, int y_is_f32, uint32_t* sol_bits_dev, int B) {
+    if (!h || !y_dev || !sol_bits_dev) return fail(PCB_EINVAL, "pcb_decode_batch_dev_noalloc: null argument");
+    if (!h->code_set) return fail(PCB_ESTATE, "pcb_decode_batch_dev_noalloc: call pcb_set_code first");
+    if (B <= 0) return B == 0 ? PCB_OK : fail(PCB_EINVAL, "pcb_decode_batch_dev_noalloc: B < 0");
+    if (!h->d_noalloc) return fail(PCB_ESTATE, "pcb_decode_batch_dev_noalloc: the static scratch array has no address on device %d", h->device);
+    if (int r = ensure_device(h)) return r;
+    // one warp decodes one frame at a time and owns scratch_per_warp bytes of the array: as many blocks as fit
+    const size_t per_block = h->scratch_per_warp * (size_t)h->wpb;
+    if (per_block > h->noalloc_bytes)
+        return fail(PCB_EINVAL,
+                    "pcb_decode_batch_dev_noalloc: n = %d, L = %d needs %zu bytes of LLR scratch per block of %d warps, the static "
+                    "array holds %zu (PCB_NOALLOC_SCRATCH_BYTES); use pcb_decode_batch_dev",
+                    h->n, h->L, per_block, h->wpb, h->noalloc_bytes);
+    if (B > PCB_NOALLOC_MAX_FRAMES)
+        return fail(PCB_EINVAL, "pcb_decode_batch_dev_noalloc: B = %d exceeds the limit of %d frames per call", B, PCB_NOALLOC_MAX_FRAMES);
+    int blocks = (B + h->wpb - 1) / h->wpb;
+    const int resident = h->sm_count * h->bps;
+    if (blocks > resident) blocks = resident;
+    if (per_block && (size_t)blocks > h->noalloc_bytes / per_block) blocks = (int)(h->noalloc_bytes / per_block);
+    DecodeArgs a = make_args(h, y_dev, y_is_f32, nullptr, sol_bits_dev, B);
+    a.scratch = h->d_noalloc;
+    CK(launch_decode_generic(a, h->L, h->decoder, h->fp64, blocks, h->wpb, h->sc));
+    h->launches++;
+    CK(cudaStreamSynchronize(h->sc));
     return PCB_OK;
 }
 

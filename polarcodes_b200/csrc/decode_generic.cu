@@ -408,6 +408,35 @@ cudaError_t launch_decode_generic(const DecodeArgs& a, int L, int mode, int fp64
 }
 
 
+// ---- no-allocation variant (pcb_decode_batch_dev_noalloc) --------------------------------------
+// The large LLR layers of this kernel live in a global scratch (DecodeArgs::scratch, one slice per
+// resident warp).  For callers that may not allocate (CUDA graph capture, serving loops), the same
+// kernel runs with its slices in this file-scope array: every GPU that loads the library holds
+// PCB_NOALLOC_SCRATCH_BYTES of it until the process exits.  Nothing in it has to start at zero (every
+// layer is written before it is read within a frame); all calls on a device share it, so two calls
+// that overlap on the GPU race.
+static __device__ __align__(256) unsigned char g_noalloc_scratch[PCB_NOALLOC_SCRATCH_BYTES];
+
+// The array's name is a host-side stand-in in host code: the device address comes from
+// cudaGetSymbolAddress, once per device, with that device current (called from pcb_create).
+cudaError_t noalloc_scratch_address(unsigned char** ptr, size_t* bytes) {
+    static unsigned char* cached[64] = {};
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    if (dev < 0 || dev >= 64) return cudaErrorInvalidDevice;
+    if (!cached[dev]) {
+        unsigned char* p = nullptr;
+        e = cudaGetSymbolAddress((void**)&p, g_noalloc_scratch);
+        if (e != cudaSuccess) return e;
+        cached[dev] = p;
+    }
+    *ptr = cached[dev];
+    if (bytes) *bytes = PCB_NOALLOC_SCRATCH_BYTES;
+    return cudaSuccess;
+}
+
+
 template <typename T, int L, int MODE>
 static cudaError_t occ_one(int wpb, size_t smem, int* bps) {
     cudaError_t e = cudaFuncSetAttribute(decode_generic_kernel<T, L, MODE>,

@@ -67,4 +67,11 @@ cudaError_t launch_scl_select(const SelectArgs& a, int sm_count, cudaStream_t st
 cudaError_t launch_decode_generic(const DecodeArgs& a, int L, int mode, int fp64, int blocks, int wpb,
                                   cudaStream_t st);
 
+// pcb_decode_batch_dev_noalloc: size of the file-scope scratch array of decode_generic.cu and its device
+// address on the current device (cudaGetSymbolAddress, cached per device)
+#ifndef PCB_NOALLOC_SCRATCH_BYTES
+#define PCB_NOALLOC_SCRATCH_BYTES (8u << 20)      // = include/polar_b200.h
+#endif
+cudaError_t noalloc_scratch_address(unsigned char** ptr, size_t* bytes);
+
 }  // namespace pcb
