@@ -39,6 +39,14 @@ bool sc32_is_big(int m);
 size_t sc32_big_scratch_bytes(int n, int blocks, int fp64);
 cudaError_t launch_decode_sc32(const DecodeArgs& a, const uint32_t* info_w, const uint32_t* fv_w, void* yt, void* scratch,
                                uint32_t* tmp_bits, int fp64, int exact, int blocks, int sm_count, cudaStream_t st);
+cudaError_t launch_sc_expand(const uint32_t* bits, int* sol, size_t total, int sm_count, cudaStream_t st);
+// SC decoders, one tile of 32 frames per block with the whole level store on chip and a pruned tree walk (decode_sct.cu)
+bool sct_supported(int m);
+cudaError_t sct_occupancy(int m, int fp64, int exact, int W, int vs, int* bps, size_t* smem, size_t* glob);
+int sct_build_ops(int n, int m, int W, const uint32_t* info_w, const uint32_t* fv_w, uint32_t* ops_out, int cap, uint32_t* pops_out, int pcap,
+                  int* npops);
+cudaError_t launch_decode_sct(const DecodeArgs& a, const uint32_t* d_ops, int nops, const uint32_t* d_pops, int npops, uint32_t* bits, void* glev,
+                              int fp64, int exact, int W, int vs, int blocks, cudaStream_t st);
 // lane-per-path list kernel, 32 / L frames per warp (decode_scl8q.cu): L = 8 and L = 32
 bool scl8q_supported(int m, int L);
 int scl8q_frames_per_warp(int L);
@@ -156,6 +164,11 @@ struct pcb_handle {
     bool quad = false;              // same as fast8 (kept: the launch code reads better with both names)
     bool sc32 = false;              // min-sum SC: lane-per-frame kernel (decode_sc32.cu) instead of the generic one
     int sc32_bps = 0, sc32_smem = 0;
+    bool sct = false;               // SC decoders: tile-per-block kernel (decode_sct.cu) instead of sc32
+    int sct_bps = 0, sct_nops = 0, sct_npops = 0, sct_W = 4, sct_vs = 2;
+    size_t sct_smem = 0, sct_glob = 0;
+    uint32_t* d_sct_ops = nullptr;  // the pruned tree walk of the uploaded frozen pattern (pcb_set_code): warp 0's list, then the other warps'
+    void* d_sct_glev = nullptr;     // levels 2 .. vs-1 (and the heap for n > 2048) of every resident block
     void* d_yt = nullptr;           // sc32: transposed channel values of the batch
     void* d_sc32_scratch = nullptr; // sc32: size-256 level of every resident block (stays in L2)
     uint32_t* d_sc32_bits = nullptr; // sc32: packed decisions when the caller wants one int per bit
@@ -247,6 +260,31 @@ static int configure(pcb_handle* h) {
     h->sc32 = (h->decoder == 2 || h->decoder == 1) && sc32_supported(h->m) && !getenv("PCB_FORCE_GENERIC");
     if (h->sc32 && (sc32_occupancy(h->m, h->fp64, &h->sc32_bps, &h->sc32_smem) != cudaSuccess || h->sc32_bps == 0)) {
         cudaGetLastError(); h->sc32 = false;
+    }
+    h->sct = (h->decoder == 2 || h->decoder == 1) && sct_supported(h->m) && !getenv("PCB_FORCE_GENERIC") && !getenv("PCB_SC_LANE");   // PCB_SC_LANE=1: the lane-per-frame kernel (A/B)
+    if (h->sct && h->m > 11 && !getenv("PCB_T_BIG")) h->sct = false;     // n > 2048: the lane-per-frame kernel streams better (PCB_T_BIG=1: A/B)
+    if (h->sct) {
+        // Launch shape (tools/sct_sweep.py): warps per tile, and the first level kept in shared memory -- the rest of the
+        // level store lives in the block's global slice (L2).  What decides is how many tiles are resident: the leaf walk
+        // of a tile runs on one warp, the other tiles of the SM fill its gaps, so the shared-memory levels are kept to 16 KB.
+        const bool exact = h->decoder == 1;
+        const char* we = getenv("PCB_T_W");
+        const int wv = we ? atoi(we) : 0;
+        h->sct_W = (wv == 1 || wv == 2 || wv == 4 || wv == 8) ? wv
+                   : exact ? 2 : h->n <= 256 ? 1 : h->n == 512 ? 2 : h->fp64 ? 4 : h->n == 1024 ? 2 : 4;
+        if (h->n < 512 && h->sct_W > 4) h->sct_W = 4;
+        const char* ve = getenv("PCB_T_VS");
+        int vs = h->n > 2048 ? 3 : 2;
+        while (vs < h->m - 4 && (size_t)((h->n >> (vs - 1)) - 8) * 32 * h->sizeofT > 16384) vs++;
+        if (ve && atoi(ve) >= (h->n > 2048 ? 3 : 2) && atoi(ve) <= h->m - 4) vs = atoi(ve);
+        int bps = 0;
+        if (sct_occupancy(h->m, h->fp64, exact, h->sct_W, vs, &bps, &h->sct_smem, &h->sct_glob) != cudaSuccess || bps == 0) {
+            cudaGetLastError(); h->sct = false;
+        } else {
+            h->sct_vs = vs; h->sct_bps = bps;
+            const char* be = getenv("PCB_T_BPS");                // experiment: fewer resident tiles per SM
+            if (be && atoi(be) > 0 && atoi(be) < h->sct_bps) h->sct_bps = atoi(be);
+        }
     }
     if (h->sc32) {
         // every resident warp keeps a 64 KB (fp64) / 32 KB (fp32) level buffer that has to stay in L2:
@@ -375,7 +413,7 @@ void pcb_destroy(pcb_handle* h) {
         if (h->ev_out[s]) cudaEventDestroy(h->ev_out[s]);
     }
     cudaFree(h->d_ymc); cudaFree(h->d_tx); cudaFree(h->d_dec); cudaFree(h->d_counters);
-    cudaFree(h->d_eu); cudaFree(h->d_ex); cudaFree(h->d_redo); cudaFree(h->d_qscratch); cudaFree(h->d_synd); cudaFree(h->d_gcrc); cudaFree(h->d_mc_redo); cudaFree(h->d_xhat); cudaFree(h->d_skip); cudaFree(h->d_y32); cudaFree(h->d_yscr); cudaFree(h->d_yt); cudaFree(h->d_sc32_scratch); cudaFree(h->d_sc32_bits);
+    cudaFree(h->d_eu); cudaFree(h->d_ex); cudaFree(h->d_redo); cudaFree(h->d_qscratch); cudaFree(h->d_synd); cudaFree(h->d_gcrc); cudaFree(h->d_mc_redo); cudaFree(h->d_xhat); cudaFree(h->d_skip); cudaFree(h->d_y32); cudaFree(h->d_yscr); cudaFree(h->d_yt); cudaFree(h->d_sc32_scratch); cudaFree(h->d_sc32_bits); cudaFree(h->d_sct_ops); cudaFree(h->d_sct_glev);
     if (h->comm) nccl_api().CommDestroy(h->comm);
     cudaFree(h->d_red);
     cudaFreeHost(h->h_stage[0]); cudaFreeHost(h->h_stage[1]); delete h->narrow;
@@ -409,6 +447,19 @@ int pcb_set_code(pcb_handle* h, const int* frozen_mask, double sigma) {
     CK(cudaMemcpyAsync(h->d_info_pos, pos.data(), (size_t)n * 2, cudaMemcpyHostToDevice, h->sc));
     CK(cudaStreamSynchronize(h->sc));
     h->h_info_w = im; h->h_fv_w = fv;
+    if (h->sct) {
+        // the frozen pattern decides which subtrees need no LLR work at all: compile the pruned tree walk once per code
+        int npops = 0;
+        const int nops = sct_build_ops(n, h->m, h->sct_W, im.data(), fv.data(), nullptr, 0, nullptr, 0, &npops);
+        std::vector<uint32_t> ops((size_t)nops + npops + 1);
+        sct_build_ops(n, h->m, h->sct_W, im.data(), fv.data(), ops.data(), nops, ops.data() + nops, npops, nullptr);
+        if (h->d_sct_ops) { CK(cudaFree(h->d_sct_ops)); h->d_sct_ops = nullptr; }
+        CK(cudaMalloc(&h->d_sct_ops, ops.size() * 4));
+        CK(cudaMemcpyAsync(h->d_sct_ops, ops.data(), ops.size() * 4, cudaMemcpyHostToDevice, h->sc));
+        CK(cudaStreamSynchronize(h->sc));
+        h->sct_npops = npops;
+        h->sct_nops = nops;
+    }
     if (h->decoder == 3 && h->crc > 0 && h->quad) {
         // The final selection (SCLDecoderMinsum.cpp:442-472) keeps the first slot whose CRC passes:
         // crc(sol[0..k)) == the bits sol[k..k+crc), with sol the information positions of
@@ -477,6 +528,14 @@ int pcb_info(pcb_handle* h, int* sm_count, int* warps_per_block, int* blocks, in
              int* first_smem_layer, uint64_t* kernel_launches) {
     if (!h) return fail(PCB_EINVAL, "pcb_info: null handle");
     if (sm_count) *sm_count = h->sm_count;
+    if (h->sct) {
+        if (warps_per_block) *warps_per_block = h->sct_W;
+        if (blocks) *blocks = h->sm_count * h->sct_bps;
+        if (smem_per_block) *smem_per_block = (int)h->sct_smem;
+        if (first_smem_layer) *first_smem_layer = h->sct_vs;
+        if (kernel_launches) *kernel_launches = h->launches;
+        return PCB_OK;
+    }
     const int fw = h->fast8 && h->quad ? scl8q_warps_per_block(h->m, h->L) : 1;
     if (warps_per_block) *warps_per_block = h->fast8 ? fw : h->wpb;
     if (blocks) *blocks = h->fast8 ? fast_blocks(h) / fw : max_blocks(h);
@@ -598,6 +657,37 @@ static cudaError_t launch(pcb_handle* h, const DecodeArgs& a, cudaStream_t st, b
             return cudaErrorInvalidValue;
         }
         if (e != cudaSuccess) return e;
+        f.use_redo_list = 1;
+        h->launches++;
+        return launch_decode_generic(f, h->L, h->decoder, h->fp64, max_blocks(h), h->wpb, st);
+    }
+    if (h->sct) {
+        cudaError_t e = ensure_redo(h, (size_t)a.B);
+        if (e != cudaSuccess) return e;
+        if (!a.sol_bits && h->sc32_bits_cap < (size_t)a.B * (h->n / 32)) {
+            cudaFree(h->d_sc32_bits); h->d_sc32_bits = nullptr; h->sc32_bits_cap = 0;
+            cudaError_t e0 = cudaMalloc(&h->d_sc32_bits, (size_t)a.B * (h->n / 32) * 4);
+            if (e0 != cudaSuccess) return e0;
+            h->sc32_bits_cap = (size_t)a.B * (h->n / 32);
+        }
+        e = cudaMemsetAsync(h->d_redo, 0, 2 * sizeof(int), st);
+        if (e != cudaSuccess) return e;
+        // frames in which an all-information subtree saw a zero (or vanishing) LLR come back on the redo list and are
+        // decoded by the generic kernel right behind (normally an empty launch)
+        DecodeArgs f = a;
+        f.redo_count = h->d_redo; f.redo_list = h->d_redo + 2; f.use_redo_list = 0;
+        uint32_t* bits = a.sol_bits ? a.sol_bits : h->d_sc32_bits;
+        if (h->sct_glob && !h->d_sct_glev) {
+            cudaError_t e0 = cudaMalloc(&h->d_sct_glev, h->sct_glob * (size_t)h->sm_count * h->sct_bps);
+            if (e0 != cudaSuccess) return e0;
+        }
+        e = launch_decode_sct(f, h->d_sct_ops, h->sct_nops, h->d_sct_ops + h->sct_nops, h->sct_npops, bits, h->d_sct_glev, h->fp64, h->decoder == 1,
+                              h->sct_W, h->sct_vs, h->sm_count * h->sct_bps, st);
+        if (e != cudaSuccess) return e;
+        if (a.sol) {
+            e = launch_sc_expand(bits, a.sol, (size_t)a.B * h->n, h->sm_count, st);
+            if (e != cudaSuccess) return e;
+        }
         f.use_redo_list = 1;
         h->launches++;
         return launch_decode_generic(f, h->L, h->decoder, h->fp64, max_blocks(h), h->wpb, st);
@@ -891,7 +981,7 @@ static size_t mc_batch(pcb_handle* h) {
     if (h->sc32 && !env) {
         // lane-per-frame kernels walk the tiles of 32 frames with a static stride: whole waves of
         // the resident grid (one tile per warp and wave), at least one (n = 32768: 42 624 frames)
-        const size_t wave = (size_t)h->sm_count * h->sc32_bps * 32;
+        const size_t wave = (size_t)h->sm_count * (h->sct ? h->sct_bps : h->sc32_bps) * 32;
         b = (b + wave - 1) / wave * wave;
     }
     return b;

@@ -24,6 +24,7 @@
 
 #include "decode_common.cuh"
 #include "decode_launch.h"
+#include "sc_ops.cuh"
 
 #ifndef PCB_S_FE
 #define PCB_S_FE 5       // log2 of the largest stored layer: 32 (6: twice the shared memory per warp, half the fused work)
@@ -61,18 +62,6 @@ struct Args {
     uint32_t fv_w[64];
 };
 
-// f and g of the decoder: min-sum (SCDecoderMinsum.cpp:14-26) or exact (SCDecoder.cpp:19-36, double only)
-template <bool EXACT, typename T>
-__device__ __forceinline__ T opf(T a, T b) {
-    if constexpr (EXACT) return (T)f_exact((double)a, (double)b);
-    else return f_minsum<T>(a, b);
-}
-template <bool EXACT, typename T>
-__device__ __forceinline__ T opg(T a, T b, int c) {
-    if constexpr (EXACT) return (T)g_exact((double)a, (double)b, c);
-    else return g_minsum<T>(a, b, c);
-}
-
 // Element x of level BASE + LEVELS from the 2^LEVELS elements of level BASE it depends on (level v
 // has n >> v elements, level 0 = channel values; element x of level v pairs x and x + (n >> v) of
 // level v - 1, its partial-sum bit sits at heap bit (n >> v) + x).  All loads first (one basic
@@ -108,29 +97,6 @@ __device__ __forceinline__ void fuse(const T* __restrict__ src, const uint32_t* 
             }
         }
         out[o] = v[o][0];
-    }
-}
-
-// SC decoding of a subtree of S leaves held in registers (SCDecoderMinsum.cpp:32-66): returns its
-// partial sums, the decisions in phase order in ub.  ib/fb: information flags / frozen values.
-template <int S, bool EXACT, typename T>
-__device__ __forceinline__ uint32_t sc_node(const T (&a)[S], uint32_t ib, uint32_t fb, uint32_t& ub) {
-    if constexpr (S == 1) {
-        const uint32_t u = (ib & 1u) ? (a[0] > (T)0 ? 0u : 1u) : (fb & 1u);   // :33-47, an LLR of exactly 0 decodes to 1
-        ub = u;
-        return u;
-    } else {
-        constexpr int Hf = S / 2;
-        T l[Hf], r[Hf];
-#pragma unroll
-        for (int j = 0; j < Hf; j++) l[j] = opf<EXACT, T>(a[j], a[j + Hf]);
-        uint32_t uL, uR;
-        const uint32_t pL = sc_node<Hf, EXACT, T>(l, ib, fb, uL);
-#pragma unroll
-        for (int j = 0; j < Hf; j++) r[j] = opg<EXACT, T>(a[j], a[j + Hf], (int)((pL >> j) & 1u));
-        const uint32_t pR = sc_node<Hf, EXACT, T>(r, ib >> Hf, fb >> Hf, uR);
-        ub = uL | (uR << Hf);
-        return (pL ^ pR) | (pR << Hf);
     }
 }
 
@@ -441,6 +407,14 @@ static cudaError_t occ_m(int* bps, int* bytes) {
 }
 
 }  // namespace s32
+
+// packed decisions [B][n/32] -> one int per bit [B][n]
+cudaError_t launch_sc_expand(const uint32_t* bits, int* sol, size_t total, int sm_count, cudaStream_t st) {
+    size_t eb = (total + 255) / 256;
+    if (eb > (size_t)sm_count * 32) eb = (size_t)sm_count * 32;
+    s32::sc32_expand_kernel<<<(unsigned)eb, 256, 0, st>>>(bits, sol, total);
+    return cudaGetLastError();
+}
 
 bool sc32_supported(int m) { return m >= 7 && m <= 16; }
 bool sc32_is_big(int m) { return m > 11; }

@@ -1,0 +1,572 @@
+// SC decoders (SCDecoderMinsum.cpp:14-76 min-sum, SCDecoder.cpp:13-86 exact), one TILE of 32 frames per
+// block: lane = frame as in decode_sc32.cu, but the W warps of a block share the tile and split the rows of
+// a level between them, every level a node needs is STORED (nothing is recomputed), the channel values are
+// read in place (no transposed copy of the batch), and the code tree is pruned.
+//
+//  * Index space: element x of level v (n >> v rows) pairs rows x and x + (n >> v) of level v - 1
+//    (half-split pairing on the bit-reversed channel index).  Rows are [x][lane], so
+//    every access of a warp is one conflict-free row and all arithmetic of a frame stays in its lane.
+//  * Levels 1 and 2 are fused: output x of level 2 needs y[4r .. 4r+3] with r = bitrev(x), 32 contiguous
+//    bytes of the frame's own row (one sector per lane, read straight from the caller's batch, the next
+//    group of loads in flight while the current one is consumed); level 1 is never stored.  The channel
+//    values are read four times per frame (once per level-2 node).
+//  * Levels VS .. m-3 (sizes .. 8) live in shared memory, levels 2 .. VS-1 in a per-block global store that
+//    stays in L2 (VS is chosen so that three tiles fit an SM: while warp 0 of one tile walks its leaves the
+//    other tiles use the SM); a size-8 subtree is decoded in registers; partial sums are bit-packed per lane
+//    (register word + heap, the combine of SCLDecoderMinsum.cpp:287-305).
+//  * Pruning (the frozen pattern is known when the code is set, so the host compiles the tree walk into a
+//    list of ops the block interprets; control is uniform for the whole grid):
+//      - a subtree whose positions are all frozen (values 0) needs no LLR at all: its decisions are the
+//        frozen values, its partial sums are zero, and the f that would feed it is skipped;
+//      - a subtree whose positions are all information bits decodes to the hard decisions of its input
+//        LLRs (partial sums = signs, u = signs F^(x)s): in min-sum arithmetic every g inside adds two
+//        same-signed values and every f takes a min, so no LLR of the subtree can be zero or change the
+//        sign pattern PROVIDED no input is zero and no product of two inputs underflows (|alpha| >= 2^-511;
+//        2^-63 in float).  A frame that violates this anywhere is put on the redo list and decoded again by
+//        the reference-literal generic kernel right behind this one (DecodeArgs::redo_*).
+//    What is left at (1024, 512): 62 % of the f/g updates, 43 of 128 size-8 subtrees.
+//  * Ops on levels with enough rows are executed by all warps (a barrier on either side), the small ones and
+//    the leaf work by warp 0 alone; the other warps read their own list (the shared ops only).
+// Arithmetic is the reference's, operation for operation, in its precision: bit-exact decisions.
+#include <cfloat>
+#include <cstdio>
+#include <cstdlib>
+#include <vector>
+
+#include "decode_common.cuh"
+#include "decode_launch.h"
+#include "sc_ops.cuh"
+
+#ifndef PCB_T_U
+#define PCB_T_U 4          // rows per loop iteration of a level op (loads in flight: 2U, fused 4U)
+#endif
+#ifndef PCB_T_PARMIN
+#define PCB_T_PARMIN 4     // a level op is split between the warps when each gets at least this many rows (a multiple of PCB_T_U)
+#endif
+#ifndef PCB_T_YHINT
+#define PCB_T_YHINT 1      // L2 evict-first hint on the channel-value loads
+#endif
+#ifndef PCB_T_TOPU
+#define PCB_T_TOPU 4       // level-2 outputs per group of the top op (two groups of 4 * TOPU channel values in flight per lane)
+#endif
+
+namespace pcb {
+namespace sct {
+
+enum : uint32_t { OP_TOP2 = 0, OP_LEVEL = 1, OP_NODE8 = 2, OP_RATE0 = 3, OP_RATE1 = 4 };
+// op word: type [0,4) | v [4,9) | isg 9 | fuse 10 | parallel 11 | sync_before 12 | aux [13,32)
+static inline uint32_t mk(uint32_t type, int v, int isg, int fuse, int par, int aux) {
+    return type | ((uint32_t)v << 4) | ((uint32_t)isg << 9) | ((uint32_t)fuse << 10) | ((uint32_t)par << 11) | ((uint32_t)aux << 13);
+}
+
+struct Args {
+    DecodeArgs a;
+    const uint32_t* ops;     // warp 0: every op
+    const uint32_t* pops;    // the other warps: the ops all warps execute
+    int nops, npops;
+    uint32_t* bits;          // [B][n/32] packed decisions
+    int ntiles;
+    int vs;                  // first level in shared memory (2: all of them)
+    void* glev;              // per block: levels 2 .. vs-1, then (n > 2048) the heap
+};
+
+template <typename T>
+struct Tiny;                 // smallest input magnitude for which no product of two LLRs underflows
+template <>
+struct Tiny<double> {
+    static __device__ __forceinline__ bool ok(double a) { return fabs(a) >= 0x1p-511; }    // false for 0 and NaN
+};
+template <>
+struct Tiny<float> {
+    static __device__ __forceinline__ bool ok(float a) { return fabsf(a) >= 0x1p-63f; }
+};
+
+__device__ __forceinline__ uint32_t xform8(uint32_t x) {       // u <-> partial sums of a size-8 node, packed
+    x ^= (x >> 1) & 0x55u; x ^= (x >> 2) & 0x33u; x ^= (x >> 4) & 0x0Fu;
+    return x;
+}
+
+// State of warp 0 (the one that walks the leaves): one frame per lane.
+struct Walk {
+    uint32_t w0, uacc;       // partial sums of sizes < 32 (size S at bits [S, 2S)); decisions of the current 32 phases
+    uint32_t* H;             // this lane's column of the heap: word w at H[w * 32]
+    uint32_t* bits;          // this lane's packed decisions
+    bool store;              // frame < B
+    int M;
+    // one 8-phase block is decided: ub = its decisions in phase order, Tps = its partial sums
+    __device__ __forceinline__ void finish_block(int blk, uint32_t ub, uint32_t Tps) {
+        uacc |= ub << (8 * (blk & 3));
+        if ((blk & 3) == 3) {
+            if (store) bits[blk >> 2] = uacc;
+            uacc = 0;
+        }
+        const int d2 = min(M, 3 + __ffs(blk + 1) - 1);     // SCLDecoderMinsum.cpp:287-305
+        if (d2 == 3) { w0 = (w0 & ~0xFF00u) | (Tps << 8); return; }
+        Tps = (((w0 >> 8) ^ Tps) & 0xFFu) | (Tps << 8);
+        if (d2 == 4) { w0 = (w0 & 0x0000FFFFu) | (Tps << 16); return; }
+        Tps = (((w0 >> 16) ^ Tps) & 0xFFFFu) | (Tps << 16);
+        if (d2 == M) return;                               // the whole codeword: nobody reads it
+        const int D = 1 << d2;
+        H[(2 * D / 32 - 1) * 32] = Tps;
+        grow(32, D);
+    }
+    // the last `w` bits of the size-D array at heap bits [D, 2D) are in place: prepend (left node ^ them) until it is full
+    __device__ __forceinline__ void grow(int w, int D) {
+#pragma unroll 1
+        for (; w < D; w <<= 1) {
+            const int nw = w >> 5;
+#pragma unroll 1
+            for (int kk = 0; kk < nw; kk++)
+                H[((2 * D - 2 * w) / 32 + kk) * 32] = H[(nw + kk) * 32] ^ H[((2 * D - w) / 32 + kk) * 32];
+        }
+    }
+    // an all-frozen node of nblk >= 4 blocks (a multiple of 4, aligned): zero decisions, zero partial sums
+    __device__ __forceinline__ void finish_zero_words(int blk0, int nblk) {
+        if (store) {
+#pragma unroll 1
+            for (int w = 0; w < nblk / 4; w++) bits[(blk0 >> 2) + w] = 0u;
+        }
+        const int last = blk0 + nblk - 1;
+        const int d2 = min(M, 3 + __ffs(last + 1) - 1);
+        if (d2 == M) return;
+        const int D = 1 << d2, Dn = nblk * 8;
+#pragma unroll 1
+        for (int kk = 0; kk < Dn / 32; kk++) H[((2 * D - Dn) / 32 + kk) * 32] = 0u;
+        grow(Dn, D);
+    }
+};
+
+// GL: some levels (and for n > 2048 the heap) live in the block's global store; all pointers are then generic
+template <typename T, bool EXACT, bool GL>
+struct Tile {
+    T* P;                    // lane column of the shared-memory level store
+    T* G;                    // GL: lane column of the global level store
+    uint32_t* H;             // lane column of the heap
+    int n, m, vs;
+    uint32_t wk_w0;          // warp 0: copy of Walk::w0 for the g of levels with fewer than 32 rows (serial ops only)
+    __device__ __forceinline__ T* lev(int v) const {         // level v: n >> v rows
+        if (GL && v < vs) return G + (size_t)((n >> 1) - (n >> (v - 1))) * 32;
+        const int first = GL ? vs : 2;
+        return P + ((n >> (first - 1)) - (n >> (v - 1))) * 32;
+    }
+    __device__ __forceinline__ uint32_t sbit(int pos) const { return (H[(pos >> 5) * 32] << (31 - (pos & 31))) & 0x80000000u; }
+
+    // ---- levels 1 and 2 of node q (G1: level 1 is a g-level, G2: level 2 is), optionally f to level 3 ----
+    // The warp stages 128 bytes of each of its 32 frames per step with cp.async (8 lanes per frame: every global
+    // access is a whole line), two steps in flight, and each lane then reads its own frame's piece: outputs
+    // r .. r + RB - 1 of level 2 in bit-reversed order (rows x = bitrev(r)).
+    static constexpr int STAGE_ROW = 144;                     // 128 bytes + 16: LDS.128 of 32 rows is conflict-free
+    static constexpr int STAGE_BYTES = 2 * 32 * STAGE_ROW;    // per warp
+    template <typename YT, bool G1, bool G2>
+    __device__ __forceinline__ void top2(const YT* __restrict__ ybatch, int tile, int B, bool fuse3, double sigma2, int nw, int wi, int lane,
+                                         unsigned char* stage) const {
+        constexpr int RB = 128 / (4 * (int)sizeof(YT));       // level-2 outputs per step: 4 (double input) or 8 (float)
+        const int R = n >> 2, per = R / nw, r0 = wi * per, sh = 32 - (m - 2), nsteps = per / RB;
+        T* d2 = lev(2);
+        T* d3 = lev(3);
+        const unsigned sbase = (unsigned)__cvta_generic_to_shared(stage);
+#if PCB_T_YHINT
+        // the channel values are streamed (four passes a quarter of a decode apart, far more tiles in flight than L2 holds):
+        // they leave L2 first, the level store of the resident tiles stays
+        uint64_t ypol;
+        asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(ypol));
+#endif
+        auto issue = [&](int c) {
+            const char* src0 = reinterpret_cast<const char*>(ybatch) + (size_t)(r0 + c * RB) * 4 * sizeof(YT) + (lane & 7) * 16;
+            const unsigned dst0 = sbase + (c & 1) * (32 * STAGE_ROW) + (lane & 7) * 16;
+#pragma unroll
+            for (int j = 0; j < 8; j++) {
+                const int f = j * 4 + (lane >> 3);
+                const size_t row = (size_t)min(tile * 32 + f, B - 1) * n * sizeof(YT);
+#if PCB_T_YHINT
+                asm volatile("cp.async.cg.shared.global.L2::cache_hint [%0], [%1], 16, %2;" ::"r"(dst0 + f * STAGE_ROW), "l"(src0 + row), "l"(ypol) : "memory");
+#else
+                asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst0 + f * STAGE_ROW), "l"(src0 + row) : "memory");
+#endif
+            }
+            asm volatile("cp.async.commit_group;" ::: "memory");
+        };
+        issue(0);
+#pragma unroll 1
+        for (int c = 0; c < nsteps; c++) {
+            if (c + 1 < nsteps) {
+                issue(c + 1);
+                asm volatile("cp.async.wait_group 1;" ::: "memory");
+            } else {
+                asm volatile("cp.async.wait_group 0;" ::: "memory");
+            }
+            __syncwarp();
+            const unsigned char* mine = stage + (c & 1) * (32 * STAGE_ROW) + lane * STAGE_ROW;
+            T y[RB][4];
+            if constexpr (sizeof(YT) == 8) {
+#pragma unroll
+                for (int i = 0; i < RB; i++) {
+                    const double2 a = *reinterpret_cast<const double2*>(mine + 32 * i), b = *reinterpret_cast<const double2*>(mine + 32 * i + 16);
+                    y[i][0] = (T)a.x; y[i][1] = (T)a.y; y[i][2] = (T)b.x; y[i][3] = (T)b.y;
+                }
+            } else {
+#pragma unroll
+                for (int i = 0; i < RB; i++) {
+                    const float4 a = *reinterpret_cast<const float4*>(mine + 16 * i);
+                    y[i][0] = (T)a.x; y[i][1] = (T)a.y; y[i][2] = (T)a.z; y[i][3] = (T)a.w;
+                }
+            }
+            if constexpr (EXACT) {                           // SCDecoder.cpp:15-17, :77-79
+#pragma unroll
+                for (int i = 0; i < RB; i++)
+#pragma unroll
+                    for (int t = 0; t < 4; t++) {
+                        double v = (double)y[i][t] * 2. / sigma2;
+                        if (isinf(v)) v = DBL_MAX;
+                        y[i][t] = (T)v;
+                    }
+            }
+            const int r = r0 + c * RB;
+            T o[RB];
+#pragma unroll
+            for (int i = 0; i < RB; i++) {
+                const int x = (int)(__brev((unsigned)(r + i)) >> sh);
+                T la, lb;
+                if constexpr (G1) {
+                    la = s32::opg2<EXACT, T>(y[i][0], y[i][1], sbit((n >> 1) + x));
+                    lb = s32::opg2<EXACT, T>(y[i][2], y[i][3], sbit((n >> 1) + x + (n >> 2)));
+                } else {
+                    la = s32::opf2<EXACT, T>(y[i][0], y[i][1]);
+                    lb = s32::opf2<EXACT, T>(y[i][2], y[i][3]);
+                }
+                if constexpr (G2) o[i] = s32::opg2<EXACT, T>(la, lb, sbit((n >> 2) + x));
+                else o[i] = s32::opf2<EXACT, T>(la, lb);
+                d2[(size_t)x * 32] = o[i];
+            }
+            if (fuse3) {                                     // rows x and x + n/8 of level 2 sit at r and r + 1
+#pragma unroll
+                for (int i = 0; i < RB; i += 2) d3[(size_t)(__brev((unsigned)(r + i)) >> sh) * 32] = s32::opf2<EXACT, T>(o[i], o[i + 1]);
+            }
+            __syncwarp();                                    // this buffer takes step c + 2 next
+        }
+    }
+    template <typename YT>
+    __device__ __forceinline__ void top2q(const YT* __restrict__ ybatch, int tile, int B, int q, bool fuse3, double sigma2, int nw, int wi, int lane,
+                                          unsigned char* stage) const {
+        if (q == 0) top2<YT, false, false>(ybatch, tile, B, fuse3, sigma2, nw, wi, lane, stage);
+        else if (q == 1) top2<YT, false, true>(ybatch, tile, B, fuse3, sigma2, nw, wi, lane, stage);
+        else if (q == 2) top2<YT, true, false>(ybatch, tile, B, fuse3, sigma2, nw, wi, lane, stage);
+        else top2<YT, true, true>(ybatch, tile, B, fuse3, sigma2, nw, wi, lane, stage);
+    }
+
+    // ---- level v (S = n >> v rows) from level v - 1; fuse: level v + 1 = f(level v) in the same pass ----
+    template <bool ISG>
+    __device__ __forceinline__ void level_t(int v, bool fuse, int nw, int wi) const {
+        constexpr int U = PCB_T_U;
+        const int S = n >> v;
+        const T* src = lev(v - 1);
+        T* dst = lev(v);
+        if (fuse) {
+            T* dst2 = lev(v + 1);
+            const int Hs = S >> 1, per = Hs / nw, x0 = wi * per;      // (the host makes per a multiple of U)
+            const T* s0 = src + (size_t)x0 * 32;
+            T* q0 = dst + (size_t)x0 * 32;
+            T* q2 = dst2 + (size_t)x0 * 32;
+            const size_t oS = (size_t)S * 32, oH = (size_t)Hs * 32;
+#pragma unroll 1
+            for (int x = x0; x < x0 + per; x += U, s0 += U * 32, q0 += U * 32, q2 += U * 32) {
+                // (issuing the loads of the next iteration before the arithmetic of this one doubles the registers: 50 instead of 77 M frames/s)
+                T a0[U], b0[U], a1[U], b1[U];
+#pragma unroll
+                for (int i = 0; i < U; i++) {
+                    a0[i] = s0[i * 32]; b0[i] = s0[oS + i * 32];
+                    a1[i] = s0[oH + i * 32]; b1[i] = s0[oH + oS + i * 32];
+                }
+                uint32_t c0 = 0, c1 = 0;                             // the bit of row x + i at bit 32 - U + i
+                if constexpr (ISG) {
+                    if (S >= 32) { c0 = H[((S + x) >> 5) * 32] << (32 - U - (x & 31)); c1 = H[((S + x + Hs) >> 5) * 32] << (32 - U - ((x + Hs) & 31)); }
+                    else { c0 = wk_w0 << (32 - U - (S + x)); c1 = wk_w0 << (32 - U - (S + x + Hs)); }
+                }
+#pragma unroll
+                for (int i = 0; i < U; i++) {
+                    T o0, o1;
+                    if constexpr (ISG) {
+                        o0 = s32::opg2<EXACT, T>(a0[i], b0[i], (c0 << (U - 1 - i)) & 0x80000000u);
+                        o1 = s32::opg2<EXACT, T>(a1[i], b1[i], (c1 << (U - 1 - i)) & 0x80000000u);
+                    } else {
+                        o0 = s32::opf2<EXACT, T>(a0[i], b0[i]);
+                        o1 = s32::opf2<EXACT, T>(a1[i], b1[i]);
+                    }
+                    q0[i * 32] = o0;
+                    q0[oH + i * 32] = o1;
+                    q2[i * 32] = s32::opf2<EXACT, T>(o0, o1);
+                }
+            }
+            return;
+        }
+        const int per = S / nw, x0 = wi * per;
+        const T* s0 = src + (size_t)x0 * 32;
+        T* q0 = dst + (size_t)x0 * 32;
+        const size_t oS = (size_t)S * 32;
+#pragma unroll 1
+        for (int x = x0; x < x0 + per; x += U, s0 += U * 32, q0 += U * 32) {
+            T a[U], b[U];
+#pragma unroll
+            for (int i = 0; i < U; i++) { a[i] = s0[i * 32]; b[i] = s0[oS + i * 32]; }
+            uint32_t c = 0;
+            if constexpr (ISG) c = S >= 32 ? H[((S + x) >> 5) * 32] << (32 - U - (x & 31)) : wk_w0 << (32 - U - (S + x));
+#pragma unroll
+            for (int i = 0; i < U; i++) {
+                if constexpr (ISG) q0[i * 32] = s32::opg2<EXACT, T>(a[i], b[i], (c << (U - 1 - i)) & 0x80000000u);
+                else q0[i * 32] = s32::opf2<EXACT, T>(a[i], b[i]);
+            }
+        }
+    }
+    __device__ __forceinline__ void level(int v, bool isg, bool fuse, int nw, int wi) const {
+        if (isg) level_t<true>(v, fuse, nw, wi);
+        else level_t<false>(v, fuse, nw, wi);
+    }
+};
+
+template <typename T, bool EXACT, int W, bool GL>
+__global__ void __launch_bounds__(32 * W) decode_sct_kernel(const __grid_constant__ Args S) {
+    const DecodeArgs& A = S.a;
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int n = A.n, m = A.m, NW = n >> 5;
+    Tile<T, EXACT, GL> t;
+    t.n = n; t.m = m; t.vs = GL ? S.vs : 2;
+    t.wk_w0 = 0;
+    const int srows = (n >> (t.vs - 1)) - 8;                   // rows of the shared-memory levels
+    t.P = reinterpret_cast<T*>(smem_raw) + lane;
+    t.G = nullptr;
+    t.H = reinterpret_cast<uint32_t*>(reinterpret_cast<T*>(smem_raw) + srows * 32) + lane;
+    // staging area of the top op, one slice per warp, behind the levels and the (shared-memory) heap
+    unsigned char* stage = smem_raw + (size_t)srows * 32 * sizeof(T) + (n > 2048 ? 0 : (size_t)NW * 32 * 4) + (size_t)warp * Tile<T, EXACT, GL>::STAGE_BYTES;
+    if constexpr (GL) {
+        const size_t grows = (size_t)(n >> 1) - (n >> (t.vs - 1));
+        const size_t per_block = grows * 32 * sizeof(T) + (n > 2048 ? (size_t)NW * 32 * 4 : 0);
+        unsigned char* gb = reinterpret_cast<unsigned char*>(S.glev) + (size_t)blockIdx.x * per_block;
+        t.G = reinterpret_cast<T*>(gb) + lane;
+        if (n > 2048) t.H = reinterpret_cast<uint32_t*>(gb + grows * 32 * sizeof(T)) + lane;
+    }
+    const double sigma2 = A.sigma * A.sigma;
+    const uint32_t* ops = warp == 0 ? S.ops : S.pops;
+    const int nops = warp == 0 ? S.nops : S.npops;
+
+    for (int tile = blockIdx.x; tile < S.ntiles; tile += gridDim.x) {
+        const int frame = tile * 32 + lane, fr = min(frame, A.B - 1);
+        Walk wk;
+        wk.w0 = 0; wk.uacc = 0; wk.H = t.H; wk.bits = S.bits + (size_t)fr * NW; wk.store = frame < A.B; wk.M = m;
+        bool bad = false;
+#pragma unroll 1
+        for (int i = 0; i < nops; i++) {
+            const uint32_t op = __ldg(ops + i);
+            const uint32_t type = op & 15u;
+            const int v = (op >> 4) & 31, aux = (int)(op >> 13);
+            const bool isg = (op >> 9) & 1u, fuse = (op >> 10) & 1u, par = (op >> 11) & 1u, syncb = (op >> 12) & 1u;
+            if (type == OP_TOP2) {
+                if (syncb) __syncthreads();
+                if (A.y_f32) t.template top2q<float>(reinterpret_cast<const float*>(A.y), tile, A.B, aux, fuse, sigma2, W, warp, lane, stage);
+                else t.template top2q<double>(reinterpret_cast<const double*>(A.y), tile, A.B, aux, fuse, sigma2, W, warp, lane, stage);
+                __syncthreads();
+            } else if (type == OP_LEVEL) {
+                if (par) {
+                    if (syncb) __syncthreads();
+                    t.level(v, isg, fuse, W, warp);
+                    __syncthreads();
+                } else {                                   // (warp 0 only: the other warps' list has no such op)
+                    t.wk_w0 = wk.w0;
+                    t.level(v, isg, fuse, 1, 0);
+                }
+            } else if (type == OP_NODE8) {
+                T a[8];
+                const T* src = t.lev(m - 3);
+#pragma unroll
+                for (int j = 0; j < 8; ++j) a[j] = src[j * 32];
+                const uint32_t ib = (__ldg(A.info_mask + (aux >> 2)) >> (8 * (aux & 3))) & 0xFFu;
+                const uint32_t fb = (__ldg(A.frozen_val + (aux >> 2)) >> (8 * (aux & 3))) & 0xFFu;
+                uint32_t ub;
+                const uint32_t Tps = s32::sc_node<8, EXACT, T>(a, ib, fb, ub);
+                wk.finish_block(aux, ub, Tps);
+            } else if (type == OP_RATE0) {                 // v = log2 of the number of 8-phase blocks
+                const int nblk = 1 << v;
+                if (nblk >= 4) wk.finish_zero_words(aux, nblk);
+                else {
+#pragma unroll 1
+                    for (int b = 0; b < nblk; b++) wk.finish_block(aux + b, 0u, 0u);
+                }
+            } else {                                       // OP_RATE1: v = log2 of the node size (8, 16 or 32)
+                const int Sz = 1 << v;
+                const T* src = t.lev(m - v);
+                uint32_t beta = 0;
+                bool ok = true;
+#pragma unroll 4
+                for (int j = 0; j < Sz; j++) {
+                    const T al = src[(size_t)j * 32];
+                    ok = ok && Tiny<T>::ok(al);
+                    beta |= (al > (T)0 ? 0u : 1u) << j;
+                }
+                bad = bad || !ok;
+                uint32_t u = beta;                         // u = beta F^(x)v, packed
+                u ^= (u >> 1) & 0x55555555u; u ^= (u >> 2) & 0x33333333u; u ^= (u >> 4) & 0x0F0F0F0Fu;
+                if (Sz >= 16) u ^= (u >> 8) & 0x00FF00FFu;
+                if (Sz >= 32) u ^= (u >> 16) & 0x0000FFFFu;
+#pragma unroll 1
+                for (int b = 0; b < Sz / 8; b++) {
+                    const uint32_t ub = (u >> (8 * b)) & 0xFFu;
+                    wk.finish_block(aux + b, ub, xform8(ub));
+                }
+            }
+        }
+        if (warp == 0 && bad && wk.store && A.redo_count) A.redo_list[atomicAdd(A.redo_count, 1)] = frame;
+        __syncthreads();                                   // the next tile reuses the level store and the heap
+    }
+}
+
+// ---- host: compile the pruned tree walk of a frozen pattern into the op list --------------------------------
+struct Builder {
+    int n, m, W;
+    const uint32_t* info;    // n/32 words, bit set = information position
+    const uint32_t* fv;      // frozen values
+    std::vector<uint32_t> ops, pops;
+    int count(const uint32_t* w, int lo, int S) const {
+        int c = 0;
+        for (int i = lo; i < lo + S; i++) c += (w[i >> 5] >> (i & 31)) & 1u;
+        return c;
+    }
+    bool rate0(int lo, int S) const { return S >= 8 && count(info, lo, S) == 0 && count(fv, lo, S) == 0; }
+    bool rate1(int lo, int S) const { return S >= 8 && S <= 32 && count(info, lo, S) == S; }
+    void node(int lo, int d) {       // a node at depth d >= 2: its input is level d
+        const int S = n >> d;
+        if (rate0(lo, S)) { int lg = 0; while ((8 << lg) < S) lg++; ops.push_back(mk(OP_RATE0, lg, 0, 0, 0, lo / 8)); return; }
+        if (rate1(lo, S)) { int lg = 3; while ((1 << lg) < S) lg++; ops.push_back(mk(OP_RATE1, lg, 0, 0, 0, lo / 8)); return; }
+        if (S == 8) { ops.push_back(mk(OP_NODE8, 0, 0, 0, 0, lo / 8)); return; }
+        const int h = S / 2;
+        if (!rate0(lo, h)) ops.push_back(mk(OP_LEVEL, d + 1, 0, 0, 0, 0));
+        node(lo, d + 1);
+        if (!rate0(lo + h, h)) ops.push_back(mk(OP_LEVEL, d + 1, 1, 0, 0, 0));
+        node(lo + h, d + 1);
+    }
+    void build() {
+        for (int q = 0; q < 4; q++) {
+            const int lo = q * (n / 4);
+            if (!rate0(lo, n / 4)) ops.push_back(mk(OP_TOP2, 2, 0, 0, 1, q));
+            node(lo, 2);
+        }
+        // fuse an op with the f-level that follows it; mark what all warps execute
+        std::vector<uint32_t> out;
+        for (size_t i = 0; i < ops.size(); i++) {
+            uint32_t op = ops[i];
+            const uint32_t type = op & 15u;
+            const int v = (op >> 4) & 31;
+            if ((type == OP_TOP2 || type == OP_LEVEL) && i + 1 < ops.size()) {
+                const uint32_t nx = ops[i + 1];
+                if ((nx & 15u) == OP_LEVEL && (int)((nx >> 4) & 31) == v + 1 && !((nx >> 9) & 1u) && v + 1 <= m - 3) { op |= 1u << 10; i++; }
+            }
+            if (type == OP_LEVEL) {
+                // all warps: the heap must hold the partial sums (S >= 32; warp 0 keeps the smaller ones in a register)
+                // and every warp gets at least one full iteration
+                const int S = n >> v;
+                const bool fuse = (op >> 10) & 1u;
+                if (S >= 32 && (fuse ? S / 2 : S) / W >= PCB_T_PARMIN) op |= 1u << 11;
+            }
+            out.push_back(op);
+        }
+        // a barrier in front of an op all warps execute when warp 0 has worked alone since the last one
+        bool serial_since = true;
+        for (auto& op : out) {
+            const uint32_t type = op & 15u;
+            const bool par = type == OP_TOP2 || (type == OP_LEVEL && ((op >> 11) & 1u));
+            if (par) { if (serial_since) op |= 1u << 12; serial_since = false; pops.push_back(op); }
+            else serial_since = true;
+        }
+        ops.swap(out);
+    }
+};
+
+template <typename T>
+static size_t smem_bytes(int n, int vs, int W) {
+    return (size_t)((n >> (vs - 1)) - 8) * 32 * sizeof(T) + (n > 2048 ? 0 : (size_t)(n >> 5) * 32 * 4) + (size_t)W * (2 * 32 * 144);
+}
+template <typename T>
+static size_t glob_bytes(int n, int vs) {
+    return (size_t)((n >> 1) - (n >> (vs - 1))) * 32 * sizeof(T) + (n > 2048 ? (size_t)(n >> 5) * 32 * 4 : 0);
+}
+
+template <typename T, bool EXACT, int W, bool GL>
+static cudaError_t attr(int n, int vs, int* bps) {
+    const size_t smem = smem_bytes<T>(n, vs, W);
+    cudaError_t e = cudaFuncSetAttribute(decode_sct_kernel<T, EXACT, W, GL>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    return cudaOccupancyMaxActiveBlocksPerMultiprocessor(bps, decode_sct_kernel<T, EXACT, W, GL>, 32 * W, smem);
+}
+template <typename T, bool EXACT, int W, bool GL>
+static cudaError_t go(const Args& s, int blocks, cudaStream_t st) {
+    const size_t smem = smem_bytes<T>(s.a.n, s.vs, W);
+    cudaError_t e = cudaFuncSetAttribute(decode_sct_kernel<T, EXACT, W, GL>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);   // (the occupancy probe tries several sizes)
+    if (e != cudaSuccess) return e;
+    decode_sct_kernel<T, EXACT, W, GL><<<blocks, 32 * W, smem, st>>>(s);
+    return cudaGetLastError();
+}
+
+}  // namespace sct
+
+// W: 1, 2, 4 or 8 warps per tile.  vs: first level in shared memory (2 = all).
+#define PCB_SCT_W(FN, WW, ...)                                                                                            \
+    {                                                                                                                     \
+        if (vs > 2) { if (exact) return sct::FN<double, true, WW, true>(__VA_ARGS__);                                     \
+                      return fp64 ? sct::FN<double, false, WW, true>(__VA_ARGS__) : sct::FN<float, false, WW, true>(__VA_ARGS__); }   \
+        if (exact) return sct::FN<double, true, WW, false>(__VA_ARGS__);                                                   \
+        return fp64 ? sct::FN<double, false, WW, false>(__VA_ARGS__) : sct::FN<float, false, WW, false>(__VA_ARGS__);      \
+    }
+#define PCB_SCT_DISPATCH(FN, ...)                   \
+    if (W == 8) PCB_SCT_W(FN, 8, __VA_ARGS__)       \
+    if (W == 2) PCB_SCT_W(FN, 2, __VA_ARGS__)       \
+    if (W == 1) PCB_SCT_W(FN, 1, __VA_ARGS__)       \
+    PCB_SCT_W(FN, 4, __VA_ARGS__)
+
+bool sct_supported(int m) { return m >= 7 && m <= 16; }
+
+// shared memory per block, global store per block, resident blocks per SM for (n, vs, W)
+cudaError_t sct_occupancy(int m, int fp64, int exact, int W, int vs, int* bps, size_t* smem, size_t* glob) {
+    const int n = 1 << m;
+    *smem = fp64 ? sct::smem_bytes<double>(n, vs, W) : sct::smem_bytes<float>(n, vs, W);
+    *glob = fp64 ? sct::glob_bytes<double>(n, vs) : sct::glob_bytes<float>(n, vs);
+    if (*smem > 227 * 1024) { *bps = 0; return cudaSuccess; }
+    PCB_SCT_DISPATCH(attr, n, vs, bps)
+}
+
+// the two op lists of a frozen pattern (host): every op (warp 0), the ops all warps execute; null pointers to size them
+int sct_build_ops(int n, int m, int W, const uint32_t* info_w, const uint32_t* fv_w, uint32_t* ops_out, int cap, uint32_t* pops_out, int pcap,
+                  int* npops) {
+    sct::Builder b;
+    b.n = n; b.m = m; b.W = W; b.info = info_w; b.fv = fv_w;
+    b.build();
+    if (npops) *npops = (int)b.pops.size();
+    if (ops_out) {
+        if ((int)b.ops.size() > cap) return -1;
+        for (size_t i = 0; i < b.ops.size(); i++) ops_out[i] = b.ops[i];
+    }
+    if (pops_out) {
+        if ((int)b.pops.size() > pcap) return -1;
+        for (size_t i = 0; i < b.pops.size(); i++) pops_out[i] = b.pops[i];
+    }
+    return (int)b.ops.size();
+}
+
+// a: y / y_f32 / B / redo_count + redo_list (device; the count is zeroed by the caller) as for the list kernel;
+// d_ops / d_pops: device copies of the op lists; bits: [B][n/32] packed decisions; glev: blocks * glob bytes
+cudaError_t launch_decode_sct(const DecodeArgs& a, const uint32_t* d_ops, int nops, const uint32_t* d_pops, int npops, uint32_t* bits, void* glev,
+                              int fp64, int exact, int W, int vs, int blocks, cudaStream_t st) {
+    sct::Args s;
+    s.a = a; s.ops = d_ops; s.nops = nops; s.pops = d_pops; s.npops = npops; s.bits = bits; s.ntiles = (a.B + 31) / 32;
+    s.vs = vs; s.glev = glev;
+    if (blocks > s.ntiles) blocks = s.ntiles;
+    static const bool dbg = getenv("PCB_DEBUG_SCT") != nullptr;
+    if (dbg) fprintf(stderr, "sct launch: n %d W %d vs %d blocks %d nops %d npops %d fp64 %d exact %d pending error: %s\n", a.n, W, vs, blocks, nops, npops, fp64, exact,
+                     cudaGetErrorString(cudaPeekAtLastError()));
+    PCB_SCT_DISPATCH(go, s, blocks, st)
+}
+
+}  // namespace pcb
+
+// test hook (not part of include/polar_b200.h): the op list of a frozen pattern, for the host-side emulation in tests/
+extern "C" int pcb_dbg_sct_ops(int n, int m, const uint32_t* info_w, const uint32_t* fv_w, uint32_t* ops_out, int cap) {
+    return pcb::sct_build_ops(n, m, 4, info_w, fv_w, ops_out, cap, nullptr, 0, nullptr);
+}
