@@ -70,16 +70,7 @@ struct Args {
     void* glev;              // per block: levels 2 .. vs-1, then (n > 2048) the heap
 };
 
-template <typename T>
-struct Tiny;                 // smallest input magnitude for which no product of two LLRs underflows
-template <>
-struct Tiny<double> {
-    static __device__ __forceinline__ bool ok(double a) { return fabs(a) >= 0x1p-511; }    // false for 0 and NaN
-};
-template <>
-struct Tiny<float> {
-    static __device__ __forceinline__ bool ok(float a) { return fabsf(a) >= 0x1p-63f; }
-};
+using s32::Tiny;
 
 __device__ __forceinline__ uint32_t xform8(uint32_t x) {       // u <-> partial sums of a size-8 node, packed
     x ^= (x >> 1) & 0x55u; x ^= (x >> 2) & 0x33u; x ^= (x >> 4) & 0x0Fu;
@@ -382,7 +373,7 @@ __global__ void __launch_bounds__(32 * W) decode_sct_kernel(const __grid_constan
                 const uint32_t ib = (__ldg(A.info_mask + (aux >> 2)) >> (8 * (aux & 3))) & 0xFFu;
                 const uint32_t fb = (__ldg(A.frozen_val + (aux >> 2)) >> (8 * (aux & 3))) & 0xFFu;
                 uint32_t ub;
-                const uint32_t Tps = s32::sc_node<8, EXACT, T>(a, ib, fb, ub);
+                const uint32_t Tps = s32::sc_node_p<8, EXACT, T>(a, ib, fb, ub, bad);
                 wk.finish_block(aux, ub, Tps);
             } else if (type == OP_RATE0) {                 // v = log2 of the number of 8-phase blocks
                 const int nblk = 1 << v;
