@@ -38,6 +38,13 @@ extern "C" {
  *            1 = fp32 fast mode for decoder 2 (not bit-exact by contract; FER checked statistically) */
 #define PCB_PREC_STRICT 0
 #define PCB_PREC_FP32 1
+/* 2 = 8-bit min-sum for decoder 2, four LLRs per 32-bit register: the mode the reference sketches and never wires up
+ * (Decodef_char / Decodeg_char, SCDecoderMinsum.cpp:17-30; the scale `2 << qFraction`, SCLDecoderMinsum.cpp:405,
+ * conf.txt:9).  q(y) = clamp(rint(y * (2 << q)), -127, 127), f = Decodef_char, g = Decodeg_char with the sum clamped to
+ * +-127 instead of wrapping.  A mode of its own, with its own FER curve (not bit-exact with the double decoder; bit-exact
+ * with its definition, po_sc8_decode_batch of the CPU restatement under oracle/).  n in [64, 4096].  Pass PCB_PREC_INT8_Q(qFraction). */
+#define PCB_PREC_INT8 2
+#define PCB_PREC_INT8_Q(q) (PCB_PREC_INT8 | ((q) << 8))
 
 typedef struct pcb_handle pcb_handle;
 

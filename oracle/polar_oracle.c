@@ -418,6 +418,73 @@ int po_scl_decode(int n, int L, int k, int crc, const double* y, const int* mask
     return 0;
 }
 
+/* ------------------------------------------------------------------ 8-bit min-sum SC ---
+ * The reference sketches an 8-bit decoder and never wires it up: Decodef_char / Decodeg_char
+ * (SCDecoderMinsum.cpp:17-30) and the quantiser scale `fraction = 2 << qFraction`
+ * (SCLDecoderMinsum.cpp:405, conf.txt:9).  This restatement is the definition of the product's
+ * PCB_PREC_INT8 mode (a mode of its own: NOT bit-exact with the double decoder, reported with its
+ * own FER curve): the tree walk of SCDecoderMinsum.cpp:32-66 on int8 LLRs
+ *   q(y)     = clamp(rint(y * (2 << qFraction)), -127, 127)          (round half to even)
+ *   f(a, b)  = Decodef_char(a, b): min(|a|, |b|), negative iff the sign bits differ
+ *   g(a,b,c) = clamp(b + a * (1 - 2c), -127, 127)   (Decodeg_char is the same sum WITHOUT the clamp: it
+ *              wraps in 8 bits, which no fixed-point decoder can live with; the clamp is this mode's
+ *              one documented deviation from the sketch)
+ *   decision = llr > 0 ? 0 : 1. */
+int po_q8(double y, int qfraction) {
+    double v = rint(y * (double)(2 << qfraction));
+    if (!(v >= -127.)) v = -127.;      /* (NaN -> -127) */
+    if (v > 127.) v = 127.;
+    return (int)v;
+}
+int po_f8(int r1, int r2) {
+    int m1 = r1 > 0 ? r1 : -r1, m2 = r2 > 0 ? r2 : -r2;
+    int mm = m1 < m2 ? m1 : m2;
+    return (((r1 ^ r2) & 0x80) == 0) ? mm : -mm;
+}
+int po_g8(int r1, int r2, int b) {
+    int v = r2 + r1 * (1 - b * 2);
+    return v > 127 ? 127 : v < -127 ? -127 : v;
+}
+static void sc8_node(int size, int depth, int** llr, int** bits, const int* mask, int* sol, int* pos) {
+    int* in = llr[depth];
+    int* out = bits[depth];
+    if (size == 2) {
+        int u1 = mask[*pos] != -1 ? mask[*pos] : (po_f8(in[0], in[1]) > 0 ? 0 : 1);
+        sol[(*pos)++] = u1;
+        int u2 = mask[*pos] != -1 ? mask[*pos] : (po_g8(in[0], in[1], u1) > 0 ? 0 : 1);
+        sol[(*pos)++] = u2;
+        out[0] = u1 ^ u2;
+        out[1] = u2;
+        return;
+    }
+    int* ch = llr[depth + 1];
+    int* cb = bits[depth + 1];
+    for (int i = 0; i < size; i += 2) ch[i / 2] = po_f8(in[i], in[i + 1]);
+    sc8_node(size / 2, depth + 1, llr, bits, mask, sol, pos);
+    for (int i = 0; i < size; i += 2) { out[i] = cb[i / 2]; ch[i / 2] = po_g8(in[i], in[i + 1], out[i]); }
+    sc8_node(size / 2, depth + 1, llr, bits, mask, sol, pos);
+    for (int i = 0; i < size; i += 2) { out[i] ^= cb[i / 2]; out[i + 1] = cb[i / 2]; }
+}
+int po_sc8_decode_batch(int n, int qfraction, const double* y, const int* mask, int* sol, int frames) {
+    int m = 0;
+    while ((1 << m) < n) m++;
+    int** llr = (int**)malloc(sizeof(int*) * (m + 1));
+    int** bits = (int**)malloc(sizeof(int*) * (m + 1));
+    for (int d = 0; d <= m; d++) {
+        int s = (n >> d) > 2 ? (n >> d) : 2;
+        llr[d] = (int*)malloc(sizeof(int) * s);
+        bits[d] = (int*)malloc(sizeof(int) * s);
+    }
+    for (int f = 0; f < frames; f++) {
+        for (int i = 0; i < n; i++) llr[0][i] = po_q8(y[(size_t)f * n + i], qfraction);
+        int pos = 0;
+        sc8_node(n, 0, llr, bits, mask, sol + (size_t)f * n, &pos);
+    }
+    for (int d = 0; d <= m; d++) { free(llr[d]); free(bits[d]); }
+    free(llr); free(bits);
+    return 0;
+}
+
 /* ------------------------------------------------------------------ batch helpers --- */
 
 int po_decode_batch(int decoder, int n, int L, int k, int crc, double sigma, const double* y,

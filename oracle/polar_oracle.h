@@ -33,6 +33,11 @@ int po_scl_decode(int n, int L, int k, int crc, const double* y, const int* mask
 /* batch helpers: decoder 1 SC, 2 SCMinsum, 3 SCLMinsum; sol stride = n (1,2) or k+crc (3) */
 int po_decode_batch(int decoder, int n, int L, int k, int crc, double sigma, const double* y,
                     const int* mask, int* sol, int frames);
+/* 8-bit min-sum SC (the product's PCB_PREC_INT8 mode; see polar_oracle.c) */
+int po_q8(double y, int qfraction);
+int po_f8(int r1, int r2);
+int po_g8(int r1, int r2, int b);
+int po_sc8_decode_batch(int n, int qfraction, const double* y, const int* mask, int* sol, int frames);
 double po_time_decode(int decoder, int n, int L, int k, int crc, double sigma, const double* y,
                       const int* mask, int frames, int reps);
 

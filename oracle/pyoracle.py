@@ -133,6 +133,14 @@ class Oracle(_Base):
         assert rc == 0
         return sol
 
+    def decode_int8(self, n, qfraction, y, mask):
+        """8-bit min-sum SC (polar_oracle.c: the definition of the product's PCB_PREC_INT8 mode) -> [B][n] decisions."""
+        y = _f64(y).reshape(-1, n)
+        sol = np.zeros((y.shape[0], n), np.int32)
+        self.lib.po_sc8_decode_batch.argtypes = [C.c_int, C.c_int, _dp, _ip, _ip, C.c_int]
+        assert self.lib.po_sc8_decode_batch(n, qfraction, y, _i32(mask), sol, y.shape[0]) == 0
+        return sol
+
     def time_decode(self, decoder, n, L, k, crc, sigma, y, mask, reps=1):
         y = _f64(y).reshape(-1, n)
         return self.lib.po_time_decode(decoder, n, L, k, crc, sigma, y, _i32(mask), y.shape[0], reps)

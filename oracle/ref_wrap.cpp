@@ -220,4 +220,7 @@ int ref_fer_point(int n, int k, int crc, int L, int decoder, int zcomputer, doub
     return er;
 }
 
+// the reference's 8-bit sketches (SCDecoderMinsum.cpp:17-30), never called by its own decoders
+int ref_decodef_char(int r1, int r2) { return (int)SCDecoderMinsum::Decodef_char((char)r1, (char)r2); }
+int ref_decodeg_char(int r1, int r2, int b) { return (int)(signed char)SCDecoderMinsum::Decodeg_char((char)r1, (char)r2, b); }
 }  // extern "C"

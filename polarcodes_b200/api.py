@@ -16,7 +16,12 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("PCB_LIB_PATH") or os.path.join(HERE, "libpolar_b200.so")
 
 SC, SCMINSUM, SCLMINSUM = 1, 2, 3
-STRICT, FP32 = 0, 1
+STRICT, FP32, INT8 = 0, 1, 2
+
+
+def int8_q(qfraction):
+    """precision argument of the 8-bit min-sum mode with the scale 2 << qfraction (PCB_PREC_INT8_Q)."""
+    return INT8 | (int(qfraction) << 8)
 
 _ip = np.ctypeslib.ndpointer(dtype=np.int32, flags="C_CONTIGUOUS")
 _dp = np.ctypeslib.ndpointer(dtype=np.float64, flags="C_CONTIGUOUS")

@@ -17,7 +17,7 @@ ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
 # -fmad=false: no mul+add contraction anywhere on the decode path (bit-exact LLR arithmetic);
 # no --use_fast_math, denormals kept (ftz off is the default).
 NVCC_FLAGS = ["-O3", "-std=c++17", "-lineinfo", "-fmad=false", "-Xcompiler", "-fPIC", "-Xcompiler", "-ffp-contract=off"]
-CUDA_SOURCES = ["decode_generic.cu", "decode_scl8q.cu", "scl_select.cu", "decode_sc32.cu", "decode_sct.cu", "aux_kernels.cu", "capi.cu"]
+CUDA_SOURCES = ["decode_generic.cu", "decode_scl8q.cu", "scl_select.cu", "decode_sc32.cu", "decode_sct.cu", "decode_sc8.cu", "aux_kernels.cu", "capi.cu"]
 CXX_SOURCES = ["construct.cpp"]
 
 

@@ -47,6 +47,14 @@ int sct_build_ops(int n, int m, int W, const uint32_t* info_w, const uint32_t* f
                   int* npops);
 cudaError_t launch_decode_sct(const DecodeArgs& a, const uint32_t* d_ops, int nops, const uint32_t* d_pops, int npops, uint32_t* bits, void* glev,
                               int fp64, int exact, int W, int vs, int blocks, cudaStream_t st);
+// 8-bit min-sum SC, four LLRs per register (decode_sc8.cu; PCB_PREC_INT8)
+bool sc8_supported(int m);
+size_t sc8_yq_bytes(int n, int B);
+cudaError_t sc8_occupancy(int m, int* bps, size_t* smem);
+int sc8_build_ops(int n, int m, const uint32_t* info_w, const uint32_t* fv_w, uint32_t* ops_out, int cap);
+size_t sc8_glev_bytes(int n, int blocks);
+cudaError_t launch_decode_sc8(const DecodeArgs& a, int qfraction, const uint32_t* d_ops, int nops, uint32_t* yq, uint32_t* glev, uint32_t* bits, int blocks,
+                              int sm_count, cudaStream_t st);
 // lane-per-path list kernel, 32 / L frames per warp (decode_scl8q.cu): L = 8 and L = 32
 bool scl8q_supported(int m, int L);
 int scl8q_frames_per_warp(int L);
@@ -164,6 +172,10 @@ struct pcb_handle {
     bool quad = false;              // same as fast8 (kept: the launch code reads better with both names)
     bool sc32 = false;              // min-sum SC: lane-per-frame kernel (decode_sc32.cu) instead of the generic one
     int sc32_bps = 0, sc32_smem = 0;
+    bool sc8 = false;               // decoder 2 in PCB_PREC_INT8: decode_sc8.cu
+    int qfrac = 0, sc8_bps = 0, sc8_nops = 0;
+    size_t sc8_smem = 0, yq_cap = 0;
+    uint32_t *d_sc8_ops = nullptr, *d_yq = nullptr, *d_sc8_glev = nullptr;
     bool sct = false;               // SC decoders: tile-per-block kernel (decode_sct.cu) instead of sc32
     int sct_bps = 0, sct_nops = 0, sct_npops = 0, sct_W = 4, sct_vs = 2;
     size_t sct_smem = 0, sct_glob = 0;
@@ -257,11 +269,20 @@ static int configure(pcb_handle* h) {
             h->f_bps = bps; h->f_warp_smem = wb; h->quad = true;
         }
     }
-    h->sc32 = (h->decoder == 2 || h->decoder == 1) && sc32_supported(h->m) && !getenv("PCB_FORCE_GENERIC");
+    h->sc8 = h->decoder == 2 && h->precision == PCB_PREC_INT8;
+    if (h->sc8) {
+        if (!sc8_supported(h->m) || sc8_occupancy(h->m, &h->sc8_bps, &h->sc8_smem) != cudaSuccess || h->sc8_bps == 0) {
+            cudaGetLastError();
+            return fail(PCB_EINVAL, "PCB_PREC_INT8 needs n in [64, 4096]");
+        }
+        const char* be = getenv("PCB_8_BPS");
+        if (be && atoi(be) > 0 && atoi(be) < h->sc8_bps) h->sc8_bps = atoi(be);
+    }
+    h->sc32 = !h->sc8 && (h->decoder == 2 || h->decoder == 1) && sc32_supported(h->m) && !getenv("PCB_FORCE_GENERIC");
     if (h->sc32 && (sc32_occupancy(h->m, h->fp64, &h->sc32_bps, &h->sc32_smem) != cudaSuccess || h->sc32_bps == 0)) {
         cudaGetLastError(); h->sc32 = false;
     }
-    h->sct = (h->decoder == 2 || h->decoder == 1) && sct_supported(h->m) && !getenv("PCB_FORCE_GENERIC") && !getenv("PCB_SC_LANE");   // PCB_SC_LANE=1: the lane-per-frame kernel (A/B)
+    h->sct = !h->sc8 && (h->decoder == 2 || h->decoder == 1) && sct_supported(h->m) && !getenv("PCB_FORCE_GENERIC") && !getenv("PCB_SC_LANE");   // PCB_SC_LANE=1: the lane-per-frame kernel (A/B)
     if (h->sct && h->m > 11 && !getenv("PCB_T_BIG")) h->sct = false;     // n > 2048: the lane-per-frame kernel streams better (PCB_T_BIG=1: A/B)
     if (h->sct) {
         // Launch shape (tools/sct_sweep.py): warps per tile, and the first level kept in shared memory -- the rest of the
@@ -340,6 +361,10 @@ pcb_handle* pcb_create(int device, int n, int k, int crc, int L, int decoder, in
     while ((1 << m) < n) m++;
     if (n < 2 || n > 65536 || (1 << m) != n) { fail(PCB_EINVAL, "n must be a power of two in [2, 65536]"); return nullptr; }
     if (decoder < 1 || decoder > 3) { fail(PCB_EINVAL, "decoder must be 1 (SC), 2 (SCMinsum) or 3 (SCLMinsum)"); return nullptr; }
+    if ((precision & 0xFF) > PCB_PREC_INT8 || precision < 0 || ((precision & 0xFF) == PCB_PREC_INT8 && decoder != 2)) {
+        fail(PCB_EINVAL, "precision must be PCB_PREC_STRICT, PCB_PREC_FP32 or (decoder 2 only) PCB_PREC_INT8_Q(q)");
+        return nullptr;
+    }
     if (decoder != 3) L = 1;   // the CRC still matters to decoders 1, 2: the loop appends it for every decoder (PolarCodes.cpp:136-155)
     if (L < 1 || L > 32 || (L & (L - 1))) { fail(PCB_EINVAL, "L must be a power of two in [1, 32]"); return nullptr; }
     if (crc != 0 && crc != 8 && crc != 16) { fail(PCB_EINVAL, "crc must be 0, 8 or 16"); return nullptr; }
@@ -358,8 +383,9 @@ pcb_handle* pcb_create(int device, int n, int k, int crc, int L, int decoder, in
     if (device < 0 || device >= cnt) { fail(PCB_EINVAL, "device %d out of range (%d devices)", device, cnt); return nullptr; }
     pcb_handle* h = new pcb_handle();
     h->device = device; h->n = n; h->m = m; h->k = k; h->crc = crc; h->L = L; h->decoder = decoder;
-    h->precision = precision;
-    h->fp64 = (decoder == 1) || (decoder == 2 && precision == PCB_PREC_STRICT);
+    h->precision = precision & 0xFF;
+    h->qfrac = (precision >> 8) & 0xF;
+    h->fp64 = (decoder == 1) || (decoder == 2 && h->precision == PCB_PREC_STRICT);
     h->sizeofT = h->fp64 ? 8 : 4;
     h->stride = decoder == 3 ? k + crc : n;
     h->EW = (h->stride + 31) / 32;
@@ -413,7 +439,7 @@ void pcb_destroy(pcb_handle* h) {
         if (h->ev_out[s]) cudaEventDestroy(h->ev_out[s]);
     }
     cudaFree(h->d_ymc); cudaFree(h->d_tx); cudaFree(h->d_dec); cudaFree(h->d_counters);
-    cudaFree(h->d_eu); cudaFree(h->d_ex); cudaFree(h->d_redo); cudaFree(h->d_qscratch); cudaFree(h->d_synd); cudaFree(h->d_gcrc); cudaFree(h->d_mc_redo); cudaFree(h->d_xhat); cudaFree(h->d_skip); cudaFree(h->d_y32); cudaFree(h->d_yscr); cudaFree(h->d_yt); cudaFree(h->d_sc32_scratch); cudaFree(h->d_sc32_bits); cudaFree(h->d_sct_ops); cudaFree(h->d_sct_glev);
+    cudaFree(h->d_eu); cudaFree(h->d_ex); cudaFree(h->d_redo); cudaFree(h->d_qscratch); cudaFree(h->d_synd); cudaFree(h->d_gcrc); cudaFree(h->d_mc_redo); cudaFree(h->d_xhat); cudaFree(h->d_skip); cudaFree(h->d_y32); cudaFree(h->d_yscr); cudaFree(h->d_yt); cudaFree(h->d_sc32_scratch); cudaFree(h->d_sc32_bits); cudaFree(h->d_sct_ops); cudaFree(h->d_sct_glev); cudaFree(h->d_sc8_ops); cudaFree(h->d_yq); cudaFree(h->d_sc8_glev);
     if (h->comm) nccl_api().CommDestroy(h->comm);
     cudaFree(h->d_red);
     cudaFreeHost(h->h_stage[0]); cudaFreeHost(h->h_stage[1]); delete h->narrow;
@@ -447,6 +473,16 @@ int pcb_set_code(pcb_handle* h, const int* frozen_mask, double sigma) {
     CK(cudaMemcpyAsync(h->d_info_pos, pos.data(), (size_t)n * 2, cudaMemcpyHostToDevice, h->sc));
     CK(cudaStreamSynchronize(h->sc));
     h->h_info_w = im; h->h_fv_w = fv;
+    if (h->sc8) {
+        const int nops = sc8_build_ops(n, h->m, im.data(), fv.data(), nullptr, 0);
+        std::vector<uint32_t> ops((size_t)nops + 1);
+        sc8_build_ops(n, h->m, im.data(), fv.data(), ops.data(), nops);
+        if (h->d_sc8_ops) { CK(cudaFree(h->d_sc8_ops)); h->d_sc8_ops = nullptr; }
+        CK(cudaMalloc(&h->d_sc8_ops, ops.size() * 4));
+        CK(cudaMemcpyAsync(h->d_sc8_ops, ops.data(), ops.size() * 4, cudaMemcpyHostToDevice, h->sc));
+        CK(cudaStreamSynchronize(h->sc));
+        h->sc8_nops = nops;
+    }
     if (h->sct) {
         // the frozen pattern decides which subtrees need no LLR work at all: compile the pruned tree walk once per code
         int npops = 0;
@@ -528,6 +564,14 @@ int pcb_info(pcb_handle* h, int* sm_count, int* warps_per_block, int* blocks, in
              int* first_smem_layer, uint64_t* kernel_launches) {
     if (!h) return fail(PCB_EINVAL, "pcb_info: null handle");
     if (sm_count) *sm_count = h->sm_count;
+    if (h->sc8) {
+        if (warps_per_block) *warps_per_block = 1;
+        if (blocks) *blocks = h->sm_count * h->sc8_bps;
+        if (smem_per_block) *smem_per_block = (int)h->sc8_smem;
+        if (first_smem_layer) *first_smem_layer = 1;
+        if (kernel_launches) *kernel_launches = h->launches;
+        return PCB_OK;
+    }
     if (h->sct) {
         if (warps_per_block) *warps_per_block = h->sct_W;
         if (blocks) *blocks = h->sm_count * h->sct_bps;
@@ -661,6 +705,31 @@ static cudaError_t launch(pcb_handle* h, const DecodeArgs& a, cudaStream_t st, b
         h->launches++;
         return launch_decode_generic(f, h->L, h->decoder, h->fp64, max_blocks(h), h->wpb, st);
     }
+    if (h->sc8) {
+        const size_t need = sc8_yq_bytes(h->n, a.B);
+        if (h->yq_cap < need) {
+            cudaFree(h->d_yq); h->d_yq = nullptr; h->yq_cap = 0;
+            cudaError_t e0 = cudaMalloc(&h->d_yq, need);
+            if (e0 != cudaSuccess) return e0;
+            h->yq_cap = need;
+        }
+        if (!a.sol_bits && h->sc32_bits_cap < (size_t)a.B * (h->n / 32)) {
+            cudaFree(h->d_sc32_bits); h->d_sc32_bits = nullptr; h->sc32_bits_cap = 0;
+            cudaError_t e0 = cudaMalloc(&h->d_sc32_bits, (size_t)a.B * (h->n / 32) * 4);
+            if (e0 != cudaSuccess) return e0;
+            h->sc32_bits_cap = (size_t)a.B * (h->n / 32);
+        }
+        uint32_t* bits = a.sol_bits ? a.sol_bits : h->d_sc32_bits;
+        h->launches++;                        // quantiser + decoder
+        if (!h->d_sc8_glev) {
+            cudaError_t e0 = cudaMalloc(&h->d_sc8_glev, sc8_glev_bytes(h->n, h->sm_count * h->sc8_bps));
+            if (e0 != cudaSuccess) return e0;
+        }
+        cudaError_t e = launch_decode_sc8(a, h->qfrac, h->d_sc8_ops, h->sc8_nops, h->d_yq, h->d_sc8_glev, bits, h->sm_count * h->sc8_bps, h->sm_count, st);
+        if (e != cudaSuccess) return e;
+        if (a.sol) return launch_sc_expand(bits, a.sol, (size_t)a.B * h->n, h->sm_count, st);
+        return cudaSuccess;
+    }
     if (h->sct) {
         cudaError_t e = ensure_redo(h, (size_t)a.B);
         if (e != cudaSuccess) return e;
@@ -755,7 +824,7 @@ static int decode_host(pcb_handle* h, const void* y, int y_f32, int* sol, uint32
     if (chunk > (size_t)B) chunk = (size_t)B;
     if (int r = ensure_slots(h, chunk, ybpf)) return r;
     // float decoders fed with doubles: narrow on the host cores, copy 4 bytes per value
-    const bool narrow = !y_f32 && !h->fp64 && !getenv("PCB_NO_HOST_NARROW");
+    const bool narrow = !y_f32 && !h->fp64 && !h->sc8 && !getenv("PCB_NO_HOST_NARROW");   // (the 8-bit mode quantises the doubles themselves)
     const bool mixed = narrow && h->fast8 && h->quad && !getenv("PCB_NO_MIXED_INPUT");
     const double* mix_tail = nullptr;
     int mix_nf = 0;
@@ -978,7 +1047,7 @@ static size_t mc_batch(pcb_handle* h) {
     if (env) b = (size_t)atol(env);
     const size_t minb = h->fast8 ? (size_t)fast_blocks(h) * (h->quad ? scl8q_frames_per_warp(h->L) : 1) : (size_t)max_blocks(h) * h->wpb;
     if (b < minb) b = minb;
-    if (h->sc32 && !env) {
+    if ((h->sc32 || h->sct) && !env) {
         // lane-per-frame kernels walk the tiles of 32 frames with a static stride: whole waves of
         // the resident grid (one tile per warp and wave), at least one (n = 32768: 42 624 frames)
         const size_t wave = (size_t)h->sm_count * (h->sct ? h->sct_bps : h->sc32_bps) * 32;

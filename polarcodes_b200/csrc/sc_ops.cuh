@@ -41,6 +41,15 @@ __device__ __forceinline__ double g_sign(double a, double b, uint32_t signbit) {
     return b + __hiloint2double(__double2hiint(a) ^ (int)signbit, __double2loint(a));
 }
 __device__ __forceinline__ float g_sign(float a, float b, uint32_t signbit) { return b + __uint_as_float(__float_as_uint(a) ^ signbit); }
+// 8-bit min-sum (decode_sc8.cu; the reference's sketch SCDecoderMinsum.cpp:17-30, g saturating): values in [-127, 127]
+__device__ __forceinline__ int f_minsum_fast(int a, int b) {
+    const int mm = min(abs(a), abs(b));
+    return ((a ^ b) < 0) ? -mm : mm;
+}
+__device__ __forceinline__ int g_sign(int a, int b, uint32_t signbit) {
+    const int v = b + (signbit ? -a : a);
+    return max(-127, min(127, v));
+}
 template <bool EXACT, typename T>
 __device__ __forceinline__ T opf2(T a, T b) {
     if constexpr (EXACT) return (T)f_exact((double)a, (double)b);
@@ -89,7 +98,11 @@ struct Tiny<float> {
 // tests are uniform branches): an all-frozen (zeros) subtree costs nothing, an all-information subtree is the hard
 // decisions of its inputs -- exact unless an input is zero or tiny, which sets `bad` (the frame is decoded again
 // by the generic kernel).
-template <int S, bool EXACT, typename T>
+template <>
+struct Tiny<int> {
+    static __device__ __forceinline__ bool ok(int a) { return a != 0; }
+};
+template <int S, bool EXACT, typename T, bool R1 = true>
 __device__ __forceinline__ uint32_t sc_node_p(const T (&a)[S], uint32_t ib, uint32_t fb, uint32_t& ub, bool& bad) {
     if constexpr (S == 1) {
         const uint32_t u = (ib & 1u) ? (a[0] > (T)0 ? 0u : 1u) : (fb & 1u);
@@ -98,7 +111,7 @@ __device__ __forceinline__ uint32_t sc_node_p(const T (&a)[S], uint32_t ib, uint
     } else {
         constexpr uint32_t ALL = (1u << S) - 1;
         if (((ib | fb) & ALL) == 0u) { ub = 0u; return 0u; }
-        if ((ib & ALL) == ALL) {
+        if (R1 && (ib & ALL) == ALL) {
             uint32_t beta = 0;
             bool ok = true;
 #pragma unroll
@@ -121,11 +134,11 @@ __device__ __forceinline__ uint32_t sc_node_p(const T (&a)[S], uint32_t ib, uint
         if (((ib | fb) & HALF) != 0u) {
 #pragma unroll
             for (int j = 0; j < Hf; j++) l[j] = opf2<EXACT, T>(a[j], a[j + Hf]);
-            pL = sc_node_p<Hf, EXACT, T>(l, ib, fb, uL, bad);
+            pL = sc_node_p<Hf, EXACT, T, R1>(l, ib, fb, uL, bad);
         }
 #pragma unroll
         for (int j = 0; j < Hf; j++) r[j] = opg2<EXACT, T>(a[j], a[j + Hf], (pL << (31 - j)) & 0x80000000u);
-        const uint32_t pR = sc_node_p<Hf, EXACT, T>(r, ib >> Hf, fb >> Hf, uR, bad);
+        const uint32_t pR = sc_node_p<Hf, EXACT, T, R1>(r, ib >> Hf, fb >> Hf, uR, bad);
         ub = uL | (uR << Hf);
         return (pL ^ pR) | (pR << Hf);
     }

@@ -12,6 +12,7 @@ import polarcodes_b200 as pb
 CONFIGS = [
     ("A  SCMinsum 1024/512 fp64", 1024, 512, pb.SCMINSUM, pb.STRICT, 1 << 18),
     ("A' SCMinsum 1024/512 fp32", 1024, 512, pb.SCMINSUM, pb.FP32, 1 << 18),
+    ("A8 SCMinsum 1024/512 int8 q2", 1024, 512, pb.SCMINSUM, pb.int8_q(2), 1 << 18),
     ("B  SC exact 256/128", 256, 128, pb.SC, pb.STRICT, 1 << 18),
     ("   SCMinsum 256/128 fp64", 256, 128, pb.SCMINSUM, pb.STRICT, 1 << 18),
     ("   SCMinsum 512/256 fp64", 512, 256, pb.SCMINSUM, pb.STRICT, 1 << 18),
@@ -29,7 +30,8 @@ for name, N, K, dec, prec, B in CONFIGS:
     B = max(32, int(B * SCALE)) + 5            # a ragged last tile
     code = pb.Code(N, K, 0, 2.0)
     res = {}
-    for variant in ("tile", "lane"):
+    int8 = prec not in (pb.STRICT, pb.FP32)
+    for variant in ("tile",) if int8 else ("tile", "lane"):
         if variant == "lane":
             os.environ["PCB_SC_LANE"] = "1"
         try:
@@ -45,6 +47,8 @@ for name, N, K, dec, prec, B in CONFIGS:
         ms = [d.decode_dev(y.data_ptr(), f32, out.data_ptr(), B) for _ in range(4)]
         res[variant] = (B / (min(ms) * 1e-3) / 1e6, out.clone(), d.info())
         del d
+    if int8:
+        res["lane"] = (0.0, res["tile"][1], None)
     diff = (res["tile"][1] != res["lane"][1]).any(dim=1).sum().item()
     i = res["tile"][2]
     print(f"{name:30s} tile {res['tile'][0]:8.2f}  lane {res['lane'][0]:8.2f} Mframes/s   frames that differ: {diff} of {B}   "
