@@ -201,6 +201,7 @@ def sweep_configs(pb, torch, dev, peaks, traffic):
     cfgs = [  # key, label, decoder, n, k, crc, L, precision, double input, frames
         ("A", "SCDecoderMinsum N=1024 K=512 fp64 (double y)", pb.SCMINSUM, 1024, 512, 0, 1, pb.STRICT, True, 1 << 20),
         ("A_fp32", "SCDecoderMinsum N=1024 K=512 fp32 fast mode (float y; not bit-exact by contract)", pb.SCMINSUM, 1024, 512, 0, 1, pb.FP32, False, 1 << 20),
+        ("A_int8", "SCDecoderMinsum N=1024 K=512 8-bit mode, qFraction 2 (double y; a mode of its own: FER in profiles/r2_int8_fer.txt)", pb.SCMINSUM, 1024, 512, 0, 1, pb.int8_q(2), True, 1 << 20),
         ("B", "exact SCDecoder N=256 K=128 fp64 (double y)", pb.SC, 256, 128, 0, 1, pb.STRICT, True, 1 << 20),
         ("C_crc16", "SCLDecoderMinsum L=8 N=1024 K=512 crc=16 (double y)", pb.SCLMINSUM, 1024, 512, 16, 8, pb.STRICT, True, 1 << 20),
         ("conf_txt", "SCLDecoderMinsum L=4 N=2048 K=1024 crc=16 (the reference's shipped conf.txt; double y)", pb.SCLMINSUM, 2048, 1024, 16, 4, pb.STRICT, True, 1 << 18),
@@ -246,6 +247,26 @@ def sweep_configs(pb, torch, dev, peaks, traffic):
         dec.close()
         del y, tx, sol
     torch.cuda.empty_cache()
+    return out
+
+
+def encode_leg(pb, torch, dev, peaks):
+    """Encoder.cpp:57-83 on packed device-resident frames (pcb_encode_batch_dev): frames/s and the HBM fraction (n / 4 bytes per frame)."""
+    out = []
+    for key, n, shuffle, B in (("N=1024 natural order (decoder 3)", 1024, 0, 1 << 22), ("N=1024 with ReverseShuffle (decoders 1, 2)", 1024, 1, 1 << 22),
+                               ("N=32768 with ReverseShuffle", 32768, 1, 1 << 17)):
+        dec = pb.Decoder(n, n // 2, 0, 1, pb.SCMINSUM, device=dev.index)
+        u = torch.randint(-2 ** 31, 2 ** 31 - 1, (B, n // 32), dtype=torch.int32, device=dev)
+        x = torch.empty_like(u)
+        for _ in range(2):
+            dec.encode_dev(u.data_ptr(), x.data_ptr(), shuffle, B)
+        ms = float(np.mean([dec.encode_dev(u.data_ptr(), x.data_ptr(), shuffle, B) for _ in range(10)]))
+        fps = B / (ms * 1e-3)
+        gbs = fps * (n / 4) / 1e9
+        out.append({"workload": key, "frames_per_launch": B, "kernel_ms": ms, "frames_per_s": fps, "coded_gbit_per_s": fps * n / 1e9,
+                    "algorithmic_bytes_per_frame": n // 4, "hbm_GBps": gbs, "hbm_frac": gbs / peaks["hbm_gbs"] if peaks.get("hbm_gbs") else None})
+        dec.close()
+        del u, x
     return out
 
 
@@ -484,6 +505,7 @@ def main():
         if world == 1 and not args.no_extras:
             line["configs"] = sweep_configs(pb, torch, dev, peaks, traffic_all)
             line["montecarlo"] = montecarlo_leg(pb, dev)
+            line["encode"] = encode_leg(pb, torch, dev, peaks)
         if not args.no_cpu and world == 1:
             cores = os.cpu_count() or 1
             sample = int(cores * 1300 * 12)

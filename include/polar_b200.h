@@ -97,6 +97,12 @@ int pcb_set_code(pcb_handle* h, const int* frozen_mask, double sigma);
  * with_shuffle != 0: x = bitrev(u) F^(x)m (used with decoders 1,2); 0: x = u F^(x)m (decoder 3). */
 int pcb_encode_batch(pcb_handle* h, const int* u, int* x, int with_shuffle, int B);
 
+/* The same on packed frames (the throughput path: n / 4 bytes per frame over the link or HBM instead of 8 n):
+ * u_bits[B][words] -> x_bits[B][words], words = max(n / 32, 1), bit t of a frame at word t / 32, bit t % 32.
+ * _packed: host buffers, chunked and double-buffered; _dev: device buffers, ms (may be NULL) = kernel time. */
+int pcb_encode_batch_packed(pcb_handle* h, const uint32_t* u_bits, uint32_t* x_bits, int with_shuffle, int B);
+int pcb_encode_batch_dev(pcb_handle* h, const uint32_t* u_bits_dev, uint32_t* x_bits_dev, int with_shuffle, int B, float* ms);
+
 /* Decode B frames. y[B][n] are the raw channel values the reference passes to *::Decode
  * (PolarCodes.cpp:162,171,180).  sol is [B][n] for decoders 1,2 (full u-hat incl. frozen
  * positions) and [B][k+crc] for decoder 3 (info + crc bits), one int per bit.

@@ -48,6 +48,8 @@ SIGNATURES = {
     "pcb_destroy": (None, [C.c_void_p]),
     "pcb_set_code": (C.c_int, [C.c_void_p, _ip, C.c_double]),
     "pcb_encode_batch": (C.c_int, [C.c_void_p, _ip, _ip, C.c_int, C.c_int]),
+    "pcb_encode_batch_packed": (C.c_int, [C.c_void_p, _up, _up, C.c_int, C.c_int]),
+    "pcb_encode_batch_dev": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.POINTER(C.c_float)]),
     "pcb_decode_batch": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int]),
     "pcb_decode_batch_f32": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int]),
     "pcb_decode_batch_f32_packed": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int]),
@@ -178,6 +180,18 @@ class Decoder:
         x = np.zeros_like(u)
         _check(lib().pcb_encode_batch(self._h, u, x, int(bool(with_shuffle)), u.shape[0]))
         return x
+
+    def encode_packed(self, u_bits, with_shuffle):
+        """u_bits [B][max(n/32,1)] uint32 -> x_bits, same shape (bit t of a frame at word t // 32, bit t % 32)."""
+        u_bits = np.ascontiguousarray(u_bits, dtype=np.uint32).reshape(-1, max(self.n // 32, 1))
+        x = np.zeros_like(u_bits)
+        _check(lib().pcb_encode_batch_packed(self._h, u_bits, x, int(bool(with_shuffle)), u_bits.shape[0]))
+        return x
+
+    def encode_dev(self, u_bits_dev_ptr, x_bits_dev_ptr, with_shuffle, B):
+        ms = C.c_float(0)
+        _check(lib().pcb_encode_batch_dev(self._h, u_bits_dev_ptr, x_bits_dev_ptr, int(bool(with_shuffle)), B, C.byref(ms)))
+        return ms.value
 
     def decode(self, y):
         """y [B][n] float64 (the reference's type) or float32 -> sol [B][stride] int32."""

@@ -23,6 +23,7 @@ struct GenArgs {
 
 cudaError_t launch_encode(const int* d_u, int* d_x, int n, int m, int with_shuffle, int B, int sm_count,
                           cudaStream_t st);
+cudaError_t launch_encode_packed(const uint32_t* d_u, uint32_t* d_x, int n, int m, int with_shuffle, int B, int sm_count, cudaStream_t st);
 cudaError_t launch_generate(const GenArgs& g, int sm_count, cudaStream_t st);
 // pre-pass of the list-8 quad kernel: y64 (may be null) -> y32 conversion and the range check that
 // fills the redo list (see aux_kernels.cu)

@@ -234,6 +234,8 @@ struct pcb_handle {
     // encode buffers
     size_t enc_frames = 0;
     int *d_eu = nullptr, *d_ex = nullptr;
+    size_t encp_frames = 0;
+    uint32_t *d_epu[2] = {}, *d_epx[2] = {};   // packed encode: two slots
     uint64_t launches = 0;
     // counter reduction across the ranks of a box (pcb_comm_init): NCCL communicator + device buffer
     void* comm = nullptr;
@@ -439,7 +441,7 @@ void pcb_destroy(pcb_handle* h) {
         if (h->ev_out[s]) cudaEventDestroy(h->ev_out[s]);
     }
     cudaFree(h->d_ymc); cudaFree(h->d_tx); cudaFree(h->d_dec); cudaFree(h->d_counters);
-    cudaFree(h->d_eu); cudaFree(h->d_ex); cudaFree(h->d_redo); cudaFree(h->d_qscratch); cudaFree(h->d_synd); cudaFree(h->d_gcrc); cudaFree(h->d_mc_redo); cudaFree(h->d_xhat); cudaFree(h->d_skip); cudaFree(h->d_y32); cudaFree(h->d_yscr); cudaFree(h->d_yt); cudaFree(h->d_sc32_scratch); cudaFree(h->d_sc32_bits); cudaFree(h->d_sct_ops); cudaFree(h->d_sct_glev); cudaFree(h->d_sc8_ops); cudaFree(h->d_yq); cudaFree(h->d_sc8_glev);
+    cudaFree(h->d_eu); cudaFree(h->d_ex); cudaFree(h->d_epu[0]); cudaFree(h->d_epu[1]); cudaFree(h->d_epx[0]); cudaFree(h->d_epx[1]); cudaFree(h->d_redo); cudaFree(h->d_qscratch); cudaFree(h->d_synd); cudaFree(h->d_gcrc); cudaFree(h->d_mc_redo); cudaFree(h->d_xhat); cudaFree(h->d_skip); cudaFree(h->d_y32); cudaFree(h->d_yscr); cudaFree(h->d_yt); cudaFree(h->d_sc32_scratch); cudaFree(h->d_sc32_bits); cudaFree(h->d_sct_ops); cudaFree(h->d_sct_glev); cudaFree(h->d_sc8_ops); cudaFree(h->d_yq); cudaFree(h->d_sc8_glev);
     if (h->comm) nccl_api().CommDestroy(h->comm);
     cudaFree(h->d_red);
     cudaFreeHost(h->h_stage[0]); cudaFreeHost(h->h_stage[1]); delete h->narrow;
@@ -1005,6 +1007,47 @@ int pcb_encode_batch(pcb_handle* h, const int* u, int* x, int with_shuffle, int 
         CK(cudaMemcpyAsync(x + f0 * h->n, h->d_ex, (size_t)nb * h->n * 4, cudaMemcpyDeviceToHost, h->sc));
         CK(cudaStreamSynchronize(h->sc));
     }
+    return PCB_OK;
+}
+
+// Packed variants of pcb_encode_batch (Encoder.cpp:77-83): 32 bits per word in and out.
+int pcb_encode_batch_dev(pcb_handle* h, const uint32_t* u_bits_dev, uint32_t* x_bits_dev, int with_shuffle, int B, float* ms) {
+    if (!h || !u_bits_dev || !x_bits_dev) return fail(PCB_EINVAL, "pcb_encode_batch_dev: null argument");
+    if (B <= 0) return B == 0 ? PCB_OK : fail(PCB_EINVAL, "B < 0");
+    if (int r = ensure_device(h)) return r;
+    CK(cudaEventRecord(h->t0, h->sc));
+    CK(launch_encode_packed(u_bits_dev, x_bits_dev, h->n, h->m, with_shuffle != 0, B, h->sm_count, h->sc));
+    CK(cudaEventRecord(h->t1, h->sc));
+    h->launches++;
+    CK(cudaStreamSynchronize(h->sc));
+    if (ms) CK(cudaEventElapsedTime(ms, h->t0, h->t1));
+    return PCB_OK;
+}
+
+int pcb_encode_batch_packed(pcb_handle* h, const uint32_t* u_bits, uint32_t* x_bits, int with_shuffle, int B) {
+    if (!h || !u_bits || !x_bits) return fail(PCB_EINVAL, "pcb_encode_batch_packed: null argument");
+    if (B <= 0) return B == 0 ? PCB_OK : fail(PCB_EINVAL, "B < 0");
+    if (int r = ensure_device(h)) return r;
+    const size_t NW = h->n >= 32 ? h->n / 32 : 1;
+    size_t chunk = ((size_t)16 << 20) / (NW * 4);                      // two slots of 16 MiB each way
+    if (chunk > (size_t)B) chunk = (size_t)B;
+    if (h->encp_frames < chunk) {
+        for (int s2 = 0; s2 < 2; s2++) { cudaFree(h->d_epu[s2]); cudaFree(h->d_epx[s2]); h->d_epu[s2] = h->d_epx[s2] = nullptr; }
+        h->encp_frames = 0;
+        for (int s2 = 0; s2 < 2; s2++) { CK(cudaMalloc(&h->d_epu[s2], chunk * NW * 4)); CK(cudaMalloc(&h->d_epx[s2], chunk * NW * 4)); }
+        h->encp_frames = chunk;
+    }
+    // copy in / encode / copy out of a chunk are ordered on one stream; a slot is reused two chunks later, behind its copy out
+    int c = 0;
+    for (size_t f0 = 0; f0 < (size_t)B; f0 += chunk, c++) {
+        const int s2 = c & 1;
+        const int nb = (int)((size_t)B - f0 < chunk ? (size_t)B - f0 : chunk);
+        CK(cudaMemcpyAsync(h->d_epu[s2], u_bits + f0 * NW, (size_t)nb * NW * 4, cudaMemcpyHostToDevice, h->sc));
+        CK(launch_encode_packed(h->d_epu[s2], h->d_epx[s2], h->n, h->m, with_shuffle != 0, nb, h->sm_count, h->sc));
+        h->launches++;
+        CK(cudaMemcpyAsync(x_bits + f0 * NW, h->d_epx[s2], (size_t)nb * NW * 4, cudaMemcpyDeviceToHost, h->sc));
+    }
+    CK(cudaStreamSynchronize(h->sc));
     return PCB_OK;
 }
 
