@@ -20,6 +20,8 @@
 //                    /tmp/pcb_nccl_id.<parent pid>.<MASTER_PORT>), prints, checkpoints and writes the
 //                    result file; the counters equal those of a one-GPU run (Philox is keyed by the
 //                    global frame id).
+//   PCB_PREC=fp32|int8  decoder 2 only: the fp32 fast mode, or the 8-bit mode with the scale 2 << qFraction of conf.txt line 9
+//                    (the reference reads qFraction and never uses it: SCLDecoderMinsum.cpp:405); default = the reference's arithmetic
 //   PCB_SEED=<s>     Philox seed (default 0x5EED0000 + SNR index as SURVEY.md §8(d))
 //   PCB_CSV=<file>   extra CSV with BER, frames/s, info Gbit/s per SNR point
 //   PCB_CONF=<file>  configuration file (default conf.txt in the CWD, like the reference)
@@ -192,7 +194,13 @@ int main() {
 
     std::vector<pcb_handle*> hs(gpus, nullptr);
     for (int g = 0; g < gpus; g++) {
-        hs[g] = pcb_create(world > 1 ? local_rank : g, n, k, ecrc, L, decoder, PCB_PREC_STRICT);
+        int prec = PCB_PREC_STRICT;
+        if (const char* pe = std::getenv("PCB_PREC")) {
+            if (decoder == 2 && std::string(pe) == "fp32") prec = PCB_PREC_FP32;
+            else if (decoder == 2 && std::string(pe) == "int8") prec = PCB_PREC_INT8_Q(qFraction);
+            else if (*pe) { std::fprintf(stderr, "PCB_PREC=%s: decoder 2 takes fp32 or int8\n", pe); return 2; }
+        }
+        hs[g] = pcb_create(world > 1 ? local_rank : g, n, k, ecrc, L, decoder, prec);
         if (!hs[g]) fail("pcb_create");
     }
     if (world > 1) {

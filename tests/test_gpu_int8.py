@@ -67,3 +67,20 @@ def test_int8_mode_fer_stays_near_the_double_decoder():
     assert fer0 > 1e-3
     assert fers[2] < 2.0 * fer0 and fers[3] < 2.0 * fer0 and fers[1] < 6.0 * fer0, (fer0, fers)
     assert min(fers.values()) > 0.5 * fer0, (fer0, fers)
+
+
+def test_driver_runs_the_8_bit_mode_with_conf_txt_qfraction(tmp_path):
+    """PCB_PREC=int8: conf.txt line 9 (qFraction, read and never used by the reference, PolarCodes.cpp:275) sets the scale;
+    the counters are those of pcb_montecarlo on an INT8 handle with the same seed."""
+    import os
+    import subprocess
+    host = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "polarcodes_b200", "host")
+    subprocess.check_call(["make", "-s", "-C", host])
+    (tmp_path / "conf.txt").write_text("1\n1024\n512\n50000\n2\n2\n1\n0\n3\n1\n2.5\n")
+    env = dict(os.environ, PCB_PREC="int8", PCB_CSV=str(tmp_path / "o.csv"), PCB_SEED="77")
+    r = subprocess.run([os.path.join(host, "polarcodes_driver")], cwd=tmp_path, capture_output=True, text=True, env=env)
+    assert r.returncode == 0, r.stderr
+    row = open(tmp_path / "o.csv").read().strip().split("\n")[1].split(",")
+    d, _ = _dec(1024, 512, 3, snr=2.5)
+    want = d.montecarlo(2.5, 50000, seed=77)
+    assert (int(row[1]), int(row[2])) == (want["frames"], want["frame_errors"])
