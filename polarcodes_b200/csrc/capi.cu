@@ -293,12 +293,18 @@ static int configure(pcb_handle* h) {
         const bool exact = h->decoder == 1;
         const char* we = getenv("PCB_T_W");
         const int wv = we ? atoi(we) : 0;
-        h->sct_W = (wv == 1 || wv == 2 || wv == 4 || wv == 8) ? wv
-                   : exact ? 2 : h->n <= 256 ? 1 : h->n == 512 ? 2 : h->fp64 ? 4 : h->n == 1024 ? 2 : 4;
+        // measured best shapes (B200, tools/sct_sweep.py): {W, VS} per (arithmetic, n); elsewhere 16 KB of shared-memory levels
+        int tw = exact ? (h->n <= 512 ? 2 : 4) : h->n <= 256 ? 1 : h->n == 512 ? 2 : 4, tvs = 0;
+        if (exact) tvs = 4;
+        else if (h->fp64) tvs = h->n == 2048 ? 5 : 4;
+        else { if (h->n == 1024) { tw = 1; tvs = 5; } else if (h->n == 2048) tvs = 4; else if (h->n <= 256) tvs = 2; }
+        h->sct_W = (wv == 1 || wv == 2 || wv == 4 || wv == 8) ? wv : tw;
         if (h->n < 512 && h->sct_W > 4) h->sct_W = 4;
         const char* ve = getenv("PCB_T_VS");
         int vs = h->n > 2048 ? 3 : 2;
         while (vs < h->m - 4 && (size_t)((h->n >> (vs - 1)) - 8) * 32 * h->sizeofT > 16384) vs++;
+        if (tvs && h->n <= 2048 && h->n >= 256) vs = tvs < h->m - 4 ? tvs : h->m - 4;
+        if (vs < 2) vs = 2;
         if (ve && atoi(ve) >= (h->n > 2048 ? 3 : 2) && atoi(ve) <= h->m - 4) vs = atoi(ve);
         int bps = 0;
         if (sct_occupancy(h->m, h->fp64, exact, h->sct_W, vs, &bps, &h->sct_smem, &h->sct_glob) != cudaSuccess || bps == 0) {

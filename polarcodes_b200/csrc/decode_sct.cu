@@ -38,6 +38,12 @@
 #include "sc_ops.cuh"
 #include "sct_common.cuh"
 
+#ifndef PCB_T_MINWARPS
+#define PCB_T_MINWARPS 0   // register budget: this many warps have to fit an SM (0: the compiler's own choice)
+#endif
+#ifndef PCB_T_CHUNK
+#define PCB_T_CHUNK 128    // bytes of a frame's row staged per step of the top op
+#endif
 #ifndef PCB_T_YHINT
 #define PCB_T_YHINT 1      // L2 evict-first hint on the channel-value loads
 #endif
@@ -80,12 +86,14 @@ struct Tile {
     // The warp stages 128 bytes of each of its 32 frames per step with cp.async (8 lanes per frame: every global
     // access is a whole line), two steps in flight, and each lane then reads its own frame's piece: outputs
     // r .. r + RB - 1 of level 2 in bit-reversed order (rows x = bitrev(r)).
-    static constexpr int STAGE_ROW = 144;                     // 128 bytes + 16: LDS.128 of 32 rows is conflict-free
+    static constexpr int STAGE_CHUNK = PCB_T_CHUNK;           // bytes of a frame's row per step (128 or 64)
+    static constexpr int STAGE_ROW = STAGE_CHUNK + 16;        // + 16: LDS.128 of 32 rows is conflict-free
     static constexpr int STAGE_BYTES = 2 * 32 * STAGE_ROW;    // per warp
     template <typename YT, bool G1, bool G2>
     __device__ __forceinline__ void top2(const YT* __restrict__ ybatch, int tile, int B, bool fuse3, double sigma2, int nw, int wi, int lane,
                                          unsigned char* stage) const {
-        constexpr int RB = 128 / (4 * (int)sizeof(YT));       // level-2 outputs per step: 4 (double input) or 8 (float)
+        constexpr int RB = STAGE_CHUNK / (4 * (int)sizeof(YT)); // level-2 outputs per step: 4 (double input) or 8 (float) with 128-byte chunks
+        constexpr int LPF = STAGE_CHUNK / 16, FPI = 32 / LPF;  // lanes per frame, frames per cp.async instruction
         const int R = n >> 2, per = R / nw, r0 = wi * per, sh = 32 - (m - 2), nsteps = per / RB;
         T* d2 = lev(2);
         T* d3 = lev(3);
@@ -97,11 +105,11 @@ struct Tile {
         asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(ypol));
 #endif
         auto issue = [&](int c) {
-            const char* src0 = reinterpret_cast<const char*>(ybatch) + (size_t)(r0 + c * RB) * 4 * sizeof(YT) + (lane & 7) * 16;
-            const unsigned dst0 = sbase + (c & 1) * (32 * STAGE_ROW) + (lane & 7) * 16;
+            const char* src0 = reinterpret_cast<const char*>(ybatch) + (size_t)(r0 + c * RB) * 4 * sizeof(YT) + (lane % LPF) * 16;
+            const unsigned dst0 = sbase + (c & 1) * (32 * STAGE_ROW) + (lane % LPF) * 16;
 #pragma unroll
-            for (int j = 0; j < 8; j++) {
-                const int f = j * 4 + (lane >> 3);
+            for (int j = 0; j < LPF; j++) {
+                const int f = j * FPI + lane / LPF;
                 const size_t row = (size_t)min(tile * 32 + f, B - 1) * n * sizeof(YT);
 #if PCB_T_YHINT
                 asm volatile("cp.async.cg.shared.global.L2::cache_hint [%0], [%1], 16, %2;" ::"r"(dst0 + f * STAGE_ROW), "l"(src0 + row), "l"(ypol) : "memory");
@@ -249,7 +257,7 @@ struct Tile {
 };
 
 template <typename T, bool EXACT, int W, bool GL>
-__global__ void __launch_bounds__(32 * W) decode_sct_kernel(const __grid_constant__ Args S) {
+__global__ void __launch_bounds__(32 * W, PCB_T_MINWARPS / W) decode_sct_kernel(const __grid_constant__ Args S) {
     const DecodeArgs& A = S.a;
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -260,9 +268,15 @@ __global__ void __launch_bounds__(32 * W) decode_sct_kernel(const __grid_constan
     const int srows = (n >> (t.vs - 1)) - 8;                   // rows of the shared-memory levels
     t.P = reinterpret_cast<T*>(smem_raw) + lane;
     t.G = nullptr;
-    t.H = reinterpret_cast<uint32_t*>(reinterpret_cast<T*>(smem_raw) + srows * 32) + lane;
-    // staging area of the top op, one slice per warp, behind the levels and the (shared-memory) heap
-    unsigned char* stage = smem_raw + (size_t)srows * 32 * sizeof(T) + (n > 2048 ? 0 : (size_t)NW * 32 * 4) + (size_t)warp * Tile<T, EXACT, GL>::STAGE_BYTES;
+    // [levels vs .. m-3 | staging area of the top op, one slice per warp][heap (n <= 2048)][staging area when it cannot alias the levels]
+    // With vs >= 4 the top op writes no shared-memory level (levels 2, 3 are global) and every shared-memory level is dead
+    // while it runs (recomputed before its next use), so the staging slices alias the level region.
+    const bool alias = GL && t.vs >= 4;
+    size_t region = (size_t)srows * 32 * sizeof(T);
+    if (alias && region < (size_t)W * Tile<T, EXACT, GL>::STAGE_BYTES) region = (size_t)W * Tile<T, EXACT, GL>::STAGE_BYTES;
+    const size_t heap_bytes = n > 2048 ? 0 : (size_t)NW * 32 * 4;
+    t.H = reinterpret_cast<uint32_t*>(smem_raw + region) + lane;
+    unsigned char* stage = smem_raw + (alias ? 0 : region + heap_bytes) + (size_t)warp * Tile<T, EXACT, GL>::STAGE_BYTES;
     if constexpr (GL) {
         const size_t grows = (size_t)(n >> 1) - (n >> (t.vs - 1));
         const size_t per_block = grows * 32 * sizeof(T) + (n > 2048 ? (size_t)NW * 32 * 4 : 0);
@@ -345,8 +359,11 @@ __global__ void __launch_bounds__(32 * W) decode_sct_kernel(const __grid_constan
 }
 
 template <typename T>
-static size_t smem_bytes(int n, int vs, int W) {
-    return (size_t)((n >> (vs - 1)) - 8) * 32 * sizeof(T) + (n > 2048 ? 0 : (size_t)(n >> 5) * 32 * 4) + (size_t)W * (2 * 32 * 144);
+static size_t smem_bytes(int n, int vs, int W) {      // (the layout of decode_sct_kernel)
+    const size_t levels = (size_t)((n >> (vs - 1)) - 8) * 32 * sizeof(T), heap = n > 2048 ? 0 : (size_t)(n >> 5) * 32 * 4;
+    const size_t stage = (size_t)W * (2 * 32 * (PCB_T_CHUNK + 16));
+    if (vs >= 4) return (levels > stage ? levels : stage) + heap;
+    return levels + heap + stage;
 }
 template <typename T>
 static size_t glob_bytes(int n, int vs) {

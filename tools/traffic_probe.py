@@ -22,6 +22,7 @@ CONFIGS = [
     ("C", 3, 1024, 512, 0, 8, 0, True, 1 << 18),
     ("A", 2, 1024, 512, 0, 1, 0, True, 1 << 18),
     ("A_fp32", 2, 1024, 512, 0, 1, 1, False, 1 << 18),
+    ("A_int8", 2, 1024, 512, 0, 1, 2 | (2 << 8), True, 1 << 18),
     ("B", 1, 256, 128, 0, 1, 0, True, 1 << 18),
     ("C_crc16", 3, 1024, 512, 16, 8, 0, True, 1 << 18),
     ("conf_txt", 3, 2048, 1024, 16, 4, 0, True, 1 << 17),
@@ -82,7 +83,7 @@ def parse(src, dst):
             continue
         if ci < 0 or ci >= len(CONFIGS):
             continue
-        if not any(t in nm for t in ("decode_", "prepass", "transpose", "expand")):
+        if not any(t in nm for t in ("decode_", "prepass", "transpose", "expand", "scl_select", "quantise")):
             continue                                        # torch's own kernels (the float -> double widening)
         key, B = CONFIGS[ci][0], CONFIGS[ci][8]
         o = out.setdefault(key, {"frames_per_launch": B, "dram_bytes_read": 0.0, "dram_bytes_write": 0.0, "kernel_s": 0.0,
