@@ -297,7 +297,7 @@ static int configure(pcb_handle* h) {
         int tw = exact ? (h->n <= 512 ? 2 : 4) : h->n <= 256 ? 1 : h->n == 512 ? 2 : 4, tvs = 0;
         if (exact) tvs = 4;
         else if (h->fp64) tvs = h->n == 2048 ? 5 : 4;
-        else { if (h->n == 1024) { tw = 1; tvs = 5; } else if (h->n == 2048) tvs = 4; else if (h->n <= 256) tvs = 2; }
+        else { if (h->n >= 1024) tvs = 4; else if (h->n <= 256) tvs = 2; }     // (fp32, n = 1024: one warp / VS 5 is 13 % faster at 2^18 frames and 10 % slower at 2^20)
         h->sct_W = (wv == 1 || wv == 2 || wv == 4 || wv == 8) ? wv : tw;
         if (h->n < 512 && h->sct_W > 4) h->sct_W = 4;
         const char* ve = getenv("PCB_T_VS");
