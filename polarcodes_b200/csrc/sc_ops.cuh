@@ -50,9 +50,15 @@ __device__ __forceinline__ int g_sign(int a, int b, uint32_t signbit) {
     const int v = b + (signbit ? -a : a);
     return max(-127, min(127, v));
 }
+// one copy of the tanh / atanh sequence per kernel (inlined at every call site the exact-SC tile kernel is 1 MB of SASS)
+#ifndef PCB_EXACT_INLINE
+static __device__ __noinline__ double f_exact_call(double a, double b) { return f_exact(a, b); }
+#else
+__device__ __forceinline__ double f_exact_call(double a, double b) { return f_exact(a, b); }
+#endif
 template <bool EXACT, typename T>
 __device__ __forceinline__ T opf2(T a, T b) {
-    if constexpr (EXACT) return (T)f_exact((double)a, (double)b);
+    if constexpr (EXACT) return (T)f_exact_call((double)a, (double)b);
     else return f_minsum_fast(a, b);
 }
 // SCDecoder.cpp:27-36 is b == 0 ? y1 + y2 : y2 - y1: the same sum with the sign of y1 flipped
