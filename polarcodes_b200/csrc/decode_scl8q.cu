@@ -69,6 +69,9 @@
 #ifndef PCB_Q_GH_SMALL
 #define PCB_Q_GH_SMALL 0   // the same for the other N >= 1024 variants
 #endif
+#ifndef PCB_Q_RL3
+#define PCB_Q_RL3 1        // N = 2048, 16/32 paths: layer 3 is never stored -- the g of layer 4 recomputes it from the channel values
+#endif
 #ifndef PCB_Q_R1FAST
 #define PCB_Q_R1FAST 1     // rate-1 nodes of size 4 and 8 from the signs and the smallest magnitude of their inputs
 #endif
@@ -90,7 +93,7 @@
 #define PCB_Q_MW_BIG 1
 #endif
 #ifndef PCB_Q_WCAP
-#define PCB_Q_WCAP 18      // most warps of such a block (18 warps keep 113 registers each)
+#define PCB_Q_WCAP 20      // most warps of such a block (20 warps: 102 registers each, all of the shared memory; 18: -1 %)
 #endif
 #ifndef PCB_Q_CPA
 #define PCB_Q_CPA 1
@@ -131,6 +134,11 @@ struct Geo {
     // shared memory per warp (12 resident warps per SM instead of 8; the throughput follows the
     // number of resident warps).  With 8 paths the staging area of the top stage would not fit.
     static constexpr bool GL5 = GL4 && M >= 11 && LL >= 16 && PCB_Q_GL5;
+    // RL3 (with GL5): layer 3 (half of the scratch, 32 KB per frame at L = 32) is not stored at all.  The top stage
+    // produces layers 3 and 4 together from the channel values; at the g of layer 4 it runs again (same partial sums of
+    // layers 1-3: they only change at top-stage boundaries, and a clone inherits the slot fields that find them) and
+    // combines the two halves with g instead of f.  More arithmetic, far less scratch: what is left fits L2.
+    static constexpr bool RL3 = GL5 && PCB_Q_RL3;
     static constexpr int LS = GL5 ? 6 : GL4 ? 5 : GL3 ? 4 : 3;  // first LLR layer in shared memory
     static constexpr int NW = N / 32;       // words of a full-length bit array
     // Partial-sum heap of a slot: the layer of size S at words [S/32, 2S/32).  GH: the two largest
@@ -171,7 +179,7 @@ struct Geo {
     static constexpr int OFF_KEYS = (PFLOATS + LL * HS + 3) & ~3;
     static constexpr int FRAME_WORDS = (OFF_KEYS + (MERGE ? 4 : 2) * LL + 3) & ~3;   // LLRs, heaps, candidate keys
     static constexpr int TOTAL = FPW * FRAME_WORDS * 4;
-    static constexpr int L3_BLOCK_FLOAT4 = GL3 ? FPW * Q3 * LL : 0;   // global scratch per block: [frame][k][slot] float4
+    static constexpr int L3_BLOCK_FLOAT4 = GL3 && !RL3 ? FPW * Q3 * LL : 0;   // global scratch per block: [frame][k][slot] float4
     static constexpr int L4_BLOCK_FLOAT4 = GL4 ? FPW * (Q3 / 2) * LL : 0;
     static constexpr int L5_BLOCK_FLOAT4 = GL5 ? FPW * (Q3 / 4) * LL : 0;
     static constexpr int HG_BLOCK_FLOAT4 = GH ? FPW * (NW - NW / 4) * LL / 4 : 0;
@@ -546,13 +554,13 @@ struct Dec {
         asm volatile("cp.async.commit_group;" ::: "memory");
     }
 
-    __device__ __forceinline__ void top_gl3(int ev, const YT* ybase) {
+    __device__ __forceinline__ void top_gl3(int ev, const YT* ybase, bool g4 = false) {
         constexpr int E = G::N / 8, N4 = G::N / 4, Q = G::Q3, NR = Q / 16, TU = PCB_Q_TOPU;
         [[maybe_unused]] constexpr int SG = PCB_Q_STG;
         const bool g1 = ev & 4, g2 = ev & 2, g3 = ev & 1;
         const float* R = P + G::STAGE_OFF;
         float* dst4 = G::GL4 ? nullptr : arr(4, p);
-        float4* dst3 = L3 + p;
+        [[maybe_unused]] float4* dst3 = G::RL3 ? nullptr : L3 + p;
         __syncwarp();                            // everyone is done with the previous subtree
         const bool chunked = g1 || G::CHUNKF;    // channel values staged chunk by chunk (else: layer 1 = f staged whole)
         if (!chunked) {
@@ -584,6 +592,8 @@ struct Dec {
             }
 #endif
             uint32_t c1[4][2], c2[2][2], c3[2];
+            [[maybe_unused]] uint32_t c4 = 0;
+            if constexpr (G::RL3) { if (g4) c4 = cword(4, 0, r); }
 #pragma unroll
             for (int h = 0; h < 2; h++) {
                 const int w32 = h * (Q / 16) + r;
@@ -629,9 +639,10 @@ struct Dec {
                     if (g2) { l2[0] = gs4(l1[0], l1[2], c2[0][h], 4 * kk); l2[1] = gs4(l1[1], l1[3], c2[1][h], 4 * kk); }
                     else { l2[0] = ff4(l1[0], l1[2]); l2[1] = ff4(l1[1], l1[3]); }
                     o[h] = g3 ? gs4(l2[0], l2[1], c3[h], 4 * kk) : ff4(l2[0], l2[1]);
-                    dst3[k * LL] = o[h];
+                    if constexpr (!G::RL3) dst3[k * LL] = o[h];
                 }
-                if constexpr (G::GL4) L4[(r * 8 + kk) * LL + p] = ff4(o[0], o[1]);
+                if constexpr (G::RL3) L4[(r * 8 + kk) * LL + p] = g4 ? gs4(o[0], o[1], c4, 4 * kk) : ff4(o[0], o[1]);
+                else if constexpr (G::GL4) L4[(r * 8 + kk) * LL + p] = ff4(o[0], o[1]);
                 else *reinterpret_cast<float4*>(dst4 + 4 * (r * 8 + kk)) = ff4(o[0], o[1]);
             }
 #if PCB_Q_CPA
@@ -903,10 +914,11 @@ struct Dec {
         static_assert(LR > G::LS, "register chains start below the first shared-memory layer");
         const int z = blk ? (__ffs(blk) - 1) : 31;
         int ll, own;    // layers own.. are recomputed, the f-layers below ll are still to do
-        if (z >= M - 6) {                                  // i0 is a multiple of N/8
-            if constexpr (G::GL3) { top_gl3(blk >> (M - 6), ybase); ll = 4; }
+        const bool topev = z >= M - 6;                     // i0 is a multiple of N/8
+        if (topev || (G::RL3 && G::LBOT - z == 4)) {       // RL3: also at the g of layer 4 (layer 3 is recomputed, not read)
+            if constexpr (G::GL3) { top_gl3(blk >> (M - 6), ybase, !topev); ll = 4; }
             else { top3(blk >> (M - 6), ybase); ll = 3; }
-            own = G::LTOP;
+            own = topev ? G::LTOP : 4;
         } else {
             __syncwarp();
             ll = own = G::LBOT - z;
