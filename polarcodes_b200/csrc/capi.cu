@@ -285,7 +285,8 @@ static int configure(pcb_handle* h) {
         cudaGetLastError(); h->sc32 = false;
     }
     h->sct = !h->sc8 && (h->decoder == 2 || h->decoder == 1) && sct_supported(h->m) && !getenv("PCB_FORCE_GENERIC") && !getenv("PCB_SC_LANE");   // PCB_SC_LANE=1: the lane-per-frame kernel (A/B)
-    if (h->sct && h->m > 11 && !getenv("PCB_T_BIG")) h->sct = false;     // n > 2048: the lane-per-frame kernel streams better (PCB_T_BIG=1: A/B)
+    // n > 2048: every level above the last 120 rows and the heap live in the block's global slice; four warps per tile and
+    // 740 tiles in flight move 4.4 MB per frame where the lane-per-frame kernel moves 5.9 (config E: 1.17 vs 0.95 M frames/s)
     if (h->sct) {
         // Launch shape (tools/sct_sweep.py): warps per tile, and the first level kept in shared memory -- the rest of the
         // level store lives in the block's global slice (L2).  What decides is how many tiles are resident: the leaf walk
@@ -304,6 +305,7 @@ static int configure(pcb_handle* h) {
         int vs = h->n > 2048 ? 3 : 2;
         while (vs < h->m - 4 && (size_t)((h->n >> (vs - 1)) - 8) * 32 * h->sizeofT > 16384) vs++;
         if (tvs && h->n <= 2048 && h->n >= 256) vs = tvs < h->m - 4 ? tvs : h->m - 4;
+        if (h->n > 2048) { vs = h->m - 6; if (!(wv == 1 || wv == 2 || wv == 4 || wv == 8)) h->sct_W = 4; }
         if (vs < 2) vs = 2;
         if (ve && atoi(ve) >= (h->n > 2048 ? 3 : 2) && atoi(ve) <= h->m - 4) vs = atoi(ve);
         int bps = 0;

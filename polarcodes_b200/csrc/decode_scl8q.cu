@@ -72,6 +72,9 @@
 #ifndef PCB_Q_RL3
 #define PCB_Q_RL3 1        // N = 2048, 16/32 paths: layer 3 is never stored -- the g of layer 4 recomputes it from the channel values
 #endif
+#ifndef PCB_Q_RL3_SMALL
+#define PCB_Q_RL3_SMALL 0  // the same for the other variants with layer 4 in the scratch (L = 8, N = 1024: the headline)
+#endif
 #ifndef PCB_Q_R1FAST
 #define PCB_Q_R1FAST 1     // rate-1 nodes of size 4 and 8 from the signs and the smallest magnitude of their inputs
 #endif
@@ -138,7 +141,7 @@ struct Geo {
     // produces layers 3 and 4 together from the channel values; at the g of layer 4 it runs again (same partial sums of
     // layers 1-3: they only change at top-stage boundaries, and a clone inherits the slot fields that find them) and
     // combines the two halves with g instead of f.  More arithmetic, far less scratch: what is left fits L2.
-    static constexpr bool RL3 = GL5 && PCB_Q_RL3;
+    static constexpr bool RL3 = GL4 && (GL5 ? PCB_Q_RL3 : PCB_Q_RL3_SMALL);
     static constexpr int LS = GL5 ? 6 : GL4 ? 5 : GL3 ? 4 : 3;  // first LLR layer in shared memory
     static constexpr int NW = N / 32;       // words of a full-length bit array
     // Partial-sum heap of a slot: the layer of size S at words [S/32, 2S/32).  GH: the two largest

@@ -20,7 +20,9 @@ CONFIGS = [
     ("   SCMinsum 128/64 fp64", 128, 64, pb.SCMINSUM, pb.STRICT, 1 << 18),
     ("   SCMinsum 2048/1024 fp64", 2048, 1024, pb.SCMINSUM, pb.STRICT, 1 << 17),
     ("   SCMinsum 4096/2048 fp64", 4096, 2048, pb.SCMINSUM, pb.STRICT, 1 << 16),
-    ("E  SCMinsum 32768/16384 fp64", 32768, 16384, pb.SCMINSUM, pb.STRICT, 42624),
+    ("   SCMinsum 8192/4096 fp64", 8192, 4096, pb.SCMINSUM, pb.STRICT, 1 << 16),
+    ("   SCMinsum 32768/16384 fp32", 32768, 16384, pb.SCMINSUM, pb.FP32, 1 << 15),
+    ("E  SCMinsum 32768/16384 fp64", 32768, 16384, pb.SCMINSUM, pb.STRICT, 1 << 16),
 ]
 ONLY = os.environ.get("PCB_SWEEP_ONLY")
 SCALE = float(os.environ.get("PCB_SWEEP_SCALE", "1"))
