@@ -296,6 +296,9 @@ def montecarlo_leg(pb, dev):
 
 
 def main():
+    if os.environ.get("PCB_BENCH_WATCHDOG"):                  # debugging aid: where is a hung rank?
+        import faulthandler
+        faulthandler.dump_traceback_later(int(os.environ["PCB_BENCH_WATCHDOG"]), exit=True)
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=10)
@@ -513,6 +516,8 @@ def main():
             line["cpu_baseline"] = {"value": cfps * K / 1e9, "unit": "Gbit/s", "frames_per_s": cfps, "cores": cores,
                                     "kind": kind, "sample": f"{nf} distinct frames of the same workload, {cores} processes, decode-only, {wall:.1f} s"}
         print(json.dumps(line), flush=True)
+    else:
+        dec.close()                                           # every rank releases its handle (and its communicator)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()

@@ -450,7 +450,9 @@ void pcb_destroy(pcb_handle* h) {
     }
     cudaFree(h->d_ymc); cudaFree(h->d_tx); cudaFree(h->d_dec); cudaFree(h->d_counters);
     cudaFree(h->d_eu); cudaFree(h->d_ex); cudaFree(h->d_epu[0]); cudaFree(h->d_epu[1]); cudaFree(h->d_epx[0]); cudaFree(h->d_epx[1]); cudaFree(h->d_redo); cudaFree(h->d_qscratch); cudaFree(h->d_synd); cudaFree(h->d_gcrc); cudaFree(h->d_mc_redo); cudaFree(h->d_xhat); cudaFree(h->d_skip); cudaFree(h->d_y32); cudaFree(h->d_yscr); cudaFree(h->d_yt); cudaFree(h->d_sc32_scratch); cudaFree(h->d_sc32_bits); cudaFree(h->d_sct_ops); cudaFree(h->d_sct_glev); cudaFree(h->d_sc8_ops); cudaFree(h->d_yq); cudaFree(h->d_sc8_glev);
-    if (h->comm) nccl_api().CommDestroy(h->comm);
+    // ncclCommDestroy may wait for the other ranks of the communicator; a handle is destroyed by its owner alone (the work on
+    // its stream has been synchronised above), so the communicator is aborted where the library offers that
+    if (h->comm) { NcclApi& nc = nccl_api(); if (nc.CommAbort) nc.CommAbort(h->comm); else nc.CommDestroy(h->comm); }
     cudaFree(h->d_red);
     cudaFreeHost(h->h_stage[0]); cudaFreeHost(h->h_stage[1]); delete h->narrow;
     if (h->t0) cudaEventDestroy(h->t0);

@@ -19,6 +19,7 @@ struct NcclApi {
     int (*CommInitRank)(Comm*, int, UniqueId, int) = nullptr;
     int (*AllReduce)(const void*, void*, size_t, int, int, Comm, cudaStream_t) = nullptr;
     int (*CommDestroy)(Comm) = nullptr;
+    int (*CommAbort)(Comm) = nullptr;                   // optional: teardown that does not wait for the other ranks
     const char* (*GetErrorString)(int) = nullptr;
     void* so = nullptr;
 
@@ -40,6 +41,7 @@ struct NcclApi {
         AllReduce = reinterpret_cast<decltype(AllReduce)>(dlsym(so, "ncclAllReduce"));
         CommDestroy = reinterpret_cast<decltype(CommDestroy)>(dlsym(so, "ncclCommDestroy"));
         GetErrorString = reinterpret_cast<decltype(GetErrorString)>(dlsym(so, "ncclGetErrorString"));
+        CommAbort = reinterpret_cast<decltype(CommAbort)>(dlsym(so, "ncclCommAbort"));
         if (!GetUniqueId || !CommInitRank || !AllReduce || !CommDestroy || !GetErrorString) { so = nullptr; return "libnccl lacks an entry point"; }
         return nullptr;
     }
