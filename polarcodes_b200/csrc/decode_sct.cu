@@ -47,6 +47,9 @@
 #ifndef PCB_T_YHINT
 #define PCB_T_YHINT 1      // L2 evict-first hint on the channel-value loads
 #endif
+#ifndef PCB_T_SERIAL_LDS
+#define PCB_T_SERIAL_LDS 1 // warp 0's serial ops address the shared-memory levels directly (LDS / STS instead of generic accesses)
+#endif
 #ifndef PCB_T_TOPU
 #define PCB_T_TOPU 4       // level-2 outputs per group of the top op (two groups of 4 * TOPU channel values in flight per lane)
 #endif
@@ -80,6 +83,8 @@ struct Tile {
         const int first = GL ? vs : 2;
         return P + ((n >> (first - 1)) - (n >> (v - 1))) * 32;
     }
+    // a level known to be in shared memory (v >= vs): no address-space select, the accesses compile to LDS / STS
+    __device__ __forceinline__ T* lev_s(int v) const { return P + ((n >> ((GL ? vs : 2) - 1)) - (n >> (v - 1))) * 32; }
     __device__ __forceinline__ uint32_t sbit(int pos) const { return (H[(pos >> 5) * 32] << (31 - (pos & 31))) & 0x80000000u; }
 
     // ---- levels 1 and 2 of node q (G1: level 1 is a g-level, G2: level 2 is), optionally f to level 3 ----
@@ -188,14 +193,15 @@ struct Tile {
     }
 
     // ---- level v (S = n >> v rows) from level v - 1; fuse: level v + 1 = f(level v) in the same pass ----
-    template <bool ISG>
+    // SM: source and destinations are shared-memory levels (the serial ops of warp 0: at most 16 rows)
+    template <bool ISG, bool SM>
     __device__ __forceinline__ void level_t(int v, bool fuse, int nw, int wi) const {
         constexpr int U = PCB_T_U;
         const int S = n >> v;
-        const T* src = lev(v - 1);
-        T* dst = lev(v);
+        const T* src = SM ? lev_s(v - 1) : lev(v - 1);
+        T* dst = SM ? lev_s(v) : lev(v);
         if (fuse) {
-            T* dst2 = lev(v + 1);
+            T* dst2 = SM ? lev_s(v + 1) : lev(v + 1);
             const int Hs = S >> 1, per = Hs / nw, x0 = wi * per;      // (the host makes per a multiple of U)
             const T* s0 = src + (size_t)x0 * 32;
             T* q0 = dst + (size_t)x0 * 32;
@@ -251,13 +257,19 @@ struct Tile {
         }
     }
     __device__ __forceinline__ void level(int v, bool isg, bool fuse, int nw, int wi) const {
-        if (isg) level_t<true>(v, fuse, nw, wi);
-        else level_t<false>(v, fuse, nw, wi);
+        if (isg) level_t<true, false>(v, fuse, nw, wi);
+        else level_t<false, false>(v, fuse, nw, wi);
+    }
+    __device__ __forceinline__ void level_serial(int v, bool isg, bool fuse) const {
+        if (GL && PCB_T_SERIAL_LDS && v - 1 >= vs) {
+            if (isg) level_t<true, true>(v, fuse, 1, 0);
+            else level_t<false, true>(v, fuse, 1, 0);
+        } else level(v, isg, fuse, 1, 0);
     }
 };
 
 template <typename T, bool EXACT, int W, bool GL>
-__global__ void __launch_bounds__(32 * W, PCB_T_MINWARPS / W) decode_sct_kernel(const __grid_constant__ Args S) {
+__global__ void __launch_bounds__(32 * W, EXACT ? 0 : PCB_T_MINWARPS / W) decode_sct_kernel(const __grid_constant__ Args S) {
     const DecodeArgs& A = S.a;
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -311,11 +323,11 @@ __global__ void __launch_bounds__(32 * W, PCB_T_MINWARPS / W) decode_sct_kernel(
                     __syncthreads();
                 } else {                                   // (warp 0 only: the other warps' list has no such op)
                     t.wk_w0 = wk.w0;
-                    t.level(v, isg, fuse, 1, 0);
+                    t.level_serial(v, isg, fuse);
                 }
             } else if (type == OP_NODE8) {
                 T a[8];
-                const T* src = t.lev(m - 3);
+                const T* src = PCB_T_SERIAL_LDS ? t.lev_s(m - 3) : t.lev(m - 3);
 #pragma unroll
                 for (int j = 0; j < 8; ++j) a[j] = src[j * 32];
                 const uint32_t ib = (__ldg(A.info_mask + (aux >> 2)) >> (8 * (aux & 3))) & 0xFFu;
@@ -332,15 +344,18 @@ __global__ void __launch_bounds__(32 * W, PCB_T_MINWARPS / W) decode_sct_kernel(
                 }
             } else {                                       // OP_RATE1: v = log2 of the node size (8, 16 or 32)
                 const int Sz = 1 << v;
-                const T* src = t.lev(m - v);
                 uint32_t beta = 0;
                 bool ok = true;
+                auto hard = [&](const T* src) {
 #pragma unroll 4
-                for (int j = 0; j < Sz; j++) {
-                    const T al = src[(size_t)j * 32];
-                    ok = ok && Tiny<T>::ok(al);
-                    beta |= (al > (T)0 ? 0u : 1u) << j;
-                }
+                    for (int j = 0; j < Sz; j++) {
+                        const T al = src[(size_t)j * 32];
+                        ok = ok && Tiny<T>::ok(al);
+                        beta |= (al > (T)0 ? 0u : 1u) << j;
+                    }
+                };
+                if (GL && PCB_T_SERIAL_LDS && m - v >= t.vs) hard(t.lev_s(m - v));
+                else hard(t.lev(m - v));
                 bad = bad || !ok;
                 uint32_t u = beta;                         // u = beta F^(x)v, packed
                 u ^= (u >> 1) & 0x55555555u; u ^= (u >> 2) & 0x33333333u; u ^= (u >> 4) & 0x0F0F0F0Fu;
