@@ -268,8 +268,11 @@ struct Tile {
     }
 };
 
-template <typename T, bool EXACT, int W, bool GL>
-__global__ void __launch_bounds__(32 * W, EXACT ? 0 : PCB_T_MINWARPS / W) decode_sct_kernel(const __grid_constant__ Args S) {
+// HG: the heap is in the global store too (n > 2048); otherwise its accesses compile to LDS / STS.  The n > 2048 kernels are
+// bound by DRAM latency and want 20 warps per SM (at most 96 registers; 24 for fp32); the others run faster with the registers
+// the compiler takes (122 for fp64, four blocks of four warps per SM) than with a fifth block.
+template <typename T, bool EXACT, int W, bool GL, bool HG>
+__global__ void __launch_bounds__(32 * W, EXACT ? 0 : (HG ? (sizeof(T) == 4 ? 24 : 20) : PCB_T_MINWARPS) / W) decode_sct_kernel(const __grid_constant__ Args S) {
     const DecodeArgs& A = S.a;
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -286,15 +289,15 @@ __global__ void __launch_bounds__(32 * W, EXACT ? 0 : PCB_T_MINWARPS / W) decode
     const bool alias = GL && t.vs >= 4;
     size_t region = (size_t)srows * 32 * sizeof(T);
     if (alias && region < (size_t)W * Tile<T, EXACT, GL>::STAGE_BYTES) region = (size_t)W * Tile<T, EXACT, GL>::STAGE_BYTES;
-    const size_t heap_bytes = n > 2048 ? 0 : (size_t)NW * 32 * 4;
+    const size_t heap_bytes = HG ? 0 : (size_t)NW * 32 * 4;
     t.H = reinterpret_cast<uint32_t*>(smem_raw + region) + lane;
     unsigned char* stage = smem_raw + (alias ? 0 : region + heap_bytes) + (size_t)warp * Tile<T, EXACT, GL>::STAGE_BYTES;
     if constexpr (GL) {
         const size_t grows = (size_t)(n >> 1) - (n >> (t.vs - 1));
-        const size_t per_block = grows * 32 * sizeof(T) + (n > 2048 ? (size_t)NW * 32 * 4 : 0);
+        const size_t per_block = grows * 32 * sizeof(T) + (HG ? (size_t)NW * 32 * 4 : 0);
         unsigned char* gb = reinterpret_cast<unsigned char*>(S.glev) + (size_t)blockIdx.x * per_block;
         t.G = reinterpret_cast<T*>(gb) + lane;
-        if (n > 2048) t.H = reinterpret_cast<uint32_t*>(gb + grows * 32 * sizeof(T)) + lane;
+        if constexpr (HG) t.H = reinterpret_cast<uint32_t*>(gb + grows * 32 * sizeof(T)) + lane;
     }
     const double sigma2 = A.sigma * A.sigma;
     const uint32_t* ops = warp == 0 ? S.ops : S.pops;
@@ -385,31 +388,35 @@ static size_t glob_bytes(int n, int vs) {
     return (size_t)((n >> 1) - (n >> (vs - 1))) * 32 * sizeof(T) + (n > 2048 ? (size_t)(n >> 5) * 32 * 4 : 0);
 }
 
-template <typename T, bool EXACT, int W, bool GL>
+template <typename T, bool EXACT, int W, bool GL, bool HG>
 static cudaError_t attr(int n, int vs, int* bps) {
     const size_t smem = smem_bytes<T>(n, vs, W);
-    cudaError_t e = cudaFuncSetAttribute(decode_sct_kernel<T, EXACT, W, GL>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    cudaError_t e = cudaFuncSetAttribute(decode_sct_kernel<T, EXACT, W, GL, HG>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
-    return cudaOccupancyMaxActiveBlocksPerMultiprocessor(bps, decode_sct_kernel<T, EXACT, W, GL>, 32 * W, smem);
+    return cudaOccupancyMaxActiveBlocksPerMultiprocessor(bps, decode_sct_kernel<T, EXACT, W, GL, HG>, 32 * W, smem);
 }
-template <typename T, bool EXACT, int W, bool GL>
+template <typename T, bool EXACT, int W, bool GL, bool HG>
 static cudaError_t go(const Args& s, int blocks, cudaStream_t st) {
     const size_t smem = smem_bytes<T>(s.a.n, s.vs, W);
-    cudaError_t e = cudaFuncSetAttribute(decode_sct_kernel<T, EXACT, W, GL>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);   // (the occupancy probe tries several sizes)
+    cudaError_t e = cudaFuncSetAttribute(decode_sct_kernel<T, EXACT, W, GL, HG>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);   // (the occupancy probe tries several sizes)
     if (e != cudaSuccess) return e;
-    decode_sct_kernel<T, EXACT, W, GL><<<blocks, 32 * W, smem, st>>>(s);
+    decode_sct_kernel<T, EXACT, W, GL, HG><<<blocks, 32 * W, smem, st>>>(s);
     return cudaGetLastError();
 }
 
 }  // namespace sct
 
 // W: 1, 2, 4 or 8 warps per tile.  vs: first level in shared memory (2 = all).
+#define PCB_SCT_G(FN, WW, GG, HH, ...)                                                                                   \
+    {                                                                                                                     \
+        if (exact) return sct::FN<double, true, WW, GG, HH>(__VA_ARGS__);                                                 \
+        return fp64 ? sct::FN<double, false, WW, GG, HH>(__VA_ARGS__) : sct::FN<float, false, WW, GG, HH>(__VA_ARGS__);   \
+    }
 #define PCB_SCT_W(FN, WW, ...)                                                                                            \
     {                                                                                                                     \
-        if (vs > 2) { if (exact) return sct::FN<double, true, WW, true>(__VA_ARGS__);                                     \
-                      return fp64 ? sct::FN<double, false, WW, true>(__VA_ARGS__) : sct::FN<float, false, WW, true>(__VA_ARGS__); }   \
-        if (exact) return sct::FN<double, true, WW, false>(__VA_ARGS__);                                                   \
-        return fp64 ? sct::FN<double, false, WW, false>(__VA_ARGS__) : sct::FN<float, false, WW, false>(__VA_ARGS__);      \
+        if (vs > 2 && n > 2048) PCB_SCT_G(FN, WW, true, true, __VA_ARGS__)                                                \
+        if (vs > 2) PCB_SCT_G(FN, WW, true, false, __VA_ARGS__)                                                           \
+        PCB_SCT_G(FN, WW, false, false, __VA_ARGS__)                                                                      \
     }
 #define PCB_SCT_DISPATCH(FN, ...)                   \
     if (W == 8) PCB_SCT_W(FN, 8, __VA_ARGS__)       \
@@ -454,6 +461,7 @@ cudaError_t launch_decode_sct(const DecodeArgs& a, const uint32_t* d_ops, int no
     s.a = a; s.ops = d_ops; s.nops = nops; s.pops = d_pops; s.npops = npops; s.bits = bits; s.ntiles = (a.B + 31) / 32;
     s.vs = vs; s.glev = glev;
     if (blocks > s.ntiles) blocks = s.ntiles;
+    const int n = a.n;
     static const bool dbg = getenv("PCB_DEBUG_SCT") != nullptr;
     if (dbg) fprintf(stderr, "sct launch: n %d W %d vs %d blocks %d nops %d npops %d fp64 %d exact %d pending error: %s\n", a.n, W, vs, blocks, nops, npops, fp64, exact,
                      cudaGetErrorString(cudaPeekAtLastError()));
