@@ -120,7 +120,11 @@ int pcb_decode_batch_f32(pcb_handle* h, const float* y, int* sol, int B);
 int pcb_decode_batch_f32_packed(pcb_handle* h, const float* y, uint32_t* sol_bits, int B);
 /* Device-resident variant: y_dev is a device pointer ([B][n] float if y_is_f32 else double),
  * sol_bits_dev a device pointer to [B][words] uint32. Runs on the handle's stream and
- * synchronises before returning. ms (may be NULL) receives the kernel time from CUDA events. */
+ * synchronises before returning. ms (may be NULL) receives the kernel time from CUDA events.
+ * Stream ordering of every *_dev entry point: the handle's stream is non-blocking; the call is
+ * ordered after the work already queued on the legacy default stream (where a torch caller's
+ * tensors are produced), and it returns with its own work complete. A caller that fills the
+ * buffers on other non-blocking streams synchronises those before calling. */
 int pcb_decode_batch_dev(pcb_handle* h, const void* y_dev, int y_is_f32, uint32_t* sol_bits_dev, int B,
                          float* ms);
 

@@ -203,7 +203,7 @@ struct pcb_handle {
     size_t redo_cap = 0;
     size_t scratch_per_warp = 0;
     cudaStream_t sc = nullptr, sin = nullptr, sout = nullptr;
-    cudaEvent_t ev_in[2] = {}, ev_k[2] = {}, ev_out[2] = {}, t0 = nullptr, t1 = nullptr;
+    cudaEvent_t ev_in[2] = {}, ev_k[2] = {}, ev_out[2] = {}, t0 = nullptr, t1 = nullptr, ev_caller = nullptr;
     uint32_t *d_info_mask = nullptr, *d_frozen_val = nullptr;
     uint16_t* d_info_pos = nullptr;
     unsigned char* d_scratch = nullptr;
@@ -295,9 +295,9 @@ static int configure(pcb_handle* h) {
         const char* we = getenv("PCB_T_W");
         const int wv = we ? atoi(we) : 0;
         // measured best shapes (B200, tools/sct_sweep.py): {W, VS} per (arithmetic, n); elsewhere 16 KB of shared-memory levels
-        int tw = exact ? (h->n <= 512 ? 2 : 4) : h->n <= 256 ? 1 : h->n == 512 ? 2 : 4, tvs = 0;
+        int tw = exact ? (h->n <= 256 ? 1 : h->n <= 512 ? 2 : 4) : h->n <= 256 ? 1 : h->n == 512 ? 2 : 4, tvs = 0;
         if (exact) tvs = 4;
-        else if (h->fp64) tvs = h->n == 2048 ? 5 : 4;
+        else if (h->fp64) tvs = h->n == 2048 ? 5 : h->n <= 256 ? 3 : 4;
         else { if (h->n >= 1024) tvs = 4; else if (h->n <= 256) tvs = 2; }     // (fp32, n = 1024: one warp / VS 5 is 13 % faster at 2^18 frames and 10 % slower at 2^20)
         h->sct_W = (wv == 1 || wv == 2 || wv == 4 || wv == 8) ? wv : tw;
         if (h->n < 512 && h->sct_W > 4) h->sct_W = 4;
@@ -420,6 +420,7 @@ pcb_handle* pcb_create(int device, int n, int k, int crc, int L, int decoder, in
         if ((e = cudaEventCreate(&h->ev_c0[s])) != cudaSuccess) return bail("event", e);
         if ((e = cudaEventCreate(&h->ev_c1[s])) != cudaSuccess) return bail("event", e);
     }
+    if ((e = cudaEventCreateWithFlags(&h->ev_caller, cudaEventDisableTiming)) != cudaSuccess) return bail("event", e);
     if ((e = cudaEventCreate(&h->t0)) != cudaSuccess) return bail("event", e);
     if ((e = cudaEventCreate(&h->t1)) != cudaSuccess) return bail("event", e);
     const int NW = (n + 31) / 32;
@@ -455,6 +456,7 @@ void pcb_destroy(pcb_handle* h) {
     if (h->comm) { NcclApi& nc = nccl_api(); if (nc.CommAbort) nc.CommAbort(h->comm); else nc.CommDestroy(h->comm); }
     cudaFree(h->d_red);
     cudaFreeHost(h->h_stage[0]); cudaFreeHost(h->h_stage[1]); delete h->narrow;
+    if (h->ev_caller) cudaEventDestroy(h->ev_caller);
     if (h->t0) cudaEventDestroy(h->t0);
     if (h->t1) cudaEventDestroy(h->t1);
     if (h->sc) cudaStreamDestroy(h->sc);
@@ -942,6 +944,14 @@ static int decode_host(pcb_handle* h, const void* y, int y_f32, int* sol, uint32
     return PCB_OK;
 }
 
+// The device-pointer entry points run on the handle's own non-blocking stream, which does not wait for the legacy default
+// stream the caller's buffers are usually produced on (torch's current stream unless the caller changed it): order the
+// call after everything already queued there.  (A caller with its own non-blocking streams synchronises them itself.)
+static cudaError_t after_callers_stream(pcb_handle* h) {
+    const cudaError_t e = cudaEventRecord(h->ev_caller, cudaStreamLegacy);
+    return e != cudaSuccess ? e : cudaStreamWaitEvent(h->sc, h->ev_caller, 0);
+}
+
 extern "C" {
 
 int pcb_decode_batch(pcb_handle* h, const double* y, int* sol, int B) { return decode_host(h, y, 0, sol, nullptr, B); }
@@ -956,6 +966,7 @@ int pcb_decode_batch_dev(pcb_handle* h, const void* y_dev, int y_is_f32, uint32_
     if (B <= 0) return B == 0 ? PCB_OK : fail(PCB_EINVAL, "B < 0");
     if (int r = ensure_device(h)) return r;
     DecodeArgs a = make_args(h, y_dev, y_is_f32, nullptr, sol_bits_dev, B);
+    CK(after_callers_stream(h));
     CK(cudaEventRecord(h->t0, h->sc));
     CK(launch(h, a, h->sc));
     CK(cudaEventRecord(h->t1, h->sc));
@@ -989,6 +1000,7 @@ int pcb_decode_batch_dev_noalloc(pcb_handle* h, const void* y_dev, int y_is_f32,
     if (per_block && (size_t)blocks > h->noalloc_bytes / per_block) blocks = (int)(h->noalloc_bytes / per_block);
     DecodeArgs a = make_args(h, y_dev, y_is_f32, nullptr, sol_bits_dev, B);
     a.scratch = h->d_noalloc;
+    CK(after_callers_stream(h));
     CK(launch_decode_generic(a, h->L, h->decoder, h->fp64, blocks, h->wpb, h->sc));
     h->launches++;
     CK(cudaStreamSynchronize(h->sc));
@@ -1025,6 +1037,7 @@ int pcb_encode_batch_dev(pcb_handle* h, const uint32_t* u_bits_dev, uint32_t* x_
     if (!h || !u_bits_dev || !x_bits_dev) return fail(PCB_EINVAL, "pcb_encode_batch_dev: null argument");
     if (B <= 0) return B == 0 ? PCB_OK : fail(PCB_EINVAL, "B < 0");
     if (int r = ensure_device(h)) return r;
+    CK(after_callers_stream(h));
     CK(cudaEventRecord(h->t0, h->sc));
     CK(launch_encode_packed(u_bits_dev, x_bits_dev, h->n, h->m, with_shuffle != 0, B, h->sm_count, h->sc));
     CK(cudaEventRecord(h->t1, h->sc));
@@ -1245,6 +1258,7 @@ int pcb_generate_batch_dev(pcb_handle* h, double snr_db, uint64_t seed, uint64_t
     if (int r = ensure_device(h)) return r;
     GenArgs g = gen_args(h, snr_db, seed, first_frame_id, B);
     g.y = y_dev; g.tx_bits = tx_bits_dev;
+    CK(after_callers_stream(h));
     CK(launch_generate(g, h->sm_count, h->sc));
     h->launches++;
     CK(cudaStreamSynchronize(h->sc));
@@ -1283,6 +1297,7 @@ int pcb_count_errors_dev(pcb_handle* h, const uint32_t* dec_bits_dev, const uint
     if (int r = ensure_device(h)) return r;
     if (!h->d_red) CK(cudaMalloc(&h->d_red, 8 * sizeof(unsigned long long)));
     const unsigned long long init[3] = {(unsigned long long)B, 0ull, 0ull};
+    CK(after_callers_stream(h));
     CK(cudaMemcpyAsync(h->d_red, init, sizeof init, cudaMemcpyHostToDevice, h->sc));
     if (B) {
         CK(launch_count(dec_bits_dev, tx_bits_dev, h->EW, h->decoder == 3 ? h->k : h->n, B, h->d_red + 1, h->sc));

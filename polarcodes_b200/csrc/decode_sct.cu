@@ -193,7 +193,7 @@ struct Tile {
     }
 
     // ---- level v (S = n >> v rows) from level v - 1; fuse: level v + 1 = f(level v) in the same pass ----
-    // SM: source and destinations are shared-memory levels (the serial ops of warp 0: at most 16 rows)
+    // SM: source and destinations are shared-memory levels (v - 1 >= vs)
     template <bool ISG, bool SM>
     __device__ __forceinline__ void level_t(int v, bool fuse, int nw, int wi) const {
         constexpr int U = PCB_T_U;
@@ -257,14 +257,13 @@ struct Tile {
         }
     }
     __device__ __forceinline__ void level(int v, bool isg, bool fuse, int nw, int wi) const {
-        if (isg) level_t<true, false>(v, fuse, nw, wi);
-        else level_t<false, false>(v, fuse, nw, wi);
-    }
-    __device__ __forceinline__ void level_serial(int v, bool isg, bool fuse) const {
-        if (GL && PCB_T_SERIAL_LDS && v - 1 >= vs) {
-            if (isg) level_t<true, true>(v, fuse, 1, 0);
-            else level_t<false, true>(v, fuse, 1, 0);
-        } else level(v, isg, fuse, 1, 0);
+        if (GL && PCB_T_SERIAL_LDS && v - 1 >= vs) {             // shared memory to shared memory
+            if (isg) level_t<true, true>(v, fuse, nw, wi);
+            else level_t<false, true>(v, fuse, nw, wi);
+        } else {
+            if (isg) level_t<true, false>(v, fuse, nw, wi);
+            else level_t<false, false>(v, fuse, nw, wi);
+        }
     }
 };
 
@@ -326,7 +325,7 @@ __global__ void __launch_bounds__(32 * W, EXACT ? 0 : (HG ? (sizeof(T) == 4 ? 24
                     __syncthreads();
                 } else {                                   // (warp 0 only: the other warps' list has no such op)
                     t.wk_w0 = wk.w0;
-                    t.level_serial(v, isg, fuse);
+                    t.level(v, isg, fuse, 1, 0);
                 }
             } else if (type == OP_NODE8) {
                 T a[8];

@@ -111,3 +111,22 @@ def test_double_device_batch_equals_float_batch():
         d.decode_dev(y64.data_ptr(), False, out.data_ptr(), B)
     torch.cuda.synchronize()
     assert torch.equal(out, ref)
+
+
+def test_dev_entry_points_wait_for_the_callers_default_stream():
+    """The handle's stream is non-blocking: a *_dev call is ordered after what the caller queued on the default stream
+    (include/polar_b200.h, pcb_decode_batch_dev), so a batch still being written there is decoded complete."""
+    n, k = 1024, 512
+    d = _handle(n, k, 0, 1, pb.SCMINSUM)
+    y, _ = _batch(d, n, 1 << 15)
+    ref = _decode(d, y)
+    for rep in range(3):
+        late = torch.zeros_like(y)
+        torch.cuda.synchronize()
+        filler = torch.randn(1 << 26, device="cuda")
+        for _ in range(4):
+            filler = filler * 1.0001 + 1.0                      # a few ms of queued work in front of the copy
+        late.copy_(y)
+        out = torch.zeros((y.shape[0], d.words), dtype=torch.int32, device="cuda")
+        d.decode_dev(late.data_ptr(), True, out.data_ptr(), y.shape[0])     # no synchronize in between
+        assert torch.equal(out, ref)
