@@ -110,7 +110,7 @@ __global__ void __launch_bounds__(32) decode_sc8_kernel(const __grid_constant__ 
     uint32_t* P = reinterpret_cast<uint32_t*>(smem_raw) + lane;           // level v >= 2 ((n >> v) / 4 rows) at row (n/2 - (n >> (v - 1))) / 4
     uint32_t* H = reinterpret_cast<uint32_t*>(smem_raw) + (((n >> 1) - 8) >> 2) * 32 + lane;
     uint32_t* G1 = S.glev + (size_t)blockIdx.x * (n >> 3) * 32 + lane;  // level 1
-    auto lev = [&](int v) -> uint32_t* { return v == 1 ? G1 : P + (((n >> 1) - (n >> (v - 1))) >> 2) * 32; };
+    auto levs = [&](int v) -> uint32_t* { return P + (((n >> 1) - (n >> (v - 1))) >> 2) * 32; };   // v >= 2: shared memory
 
     for (int tile = blockIdx.x; tile < S.ntiles; tile += gridDim.x) {
         const int frame = tile * 32 + lane, fr = min(frame, A.B - 1);
@@ -126,21 +126,26 @@ __global__ void __launch_bounds__(32) decode_sc8_kernel(const __grid_constant__ 
             const bool isg = (op >> 9) & 1u;
             if (type == sct::OP_LEVEL) {
                 const int Sz = n >> v, R = Sz >> 2;                      // elements, rows
-                const uint32_t* src = v == 1 ? y0 : lev(v - 1);
-                uint32_t* dst = lev(v);
-                if (isg) {
+                // one inlined copy per address-space pair (global -> global, global -> shared, shared -> shared): with a
+                // pointer selected at run time every access would be a generic LD / ST
+                auto run = [&](const uint32_t* __restrict__ src, uint32_t* __restrict__ dst) {
+                    if (isg) {
 #pragma unroll 4
-                    for (int r = 0; r < R; r++) {
-                        const int pos = Sz + 4 * r;
-                        const uint32_t nib = (Sz >= 32 ? H[(pos >> 5) * 32] >> (pos & 31) : wk.w0 >> pos) & 15u;
-                        dst[r * 32] = g4(src[r * 32], src[(r + R) * 32], nib);
+                        for (int r = 0; r < R; r++) {
+                            const int pos = Sz + 4 * r;
+                            const uint32_t nib = (Sz >= 32 ? H[(pos >> 5) * 32] >> (pos & 31) : wk.w0 >> pos) & 15u;
+                            dst[r * 32] = g4(src[r * 32], src[(r + R) * 32], nib);
+                        }
+                    } else {
+#pragma unroll 4
+                        for (int r = 0; r < R; r++) dst[r * 32] = f4(src[r * 32], src[(r + R) * 32]);
                     }
-                } else {
-#pragma unroll 4
-                    for (int r = 0; r < R; r++) dst[r * 32] = f4(src[r * 32], src[(r + R) * 32]);
-                }
+                };
+                if (v == 1) run(y0, G1);
+                else if (v == 2) run(G1, levs(2));
+                else run(levs(v - 1), levs(v));
             } else if (type == sct::OP_NODE8) {
-                const uint32_t* src = lev(m - 3);
+                const uint32_t* src = levs(m - 3);
                 const uint32_t p0 = src[0], p1 = src[32];
                 int a[8];
 #pragma unroll

@@ -9,9 +9,9 @@ R=$(cd "$(dirname "$0")/.." && pwd); D=$(mktemp -d)
 (cd $D && cuobjdump -xelf all $R/polarcodes_b200/libpolar_b200.so >/dev/null)
 for spec in "decode_scl8q:scl8q_kernelILi10ELi8EfLi0E:SCL-8 N=1024 float batch (headline C)" "decode_scl8q:scl8q_kernelILi10ELi8EfLi1E:SCL-8 N=1024 double batch (narrowing prologue)" \
             "decode_scl8q:scl8q_kernelILi11ELi32EfLi0E:SCL-32 N=2048 (config D)" "decode_scl8q:scl8q_kernelILi11ELi4EfLi0E:SCL-4 N=2048 (conf.txt)" \
-            "decode_scl8q:fork_slowILi8ELb0E:fork_slow<8> (out of line)" "decode_sct:sct_kernelIdLb0ELi4ELb1E:SC min-sum fp64, 4 warps per tile, global level slice (config A)" \
-            "decode_sct:sct_kernelIdLb1ELi2ELb1E:exact SC, 2 warps per tile (config B)" "decode_sc8:decode_sc8_kernel:8-bit SC" \
-            "decode_sc32:sc32big_kernelIdLb0E:SC min-sum fp64 n > 2048 (config E)"; do
+            "decode_scl8q:fork_slowILi8ELb0E:fork_slow<8> (out of line)" "decode_sct:sct_kernelIdLb0ELi4ELb1ELb0E:SC min-sum fp64, 4 warps per tile, global level slice, heap in shared memory (config A)" \
+            "decode_sct:sct_kernelIdLb1ELi1ELb1ELb0E:exact SC, 1 warp per tile (config B)" "decode_sct:sct_kernelIdLb0ELi4ELb1ELb1E:SC min-sum fp64 n > 2048, levels and heap in the global slice (config E)" "decode_sc8:decode_sc8_kernel:8-bit SC" \
+            "decode_sc32:sc32big_kernelIdLb0E:lane-per-frame SC min-sum fp64 n > 2048 (PCB_SC_LANE=1)"; do
   IFS=: read file pat label <<< "$spec"
   CUB=$(ls $D/${file}*.cubin | head -1)
   nvdisasm -c $CUB > $D/all.sass
