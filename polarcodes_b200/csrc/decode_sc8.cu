@@ -20,6 +20,12 @@
 #include "sc_ops.cuh"
 #include "sct_common.cuh"
 
+#include <cstdlib>
+
+#ifndef PCB_8_VS_DEFAULT
+#define PCB_8_VS_DEFAULT 5   // the first level kept in shared memory is at most level m - 5 (64 values)
+#endif
+
 namespace pcb {
 namespace sc8 {
 
@@ -61,7 +67,8 @@ struct Args {
     const uint32_t* ops;
     int nops;
     const uint32_t* yq;      // [tile][n/4][32] quantised channel values, bit-reversed order, four per word
-    uint32_t* glev;          // per block: level 1 (n/8 rows of 32 words; stays in L2), which halves the shared memory of a tile
+    uint32_t* glev;          // per block: levels 1 .. vs - 1 (stay in L2), which shrinks the shared memory of a tile
+    int vs;                  // first level in shared memory (2 or more)
     uint32_t* bits;          // [B][n/32] packed decisions
     int ntiles;
 };
@@ -107,10 +114,12 @@ __global__ void __launch_bounds__(32) decode_sc8_kernel(const __grid_constant__ 
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int lane = threadIdx.x;
     const int n = A.n, m = A.m, NW = n >> 5;
-    uint32_t* P = reinterpret_cast<uint32_t*>(smem_raw) + lane;           // level v >= 2 ((n >> v) / 4 rows) at row (n/2 - (n >> (v - 1))) / 4
-    uint32_t* H = reinterpret_cast<uint32_t*>(smem_raw) + (((n >> 1) - 8) >> 2) * 32 + lane;
-    uint32_t* G1 = S.glev + (size_t)blockIdx.x * (n >> 3) * 32 + lane;  // level 1
-    auto levs = [&](int v) -> uint32_t* { return P + (((n >> 1) - (n >> (v - 1))) >> 2) * 32; };   // v >= 2: shared memory
+    const int vs = S.vs, ntop = n >> (vs - 1);                           // bytes per frame of the levels from vs down: ntop - 8
+    uint32_t* P = reinterpret_cast<uint32_t*>(smem_raw) + lane;          // level v >= vs ((n >> v) / 4 rows) at row (ntop - (n >> (v - 1))) / 4
+    uint32_t* H = reinterpret_cast<uint32_t*>(smem_raw) + ((ntop - 8) >> 2) * 32 + lane;
+    uint32_t* G = S.glev + (size_t)blockIdx.x * ((n - ntop) >> 2) * 32 + lane;   // levels 1 .. vs - 1: level v at row (n - (n >> (v - 1))) / 4
+    auto levs = [&](int v) -> uint32_t* { return P + ((ntop - (n >> (v - 1))) >> 2) * 32; };      // v >= vs: shared memory
+    auto levg = [&](int v) -> uint32_t* { return G + ((n - (n >> (v - 1))) >> 2) * 32; };         // v < vs: the block's global slice
 
     for (int tile = blockIdx.x; tile < S.ntiles; tile += gridDim.x) {
         const int frame = tile * 32 + lane, fr = min(frame, A.B - 1);
@@ -141,8 +150,9 @@ __global__ void __launch_bounds__(32) decode_sc8_kernel(const __grid_constant__ 
                         for (int r = 0; r < R; r++) dst[r * 32] = f4(src[r * 32], src[(r + R) * 32]);
                     }
                 };
-                if (v == 1) run(y0, G1);
-                else if (v == 2) run(G1, levs(2));
+                if (v == 1) run(y0, levg(1));
+                else if (v < vs) run(levg(v - 1), levg(v));
+                else if (v == vs) run(levg(v - 1), levs(v));
                 else run(levs(v - 1), levs(v));
             } else if (type == sct::OP_NODE8) {
                 const uint32_t* src = levs(m - 3);
@@ -168,17 +178,32 @@ __global__ void __launch_bounds__(32) decode_sc8_kernel(const __grid_constant__ 
     }
 }
 
-static size_t smem_bytes(int n) { return (size_t)(((n >> 1) - 8) >> 2) * 128 + (size_t)(n >> 5) * 128; }
+static size_t smem_bytes(int n, int vs) { return (size_t)(((n >> (vs - 1)) - 8) >> 2) * 128 + (size_t)(n >> 5) * 128; }
+// first shared-memory level: the smallest one that lets an SM hold 32 one-warp blocks (the hardware's limit; 6 KB per tile),
+// at most m - 5 (64 values) -- n = 1024: 115 M frames/s with 10 blocks per SM (vs 2), 138 with 32 (vs 5); n = 256: vs 2; n = 2048: vs 6
+static int first_smem_level(int m) {
+    static const char* e = getenv("PCB_8_VS");
+    int vs = 2;
+    while (vs < m - PCB_8_VS_DEFAULT && smem_bytes(1 << m, vs) > 6144) vs++;
+    if (e) vs = atoi(e);
+    if (vs < 2) vs = 2;
+    if (vs > m - 3) vs = m - 3;
+    return vs;
+}
 
 }  // namespace sc8
 
 bool sc8_supported(int m) { return m >= 6 && m <= 12; }
 size_t sc8_yq_bytes(int n, int B) { return (size_t)((B + 31) / 32) * 32 * (size_t)n; }
-size_t sc8_glev_bytes(int n, int blocks) { return (size_t)blocks * (n >> 3) * 128; }
+size_t sc8_glev_bytes(int n, int blocks) {
+    int m = 0;
+    while ((1 << m) < n) m++;
+    return (size_t)blocks * ((n - (n >> (sc8::first_smem_level(m) - 1))) >> 2) * 128;
+}
 
 cudaError_t sc8_occupancy(int m, int* bps, size_t* smem) {
     const int n = 1 << m;
-    *smem = sc8::smem_bytes(n);
+    *smem = sc8::smem_bytes(n, sc8::first_smem_level(m));
     if (*smem > 227 * 1024) { *bps = 0; return cudaSuccess; }
     cudaError_t e = cudaFuncSetAttribute(sc8::decode_sc8_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)*smem);
     if (e != cudaSuccess) return e;
@@ -219,7 +244,8 @@ cudaError_t launch_decode_sc8(const DecodeArgs& a, int qfraction, const uint32_t
     sc8::Args s;
     s.a = a; s.ops = d_ops; s.nops = nops; s.yq = yq; s.glev = glev; s.bits = bits; s.ntiles = ntiles;
     if (blocks > ntiles) blocks = ntiles;
-    const size_t smem = sc8::smem_bytes(a.n);
+    s.vs = sc8::first_smem_level(a.m);
+    const size_t smem = sc8::smem_bytes(a.n, s.vs);
     e = cudaFuncSetAttribute(sc8::decode_sc8_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
     sc8::decode_sc8_kernel<<<blocks, 32, smem, st>>>(s);

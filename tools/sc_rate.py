@@ -13,6 +13,8 @@ CONFIGS = [
     ("A  SCMinsum 1024/512 fp64", 1024, 512, pb.SCMINSUM, pb.STRICT, 1 << 18),
     ("A' SCMinsum 1024/512 fp32", 1024, 512, pb.SCMINSUM, pb.FP32, 1 << 18),
     ("A8 SCMinsum 1024/512 int8 q2", 1024, 512, pb.SCMINSUM, pb.int8_q(2), 1 << 18),
+    ("8  SCMinsum 256/128 int8 q2", 256, 128, pb.SCMINSUM, pb.int8_q(2), 1 << 18),
+    ("8  SCMinsum 2048/1024 int8 q2", 2048, 1024, pb.SCMINSUM, pb.int8_q(2), 1 << 17),
     ("B  SC exact 256/128", 256, 128, pb.SC, pb.STRICT, 1 << 18),
     ("   SCMinsum 256/128 fp64", 256, 128, pb.SCMINSUM, pb.STRICT, 1 << 18),
     ("   SCMinsum 512/256 fp64", 512, 256, pb.SCMINSUM, pb.STRICT, 1 << 18),
