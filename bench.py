@@ -206,7 +206,7 @@ def sweep_configs(pb, torch, dev, peaks, traffic):
         ("C_crc16", "SCLDecoderMinsum L=8 N=1024 K=512 crc=16 (double y)", pb.SCLMINSUM, 1024, 512, 16, 8, pb.STRICT, True, 1 << 20),
         ("conf_txt", "SCLDecoderMinsum L=4 N=2048 K=1024 crc=16 (the reference's shipped conf.txt; double y)", pb.SCLMINSUM, 2048, 1024, 16, 4, pb.STRICT, True, 1 << 18),
         ("D", "SCLDecoderMinsum L=32 N=2048 K=1024 crc=0 (double y)", pb.SCLMINSUM, 2048, 1024, 0, 32, pb.STRICT, True, 1 << 16),
-        ("E", "SCDecoderMinsum N=32768 K=16384 fp64 (double y)", pb.SCMINSUM, 32768, 16384, 0, 1, pb.STRICT, True, 1 << 15),
+        ("E", "SCDecoderMinsum N=32768 K=16384 fp64 (double y)", pb.SCMINSUM, 32768, 16384, 0, 1, pb.STRICT, True, 1 << 16),
     ]
     out = []
     for key, label, decoder, n, k, crc, L, prec, dbl, B in cfgs:
