@@ -10,6 +10,9 @@
 // Bits are packed 32 per word; butterfly stages with stride < 32 are in-word shifts/XORs,
 // larger strides are word XORs in shared memory.
 #include "aux_kernels.h"
+
+#include <cstdint>
+#include <cstdlib>
 #include "gen_common.cuh"
 
 namespace pcb {
@@ -72,21 +75,51 @@ cudaError_t launch_encode(const int* d_u, int* d_x, int n, int m, int with_shuff
     return cudaGetLastError();
 }
 
+// One exchange of the bit-reversal network below: lane bit s of a word's holder swaps with bit log2(D) of the bit positions
+// (M: the positions where that bit is 0).
+__device__ __forceinline__ uint32_t brev_stage(uint32_t v, int lane, int s, int D, uint32_t M) {
+    const uint32_t y = __shfl_xor_sync(0xffffffffu, v, 1 << s);
+    return ((lane >> s) & 1) ? (v & ~M) | ((y & ~M) >> D) : (v & M) | ((y & M) << D);
+}
+__device__ __forceinline__ int pad32(int a) { return a + (a >> 5); }      // one spare word per 32: strided rows without bank conflicts
+
 // The same encoder on packed frames: u_bits / x_bits are [B][max(n/32, 1)] words, bit t of a frame at word t / 32, bit t % 32.
 // 2 * n / 8 bytes of HBM traffic per frame instead of 8 n.
+// ReverseShuffle (Resources.cpp:148-158) for n >= 1024, on words: index i = (j, c, t) with j the top five bits, t the low
+// five (the bit inside a word) goes to (brev5(t), brev(c), brev5(j)).  For a fixed c the 32 words j = 0..31 form a
+// 32 x 32 bit matrix that has to be transposed with both indices bit-reversed: five shuffle stages, stage s exchanging
+// lane bit s with position bit 4 - s, do exactly that (lane j holds word j before, lane t' = brev5(t) the output word
+// after).  40 instructions per 32 words instead of 32 ballots with their gathers.
 __global__ void __launch_bounds__(128) encode_packed_kernel(const uint32_t* __restrict__ u, uint32_t* __restrict__ x, int n, int m,
                                                             int with_shuffle, int B) {
     extern __shared__ uint32_t enc_smem[];
     const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5, wpb = blockDim.x >> 5;
     const int NW = n >= 32 ? n / 32 : 1;
-    uint32_t* W = enc_smem + wib * 2 * NW;
-    uint32_t* U = W + NW;
+    const int NP = NW + (NW >> 5) + 1;                      // padded length
+    uint32_t* W = enc_smem + wib * 2 * NP;
+    uint32_t* U = W + NP;
     for (int frame = blockIdx.x * wpb + wib; frame < B; frame += gridDim.x * wpb) {
         const uint32_t* uf = u + (size_t)frame * NW;
-        if (with_shuffle) {
+        if (with_shuffle && m >= 10) {
+            const int S = NW >> 5, sb = m - 10;
+            for (int a = lane; a < NW; a += 32) W[pad32(a)] = uf[a];
+            __syncwarp();
+            for (int c = 0; c < S; c++) {
+                uint32_t v = W[pad32(lane * S + c)];
+                v = brev_stage(v, lane, 0, 16, 0x0000FFFFu);
+                v = brev_stage(v, lane, 1, 8, 0x00FF00FFu);
+                v = brev_stage(v, lane, 2, 4, 0x0F0F0F0Fu);
+                v = brev_stage(v, lane, 3, 2, 0x33333333u);
+                v = brev_stage(v, lane, 4, 1, 0x55555555u);
+                const int cr = sb ? (int)(__brev((unsigned)c) >> (32 - sb)) : 0;
+                U[pad32(lane * S + cr)] = v;
+            }
+            __syncwarp();
+            for (int a = lane; a < NW; a += 32) W[a] = U[pad32(a)];
+        } else if (with_shuffle) {
             for (int a = lane; a < NW; a += 32) U[a] = uf[a];
             __syncwarp();
-            for (int w = 0; w < NW; w++) {                 // bit-reversed gather (Resources.cpp:148-158), one output word per ballot
+            for (int w = 0; w < NW; w++) {                 // n < 1024: bit-reversed gather, one output word per ballot
                 const int i = w * 32 + lane;
                 int bit = 0;
                 if (i < n) {
@@ -107,12 +140,95 @@ __global__ void __launch_bounds__(128) encode_packed_kernel(const uint32_t* __re
     }
 }
 
+// n = 1024 S (S = 1, 2, 4): the frame lives in registers, lane l holds words l S .. l S + S - 1 -- exactly the operands of the
+// bit-reversal network above (word (j, c) in lane j) and of its result (word (t', brev(c)) in lane t').  The cross-word
+// stages of the transform are register XORs (distance < S) and shuffles (distance / S lanes); no shared memory, F
+// frames per warp in flight.
+template <int S, int F>
+__global__ void __launch_bounds__(256) encode_packed_reg_kernel(const uint32_t* __restrict__ u, uint32_t* __restrict__ x, int with_shuffle, int B) {
+    constexpr int NW = 32 * S;
+    constexpr int LS = S == 1 ? 0 : S == 2 ? 1 : 2;
+    const int lane = threadIdx.x & 31;
+    const long warp = ((long)blockIdx.x * blockDim.x + threadIdx.x) >> 5, nwarps = ((long)gridDim.x * blockDim.x) >> 5;
+    for (long f0 = warp * F; f0 < B; f0 += nwarps * F) {
+        uint32_t v[F][S];
+#pragma unroll
+        for (int k = 0; k < F; k++) {
+            const long f = f0 + k < B ? f0 + k : (long)B - 1;
+            const uint32_t* p = u + f * NW + lane * S;
+            if constexpr (S == 1) v[k][0] = __ldg(p);
+            else if constexpr (S == 2) { const uint2 t = __ldg(reinterpret_cast<const uint2*>(p)); v[k][0] = t.x; v[k][1] = t.y; }
+            else { const uint4 t = __ldg(reinterpret_cast<const uint4*>(p)); v[k][0] = t.x; v[k][1] = t.y; v[k][2] = t.z; v[k][3] = t.w; }
+        }
+#pragma unroll
+        for (int k = 0; k < F; k++) {
+            if (with_shuffle) {
+                uint32_t o[S];
+#pragma unroll
+                for (int c = 0; c < S; c++) {
+                    uint32_t w = v[k][c];
+                    w = brev_stage(w, lane, 0, 16, 0x0000FFFFu);
+                    w = brev_stage(w, lane, 1, 8, 0x00FF00FFu);
+                    w = brev_stage(w, lane, 2, 4, 0x0F0F0F0Fu);
+                    w = brev_stage(w, lane, 3, 2, 0x33333333u);
+                    w = brev_stage(w, lane, 4, 1, 0x55555555u);
+                    constexpr int R4[4] = {0, 2, 1, 3};
+                    o[LS == 2 ? R4[c & 3] : c] = w;              // brev(c) over log2(S) bits (S = 2: identity)
+                }
+#pragma unroll
+                for (int c = 0; c < S; c++) v[k][c] = o[c];
+            }
+#pragma unroll
+            for (int r = 0; r < S; r++) v[k][r] = inword_transform(v[k][r], 32);
+#pragma unroll
+            for (int sw = 1; sw < S; sw <<= 1)
+#pragma unroll
+                for (int r = 0; r < S; r++)
+                    if (!(r & sw)) v[k][r] ^= v[k][r + sw];
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1)
+#pragma unroll
+                for (int r = 0; r < S; r++) {
+                    const uint32_t y = __shfl_xor_sync(0xffffffffu, v[k][r], d);
+                    if (!(lane & d)) v[k][r] ^= y;
+                }
+        }
+#pragma unroll
+        for (int k = 0; k < F; k++) {
+            if (f0 + k >= B) break;
+            uint32_t* q = x + (f0 + k) * NW + lane * S;
+            if constexpr (S == 1) *q = v[k][0];
+            else if constexpr (S == 2) *reinterpret_cast<uint2*>(q) = make_uint2(v[k][0], v[k][1]);
+            else *reinterpret_cast<uint4*>(q) = make_uint4(v[k][0], v[k][1], v[k][2], v[k][3]);
+        }
+    }
+}
+
+template <int S, int F>
+static cudaError_t launch_encode_reg(const uint32_t* d_u, uint32_t* d_x, int with_shuffle, int B, int sm_count, cudaStream_t st) {
+    long blocks = ((long)B + 8 * F - 1) / (8 * F);
+    if (blocks > (long)sm_count * 8) blocks = (long)sm_count * 8;
+    encode_packed_reg_kernel<S, F><<<(int)blocks, 256, 0, st>>>(d_u, d_x, with_shuffle, B);
+    return cudaGetLastError();
+}
+
 cudaError_t launch_encode_packed(const uint32_t* d_u, uint32_t* d_x, int n, int m, int with_shuffle, int B, int sm_count, cudaStream_t st) {
+    if (((reinterpret_cast<uintptr_t>(d_u) | reinterpret_cast<uintptr_t>(d_x)) & 15) == 0 && !getenv("PCB_ENC_SMEM")) {   // (vector accesses)
+        if (n == 1024) return launch_encode_reg<1, 4>(d_u, d_x, with_shuffle, B, sm_count, st);
+        if (n == 2048) return launch_encode_reg<2, 4>(d_u, d_x, with_shuffle, B, sm_count, st);
+        if (n == 4096) return launch_encode_reg<4, 2>(d_u, d_x, with_shuffle, B, sm_count, st);
+    }
     const int wpb = 4;
     const int NW = n >= 32 ? n / 32 : 1;
+    const int NP = NW + (NW >> 5) + 1;
     int blocks = (B + wpb - 1) / wpb;
     if (blocks > sm_count * 16) blocks = sm_count * 16;
-    encode_packed_kernel<<<blocks, wpb * 32, (size_t)wpb * 2 * NW * 4, st>>>(d_u, d_x, n, m, with_shuffle, B);
+    const size_t smem = (size_t)wpb * 2 * NP * 4;
+    if (smem > 48 * 1024) {
+        const cudaError_t e = cudaFuncSetAttribute(encode_packed_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return e;
+    }
+    encode_packed_kernel<<<blocks, wpb * 32, smem, st>>>(d_u, d_x, n, m, with_shuffle, B);
     return cudaGetLastError();
 }
 
