@@ -67,7 +67,10 @@
 #define PCB_Q_GH 1         // N = 2048, 16/32 paths: the two largest partial-sum layers in the global scratch
 #endif
 #ifndef PCB_Q_GH_SMALL
-#define PCB_Q_GH_SMALL 0   // the same for the other N >= 1024 variants
+#define PCB_Q_GH_SMALL 0   // the same for the N = 1024 variants
+#endif
+#ifndef PCB_Q_GH_M11
+#define PCB_Q_GH_M11 1     // N = 2048, 2..8 paths (the shipped conf.txt): 20 instead of 26 KB of shared memory per warp, 11 resident warps instead of 8
 #endif
 #ifndef PCB_Q_RL3
 #define PCB_Q_RL3 1        // N = 2048, 16/32 paths: layer 3 is never stored -- the g of layer 4 recomputes it from the channel values
@@ -147,7 +150,7 @@ struct Geo {
     // Partial-sum heap of a slot: the layer of size S at words [S/32, 2S/32).  GH: the two largest
     // layers (words >= SPLITW, three quarters of the heap) live in the global scratch as
     // [word][slot]; they are touched at the top-stage events and by the rare big combines only.
-    static constexpr bool GH = M >= 10 && ((M >= 11 && LL >= 16) ? PCB_Q_GH : PCB_Q_GH_SMALL);
+    static constexpr bool GH = M >= 10 && (M >= 11 ? (LL >= 16 ? PCB_Q_GH : PCB_Q_GH_M11) : PCB_Q_GH_SMALL);
     static constexpr int SPLITW = GH ? NW / 4 : (1 << 20);
     static constexpr int HS = GH ? SPLITW + 1 : NW + 1;       // slot stride of the shared-memory part
     static constexpr int XHS = NW + 1;      // slot stride of the final codeword estimates
