@@ -79,6 +79,7 @@ __global__ void __launch_bounds__(256) sc8_quantise_kernel(const YT* __restrict_
     extern __shared__ uint32_t sm[];                   // [32 frames][n/4 + 1] words
     const int W4 = n >> 2, stride = W4 + 1;
     for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+#pragma unroll 2
         for (int idx = threadIdx.x; idx < 32 * W4; idx += 256) {      // four consecutive source values per thread: coalesced
             const int f = idx / W4, c = idx - f * W4;
             const int frame = min(tile * 32 + f, B - 1);
@@ -228,7 +229,10 @@ cudaError_t launch_decode_sc8(const DecodeArgs& a, int qfraction, const uint32_t
     const int ntiles = (a.B + 31) / 32;
     const float scale = (float)(2 << qfraction);
     const size_t qsm = (size_t)32 * ((a.n >> 2) + 1) * 4;
-    int qb = ntiles < sm_count * 4 ? ntiles : sm_count * 4;
+    int qpb = (int)((227 * 1024) / (qsm + 1024));             // blocks an SM holds (33 KB each at n = 1024)
+    if (qpb > 8) qpb = 8;
+    if (qpb < 1) qpb = 1;
+    int qb = ntiles < sm_count * qpb ? ntiles : sm_count * qpb;
     cudaError_t e;
     if (a.y_f32) {
         e = cudaFuncSetAttribute(sc8::sc8_quantise_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)qsm);
