@@ -69,6 +69,9 @@
 #ifndef PCB_Q_GH_SMALL
 #define PCB_Q_GH_SMALL 0   // the same for the N = 1024 variants
 #endif
+#ifndef PCB_Q_GH_M10S
+#define PCB_Q_GH_M10S 0    // N = 1024, 2 or 4 paths: measured L = 4 +2 % (12 warps instead of 10), L = 2 -5 %: off
+#endif
 #ifndef PCB_Q_GH_M11
 #define PCB_Q_GH_M11 1     // N = 2048, 2..8 paths (the shipped conf.txt): 20 instead of 26 KB of shared memory per warp, 11 resident warps instead of 8
 #endif
@@ -150,7 +153,7 @@ struct Geo {
     // Partial-sum heap of a slot: the layer of size S at words [S/32, 2S/32).  GH: the two largest
     // layers (words >= SPLITW, three quarters of the heap) live in the global scratch as
     // [word][slot]; they are touched at the top-stage events and by the rare big combines only.
-    static constexpr bool GH = M >= 10 && (M >= 11 ? (LL >= 16 ? PCB_Q_GH : PCB_Q_GH_M11) : PCB_Q_GH_SMALL);
+    static constexpr bool GH = M >= 10 && (M >= 11 ? (LL >= 16 ? PCB_Q_GH : PCB_Q_GH_M11) : LL <= 4 ? PCB_Q_GH_M10S : PCB_Q_GH_SMALL);
     static constexpr int SPLITW = GH ? NW / 4 : (1 << 20);
     static constexpr int HS = GH ? SPLITW + 1 : NW + 1;       // slot stride of the shared-memory part
     static constexpr int XHS = NW + 1;      // slot stride of the final codeword estimates
