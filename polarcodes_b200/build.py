@@ -7,6 +7,7 @@ import os
 import shutil
 import subprocess
 import sys
+from concurrent.futures import ThreadPoolExecutor
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
@@ -37,14 +38,19 @@ def build(force=False, verbose=False):
     headers = [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith((".h", ".cuh"))]
     headers.append(os.path.join(os.path.dirname(HERE), "include", "polar_b200.h"))
     headers.append(os.path.abspath(__file__))
-    objs = []
+    objs, cmds = [], []
     for src in CUDA_SOURCES + CXX_SOURCES:
         sp = os.path.join(CSRC, src)
         op = os.path.join(OBJ, src + ".o")
         objs.append(op)
         if force or _stale(op, [sp] + headers):
-            cmd = [_nvcc()] + ARCH + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-c", sp, "-o", op]
-            subprocess.check_call(cmd)
+            cmds.append([_nvcc()] + ARCH + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-c", sp, "-o", op])
+    # the translation units are independent: compile them side by side (the two largest take about a minute each)
+    jobs = max(1, min(len(cmds), int(os.environ.get("PCB_BUILD_JOBS", "0")) or (os.cpu_count() or 1)))
+    with ThreadPoolExecutor(max_workers=jobs) as pool:
+        for rc, cmd in zip(pool.map(lambda c: subprocess.call(c), cmds), cmds):
+            if rc:
+                raise subprocess.CalledProcessError(rc, cmd)
     if force or _stale(OUT, objs):
         subprocess.check_call([_nvcc()] + ARCH + ["-shared", "-o", OUT] + objs + ["-lcudart", "-ldl"])
     return OUT
