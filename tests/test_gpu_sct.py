@@ -94,3 +94,30 @@ def test_exact_sc_tile_kernel_against_generic_kernel():
     y = _batch(n, 4096, code.sigma, 3, "gauss")
     a, b = fast.decode(y), slow.decode(y)
     assert ((a != b).any(axis=1)).sum() <= 2
+
+
+@pytest.mark.parametrize("n,k,prec,W,VS", [
+    (1024, 512, pb.STRICT, 1, 2), (1024, 512, pb.STRICT, 2, 3), (1024, 512, pb.STRICT, 4, 5), (1024, 512, pb.STRICT, 8, 4),
+    (1024, 512, pb.FP32, 1, 5), (1024, 512, pb.FP32, 2, 2), (1024, 512, pb.FP32, 8, 6), (256, 128, pb.STRICT, 2, 2),
+    (256, 128, pb.FP32, 4, 3), (2048, 1024, pb.STRICT, 2, 6), (4096, 2048, pb.STRICT, 1, 6), (4096, 2048, pb.STRICT, 2, 4),
+    (4096, 2048, pb.FP32, 8, 6), (8192, 4096, pb.STRICT, 4, 7)])
+def test_every_launch_shape_decodes_the_same(monkeypatch, n, k, prec, W, VS):
+    """Warps per tile and the first shared-memory level select different instantiations of the kernel (levels addressed as
+    shared memory, as global memory, or through generic pointers; heap in shared memory or in the block's global slice):
+    each one must give the bits of the reference-literal kernel."""
+    monkeypatch.setenv("PCB_T_W", str(W))
+    monkeypatch.setenv("PCB_T_VS", str(VS))
+    try:
+        fast, code = _dec(n, k, pb.SCMINSUM, prec)
+    except pb.PolarError:
+        pytest.skip("shape does not fit an SM")
+    monkeypatch.delenv("PCB_T_W")
+    monkeypatch.delenv("PCB_T_VS")
+    i = fast.info()
+    if (i["warps_per_block"], i["first_smem_layer"]) != (W, VS):
+        pytest.skip(f"shape not honoured for this code: {i}")
+    slow, _ = _dec(n, k, pb.SCMINSUM, prec, generic=True)
+    for kind, B in (("gauss", 700), ("quantised", 65)):
+        y = _batch(n, B, code.sigma, n + W + VS, kind)
+        bad = np.flatnonzero((fast.decode(y) != slow.decode(y)).any(axis=1))
+        assert bad.size == 0, f"n={n} W={W} VS={VS} {kind}: frames {bad[:8]} differ"
