@@ -183,7 +183,7 @@ static size_t smem_bytes(int n, int vs) { return (size_t)(((n >> (vs - 1)) - 8) 
 // first shared-memory level: the smallest one that lets an SM hold 32 one-warp blocks (the hardware's limit; 6 KB per tile),
 // at most m - 5 (64 values) -- n = 1024: 115 M frames/s with 10 blocks per SM (vs 2), 138 with 32 (vs 5); n = 256: vs 2; n = 2048: vs 6
 static int first_smem_level(int m) {
-    static const char* e = getenv("PCB_8_VS");
+    const char* e = getenv("PCB_8_VS");
     int vs = 2;
     while (vs < m - PCB_8_VS_DEFAULT && smem_bytes(1 << m, vs) > 6144) vs++;
     if (e) vs = atoi(e);

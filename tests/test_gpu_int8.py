@@ -84,3 +84,14 @@ def test_driver_runs_the_8_bit_mode_with_conf_txt_qfraction(tmp_path):
     d, _ = _dec(1024, 512, 3, snr=2.5)
     want = d.montecarlo(2.5, 50000, seed=77)
     assert (int(row[1]), int(row[2])) == (want["frames"], want["frame_errors"])
+
+
+@pytest.mark.parametrize("n,k,vs", [(1024, 512, 2), (1024, 512, 3), (1024, 512, 7), (2048, 1024, 4), (256, 128, 4), (64, 32, 3)])
+def test_int8_mode_with_every_first_shared_memory_level(oracle, monkeypatch, n, k, vs):
+    """PCB_8_VS moves levels between shared memory and the block's global slice (three inlined copies of the level op, one
+    per address-space pair): the bits stay those of the definition."""
+    monkeypatch.setenv("PCB_8_VS", str(vs))
+    d, code = _dec(n, k, 2)
+    rng = np.random.default_rng(n + vs)
+    y = 1.0 + code.sigma * rng.standard_normal((500, n))
+    assert (d.decode(y) == oracle.decode_int8(n, 2, y, code.mask)).all()
