@@ -22,6 +22,9 @@
 
 #include <cstdlib>
 
+#ifndef PCB_8_QU
+#define PCB_8_QU 4           // frames per iteration of the fused quantiser (4 x 4 loads in flight per lane)
+#endif
 #ifndef PCB_8_VS_DEFAULT
 #define PCB_8_VS_DEFAULT 5   // the first level kept in shared memory is at most level m - 5 (64 values)
 #endif
@@ -66,12 +69,23 @@ struct Args {
     DecodeArgs a;
     const uint32_t* ops;
     int nops;
-    const uint32_t* yq;      // [tile][n/4][32] quantised channel values, bit-reversed order, four per word
+    uint32_t* yq;            // quantised channel values, bit-reversed order, four per word: [tile][n/4][32] from the pre-pass, or
+                             // (fused) one [n/4][32] slice per block that the tile's prologue fills
+    int fused;               // the decoding warp quantises its own tile (no pre-pass)
+    float scale;
     uint32_t* glev;          // per block: levels 1 .. vs - 1 (stay in L2), which shrinks the shared memory of a tile
     int vs;                  // first level in shared memory (2 or more)
     uint32_t* bits;          // [B][n/32] packed decisions
     int ntiles;
 };
+
+// q(y) = clamp(rint(y * scale), -127, 127) in double as the definition has it (oracle po_q8: round to nearest even, NaN -> -127):
+// the conversion instruction rounds the same way and saturates, the compare sends NaN and everything below -127 to -127
+__device__ __forceinline__ int q8i(double v, double sc) {
+    const double p = v * sc;
+    return p >= -127. ? min(127, __double2int_rn(p)) : -127;
+}
+__device__ __forceinline__ uint32_t q8(double v, double sc) { return (uint32_t)q8i(v, sc) & 0xFFu; }
 
 // y[B][n] (double or float) -> yq[tile][x4][lane]: byte j of the word = q(y[frame][bitrev(4 x4 + j)]), frame = tile * 32 + lane
 template <typename YT>
@@ -84,21 +98,18 @@ __global__ void __launch_bounds__(256) sc8_quantise_kernel(const YT* __restrict_
             const int f = idx / W4, c = idx - f * W4;
             const int frame = min(tile * 32 + f, B - 1);
             const YT* src = y + (size_t)frame * n + 4 * c;
-            float v[4];
+            int v[4];
             if constexpr (sizeof(YT) == 8) {
                 const double2 p0 = *reinterpret_cast<const double2*>(src), p1 = *reinterpret_cast<const double2*>(src + 2);
-                // rint(y * scale) in double as the definition has it; the clamp makes the narrowing exact
-                v[0] = (float)fmax(-127., fmin(127., rint(p0.x * (double)scale))); v[1] = (float)fmax(-127., fmin(127., rint(p0.y * (double)scale)));
-                v[2] = (float)fmax(-127., fmin(127., rint(p1.x * (double)scale))); v[3] = (float)fmax(-127., fmin(127., rint(p1.y * (double)scale)));
+                v[0] = q8i(p0.x, (double)scale); v[1] = q8i(p0.y, (double)scale); v[2] = q8i(p1.x, (double)scale); v[3] = q8i(p1.y, (double)scale);
             } else {
                 const float4 p = *reinterpret_cast<const float4*>(src);
-                v[0] = (float)fmax(-127., fmin(127., rint((double)p.x * (double)scale))); v[1] = (float)fmax(-127., fmin(127., rint((double)p.y * (double)scale)));
-                v[2] = (float)fmax(-127., fmin(127., rint((double)p.z * (double)scale))); v[3] = (float)fmax(-127., fmin(127., rint((double)p.w * (double)scale)));
+                v[0] = q8i((double)p.x, (double)scale); v[1] = q8i((double)p.y, (double)scale); v[2] = q8i((double)p.z, (double)scale); v[3] = q8i((double)p.w, (double)scale);
             }
 #pragma unroll
             for (int j = 0; j < 4; j++) {
                 const int x = (int)(__brev((unsigned)(4 * c + j)) >> (32 - m));
-                reinterpret_cast<signed char*>(sm + f * stride)[x] = (signed char)(int)v[j];
+                reinterpret_cast<signed char*>(sm + f * stride)[x] = (signed char)v[j];
             }
         }
         __syncthreads();
@@ -110,7 +121,36 @@ __global__ void __launch_bounds__(256) sc8_quantise_kernel(const YT* __restrict_
     }
 }
 
-__global__ void __launch_bounds__(32) decode_sc8_kernel(const __grid_constant__ Args S) {
+// The quantiser as the prologue of a tile (same mapping as sc8_quantise_kernel): lane l of step g reads the values at offset
+// o = 32 g + l of the four quarters of a frame (coalesced), packs them into word x4 = bitrev(o) of that frame (byte j holds
+// quarter bitrev2(j)), and a 32 x 32 word transpose through shared memory turns 32 frames into rows [x4][lane = frame].
+// The DRAM reads of one tile then overlap the decoding of the other tiles of the SM instead of being a pass of their own.
+template <typename YT>
+__device__ __forceinline__ void quantise_tile(const YT* __restrict__ y, int n, int m, int B, int tile, double sc, uint32_t* __restrict__ slice,
+                                              uint32_t* tb, int lane) {
+    const int Q = n >> 2;
+    constexpr int QU = PCB_8_QU;
+    for (int g0 = 0; g0 < Q; g0 += 32) {
+        const int o = g0 + lane;
+        const bool act = o < Q;
+#pragma unroll QU
+        for (int f = 0; f < 32; f++) {
+            const int frame = min(tile * 32 + f, B - 1);
+            const YT* src = y + (size_t)frame * n + (act ? o : 0);
+            const YT v0 = src[0], v1 = src[Q], v2 = src[2 * Q], v3 = src[3 * Q];
+            tb[lane * 33 + f] = q8((double)v0, sc) | (q8((double)v2, sc) << 8) | (q8((double)v1, sc) << 16) | (q8((double)v3, sc) << 24);
+        }
+        __syncwarp();
+        const int rows = min(32, Q - g0);
+        for (int r = 0; r < rows; r++) {
+            const int x4 = (int)(__brev((unsigned)(g0 + r)) >> (32 - (m - 2)));
+            slice[x4 * 32 + lane] = tb[r * 33 + lane];
+        }
+        __syncwarp();
+    }
+}
+
+__global__ void __launch_bounds__(32, 32) decode_sc8_kernel(const __grid_constant__ Args S) {
     const DecodeArgs& A = S.a;
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int lane = threadIdx.x;
@@ -124,7 +164,13 @@ __global__ void __launch_bounds__(32) decode_sc8_kernel(const __grid_constant__ 
 
     for (int tile = blockIdx.x; tile < S.ntiles; tile += gridDim.x) {
         const int frame = tile * 32 + lane, fr = min(frame, A.B - 1);
-        const uint32_t* y0 = S.yq + (size_t)tile * (n >> 2) * 32 + lane;
+        const uint32_t* y0 = S.yq + (size_t)(S.fused ? blockIdx.x : tile) * (n >> 2) * 32 + lane;
+        if (S.fused) {                                       // (the level region and the heap are dead between tiles: 32 x 33 words of them)
+            uint32_t* tb = reinterpret_cast<uint32_t*>(smem_raw);
+            uint32_t* slice = S.yq + (size_t)blockIdx.x * (n >> 2) * 32;
+            if (A.y_f32) quantise_tile(reinterpret_cast<const float*>(A.y), n, m, A.B, tile, (double)S.scale, slice, tb, lane);
+            else quantise_tile(reinterpret_cast<const double*>(A.y), n, m, A.B, tile, (double)S.scale, slice, tb, lane);
+        }
         sct::Walk wk;
         wk.w0 = 0; wk.uacc = 0; wk.H = H; wk.bits = S.bits + (size_t)fr * NW; wk.store = frame < A.B; wk.M = m;
         bool bad = false;
@@ -179,7 +225,10 @@ __global__ void __launch_bounds__(32) decode_sc8_kernel(const __grid_constant__ 
     }
 }
 
-static size_t smem_bytes(int n, int vs) { return (size_t)(((n >> (vs - 1)) - 8) >> 2) * 128 + (size_t)(n >> 5) * 128; }
+static size_t smem_bytes(int n, int vs) {
+    const size_t walk = (size_t)(((n >> (vs - 1)) - 8) >> 2) * 128 + (size_t)(n >> 5) * 128, transpose = 32 * 33 * 4;   // (the fused quantiser's buffer)
+    return walk > transpose ? walk : transpose;
+}
 // first shared-memory level: the smallest one that lets an SM hold 32 one-warp blocks (the hardware's limit; 6 KB per tile),
 // at most m - 5 (64 values) -- n = 1024: 115 M frames/s with 10 blocks per SM (vs 2), 138 with 32 (vs 5); n = 256: vs 2; n = 2048: vs 6
 static int first_smem_level(int m) {
@@ -228,25 +277,28 @@ cudaError_t launch_decode_sc8(const DecodeArgs& a, int qfraction, const uint32_t
                               int sm_count, cudaStream_t st) {
     const int ntiles = (a.B + 31) / 32;
     const float scale = (float)(2 << qfraction);
-    const size_t qsm = (size_t)32 * ((a.n >> 2) + 1) * 4;
-    int qpb = (int)((227 * 1024) / (qsm + 1024));             // blocks an SM holds (33 KB each at n = 1024)
-    if (qpb > 8) qpb = 8;
-    if (qpb < 1) qpb = 1;
-    int qb = ntiles < sm_count * qpb ? ntiles : sm_count * qpb;
+    const bool fused = getenv("PCB_8_PREPASS") == nullptr;     // PCB_8_PREPASS=1: the quantiser as a pass of its own (A/B, tests)
     cudaError_t e;
-    if (a.y_f32) {
-        e = cudaFuncSetAttribute(sc8::sc8_quantise_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)qsm);
+    if (!fused) {
+        const size_t qsm = (size_t)32 * ((a.n >> 2) + 1) * 4;
+        int qpb = (int)((227 * 1024) / (qsm + 1024));             // blocks an SM holds (33 KB each at n = 1024)
+        if (qpb > 8) qpb = 8;
+        if (qpb < 1) qpb = 1;
+        int qb = ntiles < sm_count * qpb ? ntiles : sm_count * qpb;
+        if (a.y_f32) {
+            e = cudaFuncSetAttribute(sc8::sc8_quantise_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)qsm);
+            if (e != cudaSuccess) return e;
+            sc8::sc8_quantise_kernel<float><<<qb, 256, qsm, st>>>((const float*)a.y, yq, a.n, a.m, a.B, ntiles, scale);
+        } else {
+            e = cudaFuncSetAttribute(sc8::sc8_quantise_kernel<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)qsm);
+            if (e != cudaSuccess) return e;
+            sc8::sc8_quantise_kernel<double><<<qb, 256, qsm, st>>>((const double*)a.y, yq, a.n, a.m, a.B, ntiles, scale);
+        }
+        e = cudaGetLastError();
         if (e != cudaSuccess) return e;
-        sc8::sc8_quantise_kernel<float><<<qb, 256, qsm, st>>>((const float*)a.y, yq, a.n, a.m, a.B, ntiles, scale);
-    } else {
-        e = cudaFuncSetAttribute(sc8::sc8_quantise_kernel<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)qsm);
-        if (e != cudaSuccess) return e;
-        sc8::sc8_quantise_kernel<double><<<qb, 256, qsm, st>>>((const double*)a.y, yq, a.n, a.m, a.B, ntiles, scale);
     }
-    e = cudaGetLastError();
-    if (e != cudaSuccess) return e;
     sc8::Args s;
-    s.a = a; s.ops = d_ops; s.nops = nops; s.yq = yq; s.glev = glev; s.bits = bits; s.ntiles = ntiles;
+    s.a = a; s.ops = d_ops; s.nops = nops; s.yq = yq; s.glev = glev; s.bits = bits; s.ntiles = ntiles; s.fused = fused ? 1 : 0; s.scale = scale;
     if (blocks > ntiles) blocks = ntiles;
     s.vs = sc8::first_smem_level(a.m);
     const size_t smem = sc8::smem_bytes(a.n, s.vs);

@@ -25,6 +25,7 @@ def test_int8_mode_equals_its_definition(oracle, n, k, q):
     for B in (1, 33, 300):
         y = 1.0 + code.sigma * rng.standard_normal((B, n))
         y[0, :8] = [0.0, -0.0, 1e9, -1e9, 0.0624, -0.0626, 127.5 / (2 << q), -1e-300]   # zeros, saturation, rounding ties
+        y[0, 8:12] = [np.nan, -127.5 / (2 << q), np.inf, -np.inf]                      # the definition sends NaN to -127
         want = oracle.decode_int8(n, q, y, code.mask)
         got = d.decode(y)
         bad = np.flatnonzero((got != want).any(axis=1))
@@ -95,3 +96,16 @@ def test_int8_mode_with_every_first_shared_memory_level(oracle, monkeypatch, n, 
     rng = np.random.default_rng(n + vs)
     y = 1.0 + code.sigma * rng.standard_normal((500, n))
     assert (d.decode(y) == oracle.decode_int8(n, 2, y, code.mask)).all()
+
+
+def test_int8_quantiser_as_a_pass_of_its_own(oracle, monkeypatch):
+    """PCB_8_PREPASS=1 runs sc8_quantise_kernel in front of the decoder instead of the tile prologue: same bits."""
+    monkeypatch.setenv("PCB_8_PREPASS", "1")
+    for n, k in ((128, 64), (1024, 512)):
+        d, code = _dec(n, k, 2)
+        rng = np.random.default_rng(n)
+        y = 1.0 + code.sigma * rng.standard_normal((333, n))
+        y[3, :4] = [np.nan, 1e9, -1e9, 0.0]
+        assert (d.decode(y) == oracle.decode_int8(n, 2, y, code.mask)).all()
+        yf = y.astype(np.float32)
+        assert (d.decode(yf) == oracle.decode_int8(n, 2, yf.astype(np.float64), code.mask)).all()
