@@ -81,6 +81,15 @@ __device__ __forceinline__ uint32_t brev_stage(uint32_t v, int lane, int s, int 
     const uint32_t y = __shfl_xor_sync(0xffffffffu, v, 1 << s);
     return ((lane >> s) & 1) ? (v & ~M) | ((y & ~M) >> D) : (v & M) | ((y & M) << D);
 }
+// the two stages that move whole bytes, as one PRMT each
+__device__ __forceinline__ uint32_t brev_stage16(uint32_t v, int lane) {      // lane bit 0 <-> position bit 4
+    const uint32_t y = __shfl_xor_sync(0xffffffffu, v, 1);
+    return __byte_perm(v, y, (lane & 1) ? 0x3276u : 0x5410u);
+}
+__device__ __forceinline__ uint32_t brev_stage8(uint32_t v, int lane) {       // lane bit 1 <-> position bit 3
+    const uint32_t y = __shfl_xor_sync(0xffffffffu, v, 2);
+    return __byte_perm(v, y, (lane & 2) ? 0x3715u : 0x6240u);
+}
 __device__ __forceinline__ int pad32(int a) { return a + (a >> 5); }      // one spare word per 32: strided rows without bank conflicts
 
 // The same encoder on packed frames: u_bits / x_bits are [B][max(n/32, 1)] words, bit t of a frame at word t / 32, bit t % 32.
@@ -106,8 +115,8 @@ __global__ void __launch_bounds__(128) encode_packed_kernel(const uint32_t* __re
             __syncwarp();
             for (int c = 0; c < S; c++) {
                 uint32_t v = W[pad32(lane * S + c)];
-                v = brev_stage(v, lane, 0, 16, 0x0000FFFFu);
-                v = brev_stage(v, lane, 1, 8, 0x00FF00FFu);
+                v = brev_stage16(v, lane);
+                v = brev_stage8(v, lane);
                 v = brev_stage(v, lane, 2, 4, 0x0F0F0F0Fu);
                 v = brev_stage(v, lane, 3, 2, 0x33333333u);
                 v = brev_stage(v, lane, 4, 1, 0x55555555u);
@@ -167,8 +176,8 @@ __global__ void __launch_bounds__(256) encode_packed_reg_kernel(const uint32_t* 
 #pragma unroll
                 for (int c = 0; c < S; c++) {
                     uint32_t w = v[k][c];
-                    w = brev_stage(w, lane, 0, 16, 0x0000FFFFu);
-                    w = brev_stage(w, lane, 1, 8, 0x00FF00FFu);
+                    w = brev_stage16(w, lane);
+                    w = brev_stage8(w, lane);
                     w = brev_stage(w, lane, 2, 4, 0x0F0F0F0Fu);
                     w = brev_stage(w, lane, 3, 2, 0x33333333u);
                     w = brev_stage(w, lane, 4, 1, 0x55555555u);
