@@ -149,14 +149,19 @@ __global__ void __launch_bounds__(128) encode_packed_kernel(const uint32_t* __re
     }
 }
 
-// n = 1024 S (S = 1, 2, 4): the frame lives in registers, lane l holds words l S .. l S + S - 1 -- exactly the operands of the
+__host__ __device__ constexpr int brev_small(int c, int bits) {
+    int r = 0;
+    for (int i = 0; i < bits; i++) r |= ((c >> i) & 1) << (bits - 1 - i);
+    return r;
+}
+// n = 1024 S (S = 1 .. 32): the frame lives in registers, lane l holds words l S .. l S + S - 1 -- exactly the operands of the
 // bit-reversal network above (word (j, c) in lane j) and of its result (word (t', brev(c)) in lane t').  The cross-word
 // stages of the transform are register XORs (distance < S) and shuffles (distance / S lanes); no shared memory, F
 // frames per warp in flight.
 template <int S, int F>
 __global__ void __launch_bounds__(256) encode_packed_reg_kernel(const uint32_t* __restrict__ u, uint32_t* __restrict__ x, int with_shuffle, int B) {
     constexpr int NW = 32 * S;
-    constexpr int LS = S == 1 ? 0 : S == 2 ? 1 : 2;
+    constexpr int LS = S == 1 ? 0 : S == 2 ? 1 : S == 4 ? 2 : S == 8 ? 3 : S == 16 ? 4 : 5;
     const int lane = threadIdx.x & 31;
     const long warp = ((long)blockIdx.x * blockDim.x + threadIdx.x) >> 5, nwarps = ((long)gridDim.x * blockDim.x) >> 5;
     for (long f0 = warp * F; f0 < B; f0 += nwarps * F) {
@@ -167,7 +172,13 @@ __global__ void __launch_bounds__(256) encode_packed_reg_kernel(const uint32_t* 
             const uint32_t* p = u + f * NW + lane * S;
             if constexpr (S == 1) v[k][0] = __ldg(p);
             else if constexpr (S == 2) { const uint2 t = __ldg(reinterpret_cast<const uint2*>(p)); v[k][0] = t.x; v[k][1] = t.y; }
-            else { const uint4 t = __ldg(reinterpret_cast<const uint4*>(p)); v[k][0] = t.x; v[k][1] = t.y; v[k][2] = t.z; v[k][3] = t.w; }
+            else {
+#pragma unroll
+                for (int q = 0; q < S / 4; q++) {
+                    const uint4 t = __ldg(reinterpret_cast<const uint4*>(p) + q);
+                    v[k][4 * q] = t.x; v[k][4 * q + 1] = t.y; v[k][4 * q + 2] = t.z; v[k][4 * q + 3] = t.w;
+                }
+            }
         }
 #pragma unroll
         for (int k = 0; k < F; k++) {
@@ -181,8 +192,7 @@ __global__ void __launch_bounds__(256) encode_packed_reg_kernel(const uint32_t* 
                     w = brev_stage(w, lane, 2, 4, 0x0F0F0F0Fu);
                     w = brev_stage(w, lane, 3, 2, 0x33333333u);
                     w = brev_stage(w, lane, 4, 1, 0x55555555u);
-                    constexpr int R4[4] = {0, 2, 1, 3};
-                    o[LS == 2 ? R4[c & 3] : c] = w;              // brev(c) over log2(S) bits (S = 2: identity)
+                    o[brev_small(c, LS)] = w;                    // brev(c) over log2(S) bits
                 }
 #pragma unroll
                 for (int c = 0; c < S; c++) v[k][c] = o[c];
@@ -208,7 +218,10 @@ __global__ void __launch_bounds__(256) encode_packed_reg_kernel(const uint32_t* 
             uint32_t* q = x + (f0 + k) * NW + lane * S;
             if constexpr (S == 1) *q = v[k][0];
             else if constexpr (S == 2) *reinterpret_cast<uint2*>(q) = make_uint2(v[k][0], v[k][1]);
-            else *reinterpret_cast<uint4*>(q) = make_uint4(v[k][0], v[k][1], v[k][2], v[k][3]);
+            else {
+#pragma unroll
+                for (int j = 0; j < S / 4; j++) reinterpret_cast<uint4*>(q)[j] = make_uint4(v[k][4 * j], v[k][4 * j + 1], v[k][4 * j + 2], v[k][4 * j + 3]);
+            }
         }
     }
 }
@@ -226,6 +239,9 @@ cudaError_t launch_encode_packed(const uint32_t* d_u, uint32_t* d_x, int n, int 
         if (n == 1024) return launch_encode_reg<1, 4>(d_u, d_x, with_shuffle, B, sm_count, st);
         if (n == 2048) return launch_encode_reg<2, 4>(d_u, d_x, with_shuffle, B, sm_count, st);
         if (n == 4096) return launch_encode_reg<4, 2>(d_u, d_x, with_shuffle, B, sm_count, st);
+        if (n == 8192) return launch_encode_reg<8, 1>(d_u, d_x, with_shuffle, B, sm_count, st);
+        if (n == 16384) return launch_encode_reg<16, 1>(d_u, d_x, with_shuffle, B, sm_count, st);
+        if (n == 32768) return launch_encode_reg<32, 1>(d_u, d_x, with_shuffle, B, sm_count, st);
     }
     const int wpb = 4;
     const int NW = n >= 32 ? n / 32 : 1;

@@ -17,7 +17,7 @@ def _pack(bits):
     return out
 
 
-@pytest.mark.parametrize("n", [8, 32, 64, 512, 1024, 2048, 4096, 32768])
+@pytest.mark.parametrize("n", [8, 32, 64, 512, 1024, 2048, 4096, 16384, 32768, 65536])
 @pytest.mark.parametrize("shuffle", [0, 1])
 def test_packed_encoder_equals_int_per_bit_encoder(n, shuffle):
     d = pb.Decoder(n, max(n // 2, 1), 0, 1, pb.SCMINSUM, device=0)
@@ -48,9 +48,9 @@ def test_device_encoder_equals_host_packed_encoder():
             assert torch.equal(y, u)
 
 
-@pytest.mark.parametrize("n", [1024, 2048, 4096])
+@pytest.mark.parametrize("n", [1024, 2048, 4096, 8192, 16384, 32768])
 def test_register_and_shared_memory_encoders_agree(n, monkeypatch):
-    """n = 1024 / 2048 / 4096 run a register-resident kernel; PCB_ENC_SMEM=1 selects the shared-memory one all other sizes use."""
+    """n = 1024 .. 32768 run a register-resident kernel; PCB_ENC_SMEM=1 selects the shared-memory one all other sizes use."""
     d = pb.Decoder(n, n // 2, 0, 1, pb.SCMINSUM, device=0)
     rng = np.random.default_rng(n)
     u = rng.integers(0, 2 ** 32, size=(1001, n // 32), dtype=np.uint64).astype(np.uint32)
