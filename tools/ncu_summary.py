@@ -1,5 +1,5 @@
 #!/usr/bin/env python
-"""Print the handful of ncu raw-page metrics this project tracks. usage: ncu_summary.py <rep> [frames]"""
+"""Print the handful of ncu raw-page metrics this project tracks. usage: ncu_summary.py <rep> [frames] [launch index, default 0]"""
 import csv
 import subprocess
 import sys
@@ -8,7 +8,7 @@ rep = sys.argv[1]
 frames = int(sys.argv[2]) if len(sys.argv) > 2 else 0
 out = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
 rows = list(csv.reader(out.splitlines()))
-hdr, units, vals = rows[0], rows[1], rows[2]
+hdr, units, vals = rows[0], rows[1], rows[2 + (int(sys.argv[3]) if len(sys.argv) > 3 else 0)]
 d = {h: (v, u) for h, u, v in zip(hdr, units, vals)}
 keys = ["Kernel Name", "gpu__time_duration.sum", "launch__registers_per_thread", "launch__grid_size", "launch__block_size",
         "launch__shared_mem_per_block_dynamic", "launch__occupancy_limit_shared_mem", "launch__occupancy_limit_registers",
