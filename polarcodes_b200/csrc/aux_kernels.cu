@@ -326,8 +326,20 @@ __global__ void __launch_bounds__(128) generate_kernel(GenArgs G) {
         if (G.tx_bits) {   // what the decoder output is compared with
             const int TW = G.tx_words;
             uint32_t* tx = G.tx_bits + (size_t)f * TW;
-            if (G.tx_is_u) {
-                // u in natural index order: undo the shuffle on the fly
+            if (G.tx_is_u && G.with_shuffle && m >= 10 && TW == NW) {
+                // u in natural index order: the shuffle is an involution, the network of the packed encoder undoes it
+                const int S = NW >> 5, sb = m - 10;
+                for (int c = 0; c < S; c++) {
+                    uint32_t v = W[lane * S + c];
+                    v = brev_stage16(v, lane);
+                    v = brev_stage8(v, lane);
+                    v = brev_stage(v, lane, 2, 4, 0x0F0F0F0Fu);
+                    v = brev_stage(v, lane, 3, 2, 0x33333333u);
+                    v = brev_stage(v, lane, 4, 1, 0x55555555u);
+                    tx[lane * S + (sb ? (int)(__brev((unsigned)c) >> (32 - sb)) : 0)] = v;
+                }
+            } else if (G.tx_is_u) {
+                // (n < 1024) bit by bit
                 for (int w = lane; w < TW; w += 32) {
                     uint32_t v = 0;
                     if (!G.with_shuffle) v = W[w];
