@@ -476,14 +476,15 @@ def main():
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * elapsed / args.steps,
             "timed_region_s": elapsed,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": workload_config(args.crc),
+            "config": {**workload_config(args.crc), "frames_per_step_per_gpu": B,
+                       "l2": f"inputs larger than L2: {B * N * 8 / 2**30:.0f} GiB of channel values per step and GPU, every frame read once per step; no flush needed"},
             "setup": {"frames_per_step_per_gpu": B,
                       "input": f"double y[B][n] resident in HBM ({B * N * 8 / 2**30:.0f} GiB/step > L2, no flush needed)",
                       "step": "pcb_decode_batch_dev + pcb_count_errors_dev" + (" (ncclAllReduce of the 3 counters inside)" if world > 1 else ""),
                       "collectives_per_step": 1 if world > 1 else 0, "launch": info},
             "roofline": {"bound": "alu", "achieved": ach, "peak": peak_lane, "unit": "Tlane-op/s", "frac": ach / peak_lane,
                          "traffic": traffic, "traffic_source": traffic_src, "lane_ops_per_frame": ops, "kernel_ms": kms,
-                         "kernel_ms_covers": "scl8_prepass + decode_scl8q + decode_generic (empty redo list), CUDA events on the launch stream",
+                         "kernel_ms_covers": "decode_scl8q (narrowing and range check in its prologue) + scl_select + decode_generic (empty redo list), CUDA events on the launch stream",
                          "peak_source": f"{info['sm_count']} SMs x 128 fp32/int lanes x {sm_max:.0f} MHz (SURVEY.md §8(d)); no tensor/HBM bound applies",
                          "executed": executed,
                          "hbm": {"algorithmic_GBps": hbm_bytes / (kms * 1e-3) / 1e9, "peak_GBps": peaks.get("hbm_gbs"),
