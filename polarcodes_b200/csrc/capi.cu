@@ -50,11 +50,11 @@ cudaError_t launch_decode_sct(const DecodeArgs& a, const uint32_t* d_ops, int no
 // 8-bit min-sum SC, four LLRs per register (decode_sc8.cu; PCB_PREC_INT8)
 bool sc8_supported(int m);
 size_t sc8_yq_bytes(int n, int B);
-cudaError_t sc8_occupancy(int m, int* bps, size_t* smem);
+cudaError_t sc8_occupancy(int m, int* bps, size_t* smem, int* vs);
 int sc8_build_ops(int n, int m, const uint32_t* info_w, const uint32_t* fv_w, uint32_t* ops_out, int cap);
-size_t sc8_glev_bytes(int n, int blocks);
+size_t sc8_glev_bytes(int n, int blocks, int vs);
 cudaError_t launch_decode_sc8(const DecodeArgs& a, int qfraction, const uint32_t* d_ops, int nops, uint32_t* yq, uint32_t* glev, uint32_t* bits, int blocks,
-                              int sm_count, cudaStream_t st);
+                              int sm_count, int vs, cudaStream_t st);
 // lane-per-path list kernel, 32 / L frames per warp (decode_scl8q.cu): L = 8 and L = 32
 bool scl8q_supported(int m, int L);
 int scl8q_frames_per_warp(int L);
@@ -175,6 +175,7 @@ struct pcb_handle {
     bool sc8 = false;               // decoder 2 in PCB_PREC_INT8: decode_sc8.cu
     int qfrac = 0, sc8_bps = 0, sc8_nops = 0;
     size_t sc8_smem = 0, yq_cap = 0;
+    int sc8_vs = 2;
     uint32_t *d_sc8_ops = nullptr, *d_yq = nullptr, *d_sc8_glev = nullptr;
     bool sct = false;               // SC decoders: tile-per-block kernel (decode_sct.cu) instead of sc32
     int sct_bps = 0, sct_nops = 0, sct_npops = 0, sct_W = 4, sct_vs = 2;
@@ -273,7 +274,7 @@ static int configure(pcb_handle* h) {
     }
     h->sc8 = h->decoder == 2 && h->precision == PCB_PREC_INT8;
     if (h->sc8) {
-        if (!sc8_supported(h->m) || sc8_occupancy(h->m, &h->sc8_bps, &h->sc8_smem) != cudaSuccess || h->sc8_bps == 0) {
+        if (!sc8_supported(h->m) || sc8_occupancy(h->m, &h->sc8_bps, &h->sc8_smem, &h->sc8_vs) != cudaSuccess || h->sc8_bps == 0) {
             cudaGetLastError();
             return fail(PCB_EINVAL, "PCB_PREC_INT8 needs n in [64, 4096]");
         }
@@ -582,7 +583,7 @@ int pcb_info(pcb_handle* h, int* sm_count, int* warps_per_block, int* blocks, in
         if (warps_per_block) *warps_per_block = 1;
         if (blocks) *blocks = h->sm_count * h->sc8_bps;
         if (smem_per_block) *smem_per_block = (int)h->sc8_smem;
-        if (first_smem_layer) *first_smem_layer = 1;
+        if (first_smem_layer) *first_smem_layer = h->sc8_vs;
         if (kernel_launches) *kernel_launches = h->launches;
         return PCB_OK;
     }
@@ -736,10 +737,10 @@ static cudaError_t launch(pcb_handle* h, const DecodeArgs& a, cudaStream_t st, b
         uint32_t* bits = a.sol_bits ? a.sol_bits : h->d_sc32_bits;
         h->launches++;                        // quantiser + decoder
         if (!h->d_sc8_glev) {
-            cudaError_t e0 = cudaMalloc(&h->d_sc8_glev, sc8_glev_bytes(h->n, h->sm_count * h->sc8_bps));
+            cudaError_t e0 = cudaMalloc(&h->d_sc8_glev, sc8_glev_bytes(h->n, h->sm_count * h->sc8_bps, h->sc8_vs));
             if (e0 != cudaSuccess) return e0;
         }
-        cudaError_t e = launch_decode_sc8(a, h->qfrac, h->d_sc8_ops, h->sc8_nops, h->d_yq, h->d_sc8_glev, bits, h->sm_count * h->sc8_bps, h->sm_count, st);
+        cudaError_t e = launch_decode_sc8(a, h->qfrac, h->d_sc8_ops, h->sc8_nops, h->d_yq, h->d_sc8_glev, bits, h->sm_count * h->sc8_bps, h->sm_count, h->sc8_vs, st);
         if (e != cudaSuccess) return e;
         if (a.sol) return launch_sc_expand(bits, a.sol, (size_t)a.B * h->n, h->sm_count, st);
         return cudaSuccess;

@@ -245,15 +245,13 @@ static int first_smem_level(int m) {
 
 bool sc8_supported(int m) { return m >= 6 && m <= 12; }
 size_t sc8_yq_bytes(int n, int B) { return (size_t)((B + 31) / 32) * 32 * (size_t)n; }
-size_t sc8_glev_bytes(int n, int blocks) {
-    int m = 0;
-    while ((1 << m) < n) m++;
-    return (size_t)blocks * ((n - (n >> (sc8::first_smem_level(m) - 1))) >> 2) * 128;
-}
+size_t sc8_glev_bytes(int n, int blocks, int vs) { return (size_t)blocks * ((n - (n >> (vs - 1))) >> 2) * 128; }
 
-cudaError_t sc8_occupancy(int m, int* bps, size_t* smem) {
+// vs: the first shared-memory level chosen for this code length (the handle keeps it: slice size and launch must agree)
+cudaError_t sc8_occupancy(int m, int* bps, size_t* smem, int* vs) {
     const int n = 1 << m;
-    *smem = sc8::smem_bytes(n, sc8::first_smem_level(m));
+    *vs = sc8::first_smem_level(m);
+    *smem = sc8::smem_bytes(n, *vs);
     if (*smem > 227 * 1024) { *bps = 0; return cudaSuccess; }
     cudaError_t e = cudaFuncSetAttribute(sc8::decode_sc8_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)*smem);
     if (e != cudaSuccess) return e;
@@ -274,7 +272,7 @@ int sc8_build_ops(int n, int m, const uint32_t* info_w, const uint32_t* fv_w, ui
 
 // a: y / y_f32 / B; qfraction: the scale is 2 << qfraction; yq: sc8_yq_bytes of scratch; bits: [B][n/32]
 cudaError_t launch_decode_sc8(const DecodeArgs& a, int qfraction, const uint32_t* d_ops, int nops, uint32_t* yq, uint32_t* glev, uint32_t* bits, int blocks,
-                              int sm_count, cudaStream_t st) {
+                              int sm_count, int vs, cudaStream_t st) {
     const int ntiles = (a.B + 31) / 32;
     const float scale = (float)(2 << qfraction);
     const bool fused = getenv("PCB_8_PREPASS") == nullptr;     // PCB_8_PREPASS=1: the quantiser as a pass of its own (A/B, tests)
@@ -300,7 +298,7 @@ cudaError_t launch_decode_sc8(const DecodeArgs& a, int qfraction, const uint32_t
     sc8::Args s;
     s.a = a; s.ops = d_ops; s.nops = nops; s.yq = yq; s.glev = glev; s.bits = bits; s.ntiles = ntiles; s.fused = fused ? 1 : 0; s.scale = scale;
     if (blocks > ntiles) blocks = ntiles;
-    s.vs = sc8::first_smem_level(a.m);
+    s.vs = vs;
     const size_t smem = sc8::smem_bytes(a.n, s.vs);
     e = cudaFuncSetAttribute(sc8::decode_sc8_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
